@@ -1,0 +1,256 @@
+/*
+ * rtcore.h — C ABI of the B200-native path-tracing core (librtcore.so).
+ *
+ * Drop-in boundary for the one data-parallel hot path of calvin-godfrey/RustRaytracer
+ * (SURVEY.md §8b).  The reference has no FFI of its own; these entry points sit directly
+ * behind the Rust items its render driver and scene code call, and are what a Rust
+ * `extern "C"` shim would bind.  Each entry point cites the reference
+ * item it replaces as `file:line` relative to the reference's `src/`.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; all host arrays are borrowed for the duration of the call;
+ *   - every function returns an rt_status (0 = OK); the message of the last failure on the
+ *     calling thread is available from rt_last_error_string(); nothing unwinds across the ABI;
+ *   - all arithmetic inputs are f64, as in the reference; indices are uint32_t with
+ *     RT_NONE (0xFFFFFFFF) standing for the reference's `usize::MAX` sentinel;
+ *   - there is NO CPU fallback: every compute entry point fails with RT_ERR_CUDA when no
+ *     CUDA device is usable.
+ */
+#ifndef RTCORE_H
+#define RTCORE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_NONE 0xFFFFFFFFu
+
+typedef int32_t rt_status;
+enum {
+    RT_OK = 0,
+    RT_ERR_INVALID = 1,     /* bad argument / inconsistent scene tables            */
+    RT_ERR_CUDA = 2,        /* CUDA runtime error or no device                      */
+    RT_ERR_STATE = 3,       /* call order (e.g. render before commit)               */
+    RT_ERR_CANCELLED = 4,   /* rt_render stopped by rt_render_cancel                */
+    RT_ERR_IO = 5           /* file could not be read / parsed (host scene layer)   */
+};
+
+/* ---------------------------------------------------------------- scene tables
+ * Mirror of `struct Objects { meshes, objs, lights, materials, textures, node }`
+ * (geometry.rs:13-21).  Cross indices keep the reference's meaning.               */
+
+/* `enum Primitive` (primitive.rs:10-61).  FlipFace{obj} is the `flip_face` flag on the
+ * wrapped primitive (it only toggles `front` and negates the sampled normal,
+ * primitive.rs:300-310,533-537).                                                     */
+enum { RT_PRIM_SPHERE = 0, RT_PRIM_TRIANGLE = 1, RT_PRIM_XY_RECT = 2, RT_PRIM_XZ_RECT = 3, RT_PRIM_YZ_RECT = 4 };
+
+typedef struct rt_primitive {
+    uint32_t type;         /* RT_PRIM_*                                                     */
+    uint32_t flip_face;    /* 1 = wrapped in Primitive::FlipFace                            */
+    uint32_t mat_index;    /* index into materials                                          */
+    uint32_t light_index;  /* index into lights, RT_NONE = not emissive (usize::MAX)        */
+    uint32_t mesh_index;   /* triangle: mesh                                                */
+    uint32_t ind;          /* triangle: offset of its first index in mesh.ind (multiple of 3) */
+    uint32_t transform;    /* rect: index into transforms, RT_NONE = None                   */
+    uint32_t _pad;
+    double   v[5];         /* sphere: cx,cy,cz,r,-   rect: a0,b0,a1,b1,k  (xy: x0,y0,x1,y1,k;
+                              xz: x0,z0,x1,z1,k; yz: y0,z0,y1,z1,k)                        */
+} rt_primitive;
+
+/* `enum Texture` (material.rs:520-539) */
+enum { RT_TEX_SOLID = 0, RT_TEX_CHECKERED = 1 };
+typedef struct rt_texture {
+    uint32_t type;
+    uint32_t odd, even;    /* checkered: texture ids (material.rs:528-532)                  */
+    uint32_t _pad;
+    double   color[3];     /* solid colour                                                  */
+    double   frequency;    /* checkered                                                     */
+} rt_texture;
+
+/* `enum Material` (material.rs:17-73); Disney is out of scope. */
+enum { RT_MAT_MATTE = 0, RT_MAT_LIGHT = 1, RT_MAT_PLASTIC = 2, RT_MAT_GLASS = 3, RT_MAT_METAL = 4, RT_MAT_MIRROR = 5 };
+typedef struct rt_material {
+    uint32_t type;
+    uint32_t remap_roughness;
+    /* texture ids:  Matte {k_d}            Light {texture}      Plastic {k_d,k_s}
+     *               Glass {k_r,k_t}        Mirror {color}
+     *               Metal {eta,k,rough,urough,vrough}  (urough/vrough may be RT_NONE)      */
+    uint32_t tex[5];
+    uint32_t _pad;
+    /* scalars:      Matte {sigma}   Plastic {roughness}   Glass {u_roughness,v_roughness,index} */
+    double   f[3];
+} rt_material;
+
+/* `enum Light` (light.rs:30-80); only Diffuse (area) lights are reachable from the five
+ * benchmark configurations.                                            */
+enum { RT_LIGHT_DIFFUSE = 0 };
+typedef struct rt_light {
+    uint32_t type;
+    uint32_t prim_index;   /* the emitting primitive (light.rs:62)                          */
+    uint32_t two_sided;
+    uint32_t _pad;
+    double   color[3];
+    /* `area` (light.rs:63) is derived from the primitive at commit (primitive.rs:339-359)  */
+} rt_light;
+
+/* `struct Camera` (geometry.rs:95-108) */
+typedef struct rt_camera {
+    double origin[3];
+    double upper_left_corner[3];
+    double horizontal_offset[3];
+    double vertical_offset[3];
+    double u[3], v[3], w[3];
+    double lens_radius, t0, t1;
+} rt_camera;
+
+/* `struct Ray` (geometry.rs:211-236): direction is NOT normalised, t is in units of |dir|. */
+typedef struct rt_ray {
+    double origin[3];
+    double dir[3];
+} rt_ray;
+
+/* The fields of `HitRecord` (hittable.rs:51-72) the path integrator consumes.
+ * prim_index == RT_NONE encodes `Option::None`.                                     */
+typedef struct rt_hit {
+    double   t;
+    double   p[3];
+    double   n[3];          /* geometric normal after set_front (hittable.rs:186-189)        */
+    double   ns[3];         /* shading.n                                                     */
+    double   uv[2];
+    uint32_t prim_index;
+    uint32_t front;         /* HitRecord::front (after FlipFace toggling)                    */
+} rt_hit;
+
+/* one `Visibility{p0,p1}` query (hittable.rs:15-40) */
+typedef struct rt_shadow_query {
+    double   p0[3];
+    double   p1[3];
+    uint32_t p1_prim_index; /* p1.prim_index                                                 */
+    uint32_t infinite_light;
+} rt_shadow_query;
+
+/* `IntType::Path{max_depth, invisible_light}` (integrator.rs:37-40) */
+enum { RT_INTEGRATOR_PATH = 0 };
+typedef struct rt_integrator_desc {
+    uint32_t kind;
+    uint32_t max_depth;
+    uint32_t invisible_light;
+    uint32_t _pad;
+} rt_integrator_desc;
+
+/* What `GLOBAL_STATE` width/height/spp (main.rs:74-88) and the tile/sample partition of
+ * render.rs carry.  spp is used as given: the caller applies next_power_of_two
+ * (sampler.rs:637-640) — rt_round_spp() does it.                                      */
+typedef struct rt_film_desc {
+    uint32_t width, height;
+    uint32_t sample_begin, sample_end;   /* samples [begin,end) of every pixel in the window */
+    uint32_t x0, y0, x1, y1;             /* pixel window [x0,x1) x [y0,y1) (a tile, or the image) */
+    uint64_t seed;                       /* counter-based RNG key                            */
+} rt_film_desc;
+
+typedef struct rt_counters {
+    uint64_t paths;          /* camera samples generated                                     */
+    uint64_t extend_rays;    /* ray type A: get_intersection in li (integrator.rs:388)       */
+    uint64_t shadow_rays;    /* ray type B: Visibility::unoccluded (integrator.rs:584)       */
+    uint64_t probe_rays;     /* ray type C: MIS BSDF probe (integrator.rs:615)               */
+    uint64_t iterations;     /* wavefront iterations                                         */
+    double   render_ms;      /* device time of the last rt_render (CUDA events)              */
+    double   traverse_ms;    /* device time inside extend + connect kernels                  */
+} rt_counters;
+
+typedef struct rt_scene rt_scene;
+typedef struct rt_film rt_film;
+
+/* ---------------------------------------------------------------- library */
+const char* rt_last_error_string(void);
+const char* rt_version_string(void);
+/* number of usable CUDA devices (0 ⇒ every compute call fails with RT_ERR_CUDA) */
+int32_t     rt_device_count(void);
+rt_status   rt_set_device(int32_t device);
+uint32_t    rt_round_spp(uint32_t spp);                      /* sampler.rs:637-640 */
+
+/* Camera::new_motion_blur (geometry.rs:133-175) */
+rt_status rt_camera_look_at(const double from[3], const double to[3], const double up[3],
+                            double aspect_ratio, double vfov, double aperture, double focus_dist,
+                            double t0, double t1, rt_camera* out);
+
+/* ---------------------------------------------------------------- scene build
+ * Replaces the `get_objects_mut()` pushes of scenes.rs and the final
+ * `objects.node = BvhNode::new(..)` (e.g. scenes.rs:368-371).                        */
+rt_status rt_scene_create(rt_scene** out);
+rt_status rt_scene_destroy(rt_scene* scene);                 /* geometry.rs:42-55 clear_objects */
+
+/* objects.meshes.push(Mesh{ind,p,n,uv}) (hittable.rs:242-250).  normals / uvs may be NULL
+ * (n_normals / n_uvs = 0).  Positions are already transformed (parser.rs:29,45).       */
+rt_status rt_scene_add_mesh(rt_scene* scene, uint64_t n_points, const double* points_xyz,
+                            uint64_t n_normals, const double* normals_xyz,
+                            uint64_t n_uvs, const double* uvs,
+                            uint64_t n_indices, const uint32_t* indices, uint32_t* mesh_index_out);
+/* rect transforms: a row-major 4x4 `Projective3` (primitive.rs:36,46,56) */
+rt_status rt_scene_add_transform(rt_scene* scene, const double m_row_major[16], uint32_t* index_out);
+/* objects.objs.push / extend */
+rt_status rt_scene_add_primitives(rt_scene* scene, uint64_t n, const rt_primitive* prims, uint32_t* first_index_out);
+/* Mesh::generate_triangles (hittable.rs:257-288) + objs.extend: one Triangle per face */
+rt_status rt_scene_add_mesh_triangles(rt_scene* scene, uint32_t mesh_index, uint32_t mat_index, uint32_t* first_index_out);
+/* Primitive::set_light_index (primitive.rs:318-337) */
+rt_status rt_scene_set_light_index(rt_scene* scene, uint32_t prim_index, uint32_t light_index);
+rt_status rt_scene_set_textures(rt_scene* scene, uint64_t n, const rt_texture* textures);
+rt_status rt_scene_set_materials(rt_scene* scene, uint64_t n, const rt_material* materials);
+rt_status rt_scene_set_lights(rt_scene* scene, uint64_t n, const rt_light* lights);
+/* Builds the acceleration structure, flattens every table to its SoA device layout and
+ * uploads it to the current device.  ⇔ BvhNode::new (hittable.rs:637-723).            */
+rt_status rt_scene_commit(rt_scene* scene);
+rt_status rt_scene_num_primitives(const rt_scene* scene, uint64_t* out);
+/* bytes of device memory held by the committed scene: nodes, leaf slots, tables */
+rt_status rt_scene_device_bytes(const rt_scene* scene, uint64_t* nodes, uint64_t* leaves, uint64_t* tables);
+
+/* ---------------------------------------------------------------- intersection
+ * geometry::get_intersection(&Ray) -> Option<HitRecord> (geometry.rs:238-240):
+ * closest hit in (SMALL, INFINITY) over the whole scene.  Host buffers.               */
+rt_status rt_intersect(rt_scene* scene, uint64_t n, const rt_ray* rays, rt_hit* hits);
+/* same, caller-chosen [tmin,tmax] ⇔ BvhNode::intersects(ray,tmin,tmax,0) (hittable.rs:591) */
+rt_status rt_intersect_range(rt_scene* scene, uint64_t n, const rt_ray* rays, double tmin, double tmax, rt_hit* hits);
+/* device-resident variant: `rays`/`hits` are device pointers on the scene's device; the
+ * launch is enqueued on `cuda_stream` (a cudaStream_t, NULL = default) and not synchronised. */
+rt_status rt_intersect_device(rt_scene* scene, uint64_t n, const rt_ray* d_rays, double tmin, double tmax,
+                              rt_hit* d_hits, void* cuda_stream);
+/* closest-hit ids only (prim_index, t): 16 bytes per ray out — the ray-cast sweep entry */
+rt_status rt_closest_device(rt_scene* scene, uint64_t n, const rt_ray* d_rays, double tmin, double tmax,
+                            uint32_t* d_prim, double* d_t, void* cuda_stream);
+/* Visibility::unoccluded(infinite_light) -> bool (hittable.rs:25-39).  Host buffers.   */
+rt_status rt_occluded(rt_scene* scene, uint64_t n, const rt_shadow_query* queries, uint8_t* unoccluded_out);
+rt_status rt_occluded_device(rt_scene* scene, uint64_t n, const rt_shadow_query* d_queries,
+                             uint8_t* d_unoccluded_out, void* cuda_stream);
+
+/* ---------------------------------------------------------------- render
+ * Film = the reference's `Vec<Vec<(f64,f64,f64,u32)>>` running sums (render.rs:18-22),
+ * flattened row-major as 4 doubles (r,g,b,n) per pixel, pixel (0,0) = upper-left.      */
+rt_status rt_film_create(uint32_t width, uint32_t height, rt_film** out);
+/* film over caller-owned DEVICE memory of width*height*4 doubles (e.g. a torch tensor, so
+ * that the multi-GPU sum can be an NCCL all-reduce on that tensor)                     */
+rt_status rt_film_create_external(uint32_t width, uint32_t height, void* device_rgba_f64, rt_film** out);
+rt_status rt_film_destroy(rt_film* film);
+rt_status rt_film_clear(rt_film* film);
+/* util::thread_safe_* read side (util.rs:300-371): copy sums to host                   */
+rt_status rt_film_read(rt_film* film, double* host_rgba);
+/* point_to_color (util.rs:441-471) on the device: (sum/n) -> ACES approx -> gamma -> u8 */
+rt_status rt_film_resolve_rgb8(rt_film* film, uint8_t* host_rgb);
+
+/* render::tile_multithread / Integrator::render / single_sample
+ * (render.rs:13, integrator.rs:336-369): adds `sample_end-sample_begin` samples for
+ * every pixel of the window to `film`.  Blocking.                                     */
+rt_status rt_render(rt_scene* scene, const rt_camera* camera, const rt_integrator_desc* integrator,
+                    const rt_film_desc* desc, rt_film* film);
+/* GLOBAL_STATE.stop_render (main.rs:75,317-318; render.rs:93) */
+rt_status rt_render_cancel(rt_scene* scene);
+rt_status rt_get_counters(const rt_scene* scene, rt_counters* out);
+/* size of the wavefront (paths in flight); default 1<<22 */
+rt_status rt_set_wavefront_size(rt_scene* scene, uint32_t paths);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTCORE_H */

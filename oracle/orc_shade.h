@@ -1,0 +1,672 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see orc_math.h).  PARITY UNPINNED.
+// L1/L2 of the reference: textures, materials, BSDF/BxDF lobes, microfacets, area lights,
+// the MIS path integrator.  Quirks listed in SURVEY.md §8.1 are reproduced on purpose.
+#pragma once
+#include "orc_geom.h"
+
+namespace orc {
+
+// ------------------------------------------------------------------ bxdf.rs:12-68 local-frame helpers
+inline double cos_theta(const V3& v) { return v.z; }
+inline double cos_sq_theta(const V3& v) { return v.z * v.z; }
+inline double abs_cos_theta(const V3& v) { return std::fabs(v.z); }
+inline double sin_sq_theta(const V3& v) { return rmax(0., 1. - cos_sq_theta(v)); }
+inline double sin_theta(const V3& v) { return std::sqrt(sin_sq_theta(v)); }
+inline double tan_theta(const V3& v) { return sin_theta(v) / cos_theta(v); }
+inline double tan_sq_theta(const V3& v) { return sin_sq_theta(v) / cos_sq_theta(v); }
+inline double cos_phi(const V3& v) { double s = sin_theta(v); return s == 0. ? 1. : clampd(v.x / s, -1., 1.); }
+inline double sin_phi(const V3& v) { double s = sin_theta(v); return s == 0. ? 1. : clampd(v.y / s, -1., 1.); }
+inline double cos_sq_phi(const V3& v) { return cos_phi(v) * cos_phi(v); }
+inline double sin_sq_phi(const V3& v) { return sin_phi(v) * sin_phi(v); }
+inline bool matches_flags(uint8_t flag, uint8_t other) { return (flag & other) == flag; }
+inline bool same_hemisphere(const V3& v, const V3& w) { return v.z * w.z > 0.; }           // util.rs:591-593
+inline V3 reflect(const V3& v, const V3& n) { double s = 2. * dot(v, n); return -v + n * s; }  // util.rs:203-206
+// util.rs:376-385
+inline bool refract(const V3& vec, const V3& n, double eta, V3& out) {
+    double cos_theta_i = dot(n, vec) / norm(vec);
+    double sin2_theta_i = rmax(0., 1. - cos_theta_i * cos_theta_i);
+    double sin2_theta_t = eta * eta * sin2_theta_i;
+    if (sin2_theta_t >= 1.) return false;
+    double cos_theta_t = std::sqrt(1. - sin2_theta_t);
+    out = eta * (-vec) + (eta * cos_theta_i - cos_theta_t) * V3(n.x, n.y, n.z);
+    return true;
+}
+
+// bxdf.rs:113-136
+inline double fr_dielectric(double cos_theta_i, double eta_i, double eta_t) {
+    cos_theta_i = clampd(cos_theta_i, -1., 1.);
+    double index_i = eta_i, index_t = eta_t;
+    if (cos_theta_i < 0.) { index_i = eta_t; index_t = eta_i; cos_theta_i = std::fabs(cos_theta_i); }
+    double sin_theta_i = std::sqrt(rmax(0., 1. - cos_theta_i * cos_theta_i));
+    double sin_theta_t = index_i / index_t * sin_theta_i;
+    double cos_theta_t = std::sqrt(rmax(0., 1. - sin_theta_t * sin_theta_t));
+    if (sin_theta_t >= 1.) return 1.;
+    double r_parl = ((index_t * cos_theta_i) - (index_i * cos_theta_t)) / ((index_t * cos_theta_i) + (index_i * cos_theta_t));
+    double r_perp = ((index_i * cos_theta_i) - (index_t * cos_theta_t)) / ((index_i * cos_theta_i) + (index_t * cos_theta_t));
+    return (r_parl * r_parl + r_perp * r_perp) / 2.;
+}
+// bxdf.rs:141-170
+inline V3 fr_conductor(double cos_theta_i, const V3& eta, const V3& eta_k) {
+    cos_theta_i = clampd(cos_theta_i, -1., 1.);
+    double c2 = cos_theta_i * cos_theta_i, s2 = 1. - c2;
+    V3 eta2 = cmul(eta, eta), etak2 = cmul(eta_k, eta_k);
+    V3 t0 = (eta2 - etak2) - V3(s2, s2, s2);
+    V3 a2pb2 = cmul(t0, t0) + cmul(eta2, etak2) * 4.;
+    a2pb2 = V3(std::sqrt(a2pb2.x), std::sqrt(a2pb2.y), std::sqrt(a2pb2.z));
+    V3 t1 = a2pb2 + V3(c2, c2, c2);
+    V3 a = (a2pb2 + t0) * 0.5;
+    a = V3(std::sqrt(a.x), std::sqrt(a.y), std::sqrt(a.z));
+    V3 t2 = a * (2. * cos_theta_i);
+    V3 rs = cdiv(t1 - t2, t1 + t2);
+    V3 t3 = a2pb2 * c2 + V3(s2 * s2, s2 * s2, s2 * s2);
+    V3 t4 = t2 * s2;
+    V3 rp = cmul(rs, cdiv(t3 - t4, t3 + t4));
+    return (rp + rs) * 0.5;
+}
+// Fresnel::evaluate (bxdf.rs:190-211): the dielectric arm passes (|cos|, eta_t, eta_i) — swapped
+inline V3 fresnel_evaluate(const Fresnel& f, double cos_theta_i) {
+    switch (f.kind) {
+        case F_DIELECTRIC: { double v = fr_dielectric(std::fabs(cos_theta_i), f.eta_t, f.eta_i); return V3(v, v, v); }
+        case F_CONDUCTOR: return fr_conductor(std::fabs(cos_theta_i), f.eta, f.k);
+        default: return white();
+    }
+}
+
+// ------------------------------------------------------------------ microfacet.rs (TrowbridgeReitz, Empty)
+inline double mfd_d(const Mfd& m, const V3& wh) {                       // microfacet.rs:53-68
+    if (m.empty) return 0.;
+    double t2 = tan_sq_theta(wh);
+    if (t2 == INFINITY) return 0.;
+    double cos4 = cos_sq_theta(wh) * cos_sq_theta(wh);
+    double e = (cos_sq_phi(wh) / (m.alpha_x * m.alpha_x) + sin_sq_phi(wh) / (m.alpha_y * m.alpha_y)) * t2;
+    return 1. / (PI * m.alpha_x * m.alpha_y * cos4 * (1. + e) * (1. + e));
+}
+inline double mfd_lambda(const Mfd& m, const V3& w) {                   // microfacet.rs:109-123
+    if (m.empty) return 0.;
+    double att = std::fabs(tan_theta(w));
+    if (att == INFINITY) return 0.;
+    double alpha = std::sqrt(cos_sq_phi(w) * m.alpha_x * m.alpha_x + sin_sq_phi(w) * m.alpha_y * m.alpha_y);
+    double a2t2 = (alpha * att) * (alpha * att);
+    return (-1. + std::sqrt(1. + a2t2)) / 2.;
+}
+inline double mfd_g1(const Mfd& m, const V3& w) { return 1. / (1. + mfd_lambda(m, w)); }                 // :143-145
+inline double mfd_g(const Mfd& m, const V3& wo, const V3& wi) { return 1. / (1. + mfd_lambda(m, wo) + mfd_lambda(m, wi)); }  // :151-155
+inline double mfd_pdf(const Mfd& m, const V3& wo, const V3& wh) {       // microfacet.rs:159-172
+    if (!m.empty) return mfd_d(m, wh) * mfd_g1(m, wo) * std::fabs(dot(wo, wh)) / abs_cos_theta(wo);
+    return mfd_d(m, wh) * abs_cos_theta(wh);
+}
+inline double tr_roughness_to_alpha(double roughness) {                 // microfacet.rs:442-446
+    roughness = rmax(roughness, 1e-5);
+    double x = std::log(roughness);
+    return 1.62142 + 0.819955 * x + 0.1734 * x * x + 0.0171201 * x * x * x + 0.000640711 * x * x * x * x;
+}
+inline Mfd make_trowbridge_reitz(double ax, double ay) { Mfd m; m.empty = false; m.alpha_x = rmax(ax, 1e-3); m.alpha_y = rmax(ay, 1e-3); return m; }  // :340-348
+inline V2 tr_sample_11(double cos_t, double u1, double u2) {            // microfacet.rs:469-512
+    if (cos_t > 0.9999) {
+        double r = std::sqrt(u1 / (1. - u1)), phi = 2. * PI * u2;
+        return V2(r * std::cos(phi), r * std::sin(phi));
+    }
+    double sin_t = rmax(0., std::sqrt(1. - cos_t * cos_t));
+    double tan_t = sin_t / cos_t;
+    double a = 1. / tan_t;
+    double g1 = 2. / (1. + std::sqrt(1. + 1. / (a * a)));
+    a = 2. * u1 / g1 - 1.;
+    double tmp = 1. / (a * a - 1.);
+    if (tmp > 1e10) tmp = 1e10;
+    double b = tan_t;
+    double d = std::sqrt(rmax(0., b * b * tmp * tmp - (a * a - b * b) * tmp));
+    double sx1 = b * tmp - d, sx2 = b * tmp + d;
+    double slope_x = (a < 0. || sx2 > 1. / tan_t) ? sx1 : sx2;
+    double s, nu2;
+    if (u2 > 0.5) { s = 1.; nu2 = 2. * (u2 - 0.5); } else { s = -1.; nu2 = 2. * (0.5 - u2); }
+    double z = (nu2 * (nu2 * (nu2 * 0.27385 - 0.73369) + 0.46341)) / (nu2 * (nu2 * (nu2 * 0.093073 + 0.309420) - 1.) + 0.597999);
+    double slope_y = s * z * std::sqrt(1. + slope_x * slope_x);
+    return V2(slope_x, slope_y);
+}
+inline V3 tr_sample(const V3& wi, double ax, double ay, double u1, double u2) {  // microfacet.rs:448-467
+    V3 wi_s = normalize(V3(ax * wi.x, ay * wi.y, wi.z));
+    V2 slope = tr_sample_11(cos_theta(wi_s), u1, u2);
+    double sx = slope.x, sy = slope.y;
+    double sp = sin_phi(wi_s), cp = cos_phi(wi_s);
+    double tmp = cp * sx - sp * sy;
+    sy = sp * sx + cp * sy;
+    sx = tmp;
+    sx = ax * sx; sy = ay * sy;
+    return normalize(V3(-sx, -sy, 1.));
+}
+inline V3 mfd_sample_wh(const Mfd& m, const V3& wo, const V2& u) {     // microfacet.rs:240-283
+    if (m.empty) return normalize(black());
+    bool flip = wo.z < 0.;
+    V3 fwo = flip ? -wo : wo;
+    V3 wh = tr_sample(fwo, m.alpha_x, m.alpha_y, u.x, u.y);
+    return flip ? -wh : wh;
+}
+
+// ------------------------------------------------------------------ bxdf.rs lobes
+inline Lobe make_lambert(const V3& c) { Lobe l; l.kind = L_LAMBERT_R; l.type = BSDF_REFLECTION | BSDF_DIFFUSE; l.color = c; return l; }   // :904-907
+inline Lobe make_oren_nayar(const V3& c, double sigma) {                // bxdf.rs:909-921
+    Lobe l; l.kind = L_OREN_NAYAR; l.type = BSDF_REFLECTION | BSDF_DIFFUSE; l.color = c;
+    double sr = sigma * PI / 180.0, s2 = sr * sr;
+    l.a = 1. - (s2 / (2. * (s2 + 0.33))); l.b = 0.45 * s2 / (s2 + 0.09);
+    return l;
+}
+inline Lobe make_specular_reflection(const V3& c, const Fresnel& f) { Lobe l; l.kind = L_SPEC_R; l.type = BSDF_REFLECTION | BSDF_SPECULAR; l.color = c; l.fresnel = f; return l; }  // :878-884
+inline Lobe make_specular_transmission(const V3& c, double ea, double eb, uint8_t mode) {  // :886-902
+    Lobe l; l.kind = L_SPEC_T; l.type = BSDF_TRANSMISSION | BSDF_SPECULAR; l.color = c; l.eta_a = ea; l.eta_b = eb; l.mode = mode;
+    l.fresnel.kind = F_DIELECTRIC; l.fresnel.eta_i = ea; l.fresnel.eta_t = eb; return l;
+}
+inline Lobe make_microfacet_reflection(const V3& c, const Fresnel& f, const Mfd& m) { Lobe l; l.kind = L_MICRO_R; l.type = BSDF_REFLECTION | BSDF_GLOSSY; l.color = c; l.fresnel = f; l.mfd = m; return l; }  // :923-935
+inline Lobe make_microfacet_transmission(const V3& c, const Mfd& m, double ea, double eb, uint8_t mode) {  // :937-958
+    Lobe l; l.kind = L_MICRO_T; l.type = BSDF_TRANSMISSION | BSDF_GLOSSY; l.color = c; l.mfd = m; l.eta_a = ea; l.eta_b = eb; l.mode = mode;
+    l.fresnel.kind = F_DIELECTRIC; l.fresnel.eta_i = ea; l.fresnel.eta_t = eb; return l;
+}
+inline Lobe make_fresnel_specular(const V3& r, const V3& t, double ea, double eb, uint8_t mode) {  // :974-990
+    Lobe l; l.kind = L_FRESNEL_SPEC; l.type = BSDF_TRANSMISSION | BSDF_REFLECTION | BSDF_SPECULAR; l.color = r; l.t = t; l.eta_a = ea; l.eta_b = eb; l.mode = mode; return l;
+}
+
+// Bxdf::f (bxdf.rs:328-527)
+inline V3 lobe_f(const Lobe& l, const V3& wo, const V3& wi) {
+    switch (l.kind) {
+        case L_LAMBERT_R: return l.color * INV_PI;
+        case L_OREN_NAYAR: {
+            double sti = sin_theta(wi), sto = sin_theta(wo), max_cos = 0.;
+            if (sti > SMALL && sto > SMALL) {
+                double d_cos = cos_phi(wi) * cos_phi(wo) + sin_phi(wi) * sin_phi(wo);
+                max_cos = rmax(0., d_cos);
+            }
+            double sin_alpha, tan_beta;
+            if (abs_cos_theta(wi) > abs_cos_theta(wo)) { sin_alpha = sto; tan_beta = sti / abs_cos_theta(wi); }
+            else { sin_alpha = sti; tan_beta = sto / abs_cos_theta(wi); }      // |cos θi| in both arms (§8.1 #11)
+            return l.color * (INV_PI * (l.a + l.b * max_cos * sin_alpha * tan_beta));
+        }
+        case L_MICRO_R: {
+            double cto = abs_cos_theta(wo), cti = abs_cos_theta(wi);
+            V3 wh = wi + wo;
+            if (cti == 0. || cto == 0.) return black();
+            if (wh == black()) return black();
+            wh = normalize(wh);
+            V3 f = fresnel_evaluate(l.fresnel, dot(wi, face_forward(wh, V3(0., 0., 1.))));
+            V3 comp1 = l.color * mfd_d(l.mfd, wh) * mfd_g(l.mfd, wo, wi);
+            return cmul(comp1, f * (1. / (4. * cti * cto)));
+        }
+        case L_MICRO_T: {
+            if (same_hemisphere(wo, wi)) return black();
+            double cto = cos_theta(wo), cti = cos_theta(wi);
+            if (cti == 0. || cto == 0.) return black();
+            double eta = cos_theta(wo) > 0. ? l.eta_b / l.eta_a : l.eta_a / l.eta_b;
+            V3 wh = normalize(wo + wi * eta);
+            if (wh.z < 0.) wh = -wh;
+            if (dot(wo, wh) * dot(wi, wh) > 0.) return black();
+            V3 f = fresnel_evaluate(l.fresnel, dot(wo, wh));
+            double sqrt_denom = dot(wo, wh) + eta * dot(wi, wh);
+            double factor = l.mode == RADIANCE ? 1. / eta : 1.;
+            V3 c = cmul(white() - f, l.color);
+            return c * std::fabs(mfd_d(l.mfd, wh) * mfd_g(l.mfd, wo, wi) * eta * eta * std::fabs(dot(wi, wh)) * std::fabs(dot(wo, wh)) * factor * factor /
+                                 (cti * cto * sqrt_denom * sqrt_denom));
+        }
+        default: return black();  // SpecularReflection / SpecularTransmission / FresnelSpecular
+    }
+}
+inline double default_pdf(const V3& wo, const V3& wi) { return same_hemisphere(wo, wi) ? abs_cos_theta(wi) * INV_PI : 0.; }  // bxdf.rs:829-835
+// Bxdf::pdf (bxdf.rs:721-813)
+inline double lobe_pdf(const Lobe& l, const V3& wo, const V3& wi) {
+    switch (l.kind) {
+        case L_LAMBERT_R: case L_OREN_NAYAR: case L_SPEC_R: return default_pdf(wo, wi);
+        case L_SPEC_T: return 0.;
+        case L_MICRO_R: {
+            if (!same_hemisphere(wo, wi)) return 0.;
+            V3 wh = normalize(wo + wi);
+            return mfd_pdf(l.mfd, wo, wh) / (4. * dot(wo, wh));
+        }
+        case L_MICRO_T: {
+            if (same_hemisphere(wo, wi)) return 0.;
+            double eta = cos_theta(wo) > 0. ? l.eta_b / l.eta_a : l.eta_a / l.eta_b;
+            V3 wh = normalize(wo + wi * eta);
+            if (dot(wo, wh) * dot(wi, wh) > 0.) return 0.;
+            double sqrt_denom = dot(wo, wh) + eta * dot(wi, wh);
+            double dwh_dwi = std::fabs(eta * eta * dot(wi, wh)) / (sqrt_denom * sqrt_denom);
+            return mfd_pdf(l.mfd, wo, wh) * dwh_dwi;
+        }
+        default: return 0.;  // FresnelSpecular: "unimplemented", returns 0 (bxdf.rs:777-791)
+    }
+}
+// util::rand_cosine_dir (util.rs:127-148): two fresh uniforms, NOT the supplied sample (§8.1 #9)
+inline V3 rand_cosine_dir(Rng& rng) {
+    double r1 = rng.next(), r2 = rng.next();
+    double u1 = 2. * r1 - 1., u2 = 2. * r2 - 1.;
+    if (u1 == 0. && u2 == 0.) return V3(0., 0., 1.);
+    double theta, r;
+    if (std::fabs(u1) > std::fabs(u2)) { r = u1; theta = PI / 4. * (u2 / u1); }
+    else { r = u2; theta = PI / 2. - PI / 4. * (u1 / u2); }
+    double x = r * std::cos(theta), y = r * std::sin(theta);
+    double z = std::sqrt(rmax(0., 1. - x * x - y * y));
+    return V3(x, y, z);
+}
+// Bxdf::sample_f (bxdf.rs:532-719) → (color, wi, pdf)
+inline void lobe_sample_f(const Lobe& l, const V3& wo, const V2& sample, Rng& rng, V3& color, V3& wi, double& pdf) {
+    color = black(); wi = black(); pdf = 0.;
+    switch (l.kind) {
+        case L_LAMBERT_R: case L_OREN_NAYAR: {                                  // default_sample_f bxdf.rs:815-827
+            wi = rand_cosine_dir(rng);
+            if (wo.z < 0.) wi.z *= -1.;
+            pdf = lobe_pdf(l, wo, wi); color = lobe_f(l, wo, wi); return;
+        }
+        case L_SPEC_R: {
+            wi = V3(-wo.x, -wo.y, wo.z);
+            color = cmul(l.color, fresnel_evaluate(l.fresnel, cos_theta(wi))); pdf = 1.; return;
+        }
+        case L_SPEC_T: {
+            bool entering = cos_theta(wo) > 0.;
+            double eta_i = entering ? l.eta_a : l.eta_b, eta_t = entering ? l.eta_b : l.eta_a;
+            V3 dir;
+            if (!refract(wo, face_forward(V3(0., 0., 1.), wo), eta_i / eta_t, dir)) { wi = black(); return; }
+            V3 ft = cmul(white() - fresnel_evaluate(l.fresnel, cos_theta(dir)), l.color);
+            if (l.mode == RADIANCE) ft = ft * ((eta_i * eta_i) / (eta_t * eta_t));
+            color = ft; wi = dir; pdf = 1.; return;
+        }
+        case L_MICRO_R: {
+            if (wo.z == 0.) return;
+            V3 wh = mfd_sample_wh(l.mfd, wo, sample);
+            // the `wo·wh < 0` guard has no `return` in the reference (bxdf.rs:598-600, §8.1 #10)
+            V3 w = reflect(wo, wh);
+            if (!same_hemisphere(wo, w)) return;
+            pdf = mfd_pdf(l.mfd, wo, wh) / (4. * dot(wo, wh));
+            wi = w; color = lobe_f(l, wo, wi); return;
+        }
+        case L_MICRO_T: {
+            if (wo.z == 0.) return;
+            V3 wh = mfd_sample_wh(l.mfd, wo, sample);
+            if (dot(wo, wh) < 0.) return;
+            double eta = cos_theta(wo) > 0. ? l.eta_a / l.eta_b : l.eta_b / l.eta_a;
+            V3 w;
+            if (!refract(wo, wh, eta, w)) return;
+            wi = w; pdf = lobe_pdf(l, wo, wi); color = lobe_f(l, wo, wi); return;
+        }
+        case L_FRESNEL_SPEC: {
+            double f = fr_dielectric(cos_theta(wo) / norm(wo), l.eta_a, l.eta_b);
+            if (sample.x < f) { wi = V3(-wo.x, -wo.y, wo.z); pdf = f; color = l.color * f; return; }
+            bool entering = cos_theta(wo) > 0.;
+            double eta_i = entering ? l.eta_a : l.eta_b, eta_t = entering ? l.eta_b : l.eta_a;
+            V3 dir;
+            if (!refract(wo, face_forward(V3(0., 0., 1.), wo), eta_i / eta_t, dir)) return;
+            V3 ft = l.t * (1. - f);
+            if (l.mode == RADIANCE) ft = ft * ((eta_i * eta_i) / (eta_t * eta_t));
+            color = ft; wi = dir; pdf = 1. - f; return;
+        }
+    }
+}
+
+// ------------------------------------------------------------------ bsdf.rs
+inline Bsdf bsdf_new(const HitRecord& r, double eta) {                  // bsdf.rs:26-35
+    Bsdf b; b.eta = eta; b.ns = r.shading.n; b.ng = r.n; b.ss = r.shading.dpdu;
+    b.ts = normalize(cross(r.shading.n, r.shading.dpdu)); b.n_lobes = 0;
+    return b;
+}
+inline bool bsdf_is_empty(const Bsdf& b) { return b.eta == -100.0; }
+inline void bsdf_add(Bsdf& b, const Lobe& l) { b.lobes[b.n_lobes++] = l; }
+inline uint32_t bsdf_num_components(const Bsdf& b, uint8_t t) { uint32_t c = 0; for (int i = 0; i < b.n_lobes; i++) if (matches_flags(b.lobes[i].type, t)) c++; return c; }
+inline V3 world_to_local(const Bsdf& b, const V3& v) { return V3(dot(v, b.ss), dot(v, b.ts), dot(v, b.ns)); }  // :67-69
+inline V3 local_to_world(const Bsdf& b, const V3& v) {                  // bsdf.rs:71-77
+    return V3(b.ss.x * v.x + b.ts.x * v.y + b.ns.x * v.z, b.ss.y * v.x + b.ts.y * v.y + b.ns.y * v.z, b.ss.z * v.x + b.ts.z * v.y + b.ns.z * v.z);
+}
+// Bsdf::f (bsdf.rs:83-98) — `a && b || c` precedence kept (§8.1 #6)
+inline V3 bsdf_f(const Bsdf& b, const V3& wow, const V3& wiw, uint8_t flags) {
+    V3 wi = world_to_local(b, wiw), wo = world_to_local(b, wow);
+    bool refl = dot(wiw, b.ng) * dot(wow, b.ng) > 0.;
+    V3 f = black();
+    for (int i = 0; i < b.n_lobes; i++) {
+        const Lobe& l = b.lobes[i];
+        if ((matches_flags(l.type, flags) && (refl && (l.type & BSDF_REFLECTION) > 0)) || (!refl && (l.type & BSDF_TRANSMISSION) > 0))
+            f = f + lobe_f(l, wo, wi);
+    }
+    return f;
+}
+// Bsdf::sample_f (bsdf.rs:102-164) → (color, wi world, pdf, sampled type)
+inline void bsdf_sample_f(const Bsdf& b, const V3& wow, const V2& sample, uint8_t bxdf_type, Rng& rng, V3& color, V3& wiw, double& pdf, uint8_t& sampled) {
+    color = black(); wiw = black(); pdf = 0.; sampled = 0;
+    uint32_t matching = bsdf_num_components(b, bxdf_type);
+    if (matching == 0) return;
+    uint32_t comp = std::min((uint32_t)std::floor(sample.x * (double)matching), matching - 1);
+    uint32_t count = comp; int used = -1;
+    for (int i = 0; i < b.n_lobes; i++) if (matches_flags(b.lobes[i].type, bxdf_type)) { if (count == 0) { used = i; break; } count--; }
+    const Lobe& bx = b.lobes[used];
+    uint8_t st = bx.type;
+    V3 wo = normalize(world_to_local(b, wow));
+    if (wo.z == 0.) return;
+    V3 c, wi; double p;
+    lobe_sample_f(bx, wo, sample, rng, c, wi, p);
+    if (p == 0.) return;
+    V3 w = local_to_world(b, wi);
+    if ((bx.type & BSDF_SPECULAR) == 0 && matching > 1)
+        for (int i = 0; i < b.n_lobes; i++) if (i != used && matches_flags(b.lobes[i].type, bxdf_type)) p += lobe_pdf(b.lobes[i], wo, wi);
+    if (matching > 1) p = p / (double)matching;
+    if ((bx.type & BSDF_SPECULAR) == 0) {
+        bool refl = dot(w, b.ng) * dot(wow, b.ng) > 0.;
+        c = V3(0., 0., 0.);
+        for (int i = 0; i < b.n_lobes; i++) {
+            const Lobe& l = b.lobes[i];
+            if (matches_flags(l.type, bxdf_type) && ((refl && (l.type & BSDF_REFLECTION) > 0) || (!refl && (l.type & BSDF_TRANSMISSION) > 0)))
+                c = c + lobe_f(l, wo, wi);
+        }
+    }
+    color = c; wiw = w; pdf = p; sampled = st;
+}
+// Bsdf::pdf (bsdf.rs:166-189): sums, does not average (§8.1 #8); wo is NOT normalised here
+inline double bsdf_pdf(const Bsdf& b, const V3& wow, const V3& wiw, uint8_t flags) {
+    uint32_t n = bsdf_num_components(b, BSDF_ALL);
+    if (n == 0) return 0.;
+    V3 wo = world_to_local(b, wow), wi = world_to_local(b, wiw);
+    if (wo.z == 0.) return 0.;
+    double pdf = 0.; int matching = 0;
+    for (uint32_t i = 0; i < n; i++) if (matches_flags(b.lobes[i].type, flags)) { matching++; pdf += lobe_pdf(b.lobes[i], wo, wi); }
+    return matching > 0 ? pdf : 0.;
+}
+
+// ------------------------------------------------------------------ material.rs
+// Texture::value / get_value (material.rs:542-589), SolidColor and Checkered
+inline V3 tex_value(const Scene& s, uint32_t id, double u, double v) {
+    const rt_texture& t = s.textures[id];
+    if (t.type == RT_TEX_CHECKERED) {
+        double mult = std::sin(t.frequency * u * 2. * PI) * std::sin(t.frequency * v * 2. * PI);
+        return mult < 0. ? tex_value(s, t.even, u, v) : tex_value(s, t.odd, u, v);
+    }
+    return V3(t.color[0], t.color[1], t.color[2]);
+}
+// Material::compute_scattering (material.rs:80-244), mode = RADIANCE, allow_lobes = true in the path integrator
+inline void compute_scattering(const Scene& s, HitRecord& r, uint8_t mode, bool allow_lobes) {
+    const rt_material& m = s.materials[r.mat_index];
+    double u = r.uv.x, v = r.uv.y;
+    switch (m.type) {
+        case RT_MAT_MATTE: {
+            double sig = clampd(m.f[0], 0., 90.);
+            V3 color = tex_value(s, m.tex[0], u, v);
+            if (color != black()) {
+                r.bsdf = bsdf_new(r, 1.);
+                if (sig == 0.) bsdf_add(r.bsdf, make_lambert(color)); else bsdf_add(r.bsdf, make_oren_nayar(color, sig));
+            }
+            return;
+        }
+        case RT_MAT_LIGHT: return;
+        case RT_MAT_PLASTIC: {
+            V3 color = tex_value(s, m.tex[0], u, v);
+            if (color != black()) { r.bsdf = bsdf_new(r, 1.); bsdf_add(r.bsdf, make_lambert(color)); }
+            V3 spec = tex_value(s, m.tex[1], u, v);
+            if (spec != black()) {
+                if (bsdf_is_empty(r.bsdf)) r.bsdf = bsdf_new(r, 1.);
+                Fresnel fr; fr.kind = F_DIELECTRIC; fr.eta_i = 1.5; fr.eta_t = 1.;
+                double rough = m.f[0];
+                if (m.remap_roughness) rough = tr_roughness_to_alpha(rough);
+                bsdf_add(r.bsdf, make_microfacet_reflection(spec, fr, make_trowbridge_reitz(rough, rough)));
+            }
+            return;
+        }
+        case RT_MAT_GLASS: {
+            double eta = m.f[2], urough = m.f[0], vrough = m.f[1];
+            V3 rr = tex_value(s, m.tex[0], u, v), t = tex_value(s, m.tex[1], u, v);
+            r.bsdf = bsdf_new(r, eta);
+            if (rr == black() && t == black()) return;
+            bool is_specular = urough == 0. && vrough == 0.;
+            if (is_specular && allow_lobes) { bsdf_add(r.bsdf, make_fresnel_specular(rr, t, eta, 1., mode)); return; }
+            if (m.remap_roughness) { urough = tr_roughness_to_alpha(urough); vrough = tr_roughness_to_alpha(vrough); }
+            Mfd mfd = is_specular ? Mfd() : make_trowbridge_reitz(urough, vrough);
+            if (!(rr == black())) {
+                Fresnel fr; fr.kind = F_DIELECTRIC; fr.eta_i = eta; fr.eta_t = 1.;
+                if (is_specular) bsdf_add(r.bsdf, make_specular_reflection(rr, fr)); else bsdf_add(r.bsdf, make_microfacet_reflection(rr, fr, mfd));
+            }
+            if (!(t == black())) {
+                if (is_specular) bsdf_add(r.bsdf, make_specular_transmission(t, eta, 1., mode)); else bsdf_add(r.bsdf, make_microfacet_transmission(t, mfd, eta, 1., mode));
+            }
+            return;
+        }
+        case RT_MAT_METAL: {
+            r.bsdf = bsdf_new(r, 1.);
+            V3 u_rough = tex_value(s, m.tex[3] == RT_NONE ? m.tex[2] : m.tex[3], u, v);
+            V3 v_rough = tex_value(s, m.tex[4] == RT_NONE ? m.tex[2] : m.tex[4], u, v);
+            double ur = m.remap_roughness ? tr_roughness_to_alpha(u_rough.x) : u_rough.x;
+            double vr = m.remap_roughness ? tr_roughness_to_alpha(v_rough.x) : v_rough.x;
+            Fresnel fr; fr.kind = F_CONDUCTOR; fr.eta = tex_value(s, m.tex[0], u, v); fr.k = tex_value(s, m.tex[1], u, v);
+            bsdf_add(r.bsdf, make_microfacet_reflection(white(), fr, make_trowbridge_reitz(ur, vr)));
+            return;
+        }
+        case RT_MAT_MIRROR: {
+            r.bsdf = bsdf_new(r, 1.);
+            V3 color = tex_value(s, m.tex[0], u, v);
+            if (color != black()) { Fresnel fr; fr.kind = F_NOOP; bsdf_add(r.bsdf, make_specular_reflection(color, fr)); }
+            return;
+        }
+    }
+}
+
+// ------------------------------------------------------------------ primitive.rs sampling, light.rs (Diffuse)
+inline V3 uniform_sample_sphere(const V2& u) {                          // util.rs:51-56
+    double z = 1. - 2. * u.x, r = std::sqrt(rmax(0., 1. - z * z)), phi = 2. * PI * u.y;
+    return V3(r * std::cos(phi), r * std::sin(phi), z);
+}
+inline V2 uniform_sample_triangle(const V2& u) { double s0 = std::sqrt(u.x); return V2(1. - s0, u.y * s0); }  // util.rs:62-65
+// Primitive::sample_area (primitive.rs:478-539) → (record, pdf)
+inline void sample_area(const Scene& s, const rt_primitive& pr, const V2& u, HitRecord& rec, double& pdf) {
+    switch (pr.type) {
+        case RT_PRIM_SPHERE: {
+            V3 p_obj = V3(0, 0, 0) + pr.v[3] * uniform_sample_sphere(u);   // around the ORIGIN, not the centre (§8.1 #13)
+            rec = record_normal(p_obj, normalize(p_obj - V3(0, 0, 0)));
+            break;
+        }
+        case RT_PRIM_TRIANGLE: {
+            const Mesh& m = s.meshes[pr.mesh_index];
+            V2 b = uniform_sample_triangle(u);
+            V3 p0 = m.p[m.ind[pr.ind]], p1 = m.p[m.ind[pr.ind + 1]], p2 = m.p[m.ind[pr.ind + 2]];
+            V3 p = V3(0, 0, 0) + (b.x * p0 + b.y * p1 + (1. - b.x - b.y) * p2);
+            rec = record_normal(p, normalize(V3(1., 1., 1.)));
+            if (!m.n.empty()) rec.n = normalize(b.x * m.n[m.ind[pr.ind]] + b.y * m.n[m.ind[pr.ind + 1]] + (1. - b.x - b.y) * m.n[m.ind[pr.ind + 2]]);
+            else rec.n = normalize(cross(p1 - p0, p2 - p0));
+            break;
+        }
+        case RT_PRIM_XY_RECT: rec = record_normal(V3(pr.v[0] + u.x * (pr.v[2] - pr.v[0]), pr.v[1] + u.y * (pr.v[3] - pr.v[1]), pr.v[4]), normalize(V3(0., 0., 1.))); break;
+        case RT_PRIM_XZ_RECT: rec = record_normal(V3(pr.v[0] + u.x * (pr.v[2] - pr.v[0]), pr.v[4], pr.v[1] + u.y * (pr.v[3] - pr.v[1])), normalize(V3(0., 1., 0.))); break;
+        default:              rec = record_normal(V3(pr.v[4], pr.v[0] + u.x * (pr.v[2] - pr.v[0]), pr.v[1] + u.y * (pr.v[3] - pr.v[1])), normalize(V3(1., 0., 0.))); break;
+    }
+    pdf = 1. / prim_area(s, pr);
+    if (pr.flip_face) rec.n = -rec.n;                                     // primitive.rs:533-537
+}
+// Primitive::sample (primitive.rs:445-456) → (record, pdf, wi unnormalised)
+inline void prim_sample(const Scene& s, const rt_primitive& pr, const HitRecord& in, const V2& u, HitRecord& rec, double& pdf, V3& wi) {
+    sample_area(s, pr, u, rec, pdf);
+    wi = rec.p - in.p;
+    if (norm2(wi) == 0.) pdf = 0.;
+    else { V3 wn = normalize(wi); pdf = pdf * norm2(in.p - rec.p) / std::fabs(dot(rec.n, -wn)); }
+}
+// Primitive::pdf (primitive.rs:462-473)
+inline double prim_pdf(const Scene& s, const rt_primitive& pr, const HitRecord& rec, const V3& dir) {
+    Ray ray = spawn_ray(rec, dir);
+    HitRecord nr;
+    if (!intersects_obj(s, pr, ray, 0., INF, nr)) return 0.;
+    V3 dist = rec.p - nr.p;
+    return norm2(dist) / (prim_area(s, pr) * std::fabs(dot(nr.n, -dir)));
+}
+// Light::l (light.rs:475-496)
+inline V3 light_l(const Light& l, const HitRecord& rec, const V3& w) {
+    if (dot(rec.n, w) > 0. || l.d.two_sided) return V3(l.d.color[0], l.d.color[1], l.d.color[2]);
+    return black();
+}
+// HitRecord::le (hittable.rs:215-225)
+inline V3 record_le(const Scene& s, const HitRecord& rec, const V3& w) {
+    uint32_t li = s.prims[rec.prim_index].light_index;
+    if (li == RT_NONE) return black();
+    return light_l(s.lights[li], rec, w);
+}
+// Light::sample_li, Diffuse arm (light.rs:176-203) → wi, pdf, color, visibility target
+struct LiSample { V3 wi; double pdf; V3 color; V3 p1; uint32_t p1_prim; double p1_t; };
+inline LiSample sample_li(const Scene& s, const Light& l, const HitRecord& rec, const V2& u) {
+    LiSample o;
+    const rt_primitive& pr = s.prims[l.d.prim_index];
+    HitRecord nr; double pdf; V3 wi;
+    prim_sample(s, pr, rec, u, nr, pdf, wi);
+    nr.prim_index = l.d.prim_index;
+    if (pdf == 0. || norm2(rec.p - nr.p) == 0.) {
+        o.wi = normalize(black()); o.pdf = 0.; o.color = V3(l.d.color[0], l.d.color[1], l.d.color[2]);
+        o.p1 = V3(0, 0, 0); o.p1_prim = 0; o.p1_t = 1.;
+        return o;
+    }
+    o.wi = normalize(nr.p - rec.p);
+    o.pdf = pdf;
+    o.color = light_l(l, nr, -o.wi);
+    o.p1 = nr.p; o.p1_prim = nr.prim_index; o.p1_t = nr.t;
+    return o;
+}
+// Light::pdf_li, Diffuse arm (light.rs:284)
+inline double pdf_li(const Scene& s, const Light& l, const HitRecord& rec, const V3& wi) { return prim_pdf(s, s.prims[l.d.prim_index], rec, wi); }
+
+// ------------------------------------------------------------------ integrator.rs (Path)
+struct RayCounts { uint64_t extend = 0, shadow = 0, probe = 0; };
+inline double power_heuristic(int nf, double f_pdf, int ng, double g_pdf) {     // integrator.rs:655-659
+    double f = nf * f_pdf, g = ng * g_pdf;
+    return (f * f) / (f * f + g * g);
+}
+// estimate_direct (integrator.rs:559-634), specular = false; area lights are never delta / infinite
+inline V3 estimate_direct(const Scene& s, const HitRecord& rec, const V2& u_scatter, uint32_t light_num, const V2& u_light, Rng& rng, RayCounts& rc) {
+    const Light& light = s.lights[light_num];
+    uint8_t flags = BSDF_ALL - BSDF_SPECULAR;
+    V3 ld = black();
+    LiSample ls = sample_li(s, light, rec, u_light);
+    double light_pdf = ls.pdf; V3 color = ls.color;
+    if (light_pdf > 0. && color != black()) {
+        V3 f = bsdf_f(rec.bsdf, rec.wo, ls.wi, flags) * std::fabs(dot(ls.wi, rec.shading.n));
+        double scattering_pdf = bsdf_pdf(rec.bsdf, rec.wo, ls.wi, flags);
+        if (f != black()) {
+            rc.shadow++;
+            if (!unoccluded(s, rec.p, ls.p1, ls.p1_prim, ls.p1_t, false)) color = black();
+            if (color != black()) {
+                double weight = power_heuristic(1, light_pdf, 1, scattering_pdf);
+                ld = ld + cmul(f, color) * (weight / light_pdf);
+            }
+        }
+    }
+    {
+        V3 f, wi; double scattering_pdf; uint8_t st;
+        bsdf_sample_f(rec.bsdf, rec.wo, u_scatter, flags, rng, f, wi, scattering_pdf, st);
+        f = f * std::fabs(dot(wi, rec.shading.n));
+        bool sampled_specular = (st & BSDF_SPECULAR) != 0;
+        if (f != black() && scattering_pdf > 0.) {
+            double weight = 1.;
+            if (!sampled_specular) {
+                light_pdf = pdf_li(s, light, rec, wi);
+                if (light_pdf == 0.) return ld;
+                weight = power_heuristic(1, scattering_pdf, 1, light_pdf);
+            }
+            Ray nray = spawn_ray(rec, wi);
+            HitRecord nrec; rc.probe++;
+            V3 c = black();
+            if (get_intersection(s, nray, nrec)) {
+                uint32_t li = s.prims[nrec.prim_index].light_index;
+                if (li != RT_NONE && li == light_num) c = record_le(s, nrec, -wi);
+            }   // else light.le(ray): black for area lights
+            if (c != black()) ld = ld + cmul(f, c) * (weight / scattering_pdf);
+        }
+    }
+    return ld;
+}
+// uniform_sample_one_light (integrator.rs:530-557)
+inline V3 uniform_sample_one_light(const Scene& s, const HitRecord& rec, Rng& rng, RayCounts& rc) {
+    size_t n = s.lights.size();
+    if (n == 0) return black();
+    size_t light_num = std::min(n - 1, (size_t)(rng.next() * (double)n));
+    V2 u_light; u_light.x = rng.next(); u_light.y = rng.next();
+    V2 u_scatter; u_scatter.x = rng.next(); u_scatter.y = rng.next();
+    return estimate_direct(s, rec, u_scatter, (uint32_t)light_num, u_light, rng, rc) * (double)n;
+}
+// PathIntegrator::li (integrator.rs:375-445)
+inline V3 path_li(const Scene& s, Ray ray, uint32_t max_depth, bool invisible_light, Rng& rng, RayCounts& rc) {
+    V3 beta = white(), l = black();
+    bool specular_bounce = false;
+    uint32_t bounces = 0;
+    for (;;) {
+        HitRecord rec; rc.extend++;
+        bool is_some = get_intersection(s, ray, rec);
+        if (!is_some) rec = record_basic(V3(0, 0, 0), 0.);
+        if (bounces == 0 || specular_bounce) {
+            if (is_some) {
+                if (s.prims[rec.prim_index].light_index != RT_NONE) {
+                    if (invisible_light) { ray = spawn_ray(rec, ray.d); continue; }
+                    l = l + cmul(record_le(s, rec, -ray.d), beta);
+                }
+            }   // miss: Σ light.le(ray) = 0 for area lights
+        }
+        if (!is_some || bounces >= max_depth) break;
+        compute_scattering(s, rec, RADIANCE, true);
+        l = l + cmul(uniform_sample_one_light(s, rec, rng, rc), beta);
+        V3 wo = -ray.d;
+        V2 u; u.x = rng.next(); u.y = rng.next();
+        V3 f, wi; double pdf; uint8_t flags;
+        bsdf_sample_f(rec.bsdf, wo, u, BSDF_ALL, rng, f, wi, pdf, flags);
+        if (f == black() || pdf == 0.) break;
+        beta = cmul(beta, f) * (std::fabs(dot(wi, rec.shading.n)) / pdf);
+        specular_bounce = (flags & BSDF_SPECULAR) != 0;
+        ray = spawn_ray(rec, wi);
+        if (bounces > 3) {
+            double q = rmax(0.05, 1. - rmax(beta.x, rmax(beta.y, beta.z)));
+            if (rng.next() < q) break;
+            beta = beta * (1. / (1. - q));
+        }
+        bounces++;
+    }
+    return l;
+}
+
+// Camera::get_ray (geometry.rs:177-190) with util::rand_in_disk (util.rs:105-113) and rand_range
+inline Ray camera_get_ray(const rt_camera& c, double u, double v, Rng& rng) {
+    V3 in_disk;
+    for (;;) { double x = rng.next(), y = rng.next(); if (x * x + y * y < 1.) { in_disk = V3(x, y, 0.); break; } }
+    in_disk = in_disk * c.lens_radius;
+    V3 cu(c.u[0], c.u[1], c.u[2]), cv(c.v[0], c.v[1], c.v[2]);
+    V3 offset = cu * in_disk.x + cv * in_disk.y;
+    V3 ulc(c.upper_left_corner[0], c.upper_left_corner[1], c.upper_left_corner[2]);
+    V3 ho(c.horizontal_offset[0], c.horizontal_offset[1], c.horizontal_offset[2]);
+    V3 vo(c.vertical_offset[0], c.vertical_offset[1], c.vertical_offset[2]);
+    V3 origin(c.origin[0], c.origin[1], c.origin[2]);
+    V3 to = ulc + ho * u - vo * v;
+    V3 dir = to - origin;
+    double time = c.t0 + (c.t1 - c.t0) * rng.next();
+    return Ray{origin + offset, dir - offset, time};
+}
+// PathIntegrator::single_sample (integrator.rs:357-369) + Samplers::get_camera_sample (sampler.rs:606-613)
+inline V3 single_sample(const Scene& s, const rt_camera& cam, uint32_t width, uint32_t height, uint32_t px, uint32_t py,
+                        uint32_t sample, uint64_t seed, uint32_t max_depth, bool invisible_light, RayCounts& rc) {
+    Rng rng(seed, py * width + px, sample);
+    double ox = rng.next(), oy = rng.next();
+    double fx = (double)px + ox, fy = (double)py + oy;
+    rng.next();              // time
+    rng.next(); rng.next();  // lens
+    Ray ray = camera_get_ray(cam, fx / (double)width, fy / (double)height, rng);
+    return path_li(s, ray, max_depth, invisible_light, rng, rc);
+}
+
+// Camera::new_motion_blur (geometry.rs:133-175)
+inline rt_camera camera_new(const V3& from, const V3& to, const V3& up, double aspect, double vfov, double aperture, double focus, double t0, double t1) {
+    V3 w = normalize(to - from);
+    V3 u = -normalize(cross(up, w));
+    V3 v = -normalize(cross(w, u));
+    double theta = vfov * PI / 180., h = std::tan(theta / 2.);
+    double vh = 2. * h, vw = vh * aspect;
+    V3 ho = u * (vw * focus), vo = v * (vh * focus);
+    V3 ulc = from - ho * 0.5 + vo * 0.5 + w * focus;
+    rt_camera c;
+    auto put = [](double* d, const V3& a) { d[0] = a.x; d[1] = a.y; d[2] = a.z; };
+    put(c.origin, from); put(c.upper_left_corner, ulc); put(c.horizontal_offset, ho); put(c.vertical_offset, vo);
+    put(c.u, u); put(c.v, v); put(c.w, w);
+    c.lens_radius = aperture / 2.; c.t0 = t0; c.t1 = t1;
+    return c;
+}
+
+// util::point_to_color (util.rs:441-471) with aces_comp (util.rs:400-408)
+inline double aces_comp(double x) {
+    x = x * 0.6;
+    double a = 2.51, b = 0.03, c = 2.43, d = 0.59, e = 0.14;
+    return clampd((x * (a * x + b)) / (x * (c * x + d) + e), 0., 1.);
+}
+inline uint8_t to_u8(double v) { double r = std::round(v); if (!(r > 0.)) return 0; if (r > 255.) return 255; return (uint8_t)r; }  // Rust `as u8` saturates, NaN → 0
+inline void point_to_color(const double rgbn[4], uint8_t out[3]) {
+    double scale = 1. / rgbn[3];
+    for (int i = 0; i < 3; i++) out[i] = to_u8(std::pow(aces_comp(rgbn[i] * scale), 1. / GAMMA) * 256.);
+}
+
+}  // namespace orc
