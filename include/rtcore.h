@@ -157,8 +157,10 @@ typedef struct rt_counters {
     uint64_t shadow_rays;    /* ray type B: Visibility::unoccluded (integrator.rs:584)       */
     uint64_t probe_rays;     /* ray type C: MIS BSDF probe (integrator.rs:615)               */
     uint64_t iterations;     /* wavefront iterations                                         */
-    double   render_ms;      /* device time of the last rt_render (CUDA events)              */
-    double   traverse_ms;    /* device time inside extend + connect kernels                  */
+    double   render_ms;      /* device time of the last rt_render (CUDA events on its stream) */
+    double   extend_ms;      /* summed device time of the extend (closest-hit) launches       */
+    double   shade_ms;       /* summed device time of the generate + shade launches           */
+    double   connect_ms;     /* summed device time of the shadow-connect + probe launches     */
 } rt_counters;
 
 typedef struct rt_scene rt_scene;

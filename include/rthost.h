@@ -1,0 +1,71 @@
+/*
+ * rthost.h — host scene layer of librtcore.so (C ABI).
+ *
+ * The reference keeps scene construction on the host (scenes.rs, parser.rs; north_star: "the Rust
+ * host keeps scene parsing, material setup ..."); no Rust toolchain exists in this image, so the
+ * scene builders are restated in C++ behind this small C interface.  They produce plain tables
+ * (the POD structs of rtcore.h) that are (a) pushed into an rt_scene through the public rt_scene_*
+ * calls — exactly what a Rust host would do over FFI — and (b) exported to the test-side oracle so
+ * that both sides see identical inputs.  Nothing here is on the hot path.
+ */
+#ifndef RTHOST_H
+#define RTHOST_H
+#include "rtcore.h"
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rth_scene rth_scene;
+
+typedef struct rth_params {
+    uint32_t    width, height;   /* GLOBAL_STATE aspect ratio = width/height (main.rs:84-99)          */
+    uint32_t    variant;         /* plastic_dragon: 0 = rough plastic (scenes.rs:310), 1 = rough metal
+                                    (commented metal_dragon, scenes.rs:424-471);
+                                    cornell_box_statue: 0 = matte statue, 1 = metal (scenes.rs:243-246);
+                                    two_dragons: 0 = as committed (metal dragon only), 1 = glass + metal
+                                    (commented block scenes.rs:608-611 enabled)                        */
+    uint32_t    _pad;
+    uint64_t    n_tris;          /* soup: triangle count; dragon/statue stand-ins: 0 = default          */
+    uint64_t    seed;            /* generators                                                          */
+    const char* data_dir;        /* directory holding the reference's data/ (may be NULL): real
+                                    dragon/statue OBJ files are used when found there                  */
+} rth_params;
+
+/* name ∈ { "sphere_roughness" (scenes.rs:474), "make_world" (commented, scenes.rs:15-86, seeded),
+ *          "cornell_box" (:89), "cornell_box_statue" (:200), "plastic_dragon" (:310),
+ *          "two_dragons" (:549), "soup"  }                                    */
+rt_status   rth_scene_build(const char* name, const rth_params* params, rth_scene** out);
+void        rth_scene_destroy(rth_scene* s);
+/* the (String path, Camera, Samplers) a scene function returns */
+rt_status   rth_scene_camera(const rth_scene* s, rt_camera* out);
+const char* rth_scene_png_name(const rth_scene* s);
+/* 1 when a procedural stand-in replaced a missing OBJ asset */
+int32_t     rth_scene_uses_standin(const rth_scene* s);
+
+/* table export (for the oracle / inspection): counts = meshes, prims, transforms, textures, materials, lights */
+rt_status   rth_scene_counts(const rth_scene* s, uint64_t counts[6]);
+rt_status   rth_scene_mesh_sizes(const rth_scene* s, uint32_t mesh, uint64_t sizes[4]); /* points, normals, uvs, indices */
+rt_status   rth_scene_mesh_copy(const rth_scene* s, uint32_t mesh, double* points, double* normals, double* uvs, uint32_t* indices);
+rt_status   rth_scene_copy_primitives(const rth_scene* s, rt_primitive* out);
+rt_status   rth_scene_copy_transforms(const rth_scene* s, double* out16_each);
+rt_status   rth_scene_copy_textures(const rth_scene* s, rt_texture* out);
+rt_status   rth_scene_copy_materials(const rth_scene* s, rt_material* out);
+rt_status   rth_scene_copy_lights(const rth_scene* s, rt_light* out);
+
+/* push every table into `dst` through the public rt_scene_* calls (does not commit) */
+rt_status   rth_scene_upload(const rth_scene* s, rt_scene* dst);
+
+/* parser::parse_obj (parser.rs:8-87): tobj::load_obj(path, triangulate = true), models[0] only,
+ * single-index, f32 values widened to f64, `transform` (row-major 4x4) applied to points and normals.
+ * Appends the mesh to `s` and returns its index. */
+rt_status   rth_scene_add_obj(rth_scene* s, const char* path, const double transform[16], uint32_t* mesh_index_out);
+/* an empty scene to append to */
+rt_status   rth_scene_create_empty(rth_scene** out);
+
+/* ray batches of SURVEY.md §8d: primary rays through pixel centres of a width x height image */
+rt_status   rth_primary_rays(const rt_camera* cam, uint32_t width, uint32_t height, rt_ray* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

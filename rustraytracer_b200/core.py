@@ -1,0 +1,251 @@
+"""Host-side mirror of the reference's interface for the hot path, over the C ABI.
+
+Names follow the reference (calvin-godfrey/RustRaytracer, `src/`):
+  Objects            ~ `struct Objects` / `get_objects_mut()`        geometry.rs:13-55
+  Camera             ~ `Camera::new / new_motion_blur`               geometry.rs:110-175
+  IntType            ~ `enum IntType`                                integrator.rs:26-41
+  Samplers           ~ `Samplers::new_zero_two_sequence_sampler`     sampler.rs:633-642
+  get_intersection   ~ `geometry::get_intersection`                  geometry.rs:238-240
+  unoccluded         ~ `Visibility::unoccluded`                      hittable.rs:25-39
+  tile_multithread   ~ `render::tile_multithread`                    render.rs:13-159
+Everything computes in librtcore.so on the GPU; this file only marshals buffers.
+"""
+import ctypes as C
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import _native as N
+from ._native import Camera as _CCamera, check, lib, ptr
+
+MAX_DEPTH = 25        # consts.rs:7
+TILE_SIZE = 16        # consts.rs:10
+SMALL = 0.001         # consts.rs:32
+INFINITY = 1e308      # consts.rs:30
+
+
+class Camera:
+    """`struct Camera` (geometry.rs:95-108)."""
+
+    def __init__(self, c=None):
+        self.c = c if c is not None else _CCamera()
+
+    @staticmethod
+    def new(frm, to, up, aspect_ratio, vfov, aperture, focus_dist):
+        return Camera.new_motion_blur(frm, to, up, aspect_ratio, vfov, aperture, focus_dist, 0.0, 0.0)
+
+    @staticmethod
+    def new_motion_blur(frm, to, up, aspect_ratio, vfov, aperture, focus_dist, t0, t1):
+        cam = Camera()
+        f, t, u = (np.ascontiguousarray(x, dtype=np.float64) for x in (frm, to, up))
+        check(lib().rt_camera_look_at(ptr(f), ptr(t), ptr(u), aspect_ratio, vfov, aperture, focus_dist, t0, t1, C.byref(cam.c)))
+        return cam
+
+    def primary_rays(self, width, height):
+        """Pixel-centre rays (SURVEY.md §8d batch A), `Camera::get_ray` with lens_radius = 0."""
+        rays = np.zeros(width * height, dtype=N.ray_dtype)
+        check(lib().rth_primary_rays(C.byref(self.c), width, height, ptr(rays)))
+        return rays
+
+
+@dataclass
+class IntType:
+    """`IntType::Path { max_depth, invisible_light }` (integrator.rs:37-40); the only integrator the
+    reference ever selects (main.rs:262-265)."""
+    max_depth: int = MAX_DEPTH
+    invisible_light: bool = False
+
+    @staticmethod
+    def Path(max_depth=MAX_DEPTH, invisible_light=False):
+        return IntType(max_depth, invisible_light)
+
+
+@dataclass
+class Samplers:
+    """Effective behaviour of `Samplers::new_zero_two_sequence_sampler(spp, 0)`: next_power_of_two(spp)
+    iid uniforms per pixel (sampler.rs:633-642, 306-339); here from a counter-based RNG keyed by `seed`."""
+    samples_per_pixel: int
+    seed: int = 0
+
+    @staticmethod
+    def new_zero_two_sequence_sampler(samples_per_pixel, n_sampled_dimensions=0, seed=0):
+        return Samplers(int(lib().rt_round_spp(int(samples_per_pixel))), seed)
+
+
+class Objects:
+    """The scene tables + committed BVH (`struct Objects`, geometry.rs:13-21) held by the library."""
+
+    def __init__(self):
+        self.h = C.c_void_p()
+        check(lib().rt_scene_create(C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            lib().rt_scene_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- pushes (scenes.rs style)
+    def add_mesh(self, points, normals=None, uvs=None, indices=None):
+        p = np.ascontiguousarray(points, dtype=np.float64).reshape(-1, 3)
+        n = None if normals is None or len(normals) == 0 else np.ascontiguousarray(normals, dtype=np.float64).reshape(-1, 3)
+        uv = None if uvs is None or len(uvs) == 0 else np.ascontiguousarray(uvs, dtype=np.float64).reshape(-1, 2)
+        ind = np.ascontiguousarray(indices, dtype=np.uint32).reshape(-1)
+        out = C.c_uint32()
+        check(lib().rt_scene_add_mesh(self.h, len(p), ptr(p), 0 if n is None else len(n), ptr(n), 0 if uv is None else len(uv), ptr(uv),
+                                      len(ind), ptr(ind), C.byref(out)))
+        return out.value
+
+    def add_transform(self, m4):
+        m = np.ascontiguousarray(m4, dtype=np.float64).reshape(16)
+        out = C.c_uint32()
+        check(lib().rt_scene_add_transform(self.h, ptr(m), C.byref(out)))
+        return out.value
+
+    def add_primitives(self, prims):
+        prims = np.ascontiguousarray(prims, dtype=N.prim_dtype)
+        out = C.c_uint32()
+        check(lib().rt_scene_add_primitives(self.h, len(prims), ptr(prims), C.byref(out)))
+        return out.value
+
+    def add_mesh_triangles(self, mesh_index, mat_index):
+        out = C.c_uint32()
+        check(lib().rt_scene_add_mesh_triangles(self.h, mesh_index, mat_index, C.byref(out)))
+        return out.value
+
+    def set_light_index(self, prim, light):
+        check(lib().rt_scene_set_light_index(self.h, prim, light))
+
+    def set_textures(self, t):
+        t = np.ascontiguousarray(t, dtype=N.texture_dtype)
+        check(lib().rt_scene_set_textures(self.h, len(t), ptr(t)))
+
+    def set_materials(self, m):
+        m = np.ascontiguousarray(m, dtype=N.material_dtype)
+        check(lib().rt_scene_set_materials(self.h, len(m), ptr(m)))
+
+    def set_lights(self, l):
+        l = np.ascontiguousarray(l, dtype=N.light_dtype)
+        check(lib().rt_scene_set_lights(self.h, len(l), ptr(l)))
+
+    def commit(self):
+        """`objects.node = BvhNode::new(..)` (e.g. scenes.rs:368-371): build + flatten + upload."""
+        check(lib().rt_scene_commit(self.h))
+
+    def num_primitives(self):
+        out = C.c_uint64()
+        check(lib().rt_scene_num_primitives(self.h, C.byref(out)))
+        return out.value
+
+    def device_bytes(self):
+        a, b, c = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        check(lib().rt_scene_device_bytes(self.h, C.byref(a), C.byref(b), C.byref(c)))
+        return {"nodes": a.value, "leaves": b.value, "tables": c.value}
+
+    def counters(self):
+        c = N.Counters()
+        check(lib().rt_get_counters(self.h, C.byref(c)))
+        return {k: getattr(c, k) for k, _ in N.Counters._fields_}
+
+    def set_wavefront_size(self, paths):
+        check(lib().rt_set_wavefront_size(self.h, int(paths)))
+
+
+def make_rays(origins, dirs):
+    o = np.asarray(origins, dtype=np.float64).reshape(-1, 3)
+    d = np.asarray(dirs, dtype=np.float64).reshape(-1, 3)
+    rays = np.zeros(len(o), dtype=N.ray_dtype)
+    rays["origin"] = o
+    rays["dir"] = d
+    return rays
+
+
+def get_intersection(objects, rays, tmin=SMALL, tmax=INFINITY):
+    """`geometry::get_intersection(&Ray) -> Option<HitRecord>` (geometry.rs:238-240) for a batch of rays.
+    Returns a structured array (rt_hit); prim_index == RT_NONE is `None`."""
+    rays = np.ascontiguousarray(rays, dtype=N.ray_dtype)
+    hits = np.zeros(len(rays), dtype=N.hit_dtype)
+    check(lib().rt_intersect_range(objects.h, len(rays), ptr(rays), float(tmin), float(tmax), ptr(hits)))
+    return hits
+
+
+def unoccluded(objects, p0, p1, p1_prim_index, infinite_light=False):
+    """`Visibility{p0,p1}.unoccluded(infinite_light)` (hittable.rs:25-39) for a batch of point pairs."""
+    p0 = np.asarray(p0, dtype=np.float64).reshape(-1, 3)
+    q = np.zeros(len(p0), dtype=N.shadow_dtype)
+    q["p0"] = p0
+    q["p1"] = np.asarray(p1, dtype=np.float64).reshape(-1, 3)
+    q["p1_prim_index"] = np.asarray(p1_prim_index, dtype=np.uint32)
+    q["infinite_light"] = 1 if infinite_light else 0
+    out = np.zeros(len(q), dtype=np.uint8)
+    check(lib().rt_occluded(objects.h, len(q), ptr(q), ptr(out)))
+    return out.astype(bool)
+
+
+class Film:
+    """The reference's film `Vec<Vec<(f64,f64,f64,u32)>>` (render.rs:18-22) as (h, w, 4) f64 sums on the device."""
+
+    def __init__(self, width, height, device_ptr=None):
+        self.width, self.height = width, height
+        self.h = C.c_void_p()
+        if device_ptr is None:
+            check(lib().rt_film_create(width, height, C.byref(self.h)))
+        else:
+            check(lib().rt_film_create_external(width, height, C.c_void_p(device_ptr), C.byref(self.h)))
+
+    def clear(self):
+        check(lib().rt_film_clear(self.h))
+
+    def read(self):
+        out = np.zeros((self.height, self.width, 4), dtype=np.float64)
+        check(lib().rt_film_read(self.h, ptr(out)))
+        return out
+
+    def resolve_rgb8(self):
+        """`util::point_to_color` (util.rs:441-471) on the device."""
+        out = np.zeros((self.height, self.width, 3), dtype=np.uint8)
+        check(lib().rt_film_resolve_rgb8(self.h, ptr(out)))
+        return out
+
+    def close(self):
+        if self.h:
+            lib().rt_film_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def render_samples(objects, camera, int_type, film, width, height, sample_begin, sample_end, seed=0, window=None):
+    """`Integrator::render` over a pixel window and a sample range (integrator.rs:336-348): adds
+    samples [sample_begin, sample_end) of every pixel in `window` = (x0, y0, x1, y1) to `film`."""
+    x0, y0, x1, y1 = window if window is not None else (0, 0, width, height)
+    integ = N.IntegratorDesc(0, int(int_type.max_depth), 1 if int_type.invisible_light else 0, 0)
+    fd = N.FilmDesc(width, height, int(sample_begin), int(sample_end), x0, y0, x1, y1, int(seed))
+    check(lib().rt_render(objects.h, C.byref(camera.c), C.byref(integ), C.byref(fd), film.h))
+
+
+def tile_multithread(path, camera, sampler, int_type, objects, width, height, film=None, write_png=True):
+    """`render::tile_multithread(path, camera, sampler, int_type)` (render.rs:13-159): renders
+    `sampler.samples_per_pixel` samples for every pixel and (optionally) writes the tonemapped PNG to `path`.
+    The 6 worker threads / 16x16 tile queue of the reference become one wavefront on the GPU.
+    Returns the film as an (h, w, 4) array of (r, g, b, n) sums."""
+    own = film is None
+    if own:
+        film = Film(width, height)
+    render_samples(objects, camera, int_type, film, width, height, 0, sampler.samples_per_pixel, sampler.seed)
+    if write_png and path:
+        from PIL import Image
+        Image.fromarray(film.resolve_rgb8(), "RGB").save(path)
+    out = film.read()
+    if own:
+        film.close()
+    return out

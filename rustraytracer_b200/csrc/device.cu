@@ -1,0 +1,179 @@
+// Device half of the C ABI, part 1: scene upload and the ray-batch entry points
+// (rt_intersect*, rt_closest_device, rt_occluded*).  sm_100a only; there is no CPU fallback —
+// every entry point fails with RT_ERR_CUDA when no device is usable.
+#include <cstdio>
+#include <cstring>
+#include "scene.h"
+#include "traverse.cuh"
+
+namespace rt {
+
+#define CK(call)                                                                                     \
+    do {                                                                                             \
+        cudaError_t e_ = (call);                                                                     \
+        if (e_ != cudaSuccess) { set_error(std::string(#call) + ": " + cudaGetErrorString(e_)); return RT_ERR_CUDA; } \
+    } while (0)
+
+template <class T> static rt_status up(rt_scene& s, const std::vector<T>& h, const T*& dptr, uint64_t& bytes) {
+    dptr = nullptr;
+    size_t n = h.size() * sizeof(T);
+    void* p = nullptr;
+    CK(cudaMalloc(&p, n ? n : 16));
+    s.allocations.push_back(p);
+    if (n) CK(cudaMemcpy(p, h.data(), n, cudaMemcpyHostToDevice));
+    dptr = (const T*)p; bytes += n;
+    return RT_OK;
+}
+
+rt_status upload_scene(rt_scene& s, const HostImage& img) {
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) { set_error("no CUDA device: librtcore has no CPU path"); return RT_ERR_CUDA; }
+    CK(cudaGetDevice(&s.device));
+    DScene d{}; uint64_t b = 0;
+    s.bytes_nodes = s.bytes_slots = s.bytes_tables = 0;
+    rt_status st;
+    if ((st = up(s, img.nodes, d.nodes, s.bytes_nodes))) return st;
+    if ((st = up(s, img.slots, d.slots, s.bytes_slots))) return st;
+    if ((st = up(s, img.prims, d.prims, b))) return st;
+    if ((st = up(s, img.meshes, d.meshes, b))) return st;
+    if ((st = up(s, img.points, d.points, b))) return st;
+    if ((st = up(s, img.normals, d.normals, b))) return st;
+    if ((st = up(s, img.uvs, d.uvs, b))) return st;
+    if ((st = up(s, img.tri_index, d.tri_index, b))) return st;
+    if ((st = up(s, img.shapes, d.shapes, b))) return st;
+    if ((st = up(s, s.xforms, d.xforms, b))) return st;
+    if ((st = up(s, s.textures, d.textures, b))) return st;
+    if ((st = up(s, s.materials, d.materials, b))) return st;
+    if ((st = up(s, img.lights, d.lights, b))) return st;
+    s.bytes_tables = b;
+    d.n_nodes = (uint32_t)img.nodes.size(); d.n_prims = (uint32_t)img.prims.size();
+    d.n_lights = (uint32_t)img.lights.size(); d.n_slots = (uint32_t)img.slots.size();
+    s.d = d;
+    return RT_OK;
+}
+
+void free_scene_device(rt_scene& s) {
+    for (void* p : s.allocations) cudaFree(p);
+    s.allocations.clear(); s.d = DScene{}; s.committed = false;
+}
+
+// ---------------------------------------------------------------- kernels
+__global__ void __launch_bounds__(128) k_intersect(DScene sc, uint64_t n, const rt_ray* __restrict__ rays, double tmin, double tmax, rt_hit* __restrict__ hits) {
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        const double2* rp = reinterpret_cast<const double2*>(rays + i);
+        double2 a = __ldg(rp), b = __ldg(rp + 1), c = __ldg(rp + 2);
+        D3 o = mk3(a.x, a.y, b.x), d = mk3(b.y, c.x, c.y);
+        Hit h = trace_closest(sc, o, d, tmin, tmax);
+        rt_hit out; memset(&out, 0, sizeof(out));
+        out.prim_index = RT_NONE;
+        if (h.prim != RT_NONE) {
+            Rec r;
+            if (prim_record(sc, h.prim, o, d, tmin, tmax, true, r)) {
+                out.t = r.t; out.p[0] = r.p.x; out.p[1] = r.p.y; out.p[2] = r.p.z;
+                out.n[0] = r.n.x; out.n[1] = r.n.y; out.n[2] = r.n.z;
+                out.ns[0] = r.sn.x; out.ns[1] = r.sn.y; out.ns[2] = r.sn.z;
+                out.uv[0] = r.uv.x; out.uv[1] = r.uv.y; out.prim_index = h.prim; out.front = r.front ? 1u : 0u;
+            }
+        }
+        hits[i] = out;
+    }
+}
+
+__global__ void __launch_bounds__(128) k_closest(DScene sc, uint64_t n, const rt_ray* __restrict__ rays, double tmin, double tmax,
+                                                 uint32_t* __restrict__ prim, double* __restrict__ t) {
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        const double2* rp = reinterpret_cast<const double2*>(rays + i);
+        double2 a = __ldg(rp), b = __ldg(rp + 1), c = __ldg(rp + 2);
+        Hit h = trace_closest(sc, mk3(a.x, a.y, b.x), mk3(b.y, c.x, c.y), tmin, tmax);
+        prim[i] = h.prim; t[i] = h.t;
+    }
+}
+
+__global__ void __launch_bounds__(128) k_occluded(DScene sc, uint64_t n, const rt_shadow_query* __restrict__ q, uint8_t* __restrict__ out) {
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        rt_shadow_query s = q[i];
+        out[i] = unoccluded(sc, mk3(s.p0[0], s.p0[1], s.p0[2]), mk3(s.p1[0], s.p1[1], s.p1[2]), s.p1_prim_index, s.infinite_light != 0) ? 1 : 0;
+    }
+}
+
+static int grid_for(uint64_t n, int block) {
+    int dev = 0, sms = 148; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    uint64_t want = (n + block - 1) / block;
+    uint64_t cap = (uint64_t)sms * 64;                 // a multiple of the SM count; grid-stride covers the rest
+    return (int)std::max<uint64_t>(1, std::min(want, cap));
+}
+
+static rt_status check_scene(rt_scene* s, const char* who) {
+    if (!s) { set_error(std::string(who) + ": null scene"); return RT_ERR_INVALID; }
+    if (!s->committed) { set_error(std::string(who) + ": scene not committed"); return RT_ERR_STATE; }
+    CK(cudaSetDevice(s->device));
+    return RT_OK;
+}
+
+}  // namespace rt
+
+using namespace rt;
+
+extern "C" {
+
+int32_t rt_device_count(void) { int c = 0; if (cudaGetDeviceCount(&c) != cudaSuccess) return 0; return c; }
+rt_status rt_set_device(int32_t device) { CK(cudaSetDevice(device)); return RT_OK; }
+
+rt_status rt_intersect_device(rt_scene* s, uint64_t n, const rt_ray* d_rays, double tmin, double tmax, rt_hit* d_hits, void* stream) {
+    rt_status st = check_scene(s, "rt_intersect_device"); if (st) return st;
+    if (n == 0) return RT_OK;
+    if (!d_rays || !d_hits) { set_error("rt_intersect_device: null buffer"); return RT_ERR_INVALID; }
+    k_intersect<<<grid_for(n, 128), 128, 0, (cudaStream_t)stream>>>(s->d, n, d_rays, tmin, tmax, d_hits);
+    CK(cudaGetLastError());
+    return RT_OK;
+}
+rt_status rt_closest_device(rt_scene* s, uint64_t n, const rt_ray* d_rays, double tmin, double tmax, uint32_t* d_prim, double* d_t, void* stream) {
+    rt_status st = check_scene(s, "rt_closest_device"); if (st) return st;
+    if (n == 0) return RT_OK;
+    if (!d_rays || !d_prim || !d_t) { set_error("rt_closest_device: null buffer"); return RT_ERR_INVALID; }
+    k_closest<<<grid_for(n, 128), 128, 0, (cudaStream_t)stream>>>(s->d, n, d_rays, tmin, tmax, d_prim, d_t);
+    CK(cudaGetLastError());
+    return RT_OK;
+}
+rt_status rt_occluded_device(rt_scene* s, uint64_t n, const rt_shadow_query* d_q, uint8_t* d_out, void* stream) {
+    rt_status st = check_scene(s, "rt_occluded_device"); if (st) return st;
+    if (n == 0) return RT_OK;
+    if (!d_q || !d_out) { set_error("rt_occluded_device: null buffer"); return RT_ERR_INVALID; }
+    k_occluded<<<grid_for(n, 128), 128, 0, (cudaStream_t)stream>>>(s->d, n, d_q, d_out);
+    CK(cudaGetLastError());
+    return RT_OK;
+}
+
+rt_status rt_intersect_range(rt_scene* s, uint64_t n, const rt_ray* rays, double tmin, double tmax, rt_hit* hits) {
+    rt_status st = check_scene(s, "rt_intersect"); if (st) return st;
+    if (n == 0) return RT_OK;
+    if (!rays || !hits) { set_error("rt_intersect: null buffer"); return RT_ERR_INVALID; }
+    rt_ray* d_r = nullptr; rt_hit* d_h = nullptr;
+    CK(cudaMalloc(&d_r, n * sizeof(rt_ray)));
+    if (cudaMalloc(&d_h, n * sizeof(rt_hit)) != cudaSuccess) { cudaFree(d_r); set_error("rt_intersect: out of device memory"); return RT_ERR_CUDA; }
+    cudaError_t e = cudaMemcpy(d_r, rays, n * sizeof(rt_ray), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) { st = rt_intersect_device(s, n, d_r, tmin, tmax, d_h, nullptr); if (st == RT_OK) e = cudaMemcpy(hits, d_h, n * sizeof(rt_hit), cudaMemcpyDeviceToHost); }
+    cudaFree(d_r); cudaFree(d_h);
+    if (st) return st;
+    if (e != cudaSuccess) { set_error(std::string("rt_intersect: ") + cudaGetErrorString(e)); return RT_ERR_CUDA; }
+    return RT_OK;
+}
+// geometry::get_intersection (geometry.rs:238-240): (SMALL, INFINITY)
+rt_status rt_intersect(rt_scene* s, uint64_t n, const rt_ray* rays, rt_hit* hits) { return rt_intersect_range(s, n, rays, SMALL, INF, hits); }
+
+rt_status rt_occluded(rt_scene* s, uint64_t n, const rt_shadow_query* q, uint8_t* out) {
+    rt_status st = check_scene(s, "rt_occluded"); if (st) return st;
+    if (n == 0) return RT_OK;
+    if (!q || !out) { set_error("rt_occluded: null buffer"); return RT_ERR_INVALID; }
+    rt_shadow_query* d_q = nullptr; uint8_t* d_o = nullptr;
+    CK(cudaMalloc(&d_q, n * sizeof(rt_shadow_query)));
+    if (cudaMalloc(&d_o, n) != cudaSuccess) { cudaFree(d_q); set_error("rt_occluded: out of device memory"); return RT_ERR_CUDA; }
+    cudaError_t e = cudaMemcpy(d_q, q, n * sizeof(rt_shadow_query), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) { st = rt_occluded_device(s, n, d_q, d_o, nullptr); if (st == RT_OK) e = cudaMemcpy(out, d_o, n, cudaMemcpyDeviceToHost); }
+    cudaFree(d_q); cudaFree(d_o);
+    if (st) return st;
+    if (e != cudaSuccess) { set_error(std::string("rt_occluded: ") + cudaGetErrorString(e)); return RT_ERR_CUDA; }
+    return RT_OK;
+}
+
+}  // extern "C"

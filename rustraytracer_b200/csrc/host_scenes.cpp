@@ -1,0 +1,562 @@
+// Host scene layer: the reference's scene functions (scenes.rs), OBJ ingest (parser.rs), and the
+// deterministic stand-ins / generators of SURVEY.md §8d.  Not on the hot path.
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <string>
+#include <tuple>
+#include <vector>
+#include "rt_internal.h"
+#include "../../include/rthost.h"
+
+using rt::PI;
+using rt::SMALL;
+
+struct rth_scene {
+    std::vector<rt::HostMesh> meshes;
+    // primitives in order; a triangle run of a mesh is kept implicit
+    struct Item { bool run; rt_primitive prim; uint32_t mesh, mat; };
+    std::vector<Item> items;
+    std::vector<std::pair<uint64_t, uint32_t>> light_sets;   // (prim index, light index) applied after expansion
+    std::vector<double> xforms;                               // 16 each
+    std::vector<rt_texture> textures;
+    std::vector<rt_material> materials;
+    std::vector<rt_light> lights;
+    rt_camera camera{};
+    std::string png;
+    bool standin = false;
+
+    uint64_t n_prims() const { uint64_t n = 0; for (auto& it : items) n += it.run ? meshes[it.mesh].ind.size() / 3 : 1; return n; }
+};
+
+namespace {
+
+// ---- small constructors mirroring the reference's
+uint32_t push_solid(rth_scene& s, double r, double g, double b) {                  // Texture::new_solid_color
+    rt_texture t{}; t.type = RT_TEX_SOLID; t.color[0] = r; t.color[1] = g; t.color[2] = b; s.textures.push_back(t); return (uint32_t)s.textures.size() - 1;
+}
+uint32_t push_checkered(rth_scene& s, uint32_t even, uint32_t odd, double freq) {  // Texture::new_checkered(even, odd, f) material.rs:622-628
+    rt_texture t{}; t.type = RT_TEX_CHECKERED; t.even = even; t.odd = odd; t.frequency = freq; s.textures.push_back(t); return (uint32_t)s.textures.size() - 1;
+}
+rt_material mat_base(uint32_t type) { rt_material m{}; m.type = type; for (int k = 0; k < 5; k++) m.tex[k] = RT_NONE; return m; }
+uint32_t push_matte(rth_scene& s, uint32_t kd, double sigma) { rt_material m = mat_base(RT_MAT_MATTE); m.tex[0] = kd; m.f[0] = sigma; s.materials.push_back(m); return (uint32_t)s.materials.size() - 1; }
+uint32_t push_light_mat(rth_scene& s, uint32_t tex) { rt_material m = mat_base(RT_MAT_LIGHT); m.tex[0] = tex; s.materials.push_back(m); return (uint32_t)s.materials.size() - 1; }
+uint32_t push_plastic(rth_scene& s, uint32_t kd, uint32_t ks, double rough, bool remap) { rt_material m = mat_base(RT_MAT_PLASTIC); m.tex[0] = kd; m.tex[1] = ks; m.f[0] = rough; m.remap_roughness = remap; s.materials.push_back(m); return (uint32_t)s.materials.size() - 1; }
+uint32_t push_glass(rth_scene& s, uint32_t kr, uint32_t kt, double ur, double vr, double index, bool remap) { rt_material m = mat_base(RT_MAT_GLASS); m.tex[0] = kr; m.tex[1] = kt; m.f[0] = ur; m.f[1] = vr; m.f[2] = index; m.remap_roughness = remap; s.materials.push_back(m); return (uint32_t)s.materials.size() - 1; }
+// Material::make_metal(eta_id, k_id, u_r_id, v_r_id, r_id, bump, remap) (material.rs:452-470)
+uint32_t push_metal(rth_scene& s, uint32_t eta, uint32_t k, uint32_t ur, uint32_t vr, uint32_t r, bool remap) { rt_material m = mat_base(RT_MAT_METAL); m.tex[0] = eta; m.tex[1] = k; m.tex[2] = r; m.tex[3] = ur; m.tex[4] = vr; m.remap_roughness = remap; s.materials.push_back(m); return (uint32_t)s.materials.size() - 1; }
+uint32_t push_mirror(rth_scene& s, uint32_t c) { rt_material m = mat_base(RT_MAT_MIRROR); m.tex[0] = c; s.materials.push_back(m); return (uint32_t)s.materials.size() - 1; }
+
+rt_primitive prim_base(uint32_t type, uint32_t mat) { rt_primitive p{}; p.type = type; p.mat_index = mat; p.light_index = RT_NONE; p.transform = RT_NONE; return p; }
+rt_primitive make_sphere(double cx, double cy, double cz, double r, uint32_t mat) { rt_primitive p = prim_base(RT_PRIM_SPHERE, mat); p.v[0] = cx; p.v[1] = cy; p.v[2] = cz; p.v[3] = r; return p; }
+rt_primitive make_rect(uint32_t type, double a0, double b0, double a1, double b1, double k, uint32_t mat, uint32_t xf = RT_NONE) {
+    rt_primitive p = prim_base(type, mat); p.v[0] = a0; p.v[1] = b0; p.v[2] = a1; p.v[3] = b1; p.v[4] = k; p.transform = xf; return p;
+}
+rt_primitive flip(rt_primitive p) { p.flip_face = 1; return p; }
+uint64_t push_prim(rth_scene& s, const rt_primitive& p) { uint64_t i = s.n_prims(); rth_scene::Item it{}; it.run = false; it.prim = p; s.items.push_back(it); return i; }
+uint64_t push_mesh_triangles(rth_scene& s, uint32_t mesh, uint32_t mat) { uint64_t i = s.n_prims(); rth_scene::Item it{}; it.run = true; it.mesh = mesh; it.mat = mat; s.items.push_back(it); return i; }
+uint32_t push_diffuse_light(rth_scene& s, uint64_t prim, double r, double g, double b, bool two_sided) {   // Light::make_diffuse_light light.rs:585-606
+    rt_light l{}; l.type = RT_LIGHT_DIFFUSE; l.prim_index = (uint32_t)prim; l.two_sided = two_sided; l.color[0] = r; l.color[1] = g; l.color[2] = b;
+    s.lights.push_back(l); return (uint32_t)s.lights.size() - 1;
+}
+uint32_t push_xform(rth_scene& s, const double m[16]) { s.xforms.insert(s.xforms.end(), m, m + 16); return (uint32_t)(s.xforms.size() / 16) - 1; }
+
+void camera(rth_scene& s, const double from[3], const double to[3], double aspect, double vfov, double aperture, double focus, double t0, double t1) {
+    double up[3] = {0., 1., 0.};
+    rt_camera_look_at(from, to, up, aspect, vfov, aperture, focus, t0, t1, &s.camera);
+}
+
+// ---- 4x4 helpers (row-major)
+void mat_identity(double m[16]) { for (int i = 0; i < 16; i++) m[i] = (i % 5 == 0) ? 1. : 0.; }
+void mat_mul(const double a[16], const double b[16], double o[16]) {
+    double r[16];
+    for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) { double acc = 0.; for (int k = 0; k < 4; k++) acc += a[4 * i + k] * b[4 * k + j]; r[4 * i + j] = acc; }
+    memcpy(o, r, sizeof(r));
+}
+void mat_translate(double x, double y, double z, double m[16]) { mat_identity(m); m[3] = x; m[7] = y; m[11] = z; }
+void mat_scale(double s, double m[16]) { mat_identity(m); m[0] = m[5] = m[10] = s; }
+// Rotation3::from_euler_angles(roll, pitch, yaw) = Rz(yaw) * Ry(pitch) * Rx(roll) (nalgebra)
+void mat_euler(double roll, double pitch, double yaw, double m[16]) {
+    double sr = std::sin(roll), cr = std::cos(roll), sp = std::sin(pitch), cp = std::cos(pitch), sy = std::sin(yaw), cy = std::cos(yaw);
+    mat_identity(m);
+    m[0] = cy * cp; m[1] = cy * sp * sr - sy * cr; m[2] = cy * sp * cr + sy * sr;
+    m[4] = sy * cp; m[5] = sy * sp * sr + cy * cr; m[6] = sy * sp * cr - cy * sr;
+    m[8] = -sp;     m[9] = cp * sr;                m[10] = cp * cr;
+}
+void xf_point(const double* m, const double p[3], double o[3]) {
+    double x = m[0] * p[0] + m[1] * p[1] + m[2] * p[2] + m[3], y = m[4] * p[0] + m[5] * p[1] + m[6] * p[2] + m[7];
+    double z = m[8] * p[0] + m[9] * p[1] + m[10] * p[2] + m[11], w = m[12] * p[0] + m[13] * p[1] + m[14] * p[2] + m[15];
+    o[0] = x / w; o[1] = y / w; o[2] = z / w;
+}
+void xf_vector(const double* m, const double v[3], double o[3]) {
+    o[0] = m[0] * v[0] + m[1] * v[1] + m[2] * v[2]; o[1] = m[4] * v[0] + m[5] * v[1] + m[6] * v[2]; o[2] = m[8] * v[0] + m[9] * v[1] + m[10] * v[2];
+}
+
+// ---- Philox4x32-10 for the generators
+void philox(uint32_t c[4], uint32_t k0, uint32_t k1) {
+    for (int r = 0; r < 10; r++) {
+        uint64_t p0 = (uint64_t)0xD2511F53u * c[0], p1 = (uint64_t)0xCD9E8D57u * c[2];
+        uint32_t n0 = (uint32_t)(p1 >> 32) ^ c[1] ^ k0, n1 = (uint32_t)p1, n2 = (uint32_t)(p0 >> 32) ^ c[3] ^ k1, n3 = (uint32_t)p0;
+        c[0] = n0; c[1] = n1; c[2] = n2; c[3] = n3; k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+}
+struct Gen {   // sequential uniform stream
+    uint64_t key; uint64_t ctr = 0; uint32_t buf[4]; int have = 0;
+    explicit Gen(uint64_t k) : key(k) {}
+    uint32_t u32() { if (!have) { buf[0] = (uint32_t)ctr; buf[1] = (uint32_t)(ctr >> 32); buf[2] = 0; buf[3] = 0; ctr++; philox(buf, (uint32_t)key, (uint32_t)(key >> 32)); have = 4; } return buf[--have]; }
+    double uniform() { return (double)(u32() >> 8) * (1.0 / 16777216.0); }            // 24-bit, f32-exact
+    double range(double a, double b) { return a + (b - a) * uniform(); }
+};
+
+// ---- stand-in meshes --------------------------------------------------------------------------
+// Closed genus-0 "blob": a lat-long sphere (n_u around, n_v rings incl. poles) with multi-octave
+// sinusoidal displacement, scaled into a bounding box.  Triangles: 2*n_u*(n_v-1).  Smooth vertex
+// normals (area-weighted), no uvs — like the Stanford dragon OBJ the reference loads.
+void append_blob(rt::HostMesh& m, uint32_t n_u, uint32_t n_v, uint64_t seed, const double lo[3], const double hi[3]) {
+    Gen g(seed);
+    const int OCT = 6;
+    double amp[OCT], fu[OCT], fv[OCT], pu[OCT], pv[OCT];
+    double a = 0.22;
+    for (int k = 0; k < OCT; k++) { amp[k] = a; a *= 0.55; fu[k] = (double)(2 + (int)(g.uniform() * 3.) + 3 * k * k); fv[k] = (double)(1 + (int)(g.uniform() * 3.) + 2 * k * k); pu[k] = g.range(0., 6.28318); pv[k] = g.range(0., 6.28318); }
+    uint32_t base = (uint32_t)(m.p.size() / 3);
+    auto radius = [&](double phi, double theta) {
+        double r = 1.0;
+        for (int k = 0; k < OCT; k++) r += amp[k] * std::sin(fu[k] * phi + pu[k]) * std::sin(fv[k] * theta + pv[k]) * std::sin(theta);
+        return r;
+    };
+    std::vector<double> pts;
+    auto put = [&](double phi, double theta) {
+        double r = radius(phi, theta), st = std::sin(theta);
+        pts.push_back(r * st * std::cos(phi)); pts.push_back(r * std::cos(theta)); pts.push_back(r * st * std::sin(phi));
+    };
+    put(0., 0.);                                                       // north pole
+    for (uint32_t j = 1; j < n_v; j++) for (uint32_t i = 0; i < n_u; i++) put(2. * M_PI * i / n_u, M_PI * j / n_v);
+    put(0., M_PI);                                                     // south pole
+    // fit into [lo,hi]
+    double mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
+    for (size_t i = 0; i < pts.size(); i += 3) for (int k = 0; k < 3; k++) { mn[k] = std::min(mn[k], pts[i + k]); mx[k] = std::max(mx[k], pts[i + k]); }
+    for (size_t i = 0; i < pts.size(); i += 3) for (int k = 0; k < 3; k++) {
+        double v = lo[k] + (pts[i + k] - mn[k]) / (mx[k] - mn[k]) * (hi[k] - lo[k]);
+        pts[i + k] = (double)(float)v;                                 // OBJ values are f32 (tobj) widened to f64
+    }
+    uint32_t nvert = (uint32_t)(pts.size() / 3), south = nvert - 1;
+    auto ring = [&](uint32_t j, uint32_t i) { return 1 + (j - 1) * n_u + (i % n_u); };
+    std::vector<uint32_t> idx;
+    for (uint32_t i = 0; i < n_u; i++) { idx.push_back(0); idx.push_back(ring(1, i + 1)); idx.push_back(ring(1, i)); }
+    for (uint32_t j = 1; j + 1 < n_v; j++) for (uint32_t i = 0; i < n_u; i++) {
+        uint32_t a0 = ring(j, i), a1 = ring(j, i + 1), b0 = ring(j + 1, i), b1 = ring(j + 1, i + 1);
+        idx.push_back(a0); idx.push_back(a1); idx.push_back(b0);
+        idx.push_back(a1); idx.push_back(b1); idx.push_back(b0);
+    }
+    for (uint32_t i = 0; i < n_u; i++) { idx.push_back(south); idx.push_back(ring(n_v - 1, i)); idx.push_back(ring(n_v - 1, i + 1)); }
+    std::vector<double> nrm(pts.size(), 0.);
+    for (size_t t = 0; t < idx.size(); t += 3) {
+        const double* p0 = &pts[3 * idx[t]]; const double* p1 = &pts[3 * idx[t + 1]]; const double* p2 = &pts[3 * idx[t + 2]];
+        double e1[3] = {p1[0] - p0[0], p1[1] - p0[1], p1[2] - p0[2]}, e2[3] = {p2[0] - p0[0], p2[1] - p0[1], p2[2] - p0[2]};
+        double c[3] = {e1[1] * e2[2] - e1[2] * e2[1], e1[2] * e2[0] - e1[0] * e2[2], e1[0] * e2[1] - e1[1] * e2[0]};
+        for (int v = 0; v < 3; v++) for (int k = 0; k < 3; k++) nrm[3 * idx[t + v] + k] += c[k];
+    }
+    for (size_t i = 0; i < nrm.size(); i += 3) {
+        double l = std::sqrt(nrm[i] * nrm[i] + nrm[i + 1] * nrm[i + 1] + nrm[i + 2] * nrm[i + 2]);
+        if (l > 0.) for (int k = 0; k < 3; k++) nrm[i + k] = (double)(float)(nrm[i + k] / l); else { nrm[i] = 0.; nrm[i + 1] = 1.; nrm[i + 2] = 0.; }
+    }
+    m.p.insert(m.p.end(), pts.begin(), pts.end());
+    m.n.insert(m.n.end(), nrm.begin(), nrm.end());
+    for (uint32_t v : idx) m.ind.push_back(base + v);
+}
+
+// Stand-in for data/dragon/dragon.obj (missing blob): exactly 871,414 triangles =
+// 2*660*659 (body) + 2*13*59 (a small second component), in the box the reference's camera frames.
+void dragon_standin(rt::HostMesh& m, uint64_t seed, double tx) {
+    double lo[3] = {-3.8 + tx, -2.83, -1.7}, hi[3] = {3.8 + tx, 2.53, 1.7};
+    append_blob(m, 660, 660, seed, lo, hi);
+    double lo2[3] = {2.6 + tx, 2.0, -0.4}, hi2[3] = {3.4 + tx, 2.9, 0.4};
+    append_blob(m, 13, 60, seed + 1, lo2, hi2);
+}
+// Stand-in for data/statue.obj inside the Cornell box (scenes.rs:289-292 places it around (374,*,130))
+void statue_standin(rt::HostMesh& m, uint64_t seed, uint64_t n_tris) {
+    uint32_t n = n_tris ? (uint32_t)std::max(8.0, std::sqrt((double)n_tris / 2.)) : 500;
+    double lo[3] = {190., 0., 140.}, hi[3] = {365., 420., 300.};
+    append_blob(m, n, n + 1, seed, lo, hi);
+}
+
+// ---- parser::parse_obj (parser.rs:8-87) over a tobj-2.0.2-style loader -------------------------
+bool load_obj(const char* path, const double* xf, rt::HostMesh& out, std::string& err) {
+    FILE* f = fopen(path, "rb");
+    if (!f) { err = std::string("cannot open ") + path; return false; }
+    std::vector<float> v, vn, vt;
+    std::map<std::tuple<int, int, int>, uint32_t> remap;      // tobj reindexes (v,vt,vn) triples to a single index
+    std::vector<float> pos, nor, tex; std::vector<uint32_t> ind;
+    char line[4096]; bool have_faces = false, done = false;
+    while (!done && fgets(line, sizeof(line), f)) {
+        char* p = line; while (*p == ' ' || *p == '\t') p++;
+        if (p[0] == 'v' && (p[1] == ' ' || p[1] == '\t')) { float a = 0, b = 0, c = 0; sscanf(p + 2, "%f %f %f", &a, &b, &c); v.push_back(a); v.push_back(b); v.push_back(c); }
+        else if (p[0] == 'v' && p[1] == 'n') { float a = 0, b = 0, c = 0; sscanf(p + 3, "%f %f %f", &a, &b, &c); vn.push_back(a); vn.push_back(b); vn.push_back(c); }
+        else if (p[0] == 'v' && p[1] == 't') { float a = 0, b = 0; sscanf(p + 3, "%f %f", &a, &b); vt.push_back(a); vt.push_back(b); }
+        else if (p[0] == 'f' && (p[1] == ' ' || p[1] == '\t')) {
+            std::vector<uint32_t> poly;
+            char* q = p + 1;
+            for (;;) {
+                while (*q == ' ' || *q == '\t') q++;
+                if (*q == 0 || *q == '\n' || *q == '\r' || *q == '#') break;
+                int iv = 0, it = 0, in = 0; bool ht = false, hn = false;
+                iv = (int)strtol(q, &q, 10);
+                if (*q == '/') { q++; if (*q != '/') { it = (int)strtol(q, &q, 10); ht = true; } if (*q == '/') { q++; in = (int)strtol(q, &q, 10); hn = true; } }
+                int nv = (int)(v.size() / 3), nt = (int)(vt.size() / 2), nn = (int)(vn.size() / 3);
+                iv = iv < 0 ? nv + iv : iv - 1; it = ht ? (it < 0 ? nt + it : it - 1) : -1; in = hn ? (in < 0 ? nn + in : in - 1) : -1;
+                if (iv < 0 || iv >= nv) { err = "face index out of range"; fclose(f); return false; }
+                auto key = std::make_tuple(iv, it, in);
+                auto found = remap.find(key);
+                uint32_t id;
+                if (found == remap.end()) {
+                    id = (uint32_t)(pos.size() / 3); remap[key] = id;
+                    pos.push_back(v[3 * iv]); pos.push_back(v[3 * iv + 1]); pos.push_back(v[3 * iv + 2]);
+                    if (it >= 0 && it < nt) { tex.push_back(vt[2 * it]); tex.push_back(vt[2 * it + 1]); }
+                    if (in >= 0 && in < nn) { nor.push_back(vn[3 * in]); nor.push_back(vn[3 * in + 1]); nor.push_back(vn[3 * in + 2]); }
+                } else id = found->second;
+                poly.push_back(id);
+            }
+            for (size_t k = 1; k + 1 < poly.size(); k++) { ind.push_back(poly[0]); ind.push_back(poly[k]); ind.push_back(poly[k + 1]); }   // fan triangulation
+            have_faces = true;
+        } else if ((p[0] == 'o' || p[0] == 'g') && (p[1] == ' ' || p[1] == '\t' || p[1] == '\n' || p[1] == '\r')) {
+            if (have_faces) done = true;     // only models[0] is used (parser.rs:21)
+        }
+    }
+    fclose(f);
+    if (ind.empty()) { err = std::string("no faces in ") + path; return false; }
+    size_t np = pos.size() / 3;
+    out.p.resize(3 * np);
+    for (size_t i = 0; i < np; i++) { double pt[3] = {(double)pos[3 * i], (double)pos[3 * i + 1], (double)pos[3 * i + 2]}, o[3]; xf_point(xf, pt, o); out.p[3 * i] = o[0]; out.p[3 * i + 1] = o[1]; out.p[3 * i + 2] = o[2]; }
+    if (nor.size() == pos.size()) {
+        out.n.resize(3 * np);
+        for (size_t i = 0; i < np; i++) { double vv[3] = {(double)nor[3 * i], (double)nor[3 * i + 1], (double)nor[3 * i + 2]}, o[3]; xf_vector(xf, vv, o); out.n[3 * i] = o[0]; out.n[3 * i + 1] = o[1]; out.n[3 * i + 2] = o[2]; }
+    }
+    if (tex.size() / 2 == np) { out.uv.resize(2 * np); for (size_t i = 0; i < 2 * np; i++) out.uv[i] = (double)tex[i]; }
+    out.ind = std::move(ind);
+    return true;
+}
+bool file_exists(const std::string& p) { FILE* f = fopen(p.c_str(), "rb"); if (f) { fclose(f); return true; } return false; }
+
+}  // namespace
+
+namespace {
+
+double aspect_of(const rth_params& p) { return (double)p.width / (double)p.height; }   // GLOBAL_STATE.get_aspect_ratio()
+
+// dragon mesh `which` (0: at origin, 1: translated by (5,0,0) — scenes.rs:551-552), real OBJ when available
+uint32_t add_dragon(rth_scene& s, const rth_params& p, double tx) {
+    rt::HostMesh m;
+    std::string path = p.data_dir ? std::string(p.data_dir) + "/dragon/dragon.obj" : std::string();
+    bool loaded = false;
+    if (!path.empty() && file_exists(path)) {
+        double xf[16]; mat_scale(10., xf); xf[3] = tx;      // Similarity3::new(translation, 0, 10.).to_homogeneous()
+        std::string err; loaded = load_obj(path.c_str(), xf, m, err);
+    }
+    if (!loaded) { dragon_standin(m, p.seed ? p.seed : 7, tx); s.standin = true; }
+    s.meshes.push_back(std::move(m));
+    return (uint32_t)s.meshes.size() - 1;
+}
+
+// scenes.rs:474-546
+void build_sphere_roughness(rth_scene& s, const rth_params& p) {
+    double from[3] = {-8.5, 5., 0.}, to[3] = {0., -0.15, -0.08};
+    camera(s, from, to, aspect_of(p), 70., 0.0, 10., 0., 0.);
+    uint32_t t0 = push_solid(s, 0.4 * 2., 0.15 * 2., 0.15 * 2.);        // light_gray
+    uint32_t t1 = push_solid(s, 0.15 * 2., 0.15 * 2., 0.4 * 2.);        // dark_gray
+    push_checkered(s, t0, t1, 0.1);                                      // 2
+    push_solid(s, 15., 15., 15.);                                        // 3
+    push_matte(s, 2, 0.);                                                // mat 0
+    const double space = 2.8;
+    for (int i = 1; i < 9; i++) {
+        uint32_t len = (uint32_t)s.textures.size();
+        push_solid(s, ((double)(i - 1)) / 90. + SMALL, 0., 0.);          // roughness
+        push_solid(s, 0., 0., 0.);                                       // eta = black
+        push_solid(s, 1., 1., 1.);                                       // k = white
+        push_metal(s, len + 1, len + 2, RT_NONE, RT_NONE, len, true);
+        push_prim(s, make_sphere(0., 1., -space * 4.5 + space * (double)i, 1., (uint32_t)i));
+    }
+    push_prim(s, make_rect(RT_PRIM_XZ_RECT, -10000., -10000., 10000., 10000., -0.01, 0));
+    rt_primitive light = make_rect(RT_PRIM_XZ_RECT, -10., -10., 10., 10., 50., (uint32_t)s.materials.size() - 1);
+    light.light_index = 0;
+    uint64_t li = push_prim(s, flip(light));
+    push_diffuse_light(s, li, 10., 10., 10., false);
+    s.png = "metal_spheres.png";
+}
+
+// the commented make_world (scenes.rs:15-86), regenerated with a fixed seed (its util::rand is unseeded and its
+// sky no longer exists) plus sphere_roughness's rect light: Lambertian + mirror + glass spheres
+void build_make_world(rth_scene& s, const rth_params& p) {
+    double from[3] = {13., 2., 3.}, to[3] = {0., 0., 0.};
+    camera(s, from, to, aspect_of(p), 20., 0.16 * 0., 10., 0., 0.);      // aperture 0: the lens path draws but does not move rays
+    Gen g(p.seed ? p.seed : 1);
+    push_solid(s, 201. / 256., 201. / 256., 201. / 256.);
+    push_solid(s, 51. / 256., 75.5 / 256., 25.5 / 256.);
+    push_checkered(s, 0, 1, 4.);
+    push_matte(s, 2, 0.);
+    push_prim(s, make_sphere(0., -10000., 0., 10000., 0));
+    for (int a = -11; a < 11; a++) for (int b = -11; b < 11; b++) {
+        double cx = a + 0.9 * g.uniform(), cz = b + 0.9 * g.uniform();
+        double dx = cx - 4., dz = cz;
+        if (std::sqrt(dx * dx + dz * dz) <= 0.9) continue;
+        double mat = g.uniform();
+        uint32_t m;
+        if (mat < 0.6) { uint32_t t = push_solid(s, 255. * g.uniform() * g.range(0.4, 0.8) / 256., 255. * g.uniform() * g.range(0.4, 0.8) / 256., 255. * g.uniform() * g.range(0.4, 0.8) / 256.); m = push_matte(s, t, 0.); }
+        else if (mat < 0.86) { uint32_t t = push_solid(s, g.range(30., 200.) / 256., g.range(30., 200.) / 256., g.range(30., 200.) / 256.); m = push_mirror(s, t); }
+        else { uint32_t t = push_solid(s, g.range(0.5, 1.), g.range(0.5, 1.), g.range(0.5, 1.)); m = push_glass(s, t, t, 0., 0., g.range(1.2, 1.8), true); }
+        push_prim(s, make_sphere(cx, 0.2, cz, 0.2, m));
+    }
+    { uint32_t t = push_solid(s, 0.5, 0.5, 0.5); push_prim(s, make_sphere(-4., 1., 0., 1., push_matte(s, t, 45.))); }   // Perlin texture is out of scope: grey Oren–Nayar
+    { uint32_t t = push_solid(s, 1., 1., 1.); push_prim(s, make_sphere(0., 1., 0., 1., push_glass(s, t, t, 0., 0., 1.3, true))); }
+    { uint32_t e = push_solid(s, 223.5 / 256., 85. / 256., 32.5 / 256.), k = push_solid(s, 0., 0., 0.), r = push_solid(s, 0.02, 0., 0.);
+      push_prim(s, make_sphere(4., 1., 0., 1., push_metal(s, e, k, r, r, r, true))); }
+    uint32_t lt = push_solid(s, 15., 15., 15.);
+    rt_primitive light = make_rect(RT_PRIM_XZ_RECT, -10., -10., 10., 10., 50., push_light_mat(s, lt));
+    light.light_index = 0;
+    uint64_t li = push_prim(s, flip(light));
+    push_diffuse_light(s, li, 10., 10., 10., false);
+    s.png = "sphere_world.png";
+}
+
+void cornell_walls(rth_scene& s, uint32_t green, uint32_t red, uint32_t white_m, uint32_t light_mat, bool flip_light) {
+    push_prim(s, flip(make_rect(RT_PRIM_YZ_RECT, 0., 0., 555., 555., 555., green)));
+    push_prim(s, make_rect(RT_PRIM_YZ_RECT, 0., 0., 555., 555., 0., red));
+    rt_primitive light = make_rect(RT_PRIM_XZ_RECT, 213., 227., 343., 332., 554.9, light_mat);
+    light.light_index = 0;
+    push_prim(s, flip_light ? flip(light) : light);
+    push_prim(s, make_rect(RT_PRIM_XZ_RECT, 0., 0., 555., 555., 0., white_m));
+    push_prim(s, flip(make_rect(RT_PRIM_XZ_RECT, 0., 0., 555., 555., 555., white_m)));
+    push_prim(s, flip(make_rect(RT_PRIM_XY_RECT, 0., 0., 555., 555., 555., white_m)));
+}
+// Cube::get_sides (hittable.rs:787-846): z0, z1, y0, y1, x0, x1
+void push_cube(rth_scene& s, const double mn[3], const double mx[3], uint32_t mat, uint32_t xf) {
+    push_prim(s, flip(make_rect(RT_PRIM_XY_RECT, mn[0], mn[1], mx[0], mx[1], mn[2], mat, xf)));
+    push_prim(s, make_rect(RT_PRIM_XY_RECT, mn[0], mn[1], mx[0], mx[1], mx[2], mat, xf));
+    push_prim(s, flip(make_rect(RT_PRIM_XZ_RECT, mn[0], mn[2], mx[0], mx[2], mn[1], mat, xf)));
+    push_prim(s, make_rect(RT_PRIM_XZ_RECT, mn[0], mn[2], mx[0], mx[2], mx[1], mat, xf));
+    push_prim(s, flip(make_rect(RT_PRIM_YZ_RECT, mn[1], mn[2], mx[1], mx[2], mn[0], mat, xf)));
+    push_prim(s, make_rect(RT_PRIM_YZ_RECT, mn[1], mn[2], mx[1], mx[2], mx[0], mat, xf));
+}
+// scenes.rs:89-197
+void build_cornell_box(rth_scene& s, const rth_params& p) {
+    double from[3] = {278., 278., -800.}, to[3] = {278., 278., 0.};
+    camera(s, from, to, aspect_of(p), 40., 0., 10., 0., 1.);
+    push_solid(s, 0.65, 0.05, 0.05); push_solid(s, 0.73, 0.73, 0.73); push_solid(s, 0.12, 0.45, 0.15); push_solid(s, 28.0, 28.0, 28.0);
+    push_matte(s, 0, 0.); push_matte(s, 1, 0.); push_matte(s, 2, 0.); push_light_mat(s, 3);
+    cornell_walls(s, 2, 0, 1, 3, true);
+    push_diffuse_light(s, 2, 15., 15., 15., false);
+    double t1[16], t2[16], r1[16], r2[16], first[16], second[16];
+    mat_translate(265., 0., 295., t1); mat_translate(130., 0., 65., t2);
+    mat_euler(0., 15. * PI / 180., 0., r1); mat_euler(0., -18. * PI / 180., 0., r2);
+    mat_mul(t1, r1, first); mat_mul(t2, r2, second);
+    double z[3] = {0., 0., 0.}, c1[3] = {165., 165., 165.}, c2[3] = {165., 330., 165.};
+    uint32_t xs = push_xform(s, second); push_cube(s, z, c1, 1, xs);
+    uint32_t xf = push_xform(s, first); push_cube(s, z, c2, 1, xf);
+    s.png = "cornell_box.png";
+}
+// scenes.rs:200-307
+void build_cornell_box_statue(rth_scene& s, const rth_params& p) {
+    double from[3] = {278., 278., -800.}, to[3] = {278., 278., 0.};
+    camera(s, from, to, aspect_of(p), 40., 0., 10., 0., 1.);
+    push_solid(s, 0.65, 0.05, 0.05); push_solid(s, 0.73, 0.73, 0.73); push_solid(s, 0.12, 0.45, 0.15);
+    push_solid(s, 1., 1., 1.); push_solid(s, 0.3, 0.3, 0.3); push_solid(s, 0.01, 0., 0.);
+    double sc = 0.2 / 0.3765;
+    push_solid(s, 0.1514 * sc, 0.0139 * sc, 0.3765 * sc); push_solid(s, 1.13, 1.13, 1.13);
+    push_matte(s, 1, 0.); push_matte(s, 0, 0.); push_matte(s, 2, 0.);
+    if (p.variant == 1) push_metal(s, 5, 3, 5, 5, 5, true);               // scenes.rs:244-246 as committed
+    else push_matte(s, 1, 0.);                                            // the commented matte alternative (scenes.rs:243), BASELINE config 2 "Lambertian"
+    cornell_walls(s, 2, 1, 0, 0, false);
+    push_diffuse_light(s, 2, 0.97 * 25., 0.92 * 25., 0.23 * 25., true);
+    rt::HostMesh m; bool loaded = false;
+    std::string path = p.data_dir ? std::string(p.data_dir) + "/statue.obj" : std::string();
+    if (!path.empty() && file_exists(path)) {
+        double tr[16], r1[16], scl[16], tmp[16], xf[16];
+        mat_translate(374., 435., 130., tr); mat_euler(0., 0., PI, r1); mat_scale(0.86, scl);
+        mat_mul(tr, r1, tmp); mat_mul(tmp, scl, xf);
+        std::string err; loaded = load_obj(path.c_str(), xf, m, err);
+    }
+    if (!loaded) { statue_standin(m, p.seed ? p.seed : 11, p.n_tris); s.standin = true; }
+    s.meshes.push_back(std::move(m));
+    push_mesh_triangles(s, 0, 3);
+    s.png = "cornell_statue.png";
+}
+// scenes.rs:310-375 (variant 0) and the commented metal_dragon (scenes.rs:424-471, variant 1) with the
+// two_dragons metal parameters (scenes.rs:582-606) and plastic_dragon's light
+void build_plastic_dragon(rth_scene& s, const rth_params& p) {
+    uint32_t mesh = add_dragon(s, p, 0.);
+    double radians = 5. * (PI / 180.), r = std::sqrt(82.26);
+    double from[3] = {r * std::sin(radians + PI / 4.4), 4., r * std::cos(radians + PI / 4.4)}, to[3] = {0., -0.15, -0.08};
+    camera(s, from, to, aspect_of(p), 70., 0.0, 10., 0., 0.);
+    uint32_t t0 = push_solid(s, 0.4 * 2., 0.15 * 2., 0.15 * 2.), t1 = push_solid(s, 0.15 * 2., 0.15 * 2., 0.4 * 2.);
+    push_checkered(s, t0, t1, p.variant == 1 ? 0.1 : 10000.);                                     // 2
+    uint32_t dragon_mat;
+    if (p.variant == 1) {
+        uint32_t eta = push_solid(s, 0.05, 0.5, 0.75), k = push_solid(s, 0., 0., 0.), rough = push_solid(s, 0.1, 0., 0.);
+        push_matte(s, 2, 0.);
+        dragon_mat = push_metal(s, eta, k, rough, rough, rough, true);
+    } else {
+        double sc = 0.56 / 0.3765;
+        push_solid(s, 0.1514 * sc, 0.0139 * sc, 0.3765 * sc);                                     // 3 purple
+        push_solid(s, 1., 1., 1.);                                                                // 4 spec
+        push_matte(s, 2, 0.);
+        dragon_mat = push_plastic(s, 3, 4, 0.001, true);
+    }
+    push_prim(s, make_rect(RT_PRIM_XZ_RECT, -10000., -10000., 10000., 10000., -2.83, 0));
+    push_mesh_triangles(s, mesh, dragon_mat);
+    rt_primitive light = make_rect(RT_PRIM_XZ_RECT, -5., -5., 5., 5., 15., 0);
+    light.light_index = 0;
+    uint64_t li = push_prim(s, flip(light));
+    push_diffuse_light(s, li, 4., 4., 4., false);
+    s.png = p.variant == 1 ? "metal_dragon.png" : "plastic_dragon.png";
+}
+// scenes.rs:549-624; variant 1 enables the commented block :608-611 (glass dragon = mesh 0, material 2)
+void build_two_dragons(rth_scene& s, const rth_params& p) {
+    uint32_t m0 = add_dragon(s, p, 0.), m1 = add_dragon(s, p, 5.);
+    double from[3] = {-8.5, 5., 0.}, to[3] = {0., -0.15, -0.08};
+    camera(s, from, to, aspect_of(p), 60., 0.0, 10., 0., 0.);
+    uint32_t t0 = push_solid(s, 0.4 * 2., 0.15 * 2., 0.15 * 2.), t1 = push_solid(s, 0.15 * 2., 0.15 * 2., 0.4 * 2.);
+    push_checkered(s, t0, t1, 0.1);                       // 2
+    push_solid(s, 15., 15., 15.);                         // 3
+    push_matte(s, 2, 0.);                                 // mat 0
+    push_prim(s, make_rect(RT_PRIM_XZ_RECT, -10000., -10000., 10000., 10000., -2.83, 0));
+    uint32_t lm = push_light_mat(s, 3);                   // mat 1
+    rt_primitive light = make_rect(RT_PRIM_XZ_RECT, -10., -10., 10., 10., 50., lm);
+    light.light_index = 0;
+    push_prim(s, light);                                  // prim 1, not flipped
+    push_diffuse_light(s, 1, 12., 12., 12., false);
+    push_solid(s, 1., 1., 1.); push_solid(s, 1., 1., 1.); // 4, 5
+    push_solid(s, 0.05, 0.5, 0.75); push_solid(s, 0., 0., 0.); push_solid(s, 0.1, 0., 0.);   // 6 eta, 7 k, 8 rough
+    push_glass(s, 4, 5, 0.0, 0.0, 1.5, true);             // mat 2
+    push_metal(s, 6, 7, 8, 8, 8, true);                   // mat 3
+    if (p.variant == 1) push_mesh_triangles(s, m0, 2);
+    push_mesh_triangles(s, m1, 3);
+    s.png = "two_dragons.png";
+}
+// triangle soup; centre ~ U[-1,1]^3, edges ~ U[-s,s]^3, s = 2 N^(-1/3), f32-exact values
+void build_soup(rth_scene& s, const rth_params& p) {
+    uint64_t n = p.n_tris ? p.n_tris : 1000000;
+    double from[3] = {0., 0., -4.}, to[3] = {0., 0., 0.};
+    camera(s, from, to, aspect_of(p), 40., 0.0, 10., 0., 0.);
+    int bucket = 0; while ((1ull << (bucket + 1)) <= n) bucket++;
+    uint64_t key = 0x5EED0000ull + (uint64_t)bucket + (p.seed << 32);
+    double sz = 2. * std::pow((double)n, -1. / 3.);
+    rt::HostMesh m; m.p.resize(9 * n); m.ind.resize(3 * n);
+    for (uint64_t i = 0; i < n; i++) {
+        uint32_t c0[4] = {(uint32_t)i, (uint32_t)(i >> 32), 0, 0}, c1[4] = {(uint32_t)i, (uint32_t)(i >> 32), 1, 0}, c2[4] = {(uint32_t)i, (uint32_t)(i >> 32), 2, 0};
+        philox(c0, (uint32_t)key, (uint32_t)(key >> 32)); philox(c1, (uint32_t)key, (uint32_t)(key >> 32)); philox(c2, (uint32_t)key, (uint32_t)(key >> 32));
+        auto u = [](uint32_t x) { return (double)(x >> 8) * (1.0 / 16777216.0); };
+        double c[3] = {2. * u(c0[0]) - 1., 2. * u(c0[1]) - 1., 2. * u(c0[2]) - 1.};
+        double e1[3] = {sz * (2. * u(c1[0]) - 1.), sz * (2. * u(c1[1]) - 1.), sz * (2. * u(c1[2]) - 1.)};
+        double e2[3] = {sz * (2. * u(c2[0]) - 1.), sz * (2. * u(c2[1]) - 1.), sz * (2. * u(c2[2]) - 1.)};
+        for (int k = 0; k < 3; k++) {
+            m.p[9 * i + k] = (double)(float)c[k]; m.p[9 * i + 3 + k] = (double)(float)(c[k] + e1[k]); m.p[9 * i + 6 + k] = (double)(float)(c[k] + e2[k]);
+        }
+        m.ind[3 * i] = (uint32_t)(3 * i); m.ind[3 * i + 1] = (uint32_t)(3 * i + 1); m.ind[3 * i + 2] = (uint32_t)(3 * i + 2);
+    }
+    s.meshes.push_back(std::move(m));
+    uint32_t t = push_solid(s, 0.7, 0.7, 0.7);
+    push_mesh_triangles(s, 0, push_matte(s, t, 0.));
+    s.png = "soup.png";
+}
+
+}  // namespace
+
+extern "C" {
+
+rt_status rth_scene_create_empty(rth_scene** out) { if (!out) return RT_ERR_INVALID; *out = new rth_scene(); return RT_OK; }
+rt_status rth_scene_build(const char* name, const rth_params* params, rth_scene** out) {
+    if (!name || !params || !out) { rt::set_error("rth_scene_build: null argument"); return RT_ERR_INVALID; }
+    if (params->width == 0 || params->height == 0) { rt::set_error("rth_scene_build: zero image size"); return RT_ERR_INVALID; }
+    if (params->n_tris > 170000000ull) { rt::set_error("rth_scene_build: n_tris too large"); return RT_ERR_INVALID; }
+    rth_scene* s = new rth_scene();
+    std::string n(name);
+    if (n == "sphere_roughness") build_sphere_roughness(*s, *params);
+    else if (n == "make_world") build_make_world(*s, *params);
+    else if (n == "cornell_box") build_cornell_box(*s, *params);
+    else if (n == "cornell_box_statue") build_cornell_box_statue(*s, *params);
+    else if (n == "plastic_dragon") build_plastic_dragon(*s, *params);
+    else if (n == "two_dragons") build_two_dragons(*s, *params);
+    else if (n == "soup") build_soup(*s, *params);
+    else { delete s; rt::set_error("rth_scene_build: unknown scene '" + n + "'"); return RT_ERR_INVALID; }
+    *out = s;
+    return RT_OK;
+}
+void rth_scene_destroy(rth_scene* s) { delete s; }
+rt_status rth_scene_camera(const rth_scene* s, rt_camera* out) { if (!s || !out) return RT_ERR_INVALID; *out = s->camera; return RT_OK; }
+const char* rth_scene_png_name(const rth_scene* s) { return s ? s->png.c_str() : ""; }
+int32_t rth_scene_uses_standin(const rth_scene* s) { return s && s->standin ? 1 : 0; }
+rt_status rth_scene_counts(const rth_scene* s, uint64_t c[6]) {
+    if (!s || !c) return RT_ERR_INVALID;
+    c[0] = s->meshes.size(); c[1] = s->n_prims(); c[2] = s->xforms.size() / 16; c[3] = s->textures.size(); c[4] = s->materials.size(); c[5] = s->lights.size();
+    return RT_OK;
+}
+rt_status rth_scene_mesh_sizes(const rth_scene* s, uint32_t mesh, uint64_t sz[4]) {
+    if (!s || !sz || mesh >= s->meshes.size()) return RT_ERR_INVALID;
+    const rt::HostMesh& m = s->meshes[mesh]; sz[0] = m.p.size() / 3; sz[1] = m.n.size() / 3; sz[2] = m.uv.size() / 2; sz[3] = m.ind.size();
+    return RT_OK;
+}
+rt_status rth_scene_mesh_copy(const rth_scene* s, uint32_t mesh, double* p, double* n, double* uv, uint32_t* ind) {
+    if (!s || mesh >= s->meshes.size()) return RT_ERR_INVALID;
+    const rt::HostMesh& m = s->meshes[mesh];
+    if (p) memcpy(p, m.p.data(), m.p.size() * 8); if (n) memcpy(n, m.n.data(), m.n.size() * 8);
+    if (uv) memcpy(uv, m.uv.data(), m.uv.size() * 8); if (ind) memcpy(ind, m.ind.data(), m.ind.size() * 4);
+    return RT_OK;
+}
+rt_status rth_scene_copy_primitives(const rth_scene* s, rt_primitive* out) {
+    if (!s || !out) return RT_ERR_INVALID;
+    uint64_t k = 0;
+    for (auto& it : s->items) {
+        if (!it.run) { out[k++] = it.prim; continue; }
+        uint64_t nt = s->meshes[it.mesh].ind.size() / 3;
+        for (uint64_t t = 0; t < nt; t++) { rt_primitive p = prim_base(RT_PRIM_TRIANGLE, it.mat); p.mesh_index = it.mesh; p.ind = (uint32_t)(3 * t); out[k++] = p; }
+    }
+    return RT_OK;
+}
+rt_status rth_scene_copy_transforms(const rth_scene* s, double* out) { if (!s || !out) return RT_ERR_INVALID; memcpy(out, s->xforms.data(), s->xforms.size() * 8); return RT_OK; }
+rt_status rth_scene_copy_textures(const rth_scene* s, rt_texture* out) { if (!s || !out) return RT_ERR_INVALID; memcpy(out, s->textures.data(), s->textures.size() * sizeof(rt_texture)); return RT_OK; }
+rt_status rth_scene_copy_materials(const rth_scene* s, rt_material* out) { if (!s || !out) return RT_ERR_INVALID; memcpy(out, s->materials.data(), s->materials.size() * sizeof(rt_material)); return RT_OK; }
+rt_status rth_scene_copy_lights(const rth_scene* s, rt_light* out) { if (!s || !out) return RT_ERR_INVALID; memcpy(out, s->lights.data(), s->lights.size() * sizeof(rt_light)); return RT_OK; }
+
+rt_status rth_scene_upload(const rth_scene* s, rt_scene* dst) {
+    if (!s || !dst) { rt::set_error("rth_scene_upload: null argument"); return RT_ERR_INVALID; }
+    rt_status st;
+    for (auto& m : s->meshes) {
+        uint32_t idx;
+        if ((st = rt_scene_add_mesh(dst, m.p.size() / 3, m.p.data(), m.n.size() / 3, m.n.empty() ? nullptr : m.n.data(), m.uv.size() / 2,
+                                    m.uv.empty() ? nullptr : m.uv.data(), m.ind.size(), m.ind.data(), &idx))) return st;
+    }
+    for (size_t i = 0; i < s->xforms.size() / 16; i++) if ((st = rt_scene_add_transform(dst, &s->xforms[16 * i], nullptr))) return st;
+    if ((st = rt_scene_set_textures(dst, s->textures.size(), s->textures.data()))) return st;
+    if ((st = rt_scene_set_materials(dst, s->materials.size(), s->materials.data()))) return st;
+    if ((st = rt_scene_set_lights(dst, s->lights.size(), s->lights.data()))) return st;
+    for (auto& it : s->items) {
+        if (it.run) st = rt_scene_add_mesh_triangles(dst, it.mesh, it.mat, nullptr);
+        else st = rt_scene_add_primitives(dst, 1, &it.prim, nullptr);
+        if (st) return st;
+    }
+    return RT_OK;
+}
+rt_status rth_scene_add_obj(rth_scene* s, const char* path, const double xf[16], uint32_t* out) {
+    if (!s || !path || !xf) { rt::set_error("rth_scene_add_obj: null argument"); return RT_ERR_INVALID; }
+    rt::HostMesh m; std::string err;
+    if (!load_obj(path, xf, m, err)) { rt::set_error("Failed to parse obj " + std::string(path) + ": " + err); return RT_ERR_IO; }   // parser.rs:83-85 panics
+    s->meshes.push_back(std::move(m));
+    if (out) *out = (uint32_t)s->meshes.size() - 1;
+    return RT_OK;
+}
+// pixel-centre primary rays (lens_radius = 0): Camera::get_ray (geometry.rs:177-190) at u=(x+0.5)/w, v=(y+0.5)/h
+rt_status rth_primary_rays(const rt_camera* c, uint32_t w, uint32_t h, rt_ray* out) {
+    if (!c || !out) return RT_ERR_INVALID;
+    for (uint32_t y = 0; y < h; y++) for (uint32_t x = 0; x < w; x++) {
+        double u = ((double)x + 0.5) / (double)w, v = ((double)y + 0.5) / (double)h;
+        rt_ray& r = out[(size_t)y * w + x];
+        for (int k = 0; k < 3; k++) {
+            double to = c->upper_left_corner[k] + c->horizontal_offset[k] * u - c->vertical_offset[k] * v;
+            r.origin[k] = c->origin[k]; r.dir[k] = to - c->origin[k];
+        }
+    }
+    return RT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,427 @@
+// Device half of the C ABI, part 2: the wavefront MIS path tracer.
+//
+// Replaces render::tile_multithread → PathIntegrator::render/single_sample/li (reference render.rs:13-159,
+// integrator.rs:336-445) and uniform_sample_one_light / estimate_direct (integrator.rs:530-634).
+// The reference runs one recursive f64 path per CPU thread; here a wavefront of W paths lives in HBM as
+// SoA queues and every iteration runs
+//     prepare → generate (refill with new camera samples) → extend (closest hit)
+//             → shade (emission, BSDF build, light sample, MIS BSDF sample, continuation, roulette)
+//             → connect (shadow any-hit rays, MIS probe closest-hit rays; adds to the film)
+// with queue compaction by warp-aggregated atomics.  No host synchronisation inside an iteration; the
+// host polls the control block every few iterations.  Randomness: counter-based Philox keyed by
+// (seed; pixel, sample, dimension) so a path's numbers do not depend on scheduling or on the GPU count.
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include "scene.h"
+#include "shade.cuh"
+#include "traverse.cuh"
+
+struct rt_film { double* d = nullptr; uint32_t w = 0, h = 0; bool owned = false; int device = 0; };
+
+namespace rt {
+
+#define CK(call)                                                                                     \
+    do {                                                                                             \
+        cudaError_t e_ = (call);                                                                     \
+        if (e_ != cudaSuccess) { set_error(std::string(#call) + ": " + cudaGetErrorString(e_)); return RT_ERR_CUDA; } \
+    } while (0)
+
+struct PathSet {           // SoA path state, one entry per path in flight
+    double *ox, *oy, *oz, *dx, *dy, *dz, *bx, *by, *bz;
+    uint32_t *pixel, *sample, *dim, *flags;       // flags: bits 0..15 bounces, bit 16 specular_bounce
+};
+struct ConnQ {             // shadow / probe queue: a ray (a→b or origin+dir), a pre-weighted contribution, a target
+    double *ax, *ay, *az, *bx, *by, *bz, *cr, *cg, *cb;
+    uint32_t *target, *pixel;                     // shadow: light primitive ; probe: light index
+};
+struct Ctrl {
+    uint32_t n_cur, n_new, n_tot, n_next, n_shadow, n_probe, pad0, pad1;
+    unsigned long long next_sample, sample_base, total_samples;
+    unsigned long long c_paths, c_extend, c_shadow, c_probe, c_iter;
+};
+struct RenderParams {
+    rt_camera cam; uint32_t width, height, x0, y0, ww, wh, sample_begin; uint32_t max_depth, invisible_light; uint32_t k0, k1; uint32_t W;
+};
+
+struct Wavefront {
+    uint32_t W = 0;
+    PathSet set[2]{}; ConnQ shadow{}, probe{};
+    uint32_t* hit_prim = nullptr; double* hit_t = nullptr;
+    Ctrl* ctrl = nullptr; Ctrl* h_ctrl = nullptr;
+    cudaStream_t stream = nullptr;
+    std::vector<void*> allocs;
+    std::vector<cudaEvent_t> events;
+};
+
+__device__ __forceinline__ uint32_t warp_append(uint32_t* counter) {
+    // warp-aggregated queue append: one atomic per warp (ballot + popc), everyone gets a unique slot
+    unsigned mask = __activemask();
+    int leader = __ffs(mask) - 1, lane = threadIdx.x & 31;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(counter, (uint32_t)__popc(mask));
+    base = __shfl_sync(mask, base, leader);
+    return base + __popc(mask & ((1u << lane) - 1u));
+}
+__device__ __forceinline__ void film_add(double* film, uint32_t pixel, D3 c) {
+    // util::increment_color (util.rs:208-232): the NaN guards there compare with `== NAN` and never fire
+    atomicAdd(film + 4 * (size_t)pixel + 0, c.x); atomicAdd(film + 4 * (size_t)pixel + 1, c.y); atomicAdd(film + 4 * (size_t)pixel + 2, c.z);
+}
+
+__global__ void k_prepare(Ctrl* c, uint32_t W) {
+    c->c_extend += c->n_tot; c->c_shadow += c->n_shadow; c->c_probe += c->n_probe; c->c_iter += 1;
+    uint32_t n_cur = c->n_next;
+    unsigned long long remaining = c->total_samples - c->next_sample;
+    uint32_t room = W - n_cur;
+    uint32_t n_new = (uint32_t)(remaining < (unsigned long long)room ? remaining : (unsigned long long)room);
+    c->n_cur = n_cur; c->n_new = n_new; c->n_tot = n_cur + n_new; c->n_next = 0; c->n_shadow = 0; c->n_probe = 0;
+    c->sample_base = c->next_sample; c->next_sample += n_new; c->c_paths += n_new;
+}
+
+// PathIntegrator::single_sample up to the camera ray (integrator.rs:357-365), Samplers::get_camera_sample
+// (sampler.rs:606-613), Camera::get_ray (geometry.rs:177-190)
+__global__ void __launch_bounds__(256) k_generate(const Ctrl* __restrict__ c, RenderParams rp, PathSet ps, double* film) {
+    uint32_t n_new = c->n_new, n_cur = c->n_cur; unsigned long long base = c->sample_base;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_new; i += gridDim.x * blockDim.x) {
+        unsigned long long g = base + i;
+        unsigned long long npix = (unsigned long long)rp.ww * rp.wh;
+        uint32_t s = (uint32_t)(g / npix), pi = (uint32_t)(g % npix);
+        uint32_t px = rp.x0 + pi % rp.ww, py = rp.y0 + pi / rp.ww;
+        uint32_t pixel = py * rp.width + px;
+        Rng rng; rng.k0 = rp.k0; rng.k1 = rp.k1; rng.pixel = pixel; rng.sample = rp.sample_begin + s; rng.dim = 0;
+        double offx = rng_next(rng), offy = rng_next(rng);
+        double fx = (double)px + offx, fy = (double)py + offy;
+        rng_next(rng);                       // time
+        rng_next(rng); rng_next(rng);        // lens sample (unused by get_ray, which draws its own)
+        double u = fx / (double)rp.width, v = fy / (double)rp.height;
+        D3 in_disk;
+        for (;;) { double x = rng_next(rng), y = rng_next(rng); if (x * x + y * y < 1.) { in_disk = mk3(x, y, 0.); break; } }   // util::rand_in_disk
+        in_disk = in_disk * rp.cam.lens_radius;
+        D3 offset = ld3(rp.cam.u) * in_disk.x + ld3(rp.cam.v) * in_disk.y;
+        D3 to = ld3(rp.cam.upper_left_corner) + ld3(rp.cam.horizontal_offset) * u - ld3(rp.cam.vertical_offset) * v;
+        D3 dir = to - ld3(rp.cam.origin);
+        rng_next(rng);                       // util::rand_range(t0, t1): ray time, unused by geometry
+        D3 o = ld3(rp.cam.origin) + offset, d = dir - offset;
+        uint32_t k = n_cur + i;
+        ps.ox[k] = o.x; ps.oy[k] = o.y; ps.oz[k] = o.z; ps.dx[k] = d.x; ps.dy[k] = d.y; ps.dz[k] = d.z;
+        ps.bx[k] = 1.; ps.by[k] = 1.; ps.bz[k] = 1.;
+        ps.pixel[k] = pixel; ps.sample[k] = rng.sample; ps.dim[k] = rng.dim; ps.flags[k] = 0;
+        atomicAdd(film + 4 * (size_t)pixel + 3, 1.0);       // count += 1 (util.rs:231)
+    }
+}
+
+// ray type A: geometry::get_intersection (geometry.rs:238-240)
+__global__ void __launch_bounds__(128) k_extend(const Ctrl* __restrict__ c, DScene sc, PathSet ps, uint32_t* __restrict__ hit_prim, double* __restrict__ hit_t) {
+    uint32_t n = c->n_tot;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        Hit h = trace_closest(sc, mk3(ps.ox[i], ps.oy[i], ps.oz[i]), mk3(ps.dx[i], ps.dy[i], ps.dz[i]), SMALL, INF);
+        hit_prim[i] = h.prim; hit_t[i] = h.t;
+    }
+}
+
+__device__ __forceinline__ D3 light_l(const DLight& l, D3 n, D3 w) {      // Light::l (light.rs:475-496)
+    if (dot(n, w) > 0. || l.two_sided) return ld3(l.color);
+    return mk3(0., 0., 0.);
+}
+__device__ __forceinline__ double power_heuristic(double f_pdf, double g_pdf) { double f = 1. * f_pdf, g = 1. * g_pdf; return (f * f) / (f * f + g * g); }   // integrator.rs:655-659
+
+// the body of PathIntegrator::li's loop (integrator.rs:386-443) for one path vertex
+__global__ void __launch_bounds__(128) k_shade(Ctrl* c, DScene sc, RenderParams rp, PathSet in, PathSet out, const uint32_t* __restrict__ hit_prim,
+                                              ConnQ shq, ConnQ prq, double* film) {
+    uint32_t n = c->n_tot;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        D3 o = mk3(in.ox[i], in.oy[i], in.oz[i]), d = mk3(in.dx[i], in.dy[i], in.dz[i]);
+        D3 beta = mk3(in.bx[i], in.by[i], in.bz[i]);
+        uint32_t pixel = in.pixel[i], flags = in.flags[i];
+        Rng rng; rng.k0 = rp.k0; rng.k1 = rp.k1; rng.pixel = pixel; rng.sample = in.sample[i]; rng.dim = in.dim[i];
+        uint32_t bounces = flags & 0xffffu; bool specular_bounce = (flags >> 16) & 1u;
+        uint32_t prim = hit_prim[i];
+        bool is_some = prim != RT_NONE;
+        Rec rec;
+        if (is_some) is_some = prim_record(sc, prim, o, d, SMALL, INF, true, rec);
+        bool alive = false;
+        do {
+            if (bounces == 0 || specular_bounce) {
+                if (is_some) {
+                    uint32_t li = sc.prims[prim].light;
+                    if (li != RT_NONE) {
+                        if (rp.invisible_light) { o = rec.p; alive = true; break; }          // go straight through the light, same bounce
+                        film_add(film, pixel, cmul(light_l(sc.lights[li], rec.n, -d), beta));   // HitRecord::le (hittable.rs:215-225)
+                    }
+                }   // miss: only Infinite lights emit (light.rs:499-513) — none in scope
+            }
+            if (!is_some || bounces >= rp.max_depth) break;
+            Bsdf bsdf;
+            compute_scattering(sc, rec, bsdf);
+            // uniform_sample_one_light (integrator.rs:530-557)
+            uint32_t n_lights = sc.n_lights;
+            if (n_lights != 0) {
+                uint32_t light_num = min(n_lights - 1, (uint32_t)(unsigned long long)(rng_next(rng) * (double)n_lights));
+                D2 u_light; u_light.x = rng_next(rng); u_light.y = rng_next(rng);
+                D2 u_scatter; u_scatter.x = rng_next(rng); u_scatter.y = rng_next(rng);
+                const DLight light = sc.lights[light_num];
+                const uint32_t nsf = BSDF_ALL - BSDF_SPECULAR;
+                // estimate_direct, light half (integrator.rs:573-597); Light::sample_li Diffuse (light.rs:176-203), Primitive::sample (primitive.rs:445-456)
+                {
+                    D3 p1, n1; sample_area(sc, light.prim, u_light, p1, n1);
+                    double pdf = 1. / light.area;
+                    D3 wiu = p1 - rec.p;
+                    if (norm2(wiu) == 0.) pdf = 0.;
+                    else { D3 wn = normalize(wiu); pdf = pdf * norm2(rec.p - p1) / fabs(dot(n1, -wn)); }
+                    double light_pdf; D3 color, wi = mk3(0., 0., 0.);
+                    if (pdf == 0. || norm2(rec.p - p1) == 0.) { light_pdf = 0.; color = ld3(light.color); }
+                    else { wi = normalize(p1 - rec.p); light_pdf = pdf; color = light_l(light, n1, -wi); }
+                    if (light_pdf > 0. && !is_black(color)) {
+                        D3 f = bsdf_f(bsdf, rec.wo, wi, nsf) * fabs(dot(wi, rec.sn));
+                        double scattering_pdf = bsdf_pdf(bsdf, rec.wo, wi, nsf);
+                        if (!is_black(f)) {
+                            double weight = power_heuristic(light_pdf, scattering_pdf);
+                            D3 ld = cmul(f, color) * (weight / light_pdf);
+                            D3 contrib = cmul(ld * (double)n_lights, beta);
+                            uint32_t q = warp_append(&c->n_shadow);
+                            shq.ax[q] = rec.p.x; shq.ay[q] = rec.p.y; shq.az[q] = rec.p.z; shq.bx[q] = p1.x; shq.by[q] = p1.y; shq.bz[q] = p1.z;
+                            shq.cr[q] = contrib.x; shq.cg[q] = contrib.y; shq.cb[q] = contrib.z; shq.target[q] = light.prim; shq.pixel[q] = pixel;
+                        }
+                    }
+                }
+                // estimate_direct, BSDF half (integrator.rs:601-632)
+                {
+                    D3 f, wi; double scattering_pdf; uint32_t st;
+                    bsdf_sample_f(bsdf, rec.wo, u_scatter, nsf, rng, f, wi, scattering_pdf, st);
+                    f = f * fabs(dot(wi, rec.sn));
+                    if (!is_black(f) && scattering_pdf > 0.) {
+                        double weight = 1.; bool go = true;
+                        if ((st & BSDF_SPECULAR) == 0) {
+                            // Light::pdf_li → Primitive::pdf (primitive.rs:462-473): re-intersect the ONE light primitive, tmin = 0, no leaf box
+                            Rec lr; double light_pdf = 0.;
+                            if (prim_record(sc, light.prim, rec.p, wi, 0., INF, false, lr)) light_pdf = norm2(rec.p - lr.p) / (light.area * fabs(dot(lr.n, -wi)));
+                            if (light_pdf == 0.) go = false;
+                            else weight = power_heuristic(scattering_pdf, light_pdf);
+                        }
+                        if (go) {
+                            D3 contrib = cmul((f * (weight / scattering_pdf)) * (double)n_lights, beta);   // × Le decided by the probe ray
+                            uint32_t q = warp_append(&c->n_probe);
+                            prq.ax[q] = rec.p.x; prq.ay[q] = rec.p.y; prq.az[q] = rec.p.z; prq.bx[q] = wi.x; prq.by[q] = wi.y; prq.bz[q] = wi.z;
+                            prq.cr[q] = contrib.x; prq.cg[q] = contrib.y; prq.cb[q] = contrib.z; prq.target[q] = light_num; prq.pixel[q] = pixel;
+                        }
+                    }
+                }
+            }
+            // continuation (integrator.rs:421-441)
+            D3 wo = -d;
+            D2 u; u.x = rng_next(rng); u.y = rng_next(rng);
+            D3 f, wi; double pdf; uint32_t sflags;
+            bsdf_sample_f(bsdf, wo, u, BSDF_ALL, rng, f, wi, pdf, sflags);
+            if (is_black(f) || pdf == 0.) break;
+            beta = cmul(beta, f) * (fabs(dot(wi, rec.sn)) / pdf);
+            specular_bounce = (sflags & BSDF_SPECULAR) != 0;
+            o = rec.p; d = wi;
+            if (bounces > 3) {
+                double q = fmax(0.05, 1. - fmax(beta.x, fmax(beta.y, beta.z)));
+                if (rng_next(rng) < q) break;
+                beta = beta * (1. / (1. - q));
+            }
+            bounces++;
+            alive = true;
+        } while (false);
+        if (alive) {
+            uint32_t k = warp_append(&c->n_next);
+            out.ox[k] = o.x; out.oy[k] = o.y; out.oz[k] = o.z; out.dx[k] = d.x; out.dy[k] = d.y; out.dz[k] = d.z;
+            out.bx[k] = beta.x; out.by[k] = beta.y; out.bz[k] = beta.z;
+            out.pixel[k] = pixel; out.sample[k] = rng.sample; out.dim[k] = rng.dim; out.flags[k] = (bounces & 0xffffu) | (specular_bounce ? 0x10000u : 0u);
+        }
+    }
+}
+
+// ray type B: Visibility::unoccluded (hittable.rs:25-39) as an any-hit query
+__global__ void __launch_bounds__(128) k_connect_shadow(const Ctrl* __restrict__ c, DScene sc, ConnQ q, double* film) {
+    uint32_t n = c->n_shadow;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        if (unoccluded(sc, mk3(q.ax[i], q.ay[i], q.az[i]), mk3(q.bx[i], q.by[i], q.bz[i]), q.target[i], false))
+            film_add(film, q.pixel[i], mk3(q.cr[i], q.cg[i], q.cb[i]));
+    }
+}
+// ray type C: the MIS BSDF probe (integrator.rs:614-630): closest hit; counts only if it is the sampled light
+__global__ void __launch_bounds__(128) k_connect_probe(const Ctrl* __restrict__ c, DScene sc, ConnQ q, double* film) {
+    uint32_t n = c->n_probe;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        D3 o = mk3(q.ax[i], q.ay[i], q.az[i]), d = mk3(q.bx[i], q.by[i], q.bz[i]);
+        Hit h = trace_closest(sc, o, d, SMALL, INF);
+        if (h.prim == RT_NONE) continue;
+        uint32_t li = sc.prims[h.prim].light;
+        if (li == RT_NONE || li != q.target[i]) continue;       // `lights[index].eq(light)` (integrator.rs:621)
+        Rec r;
+        if (!prim_record(sc, h.prim, o, d, SMALL, INF, true, r)) continue;
+        D3 le = light_l(sc.lights[li], r.n, -d);                 // new_record.le(&-wi)
+        if (is_black(le)) continue;
+        film_add(film, q.pixel[i], cmul(mk3(q.cr[i], q.cg[i], q.cb[i]), le));
+    }
+}
+
+// util::point_to_color (util.rs:441-471) with aces_comp (util.rs:400-408)
+__global__ void k_resolve(const double* __restrict__ film, uint64_t n, uint8_t* __restrict__ rgb) {
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        double scale = 1. / film[4 * i + 3];
+        for (int k = 0; k < 3; k++) {
+            double x = film[4 * i + k] * scale * 0.6;
+            double a = 2.51, b = 0.03, cc = 2.43, dd = 0.59, e = 0.14;
+            double v = clampd((x * (a * x + b)) / (x * (cc * x + dd) + e), 0., 1.);
+            double r = round(pow(v, 1. / 2.2) * 256.);
+            rgb[3 * i + k] = !(r > 0.) ? 0 : (r > 255. ? 255 : (uint8_t)r);          // Rust `as u8` saturates, NaN → 0
+        }
+    }
+}
+
+}  // namespace rt
+
+namespace rt {
+
+template <class T> static bool dalloc(Wavefront& w, T*& p, size_t n) {
+    void* q = nullptr;
+    if (cudaMalloc(&q, n * sizeof(T)) != cudaSuccess) return false;
+    w.allocs.push_back(q); p = (T*)q; return true;
+}
+static bool alloc_set(Wavefront& w, PathSet& s, size_t n) {
+    return dalloc(w, s.ox, n) && dalloc(w, s.oy, n) && dalloc(w, s.oz, n) && dalloc(w, s.dx, n) && dalloc(w, s.dy, n) && dalloc(w, s.dz, n) &&
+           dalloc(w, s.bx, n) && dalloc(w, s.by, n) && dalloc(w, s.bz, n) && dalloc(w, s.pixel, n) && dalloc(w, s.sample, n) && dalloc(w, s.dim, n) && dalloc(w, s.flags, n);
+}
+static bool alloc_q(Wavefront& w, ConnQ& q, size_t n) {
+    return dalloc(w, q.ax, n) && dalloc(w, q.ay, n) && dalloc(w, q.az, n) && dalloc(w, q.bx, n) && dalloc(w, q.by, n) && dalloc(w, q.bz, n) &&
+           dalloc(w, q.cr, n) && dalloc(w, q.cg, n) && dalloc(w, q.cb, n) && dalloc(w, q.target, n) && dalloc(w, q.pixel, n);
+}
+static void destroy_wavefront(Wavefront* w) {
+    if (!w) return;
+    for (void* p : w->allocs) cudaFree(p);
+    for (auto e : w->events) cudaEventDestroy(e);
+    if (w->h_ctrl) cudaFreeHost(w->h_ctrl);
+    if (w->stream) cudaStreamDestroy(w->stream);
+    delete w;
+}
+void free_wavefront(rt_scene& s) { destroy_wavefront((Wavefront*)s.wavefront); s.wavefront = nullptr; }
+
+static Wavefront* get_wavefront(rt_scene& s) {
+    if (s.wavefront) return (Wavefront*)s.wavefront;
+    Wavefront* w = new Wavefront();
+    w->W = s.wavefront_size;
+    size_t n = w->W;
+    bool ok = alloc_set(*w, w->set[0], n) && alloc_set(*w, w->set[1], n) && alloc_q(*w, w->shadow, n) && alloc_q(*w, w->probe, n) &&
+              dalloc(*w, w->hit_prim, n) && dalloc(*w, w->hit_t, n) && dalloc(*w, w->ctrl, 1) &&
+              cudaMallocHost((void**)&w->h_ctrl, sizeof(Ctrl)) == cudaSuccess && cudaStreamCreateWithFlags(&w->stream, cudaStreamNonBlocking) == cudaSuccess;
+    if (!ok) { set_error(std::string("wavefront allocation failed: ") + cudaGetErrorString(cudaGetLastError())); destroy_wavefront(w); return nullptr; }
+    s.wavefront = w;
+    return w;
+}
+
+static cudaEvent_t ev(Wavefront& w, size_t i) {
+    while (w.events.size() <= i) { cudaEvent_t e; cudaEventCreate(&e); w.events.push_back(e); }
+    return w.events[i];
+}
+
+}  // namespace rt
+
+using namespace rt;
+
+extern "C" {
+
+rt_status rt_film_create(uint32_t w, uint32_t h, rt_film** out) {
+    if (!out || !w || !h) { set_error("rt_film_create: bad argument"); return RT_ERR_INVALID; }
+    rt_film* f = new rt_film(); f->w = w; f->h = h; f->owned = true;
+    if (cudaGetDevice(&f->device) != cudaSuccess || cudaMalloc((void**)&f->d, (size_t)w * h * 4 * sizeof(double)) != cudaSuccess) {
+        set_error(std::string("rt_film_create: ") + cudaGetErrorString(cudaGetLastError())); delete f; return RT_ERR_CUDA;
+    }
+    cudaMemset(f->d, 0, (size_t)w * h * 4 * sizeof(double));
+    *out = f; return RT_OK;
+}
+rt_status rt_film_create_external(uint32_t w, uint32_t h, void* dev, rt_film** out) {
+    if (!out || !w || !h || !dev) { set_error("rt_film_create_external: bad argument"); return RT_ERR_INVALID; }
+    rt_film* f = new rt_film(); f->w = w; f->h = h; f->owned = false; f->d = (double*)dev;
+    if (cudaGetDevice(&f->device) != cudaSuccess) { set_error("rt_film_create_external: no CUDA device"); delete f; return RT_ERR_CUDA; }
+    *out = f; return RT_OK;
+}
+rt_status rt_film_destroy(rt_film* f) { if (!f) return RT_OK; if (f->owned && f->d) cudaFree(f->d); delete f; return RT_OK; }
+rt_status rt_film_clear(rt_film* f) {
+    if (!f) { set_error("rt_film_clear: null film"); return RT_ERR_INVALID; }
+    CK(cudaMemset(f->d, 0, (size_t)f->w * f->h * 4 * sizeof(double))); return RT_OK;
+}
+rt_status rt_film_read(rt_film* f, double* host) {
+    if (!f || !host) { set_error("rt_film_read: null argument"); return RT_ERR_INVALID; }
+    CK(cudaMemcpy(host, f->d, (size_t)f->w * f->h * 4 * sizeof(double), cudaMemcpyDeviceToHost)); return RT_OK;
+}
+rt_status rt_film_resolve_rgb8(rt_film* f, uint8_t* host_rgb) {
+    if (!f || !host_rgb) { set_error("rt_film_resolve_rgb8: null argument"); return RT_ERR_INVALID; }
+    uint64_t n = (uint64_t)f->w * f->h; uint8_t* d = nullptr;
+    CK(cudaMalloc((void**)&d, n * 3));
+    k_resolve<<<(unsigned)std::min<uint64_t>((n + 255) / 256, 148 * 16), 256>>>(f->d, n, d);
+    cudaError_t e = cudaMemcpy(host_rgb, d, n * 3, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    if (e != cudaSuccess) { set_error(std::string("rt_film_resolve_rgb8: ") + cudaGetErrorString(e)); return RT_ERR_CUDA; }
+    return RT_OK;
+}
+
+rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc* integ, const rt_film_desc* fd, rt_film* film) {
+    if (!s || !cam || !integ || !fd || !film) { set_error("rt_render: null argument"); return RT_ERR_INVALID; }
+    if (!s->committed) { set_error("rt_render: scene not committed"); return RT_ERR_STATE; }
+    if (integ->kind != RT_INTEGRATOR_PATH) { set_error("rt_render: only IntType::Path is implemented"); return RT_ERR_INVALID; }
+    if (fd->width != film->w || fd->height != film->h) { set_error("rt_render: film size mismatch"); return RT_ERR_INVALID; }
+    if (fd->x1 > fd->width || fd->y1 > fd->height || fd->x0 > fd->x1 || fd->y0 > fd->y1 || fd->sample_end < fd->sample_begin) { set_error("rt_render: bad window / sample range"); return RT_ERR_INVALID; }
+    if (integ->max_depth > 0xfff0u) { set_error("rt_render: max_depth too large"); return RT_ERR_INVALID; }
+    CK(cudaSetDevice(s->device));
+    Wavefront* wp = get_wavefront(*s);
+    if (!wp) return RT_ERR_CUDA;
+    Wavefront& w = *wp;
+    s->cancel.store(0);
+    RenderParams rp{};
+    rp.cam = *cam; rp.width = fd->width; rp.height = fd->height; rp.x0 = fd->x0; rp.y0 = fd->y0; rp.ww = fd->x1 - fd->x0; rp.wh = fd->y1 - fd->y0;
+    rp.sample_begin = fd->sample_begin; rp.max_depth = integ->max_depth; rp.invisible_light = integ->invisible_light;
+    rp.k0 = (uint32_t)fd->seed; rp.k1 = (uint32_t)(fd->seed >> 32); rp.W = w.W;
+    Ctrl init{}; init.total_samples = (unsigned long long)rp.ww * rp.wh * (fd->sample_end - fd->sample_begin);
+    s->counters = rt_counters{};
+    if (init.total_samples == 0) return RT_OK;
+    cudaStream_t st = w.stream;
+    CK(cudaMemcpyAsync(w.ctrl, &init, sizeof(Ctrl), cudaMemcpyHostToDevice, st));
+    int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device);
+    int g128 = (int)std::min<uint64_t>((w.W + 127) / 128, (uint64_t)sms * 32), g256 = (int)std::min<uint64_t>((w.W + 255) / 256, (uint64_t)sms * 8);
+    cudaEvent_t e_begin = ev(w, 0), e_end = ev(w, 1);
+    size_t n_ev = 2;
+    CK(cudaEventRecord(e_begin, st));
+    int cur = 0; uint64_t iter = 0; bool done = false; rt_status result = RT_OK;
+    while (!done) {
+        for (int k = 0; k < 4; k++, iter++) {
+            k_prepare<<<1, 1, 0, st>>>(w.ctrl, w.W);
+            if (k == 0) cudaMemcpyAsync(w.h_ctrl, w.ctrl, sizeof(Ctrl), cudaMemcpyDeviceToHost, st);
+            cudaEventRecord(ev(w, n_ev + 0), st);
+            k_generate<<<g256, 256, 0, st>>>(w.ctrl, rp, w.set[cur], film->d);
+            cudaEventRecord(ev(w, n_ev + 1), st);
+            k_extend<<<g128, 128, 0, st>>>(w.ctrl, s->d, w.set[cur], w.hit_prim, w.hit_t);
+            cudaEventRecord(ev(w, n_ev + 2), st);
+            k_shade<<<g128, 128, 0, st>>>(w.ctrl, s->d, rp, w.set[cur], w.set[cur ^ 1], w.hit_prim, w.shadow, w.probe, film->d);
+            cudaEventRecord(ev(w, n_ev + 3), st);
+            k_connect_shadow<<<g128, 128, 0, st>>>(w.ctrl, s->d, w.shadow, film->d);
+            k_connect_probe<<<g128, 128, 0, st>>>(w.ctrl, s->d, w.probe, film->d);
+            cudaEventRecord(ev(w, n_ev + 4), st);
+            n_ev += 5;
+            cur ^= 1;
+        }
+        CK(cudaStreamSynchronize(st));
+        if (w.h_ctrl->n_tot == 0) done = true;       // snapshot taken right after a prepare: nothing in flight, nothing left to generate
+        if (s->cancel.load()) { result = RT_ERR_CANCELLED; set_error("rt_render: cancelled"); done = true; }
+        if (n_ev > 200000) n_ev = 2;                  // very long renders: stop growing the event pool (timing breakdown becomes partial)
+    }
+    k_prepare<<<1, 1, 0, st>>>(w.ctrl, w.W);         // account the last iteration
+    CK(cudaMemcpyAsync(w.h_ctrl, w.ctrl, sizeof(Ctrl), cudaMemcpyDeviceToHost, st));
+    CK(cudaEventRecord(e_end, st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    rt_counters& c = s->counters;
+    c.paths = w.h_ctrl->c_paths; c.extend_rays = w.h_ctrl->c_extend; c.shadow_rays = w.h_ctrl->c_shadow; c.probe_rays = w.h_ctrl->c_probe; c.iterations = iter;
+    float ms = 0; cudaEventElapsedTime(&ms, e_begin, e_end); c.render_ms = ms;
+    for (size_t i = 2; i + 4 < n_ev; i += 5) {
+        float a = 0, b = 0, cc = 0, d = 0;
+        cudaEventElapsedTime(&a, w.events[i], w.events[i + 1]); cudaEventElapsedTime(&b, w.events[i + 1], w.events[i + 2]);
+        cudaEventElapsedTime(&cc, w.events[i + 2], w.events[i + 3]); cudaEventElapsedTime(&d, w.events[i + 3], w.events[i + 4]);
+        c.shade_ms += a + cc; c.extend_ms += b; c.connect_ms += d;
+    }
+    return result;
+}
+
+}  // extern "C"

@@ -1,0 +1,67 @@
+// Internal host/device layout of librtcore (not part of the ABI).
+//
+// Data layout in HBM:
+//   nodes   : BVH2, 64 B/node, four 16-byte words (Aila–Laine child-box packing), f32 boxes rounded
+//             outward from the reference's f64 primitive boxes;
+//   slots   : leaf-ordered primitive slots, 80 B each = five 16-byte words: nine f64 vertex
+//             coordinates (the reference's own f64 values — the exact test runs on them),
+//             prim id, kind;
+//   prims   : 16 B/prim record (type/flip/mesh flags, material, light, payload offset);
+//   points / normals / uvs / tri_index : the meshes, concatenated, f64 (read by shade only);
+//   shapes  : f64 payload of spheres and rects; xforms: forward + inverse 4x4 per transform.
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+#include "../../include/rtcore.h"
+
+namespace rt {
+
+constexpr double SMALL = 0.001;          // consts.rs:32
+constexpr double INF = 1e308;            // consts.rs:30
+constexpr double PI = 3.14159265358979;  // consts.rs:31
+
+struct HostMesh {
+    std::vector<double> p, n, uv;        // xyz / xyz / uv
+    std::vector<uint32_t> ind;
+};
+
+struct DNode { float v[12]; int32_t left, right, pad0, pad1; };   // 64 B
+static_assert(sizeof(DNode) == 64, "node must be 64 bytes");
+// v[0..3] = l.minx,l.maxx,l.miny,l.maxy ; v[4..7] = r.minx,r.maxx,r.miny,r.maxy ; v[8..11] = l.minz,l.maxz,r.minz,r.maxz
+
+struct DSlot { double v[9]; uint32_t prim; uint32_t kind; };      // 80 B ; kind 0 = triangle, 1 = other
+static_assert(sizeof(DSlot) == 80, "slot must be 80 bytes");
+
+struct DPrim { uint32_t info, mat, light, a; };                   // 16 B
+// info: bits 0-2 type, bit 3 flip_face, bit 4 mesh has normals, bit 5 mesh has uvs, bits 6.. mesh index
+constexpr uint32_t PI_FLIP = 8u, PI_HAS_N = 16u, PI_HAS_UV = 32u;
+
+struct DMesh { uint64_t p_base, n_base, uv_base; };               // element (vertex) offsets
+
+struct DXform { double fwd[16], inv[16]; };
+
+struct DLight { uint32_t prim, two_sided, pad0, pad1; double color[3]; double area; };
+
+// everything the kernels read; all pointers are device pointers
+struct DScene {
+    const DNode* nodes; const DSlot* slots; const DPrim* prims; const DMesh* meshes;
+    const double* points; const double* normals; const double* uvs; const uint32_t* tri_index;
+    const double* shapes; const DXform* xforms;
+    const rt_texture* textures; const rt_material* materials; const DLight* lights;
+    uint32_t n_nodes, n_prims, n_lights, n_slots;
+};
+
+struct Box64 { double mn[3], mx[3]; };
+
+// host-side primitive record kept by rt_scene (compact; triangles of a mesh are a run)
+struct HostPrim { uint8_t type, flip; uint32_t mat, light, mesh, ind, xform; uint32_t shape; };
+
+void set_error(const std::string& msg);
+
+// bvh_build.cpp: binned-SAH BVH2 over conservative f32 boxes.  Returns nodes (root = 0) and the
+// leaf-ordered primitive permutation.  max 4 prims per leaf.
+struct BuiltBvh { std::vector<DNode> nodes; std::vector<uint32_t> order; };
+void build_bvh(const std::vector<Box64>& boxes, BuiltBvh& out, int threads);
+
+}  // namespace rt

@@ -1,0 +1,43 @@
+// rt_scene: host tables + committed device image.
+#pragma once
+#include <atomic>
+#include "rt_internal.h"
+
+struct rt_scene {
+    // host tables (mirror of `Objects`, reference geometry.rs:13-21)
+    std::vector<rt::HostMesh> meshes;
+    std::vector<rt::HostPrim> prims;
+    std::vector<double> shapes;              // 12 per shape: v[0..4], xform (-1 none), f64 leaf box mn[3], mx[3]
+    std::vector<rt::DXform> xforms;
+    std::vector<rt_texture> textures;
+    std::vector<rt_material> materials;
+    std::vector<rt_light> lights;
+    // committed
+    bool committed = false;
+    int device = 0;
+    rt::DScene d{};                          // device pointers
+    std::vector<void*> allocations;          // every cudaMalloc of this scene
+    uint64_t bytes_nodes = 0, bytes_slots = 0, bytes_tables = 0;
+    // wavefront state (render.cu)
+    void* wavefront = nullptr;
+    uint32_t wavefront_size = 1u << 22;
+    std::atomic<int> cancel{0};
+    rt_counters counters{};
+};
+
+namespace rt {
+// scene_host.cpp
+Box64 prim_box(const rt_scene& s, const HostPrim& p);
+double prim_area(const rt_scene& s, const HostPrim& p);
+bool invert4(const double m[16], double out[16]);
+// what commit hands to the device uploader (device.cu)
+struct HostImage {
+    std::vector<DNode> nodes; std::vector<DSlot> slots; std::vector<DPrim> prims; std::vector<DMesh> meshes;
+    std::vector<double> points, normals, uvs, shapes; std::vector<uint32_t> tri_index;
+    std::vector<DLight> lights;
+};
+rt_status build_host_image(const rt_scene& s, HostImage& img);
+rt_status upload_scene(rt_scene& s, const HostImage& img);   // device.cu
+void free_scene_device(rt_scene& s);                          // device.cu
+void free_wavefront(rt_scene& s);                             // render.cu
+}

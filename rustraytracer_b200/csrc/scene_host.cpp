@@ -1,0 +1,341 @@
+// Host half of the C ABI: scene tables, primitive boxes, commit (BVH + SoA flatten).
+// No CUDA in this file.  Reference items are cited per function.
+#include <cmath>
+#include <cstring>
+#include <thread>
+#include "scene.h"
+
+namespace rt {
+
+static thread_local std::string g_error;
+void set_error(const std::string& msg) { g_error = msg; }
+
+static inline double rmin(double a, double b) { return std::fmin(a, b); }
+static inline double rmax(double a, double b) { return std::fmax(a, b); }
+
+// closed-form 4x4 inverse by cofactors (what nalgebra's 4x4 `try_inverse` does); row-major in/out
+bool invert4(const double m[16], double out[16]) {
+    double inv[16];
+    inv[0] = m[5] * m[10] * m[15] - m[5] * m[11] * m[14] - m[9] * m[6] * m[15] + m[9] * m[7] * m[14] + m[13] * m[6] * m[11] - m[13] * m[7] * m[10];
+    inv[4] = -m[4] * m[10] * m[15] + m[4] * m[11] * m[14] + m[8] * m[6] * m[15] - m[8] * m[7] * m[14] - m[12] * m[6] * m[11] + m[12] * m[7] * m[10];
+    inv[8] = m[4] * m[9] * m[15] - m[4] * m[11] * m[13] - m[8] * m[5] * m[15] + m[8] * m[7] * m[13] + m[12] * m[5] * m[11] - m[12] * m[7] * m[9];
+    inv[12] = -m[4] * m[9] * m[14] + m[4] * m[10] * m[13] + m[8] * m[5] * m[14] - m[8] * m[6] * m[13] - m[12] * m[5] * m[10] + m[12] * m[6] * m[9];
+    inv[1] = -m[1] * m[10] * m[15] + m[1] * m[11] * m[14] + m[9] * m[2] * m[15] - m[9] * m[3] * m[14] - m[13] * m[2] * m[11] + m[13] * m[3] * m[10];
+    inv[5] = m[0] * m[10] * m[15] - m[0] * m[11] * m[14] - m[8] * m[2] * m[15] + m[8] * m[3] * m[14] + m[12] * m[2] * m[11] - m[12] * m[3] * m[10];
+    inv[9] = -m[0] * m[9] * m[15] + m[0] * m[11] * m[13] + m[8] * m[1] * m[15] - m[8] * m[3] * m[13] - m[12] * m[1] * m[11] + m[12] * m[3] * m[9];
+    inv[13] = m[0] * m[9] * m[14] - m[0] * m[10] * m[13] - m[8] * m[1] * m[14] + m[8] * m[2] * m[13] + m[12] * m[1] * m[10] - m[12] * m[2] * m[9];
+    inv[2] = m[1] * m[6] * m[15] - m[1] * m[7] * m[14] - m[5] * m[2] * m[15] + m[5] * m[3] * m[14] + m[13] * m[2] * m[7] - m[13] * m[3] * m[6];
+    inv[6] = -m[0] * m[6] * m[15] + m[0] * m[7] * m[14] + m[4] * m[2] * m[15] - m[4] * m[3] * m[14] - m[12] * m[2] * m[7] + m[12] * m[3] * m[6];
+    inv[10] = m[0] * m[5] * m[15] - m[0] * m[7] * m[13] - m[4] * m[1] * m[15] + m[4] * m[3] * m[13] + m[12] * m[1] * m[7] - m[12] * m[3] * m[5];
+    inv[14] = -m[0] * m[5] * m[14] + m[0] * m[6] * m[13] + m[4] * m[1] * m[14] - m[4] * m[2] * m[13] - m[12] * m[1] * m[6] + m[12] * m[2] * m[5];
+    inv[3] = -m[1] * m[6] * m[11] + m[1] * m[7] * m[10] + m[5] * m[2] * m[11] - m[5] * m[3] * m[10] - m[9] * m[2] * m[7] + m[9] * m[3] * m[6];
+    inv[7] = m[0] * m[6] * m[11] - m[0] * m[7] * m[10] - m[4] * m[2] * m[11] + m[4] * m[3] * m[10] + m[8] * m[2] * m[7] - m[8] * m[3] * m[6];
+    inv[11] = -m[0] * m[5] * m[11] + m[0] * m[7] * m[9] + m[4] * m[1] * m[11] - m[4] * m[3] * m[9] - m[8] * m[1] * m[7] + m[8] * m[3] * m[5];
+    inv[15] = m[0] * m[5] * m[10] - m[0] * m[6] * m[9] - m[4] * m[1] * m[10] + m[4] * m[2] * m[9] + m[8] * m[1] * m[6] - m[8] * m[2] * m[5];
+    double det = m[0] * inv[0] + m[1] * inv[4] + m[2] * inv[8] + m[3] * inv[12];
+    if (det == 0.0) return false;
+    double inv_det = 1.0 / det;
+    for (int i = 0; i < 16; i++) out[i] = inv[i] * inv_det;
+    return true;
+}
+
+static void xf_point(const double* m, const double p[3], double o[3]) {   // Projective3::transform_point
+    double x = m[0] * p[0] + m[1] * p[1] + m[2] * p[2] + m[3];
+    double y = m[4] * p[0] + m[5] * p[1] + m[6] * p[2] + m[7];
+    double z = m[8] * p[0] + m[9] * p[1] + m[10] * p[2] + m[11];
+    double w = m[12] * p[0] + m[13] * p[1] + m[14] * p[2] + m[15];
+    o[0] = x / w; o[1] = y / w; o[2] = z / w;
+}
+
+// Bounding boxes exactly as the reference constructors make them: sphere c±r (primitive.rs:64-77),
+// rects padded ±SMALL on the constant axis (primitive.rs:93-94,111-112,...), transformed rects through
+// util::get_new_box (util.rs:493-517), triangles min/max of the vertices (hittable.rs:267-276).
+Box64 prim_box(const rt_scene& s, const HostPrim& p) {
+    Box64 b;
+    if (p.type == RT_PRIM_SPHERE) {
+        const double* v = &s.shapes[p.shape];
+        for (int k = 0; k < 3; k++) { b.mn[k] = v[k] - v[3]; b.mx[k] = v[k] + v[3]; }
+        return b;
+    }
+    if (p.type == RT_PRIM_TRIANGLE) {
+        const HostMesh& m = s.meshes[p.mesh];
+        const double* v1 = &m.p[3 * (size_t)m.ind[p.ind]]; const double* v2 = &m.p[3 * (size_t)m.ind[p.ind + 1]]; const double* v3 = &m.p[3 * (size_t)m.ind[p.ind + 2]];
+        for (int k = 0; k < 3; k++) { b.mn[k] = rmin(v1[k], rmin(v2[k], v3[k])); b.mx[k] = rmax(v1[k], rmax(v2[k], v3[k])); }
+        return b;
+    }
+    const double* v = &s.shapes[p.shape];
+    double a0 = v[0], b0 = v[1], a1 = v[2], b1 = v[3], k = v[4];
+    if (p.type == RT_PRIM_XY_RECT) { b.mn[0] = a0; b.mn[1] = b0; b.mn[2] = k - SMALL; b.mx[0] = a1; b.mx[1] = b1; b.mx[2] = k + SMALL; }
+    else if (p.type == RT_PRIM_XZ_RECT) { b.mn[0] = a0; b.mn[1] = k - SMALL; b.mn[2] = b0; b.mx[0] = a1; b.mx[1] = k + SMALL; b.mx[2] = b1; }
+    else { b.mn[0] = k - SMALL; b.mn[1] = a0; b.mn[2] = b0; b.mx[0] = k + SMALL; b.mx[1] = a1; b.mx[2] = b1; }
+    if (p.xform != RT_NONE) {
+        const double* t = s.xforms[p.xform].fwd;
+        Box64 nb; for (int a = 0; a < 3; a++) { nb.mn[a] = INF; nb.mx[a] = -INF; }
+        for (int i = 0; i < 2; i++) for (int j = 0; j < 2; j++) for (int l = 0; l < 2; l++) {
+            double pt[3] = {i == 0 ? b.mn[0] : b.mx[0], j == 0 ? b.mn[1] : b.mx[1], l == 0 ? b.mn[2] : b.mx[2]}, np[3];
+            xf_point(t, pt, np);
+            for (int a = 0; a < 3; a++) { nb.mn[a] = rmin(nb.mn[a], np[a]); nb.mx[a] = rmax(nb.mx[a], np[a]); }
+        }
+        b = nb;
+    }
+    return b;
+}
+
+// Primitive::area (primitive.rs:339-359); the sphere's 2*PI*r is the reference's value
+double prim_area(const rt_scene& s, const HostPrim& p) {
+    if (p.type == RT_PRIM_SPHERE) return 2. * PI * s.shapes[p.shape + 3];
+    if (p.type == RT_PRIM_TRIANGLE) {
+        const HostMesh& m = s.meshes[p.mesh];
+        const double* p0 = &m.p[3 * (size_t)m.ind[p.ind]]; const double* p1 = &m.p[3 * (size_t)m.ind[p.ind + 1]]; const double* p2 = &m.p[3 * (size_t)m.ind[p.ind + 2]];
+        double v1[3] = {p1[0] - p0[0], p1[1] - p0[1], p1[2] - p0[2]}, v2[3] = {p2[0] - p0[0], p2[1] - p0[1], p2[2] - p0[2]};
+        double c[3] = {v1[1] * v2[2] - v1[2] * v2[1], v1[2] * v2[0] - v1[0] * v2[2], v1[0] * v2[1] - v1[1] * v2[0]};
+        return 0.5 * std::sqrt(c[0] * c[0] + c[1] * c[1] + c[2] * c[2]);
+    }
+    const double* v = &s.shapes[p.shape];
+    return (v[2] - v[0]) * (v[3] - v[1]);
+}
+
+rt_status build_host_image(const rt_scene& s, HostImage& img) {
+    size_t n = s.prims.size();
+    // validate cross indices
+    for (size_t i = 0; i < n; i++) {
+        const HostPrim& p = s.prims[i];
+        if (p.mat >= s.materials.size()) { set_error("primitive " + std::to_string(i) + ": mat_index out of range"); return RT_ERR_INVALID; }
+        if (p.light != RT_NONE && p.light >= s.lights.size()) { set_error("primitive: light_index out of range"); return RT_ERR_INVALID; }
+    }
+    for (auto& m : s.materials) for (int k = 0; k < 5; k++) {
+        int used = m.type == RT_MAT_METAL ? 5 : (m.type == RT_MAT_PLASTIC || m.type == RT_MAT_GLASS ? 2 : 1);
+        if (k < used && m.tex[k] != RT_NONE && m.tex[k] >= s.textures.size()) { set_error("material: texture id out of range"); return RT_ERR_INVALID; }
+        if (k < used && m.tex[k] == RT_NONE && !(m.type == RT_MAT_METAL && k >= 3)) { set_error("material: missing texture id"); return RT_ERR_INVALID; }
+    }
+    for (auto& t : s.textures) if (t.type == RT_TEX_CHECKERED && (t.odd >= s.textures.size() || t.even >= s.textures.size())) { set_error("checkered texture: id out of range"); return RT_ERR_INVALID; }
+    for (auto& l : s.lights) if (l.prim_index >= n) { set_error("light: prim_index out of range"); return RT_ERR_INVALID; }
+    // meshes → concatenated f64 arrays
+    img.meshes.resize(s.meshes.size());
+    std::vector<uint64_t> idx_base(s.meshes.size());
+    uint64_t pb = 0, nb = 0, ub = 0, ib = 0;
+    for (size_t m = 0; m < s.meshes.size(); m++) {
+        img.meshes[m] = DMesh{pb, nb, ub};
+        idx_base[m] = ib;
+        pb += s.meshes[m].p.size() / 3; nb += s.meshes[m].n.size() / 3; ub += s.meshes[m].uv.size() / 2; ib += s.meshes[m].ind.size();
+    }
+    img.points.reserve(pb * 3); img.normals.reserve(nb * 3); img.uvs.reserve(ub * 2); img.tri_index.reserve(ib);
+    for (auto& m : s.meshes) {
+        img.points.insert(img.points.end(), m.p.begin(), m.p.end());
+        img.normals.insert(img.normals.end(), m.n.begin(), m.n.end());
+        img.uvs.insert(img.uvs.end(), m.uv.begin(), m.uv.end());
+        img.tri_index.insert(img.tri_index.end(), m.ind.begin(), m.ind.end());
+    }
+    // per-primitive records and boxes
+    img.shapes = s.shapes;
+    img.prims.resize(n);
+    std::vector<Box64> boxes(n);
+    int threads = (int)std::max(1u, std::thread::hardware_concurrency());
+    {
+        std::vector<std::thread> pool; size_t chunk = (n + threads - 1) / std::max(threads, 1);
+        for (int t = 0; t < threads; t++) pool.emplace_back([&, t]() {
+            size_t b = t * chunk, e = std::min(n, b + chunk);
+            for (size_t i = b; i < e; i++) {
+                const HostPrim& p = s.prims[i];
+                DPrim d; d.info = p.type | (p.flip ? PI_FLIP : 0); d.mat = p.mat; d.light = p.light; d.a = 0;
+                if (p.type == RT_PRIM_TRIANGLE) {
+                    const HostMesh& m = s.meshes[p.mesh];
+                    if (!m.n.empty()) d.info |= PI_HAS_N;
+                    if (!m.uv.empty()) d.info |= PI_HAS_UV;
+                    d.info |= p.mesh << 6;
+                    d.a = (uint32_t)(idx_base[p.mesh] + p.ind);
+                } else d.a = p.shape;
+                img.prims[i] = d;
+                boxes[i] = prim_box(s, p);
+                if (p.type != RT_PRIM_TRIANGLE) for (int k = 0; k < 3; k++) { img.shapes[p.shape + 6 + k] = boxes[i].mn[k]; img.shapes[p.shape + 9 + k] = boxes[i].mx[k]; }
+            }
+        });
+        for (auto& th : pool) th.join();
+    }
+    if (ib >= (1ull << 32)) { set_error("index buffer exceeds 2^32 entries"); return RT_ERR_INVALID; }
+    BuiltBvh bvh;
+    build_bvh(boxes, bvh, threads);
+    img.nodes = std::move(bvh.nodes);
+    img.slots.resize(n);
+    for (size_t sidx = 0; sidx < n; sidx++) {
+        uint32_t pi = bvh.order[sidx];
+        const HostPrim& p = s.prims[pi];
+        DSlot sl; memset(&sl, 0, sizeof(sl));
+        sl.prim = pi;
+        if (p.type == RT_PRIM_TRIANGLE) {
+            const HostMesh& m = s.meshes[p.mesh];
+            for (int v = 0; v < 3; v++) for (int k = 0; k < 3; k++) sl.v[3 * v + k] = m.p[3 * (size_t)m.ind[p.ind + v] + k];
+            sl.kind = 0;
+            if (!m.uv.empty()) {
+                // hittable.rs:366-378: a triangle whose uv determinant is below 1e-7 AND whose geometric
+                // normal (p2-p0)x(p1-p0) is exactly zero always returns None
+                const double* u0 = &m.uv[2 * (size_t)m.ind[p.ind]]; const double* u1 = &m.uv[2 * (size_t)m.ind[p.ind + 1]]; const double* u2 = &m.uv[2 * (size_t)m.ind[p.ind + 2]];
+                double d02x = u0[0] - u2[0], d02y = u0[1] - u2[1], d12x = u1[0] - u2[0], d12y = u1[1] - u2[1];
+                double determinant = d02x * d12y - d02y * d12x;
+                if (std::fabs(determinant) < SMALL / 10000.) {
+                    double a[3] = {sl.v[6] - sl.v[0], sl.v[7] - sl.v[1], sl.v[8] - sl.v[2]}, b[3] = {sl.v[3] - sl.v[0], sl.v[4] - sl.v[1], sl.v[5] - sl.v[2]};
+                    double c[3] = {a[1] * b[2] - a[2] * b[1], a[2] * b[0] - a[0] * b[2], a[0] * b[1] - a[1] * b[0]};
+                    if (c[0] * c[0] + c[1] * c[1] + c[2] * c[2] == 0.) sl.kind = 2;
+                }
+            }
+        } else sl.kind = 1;
+        img.slots[sidx] = sl;
+    }
+    img.lights.resize(s.lights.size());
+    for (size_t i = 0; i < s.lights.size(); i++) {
+        DLight d; memset(&d, 0, sizeof(d));
+        d.prim = s.lights[i].prim_index; d.two_sided = s.lights[i].two_sided;
+        for (int k = 0; k < 3; k++) d.color[k] = s.lights[i].color[k];
+        d.area = prim_area(s, s.prims[d.prim]);              // light.rs:603
+        img.lights[i] = d;
+    }
+    return RT_OK;
+}
+
+}  // namespace rt
+
+using namespace rt;
+
+extern "C" {
+
+const char* rt_last_error_string(void) { return g_error.c_str(); }
+const char* rt_version_string(void) { return "rtcore 0.1 (sm_100a)"; }
+uint32_t rt_round_spp(uint32_t spp) { uint32_t p = 1; while (p < spp) p <<= 1; return p; }   // sampler.rs:637-640
+
+// Camera::new_motion_blur (geometry.rs:133-175)
+rt_status rt_camera_look_at(const double from[3], const double to[3], const double up[3], double aspect, double vfov,
+                            double aperture, double focus, double t0, double t1, rt_camera* out) {
+    if (!from || !to || !up || !out) { set_error("rt_camera_look_at: null argument"); return RT_ERR_INVALID; }
+    auto normalize = [](double* v) { double n = std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]); v[0] /= n; v[1] /= n; v[2] /= n; };
+    auto cross = [](const double* a, const double* b, double* c) { c[0] = a[1] * b[2] - a[2] * b[1]; c[1] = a[2] * b[0] - a[0] * b[2]; c[2] = a[0] * b[1] - a[1] * b[0]; };
+    double w[3] = {to[0] - from[0], to[1] - from[1], to[2] - from[2]}; normalize(w);
+    double u[3]; cross(up, w, u); normalize(u); for (int k = 0; k < 3; k++) u[k] = -u[k];
+    double v[3]; cross(w, u, v); normalize(v); for (int k = 0; k < 3; k++) v[k] = -v[k];
+    double theta = vfov * PI / 180., h = std::tan(theta / 2.);
+    double vh = 2. * h, vw = vh * aspect;
+    for (int k = 0; k < 3; k++) {
+        out->origin[k] = from[k];
+        out->horizontal_offset[k] = u[k] * (vw * focus);
+        out->vertical_offset[k] = v[k] * (vh * focus);
+        out->upper_left_corner[k] = from[k] - out->horizontal_offset[k] * 0.5 + out->vertical_offset[k] * 0.5 + w[k] * focus;
+        out->u[k] = u[k]; out->v[k] = v[k]; out->w[k] = w[k];
+    }
+    out->lens_radius = aperture / 2.; out->t0 = t0; out->t1 = t1;
+    return RT_OK;
+}
+
+rt_status rt_scene_create(rt_scene** out) {
+    if (!out) { set_error("rt_scene_create: null out"); return RT_ERR_INVALID; }
+    *out = new rt_scene(); return RT_OK;
+}
+rt_status rt_scene_destroy(rt_scene* s) {
+    if (!s) return RT_OK;
+    free_wavefront(*s); free_scene_device(*s); delete s; return RT_OK;
+}
+rt_status rt_scene_add_mesh(rt_scene* s, uint64_t n_points, const double* p, uint64_t n_normals, const double* n, uint64_t n_uvs,
+                            const double* uv, uint64_t n_ind, const uint32_t* ind, uint32_t* out) {
+    if (!s || (n_points && !p) || (n_normals && !n) || (n_uvs && !uv) || (n_ind && !ind)) { set_error("rt_scene_add_mesh: null argument"); return RT_ERR_INVALID; }
+    if (n_ind % 3) { set_error("rt_scene_add_mesh: index count not a multiple of 3"); return RT_ERR_INVALID; }
+    if (n_normals && n_normals != n_points) { set_error("rt_scene_add_mesh: normals must be per point (single-index mesh)"); return RT_ERR_INVALID; }
+    if (n_uvs && n_uvs != n_points) { set_error("rt_scene_add_mesh: uvs must be per point (single-index mesh)"); return RT_ERR_INVALID; }
+    for (uint64_t i = 0; i < n_ind; i++) if (ind[i] >= n_points) { set_error("rt_scene_add_mesh: index out of range"); return RT_ERR_INVALID; }
+    HostMesh m; m.p.assign(p, p + 3 * n_points); if (n_normals) m.n.assign(n, n + 3 * n_normals); if (n_uvs) m.uv.assign(uv, uv + 2 * n_uvs); m.ind.assign(ind, ind + n_ind);
+    s->meshes.push_back(std::move(m)); s->committed = false;
+    if (out) *out = (uint32_t)s->meshes.size() - 1;
+    return RT_OK;
+}
+rt_status rt_scene_add_transform(rt_scene* s, const double m[16], uint32_t* out) {
+    if (!s || !m) { set_error("rt_scene_add_transform: null argument"); return RT_ERR_INVALID; }
+    DXform x; memcpy(x.fwd, m, sizeof(double) * 16);
+    if (!invert4(x.fwd, x.inv)) { set_error("rt_scene_add_transform: singular matrix"); return RT_ERR_INVALID; }
+    s->xforms.push_back(x); s->committed = false;
+    if (out) *out = (uint32_t)s->xforms.size() - 1;
+    return RT_OK;
+}
+rt_status rt_scene_add_primitives(rt_scene* s, uint64_t n, const rt_primitive* prims, uint32_t* first) {
+    if (!s || (n && !prims)) { set_error("rt_scene_add_primitives: null argument"); return RT_ERR_INVALID; }
+    for (uint64_t i = 0; i < n; i++) {
+        const rt_primitive& p = prims[i];
+        if (p.type > RT_PRIM_YZ_RECT) { set_error("rt_scene_add_primitives: unknown type"); return RT_ERR_INVALID; }
+        if (p.type == RT_PRIM_TRIANGLE && (p.mesh_index >= s->meshes.size() || (uint64_t)p.ind + 3 > s->meshes[p.mesh_index].ind.size())) { set_error("rt_scene_add_primitives: triangle out of range"); return RT_ERR_INVALID; }
+        if (p.type >= RT_PRIM_XY_RECT && p.transform != RT_NONE && p.transform >= s->xforms.size()) { set_error("rt_scene_add_primitives: transform out of range"); return RT_ERR_INVALID; }
+    }
+    if (first) *first = (uint32_t)s->prims.size();
+    for (uint64_t i = 0; i < n; i++) {
+        const rt_primitive& p = prims[i];
+        HostPrim h{}; h.type = (uint8_t)p.type; h.flip = p.flip_face ? 1 : 0; h.mat = p.mat_index; h.light = p.light_index;
+        h.mesh = p.mesh_index; h.ind = p.ind; h.xform = p.type >= RT_PRIM_XY_RECT ? p.transform : RT_NONE; h.shape = 0;
+        if (p.type != RT_PRIM_TRIANGLE) {
+            h.shape = (uint32_t)s->shapes.size();
+            for (int k = 0; k < 5; k++) s->shapes.push_back(p.v[k]);
+            s->shapes.push_back(h.xform == RT_NONE ? -1.0 : (double)h.xform);
+            for (int k = 0; k < 6; k++) s->shapes.push_back(0.0);     // f64 leaf box, filled at commit
+        }
+        s->prims.push_back(h);
+    }
+    s->committed = false;
+    return RT_OK;
+}
+// Mesh::generate_triangles (hittable.rs:257-288)
+rt_status rt_scene_add_mesh_triangles(rt_scene* s, uint32_t mesh, uint32_t mat, uint32_t* first) {
+    if (!s || mesh >= s->meshes.size()) { set_error("rt_scene_add_mesh_triangles: bad mesh"); return RT_ERR_INVALID; }
+    if (first) *first = (uint32_t)s->prims.size();
+    size_t ni = s->meshes[mesh].ind.size();
+    s->prims.reserve(s->prims.size() + ni / 3);
+    for (size_t i = 0; i < ni; i += 3) {
+        HostPrim h{}; h.type = RT_PRIM_TRIANGLE; h.flip = 0; h.mat = mat; h.light = RT_NONE; h.mesh = mesh; h.ind = (uint32_t)i; h.xform = RT_NONE; h.shape = 0;
+        s->prims.push_back(h);
+    }
+    s->committed = false;
+    return RT_OK;
+}
+rt_status rt_scene_set_light_index(rt_scene* s, uint32_t prim, uint32_t light) {
+    if (!s || prim >= s->prims.size()) { set_error("rt_scene_set_light_index: bad primitive"); return RT_ERR_INVALID; }
+    s->prims[prim].light = light; s->committed = false; return RT_OK;
+}
+rt_status rt_scene_set_textures(rt_scene* s, uint64_t n, const rt_texture* t) {
+    if (!s || (n && !t)) { set_error("rt_scene_set_textures: null argument"); return RT_ERR_INVALID; }
+    for (uint64_t i = 0; i < n; i++) if (t[i].type > RT_TEX_CHECKERED) { set_error("rt_scene_set_textures: unsupported texture type"); return RT_ERR_INVALID; }
+    s->textures.assign(t, t + n); s->committed = false; return RT_OK;
+}
+rt_status rt_scene_set_materials(rt_scene* s, uint64_t n, const rt_material* m) {
+    if (!s || (n && !m)) { set_error("rt_scene_set_materials: null argument"); return RT_ERR_INVALID; }
+    for (uint64_t i = 0; i < n; i++) if (m[i].type > RT_MAT_MIRROR) { set_error("rt_scene_set_materials: unsupported material type"); return RT_ERR_INVALID; }
+    s->materials.assign(m, m + n); s->committed = false; return RT_OK;
+}
+rt_status rt_scene_set_lights(rt_scene* s, uint64_t n, const rt_light* l) {
+    if (!s || (n && !l)) { set_error("rt_scene_set_lights: null argument"); return RT_ERR_INVALID; }
+    for (uint64_t i = 0; i < n; i++) if (l[i].type != RT_LIGHT_DIFFUSE) { set_error("rt_scene_set_lights: unsupported light type"); return RT_ERR_INVALID; }
+    s->lights.assign(l, l + n); s->committed = false; return RT_OK;
+}
+rt_status rt_scene_commit(rt_scene* s) {
+    if (!s) { set_error("rt_scene_commit: null scene"); return RT_ERR_INVALID; }
+    HostImage img;
+    rt_status st = build_host_image(*s, img);
+    if (st != RT_OK) return st;
+    free_wavefront(*s); free_scene_device(*s);
+    st = upload_scene(*s, img);
+    if (st != RT_OK) return st;
+    s->committed = true;
+    return RT_OK;
+}
+rt_status rt_scene_num_primitives(const rt_scene* s, uint64_t* out) {
+    if (!s || !out) { set_error("rt_scene_num_primitives: null argument"); return RT_ERR_INVALID; }
+    *out = s->prims.size(); return RT_OK;
+}
+rt_status rt_scene_device_bytes(const rt_scene* s, uint64_t* nodes, uint64_t* leaves, uint64_t* tables) {
+    if (!s) { set_error("rt_scene_device_bytes: null scene"); return RT_ERR_INVALID; }
+    if (nodes) *nodes = s->bytes_nodes; if (leaves) *leaves = s->bytes_slots; if (tables) *tables = s->bytes_tables;
+    return RT_OK;
+}
+rt_status rt_set_wavefront_size(rt_scene* s, uint32_t paths) {
+    if (!s || paths < 1024) { set_error("rt_set_wavefront_size: need >= 1024 paths"); return RT_ERR_INVALID; }
+    free_wavefront(*s); s->wavefront_size = paths; return RT_OK;
+}
+rt_status rt_render_cancel(rt_scene* s) { if (!s) return RT_ERR_INVALID; s->cancel.store(1); return RT_OK; }
+rt_status rt_get_counters(const rt_scene* s, rt_counters* out) {
+    if (!s || !out) { set_error("rt_get_counters: null argument"); return RT_ERR_INVALID; }
+    *out = s->counters; return RT_OK;
+}
+
+}  // extern "C"
