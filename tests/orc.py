@@ -1,0 +1,192 @@
+"""ctypes binding of the test-side oracle (oracle/liboracle.so).  TEST INFRASTRUCTURE ONLY."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from rustraytracer_b200 import _native as N
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+LIB = os.path.join(ORACLE_DIR, "liboracle.so")
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB):
+            subprocess.check_call(["make", "-C", ORACLE_DIR, "-s"])
+        L = C.CDLL(LIB)
+        vp, u32, u64, f64, i32 = C.c_void_p, C.c_uint32, C.c_uint64, C.c_double, C.c_int
+        L.orc_scene_create.restype = vp
+        L.orc_scene_destroy.argtypes = [vp]
+        L.orc_scene_add_mesh.argtypes = [vp, u64, vp, u64, vp, u64, vp, u64, vp]
+        L.orc_scene_add_mesh.restype = u32
+        L.orc_scene_add_transform.argtypes = [vp, vp]
+        L.orc_scene_add_transform.restype = u32
+        L.orc_scene_add_primitives.argtypes = [vp, u64, vp]
+        L.orc_scene_set_textures.argtypes = [vp, u64, vp]
+        L.orc_scene_set_materials.argtypes = [vp, u64, vp]
+        L.orc_scene_set_lights.argtypes = [vp, u64, vp]
+        L.orc_scene_commit.argtypes = [vp, u64]
+        L.orc_scene_num_primitives.argtypes = [vp]
+        L.orc_scene_num_primitives.restype = u64
+        L.orc_scene_prim_box.argtypes = [vp, u32, vp]
+        L.orc_intersect.argtypes = [vp, u64, vp, f64, f64, i32, i32, vp, vp, vp]
+        L.orc_occluded.argtypes = [vp, u64, vp, i32, vp]
+        L.orc_camera_look_at.argtypes = [vp, vp, vp, f64, f64, f64, f64, f64, f64, vp]
+        L.orc_render.argtypes = [vp, vp, u32, u32, vp, i32, vp, vp]
+        L.orc_render.restype = f64
+        L.orc_single_sample.argtypes = [vp, vp, u32, u32, u32, u32, u32, u64, u32, u32, vp]
+        L.orc_resolve_rgb8.argtypes = [vp, u64, vp]
+        L.orc_philox.argtypes = [vp, u32, u32]
+        L.orc_rng_uniform.argtypes = [u64, u32, u32, u32]
+        L.orc_rng_uniform.restype = f64
+        L.orc_bsdf_f_pdf.argtypes = [vp, u32, f64, f64, vp, vp, u32, vp, vp]
+        L.orc_bsdf_sample_f.argtypes = [vp, u32, f64, f64, vp, vp, u32, u64, u32, u32, vp]
+        L.orc_tex_value.argtypes = [vp, u32, f64, f64, vp]
+        L.orc_fr_dielectric.argtypes = [f64, f64, f64]
+        L.orc_fr_dielectric.restype = f64
+        L.orc_fr_conductor.argtypes = [f64, vp, vp, vp]
+        _lib = L
+    return _lib
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class OracleScene:
+    """Oracle-side scene fed from the SAME plain tables the CUDA library gets."""
+
+    def __init__(self, tables=None, bvh_seed=1):
+        self.h = C.c_void_p(lib().orc_scene_create())
+        if tables is not None:
+            self.load(tables)
+            self.commit(bvh_seed)
+
+    def __del__(self):
+        try:
+            if self.h:
+                lib().orc_scene_destroy(self.h)
+        except Exception:
+            pass
+
+    def load(self, t):
+        L = lib()
+        for (p, n, uv, ind) in t["meshes"]:
+            p = np.ascontiguousarray(p, dtype=np.float64); n = np.ascontiguousarray(n, dtype=np.float64)
+            uv = np.ascontiguousarray(uv, dtype=np.float64); ind = np.ascontiguousarray(ind, dtype=np.uint32)
+            L.orc_scene_add_mesh(self.h, len(p), _p(p), len(n), _p(n) if len(n) else None, len(uv), _p(uv) if len(uv) else None, len(ind), _p(ind))
+        for m in np.asarray(t["transforms"], dtype=np.float64).reshape(-1, 16):
+            m = np.ascontiguousarray(m)
+            L.orc_scene_add_transform(self.h, _p(m))
+        prims = np.ascontiguousarray(t["prims"], dtype=N.prim_dtype)
+        if len(prims):
+            L.orc_scene_add_primitives(self.h, len(prims), _p(prims))
+        tex = np.ascontiguousarray(t["textures"], dtype=N.texture_dtype)
+        L.orc_scene_set_textures(self.h, len(tex), _p(tex) if len(tex) else None)
+        mat = np.ascontiguousarray(t["materials"], dtype=N.material_dtype)
+        L.orc_scene_set_materials(self.h, len(mat), _p(mat) if len(mat) else None)
+        lig = np.ascontiguousarray(t["lights"], dtype=N.light_dtype)
+        L.orc_scene_set_lights(self.h, len(lig), _p(lig) if len(lig) else None)
+
+    def commit(self, bvh_seed=1):
+        lib().orc_scene_commit(self.h, bvh_seed)
+
+    def num_primitives(self):
+        return lib().orc_scene_num_primitives(self.h)
+
+    def prim_box(self, i):
+        out = np.zeros(6)
+        lib().orc_scene_prim_box(self.h, i, _p(out))
+        return out
+
+    def intersect(self, rays, tmin=0.001, tmax=1e308, mode=0, threads=8, want_ties=False, want_stats=False):
+        """mode 0 = reference-faithful tree, 1 = brute force (+tie sets), 2 = ordered (work counting)."""
+        rays = np.ascontiguousarray(rays, dtype=N.ray_dtype)
+        hits = np.zeros(len(rays), dtype=N.hit_dtype)
+        ties = np.full((len(rays), 4), N.RT_NONE, dtype=np.uint32) if want_ties else None
+        stats = np.zeros(2, dtype=np.uint64)
+        lib().orc_intersect(self.h, len(rays), _p(rays), tmin, tmax, mode, threads, _p(hits), _p(ties), _p(stats))
+        out = [hits]
+        if want_ties:
+            out.append(ties)
+        if want_stats:
+            out.append(stats)
+        return out[0] if len(out) == 1 else tuple(out)
+
+    def occluded(self, p0, p1, prim, infinite=False, threads=8):
+        q = np.zeros(len(p0), dtype=N.shadow_dtype)
+        q["p0"] = p0; q["p1"] = p1; q["p1_prim_index"] = prim; q["infinite_light"] = 1 if infinite else 0
+        out = np.zeros(len(q), dtype=np.uint8)
+        lib().orc_occluded(self.h, len(q), _p(q), threads, _p(out))
+        return out.astype(bool)
+
+    def render(self, camera, width, height, sample_begin, sample_end, seed=0, max_depth=25, invisible_light=False, threads=8, window=None, film=None):
+        x0, y0, x1, y1 = window if window is not None else (0, 0, width, height)
+        fd = N.FilmDesc(width, height, sample_begin, sample_end, x0, y0, x1, y1, seed)
+        if film is None:
+            film = np.zeros((height, width, 4), dtype=np.float64)
+        counts = np.zeros(3, dtype=np.uint64)
+        secs = lib().orc_render(self.h, C.byref(camera.c), max_depth, 1 if invisible_light else 0, C.byref(fd), threads, _p(film), _p(counts))
+        return film, counts, secs
+
+    def bsdf_f_pdf(self, mat, wo, wi, flags=31, u=0.3, v=0.6):
+        wo = np.ascontiguousarray(wo, dtype=np.float64); wi = np.ascontiguousarray(wi, dtype=np.float64)
+        f = np.zeros(3); pdf = C.c_double()
+        lib().orc_bsdf_f_pdf(self.h, mat, u, v, _p(wo), _p(wi), flags, _p(f), C.byref(pdf))
+        return f, pdf.value
+
+    def bsdf_sample_f(self, mat, wo, sample, flags=31, seed=0, pixel=0, smp=0, u=0.3, v=0.6):
+        wo = np.ascontiguousarray(wo, dtype=np.float64); s = np.ascontiguousarray(sample, dtype=np.float64)
+        out = np.zeros(8)
+        lib().orc_bsdf_sample_f(self.h, mat, u, v, _p(wo), _p(s), flags, seed, pixel, smp, _p(out))
+        return out[0:3], out[3:6], out[6], int(out[7])
+
+    def tex_value(self, tid, u, v):
+        out = np.zeros(3)
+        lib().orc_tex_value(self.h, tid, u, v, _p(out))
+        return out
+
+
+def resolve_rgb8(film):
+    film = np.ascontiguousarray(film, dtype=np.float64)
+    out = np.zeros(film.shape[:2] + (3,), dtype=np.uint8)
+    lib().orc_resolve_rgb8(_p(film), film.shape[0] * film.shape[1], _p(out))
+    return out
+
+
+def simple_tables(prims, textures=None, materials=None, lights=None, meshes=(), transforms=()):
+    """Plain tables for hand-built KAT scenes."""
+    if textures is None:
+        textures = np.zeros(1, dtype=N.texture_dtype); textures[0]["color"] = (0.5, 0.5, 0.5)
+    if materials is None:
+        materials = np.zeros(1, dtype=N.material_dtype); materials[0]["tex"] = N.RT_NONE; materials[0]["tex"][0] = 0
+    if lights is None:
+        lights = np.zeros(0, dtype=N.light_dtype)
+    return dict(meshes=list(meshes), prims=np.asarray(prims, dtype=N.prim_dtype), transforms=np.asarray(transforms, dtype=np.float64).reshape(-1, 16),
+                textures=textures, materials=materials, lights=lights)
+
+
+def prim(ptype, v, mat=0, flip=0, light=N.RT_NONE, mesh=0, ind=0, xf=N.RT_NONE):
+    p = np.zeros(1, dtype=N.prim_dtype)[0]
+    p["type"] = ptype; p["flip_face"] = flip; p["mat_index"] = mat; p["light_index"] = light; p["mesh_index"] = mesh; p["ind"] = ind; p["transform"] = xf
+    vv = np.zeros(5); vv[:len(v)] = v; p["v"] = vv
+    return p
+
+
+def upload_tables(t):
+    """The same tables → the CUDA library through the public ABI (needs a GPU to commit)."""
+    from rustraytracer_b200 import Objects
+    o = Objects()
+    for (p, n, uv, ind) in t["meshes"]:
+        o.add_mesh(p, n, uv, ind)
+    for m in t["transforms"]:
+        o.add_transform(m)
+    o.set_textures(t["textures"]); o.set_materials(t["materials"]); o.set_lights(t["lights"])
+    if len(t["prims"]):
+        o.add_primitives(t["prims"])
+    return o

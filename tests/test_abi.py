@@ -1,0 +1,168 @@
+"""CPU-side checks of the drop-in boundary: the C-ABI library loads, exports every declared symbol,
+fails loudly without a GPU (no CPU fallback), and the host scene layer restates scenes.rs."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import orc
+from rustraytracer_b200 import Objects, _native as N, scenes
+from rustraytracer_b200._native import RtError
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_every_declared_symbol_is_exported():
+    L = N.lib()
+    for header, listed in (("rtcore.h", N.RTCORE_SYMBOLS), ("rthost.h", N.RTHOST_SYMBOLS)):
+        text = open(os.path.join(ROOT, "include", header)).read()
+        declared = set(re.findall(r"\b(rt[h]?_[a-z0-9_]+)\s*\(", text)) - {"rt_status"}
+        assert declared == set(listed), declared ^ set(listed)
+        for name in declared:
+            assert getattr(L, name) is not None
+
+
+def test_struct_layouts_match_header():
+    assert C.sizeof(N.Camera) == 24 * 8 and C.sizeof(N.FilmDesc) == 40 and C.sizeof(N.IntegratorDesc) == 16
+    assert C.sizeof(N.Counters) == 5 * 8 + 4 * 8
+
+
+def test_round_spp_and_version():
+    L = N.lib()
+    assert [L.rt_round_spp(x) for x in (1, 2, 3, 16, 50, 64, 65, 256, 1000)] == [1, 2, 4, 16, 64, 64, 128, 256, 1024]   # sampler.rs:637-640
+    assert b"sm_100a" in L.rt_version_string()
+
+
+def test_camera_matches_oracle():
+    from rustraytracer_b200 import Camera
+    cam = Camera.new_motion_blur((278., 278., -800.), (278., 278., 0.), (0., 1., 0.), 16 / 9, 40., 0.2, 10., 0., 1.)
+    ref = N.Camera()
+    f, t, u = (np.array(x, dtype=np.float64) for x in ((278., 278., -800.), (278., 278., 0.), (0., 1., 0.)))
+    orc.lib().orc_camera_look_at(orc._p(f), orc._p(t), orc._p(u), 16 / 9, 40., 0.2, 10., 0., 1., C.byref(ref))
+    assert bytes(cam.c) == bytes(ref)
+    # upper-left origin, +u to the right, v down (geometry.rs:157-159,181-182)
+    assert cam.c.upper_left_corner[1] > 278 and cam.c.lens_radius == 0.1
+
+
+@pytest.mark.skipif(N.lib().rt_device_count() > 0, reason="checks the no-GPU failure mode")
+def test_no_cpu_fallback():
+    hs = scenes.HostScene("sphere_roughness", 32, 32)
+    o = Objects()
+    N.check(N.lib().rth_scene_upload(hs.h, o.h))
+    with pytest.raises(RtError) as e:
+        o.commit()
+    assert e.value.status == N.RT_ERR_CUDA
+    from rustraytracer_b200 import get_intersection, make_rays
+    with pytest.raises(RtError) as e:
+        get_intersection(o, make_rays([(0, 0, 0)], [(0, 0, 1)]))
+    assert e.value.status == N.RT_ERR_STATE
+
+
+def test_argument_errors():
+    o = Objects()
+    with pytest.raises(RtError):
+        o.add_mesh(np.zeros((3, 3)), indices=[0, 1, 5])          # index out of range
+    with pytest.raises(RtError):
+        o.add_mesh(np.zeros((3, 3)), indices=[0, 1])             # not a multiple of 3
+    with pytest.raises(RtError):
+        o.add_primitives([orc.prim(N.PRIM_TRIANGLE, [], mesh=3)])
+    with pytest.raises(RtError):
+        o.add_transform(np.zeros(16))                            # singular
+    t = np.zeros(1, dtype=N.texture_dtype); t["type"] = 7
+    with pytest.raises(RtError):
+        o.set_textures(t)
+    assert N.lib().rt_scene_commit(None) == N.RT_ERR_INVALID
+
+
+def test_scene_tables_sphere_roughness():
+    # scenes.rs:474-546
+    hs = scenes.HostScene("sphere_roughness", 400, 400)
+    t = hs.tables()
+    assert hs.counts() == dict(meshes=0, prims=10, transforms=0, textures=28, materials=9, lights=1)
+    assert [tuple(p["v"][:4]) for p in t["prims"][:8]] == [(0., 1., -2.8 * 4.5 + 2.8 * i, 1.) for i in range(1, 9)]
+    assert list(t["prims"]["mat_index"]) == [1, 2, 3, 4, 5, 6, 7, 8, 0, 8]
+    assert t["prims"][9]["flip_face"] == 1 and t["prims"][9]["light_index"] == 0 and t["lights"][0]["prim_index"] == 9
+    assert tuple(t["prims"][8]["v"]) == (-10000., -10000., 10000., 10000., -0.01)
+    m = t["materials"][3]      # third metal sphere: roughness texture (i-1)/90 + SMALL
+    assert m["type"] == N.MAT_METAL and m["remap_roughness"] == 1 and m["tex"][3] == N.RT_NONE and m["tex"][4] == N.RT_NONE
+    assert t["textures"][m["tex"][2]]["color"][0] == 2 / 90. + 0.001
+    assert tuple(t["textures"][m["tex"][0]]["color"]) == (0., 0., 0.) and tuple(t["textures"][m["tex"][1]]["color"]) == (1., 1., 1.)
+    chk = t["textures"][2]
+    assert chk["type"] == N.TEX_CHECKERED and chk["even"] == 0 and chk["odd"] == 1 and chk["frequency"] == 0.1
+    assert hs.png_name() == "metal_spheres.png"
+
+
+def test_scene_tables_cornell_and_dragon():
+    hs = scenes.HostScene("cornell_box", 64, 64)
+    t = hs.tables()
+    assert hs.counts()["prims"] == 18 and hs.counts()["transforms"] == 2      # 6 walls + 2 cubes x 6 (scenes.rs:114-190)
+    assert list(t["prims"]["flip_face"][:6]) == [1, 0, 1, 0, 1, 1]
+    assert t["materials"][3]["type"] == N.MAT_LIGHT and t["prims"][2]["mat_index"] == 3
+    # cube sides order z0,z1,y0,y1,x0,x1 (hittable.rs:846)
+    assert list(t["prims"]["type"][6:12]) == [N.PRIM_XY_RECT, N.PRIM_XY_RECT, N.PRIM_XZ_RECT, N.PRIM_XZ_RECT, N.PRIM_YZ_RECT, N.PRIM_YZ_RECT]
+    xf = t["transforms"][1].reshape(4, 4)          # first_transform = translate(265,0,295) * Ry(15°)
+    a = 15 * 3.14159265358979 / 180
+    assert np.allclose(xf, [[np.cos(a), 0, np.sin(a), 265], [0, 1, 0, 0], [-np.sin(a), 0, np.cos(a), 295], [0, 0, 0, 1]])
+    hd = scenes.HostScene("plastic_dragon", 64, 64)
+    c = hd.counts()
+    assert c["prims"] == 871414 + 2 and hd.uses_standin()                   # floor + dragon + light (scenes.rs:348-358)
+    td = hd.tables()
+    assert td["prims"][0]["type"] == N.PRIM_XZ_RECT and td["prims"][-1]["flip_face"] == 1 and td["lights"][0]["prim_index"] == 871415
+    assert td["materials"][1]["type"] == N.MAT_PLASTIC and td["materials"][1]["f"][0] == 0.001
+    p = td["meshes"][0][0]
+    assert p.min(0)[1] == pytest.approx(-2.83, abs=1e-5) and np.all(np.abs(p).max(0) < 4.0)
+    assert len(td["meshes"][0][1]) == len(p) and len(td["meshes"][0][2]) == 0        # normals, no uvs
+
+
+def test_obj_parser_tobj_semantics(tmp_path):
+    # parser.rs:8-87: triangulated, single-index, models[0] only, transform on points and normals
+    obj = tmp_path / "quad.obj"
+    obj.write_text("""# two objects; only the first is used
+o first
+v 0 0 0
+v 1 0 0
+v 1 1 0
+v 0 1 0
+vn 0 0 1
+vt 0 0
+vt 1 0
+vt 1 1
+vt 0 1
+f 1/1/1 2/2/1 3/3/1 4/4/1
+f -4/1/1 -3/2/1 -2/3/1
+o second
+v 5 5 5
+f 1 2 5
+""")
+    h = C.c_void_p()
+    N.check(N.lib().rth_scene_create_empty(C.byref(h)))
+    xf = np.array([2, 0, 0, 10, 0, 2, 0, 0, 0, 0, 2, 0, 0, 0, 0, 1], dtype=np.float64)
+    out = C.c_uint32()
+    N.check(N.lib().rth_scene_add_obj(h, str(obj).encode(), N.ptr(xf), C.byref(out)))
+    sz = (C.c_uint64 * 4)()
+    N.check(N.lib().rth_scene_mesh_sizes(h, 0, sz))
+    assert list(sz) == [4, 4, 4, 9]                 # 4 unique (v,vt,vn) triples; quad → 2 tris, + 1 tri
+    p = np.zeros((4, 3)); n = np.zeros((4, 3)); uv = np.zeros((4, 2)); ind = np.zeros(9, dtype=np.uint32)
+    N.check(N.lib().rth_scene_mesh_copy(h, 0, N.ptr(p), N.ptr(n), N.ptr(uv), N.ptr(ind)))
+    assert np.array_equal(p, [[10, 0, 0], [12, 0, 0], [12, 2, 0], [10, 2, 0]])
+    assert np.array_equal(n, [[0, 0, 2]] * 4)       # transform_vector: scaled, not renormalised (parser.rs:45)
+    assert list(ind) == [0, 1, 2, 0, 2, 3, 0, 1, 2]
+    assert N.lib().rth_scene_add_obj(h, b"/nonexistent.obj", N.ptr(xf), None) == N.RT_ERR_IO
+    N.lib().rth_scene_destroy(h)
+
+
+REF_DATA = "/root/reference/data"
+
+
+@pytest.mark.skipif(not os.path.exists(REF_DATA + "/material/models/Mesh000.obj"), reason="reference assets only exist in the build container")
+def test_obj_parser_on_reference_asset():
+    h = C.c_void_p()
+    N.check(N.lib().rth_scene_create_empty(C.byref(h)))
+    xf = np.eye(4).reshape(16)
+    N.check(N.lib().rth_scene_add_obj(h, (REF_DATA + "/material/models/Mesh000.obj").encode(), N.ptr(xf), None))
+    sz = (C.c_uint64 * 4)()
+    N.check(N.lib().rth_scene_mesh_sizes(h, 0, sz))
+    assert sz[3] == 3 * 13312 and sz[0] == sz[1] == sz[2]       # 13,312 triangles, v/vt/vn
+    N.lib().rth_scene_destroy(h)

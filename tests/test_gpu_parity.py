@@ -1,0 +1,261 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the f64 oracle on the same inputs.
+
+Bar (BASELINE.json north_star): bit-exact closest-hit primitive ids and hit/miss flags (an id may
+differ only inside the oracle's exact-t tie set — SURVEY.md §8.1 #4), t within rel 1e-12 and
+normals within 1e-10 absolute (the device runs the reference's f64 expression order; the slack only
+covers libm vs CUDA transcendental rounding in sphere records).  Rendered films use the same
+counter-based RNG on both sides, so they are compared per pixel, not just statistically.
+"""
+import numpy as np
+import pytest
+
+import orc
+from rustraytracer_b200 import Film, IntType, _native as N, get_intersection, make_rays, render_samples, scenes, unoccluded
+
+pytestmark = pytest.mark.gpu
+NONE = N.RT_NONE
+T_RTOL = 1e-12
+N_ATOL = 1e-10
+
+
+def compare_hits(got, want, ties=None, what=""):
+    same = got["prim_index"] == want["prim_index"]
+    if ties is not None:
+        in_tie = np.array([g in t for g, t in zip(got["prim_index"], ties)]) & (got["prim_index"] != NONE)
+    else:
+        in_tie = (got["prim_index"] != NONE) & (want["prim_index"] != NONE) & (got["t"] == want["t"])
+    bad = ~(same | in_tie)
+    assert not bad.any(), f"{what}: {bad.sum()} of {len(got)} closest-hit ids differ (first: ray {np.flatnonzero(bad)[0]}, got {got['prim_index'][bad][0]}, want {want['prim_index'][bad][0]})"
+    hit = same & (want["prim_index"] != NONE)
+    assert np.allclose(got["t"][hit], want["t"][hit], rtol=T_RTOL, atol=0), what
+    for f in ("p",):
+        assert np.allclose(got[f][hit], want[f][hit], rtol=1e-12, atol=1e-9), (what, f)
+    for f in ("n", "ns"):
+        assert np.allclose(got[f][hit], want[f][hit], rtol=0, atol=N_ATOL), (what, f)
+    assert np.allclose(got["uv"][hit], want["uv"][hit], rtol=1e-11, atol=1e-12), what
+    assert np.array_equal(got["front"][hit], want["front"][hit]), what
+    return int(in_tie.sum() - (same & in_tie).sum())
+
+
+def random_rays(rng, n, lo, hi, scale=(0.1, 10.0)):
+    o = rng.uniform(lo, hi, (n, 3))
+    d = rng.normal(size=(n, 3)) * rng.uniform(scale[0], scale[1], (n, 1))
+    return make_rays(o, d)
+
+
+def test_kat_scenes_on_gpu():
+    """The hand-derived KAT geometry of test_oracle_kat.py, GPU vs oracle, incl. axis-parallel NaN-slab rays."""
+    import test_oracle_kat as K
+    a = 15 * 3.14159265358979 / 180
+    xf = [np.cos(a), 0, np.sin(a), 265, 0, 1, 0, 0, -np.sin(a), 0, np.cos(a), 295, 0, 0, 0, 1]
+    p = np.asarray(K.TRI + [(0, 0, 1.1), (1, 0, 1.0), (0, 1, 0.9)] + [(0, 0, 2), (1, 0, 2), (0, 1, 2)], dtype=np.float64)
+    nrm = np.tile(np.array([[0, 0, -1], [0.6, 0, -0.8], [0, 0.6, -0.8]], dtype=np.float64), (3, 1))
+    mesh = (p, nrm, np.zeros((0, 2)), np.arange(9, dtype=np.uint32))
+    prims = [orc.prim(N.PRIM_TRIANGLE, [], mesh=0, ind=0), orc.prim(N.PRIM_TRIANGLE, [], mesh=0, ind=3), orc.prim(N.PRIM_TRIANGLE, [], mesh=0, ind=6),
+             orc.prim(N.PRIM_SPHERE, [3, 0, 0, 1.0]), orc.prim(N.PRIM_XZ_RECT, [-1, -2, 1, 2, -3.0], flip=1),
+             orc.prim(N.PRIM_XY_RECT, [0, 0, 165, 330, 165], xf=0), orc.prim(N.PRIM_YZ_RECT, [-1, -1, 1, 1, -4.0])]
+    t = orc.simple_tables(prims, meshes=[mesh], transforms=[xf])
+    oracle = orc.OracleScene(t)
+    gpu = orc.upload_tables(t); gpu.commit()
+    o = [(0.25, 0.25, -3), (0.25, 0.25, 3), (0.8, 0.8, -3), (0.5, 0.0, -3), (0.5, 1e-9, -3), (-2, 0, 0), (3, 0, -5), (3, 1, -5), (3, 0, 0), (0, 5, 0), (1, 5, 2),
+         (0.25, 0.25, 0.025 - 0.00005), (0.25, 0.25, 0.025 - 0.0005), (300, 100, 900), (-9, 0, 0), (0.25, 0.25, 1.5)]
+    d = [(0, 0, 1), (0, 0, -1), (0, 0, 1), (0, 0, 1), (0, 0, 1), (2, 0, 0), (0, 0, 1), (0, 0, 1), (0, 0, 1), (0, -1, 0), (0, -1, 0),
+         (0, 0, 1), (0, 0, 1), (-0.1, 0.05, -1), (1, 0.01, 0.02), (0, 0, 1)]
+    rays = make_rays(o, d)
+    want, ties = oracle.intersect(rays, mode=1, want_ties=True)
+    got = get_intersection(gpu, rays)
+    compare_hits(got, want, ties, "kat")
+    assert (want["prim_index"] != NONE).sum() >= 9
+    rng = np.random.default_rng(1)
+    rays = random_rays(rng, 20000, -6, 6)
+    want, ties = oracle.intersect(rays, mode=1, want_ties=True)
+    compare_hits(get_intersection(gpu, rays), want, ties, "kat-random")
+    for (tmin, tmax) in ((0.0, 1e308), (0.5, 2.0), (0.001, 0.9)):
+        want, ties = oracle.intersect(rays[:4000], tmin, tmax, mode=1, want_ties=True)
+        compare_hits(get_intersection(gpu, rays[:4000], tmin, tmax), want, ties, f"kat-range {tmin} {tmax}")
+
+
+def test_empty_and_single_primitive_scenes():
+    t = orc.simple_tables([])
+    gpu = orc.upload_tables(t); gpu.commit()
+    got = get_intersection(gpu, make_rays([(0, 0, 0)], [(0, 0, 1)]))
+    assert got["prim_index"][0] == NONE
+    assert len(get_intersection(gpu, np.zeros(0, dtype=N.ray_dtype))) == 0        # empty batch
+    t = orc.simple_tables([orc.prim(N.PRIM_SPHERE, [0, 0, 0, 1.0])])
+    gpu = orc.upload_tables(t); gpu.commit()
+    oracle = orc.OracleScene(t)
+    rays = random_rays(np.random.default_rng(2), 5000, -3, 3)
+    compare_hits(get_intersection(gpu, rays), oracle.intersect(rays, mode=1), None, "single sphere")
+
+
+@pytest.mark.parametrize("name", ["sphere_roughness", "cornell_box", "make_world"])
+def test_builtin_scene_rays(name):
+    hs = scenes.HostScene(name, 128, 128)
+    gpu = hs.upload()
+    oracle = orc.OracleScene(hs.tables())
+    cam = hs.camera()
+    rays = cam.primary_rays(128, 128)
+    want, ties = oracle.intersect(rays, mode=1, want_ties=True)
+    got = get_intersection(gpu, rays)
+    compare_hits(got, want, ties, name + " primary")
+    assert (want["prim_index"] != NONE).mean() > 0.5
+    # batch B: one diffuse bounce ray from every primary hit
+    hit = want["prim_index"] != NONE
+    rng = np.random.default_rng(3)
+    d = rng.normal(size=(hit.sum(), 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    d *= np.sign(np.sum(d * want["n"][hit], axis=1, keepdims=True))
+    rays2 = make_rays(want["p"][hit], d)
+    want2, ties2 = oracle.intersect(rays2, mode=1, want_ties=True)
+    compare_hits(get_intersection(gpu, rays2), want2, ties2, name + " bounce")
+    # the faithful (reference-shaped) tree gives the same answers as brute force
+    want0 = oracle.intersect(rays2, mode=0)
+    assert np.all((want0["prim_index"] == want2["prim_index"]) | (want0["t"] == want2["t"]))
+
+
+def test_dragon_scene_ray_batches():
+    """BASELINE config 3 geometry (stand-in dragon, 871,414 triangles): batch A (primary) and batch B (diffuse bounce)."""
+    hs = scenes.HostScene("plastic_dragon", 256, 256)
+    gpu = hs.upload()
+    assert gpu.num_primitives() == 871416
+    oracle = orc.OracleScene(hs.tables())
+    cam = hs.camera()
+    rays = cam.primary_rays(256, 256)
+    want = oracle.intersect(rays, mode=0)
+    got = get_intersection(gpu, rays)
+    ties = compare_hits(got, want, None, "dragon primary")
+    on_dragon = (want["prim_index"] > 0) & (want["prim_index"] < 871415)
+    assert on_dragon.mean() > 0.15
+    hit = want["prim_index"] != NONE
+    rng = np.random.default_rng(4)
+    d = rng.normal(size=(hit.sum(), 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    d *= np.sign(np.sum(d * want["n"][hit], axis=1, keepdims=True))
+    rays2 = make_rays(want["p"][hit], d)
+    want2 = oracle.intersect(rays2, mode=0)
+    ties += compare_hits(get_intersection(gpu, rays2), want2, None, "dragon bounce")
+    print(f"dragon: {len(rays) + len(rays2)} rays, {ties} resolved inside an exact-t tie")
+    # shadow queries toward the light from every primary hit
+    light_prim = 871415
+    p1 = np.stack([rng.uniform(-5, 5, hit.sum()), np.full(hit.sum(), 15.0), rng.uniform(-5, 5, hit.sum())], 1)
+    vis_o = oracle.occluded(want["p"][hit], p1, np.full(hit.sum(), light_prim, dtype=np.uint32))
+    vis_g = unoccluded(gpu, want["p"][hit], p1, np.full(hit.sum(), light_prim, dtype=np.uint32))
+    assert np.array_equal(vis_o, vis_g), f"{np.count_nonzero(vis_o != vis_g)} shadow queries differ"
+    assert 0.2 < vis_o.mean() < 0.999
+
+
+def test_soup_rays():
+    hs = scenes.HostScene("soup", 512, 512, n_tris=200000)
+    gpu = hs.upload()
+    oracle = orc.OracleScene(hs.tables())
+    rays = hs.camera().primary_rays(512, 512)[::4]
+    want = oracle.intersect(rays, mode=0)
+    compare_hits(get_intersection(gpu, rays), want, None, "soup coherent")
+    hit = want["prim_index"] != NONE
+    assert hit.mean() > 0.3
+    rng = np.random.default_rng(6)
+    d = rng.normal(size=(hit.sum(), 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays2 = make_rays(want["p"][hit], d)
+    compare_hits(get_intersection(gpu, rays2), oracle.intersect(rays2, mode=0), None, "soup incoherent")
+
+
+def test_unoccluded_matches_oracle():
+    hs = scenes.HostScene("cornell_box", 64, 64)
+    gpu = hs.upload()
+    oracle = orc.OracleScene(hs.tables())
+    rng = np.random.default_rng(7)
+    n = 20000
+    p0 = rng.uniform(1, 554, (n, 3))
+    p1 = np.stack([rng.uniform(213, 343, n), np.full(n, 554.9), rng.uniform(227, 332, n)], 1)
+    prim = np.where(rng.uniform(size=n) < 0.9, 2, rng.integers(0, 18, n)).astype(np.uint32)
+    a = oracle.occluded(p0, p1, prim)
+    b = unoccluded(gpu, p0, p1, prim)
+    assert np.array_equal(a, b) and 0.1 < a.mean() < 0.9
+    a = oracle.occluded(p0[:2000], p0[:2000] + rng.normal(size=(2000, 3)) * 2e4, prim[:2000], infinite=True)
+    b = unoccluded(gpu, p0[:2000], p0[:2000] + rng.normal(size=(2000, 3)) * 2e4, prim[:2000], infinite_light=True)
+    assert np.array_equal(a, b)
+
+
+def film_compare(g, o, what, tol=1e-7, max_bad=2e-3):
+    """Per-pixel comparison of two (h,w,4) films rendered with the same counter-based RNG.
+    A pixel may differ when a knife-edge branch (u < F, tie, roulette) flips on a last-ulp libm difference."""
+    assert np.array_equal(g[..., 3], o[..., 3]), what + ": sample counts differ"
+    err = np.abs(g[..., :3] - o[..., :3]).max(-1)
+    scale = np.abs(o[..., :3]).max(-1) + 1e-6
+    bad = (err / scale) > tol
+    both_nan = np.isnan(g[..., :3]).any(-1) & np.isnan(o[..., :3]).any(-1)
+    bad &= ~both_nan
+    frac = bad.mean()
+    mean_g, mean_o = np.nanmean(g[..., :3]), np.nanmean(o[..., :3])
+    print(f"{what}: {bad.sum()} of {bad.size} pixels differ by more than {tol:g} rel; mean {mean_g:.6g} vs {mean_o:.6g}")
+    assert frac <= max_bad, f"{what}: {frac:.3%} of pixels differ"
+    assert abs(mean_g - mean_o) <= 0.01 * abs(mean_o) + 1e-9
+    return frac
+
+
+@pytest.mark.parametrize("name,kw,depth", [("sphere_roughness", {}, 25), ("cornell_box", {}, 25), ("make_world", {}, 16),
+                                           ("plastic_dragon", {}, 8), ("plastic_dragon", {"variant": 1}, 8), ("two_dragons", {"variant": 1}, 16),
+                                           ("cornell_box_statue", {"n_tris": 20000}, 8)])
+def test_render_matches_oracle_per_pixel(name, kw, depth):
+    w = h = 48
+    spp = 4
+    hs = scenes.HostScene(name, w, h, **kw)
+    gpu = hs.upload()
+    oracle = orc.OracleScene(hs.tables())
+    cam = hs.camera()
+    film = Film(w, h)
+    render_samples(gpu, cam, IntType.Path(depth), film, w, h, 0, spp, seed=42)
+    g = film.read()
+    o, counts, _ = oracle.render(cam, w, h, 0, spp, seed=42, max_depth=depth)
+    film_compare(g, o, f"{name}{kw}")
+    c = gpu.counters()
+    assert c["paths"] == w * h * spp
+    # same ray-counting rule on both sides (extend + shadow + probe); tiny slack for flipped branches
+    for k, v in zip(("extend_rays", "shadow_rays", "probe_rays"), counts):
+        assert abs(c[k] - int(v)) <= 0.002 * int(v) + 8, (k, c[k], int(v))
+    assert np.array_equal(film.resolve_rgb8()[~np.isnan(g[..., 0])], orc.resolve_rgb8(g)[~np.isnan(g[..., 0])])      # point_to_color parity
+
+
+def test_render_partition_invariance():
+    """Size-independent properties at the render level: sample ranges and pixel windows are additive, the
+    wavefront size does not matter (RNG is keyed by pixel/sample/dimension, not by scheduling)."""
+    w = h = 96
+    hs = scenes.HostScene("sphere_roughness", w, h)
+    gpu = hs.upload()
+    cam = hs.camera()
+    it = IntType.Path(25)
+    full = Film(w, h); render_samples(gpu, cam, it, full, w, h, 0, 8, seed=5)
+    a = full.read()
+    parts = Film(w, h)
+    render_samples(gpu, cam, it, parts, w, h, 0, 3, seed=5)
+    render_samples(gpu, cam, it, parts, w, h, 3, 8, seed=5)
+    b = parts.read()
+    assert np.allclose(a, b, rtol=1e-12, atol=1e-12, equal_nan=True)
+    tiles = Film(w, h)
+    for y in range(0, h, 32):
+        for x in range(0, w, 48):
+            render_samples(gpu, cam, it, tiles, w, h, 0, 8, seed=5, window=(x, y, min(x + 48, w), min(y + 32, h)))
+    assert np.allclose(a, tiles.read(), rtol=1e-12, atol=1e-12, equal_nan=True)
+    gpu.set_wavefront_size(4096)
+    small = Film(w, h); render_samples(gpu, cam, it, small, w, h, 0, 8, seed=5)
+    assert np.allclose(a, small.read(), rtol=1e-12, atol=1e-12, equal_nan=True)
+    assert np.all(a[..., 3] == 8)
+    other = Film(w, h); render_samples(gpu, cam, it, other, w, h, 0, 8, seed=6)
+    assert not np.allclose(a, other.read(), equal_nan=True)
+
+
+def test_image_relmse_against_converged_oracle():
+    """G_S accepted iff relMSE(G_S, R) <= 1.5 relMSE(O_S, R) and mean bias <= 1 %,
+    R = oracle at 16x the samples with a different seed (an independent estimate)."""
+    w = h = 40
+    hs = scenes.HostScene("cornell_box", w, h)
+    gpu = hs.upload()
+    oracle = orc.OracleScene(hs.tables())
+    cam = hs.camera()
+    S = 16
+    film = Film(w, h); render_samples(gpu, cam, IntType.Path(25), film, w, h, 0, S, seed=1)
+    G = film.read()[..., :3] / S
+    O = oracle.render(cam, w, h, 0, S, seed=2)[0][..., :3] / S
+    R = oracle.render(cam, w, h, 0, 16 * S, seed=3)[0][..., :3] / (16 * S)
+    rel = lambda a: np.mean((a - R) ** 2 / (R ** 2 + 1e-2))
+    print(f"relMSE gpu {rel(G):.4g} oracle {rel(O):.4g}; means {G.mean():.5g} {O.mean():.5g} {R.mean():.5g}")
+    assert rel(G) <= 1.5 * rel(O)
+    assert abs(G.mean() - R.mean()) <= 0.03 * R.mean()
