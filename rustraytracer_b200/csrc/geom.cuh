@@ -173,7 +173,7 @@ __device__ __forceinline__ void rec_from_partials(Rec& r, D3 p, D2 uv, D3 dpdu, 
 // by the rt_intersect epilogue on the closest primitive only.  Bitwise the same accept arithmetic as the
 // traversal, so it cannot disagree with it.  leaf_box = false gives Primitive::intersects_obj semantics
 // (primitive.rs:372-425) plus the FlipFace toggle being skipped by the caller.
-__device__ inline bool prim_record(const DScene& sc, uint32_t prim, D3 o, D3 d, double tmin, double tmax, bool leaf_box, Rec& r) {
+static __device__ __noinline__ bool prim_record(const DScene& sc, uint32_t prim, D3 o, D3 d, double tmin, double tmax, bool leaf_box, Rec& r) {
     DPrim pr = sc.prims[prim];
     uint32_t type = pr.info & 7u;
     r.prim = prim; r.mat = pr.mat;

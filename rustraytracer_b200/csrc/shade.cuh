@@ -13,7 +13,7 @@ constexpr double INV_PI = 1.0 / PI;                                             
 // ---- counter-based RNG replacing thread_rng()/StdRng::from_entropy() (sampler.rs:318,334-337; util.rs:32-34):
 // Philox4x32-10, key = seed, counter = (pixel, sample, dim, 'RTCX'); one uniform per counter.
 struct Rng { uint32_t k0, k1, pixel, sample, dim; };
-__device__ __forceinline__ double rng_next(Rng& g) {
+static __device__ __noinline__ double rng_next(Rng& g) {
     uint32_t c0 = g.pixel, c1 = g.sample, c2 = g.dim++, c3 = 0x52544358u, k0 = g.k0, k1 = g.k1;
 #pragma unroll
     for (int r = 0; r < 10; r++) {
@@ -38,7 +38,7 @@ __device__ __forceinline__ double sin_phi(D3 v) { double s = sin_theta(v); retur
 __device__ __forceinline__ bool matches_flags(uint32_t flag, uint32_t other) { return (flag & other) == flag; }
 __device__ __forceinline__ bool same_hemisphere(D3 v, D3 w) { return v.z * w.z > 0.; }                 // util.rs:591-593
 __device__ __forceinline__ D3 reflect(D3 v, D3 n) { double s = 2. * dot(v, n); return -v + n * s; }    // util.rs:203-206
-__device__ __forceinline__ bool refract(D3 vec, D3 n, double eta, D3& out) {                           // util.rs:376-385
+static __device__ __noinline__ bool refract(D3 vec, D3 n, double eta, D3& out) {                           // util.rs:376-385
     double cos_theta_i = dot(n, vec) / norm(vec);
     double sin2_theta_i = fmax(0., 1. - cos_theta_i * cos_theta_i);
     double sin2_theta_t = eta * eta * sin2_theta_i;
@@ -47,7 +47,7 @@ __device__ __forceinline__ bool refract(D3 vec, D3 n, double eta, D3& out) {    
     out = eta * (-vec) + (eta * cos_theta_i - cos_theta_t) * n;
     return true;
 }
-__device__ inline double fr_dielectric(double cos_theta_i, double eta_i, double eta_t) {               // bxdf.rs:113-136
+static __device__ __noinline__ double fr_dielectric(double cos_theta_i, double eta_i, double eta_t) {               // bxdf.rs:113-136
     cos_theta_i = clampd(cos_theta_i, -1., 1.);
     double index_i = eta_i, index_t = eta_t;
     if (cos_theta_i < 0.) { index_i = eta_t; index_t = eta_i; cos_theta_i = fabs(cos_theta_i); }
@@ -59,7 +59,7 @@ __device__ inline double fr_dielectric(double cos_theta_i, double eta_i, double 
     double r_perp = ((index_i * cos_theta_i) - (index_t * cos_theta_t)) / ((index_i * cos_theta_i) + (index_t * cos_theta_t));
     return (r_parl * r_parl + r_perp * r_perp) / 2.;
 }
-__device__ inline D3 fr_conductor(double cos_theta_i, D3 eta, D3 eta_k) {                              // bxdf.rs:141-170
+static __device__ __noinline__ D3 fr_conductor(double cos_theta_i, D3 eta, D3 eta_k) {                              // bxdf.rs:141-170
     cos_theta_i = clampd(cos_theta_i, -1., 1.);
     double c2 = cos_theta_i * cos_theta_i, s2 = 1. - c2;
     D3 eta2 = cmul(eta, eta), etak2 = cmul(eta_k, eta_k);
@@ -99,7 +99,7 @@ __device__ __forceinline__ D3 fresnel_eval(const Lobe& l, double cos_theta_i) {
     return mk3(1., 1., 1.);
 }
 // ---- microfacet.rs, TrowbridgeReitz{sample_visible_area:true} / Empty
-__device__ inline double mfd_d(const Lobe& m, D3 wh) {                                                 // microfacet.rs:53-68
+static __device__ __noinline__ double mfd_d(const Lobe& m, D3 wh) {                                                 // microfacet.rs:53-68
     if (m.mfd_empty) return 0.;
     double t2 = tan_sq_theta(wh);
     if (isinf(t2)) return 0.;
@@ -108,7 +108,7 @@ __device__ inline double mfd_d(const Lobe& m, D3 wh) {                          
     double e = ((cp * cp) / (m.alpha_x * m.alpha_x) + (sp * sp) / (m.alpha_y * m.alpha_y)) * t2;
     return 1. / (PI * m.alpha_x * m.alpha_y * cos4 * (1. + e) * (1. + e));
 }
-__device__ inline double mfd_lambda(const Lobe& m, D3 w) {                                             // microfacet.rs:109-123
+static __device__ __noinline__ double mfd_lambda(const Lobe& m, D3 w) {                                             // microfacet.rs:109-123
     if (m.mfd_empty) return 0.;
     double att = fabs(tan_theta(w));
     if (isinf(att)) return 0.;
@@ -123,12 +123,12 @@ __device__ __forceinline__ double mfd_pdf(const Lobe& m, D3 wo, D3 wh) {        
     if (!m.mfd_empty) return mfd_d(m, wh) * mfd_g1(m, wo) * fabs(dot(wo, wh)) / abs_cos_theta(wo);
     return mfd_d(m, wh) * abs_cos_theta(wh);
 }
-__device__ __forceinline__ double tr_roughness_to_alpha(double roughness) {                            // microfacet.rs:442-446
+static __device__ __noinline__ double tr_roughness_to_alpha(double roughness) {                            // microfacet.rs:442-446
     roughness = fmax(roughness, 1e-5);
     double x = log(roughness);
     return 1.62142 + 0.819955 * x + 0.1734 * x * x + 0.0171201 * x * x * x + 0.000640711 * x * x * x * x;
 }
-__device__ inline D2 tr_sample_11(double cos_t, double u1, double u2) {                                // microfacet.rs:469-512
+static __device__ __noinline__ D2 tr_sample_11(double cos_t, double u1, double u2) {                                // microfacet.rs:469-512
     if (cos_t > 0.9999) { double r = sqrt(u1 / (1. - u1)), phi = 2. * PI * u2; return mk2(r * cos(phi), r * sin(phi)); }
     double sin_t = fmax(0., sqrt(1. - cos_t * cos_t));
     double tan_t = sin_t / cos_t;
@@ -146,7 +146,7 @@ __device__ inline D2 tr_sample_11(double cos_t, double u1, double u2) {         
     double z = (nu2 * (nu2 * (nu2 * 0.27385 - 0.73369) + 0.46341)) / (nu2 * (nu2 * (nu2 * 0.093073 + 0.309420) - 1.) + 0.597999);
     return mk2(slope_x, s * z * sqrt(1. + slope_x * slope_x));
 }
-__device__ inline D3 mfd_sample_wh(const Lobe& m, D3 wo, D2 u) {                                       // microfacet.rs:240-283, 448-467
+static __device__ __noinline__ D3 mfd_sample_wh(const Lobe& m, D3 wo, D2 u) {                                       // microfacet.rs:240-283, 448-467
     if (m.mfd_empty) return normalize(mk3(0., 0., 0.));
     bool flip = wo.z < 0.;
     D3 wi = flip ? -wo : wo;
@@ -162,7 +162,7 @@ __device__ inline D3 mfd_sample_wh(const Lobe& m, D3 wo, D2 u) {                
 }
 
 // Bxdf::f (bxdf.rs:328-527)
-__device__ inline D3 lobe_f(const Lobe& l, D3 wo, D3 wi) {
+static __device__ __noinline__ D3 lobe_f(const Lobe& l, D3 wo, D3 wi) {
     switch (l.kind) {
         case L_LAMBERT: return l.color * INV_PI;
         case L_OREN_NAYAR: {
@@ -203,7 +203,7 @@ __device__ inline D3 lobe_f(const Lobe& l, D3 wo, D3 wi) {
 }
 __device__ __forceinline__ double default_pdf(D3 wo, D3 wi) { return same_hemisphere(wo, wi) ? abs_cos_theta(wi) * INV_PI : 0.; }   // bxdf.rs:829-835
 // Bxdf::pdf (bxdf.rs:721-813)
-__device__ inline double lobe_pdf(const Lobe& l, D3 wo, D3 wi) {
+static __device__ __noinline__ double lobe_pdf(const Lobe& l, D3 wo, D3 wi) {
     switch (l.kind) {
         case L_LAMBERT: case L_OREN_NAYAR: case L_SPEC_R: return default_pdf(wo, wi);
         case L_MICRO_R: {
@@ -224,7 +224,7 @@ __device__ inline double lobe_pdf(const Lobe& l, D3 wo, D3 wi) {
     }
 }
 // util::rand_cosine_dir (util.rs:127-148)
-__device__ inline D3 rand_cosine_dir(Rng& g) {
+static __device__ __noinline__ D3 rand_cosine_dir(Rng& g) {
     double r1 = rng_next(g), r2 = rng_next(g);
     double u1 = 2. * r1 - 1., u2 = 2. * r2 - 1.;
     if (u1 == 0. && u2 == 0.) return mk3(0., 0., 1.);
@@ -235,7 +235,7 @@ __device__ inline D3 rand_cosine_dir(Rng& g) {
     return mk3(x, y, sqrt(fmax(0., 1. - x * x - y * y)));
 }
 // Bxdf::sample_f (bxdf.rs:532-719)
-__device__ inline void lobe_sample_f(const Lobe& l, D3 wo, D2 sample, Rng& g, D3& color, D3& wi, double& pdf) {
+static __device__ __noinline__ void lobe_sample_f(const Lobe& l, D3 wo, D2 sample, Rng& g, D3& color, D3& wi, double& pdf) {
     color = mk3(0., 0., 0.); wi = mk3(0., 0., 0.); pdf = 0.;
     switch (l.kind) {
         case L_LAMBERT: case L_OREN_NAYAR: {             // default_sample_f (bxdf.rs:815-827): ignores `sample`
@@ -294,7 +294,7 @@ __device__ __forceinline__ D3 local_to_world(const Bsdf& b, D3 v) {
 }
 __device__ __forceinline__ uint32_t num_components(const Bsdf& b, uint32_t t) { uint32_t c = 0; for (int i = 0; i < b.n; i++) if (matches_flags(b.lobes[i].type, t)) c++; return c; }
 // Bsdf::f (bsdf.rs:83-98), `a && b || c` precedence kept
-__device__ inline D3 bsdf_f(const Bsdf& b, D3 wow, D3 wiw, uint32_t flags) {
+static __device__ __noinline__ D3 bsdf_f(const Bsdf& b, D3 wow, D3 wiw, uint32_t flags) {
     D3 wi = world_to_local(b, wiw), wo = world_to_local(b, wow);
     bool refl = dot(wiw, b.ng) * dot(wow, b.ng) > 0.;
     D3 f = mk3(0., 0., 0.);
@@ -305,7 +305,7 @@ __device__ inline D3 bsdf_f(const Bsdf& b, D3 wow, D3 wiw, uint32_t flags) {
     return f;
 }
 // Bsdf::pdf (bsdf.rs:166-189)
-__device__ inline double bsdf_pdf(const Bsdf& b, D3 wow, D3 wiw, uint32_t flags) {
+static __device__ __noinline__ double bsdf_pdf(const Bsdf& b, D3 wow, D3 wiw, uint32_t flags) {
     if (b.n == 0) return 0.;
     D3 wo = world_to_local(b, wow), wi = world_to_local(b, wiw);
     if (wo.z == 0.) return 0.;
@@ -314,7 +314,7 @@ __device__ inline double bsdf_pdf(const Bsdf& b, D3 wow, D3 wiw, uint32_t flags)
     return matching > 0 ? pdf : 0.;
 }
 // Bsdf::sample_f (bsdf.rs:102-164)
-__device__ inline void bsdf_sample_f(const Bsdf& b, D3 wow, D2 sample, uint32_t bxdf_type, Rng& g, D3& color, D3& wiw, double& pdf, uint32_t& sampled) {
+static __device__ __noinline__ void bsdf_sample_f(const Bsdf& b, D3 wow, D2 sample, uint32_t bxdf_type, Rng& g, D3& color, D3& wiw, double& pdf, uint32_t& sampled) {
     color = mk3(0., 0., 0.); wiw = mk3(0., 0., 0.); pdf = 0.; sampled = 0;
     uint32_t matching = num_components(b, bxdf_type);
     if (matching == 0) return;
@@ -345,7 +345,7 @@ __device__ inline void bsdf_sample_f(const Bsdf& b, D3 wow, D2 sample, uint32_t 
 
 // ---- material.rs
 // Texture::value (material.rs:542-589): SolidColor, Checkered (ids may nest)
-__device__ inline D3 tex_value(const DScene& sc, uint32_t id, double u, double v) {
+static __device__ __noinline__ D3 tex_value(const DScene& sc, uint32_t id, double u, double v) {
     for (int depth = 0; depth < 8; depth++) {
         const rt_texture& t = sc.textures[id];
         if (t.type != RT_TEX_CHECKERED) return mk3(t.color[0], t.color[1], t.color[2]);
@@ -362,7 +362,7 @@ __device__ __forceinline__ void bsdf_new(Bsdf& b, const Rec& r) {               
     b.ns = r.sn; b.ng = r.n; b.ss = r.sdpdu; b.ts = normalize(cross(r.sn, r.sdpdu)); b.empty = false;
 }
 // Material::compute_scattering (material.rs:80-244), mode = RADIANCE, allow_lobes = true
-__device__ inline void compute_scattering(const DScene& sc, const Rec& r, Bsdf& b) {
+static __device__ __noinline__ void compute_scattering(const DScene& sc, const Rec& r, Bsdf& b) {
     double n1 = 1. / sqrt(3.);
     (void)n1;
     D3 e = normalize(mk3(1., 1., 1.));                 // Bsdf::empty frame (bsdf.rs:37-47)
@@ -451,7 +451,7 @@ __device__ inline void compute_scattering(const DScene& sc, const Rec& r, Bsdf& 
 
 // ---- primitive.rs sampling / light.rs Diffuse
 // Primitive::sample_area (primitive.rs:478-539): point and normal on the light's primitive
-__device__ inline void sample_area(const DScene& sc, uint32_t prim, D2 u, D3& p, D3& n) {
+static __device__ __noinline__ void sample_area(const DScene& sc, uint32_t prim, D2 u, D3& p, D3& n) {
     DPrim pr = sc.prims[prim];
     uint32_t type = pr.info & 7u;
     if (type == RT_PRIM_TRIANGLE) {
