@@ -39,7 +39,9 @@ struct Ctrl {
     uint32_t n_cur, n_new, n_tot, n_next, n_shadow, n_probe, pad0, pad1;
     unsigned long long next_sample, sample_base, total_samples;
     unsigned long long c_paths, c_extend, c_shadow, c_probe, c_iter;
+    uint32_t bin_count[16];      // paths per shading bin after extend (material type x primitive class, 15 = miss)
 };
+constexpr int N_BINS = 16;
 struct RenderParams {
     rt_camera cam; uint32_t width, height, x0, y0, ww, wh, sample_begin; uint32_t max_depth, invisible_light; uint32_t k0, k1; uint32_t W;
 };
@@ -48,6 +50,7 @@ struct Wavefront {
     uint32_t W = 0;
     PathSet set[2]{}; ConnQ shadow{}, probe{};
     uint32_t* hit_prim = nullptr; double* hit_t = nullptr;
+    uint32_t* bin_idx = nullptr;                  // N_BINS x W path indices, filled by extend
     Ctrl* ctrl = nullptr; Ctrl* h_ctrl = nullptr;
     cudaStream_t stream = nullptr;
     std::vector<void*> allocs;
@@ -76,6 +79,7 @@ __global__ void k_prepare(Ctrl* c, uint32_t W) {
     uint32_t n_new = (uint32_t)(remaining < (unsigned long long)room ? remaining : (unsigned long long)room);
     c->n_cur = n_cur; c->n_new = n_new; c->n_tot = n_cur + n_new; c->n_next = 0; c->n_shadow = 0; c->n_probe = 0;
     c->sample_base = c->next_sample; c->next_sample += n_new; c->c_paths += n_new;
+    for (int b = 0; b < N_BINS; b++) c->bin_count[b] = 0;
 }
 
 // PathIntegrator::single_sample up to the camera ray (integrator.rs:357-365), Samplers::get_camera_sample
@@ -110,12 +114,25 @@ __global__ void __launch_bounds__(256) k_generate(const Ctrl* __restrict__ c, Re
     }
 }
 
-// ray type A: geometry::get_intersection (geometry.rs:238-240)
-__global__ void __launch_bounds__(128) k_extend(const Ctrl* __restrict__ c, DScene sc, PathSet ps, uint32_t* __restrict__ hit_prim, double* __restrict__ hit_t) {
+// ray type A: geometry::get_intersection (geometry.rs:238-240).  Besides the hit, extend files every path into a
+// shading bin keyed by (material type, triangle / parametric shape) — or "miss" — with one atomic per distinct key
+// per warp (__match_any_sync), so that the shade kernel runs warps of like work instead of diverging on the
+// reference's `match material` / `match primitive` arms.
+__global__ void __launch_bounds__(128) k_extend(Ctrl* c, DScene sc, PathSet ps, uint32_t* __restrict__ hit_prim, double* __restrict__ hit_t,
+                                               uint32_t* __restrict__ bin_idx, uint32_t W) {
     uint32_t n = c->n_tot;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         Hit h = trace_closest(sc, mk3(ps.ox[i], ps.oy[i], ps.oz[i]), mk3(ps.dx[i], ps.dy[i], ps.dz[i]), SMALL, INF);
         hit_prim[i] = h.prim; hit_t[i] = h.t;
+        uint32_t key = N_BINS - 1;
+        if (h.prim != RT_NONE) { DPrim pr = sc.prims[h.prim]; key = sc.materials[pr.mat].type * 2u + ((pr.info & 7u) == RT_PRIM_TRIANGLE ? 1u : 0u); }
+        unsigned active = __activemask();
+        unsigned peers = __match_any_sync(active, key);
+        int leader = __ffs(peers) - 1, lane = threadIdx.x & 31;
+        uint32_t base = 0;
+        if (lane == leader) base = atomicAdd(&c->bin_count[key], (uint32_t)__popc(peers));
+        base = __shfl_sync(peers, base, leader);
+        bin_idx[(size_t)key * W + base + __popc(peers & ((1u << lane) - 1u))] = i;
     }
 }
 
@@ -127,9 +144,15 @@ __device__ __forceinline__ double power_heuristic(double f_pdf, double g_pdf) { 
 
 // the body of PathIntegrator::li's loop (integrator.rs:386-443) for one path vertex
 __global__ void __launch_bounds__(128) k_shade(Ctrl* c, DScene sc, RenderParams rp, PathSet in, PathSet out, const uint32_t* __restrict__ hit_prim,
-                                              ConnQ shq, ConnQ prq, double* film) {
+                                              const uint32_t* __restrict__ bin_idx, ConnQ shq, ConnQ prq, double* film) {
     uint32_t n = c->n_tot;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    uint32_t bin_end[N_BINS];
+    { uint32_t acc = 0; for (int b = 0; b < N_BINS; b++) { acc += c->bin_count[b]; bin_end[b] = acc; } }
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+        int bin = 0; uint32_t bin_begin = 0;
+#pragma unroll
+        for (int b = 0; b < N_BINS - 1; b++) if (k >= bin_end[b]) { bin = b + 1; bin_begin = bin_end[b]; }
+        const uint32_t i = bin_idx[(size_t)bin * rp.W + (k - bin_begin)];
         D3 o = mk3(in.ox[i], in.oy[i], in.oz[i]), d = mk3(in.dx[i], in.dy[i], in.dz[i]);
         D3 beta = mk3(in.bx[i], in.by[i], in.bz[i]);
         uint32_t pixel = in.pixel[i], flags = in.flags[i];
@@ -225,10 +248,10 @@ __global__ void __launch_bounds__(128) k_shade(Ctrl* c, DScene sc, RenderParams 
             alive = true;
         } while (false);
         if (alive) {
-            uint32_t k = warp_append(&c->n_next);
-            out.ox[k] = o.x; out.oy[k] = o.y; out.oz[k] = o.z; out.dx[k] = d.x; out.dy[k] = d.y; out.dz[k] = d.z;
-            out.bx[k] = beta.x; out.by[k] = beta.y; out.bz[k] = beta.z;
-            out.pixel[k] = pixel; out.sample[k] = rng.sample; out.dim[k] = rng.dim; out.flags[k] = (bounces & 0xffffu) | (specular_bounce ? 0x10000u : 0u);
+            uint32_t q = warp_append(&c->n_next);
+            out.ox[q] = o.x; out.oy[q] = o.y; out.oz[q] = o.z; out.dx[q] = d.x; out.dy[q] = d.y; out.dz[q] = d.z;
+            out.bx[q] = beta.x; out.by[q] = beta.y; out.bz[q] = beta.z;
+            out.pixel[q] = pixel; out.sample[q] = rng.sample; out.dim[q] = rng.dim; out.flags[q] = (bounces & 0xffffu) | (specular_bounce ? 0x10000u : 0u);
         }
     }
 }
@@ -305,7 +328,7 @@ static Wavefront* get_wavefront(rt_scene& s) {
     w->W = s.wavefront_size;
     size_t n = w->W;
     bool ok = alloc_set(*w, w->set[0], n) && alloc_set(*w, w->set[1], n) && alloc_q(*w, w->shadow, n) && alloc_q(*w, w->probe, n) &&
-              dalloc(*w, w->hit_prim, n) && dalloc(*w, w->hit_t, n) && dalloc(*w, w->ctrl, 1) &&
+              dalloc(*w, w->hit_prim, n) && dalloc(*w, w->hit_t, n) && dalloc(*w, w->bin_idx, n * N_BINS) && dalloc(*w, w->ctrl, 1) &&
               cudaMallocHost((void**)&w->h_ctrl, sizeof(Ctrl)) == cudaSuccess && cudaStreamCreateWithFlags(&w->stream, cudaStreamNonBlocking) == cudaSuccess;
     if (!ok) { set_error(std::string("wavefront allocation failed: ") + cudaGetErrorString(cudaGetLastError())); destroy_wavefront(w); return nullptr; }
     s.wavefront = w;
@@ -392,9 +415,9 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
             cudaEventRecord(ev(w, n_ev + 0), st);
             k_generate<<<g256, 256, 0, st>>>(w.ctrl, rp, w.set[cur], film->d);
             cudaEventRecord(ev(w, n_ev + 1), st);
-            k_extend<<<g128, 128, 0, st>>>(w.ctrl, s->d, w.set[cur], w.hit_prim, w.hit_t);
+            k_extend<<<g128, 128, 0, st>>>(w.ctrl, s->d, w.set[cur], w.hit_prim, w.hit_t, w.bin_idx, w.W);
             cudaEventRecord(ev(w, n_ev + 2), st);
-            k_shade<<<g128, 128, 0, st>>>(w.ctrl, s->d, rp, w.set[cur], w.set[cur ^ 1], w.hit_prim, w.shadow, w.probe, film->d);
+            k_shade<<<g128, 128, 0, st>>>(w.ctrl, s->d, rp, w.set[cur], w.set[cur ^ 1], w.hit_prim, w.bin_idx, w.shadow, w.probe, film->d);
             cudaEventRecord(ev(w, n_ev + 3), st);
             k_connect_shadow<<<g128, 128, 0, st>>>(w.ctrl, s->d, w.shadow, film->d);
             k_connect_probe<<<g128, 128, 0, st>>>(w.ctrl, s->d, w.probe, film->d);
