@@ -134,11 +134,15 @@ typedef struct rt_shadow_query {
 
 /* `IntType::Path{max_depth, invisible_light}` (integrator.rs:37-40) */
 enum { RT_INTEGRATOR_PATH = 0 };
+/* flags: radiometric precision of the shade kernel.  0 = f64 in the reference's operation order (films match the
+ * f64 oracle per pixel); RT_SHADE_F32 = same formulas in f32 (production speed; image parity within the stated
+ * relative MSE).  Geometry — intersection decisions, hit points, ray origins — is f64-exact in both. */
+enum { RT_SHADE_F32 = 1 };
 typedef struct rt_integrator_desc {
     uint32_t kind;
     uint32_t max_depth;
     uint32_t invisible_light;
-    uint32_t _pad;
+    uint32_t flags;
 } rt_integrator_desc;
 
 /* What `GLOBAL_STATE` width/height/spp (main.rs:74-88) and the tile/sample partition of

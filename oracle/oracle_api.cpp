@@ -115,14 +115,18 @@ void orc_camera_look_at(const double from[3], const double to[3], const double u
 // render::tile_multithread (render.rs:13-159) semantics: worker threads pull 16x16 tiles, every pixel gets
 // samples [sample_begin, sample_end).  film: width*height*4 doubles (r,g,b,n) running sums.
 // counts[0..2] += extend, shadow, probe rays.  Returns wall seconds.
-double orc_render(void* sp, const rt_camera* cam, uint32_t max_depth, uint32_t invisible_light, const rt_film_desc* d,
-                  int threads, double* film, uint64_t* counts) {
+// pixel_stride > 1 renders only pixels whose index py*width+px is a multiple of it (bounded CPU-baseline samples).
+// counts[3..4] += box / primitive tests of the extend rays under the ordered traversal when count_ordered != 0.
+double orc_render_ex(void* sp, const rt_camera* cam, uint32_t max_depth, uint32_t invisible_light, const rt_film_desc* d,
+                     int threads, double* film, uint64_t* counts, uint32_t pixel_stride, int count_ordered) {
     const Scene& s = *(Scene*)sp;
     const uint32_t TILE = 16;   // consts.rs:10
     uint32_t tx0 = d->x0 / TILE, ty0 = d->y0 / TILE, tx1 = (d->x1 + TILE - 1) / TILE, ty1 = (d->y1 + TILE - 1) / TILE;
     uint64_t ntiles = (uint64_t)(tx1 - tx0) * (ty1 - ty0);
     std::atomic<uint64_t> next(0);
     std::vector<RayCounts> rcs(std::max(threads, 1));
+    for (auto& r : rcs) r.count_ordered = count_ordered != 0;
+    if (pixel_stride == 0) pixel_stride = 1;
     auto t_start = std::chrono::steady_clock::now();
     auto worker = [&](int t) {
         for (;;) {
@@ -130,6 +134,7 @@ double orc_render(void* sp, const rt_camera* cam, uint32_t max_depth, uint32_t i
             uint32_t tx = tx0 + (uint32_t)(tile % (tx1 - tx0)), ty = ty0 + (uint32_t)(tile / (tx1 - tx0));
             for (uint32_t py = std::max(ty * TILE, d->y0); py < std::min((ty + 1) * TILE, d->y1); py++)
                 for (uint32_t px = std::max(tx * TILE, d->x0); px < std::min((tx + 1) * TILE, d->x1); px++) {
+                    if (((uint64_t)py * d->width + px) % pixel_stride != 0) continue;
                     double* cell = film + 4 * ((uint64_t)py * d->width + px);
                     for (uint32_t smp = d->sample_begin; smp < d->sample_end; smp++) {
                         V3 c = single_sample(s, *cam, d->width, d->height, px, py, smp, d->seed, max_depth, invisible_light != 0, rcs[t]);
@@ -141,8 +146,15 @@ double orc_render(void* sp, const rt_camera* cam, uint32_t max_depth, uint32_t i
     if (threads <= 1) worker(0);
     else { std::vector<std::thread> pool; for (int t = 0; t < threads; t++) pool.emplace_back(worker, t); for (auto& th : pool) th.join(); }
     double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_start).count();
-    if (counts) for (auto& r : rcs) { counts[0] += r.extend; counts[1] += r.shadow; counts[2] += r.probe; }
+    if (counts) for (auto& r : rcs) {
+        counts[0] += r.extend; counts[1] += r.shadow; counts[2] += r.probe;
+        if (count_ordered) { counts[3] += r.ordered.box_tests; counts[4] += r.ordered.prim_tests; }
+    }
     return secs;
+}
+double orc_render(void* sp, const rt_camera* cam, uint32_t max_depth, uint32_t invisible_light, const rt_film_desc* d,
+                  int threads, double* film, uint64_t* counts) {
+    return orc_render_ex(sp, cam, max_depth, invisible_light, d, threads, film, counts, 1, 0);
 }
 
 // one camera sample, for per-sample parity checks; out rgb

@@ -517,7 +517,11 @@ inline LiSample sample_li(const Scene& s, const Light& l, const HitRecord& rec, 
 inline double pdf_li(const Scene& s, const Light& l, const HitRecord& rec, const V3& wi) { return prim_pdf(s, s.prims[l.d.prim_index], rec, wi); }
 
 // ------------------------------------------------------------------ integrator.rs (Path)
-struct RayCounts { uint64_t extend = 0, shadow = 0, probe = 0; };
+struct RayCounts {
+    uint64_t extend = 0, shadow = 0, probe = 0;
+    // optional: algorithmic work of the extend rays under the ordered "reference traversal" of SURVEY.md §8(d)
+    bool count_ordered = false; TravStats ordered;
+};
 inline double power_heuristic(int nf, double f_pdf, int ng, double g_pdf) {     // integrator.rs:655-659
     double f = nf * f_pdf, g = ng * g_pdf;
     return (f * f) / (f * f + g * g);
@@ -582,6 +586,7 @@ inline V3 path_li(const Scene& s, Ray ray, uint32_t max_depth, bool invisible_li
     for (;;) {
         HitRecord rec; rc.extend++;
         bool is_some = get_intersection(s, ray, rec);
+        if (rc.count_ordered) { bool h2; HitRecord r2; closest_ordered(s, ray, SMALL, INF, h2, r2, rc.ordered); }
         if (!is_some) rec = record_basic(V3(0, 0, 0), 0.);
         if (bounces == 0 || specular_bounce) {
             if (is_some) {

@@ -15,6 +15,7 @@ RT_NONE = 0xFFFFFFFF
 RT_OK, RT_ERR_INVALID, RT_ERR_CUDA, RT_ERR_STATE, RT_ERR_CANCELLED, RT_ERR_IO = range(6)
 PRIM_SPHERE, PRIM_TRIANGLE, PRIM_XY_RECT, PRIM_XZ_RECT, PRIM_YZ_RECT = range(5)
 TEX_SOLID, TEX_CHECKERED = 0, 1
+SHADE_F32 = 1
 MAT_MATTE, MAT_LIGHT, MAT_PLASTIC, MAT_GLASS, MAT_METAL, MAT_MIRROR = range(6)
 
 # numpy mirrors of the POD structs (align=True reproduces the C layout)
@@ -38,7 +39,7 @@ class Camera(C.Structure):
 
 
 class IntegratorDesc(C.Structure):
-    _fields_ = [("kind", C.c_uint32), ("max_depth", C.c_uint32), ("invisible_light", C.c_uint32), ("_pad", C.c_uint32)]
+    _fields_ = [("kind", C.c_uint32), ("max_depth", C.c_uint32), ("invisible_light", C.c_uint32), ("flags", C.c_uint32)]
 
 
 class FilmDesc(C.Structure):

@@ -54,10 +54,13 @@ class IntType:
     reference ever selects (main.rs:262-265)."""
     max_depth: int = MAX_DEPTH
     invisible_light: bool = False
+    # radiometric precision of the shade kernel: False = f64 in the reference's operation order (per-pixel parity
+    # with the f64 oracle), True = f32 (production speed).  Intersection decisions are f64-exact in both.
+    shade_f32: bool = False
 
     @staticmethod
-    def Path(max_depth=MAX_DEPTH, invisible_light=False):
-        return IntType(max_depth, invisible_light)
+    def Path(max_depth=MAX_DEPTH, invisible_light=False, shade_f32=False):
+        return IntType(max_depth, invisible_light, shade_f32)
 
 
 @dataclass
@@ -228,7 +231,7 @@ def render_samples(objects, camera, int_type, film, width, height, sample_begin,
     """`Integrator::render` over a pixel window and a sample range (integrator.rs:336-348): adds
     samples [sample_begin, sample_end) of every pixel in `window` = (x0, y0, x1, y1) to `film`."""
     x0, y0, x1, y1 = window if window is not None else (0, 0, width, height)
-    integ = N.IntegratorDesc(0, int(int_type.max_depth), 1 if int_type.invisible_light else 0, 0)
+    integ = N.IntegratorDesc(0, int(int_type.max_depth), 1 if int_type.invisible_light else 0, N.SHADE_F32 if int_type.shade_f32 else 0)
     fd = N.FilmDesc(width, height, int(sample_begin), int(sample_end), x0, y0, x1, y1, int(seed))
     check(lib().rt_render(objects.h, C.byref(camera.c), C.byref(integ), C.byref(fd), film.h))
 

@@ -140,9 +140,11 @@ __device__ __forceinline__ D3 light_l(const DLight& l, D3 n, D3 w) {      // Lig
     if (dot(n, w) > 0. || l.two_sided) return ld3(l.color);
     return mk3(0., 0., 0.);
 }
-__device__ __forceinline__ double power_heuristic(double f_pdf, double g_pdf) { double f = 1. * f_pdf, g = 1. * g_pdf; return (f * f) / (f * f + g * g); }   // integrator.rs:655-659
+template <class R> __device__ __forceinline__ R power_heuristic(R f_pdf, R g_pdf) { R f = R(1) * f_pdf, g = R(1) * g_pdf; return (f * f) / (f * f + g * g); }   // integrator.rs:655-659
 
-// the body of PathIntegrator::li's loop (integrator.rs:386-443) for one path vertex
+// The body of PathIntegrator::li's loop (integrator.rs:386-443) for one path vertex.  R = double reproduces the
+// reference's arithmetic; R = float is the production path (geometry stays f64 in both, see shade.cuh).
+template <class R>
 __global__ void __launch_bounds__(128) k_shade(Ctrl* c, DScene sc, RenderParams rp, PathSet in, PathSet out, const uint32_t* __restrict__ hit_prim,
                                               const uint32_t* __restrict__ bin_idx, ConnQ shq, ConnQ prq, double* film) {
     uint32_t n = c->n_tot;
@@ -154,7 +156,7 @@ __global__ void __launch_bounds__(128) k_shade(Ctrl* c, DScene sc, RenderParams 
         for (int b = 0; b < N_BINS - 1; b++) if (k >= bin_end[b]) { bin = b + 1; bin_begin = bin_end[b]; }
         const uint32_t i = bin_idx[(size_t)bin * rp.W + (k - bin_begin)];
         D3 o = mk3(in.ox[i], in.oy[i], in.oz[i]), d = mk3(in.dx[i], in.dy[i], in.dz[i]);
-        D3 beta = mk3(in.bx[i], in.by[i], in.bz[i]);
+        V3<R> beta = v3<R>((R)in.bx[i], (R)in.by[i], (R)in.bz[i]);
         uint32_t pixel = in.pixel[i], flags = in.flags[i];
         Rng rng; rng.k0 = rp.k0; rng.k1 = rp.k1; rng.pixel = pixel; rng.sample = in.sample[i]; rng.dim = in.dim[i];
         uint32_t bounces = flags & 0xffffu; bool specular_bounce = (flags >> 16) & 1u;
@@ -169,19 +171,20 @@ __global__ void __launch_bounds__(128) k_shade(Ctrl* c, DScene sc, RenderParams 
                     uint32_t li = sc.prims[prim].light;
                     if (li != RT_NONE) {
                         if (rp.invisible_light) { o = rec.p; alive = true; break; }          // go straight through the light, same bounce
-                        film_add(film, pixel, cmul(light_l(sc.lights[li], rec.n, -d), beta));   // HitRecord::le (hittable.rs:215-225)
+                        film_add(film, pixel, dbl3(cmul(cast3<R>(light_l(sc.lights[li], rec.n, -d)), beta)));   // HitRecord::le (hittable.rs:215-225)
                     }
                 }   // miss: only Infinite lights emit (light.rs:499-513) — none in scope
             }
             if (!is_some || bounces >= rp.max_depth) break;
-            Bsdf bsdf;
-            compute_scattering(sc, rec, bsdf);
+            Bsdf<R> bsdf;
+            compute_scattering<R>(sc, rec, bsdf);
+            const V3<R> wo_w = cast3<R>(rec.wo), sn = cast3<R>(rec.sn);
             // uniform_sample_one_light (integrator.rs:530-557)
             uint32_t n_lights = sc.n_lights;
             if (n_lights != 0) {
                 uint32_t light_num = min(n_lights - 1, (uint32_t)(unsigned long long)(rng_next(rng) * (double)n_lights));
                 D2 u_light; u_light.x = rng_next(rng); u_light.y = rng_next(rng);
-                D2 u_scatter; u_scatter.x = rng_next(rng); u_scatter.y = rng_next(rng);
+                V2<R> u_scatter; u_scatter.x = rng_real<R>(rng); u_scatter.y = rng_real<R>(rng);
                 const DLight light = sc.lights[light_num];
                 const uint32_t nsf = BSDF_ALL - BSDF_SPECULAR;
                 // estimate_direct, light half (integrator.rs:573-597); Light::sample_li Diffuse (light.rs:176-203), Primitive::sample (primitive.rs:445-456)
@@ -191,16 +194,17 @@ __global__ void __launch_bounds__(128) k_shade(Ctrl* c, DScene sc, RenderParams 
                     D3 wiu = p1 - rec.p;
                     if (norm2(wiu) == 0.) pdf = 0.;
                     else { D3 wn = normalize(wiu); pdf = pdf * norm2(rec.p - p1) / fabs(dot(n1, -wn)); }
-                    double light_pdf; D3 color, wi = mk3(0., 0., 0.);
+                    double light_pdf; D3 color, wid = mk3(0., 0., 0.);
                     if (pdf == 0. || norm2(rec.p - p1) == 0.) { light_pdf = 0.; color = ld3(light.color); }
-                    else { wi = normalize(p1 - rec.p); light_pdf = pdf; color = light_l(light, n1, -wi); }
+                    else { wid = normalize(p1 - rec.p); light_pdf = pdf; color = light_l(light, n1, -wid); }
                     if (light_pdf > 0. && !is_black(color)) {
-                        D3 f = bsdf_f(bsdf, rec.wo, wi, nsf) * fabs(dot(wi, rec.sn));
-                        double scattering_pdf = bsdf_pdf(bsdf, rec.wo, wi, nsf);
+                        V3<R> wi = cast3<R>(wid);
+                        V3<R> f = bsdf_f<R>(bsdf, wo_w, wi, nsf) * fabs(dot(wi, sn));
+                        R scattering_pdf = bsdf_pdf<R>(bsdf, wo_w, wi, nsf);
                         if (!is_black(f)) {
-                            double weight = power_heuristic(light_pdf, scattering_pdf);
-                            D3 ld = cmul(f, color) * (weight / light_pdf);
-                            D3 contrib = cmul(ld * (double)n_lights, beta);
+                            R weight = power_heuristic<R>((R)light_pdf, scattering_pdf);
+                            V3<R> ld = cmul(f, cast3<R>(color)) * (weight / (R)light_pdf);
+                            V3<R> contrib = cmul(ld * (R)n_lights, beta);
                             uint32_t q = warp_append(&c->n_shadow);
                             shq.ax[q] = rec.p.x; shq.ay[q] = rec.p.y; shq.az[q] = rec.p.z; shq.bx[q] = p1.x; shq.by[q] = p1.y; shq.bz[q] = p1.z;
                             shq.cr[q] = contrib.x; shq.cg[q] = contrib.y; shq.cb[q] = contrib.z; shq.target[q] = light.prim; shq.pixel[q] = pixel;
@@ -209,40 +213,41 @@ __global__ void __launch_bounds__(128) k_shade(Ctrl* c, DScene sc, RenderParams 
                 }
                 // estimate_direct, BSDF half (integrator.rs:601-632)
                 {
-                    D3 f, wi; double scattering_pdf; uint32_t st;
-                    bsdf_sample_f(bsdf, rec.wo, u_scatter, nsf, rng, f, wi, scattering_pdf, st);
-                    f = f * fabs(dot(wi, rec.sn));
-                    if (!is_black(f) && scattering_pdf > 0.) {
-                        double weight = 1.; bool go = true;
+                    V3<R> f, wi; R scattering_pdf; uint32_t st;
+                    bsdf_sample_f<R>(bsdf, wo_w, u_scatter, nsf, rng, f, wi, scattering_pdf, st);
+                    f = f * fabs(dot(wi, sn));
+                    if (!is_black(f) && scattering_pdf > R(0)) {
+                        R weight = R(1); bool go = true;
+                        D3 wid = dbl3(wi);
                         if ((st & BSDF_SPECULAR) == 0) {
                             // Light::pdf_li → Primitive::pdf (primitive.rs:462-473): re-intersect the ONE light primitive, tmin = 0, no leaf box
                             Rec lr; double light_pdf = 0.;
-                            if (prim_record(sc, light.prim, rec.p, wi, 0., INF, false, lr)) light_pdf = norm2(rec.p - lr.p) / (light.area * fabs(dot(lr.n, -wi)));
+                            if (prim_record(sc, light.prim, rec.p, wid, 0., INF, false, lr)) light_pdf = norm2(rec.p - lr.p) / (light.area * fabs(dot(lr.n, -wid)));
                             if (light_pdf == 0.) go = false;
-                            else weight = power_heuristic(scattering_pdf, light_pdf);
+                            else weight = power_heuristic<R>(scattering_pdf, (R)light_pdf);
                         }
                         if (go) {
-                            D3 contrib = cmul((f * (weight / scattering_pdf)) * (double)n_lights, beta);   // × Le decided by the probe ray
+                            V3<R> contrib = cmul((f * (weight / scattering_pdf)) * (R)n_lights, beta);   // × Le decided by the probe ray
                             uint32_t q = warp_append(&c->n_probe);
-                            prq.ax[q] = rec.p.x; prq.ay[q] = rec.p.y; prq.az[q] = rec.p.z; prq.bx[q] = wi.x; prq.by[q] = wi.y; prq.bz[q] = wi.z;
+                            prq.ax[q] = rec.p.x; prq.ay[q] = rec.p.y; prq.az[q] = rec.p.z; prq.bx[q] = wid.x; prq.by[q] = wid.y; prq.bz[q] = wid.z;
                             prq.cr[q] = contrib.x; prq.cg[q] = contrib.y; prq.cb[q] = contrib.z; prq.target[q] = light_num; prq.pixel[q] = pixel;
                         }
                     }
                 }
             }
             // continuation (integrator.rs:421-441)
-            D3 wo = -d;
-            D2 u; u.x = rng_next(rng); u.y = rng_next(rng);
-            D3 f, wi; double pdf; uint32_t sflags;
-            bsdf_sample_f(bsdf, wo, u, BSDF_ALL, rng, f, wi, pdf, sflags);
-            if (is_black(f) || pdf == 0.) break;
-            beta = cmul(beta, f) * (fabs(dot(wi, rec.sn)) / pdf);
+            V3<R> wo = cast3<R>(-d);
+            V2<R> u; u.x = rng_real<R>(rng); u.y = rng_real<R>(rng);
+            V3<R> f, wi; R pdf; uint32_t sflags;
+            bsdf_sample_f<R>(bsdf, wo, u, BSDF_ALL, rng, f, wi, pdf, sflags);
+            if (is_black(f) || pdf == R(0)) break;
+            beta = cmul(beta, f) * (fabs(dot(wi, sn)) / pdf);
             specular_bounce = (sflags & BSDF_SPECULAR) != 0;
-            o = rec.p; d = wi;
+            o = rec.p; d = dbl3(wi);
             if (bounces > 3) {
-                double q = fmax(0.05, 1. - fmax(beta.x, fmax(beta.y, beta.z)));
-                if (rng_next(rng) < q) break;
-                beta = beta * (1. / (1. - q));
+                R q = fmax(R(0.05), R(1) - fmax(beta.x, fmax(beta.y, beta.z)));
+                if (rng_real<R>(rng) < q) break;
+                beta = beta * (R(1) / (R(1) - q));
             }
             bounces++;
             alive = true;
@@ -408,6 +413,7 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
     size_t n_ev = 2;
     CK(cudaEventRecord(e_begin, st));
     int cur = 0; uint64_t iter = 0; bool done = false; rt_status result = RT_OK;
+    const bool f32 = (integ->flags & RT_SHADE_F32) != 0;
     while (!done) {
         for (int k = 0; k < 4; k++, iter++) {
             k_prepare<<<1, 1, 0, st>>>(w.ctrl, w.W);
@@ -417,7 +423,8 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
             cudaEventRecord(ev(w, n_ev + 1), st);
             k_extend<<<g128, 128, 0, st>>>(w.ctrl, s->d, w.set[cur], w.hit_prim, w.hit_t, w.bin_idx, w.W);
             cudaEventRecord(ev(w, n_ev + 2), st);
-            k_shade<<<g128, 128, 0, st>>>(w.ctrl, s->d, rp, w.set[cur], w.set[cur ^ 1], w.hit_prim, w.bin_idx, w.shadow, w.probe, film->d);
+            if (f32) k_shade<float><<<g128, 128, 0, st>>>(w.ctrl, s->d, rp, w.set[cur], w.set[cur ^ 1], w.hit_prim, w.bin_idx, w.shadow, w.probe, film->d);
+            else k_shade<double><<<g128, 128, 0, st>>>(w.ctrl, s->d, rp, w.set[cur], w.set[cur ^ 1], w.hit_prim, w.bin_idx, w.shadow, w.probe, film->d);
             cudaEventRecord(ev(w, n_ev + 3), st);
             k_connect_shadow<<<g128, 128, 0, st>>>(w.ctrl, s->d, w.shadow, film->d);
             k_connect_probe<<<g128, 128, 0, st>>>(w.ctrl, s->d, w.probe, film->d);

@@ -39,6 +39,8 @@ def lib():
         L.orc_camera_look_at.argtypes = [vp, vp, vp, f64, f64, f64, f64, f64, f64, vp]
         L.orc_render.argtypes = [vp, vp, u32, u32, vp, i32, vp, vp]
         L.orc_render.restype = f64
+        L.orc_render_ex.argtypes = [vp, vp, u32, u32, vp, i32, vp, vp, u32, i32]
+        L.orc_render_ex.restype = f64
         L.orc_single_sample.argtypes = [vp, vp, u32, u32, u32, u32, u32, u64, u32, u32, vp]
         L.orc_resolve_rgb8.argtypes = [vp, u64, vp]
         L.orc_philox.argtypes = [vp, u32, u32]
@@ -124,6 +126,14 @@ class OracleScene:
         out = np.zeros(len(q), dtype=np.uint8)
         lib().orc_occluded(self.h, len(q), _p(q), threads, _p(out))
         return out.astype(bool)
+
+    def render_ex(self, camera, width, height, sample_begin, sample_end, seed=0, max_depth=25, threads=8, pixel_stride=1, count_ordered=False):
+        """Bounded-sample render: counts = extend, shadow, probe rays, ordered box tests, ordered prim tests."""
+        fd = N.FilmDesc(width, height, sample_begin, sample_end, 0, 0, width, height, seed)
+        film = np.zeros((height, width, 4), dtype=np.float64)
+        counts = np.zeros(5, dtype=np.uint64)
+        secs = lib().orc_render_ex(self.h, C.byref(camera.c), max_depth, 0, C.byref(fd), threads, _p(film), _p(counts), pixel_stride, 1 if count_ordered else 0)
+        return film, counts, secs
 
     def render(self, camera, width, height, sample_begin, sample_end, seed=0, max_depth=25, invisible_light=False, threads=8, window=None, film=None):
         x0, y0, x1, y1 = window if window is not None else (0, 0, width, height)

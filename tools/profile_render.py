@@ -6,14 +6,14 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from rustraytracer_b200 import Film, IntType, render_samples, scenes  # noqa: E402
 
 name = sys.argv[1] if len(sys.argv) > 1 else "plastic_dragon"
-variant, size, spp, depth = (int(x) for x in (sys.argv[2:6] + ["0", "512", "4", "8"][len(sys.argv) - 2:]))
+variant, size, spp, depth, f32 = (int(x) for x in (sys.argv[2:7] + ["0", "512", "4", "8", "0"][len(sys.argv) - 2:]))
 hs = scenes.HostScene(name, size, size, variant=variant)
 gpu = hs.upload()
 cam = hs.camera()
 film = Film(size, size)
 for rep in range(2):
     film.clear()
-    render_samples(gpu, cam, IntType.Path(depth), film, size, size, 0, spp, seed=rep)
+    render_samples(gpu, cam, IntType.Path(depth, shade_f32=bool(f32)), film, size, size, 0, spp, seed=rep)
     c = gpu.counters()
     rays = c["extend_rays"] + c["shadow_rays"] + c["probe_rays"]
-    print(f"{name} v{variant} {size}^2 x{spp}: {c['render_ms']:.2f} ms {rays / c['render_ms'] / 1e3:.1f} Mrays/s  extend {c['extend_ms']:.2f} shade {c['shade_ms']:.2f} connect {c['connect_ms']:.2f} iters {c['iterations']}", flush=True)
+    print(f"f32={f32} {name} v{variant} {size}^2 x{spp}: {c['render_ms']:.2f} ms {rays / c['render_ms'] / 1e3:.1f} Mrays/s  extend {c['extend_ms']:.2f} shade {c['shade_ms']:.2f} connect {c['connect_ms']:.2f} iters {c['iterations']}", flush=True)
