@@ -116,6 +116,7 @@ def main():
     ap.add_argument("--spp", type=int, default=256)
     ap.add_argument("--size", type=int, default=1024)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--shade", default="f32", choices=["f32", "f64"], help="radiometric precision of the shade kernel (geometry is f64-exact in both)")
     args = ap.parse_args()
     rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     if args.impl == "reference":
@@ -138,7 +139,7 @@ def main():
     objects = hs.upload()                                 # BVH build + flatten + H2D (outside the timed region: scene build is not the hot path)
     build_s = time.time() - t0
     cam = hs.camera()
-    integ = IntType.Path(DEPTH)
+    integ = IntType.Path(DEPTH, shade_f32=(args.shade == "f32"))
     film_t = torch.zeros(H * W * 4, dtype=torch.float64, device=f"cuda:{local}")      # torch owns the film so NCCL can reduce it in place
     film = Film(W, H, device_ptr=film_t.data_ptr())
     host_film = torch.empty(H * W * 4, dtype=torch.float64).pin_memory()
@@ -212,7 +213,7 @@ def main():
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * wall / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f64", "data": "synthetic",
+        "dtype": "f64 geometry (intersection, hit points, rays) + f32 radiometry" if args.shade == "f32" else "f64", "data": "synthetic",
         "config": {"workload": f"{SCENE} rough-plastic (stand-in dragon mesh, 871,414 tris; dragon.obj is a missing blob) {W}x{H}, max_depth {DEPTH}, {spp} spp per GPU per step",
                    "parallelism": f"scene replicated, sample-range partition x{world}, NCCL all-reduce of the film" if world > 1 else "single GPU",
                    "l2": "no explicit flush: every wavefront iteration streams ~1.4 GB of path/queue state (>> 126 MB L2); the BVH (33 MB nodes + 70 MB leaf slots) is meant to stay L2-resident",
@@ -231,6 +232,16 @@ def main():
                      "ms_per_launch": ext_ms_per_launch, "extend_Mrays_per_s": tot["extend_rays"] / max(tot["extend_ms"], 1e-9) / 1e3,
                      "note": "algorithmic bytes are counted on the ORACLE's reference traversal (median-split tree, 1 prim/leaf), so a better tree + L2 residency can exceed the HBM copy peak"},
     }
+    if world == 1 and args.shade == "f32":
+        # for the record: the same step with the shade kernel in the reference's f64 arithmetic (per-pixel parity mode)
+        integ64 = IntType.Path(DEPTH, shade_f32=False)
+        film_t.zero_(); torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        render_samples(objects, cam, integ64, film, W, H, 0, spp, seed=1234)
+        torch.cuda.synchronize()
+        c64 = objects.counters()
+        out["exact_f64_shading"] = {"value": (c64["extend_rays"] + c64["shadow_rays"] + c64["probe_rays"]) / (time.perf_counter() - t1) / 1e6, "unit": UNIT,
+                                    "kernel_ms": {"extend": c64["extend_ms"], "shade+generate": c64["shade_ms"], "connect": c64["connect_ms"]}}
     if world == 1 and not args.no_cpu_baseline:
         sys.path.insert(0, os.path.join(ROOT, "tests"))
         import orc                                         # the checker, used here ONLY as the timed CPU baseline

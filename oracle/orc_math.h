@@ -110,8 +110,8 @@ inline V3 xf_point(const M4& a, const V3& p) {
 
 // ---- counter-based RNG (replaces the reference's OS-seeded thread_rng / StdRng::from_entropy,
 // sampler.rs:318,334-337, util.rs:32-34).  Philox4x32-10 (Salmon et al., SC'11):
-// key = (seed_lo, seed_hi), counter = (pixel, sample, dim, 0x52544358); the uniform is built
-// from the first two output words as a 53-bit fraction.
+// key = (seed_lo, seed_hi), counter = (pixel, sample, dim >> 1, 0x52544358); each block yields two
+// uniforms (words 0,1 for even dim, 2,3 for odd dim), each a 53-bit fraction.
 inline void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1) {
     for (int r = 0; r < 10; r++) {
         uint64_t p0 = (uint64_t)0xD2511F53u * c[0];
@@ -127,10 +127,13 @@ inline void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1) {
 struct Rng {
     uint64_t seed; uint32_t pixel, sample, dim;
     Rng(uint64_t s, uint32_t px, uint32_t smp) : seed(s), pixel(px), sample(smp), dim(0) {}
+    // dimension d: Philox block d >> 1, words (0,1) for even d, (2,3) for odd d
     double next() {
-        uint32_t c[4] = {pixel, sample, dim++, 0x52544358u};
+        uint32_t d = dim++;
+        uint32_t c[4] = {pixel, sample, d >> 1, 0x52544358u};
         philox4x32_10(c, (uint32_t)seed, (uint32_t)(seed >> 32));
-        return ((double)(c[0] >> 5) * 67108864.0 + (double)(c[1] >> 6)) / 9007199254740992.0;
+        uint32_t a = (d & 1u) ? c[2] : c[0], b = (d & 1u) ? c[3] : c[1];
+        return ((double)(a >> 5) * 67108864.0 + (double)(b >> 6)) / 9007199254740992.0;
     }
 };
 

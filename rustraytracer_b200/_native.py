@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librtcore.so")
+LIB_PATH = os.environ.get("RT_LIBRTCORE", os.path.join(_HERE, "librtcore.so"))   # override only for A/B builds of the same library
 
 RT_NONE = 0xFFFFFFFF
 RT_OK, RT_ERR_INVALID, RT_ERR_CUDA, RT_ERR_STATE, RT_ERR_CANCELLED, RT_ERR_IO = range(6)

@@ -173,11 +173,13 @@ __device__ __forceinline__ void rec_from_partials(Rec& r, D3 p, D2 uv, D3 dpdu, 
 // by the rt_intersect epilogue on the closest primitive only.  Bitwise the same accept arithmetic as the
 // traversal, so it cannot disagree with it.  leaf_box = false gives Primitive::intersects_obj semantics
 // (primitive.rs:372-425) plus the FlipFace toggle being skipped by the caller.
-static __device__ __noinline__ bool prim_record(const DScene& sc, uint32_t prim, D3 o, D3 d, double tmin, double tmax, bool leaf_box, Rec& r) {
+// CLS: 1 = the primitive is known to be a triangle, 0 = known parametric shape, 2 = decide at run time
+template <int CLS>
+static __device__ __noinline__ bool prim_record_t(const DScene& sc, uint32_t prim, D3 o, D3 d, double tmin, double tmax, bool leaf_box, Rec& r) {
     DPrim pr = sc.prims[prim];
-    uint32_t type = pr.info & 7u;
+    uint32_t type = CLS == 1 ? (uint32_t)RT_PRIM_TRIANGLE : (pr.info & 7u);
     r.prim = prim; r.mat = pr.mat;
-    if (type == RT_PRIM_TRIANGLE) {
+    if (CLS != 0 && type == RT_PRIM_TRIANGLE) {
         const uint32_t* ti = sc.tri_index + pr.a;
         uint32_t i1 = ti[0], i2 = ti[1], i3 = ti[2];
         const DMesh ms = sc.meshes[pr.info >> 6];
@@ -263,6 +265,39 @@ static __device__ __noinline__ bool prim_record(const DScene& sc, uint32_t prim,
     }
     if (leaf_box && (pr.info & PI_FLIP)) r.front = !r.front;                     // FlipFace (primitive.rs:300-310)
     return true;
+}
+
+// Primitive::pdf's re-intersection of ONE (light) primitive (primitive.rs:462-473 → intersects_obj, no leaf box, no
+// FlipFace toggle): only the hit point and the geometric normal UP TO SIGN are consumed there
+// (`dist.magnitude_squared() / (area * |n · -dir|)`), so the triangle arm skips the shading frame.
+static __device__ __noinline__ bool prim_hit_pn(const DScene& sc, uint32_t prim, D3 o, D3 d, double tmin, double tmax, D3& p, D3& n) {
+    DPrim pr = sc.prims[prim];
+    if ((pr.info & 7u) == RT_PRIM_TRIANGLE) {
+        const uint32_t* ti = sc.tri_index + pr.a;
+        uint32_t i1 = ti[0], i2 = ti[1], i3 = ti[2];
+        const DMesh ms = sc.meshes[pr.info >> 6];
+        D3 p0 = ld3(sc.points + 3 * (ms.p_base + i1)), p1 = ld3(sc.points + 3 * (ms.p_base + i2)), p2 = ld3(sc.points + 3 * (ms.p_base + i3));
+        RayX rx = make_rayx(o, d);
+        double t, b0, b1, b2;
+        if (!tri_test(rx, p0, p1, p2, tmax, t, b0, b1, b2)) return false;
+        if (pr.info & PI_HAS_UV) {                                   // degenerate uv frame ∧ zero normal → None (hittable.rs:366-378)
+            const double* u = sc.uvs;
+            D2 uv0 = mk2(u[2 * (ms.uv_base + i1)], u[2 * (ms.uv_base + i1) + 1]), uv1 = mk2(u[2 * (ms.uv_base + i2)], u[2 * (ms.uv_base + i2) + 1]);
+            D2 uv2 = mk2(u[2 * (ms.uv_base + i3)], u[2 * (ms.uv_base + i3) + 1]);
+            double determinant = (uv0.x - uv2.x) * (uv1.y - uv2.y) - (uv0.y - uv2.y) * (uv1.x - uv2.x);
+            if (fabs(determinant) < SMALL / 10000. && norm2(cross(p2 - p0, p1 - p0)) == 0.) return false;
+        }
+        p = b0 * p0 + b1 * p1 + b2 * p2;
+        n = normalize(cross(p0 - p2, p1 - p2));
+        return true;
+    }
+    Rec r;
+    if (!prim_record_t<0>(sc, prim, o, d, tmin, tmax, false, r)) return false;
+    p = r.p; n = r.n;
+    return true;
+}
+static __device__ __forceinline__ bool prim_record(const DScene& sc, uint32_t prim, D3 o, D3 d, double tmin, double tmax, bool leaf_box, Rec& r) {
+    return prim_record_t<2>(sc, prim, o, d, tmin, tmax, leaf_box, r);
 }
 
 }  // namespace rt

@@ -12,6 +12,7 @@
 // (seed; pixel, sample, dimension) so a path's numbers do not depend on scheduling or on the GPU count.
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include "scene.h"
 #include "shade.cuh"
@@ -27,10 +28,36 @@ namespace rt {
         if (e_ != cudaSuccess) { set_error(std::string(#call) + ": " + cudaGetErrorString(e_)); return RT_ERR_CUDA; } \
     } while (0)
 
-struct PathSet {           // SoA path state, one entry per path in flight
-    double *ox, *oy, *oz, *dx, *dy, *dz, *bx, *by, *bz;
-    uint32_t *pixel, *sample, *dim, *flags;       // flags: bits 0..15 bounces, bit 16 specular_bounce
-};
+// Path state, one entry per path in flight, as two arrays of 48-byte records (three 16-byte words each).
+// extend streams `ray` in order (fully coalesced); shade reaches both through the bin index, so each path costs
+// 3 + 3 fully-used 32-byte sectors instead of the 13 quarter-used sectors of a field-per-array layout.
+struct __align__(16) PRay { double ox, oy, oz, dx, dy, dz; };
+struct __align__(16) PAux { double bx, by, bz; uint32_t pixel, sample, dim, flags; };   // flags: bits 0..15 bounces, bit 16 specular_bounce
+static_assert(sizeof(PRay) == 48 && sizeof(PAux) == 48, "path records must be 48 bytes");
+struct PathSet { PRay* ray; PAux* aux; };
+__device__ __forceinline__ PRay load_ray(const PRay* p) {
+    const double2* q = reinterpret_cast<const double2*>(p);
+    double2 a = q[0], b = q[1], c = q[2];
+    PRay r; r.ox = a.x; r.oy = a.y; r.oz = b.x; r.dx = b.y; r.dy = c.x; r.dz = c.y; return r;
+}
+__device__ __forceinline__ void store_ray(PRay* p, D3 o, D3 d) {
+    double2* q = reinterpret_cast<double2*>(p);
+    q[0] = make_double2(o.x, o.y); q[1] = make_double2(o.z, d.x); q[2] = make_double2(d.y, d.z);
+}
+__device__ __forceinline__ PAux load_aux(const PAux* p) {      // words: (bx,by) (bz,[pixel,sample]) ([dim,flags],pad)
+    const double2* q = reinterpret_cast<const double2*>(p);
+    double2 a = q[0], b = q[1], c = q[2];
+    PAux r; r.bx = a.x; r.by = a.y; r.bz = b.x;
+    r.pixel = (uint32_t)__double2loint(b.y); r.sample = (uint32_t)__double2hiint(b.y);
+    r.dim = (uint32_t)__double2loint(c.x); r.flags = (uint32_t)__double2hiint(c.x);
+    return r;
+}
+__device__ __forceinline__ void store_aux(PAux* p, double bx, double by, double bz, uint32_t pixel, uint32_t sample, uint32_t dim, uint32_t flags) {
+    double2* q = reinterpret_cast<double2*>(p);
+    q[0] = make_double2(bx, by);
+    q[1] = make_double2(bz, __hiloint2double((int)sample, (int)pixel));
+    q[2] = make_double2(__hiloint2double((int)flags, (int)dim), 0.);
+}
 struct ConnQ {             // shadow / probe queue: a ray (a→b or origin+dir), a pre-weighted contribution, a target
     double *ax, *ay, *az, *bx, *by, *bz, *cr, *cg, *cb;
     uint32_t *target, *pixel;                     // shadow: light primitive ; probe: light index
@@ -42,6 +69,9 @@ struct Ctrl {
     uint32_t bin_count[16];      // paths per shading bin after extend (material type x primitive class, 15 = miss)
 };
 constexpr int N_BINS = 16;
+#ifndef SHADE_MIN_BLOCKS
+#define SHADE_MIN_BLOCKS 4      // <= 128 registers: 16 warps/SM; measured against 3 and 5 in profiles/shade_r01_notes.md
+#endif
 struct RenderParams {
     rt_camera cam; uint32_t width, height, x0, y0, ww, wh, sample_begin; uint32_t max_depth, invisible_light; uint32_t k0, k1; uint32_t W;
 };
@@ -49,8 +79,7 @@ struct RenderParams {
 struct Wavefront {
     uint32_t W = 0;
     PathSet set[2]{}; ConnQ shadow{}, probe{};
-    uint32_t* hit_prim = nullptr; double* hit_t = nullptr;
-    uint32_t* bin_idx = nullptr;                  // N_BINS x W path indices, filled by extend
+    uint2* bin_idx = nullptr;                     // N_BINS x W (path index, hit primitive), filled by extend
     Ctrl* ctrl = nullptr; Ctrl* h_ctrl = nullptr;
     cudaStream_t stream = nullptr;
     std::vector<void*> allocs;
@@ -92,7 +121,7 @@ __global__ void __launch_bounds__(256) k_generate(const Ctrl* __restrict__ c, Re
         uint32_t s = (uint32_t)(g / npix), pi = (uint32_t)(g % npix);
         uint32_t px = rp.x0 + pi % rp.ww, py = rp.y0 + pi / rp.ww;
         uint32_t pixel = py * rp.width + px;
-        Rng rng; rng.k0 = rp.k0; rng.k1 = rp.k1; rng.pixel = pixel; rng.sample = rp.sample_begin + s; rng.dim = 0;
+        Rng rng; rng.k0 = rp.k0; rng.k1 = rp.k1; rng.pixel = pixel; rng.sample = rp.sample_begin + s; rng.dim = 0; rng.w2 = 0xffffffffu; rng.w3 = 0;
         double offx = rng_next(rng), offy = rng_next(rng);
         double fx = (double)px + offx, fy = (double)py + offy;
         rng_next(rng);                       // time
@@ -107,9 +136,8 @@ __global__ void __launch_bounds__(256) k_generate(const Ctrl* __restrict__ c, Re
         rng_next(rng);                       // util::rand_range(t0, t1): ray time, unused by geometry
         D3 o = ld3(rp.cam.origin) + offset, d = dir - offset;
         uint32_t k = n_cur + i;
-        ps.ox[k] = o.x; ps.oy[k] = o.y; ps.oz[k] = o.z; ps.dx[k] = d.x; ps.dy[k] = d.y; ps.dz[k] = d.z;
-        ps.bx[k] = 1.; ps.by[k] = 1.; ps.bz[k] = 1.;
-        ps.pixel[k] = pixel; ps.sample[k] = rng.sample; ps.dim[k] = rng.dim; ps.flags[k] = 0;
+        store_ray(ps.ray + k, o, d);
+        store_aux(ps.aux + k, 1., 1., 1., pixel, rng.sample, rng.dim, 0u);
         atomicAdd(film + 4 * (size_t)pixel + 3, 1.0);       // count += 1 (util.rs:231)
     }
 }
@@ -118,12 +146,11 @@ __global__ void __launch_bounds__(256) k_generate(const Ctrl* __restrict__ c, Re
 // shading bin keyed by (material type, triangle / parametric shape) — or "miss" — with one atomic per distinct key
 // per warp (__match_any_sync), so that the shade kernel runs warps of like work instead of diverging on the
 // reference's `match material` / `match primitive` arms.
-__global__ void __launch_bounds__(128) k_extend(Ctrl* c, DScene sc, PathSet ps, uint32_t* __restrict__ hit_prim, double* __restrict__ hit_t,
-                                               uint32_t* __restrict__ bin_idx, uint32_t W) {
+__global__ void __launch_bounds__(128) k_extend(Ctrl* c, DScene sc, PathSet ps, uint2* __restrict__ bin_idx, uint32_t W) {
     uint32_t n = c->n_tot;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        Hit h = trace_closest(sc, mk3(ps.ox[i], ps.oy[i], ps.oz[i]), mk3(ps.dx[i], ps.dy[i], ps.dz[i]), SMALL, INF);
-        hit_prim[i] = h.prim; hit_t[i] = h.t;
+        PRay r = load_ray(ps.ray + i);
+        Hit h = trace_closest(sc, mk3(r.ox, r.oy, r.oz), mk3(r.dx, r.dy, r.dz), SMALL, INF);
         uint32_t key = N_BINS - 1;
         if (h.prim != RT_NONE) { DPrim pr = sc.prims[h.prim]; key = sc.materials[pr.mat].type * 2u + ((pr.info & 7u) == RT_PRIM_TRIANGLE ? 1u : 0u); }
         unsigned active = __activemask();
@@ -132,7 +159,7 @@ __global__ void __launch_bounds__(128) k_extend(Ctrl* c, DScene sc, PathSet ps, 
         uint32_t base = 0;
         if (lane == leader) base = atomicAdd(&c->bin_count[key], (uint32_t)__popc(peers));
         base = __shfl_sync(peers, base, leader);
-        bin_idx[(size_t)key * W + base + __popc(peers & ((1u << lane) - 1u))] = i;
+        bin_idx[(size_t)key * W + base + __popc(peers & ((1u << lane) - 1u))] = make_uint2(i, h.prim);   // path index + hit primitive
     }
 }
 
@@ -144,26 +171,28 @@ template <class R> __device__ __forceinline__ R power_heuristic(R f_pdf, R g_pdf
 
 // The body of PathIntegrator::li's loop (integrator.rs:386-443) for one path vertex.  R = double reproduces the
 // reference's arithmetic; R = float is the production path (geometry stays f64 in both, see shade.cuh).
-template <class R>
-__global__ void __launch_bounds__(128) k_shade(Ctrl* c, DScene sc, RenderParams rp, PathSet in, PathSet out, const uint32_t* __restrict__ hit_prim,
-                                              const uint32_t* __restrict__ bin_idx, ConnQ shq, ConnQ prq, double* film) {
-    uint32_t n = c->n_tot;
-    uint32_t bin_end[N_BINS];
-    { uint32_t acc = 0; for (int b = 0; b < N_BINS; b++) { acc += c->bin_count[b]; bin_end[b] = acc; } }
+// One specialisation per shading bin (material type MAT x primitive class CLS): every warp runs one material's code.
+// Paths in the "miss" bin need no kernel at all: without an infinite light a miss adds nothing (light.rs:499-513).
+template <class R, int MAT, int CLS>
+__global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) k_shade(Ctrl* c, DScene sc, RenderParams rp, PathSet in, PathSet out,
+                                              const uint2* __restrict__ bin_idx, ConnQ shq, ConnQ prq, double* film) {
+    constexpr uint32_t KM = mat_km<MAT>();
+    constexpr int BIN = MAT * 2 + CLS;
+    const uint32_t n = c->bin_count[BIN];
     for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
-        int bin = 0; uint32_t bin_begin = 0;
-#pragma unroll
-        for (int b = 0; b < N_BINS - 1; b++) if (k >= bin_end[b]) { bin = b + 1; bin_begin = bin_end[b]; }
-        const uint32_t i = bin_idx[(size_t)bin * rp.W + (k - bin_begin)];
-        D3 o = mk3(in.ox[i], in.oy[i], in.oz[i]), d = mk3(in.dx[i], in.dy[i], in.dz[i]);
-        V3<R> beta = v3<R>((R)in.bx[i], (R)in.by[i], (R)in.bz[i]);
-        uint32_t pixel = in.pixel[i], flags = in.flags[i];
-        Rng rng; rng.k0 = rp.k0; rng.k1 = rp.k1; rng.pixel = pixel; rng.sample = in.sample[i]; rng.dim = in.dim[i];
+        const uint2 entry = bin_idx[(size_t)BIN * rp.W + k];
+        const uint32_t i = entry.x;
+        const PRay pr = load_ray(in.ray + i);
+        const PAux pa = load_aux(in.aux + i);
+        D3 o = mk3(pr.ox, pr.oy, pr.oz), d = mk3(pr.dx, pr.dy, pr.dz);
+        V3<R> beta = v3<R>((R)pa.bx, (R)pa.by, (R)pa.bz);
+        uint32_t pixel = pa.pixel, flags = pa.flags;
+        Rng rng; rng.k0 = rp.k0; rng.k1 = rp.k1; rng.pixel = pixel; rng.sample = pa.sample; rng.dim = pa.dim; rng.w2 = 0xffffffffu; rng.w3 = 0;
         uint32_t bounces = flags & 0xffffu; bool specular_bounce = (flags >> 16) & 1u;
-        uint32_t prim = hit_prim[i];
+        uint32_t prim = entry.y;
         bool is_some = prim != RT_NONE;
         Rec rec;
-        if (is_some) is_some = prim_record(sc, prim, o, d, SMALL, INF, true, rec);
+        if (is_some) is_some = prim_record_t<CLS>(sc, prim, o, d, SMALL, INF, true, rec);
         bool alive = false;
         do {
             if (bounces == 0 || specular_bounce) {
@@ -177,7 +206,7 @@ __global__ void __launch_bounds__(128) k_shade(Ctrl* c, DScene sc, RenderParams 
             }
             if (!is_some || bounces >= rp.max_depth) break;
             Bsdf<R> bsdf;
-            compute_scattering<R>(sc, rec, bsdf);
+            compute_scattering<R, MAT>(sc, rec, bsdf);
             const V3<R> wo_w = cast3<R>(rec.wo), sn = cast3<R>(rec.sn);
             // uniform_sample_one_light (integrator.rs:530-557)
             uint32_t n_lights = sc.n_lights;
@@ -199,8 +228,8 @@ __global__ void __launch_bounds__(128) k_shade(Ctrl* c, DScene sc, RenderParams 
                     else { wid = normalize(p1 - rec.p); light_pdf = pdf; color = light_l(light, n1, -wid); }
                     if (light_pdf > 0. && !is_black(color)) {
                         V3<R> wi = cast3<R>(wid);
-                        V3<R> f = bsdf_f<R>(bsdf, wo_w, wi, nsf) * fabs(dot(wi, sn));
-                        R scattering_pdf = bsdf_pdf<R>(bsdf, wo_w, wi, nsf);
+                        V3<R> f = bsdf_f<R, KM>(bsdf, wo_w, wi, nsf) * fabs(dot(wi, sn));
+                        R scattering_pdf = bsdf_pdf<R, KM>(bsdf, wo_w, wi, nsf);
                         if (!is_black(f)) {
                             R weight = power_heuristic<R>((R)light_pdf, scattering_pdf);
                             V3<R> ld = cmul(f, cast3<R>(color)) * (weight / (R)light_pdf);
@@ -214,15 +243,15 @@ __global__ void __launch_bounds__(128) k_shade(Ctrl* c, DScene sc, RenderParams 
                 // estimate_direct, BSDF half (integrator.rs:601-632)
                 {
                     V3<R> f, wi; R scattering_pdf; uint32_t st;
-                    bsdf_sample_f<R>(bsdf, wo_w, u_scatter, nsf, rng, f, wi, scattering_pdf, st);
+                    bsdf_sample_f<R, KM>(bsdf, wo_w, u_scatter, nsf, rng, f, wi, scattering_pdf, st);
                     f = f * fabs(dot(wi, sn));
                     if (!is_black(f) && scattering_pdf > R(0)) {
                         R weight = R(1); bool go = true;
                         D3 wid = dbl3(wi);
                         if ((st & BSDF_SPECULAR) == 0) {
                             // Light::pdf_li → Primitive::pdf (primitive.rs:462-473): re-intersect the ONE light primitive, tmin = 0, no leaf box
-                            Rec lr; double light_pdf = 0.;
-                            if (prim_record(sc, light.prim, rec.p, wid, 0., INF, false, lr)) light_pdf = norm2(rec.p - lr.p) / (light.area * fabs(dot(lr.n, -wid)));
+                            D3 lp, ln; double light_pdf = 0.;
+                            if (prim_hit_pn(sc, light.prim, rec.p, wid, 0., INF, lp, ln)) light_pdf = norm2(rec.p - lp) / (light.area * fabs(dot(ln, -wid)));
                             if (light_pdf == 0.) go = false;
                             else weight = power_heuristic<R>(scattering_pdf, (R)light_pdf);
                         }
@@ -239,7 +268,7 @@ __global__ void __launch_bounds__(128) k_shade(Ctrl* c, DScene sc, RenderParams 
             V3<R> wo = cast3<R>(-d);
             V2<R> u; u.x = rng_real<R>(rng); u.y = rng_real<R>(rng);
             V3<R> f, wi; R pdf; uint32_t sflags;
-            bsdf_sample_f<R>(bsdf, wo, u, BSDF_ALL, rng, f, wi, pdf, sflags);
+            bsdf_sample_f<R, KM>(bsdf, wo, u, BSDF_ALL, rng, f, wi, pdf, sflags);
             if (is_black(f) || pdf == R(0)) break;
             beta = cmul(beta, f) * (fabs(dot(wi, sn)) / pdf);
             specular_bounce = (sflags & BSDF_SPECULAR) != 0;
@@ -254,9 +283,8 @@ __global__ void __launch_bounds__(128) k_shade(Ctrl* c, DScene sc, RenderParams 
         } while (false);
         if (alive) {
             uint32_t q = warp_append(&c->n_next);
-            out.ox[q] = o.x; out.oy[q] = o.y; out.oz[q] = o.z; out.dx[q] = d.x; out.dy[q] = d.y; out.dz[q] = d.z;
-            out.bx[q] = beta.x; out.by[q] = beta.y; out.bz[q] = beta.z;
-            out.pixel[q] = pixel; out.sample[q] = rng.sample; out.dim[q] = rng.dim; out.flags[q] = (bounces & 0xffffu) | (specular_bounce ? 0x10000u : 0u);
+            store_ray(out.ray + q, o, d);
+            store_aux(out.aux + q, (double)beta.x, (double)beta.y, (double)beta.z, pixel, rng.sample, rng.dim, (bounces & 0xffffu) | (specular_bounce ? 0x10000u : 0u));
         }
     }
 }
@@ -310,8 +338,7 @@ template <class T> static bool dalloc(Wavefront& w, T*& p, size_t n) {
     w.allocs.push_back(q); p = (T*)q; return true;
 }
 static bool alloc_set(Wavefront& w, PathSet& s, size_t n) {
-    return dalloc(w, s.ox, n) && dalloc(w, s.oy, n) && dalloc(w, s.oz, n) && dalloc(w, s.dx, n) && dalloc(w, s.dy, n) && dalloc(w, s.dz, n) &&
-           dalloc(w, s.bx, n) && dalloc(w, s.by, n) && dalloc(w, s.bz, n) && dalloc(w, s.pixel, n) && dalloc(w, s.sample, n) && dalloc(w, s.dim, n) && dalloc(w, s.flags, n);
+    return dalloc(w, s.ray, n) && dalloc(w, s.aux, n);
 }
 static bool alloc_q(Wavefront& w, ConnQ& q, size_t n) {
     return dalloc(w, q.ax, n) && dalloc(w, q.ay, n) && dalloc(w, q.az, n) && dalloc(w, q.bx, n) && dalloc(w, q.by, n) && dalloc(w, q.bz, n) &&
@@ -333,7 +360,7 @@ static Wavefront* get_wavefront(rt_scene& s) {
     w->W = s.wavefront_size;
     size_t n = w->W;
     bool ok = alloc_set(*w, w->set[0], n) && alloc_set(*w, w->set[1], n) && alloc_q(*w, w->shadow, n) && alloc_q(*w, w->probe, n) &&
-              dalloc(*w, w->hit_prim, n) && dalloc(*w, w->hit_t, n) && dalloc(*w, w->bin_idx, n * N_BINS) && dalloc(*w, w->ctrl, 1) &&
+              dalloc(*w, w->bin_idx, n * N_BINS) && dalloc(*w, w->ctrl, 1) &&
               cudaMallocHost((void**)&w->h_ctrl, sizeof(Ctrl)) == cudaSuccess && cudaStreamCreateWithFlags(&w->stream, cudaStreamNonBlocking) == cudaSuccess;
     if (!ok) { set_error(std::string("wavefront allocation failed: ") + cudaGetErrorString(cudaGetLastError())); destroy_wavefront(w); return nullptr; }
     s.wavefront = w;
@@ -414,17 +441,21 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
     CK(cudaEventRecord(e_begin, st));
     int cur = 0; uint64_t iter = 0; bool done = false; rt_status result = RT_OK;
     const bool f32 = (integ->flags & RT_SHADE_F32) != 0;
+    const bool trace = getenv("RT_TRACE_ITER") != nullptr;     // debugging aid: per-iteration sizes and kernel times on stderr
     while (!done) {
-        for (int k = 0; k < 4; k++, iter++) {
+        for (int k = 0; k < (trace ? 1 : 4); k++, iter++) {
             k_prepare<<<1, 1, 0, st>>>(w.ctrl, w.W);
             if (k == 0) cudaMemcpyAsync(w.h_ctrl, w.ctrl, sizeof(Ctrl), cudaMemcpyDeviceToHost, st);
             cudaEventRecord(ev(w, n_ev + 0), st);
             k_generate<<<g256, 256, 0, st>>>(w.ctrl, rp, w.set[cur], film->d);
             cudaEventRecord(ev(w, n_ev + 1), st);
-            k_extend<<<g128, 128, 0, st>>>(w.ctrl, s->d, w.set[cur], w.hit_prim, w.hit_t, w.bin_idx, w.W);
+            k_extend<<<g128, 128, 0, st>>>(w.ctrl, s->d, w.set[cur], w.bin_idx, w.W);
             cudaEventRecord(ev(w, n_ev + 2), st);
-            if (f32) k_shade<float><<<g128, 128, 0, st>>>(w.ctrl, s->d, rp, w.set[cur], w.set[cur ^ 1], w.hit_prim, w.bin_idx, w.shadow, w.probe, film->d);
-            else k_shade<double><<<g128, 128, 0, st>>>(w.ctrl, s->d, rp, w.set[cur], w.set[cur ^ 1], w.hit_prim, w.bin_idx, w.shadow, w.probe, film->d);
+#define RT_SHADE(R, M) \
+            if (s->bin_mask & (1u << (M * 2))) k_shade<R, M, 0><<<g128, 128, 0, st>>>(w.ctrl, s->d, rp, w.set[cur], w.set[cur ^ 1], w.bin_idx, w.shadow, w.probe, film->d); \
+            if (s->bin_mask & (1u << (M * 2 + 1))) k_shade<R, M, 1><<<g128, 128, 0, st>>>(w.ctrl, s->d, rp, w.set[cur], w.set[cur ^ 1], w.bin_idx, w.shadow, w.probe, film->d);
+#define RT_SHADE_ALL(R) RT_SHADE(R, RT_MAT_MATTE) RT_SHADE(R, RT_MAT_LIGHT) RT_SHADE(R, RT_MAT_PLASTIC) RT_SHADE(R, RT_MAT_GLASS) RT_SHADE(R, RT_MAT_METAL) RT_SHADE(R, RT_MAT_MIRROR)
+            if (f32) { RT_SHADE_ALL(float) } else { RT_SHADE_ALL(double) }
             cudaEventRecord(ev(w, n_ev + 3), st);
             k_connect_shadow<<<g128, 128, 0, st>>>(w.ctrl, s->d, w.shadow, film->d);
             k_connect_probe<<<g128, 128, 0, st>>>(w.ctrl, s->d, w.probe, film->d);
@@ -433,6 +464,16 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
             cur ^= 1;
         }
         CK(cudaStreamSynchronize(st));
+        if (trace) {
+            float a = 0, b = 0, cc = 0, d = 0; size_t i = n_ev - 5;
+            cudaEventElapsedTime(&a, w.events[i], w.events[i + 1]); cudaEventElapsedTime(&b, w.events[i + 1], w.events[i + 2]);
+            cudaEventElapsedTime(&cc, w.events[i + 2], w.events[i + 3]); cudaEventElapsedTime(&d, w.events[i + 3], w.events[i + 4]);
+            Ctrl after; cudaMemcpy(&after, w.ctrl, sizeof(Ctrl), cudaMemcpyDeviceToHost);
+            fprintf(stderr, "iter %3llu n_tot %8u (new %8u) next %8u shadow %8u probe %7u | gen %.3f extend %.3f shade %.3f connect %.3f ms | bins", (unsigned long long)iter - 1,
+                    w.h_ctrl->n_tot, w.h_ctrl->n_new, after.n_next, after.n_shadow, after.n_probe, a, b, cc, d);
+            for (int q = 0; q < N_BINS; q++) if (after.bin_count[q]) fprintf(stderr, " %d:%u", q, after.bin_count[q]);
+            fprintf(stderr, "\n");
+        }
         if (w.h_ctrl->n_tot == 0) done = true;       // snapshot taken right after a prepare: nothing in flight, nothing left to generate
         if (s->cancel.load()) { result = RT_ERR_CANCELLED; set_error("rt_render: cancelled"); done = true; }
         if (n_ev > 200000) n_ev = 2;                  // very long renders: stop growing the event pool (timing breakdown becomes partial)

@@ -18,6 +18,7 @@ struct rt_scene {
     rt::DScene d{};                          // device pointers
     std::vector<void*> allocations;          // every cudaMalloc of this scene
     uint64_t bytes_nodes = 0, bytes_slots = 0, bytes_tables = 0;
+    uint32_t bin_mask = 0;                   // shading bins (material type * 2 + is_triangle) that occur in the scene
     // wavefront state (render.cu)
     void* wavefront = nullptr;
     uint32_t wavefront_size = 1u << 22;

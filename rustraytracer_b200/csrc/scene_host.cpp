@@ -316,6 +316,8 @@ rt_status rt_scene_commit(rt_scene* s) {
     free_wavefront(*s); free_scene_device(*s);
     st = upload_scene(*s, img);
     if (st != RT_OK) return st;
+    s->bin_mask = 0;
+    for (auto& p : s->prims) s->bin_mask |= 1u << (s->materials[p.mat].type * 2 + (p.type == RT_PRIM_TRIANGLE ? 1 : 0));
     s->committed = true;
     return RT_OK;
 }

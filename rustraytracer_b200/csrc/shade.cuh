@@ -17,10 +17,17 @@ namespace rt {
 constexpr uint32_t BSDF_REFLECTION = 1, BSDF_TRANSMISSION = 2, BSDF_DIFFUSE = 4, BSDF_GLOSSY = 8, BSDF_SPECULAR = 16, BSDF_ALL = 31;  // consts.rs:14-20
 
 // ---- counter-based RNG replacing thread_rng()/StdRng::from_entropy() (sampler.rs:318,334-337; util.rs:32-34):
-// Philox4x32-10, key = seed, counter = (pixel, sample, dim, 'RTCX'); one uniform per counter.
-struct Rng { uint32_t k0, k1, pixel, sample, dim; };
+// Philox4x32-10, key = seed, counter = (pixel, sample, dim >> 1, 'RTCX').
+// Each Philox block yields two uniforms: dimension d uses block d >> 1, words (0,1) when d is even, (2,3) when odd.
+// The block computed for an even dimension is kept for the odd one that follows.
+struct Rng { uint32_t k0, k1, pixel, sample, dim; uint32_t w2, w3; };
 static __device__ __noinline__ double rng_next(Rng& g) {
-    uint32_t c0 = g.pixel, c1 = g.sample, c2 = g.dim++, c3 = 0x52544358u, k0 = g.k0, k1 = g.k1;
+    uint32_t d = g.dim++;
+    if ((d & 1u) && g.w2 != 0xffffffffu) {                 // cached second half (0xffffffff marks "none"; a genuine all-ones word just recomputes)
+        uint32_t a = g.w2, b = g.w3; g.w2 = 0xffffffffu;
+        return ((double)(a >> 5) * 67108864.0 + (double)(b >> 6)) / 9007199254740992.0;
+    }
+    uint32_t c0 = g.pixel, c1 = g.sample, c2 = d >> 1, c3 = 0x52544358u, k0 = g.k0, k1 = g.k1;
 #pragma unroll
     for (int r = 0; r < 10; r++) {
         uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
@@ -29,6 +36,8 @@ static __device__ __noinline__ double rng_next(Rng& g) {
         c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
         k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
     }
+    if (d & 1u) return ((double)(c2 >> 5) * 67108864.0 + (double)(c3 >> 6)) / 9007199254740992.0;
+    g.w2 = c2; g.w3 = c3;
     return ((double)(c0 >> 5) * 67108864.0 + (double)(c1 >> 6)) / 9007199254740992.0;
 }
 template <class R> __device__ __forceinline__ R to_unit(double u);
@@ -113,6 +122,15 @@ template <class R> static __device__ __noinline__ V3<R> fr_conductor(R cos_theta
 // ---- lobes (bxdf.rs:213-300, in-scope subset) kept in registers/local memory: no heap, no Vec<Box<..>>
 enum { F_DIELECTRIC = 0, F_CONDUCTOR = 1, F_NOOP = 2 };
 enum { L_LAMBERT = 0, L_OREN_NAYAR = 1, L_SPEC_R = 2, L_SPEC_T = 3, L_FRESNEL_SPEC = 4, L_MICRO_R = 5, L_MICRO_T = 6 };
+// Compile-time lobe/fresnel masks: the shade kernel is specialised per material type (the bins extend fills), and each
+// specialisation only keeps the arms its material can build — small kernels that fit the instruction cache instead of
+// one 200 KB kernel (profiles/shade_r01_notes.md).  KM_ALL keeps every arm.
+constexpr uint32_t KM_F_SHIFT = 8;
+__host__ __device__ constexpr uint32_t km(int k) { return 1u << k; }
+__host__ __device__ constexpr uint32_t kmf(int f) { return 1u << (KM_F_SHIFT + f); }
+constexpr uint32_t KM_ALL = 0xffffffffu;
+#define KM_HAS(k) ((KM & km(k)) != 0u)
+#define KM_HASF(f) ((KM & kmf(f)) != 0u)
 template <class R> struct Lobe {
     int kind; uint32_t type;
     V3<R> color;              // color / r
@@ -126,9 +144,9 @@ template <class R> struct Lobe {
 template <class R> struct Bsdf { V3<R> ns, ng, ss, ts; int n; bool empty; Lobe<R> lobes[2]; };
 
 // Fresnel::evaluate (bxdf.rs:190-211); dielectric arm passes (|cos|, eta_t, eta_i)
-template <class R> __device__ __forceinline__ V3<R> fresnel_eval(const Lobe<R>& l, R cos_theta_i) {
-    if (l.fresnel == F_DIELECTRIC) { R v = fr_dielectric<R>(fabs(cos_theta_i), l.b, l.a); return v3<R>(v, v, v); }
-    if (l.fresnel == F_CONDUCTOR) return fr_conductor<R>(fabs(cos_theta_i), l.eta3, l.aux);
+template <class R, uint32_t KM> __device__ __forceinline__ V3<R> fresnel_eval(const Lobe<R>& l, R cos_theta_i) {
+    if (KM_HASF(F_DIELECTRIC) && l.fresnel == F_DIELECTRIC) { R v = fr_dielectric<R>(fabs(cos_theta_i), l.b, l.a); return v3<R>(v, v, v); }
+    if (KM_HASF(F_CONDUCTOR) && l.fresnel == F_CONDUCTOR) return fr_conductor<R>(fabs(cos_theta_i), l.eta3, l.aux);
     return v3<R>(R(1), R(1), R(1));
 }
 // ---- microfacet.rs, TrowbridgeReitz{sample_visible_area:true} / Empty
@@ -198,11 +216,11 @@ template <class R> static __device__ __noinline__ V3<R> mfd_sample_wh(const Lobe
 }
 
 // Bxdf::f (bxdf.rs:328-527)
-template <class R> static __device__ __noinline__ V3<R> lobe_f(const Lobe<R>& l, V3<R> wo, V3<R> wi) {
+template <class R, uint32_t KM> static __device__ __noinline__ V3<R> lobe_f(const Lobe<R>& l, V3<R> wo, V3<R> wi) {
     const V3<R> zero = v3<R>(R(0), R(0), R(0));
-    switch (l.kind) {
-        case L_LAMBERT: return l.color * inv_pi<R>();
-        case L_OREN_NAYAR: {
+    if (KM_HAS(L_LAMBERT) && l.kind == L_LAMBERT) return l.color * inv_pi<R>();
+    {
+        if (KM_HAS(L_OREN_NAYAR) && l.kind == L_OREN_NAYAR) {
             R sti = sin_theta(wi), sto = sin_theta(wo), max_cos = R(0);
             if (sti > R(SMALL) && sto > R(SMALL)) { R d_cos = cos_phi(wi) * cos_phi(wo) + sin_phi(wi) * sin_phi(wo); max_cos = fmax(R(0), d_cos); }
             R sin_alpha, tan_beta;
@@ -210,17 +228,17 @@ template <class R> static __device__ __noinline__ V3<R> lobe_f(const Lobe<R>& l,
             else { sin_alpha = sti; tan_beta = sto / abs_cos_theta(wi); }                   // |cos θi| in both arms (§8.1 #11)
             return l.color * (inv_pi<R>() * (l.a + l.b * max_cos * sin_alpha * tan_beta));
         }
-        case L_MICRO_R: {
+        if (KM_HAS(L_MICRO_R) && l.kind == L_MICRO_R) {
             R cto = abs_cos_theta(wo), cti = abs_cos_theta(wi);
             V3<R> wh = wi + wo;
             if (cti == R(0) || cto == R(0)) return zero;
             if (is_black(wh)) return zero;
             wh = normalize(wh);
-            V3<R> f = fresnel_eval(l, dot(wi, face_forward(wh, v3<R>(R(0), R(0), R(1)))));
+            V3<R> f = fresnel_eval<R, KM>(l, dot(wi, face_forward(wh, v3<R>(R(0), R(0), R(1)))));
             V3<R> comp1 = l.color * mfd_d(l, wh) * mfd_g(l, wo, wi);
             return cmul(comp1, f * (R(1) / (R(4) * cti * cto)));
         }
-        case L_MICRO_T: {
+        if (KM_HAS(L_MICRO_T) && l.kind == L_MICRO_T) {
             if (same_hemisphere(wo, wi)) return zero;
             R cto = wo.z, cti = wi.z;
             if (cti == R(0) || cto == R(0)) return zero;
@@ -228,27 +246,27 @@ template <class R> static __device__ __noinline__ V3<R> lobe_f(const Lobe<R>& l,
             V3<R> wh = normalize(wo + wi * eta);
             if (wh.z < R(0)) wh = -wh;
             if (dot(wo, wh) * dot(wi, wh) > R(0)) return zero;
-            V3<R> f = fresnel_eval(l, dot(wo, wh));
+            V3<R> f = fresnel_eval<R, KM>(l, dot(wo, wh));
             R sqrt_denom = dot(wo, wh) + eta * dot(wi, wh);
             R factor = R(1) / eta;                                                           // mode == RADIANCE
             V3<R> c = cmul(v3<R>(R(1), R(1), R(1)) - f, l.color);
             return c * fabs(mfd_d(l, wh) * mfd_g(l, wo, wi) * eta * eta * fabs(dot(wi, wh)) * fabs(dot(wo, wh)) * factor * factor /
                             (cti * cto * sqrt_denom * sqrt_denom));
         }
-        default: return zero;
+        return zero;
     }
 }
 template <class R> __device__ __forceinline__ R default_pdf(V3<R> wo, V3<R> wi) { return same_hemisphere(wo, wi) ? abs_cos_theta(wi) * inv_pi<R>() : R(0); }   // bxdf.rs:829-835
 // Bxdf::pdf (bxdf.rs:721-813)
-template <class R> static __device__ __noinline__ R lobe_pdf(const Lobe<R>& l, V3<R> wo, V3<R> wi) {
-    switch (l.kind) {
-        case L_LAMBERT: case L_OREN_NAYAR: case L_SPEC_R: return default_pdf(wo, wi);
-        case L_MICRO_R: {
+template <class R, uint32_t KM> static __device__ __noinline__ R lobe_pdf(const Lobe<R>& l, V3<R> wo, V3<R> wi) {
+    {
+        if ((KM_HAS(L_LAMBERT) && l.kind == L_LAMBERT) || (KM_HAS(L_OREN_NAYAR) && l.kind == L_OREN_NAYAR) || (KM_HAS(L_SPEC_R) && l.kind == L_SPEC_R)) return default_pdf(wo, wi);
+        if (KM_HAS(L_MICRO_R) && l.kind == L_MICRO_R) {
             if (!same_hemisphere(wo, wi)) return R(0);
             V3<R> wh = normalize(wo + wi);
             return mfd_pdf(l, wo, wh) / (R(4) * dot(wo, wh));
         }
-        case L_MICRO_T: {
+        if (KM_HAS(L_MICRO_T) && l.kind == L_MICRO_T) {
             if (same_hemisphere(wo, wi)) return R(0);
             R eta = wo.z > R(0) ? l.eta_b / l.eta_a : l.eta_a / l.eta_b;
             V3<R> wh = normalize(wo + wi * eta);
@@ -257,7 +275,7 @@ template <class R> static __device__ __noinline__ R lobe_pdf(const Lobe<R>& l, V
             R dwh_dwi = fabs(eta * eta * dot(wi, wh)) / (sqrt_denom * sqrt_denom);
             return mfd_pdf(l, wo, wh) * dwh_dwi;
         }
-        default: return R(0);     // SpecularTransmission: 0 ; FresnelSpecular: "unimplemented" → 0 (bxdf.rs:777-791)
+        return R(0);     // SpecularTransmission: 0 ; FresnelSpecular: "unimplemented" → 0 (bxdf.rs:777-791)
     }
 }
 // util::rand_cosine_dir (util.rs:127-148)
@@ -272,46 +290,46 @@ template <class R> static __device__ __noinline__ V3<R> rand_cosine_dir(Rng& g) 
     return v3<R>(x, y, sqrt(fmax(R(0), R(1) - x * x - y * y)));
 }
 // Bxdf::sample_f (bxdf.rs:532-719)
-template <class R> static __device__ __noinline__ void lobe_sample_f(const Lobe<R>& l, V3<R> wo, V2<R> sample, Rng& g, V3<R>& color, V3<R>& wi, R& pdf) {
+template <class R, uint32_t KM> static __device__ __noinline__ void lobe_sample_f(const Lobe<R>& l, V3<R> wo, V2<R> sample, Rng& g, V3<R>& color, V3<R>& wi, R& pdf) {
     const V3<R> zero = v3<R>(R(0), R(0), R(0)), one = v3<R>(R(1), R(1), R(1));
     color = zero; wi = zero; pdf = R(0);
-    switch (l.kind) {
-        case L_LAMBERT: case L_OREN_NAYAR: {             // default_sample_f (bxdf.rs:815-827): ignores `sample`
+    {
+        if ((KM_HAS(L_LAMBERT) && l.kind == L_LAMBERT) || (KM_HAS(L_OREN_NAYAR) && l.kind == L_OREN_NAYAR)) {             // default_sample_f (bxdf.rs:815-827): ignores `sample`
             wi = rand_cosine_dir<R>(g);
             if (wo.z < R(0)) wi.z *= R(-1);
-            pdf = lobe_pdf(l, wo, wi); color = lobe_f(l, wo, wi); return;
+            pdf = lobe_pdf<R, KM>(l, wo, wi); color = lobe_f<R, KM>(l, wo, wi); return;
         }
-        case L_SPEC_R: {
+        if (KM_HAS(L_SPEC_R) && l.kind == L_SPEC_R) {
             wi = v3<R>(-wo.x, -wo.y, wo.z);
-            color = cmul(l.color, fresnel_eval(l, wi.z)); pdf = R(1); return;
+            color = cmul(l.color, fresnel_eval<R, KM>(l, wi.z)); pdf = R(1); return;
         }
-        case L_SPEC_T: {
+        if (KM_HAS(L_SPEC_T) && l.kind == L_SPEC_T) {
             bool entering = wo.z > R(0);
             R eta_i = entering ? l.eta_a : l.eta_b, eta_t = entering ? l.eta_b : l.eta_a;
             V3<R> dir;
             if (!refract<R>(wo, face_forward(v3<R>(R(0), R(0), R(1)), wo), eta_i / eta_t, dir)) return;
-            V3<R> ft = cmul(one - fresnel_eval(l, dir.z), l.color);
+            V3<R> ft = cmul(one - fresnel_eval<R, KM>(l, dir.z), l.color);
             ft = ft * ((eta_i * eta_i) / (eta_t * eta_t));
             color = ft; wi = dir; pdf = R(1); return;
         }
-        case L_MICRO_R: {
+        if (KM_HAS(L_MICRO_R) && l.kind == L_MICRO_R) {
             if (wo.z == R(0)) return;
             V3<R> wh = mfd_sample_wh<R>(l, wo, sample);   // the wo·wh<0 guard has no `return` (bxdf.rs:598-600)
             V3<R> w = reflect(wo, wh);
             if (!same_hemisphere(wo, w)) return;
             pdf = mfd_pdf(l, wo, wh) / (R(4) * dot(wo, wh));
-            wi = w; color = lobe_f(l, wo, wi); return;
+            wi = w; color = lobe_f<R, KM>(l, wo, wi); return;
         }
-        case L_MICRO_T: {
+        if (KM_HAS(L_MICRO_T) && l.kind == L_MICRO_T) {
             if (wo.z == R(0)) return;
             V3<R> wh = mfd_sample_wh<R>(l, wo, sample);
             if (dot(wo, wh) < R(0)) return;
             R eta = wo.z > R(0) ? l.eta_a / l.eta_b : l.eta_b / l.eta_a;
             V3<R> w;
             if (!refract<R>(wo, wh, eta, w)) return;
-            wi = w; pdf = lobe_pdf(l, wo, wi); color = lobe_f(l, wo, wi); return;
+            wi = w; pdf = lobe_pdf<R, KM>(l, wo, wi); color = lobe_f<R, KM>(l, wo, wi); return;
         }
-        case L_FRESNEL_SPEC: {
+        if (KM_HAS(L_FRESNEL_SPEC) && l.kind == L_FRESNEL_SPEC) {
             R f = fr_dielectric<R>(wo.z / norm(wo), l.eta_a, l.eta_b);
             if (sample.x < f) { wi = v3<R>(-wo.x, -wo.y, wo.z); pdf = f; color = l.color * f; return; }
             bool entering = wo.z > R(0);
@@ -332,27 +350,27 @@ template <class R> __device__ __forceinline__ V3<R> local_to_world(const Bsdf<R>
 }
 template <class R> __device__ __forceinline__ uint32_t num_components(const Bsdf<R>& b, uint32_t t) { uint32_t c = 0; for (int i = 0; i < b.n; i++) if (matches_flags(b.lobes[i].type, t)) c++; return c; }
 // Bsdf::f (bsdf.rs:83-98), `a && b || c` precedence kept (§8.1 #6)
-template <class R> static __device__ __noinline__ V3<R> bsdf_f(const Bsdf<R>& b, V3<R> wow, V3<R> wiw, uint32_t flags) {
+template <class R, uint32_t KM> static __device__ __noinline__ V3<R> bsdf_f(const Bsdf<R>& b, V3<R> wow, V3<R> wiw, uint32_t flags) {
     V3<R> wi = world_to_local(b, wiw), wo = world_to_local(b, wow);
     bool refl = dot(wiw, b.ng) * dot(wow, b.ng) > R(0);
     V3<R> f = v3<R>(R(0), R(0), R(0));
     for (int i = 0; i < b.n; i++) {
         uint32_t ty = b.lobes[i].type;
-        if ((matches_flags(ty, flags) && (refl && (ty & BSDF_REFLECTION) > 0)) || (!refl && (ty & BSDF_TRANSMISSION) > 0)) f = f + lobe_f(b.lobes[i], wo, wi);
+        if ((matches_flags(ty, flags) && (refl && (ty & BSDF_REFLECTION) > 0)) || (!refl && (ty & BSDF_TRANSMISSION) > 0)) f = f + lobe_f<R, KM>(b.lobes[i], wo, wi);
     }
     return f;
 }
 // Bsdf::pdf (bsdf.rs:166-189): sums, does not average (§8.1 #8); wo is NOT normalised here
-template <class R> static __device__ __noinline__ R bsdf_pdf(const Bsdf<R>& b, V3<R> wow, V3<R> wiw, uint32_t flags) {
+template <class R, uint32_t KM> static __device__ __noinline__ R bsdf_pdf(const Bsdf<R>& b, V3<R> wow, V3<R> wiw, uint32_t flags) {
     if (b.n == 0) return R(0);
     V3<R> wo = world_to_local(b, wow), wi = world_to_local(b, wiw);
     if (wo.z == R(0)) return R(0);
     R pdf = R(0); int matching = 0;
-    for (int i = 0; i < b.n; i++) if (matches_flags(b.lobes[i].type, flags)) { matching++; pdf += lobe_pdf(b.lobes[i], wo, wi); }
+    for (int i = 0; i < b.n; i++) if (matches_flags(b.lobes[i].type, flags)) { matching++; pdf += lobe_pdf<R, KM>(b.lobes[i], wo, wi); }
     return matching > 0 ? pdf : R(0);
 }
 // Bsdf::sample_f (bsdf.rs:102-164)
-template <class R> static __device__ __noinline__ void bsdf_sample_f(const Bsdf<R>& b, V3<R> wow, V2<R> sample, uint32_t bxdf_type, Rng& g, V3<R>& color, V3<R>& wiw, R& pdf, uint32_t& sampled) {
+template <class R, uint32_t KM> static __device__ __noinline__ void bsdf_sample_f(const Bsdf<R>& b, V3<R> wow, V2<R> sample, uint32_t bxdf_type, Rng& g, V3<R>& color, V3<R>& wiw, R& pdf, uint32_t& sampled) {
     const V3<R> zero = v3<R>(R(0), R(0), R(0));
     color = zero; wiw = zero; pdf = R(0); sampled = 0;
     uint32_t matching = num_components(b, bxdf_type);
@@ -364,19 +382,19 @@ template <class R> static __device__ __noinline__ void bsdf_sample_f(const Bsdf<
     V3<R> wo = normalize(world_to_local(b, wow));
     if (wo.z == R(0)) return;
     V3<R> c, wi; R p;
-    lobe_sample_f<R>(bx, wo, sample, g, c, wi, p);
+    lobe_sample_f<R, KM>(bx, wo, sample, g, c, wi, p);
     if (p == R(0)) return;
     V3<R> w = local_to_world(b, wi);
     bool spec = (bx.type & BSDF_SPECULAR) != 0;
     if (!spec && matching > 1)
-        for (int i = 0; i < b.n; i++) if (i != used && matches_flags(b.lobes[i].type, bxdf_type)) p += lobe_pdf(b.lobes[i], wo, wi);
+        for (int i = 0; i < b.n; i++) if (i != used && matches_flags(b.lobes[i].type, bxdf_type)) p += lobe_pdf<R, KM>(b.lobes[i], wo, wi);
     if (matching > 1) p = p / (R)matching;
     if (!spec) {
         bool refl = dot(w, b.ng) * dot(wow, b.ng) > R(0);
         c = zero;
         for (int i = 0; i < b.n; i++) {
             uint32_t ty = b.lobes[i].type;
-            if (matches_flags(ty, bxdf_type) && ((refl && (ty & BSDF_REFLECTION) > 0) || (!refl && (ty & BSDF_TRANSMISSION) > 0))) c = c + lobe_f(b.lobes[i], wo, wi);
+            if (matches_flags(ty, bxdf_type) && ((refl && (ty & BSDF_REFLECTION) > 0) || (!refl && (ty & BSDF_TRANSMISSION) > 0))) c = c + lobe_f<R, KM>(b.lobes[i], wo, wi);
         }
     }
     color = c; wiw = w; pdf = p; sampled = bx.type;
@@ -403,13 +421,24 @@ template <class R> __device__ __forceinline__ void bsdf_new(Bsdf<R>& b, const Re
     b.ns = cast3<R>(r.sn); b.ng = cast3<R>(r.n); b.ss = cast3<R>(r.sdpdu); b.ts = cast3<R>(normalize(cross(r.sn, r.sdpdu))); b.empty = false;
 }
 // Material::compute_scattering (material.rs:80-244), mode = RADIANCE, allow_lobes = true
-template <class R> static __device__ __noinline__ void compute_scattering(const DScene& sc, const Rec& r, Bsdf<R>& b) {
+// lobe / fresnel arms a material type can build (material.rs:80-244); MAT < 0 = any
+template <int MAT> __host__ __device__ constexpr uint32_t mat_km() {
+    return MAT == RT_MAT_MATTE ? (km(L_LAMBERT) | km(L_OREN_NAYAR))
+         : MAT == RT_MAT_LIGHT ? 0u
+         : MAT == RT_MAT_PLASTIC ? (km(L_LAMBERT) | km(L_MICRO_R) | kmf(F_DIELECTRIC))
+         : MAT == RT_MAT_GLASS ? (km(L_FRESNEL_SPEC) | km(L_MICRO_R) | km(L_MICRO_T) | kmf(F_DIELECTRIC))
+         : MAT == RT_MAT_METAL ? (km(L_MICRO_R) | kmf(F_CONDUCTOR))
+         : MAT == RT_MAT_MIRROR ? (km(L_SPEC_R) | kmf(F_NOOP))
+         : KM_ALL;
+}
+template <class R, int MAT> static __device__ __noinline__ void compute_scattering(const DScene& sc, const Rec& r, Bsdf<R>& b) {
     V3<R> e = cast3<R>(normalize(mk3(1., 1., 1.)));    // Bsdf::empty frame (bsdf.rs:37-47)
     b.ns = e; b.ng = e; b.ss = e; b.ts = e; b.n = 0; b.empty = true;
     const rt_material& m = sc.materials[r.mat];
     double u = r.uv.x, v = r.uv.y;
-    switch (m.type) {
-        case RT_MAT_MATTE: {
+    const uint32_t mt = MAT >= 0 ? (uint32_t)MAT : m.type;
+    {
+        if (mt == RT_MAT_MATTE) {
             double sig = clampd(m.f[0], 0., 90.);
             D3 color = tex_value(sc, m.tex[0], u, v);
             if (!is_black(color)) {
@@ -424,8 +453,8 @@ template <class R> static __device__ __noinline__ void compute_scattering(const 
             }
             return;
         }
-        case RT_MAT_LIGHT: return;
-        case RT_MAT_PLASTIC: {
+        if (mt == RT_MAT_LIGHT) return;
+        if (mt == RT_MAT_PLASTIC) {
             D3 color = tex_value(sc, m.tex[0], u, v);
             if (!is_black(color)) { bsdf_new(b, r); lobe_init(b.lobes[b.n++], L_LAMBERT, BSDF_REFLECTION | BSDF_DIFFUSE, color); }
             D3 spec = tex_value(sc, m.tex[1], u, v);
@@ -440,7 +469,7 @@ template <class R> static __device__ __noinline__ void compute_scattering(const 
             }
             return;
         }
-        case RT_MAT_GLASS: {
+        if (mt == RT_MAT_GLASS) {
             double eta = m.f[2], urough = m.f[0], vrough = m.f[1];
             D3 rr = tex_value(sc, m.tex[0], u, v), t = tex_value(sc, m.tex[1], u, v);
             bsdf_new(b, r);
@@ -467,7 +496,7 @@ template <class R> static __device__ __noinline__ void compute_scattering(const 
             }
             return;
         }
-        case RT_MAT_METAL: {
+        if (mt == RT_MAT_METAL) {
             bsdf_new(b, r);
             D3 u_rough = tex_value(sc, m.tex[3] == RT_NONE ? m.tex[2] : m.tex[3], u, v);
             D3 v_rough = tex_value(sc, m.tex[4] == RT_NONE ? m.tex[2] : m.tex[4], u, v);
@@ -479,7 +508,7 @@ template <class R> static __device__ __noinline__ void compute_scattering(const 
             l.mfd_empty = false; l.alpha_x = (R)fmax(ur, 1e-3); l.alpha_y = (R)fmax(vr, 1e-3);
             return;
         }
-        case RT_MAT_MIRROR: {
+        if (mt == RT_MAT_MIRROR) {
             bsdf_new(b, r);
             D3 color = tex_value(sc, m.tex[0], u, v);
             if (!is_black(color)) lobe_init(b.lobes[b.n++], L_SPEC_R, BSDF_REFLECTION | BSDF_SPECULAR, color);
