@@ -87,13 +87,19 @@ def run_reference(args, rank, world):
     hs = scenes.HostScene(SCENE, args.size, args.size, variant=VARIANT)
     oracle = orc.OracleScene(hs.tables())
     cam = hs.camera()
-    # bounded sample: every `stride`-th pixel of the full image, 1 sample each (same scene, camera, depth, ray mix)
-    stride = 3 if cores <= 16 else 1
+    # bounded sample: every 3rd pixel of the full image x 1 spp per pass (same scene, camera, depth, ray mix); a step is
+    # as many passes (fresh sample index each) as fit ~TARGET_S seconds of all-core CPU work
+    stride, TARGET_S = 3, 6.0
     rays = secs = paths = 0
+    smp = 0
     for step in range(args.warmup + args.steps):
-        film, counts, s = oracle.render_ex(cam, args.size, args.size, step, step + 1, seed=step, max_depth=DEPTH, threads=cores, pixel_stride=stride)
+        s_rays = s_secs = s_paths = 0
+        while s_secs < (TARGET_S if step >= args.warmup else 1.0):
+            film, counts, s = oracle.render_ex(cam, args.size, args.size, smp, smp + 1, seed=1234, max_depth=DEPTH, threads=cores, pixel_stride=stride)
+            smp += 1
+            s_rays += int(counts[:3].sum()); s_secs += s; s_paths += int(film[..., 3].sum())
         if step >= args.warmup:
-            rays += int(counts[:3].sum()); secs += s; paths += int(film[..., 3].sum())
+            rays += s_rays; secs += s_secs; paths += s_paths
     v = rays / secs / 1e6
     sample = f"every {stride}th pixel of the {args.size}^2 image x 1 spp per step ({paths // args.steps} paths/step), max_depth {DEPTH}"
     print(json.dumps({
@@ -247,10 +253,12 @@ def main():
         import orc                                         # the checker, used here ONLY as the timed CPU baseline
         cores = os.cpu_count() or 1
         oracle = orc.OracleScene(hs.tables())
-        stride = 3 if cores <= 16 else 1
-        _, counts, secs = oracle.render_ex(cam, W, H, 0, 1, seed=0, max_depth=DEPTH, threads=cores, pixel_stride=stride)
-        out["cpu_baseline"] = {"value": float(counts[:3].sum()) / secs / 1e6, "unit": UNIT, "cores": cores, "kind": "port",
-                               "sample": f"every {stride}th pixel of the {W}x{H} image x 1 spp ({secs:.1f} s of {cores}-thread CPU work)"}
+        stride, c_rays, c_secs, smp = 3, 0, 0.0, 0
+        while c_secs < 12.0:                              # ~12 s of all-core CPU work on the same image
+            _, counts, secs = oracle.render_ex(cam, W, H, smp, smp + 1, seed=1234, max_depth=DEPTH, threads=cores, pixel_stride=stride)
+            c_rays += int(counts[:3].sum()); c_secs += secs; smp += 1
+        out["cpu_baseline"] = {"value": c_rays / c_secs / 1e6, "unit": UNIT, "cores": cores, "kind": "port",
+                               "sample": f"every {stride}rd pixel of the {W}x{H} image x {smp} spp ({c_secs:.1f} s of {cores}-thread CPU work)"}
     print(json.dumps(out))
     if dist:
         dist.destroy_process_group()
