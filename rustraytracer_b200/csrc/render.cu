@@ -66,6 +66,7 @@ struct Ctrl {
     uint32_t n_cur, n_new, n_tot, n_next, n_shadow, n_probe, pad0, pad1;
     unsigned long long next_sample, sample_base, total_samples;
     unsigned long long c_paths, c_extend, c_shadow, c_probe, c_iter;
+    uint32_t fetch[4];           // work counters of the persistent traversal kernels (extend, shadow, probe)
     uint32_t bin_count[16];      // paths per shading bin after extend (material type x primitive class, 15 = miss)
 };
 constexpr int N_BINS = 16;
@@ -109,6 +110,7 @@ __global__ void k_prepare(Ctrl* c, uint32_t W) {
     c->n_cur = n_cur; c->n_new = n_new; c->n_tot = n_cur + n_new; c->n_next = 0; c->n_shadow = 0; c->n_probe = 0;
     c->sample_base = c->next_sample; c->next_sample += n_new; c->c_paths += n_new;
     for (int b = 0; b < N_BINS; b++) c->bin_count[b] = 0;
+    for (int b = 0; b < 4; b++) c->fetch[b] = 0;
 }
 
 // PathIntegrator::single_sample up to the camera ray (integrator.rs:357-365), Samplers::get_camera_sample
@@ -146,21 +148,28 @@ __global__ void __launch_bounds__(256) k_generate(const Ctrl* __restrict__ c, Re
 // shading bin keyed by (material type, triangle / parametric shape) — or "miss" — with one atomic per distinct key
 // per warp (__match_any_sync), so that the shade kernel runs warps of like work instead of diverging on the
 // reference's `match material` / `match primitive` arms.
-__global__ void __launch_bounds__(128) k_extend(Ctrl* c, DScene sc, PathSet ps, uint2* __restrict__ bin_idx, uint32_t W) {
-    uint32_t n = c->n_tot;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+struct ExtendJob {
+    Ctrl* c; const DScene* sc; PathSet ps; uint2* bin_idx; uint32_t W;
+    __device__ __forceinline__ bool load(uint32_t i, TState& st, int32_t* stack) {
         PRay r = load_ray(ps.ray + i);
-        Hit h = trace_closest(sc, mk3(r.ox, r.oy, r.oz), mk3(r.dx, r.dy, r.dz), SMALL, INF);
-        uint32_t key = N_BINS - 1;
-        if (h.prim != RT_NONE) { DPrim pr = sc.prims[h.prim]; key = sc.materials[pr.mat].type * 2u + ((pr.info & 7u) == RT_PRIM_TRIANGLE ? 1u : 0u); }
+        tstate_init(st, stack, mk3(r.ox, r.oy, r.oz), mk3(r.dx, r.dy, r.dz), SMALL, INF, false, 0., 0u);
+        return true;
+    }
+    __device__ __forceinline__ void finish(uint32_t i, const TState& st) {
+        uint32_t prim = st.best.prim, key = N_BINS - 1;
+        if (prim != RT_NONE) { DPrim pr = sc->prims[prim]; key = sc->materials[pr.mat].type * 2u + ((pr.info & 7u) == RT_PRIM_TRIANGLE ? 1u : 0u); }
         unsigned active = __activemask();
         unsigned peers = __match_any_sync(active, key);
         int leader = __ffs(peers) - 1, lane = threadIdx.x & 31;
         uint32_t base = 0;
         if (lane == leader) base = atomicAdd(&c->bin_count[key], (uint32_t)__popc(peers));
         base = __shfl_sync(peers, base, leader);
-        bin_idx[(size_t)key * W + base + __popc(peers & ((1u << lane) - 1u))] = make_uint2(i, h.prim);   // path index + hit primitive
+        bin_idx[(size_t)key * W + base + __popc(peers & ((1u << lane) - 1u))] = make_uint2(i, prim);   // path index + hit primitive
     }
+};
+__global__ void __launch_bounds__(128) k_extend(Ctrl* c, DScene sc, PathSet ps, uint2* __restrict__ bin_idx, uint32_t W) {
+    ExtendJob job{c, &sc, ps, bin_idx, W};
+    trace_jobs(sc, job, c->n_tot, &c->fetch[0]);
 }
 
 __device__ __forceinline__ D3 light_l(const DLight& l, D3 n, D3 w) {      // Light::l (light.rs:475-496)
@@ -289,29 +298,56 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
     }
 }
 
-// ray type B: Visibility::unoccluded (hittable.rs:25-39) as an any-hit query
-__global__ void __launch_bounds__(128) k_connect_shadow(const Ctrl* __restrict__ c, DScene sc, ConnQ q, double* film) {
-    uint32_t n = c->n_shadow;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        if (unoccluded(sc, mk3(q.ax[i], q.ay[i], q.az[i]), mk3(q.bx[i], q.by[i], q.bz[i]), q.target[i], false))
-            film_add(film, q.pixel[i], mk3(q.cr[i], q.cg[i], q.cb[i]));
+// ray type B: Visibility::unoccluded (hittable.rs:25-39) as an any-hit query: exact hit of the light primitive first
+// (a miss means "occluded"), then search for anything closer, stopping at the first one.
+struct ShadowJob {
+    const DScene* sc; ConnQ q; double* film;
+    __device__ __forceinline__ bool load(uint32_t i, TState& st, int32_t* stack) {
+        D3 p0 = mk3(q.ax[i], q.ay[i], q.az[i]), p1 = mk3(q.bx[i], q.by[i], q.bz[i]);
+        uint32_t target = q.target[i];
+        D3 dir = p1 - p0;
+        D3 org = p0 + dir * SMALL;
+        DPrim pr = sc->prims[target];
+        double t_l;
+        if ((pr.info & 7u) == RT_PRIM_TRIANGLE) {
+            Rec r;
+            if (!prim_record_t<1>(*sc, target, org, dir, 0., INF, true, r)) return false;
+            t_l = r.t;
+        } else if (!shape_test(*sc, pr, org, dir, 0., INF, true, t_l)) return false;
+        tstate_init(st, stack, org, dir, 0., INF, true, t_l, target);
+        return true;
     }
+    __device__ __forceinline__ void finish(uint32_t i, const TState& st) {
+        if (!st.occluded) film_add(film, q.pixel[i], mk3(q.cr[i], q.cg[i], q.cb[i]));
+    }
+};
+__global__ void __launch_bounds__(128) k_connect_shadow(Ctrl* c, DScene sc, ConnQ q, double* film) {
+    ShadowJob job{&sc, q, film};
+    trace_jobs(sc, job, c->n_shadow, &c->fetch[1]);
 }
 // ray type C: the MIS BSDF probe (integrator.rs:614-630): closest hit; counts only if it is the sampled light
-__global__ void __launch_bounds__(128) k_connect_probe(const Ctrl* __restrict__ c, DScene sc, ConnQ q, double* film) {
-    uint32_t n = c->n_probe;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+struct ProbeJob {
+    const DScene* sc; ConnQ q; double* film;
+    __device__ __forceinline__ bool load(uint32_t i, TState& st, int32_t* stack) {
+        tstate_init(st, stack, mk3(q.ax[i], q.ay[i], q.az[i]), mk3(q.bx[i], q.by[i], q.bz[i]), SMALL, INF, false, 0., 0u);
+        return true;
+    }
+    __device__ __forceinline__ void finish(uint32_t i, const TState& st) {
+        uint32_t prim = st.best.prim;
+        if (prim == RT_NONE) return;
+        uint32_t li = sc->prims[prim].light;
+        if (li == RT_NONE || li != q.target[i]) return;           // `lights[index].eq(light)` (integrator.rs:621)
         D3 o = mk3(q.ax[i], q.ay[i], q.az[i]), d = mk3(q.bx[i], q.by[i], q.bz[i]);
-        Hit h = trace_closest(sc, o, d, SMALL, INF);
-        if (h.prim == RT_NONE) continue;
-        uint32_t li = sc.prims[h.prim].light;
-        if (li == RT_NONE || li != q.target[i]) continue;       // `lights[index].eq(light)` (integrator.rs:621)
         Rec r;
-        if (!prim_record(sc, h.prim, o, d, SMALL, INF, true, r)) continue;
-        D3 le = light_l(sc.lights[li], r.n, -d);                 // new_record.le(&-wi)
-        if (is_black(le)) continue;
+        if (!prim_record(*sc, prim, o, d, SMALL, INF, true, r)) return;
+        D3 le = light_l(sc->lights[li], r.n, -d);                  // new_record.le(&-wi)
+        if (is_black(le)) return;
         film_add(film, q.pixel[i], cmul(mk3(q.cr[i], q.cg[i], q.cb[i]), le));
     }
+};
+__global__ void __launch_bounds__(128) k_connect_probe(Ctrl* c, DScene sc, ConnQ q, double* film) {
+    ProbeJob job{&sc, q, film};
+    trace_jobs(sc, job, c->n_probe, &c->fetch[2]);
 }
 
 // util::point_to_color (util.rs:441-471) with aces_comp (util.rs:400-408)
@@ -435,7 +471,7 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
     cudaStream_t st = w.stream;
     CK(cudaMemcpyAsync(w.ctrl, &init, sizeof(Ctrl), cudaMemcpyHostToDevice, st));
     int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device);
-    int g128 = (int)std::min<uint64_t>((w.W + 127) / 128, (uint64_t)sms * 32), g256 = (int)std::min<uint64_t>((w.W + 255) / 256, (uint64_t)sms * 8);
+    int g128 = (int)std::min<uint64_t>((w.W + 127) / 128, (uint64_t)sms * 32), gtrace = sms * 8, g256 = (int)std::min<uint64_t>((w.W + 255) / 256, (uint64_t)sms * 8);
     cudaEvent_t e_begin = ev(w, 0), e_end = ev(w, 1);
     size_t n_ev = 2;
     CK(cudaEventRecord(e_begin, st));
@@ -449,7 +485,7 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
             cudaEventRecord(ev(w, n_ev + 0), st);
             k_generate<<<g256, 256, 0, st>>>(w.ctrl, rp, w.set[cur], film->d);
             cudaEventRecord(ev(w, n_ev + 1), st);
-            k_extend<<<g128, 128, 0, st>>>(w.ctrl, s->d, w.set[cur], w.bin_idx, w.W);
+            k_extend<<<gtrace, 128, 0, st>>>(w.ctrl, s->d, w.set[cur], w.bin_idx, w.W);
             cudaEventRecord(ev(w, n_ev + 2), st);
 #define RT_SHADE(R, M) \
             if (s->bin_mask & (1u << (M * 2))) k_shade<R, M, 0><<<g128, 128, 0, st>>>(w.ctrl, s->d, rp, w.set[cur], w.set[cur ^ 1], w.bin_idx, w.shadow, w.probe, film->d); \
@@ -457,8 +493,8 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
 #define RT_SHADE_ALL(R) RT_SHADE(R, RT_MAT_MATTE) RT_SHADE(R, RT_MAT_LIGHT) RT_SHADE(R, RT_MAT_PLASTIC) RT_SHADE(R, RT_MAT_GLASS) RT_SHADE(R, RT_MAT_METAL) RT_SHADE(R, RT_MAT_MIRROR)
             if (f32) { RT_SHADE_ALL(float) } else { RT_SHADE_ALL(double) }
             cudaEventRecord(ev(w, n_ev + 3), st);
-            k_connect_shadow<<<g128, 128, 0, st>>>(w.ctrl, s->d, w.shadow, film->d);
-            k_connect_probe<<<g128, 128, 0, st>>>(w.ctrl, s->d, w.probe, film->d);
+            k_connect_shadow<<<gtrace, 128, 0, st>>>(w.ctrl, s->d, w.shadow, film->d);
+            k_connect_probe<<<gtrace, 128, 0, st>>>(w.ctrl, s->d, w.probe, film->d);
             cudaEventRecord(ev(w, n_ev + 4), st);
             n_ev += 5;
             cur ^= 1;

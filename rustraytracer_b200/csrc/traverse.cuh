@@ -196,4 +196,107 @@ __device__ __forceinline__ bool unoccluded(const DScene& sc, D3 p0, D3 p1, uint3
     return !trace_any(sc, org, dir, 0., INF, t_l, p1_prim);
 }
 
+// ------------------------------------------------------------------------------------------------------------
+// Persistent traversal with dynamic ray fetch.
+//
+// A warp that walks 32 incoherent rays in lock-step idles most of its lanes: rays finish after very different
+// numbers of steps (ncu on the first version of k_extend: 7.9 of 32 lanes active on average).  Here every lane owns a
+// resumable traversal state; a warp keeps stepping its live rays and, as soon as fewer than REFILL lanes are live,
+// the idle lanes fetch fresh rays from a global work counter (one atomic per warp per refill) — the scheme of
+// Aila & Laine, "Understanding the efficiency of ray traversal on GPUs", restated for this BVH and the f64 leaf tests.
+// A Job supplies: load(i, TState&) -> bool (false = nothing to trace, the job already finished ray i) and
+// finish(i, const TState&).
+struct TState {
+    RayX rx; RayF rf;
+    float ftmin, ftmax;
+    double tmin, tmax, t_limit;
+    uint32_t skip; bool any, occluded;
+    Hit best;
+    int32_t cur; int sp;
+};
+__device__ __forceinline__ void tstate_init(TState& s, int32_t* stack, D3 o, D3 d, double tmin, double tmax, bool any, double t_limit, uint32_t skip) {
+    s.rx = make_rayx(o, d); s.rf = make_rayf(o, d);
+    s.tmin = tmin; s.tmax = tmax; s.any = any; s.t_limit = t_limit; s.skip = skip; s.occluded = false;
+    s.ftmin = f32_down(tmin); s.ftmin = s.ftmin - fabsf(s.ftmin) * 4.8e-7f;
+    s.ftmax = f32_up(fmin(any ? fmin(tmax, t_limit) : tmax, 3.0e38));
+    s.best.t = 0.; s.best.prim = RT_NONE;
+    s.sp = 0; stack[s.sp++] = SENTINEL; s.cur = 0;
+}
+// one macro step: walk inner nodes down to the next leaf, test that leaf, pop.  Returns true when the ray is finished.
+__device__ __forceinline__ bool tstate_step(const DScene& sc, TState& s, int32_t* stack) {
+    const float4* __restrict__ nodes = reinterpret_cast<const float4*>(sc.nodes);
+    int32_t cur = s.cur;
+    while (cur >= 0 && cur != SENTINEL) {
+        const float4* np = nodes + 4 * (size_t)cur;
+        float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2);
+        int4 ch = __ldg(reinterpret_cast<const int4*>(np + 3));
+        float tl, tr;
+        bool hl = box_test(s.rf, n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, s.ftmin, s.ftmax, tl);
+        bool hr = box_test(s.rf, n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, s.ftmin, s.ftmax, tr);
+        if (hl && hr) {
+            int32_t near = ch.x, far = ch.y;
+            if (tr < tl) { near = ch.y; far = ch.x; }
+            if (s.sp < STACK) stack[s.sp++] = far;
+            cur = near;
+        } else if (hl) cur = ch.x;
+        else if (hr) cur = ch.y;
+        else cur = stack[--s.sp];
+    }
+    if (cur == SENTINEL) { s.cur = cur; return true; }
+    uint32_t v = (uint32_t)~cur, first = v >> 2, count = (v & 3u) + 1u;
+    for (uint32_t k = first; k < first + count; k++) {
+        double t; uint32_t prim;
+        if (!slot_test(sc, sc.slots, k, s.rx, s.tmin, s.tmax, t, prim)) continue;
+        if (s.any) {
+            // the closest-hit rule keeps the smaller primitive index on an exact tie
+            if (prim != s.skip && (t < s.t_limit || (t == s.t_limit && prim < s.skip))) { s.occluded = true; s.cur = SENTINEL; return true; }
+        } else if (s.best.prim == RT_NONE || t < s.best.t || (t == s.best.t && prim < s.best.prim)) {
+            s.best.t = t; s.best.prim = prim;
+            s.ftmax = fminf(s.ftmax, f32_up(t));
+        }
+    }
+    cur = stack[--s.sp];
+    s.cur = cur;
+    return cur == SENTINEL;
+}
+
+constexpr int REFILL = 20;      // refetch when fewer than this many lanes of the warp are live (measured: profiles/extend_r01_notes.md)
+
+template <class Job>
+__device__ __forceinline__ void trace_jobs(const DScene& sc, Job& job, uint32_t n, uint32_t* counter) {
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    int32_t stack[STACK];
+    TState st; st.cur = SENTINEL; st.sp = 0;
+    bool active = false, exhausted = false;
+    uint32_t idx = 0;
+    if (sc.n_nodes == 0) {      // empty scene: every ray misses
+        for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+            if (job.load(i, st, stack)) { st.best.prim = RT_NONE; st.occluded = false; job.finish(i, st); }
+        }
+        return;
+    }
+    for (;;) {
+        unsigned idle = __ballot_sync(FULL, !active);
+        if (idle && !exhausted) {
+            int leader = __ffs(idle) - 1;
+            uint32_t base = 0;
+            if (lane == leader) base = atomicAdd(counter, (uint32_t)__popc(idle));
+            base = __shfl_sync(FULL, base, leader);
+            if (!active) {
+                idx = base + __popc(idle & ((1u << lane) - 1u));
+                if (idx < n) active = job.load(idx, st, stack);
+            }
+            if (base + __popc(idle) >= n) exhausted = true;
+        }
+        if (!__any_sync(FULL, active)) { if (exhausted) break; else continue; }
+        for (;;) {
+            if (active && tstate_step(sc, st, stack)) { job.finish(idx, st); active = false; }
+            unsigned act = __ballot_sync(FULL, active);
+            if (act == 0u) break;
+            if (!exhausted && __popc(act) < REFILL) break;
+        }
+    }
+}
+
 }  // namespace rt
