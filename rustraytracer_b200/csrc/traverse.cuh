@@ -222,45 +222,46 @@ __device__ __forceinline__ void tstate_init(TState& s, int32_t* stack, D3 o, D3 
     s.best.t = 0.; s.best.prim = RT_NONE;
     s.sp = 0; stack[s.sp++] = SENTINEL; s.cur = 0;
 }
-// one macro step: walk inner nodes down to the next leaf, test that leaf, pop.  Returns true when the ray is finished.
-__device__ __forceinline__ bool tstate_step(const DScene& sc, TState& s, int32_t* stack) {
-    const float4* __restrict__ nodes = reinterpret_cast<const float4*>(sc.nodes);
-    int32_t cur = s.cur;
-    while (cur >= 0 && cur != SENTINEL) {
-        const float4* np = nodes + 4 * (size_t)cur;
-        float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2);
-        int4 ch = __ldg(reinterpret_cast<const int4*>(np + 3));
-        float tl, tr;
-        bool hl = box_test(s.rf, n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, s.ftmin, s.ftmax, tl);
-        bool hr = box_test(s.rf, n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, s.ftmin, s.ftmax, tr);
-        if (hl && hr) {
-            int32_t near = ch.x, far = ch.y;
-            if (tr < tl) { near = ch.y; far = ch.x; }
-            if (s.sp < STACK) stack[s.sp++] = far;
-            cur = near;
-        } else if (hl) cur = ch.x;
-        else if (hr) cur = ch.y;
-        else cur = stack[--s.sp];
-    }
-    if (cur == SENTINEL) { s.cur = cur; return true; }
-    uint32_t v = (uint32_t)~cur, first = v >> 2, count = (v & 3u) + 1u;
+// one inner-node step: test both children, descend into the nearer hit child, push the other, or pop
+__device__ __forceinline__ void node_step(const DScene& sc, TState& s, int32_t* stack) {
+    const float4* np = reinterpret_cast<const float4*>(sc.nodes) + 4 * (size_t)s.cur;
+    float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2);
+    int4 ch = __ldg(reinterpret_cast<const int4*>(np + 3));
+    float tl, tr;
+    bool hl = box_test(s.rf, n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, s.ftmin, s.ftmax, tl);
+    bool hr = box_test(s.rf, n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, s.ftmin, s.ftmax, tr);
+    if (hl && hr) {
+        int32_t near = ch.x, far = ch.y;
+        if (tr < tl) { near = ch.y; far = ch.x; }
+        if (s.sp < STACK) stack[s.sp++] = far;
+        s.cur = near;
+    } else if (hl) s.cur = ch.x;
+    else if (hr) s.cur = ch.y;
+    else s.cur = stack[--s.sp];
+}
+// one leaf: the reference-exact test of its 1..4 slots, then pop
+__device__ __forceinline__ void leaf_step(const DScene& sc, TState& s, int32_t* stack) {
+    uint32_t v = (uint32_t)~s.cur, first = v >> 2, count = (v & 3u) + 1u;
     for (uint32_t k = first; k < first + count; k++) {
         double t; uint32_t prim;
         if (!slot_test(sc, sc.slots, k, s.rx, s.tmin, s.tmax, t, prim)) continue;
         if (s.any) {
             // the closest-hit rule keeps the smaller primitive index on an exact tie
-            if (prim != s.skip && (t < s.t_limit || (t == s.t_limit && prim < s.skip))) { s.occluded = true; s.cur = SENTINEL; return true; }
+            if (prim != s.skip && (t < s.t_limit || (t == s.t_limit && prim < s.skip))) { s.occluded = true; s.cur = SENTINEL; return; }
         } else if (s.best.prim == RT_NONE || t < s.best.t || (t == s.best.t && prim < s.best.prim)) {
             s.best.t = t; s.best.prim = prim;
             s.ftmax = fminf(s.ftmax, f32_up(t));
         }
     }
-    cur = stack[--s.sp];
-    s.cur = cur;
-    return cur == SENTINEL;
+    s.cur = stack[--s.sp];
 }
 
-constexpr int REFILL = 20;      // refetch when fewer than this many lanes of the warp are live (measured: profiles/extend_r01_notes.md)
+#ifndef RT_REFILL
+#define RT_REFILL 20        // refetch when fewer than this many lanes of the warp hold a live ray
+#endif
+#ifndef RT_NODE_MIN
+#define RT_NODE_MIN 12      // leave the node phase for the leaf phase when fewer lanes than this still walk inner nodes
+#endif
 
 template <class Job>
 __device__ __forceinline__ void trace_jobs(const DScene& sc, Job& job, uint32_t n, uint32_t* counter) {
@@ -291,10 +292,21 @@ __device__ __forceinline__ void trace_jobs(const DScene& sc, Job& job, uint32_t 
         }
         if (!__any_sync(FULL, active)) { if (exhausted) break; else continue; }
         for (;;) {
-            if (active && tstate_step(sc, st, stack)) { job.finish(idx, st); active = false; }
+            // node phase: all lanes that sit on an inner node step together; lanes already at a leaf wait, but only
+            // while at least RT_NODE_MIN lanes are still walking
+            for (;;) {
+                bool at_node = active && st.cur >= 0 && st.cur != SENTINEL;
+                unsigned m = __ballot_sync(FULL, at_node);
+                if (m == 0u) break;
+                if (__popc(m) < RT_NODE_MIN && __any_sync(FULL, active && st.cur < 0)) break;
+                if (at_node) node_step(sc, st, stack);
+            }
+            // leaf phase
+            if (active && st.cur < 0) leaf_step(sc, st, stack);
+            if (active && st.cur == SENTINEL) { job.finish(idx, st); active = false; }
             unsigned act = __ballot_sync(FULL, active);
             if (act == 0u) break;
-            if (!exhausted && __popc(act) < REFILL) break;
+            if (!exhausted && __popc(act) < RT_REFILL) break;
         }
     }
 }
