@@ -60,12 +60,16 @@ typedef struct rt_primitive {
                               xz: x0,z0,x1,z1,k; yz: y0,z0,y1,z1,k)                        */
 } rt_primitive;
 
-/* `enum Texture` (material.rs:520-539) */
-enum { RT_TEX_SOLID = 0, RT_TEX_CHECKERED = 1 };
+/* `enum Texture` (material.rs:520-539); Perlin is out of scope.
+ * Hdr{meta,data} and Image{img} keep their texels in an image added with rt_scene_add_image_*:
+ * Hdr looks up the nearest texel at (round((1-u)*W) % W, round(v*H) % H), re-quantises it to RGBE8
+ * and returns (c+0.5)*2^(e-128)/256 (material.rs:570-587); Image looks up (round(u*W) % W,
+ * round((1-v)*H) % H) and returns c/255 (material.rs:601-611).                          */
+enum { RT_TEX_SOLID = 0, RT_TEX_CHECKERED = 1, RT_TEX_HDR = 2, RT_TEX_IMAGE = 3 };
 typedef struct rt_texture {
     uint32_t type;
     uint32_t odd, even;    /* checkered: texture ids (material.rs:528-532)                  */
-    uint32_t _pad;
+    uint32_t image;        /* hdr / image: index returned by rt_scene_add_image_*           */
     double   color[3];     /* solid colour                                                  */
     double   frequency;    /* checkered                                                     */
 } rt_texture;
@@ -84,15 +88,20 @@ typedef struct rt_material {
     double   f[3];
 } rt_material;
 
-/* `enum Light` (light.rs:30-80); only Diffuse (area) lights are reachable from the five
- * benchmark configurations.                                            */
-enum { RT_LIGHT_DIFFUSE = 0 };
+/* `enum Light` (light.rs:30-80): Diffuse (area) lights and the Infinite (environment map)
+ * light; the delta lights (Point / Spot / Distant) are out of scope.
+ * Infinite: Light::make_infinite_light(to_world, n_samples, text_id) (light.rs:608-638) — the
+ * (2W x 2H) luminance*sin(theta) table and its Distribution2D (distribution.rs:98-148) are built
+ * at commit from the texture; world_radius is the reference's fixed 10000 (light.rs:636).   */
+enum { RT_LIGHT_DIFFUSE = 0, RT_LIGHT_INFINITE = 1 };
 typedef struct rt_light {
     uint32_t type;
-    uint32_t prim_index;   /* the emitting primitive (light.rs:62)                          */
-    uint32_t two_sided;
+    uint32_t prim_index;   /* diffuse: the emitting primitive (light.rs:62)                 */
+    uint32_t two_sided;    /* diffuse                                                       */
+    uint32_t text_id;      /* infinite: environment texture (light.rs:74)                   */
+    double   color[3];     /* diffuse                                                       */
+    uint32_t transform;    /* infinite: to_world as an index into transforms, RT_NONE = identity */
     uint32_t _pad;
-    double   color[3];
     /* `area` (light.rs:63) is derived from the primitive at commit (primitive.rs:339-359)  */
 } rt_light;
 
@@ -203,6 +212,11 @@ rt_status rt_scene_add_primitives(rt_scene* scene, uint64_t n, const rt_primitiv
 rt_status rt_scene_add_mesh_triangles(rt_scene* scene, uint32_t mesh_index, uint32_t mat_index, uint32_t* first_index_out);
 /* Primitive::set_light_index (primitive.rs:318-337) */
 rt_status rt_scene_set_light_index(rt_scene* scene, uint32_t prim_index, uint32_t light_index);
+/* Texture::new_hdr (material.rs:626-642): the decoded `Vec<Rgb<f32>>`, row-major, width*height*3
+ * floats.  The RGBE8 re-quantisation of material.rs:578 (image 0.23 `to_rgbe8`) is applied once here. */
+rt_status rt_scene_add_image_hdr(rt_scene* scene, uint32_t width, uint32_t height, const float* rgb, uint32_t* image_index_out);
+/* Texture::new_texture (material.rs:613-616): an `RgbImage`, row-major, width*height*3 bytes       */
+rt_status rt_scene_add_image_rgb8(rt_scene* scene, uint32_t width, uint32_t height, const uint8_t* rgb, uint32_t* image_index_out);
 rt_status rt_scene_set_textures(rt_scene* scene, uint64_t n, const rt_texture* textures);
 rt_status rt_scene_set_materials(rt_scene* scene, uint64_t n, const rt_material* materials);
 rt_status rt_scene_set_lights(rt_scene* scene, uint64_t n, const rt_light* lights);

@@ -37,16 +37,16 @@ static_assert(sizeof(PRay) == 48 && sizeof(PAux) == 48, "path records must be 48
 struct PathSet { PRay* ray; PAux* aux; };
 __device__ __forceinline__ PRay load_ray(const PRay* p) {
     const double2* q = reinterpret_cast<const double2*>(p);
-    double2 a = q[0], b = q[1], c = q[2];
+    double2 a = __ldcs(q), b = __ldcs(q + 1), c = __ldcs(q + 2);     // streaming: path state must not evict the BVH from L2
     PRay r; r.ox = a.x; r.oy = a.y; r.oz = b.x; r.dx = b.y; r.dy = c.x; r.dz = c.y; return r;
 }
 __device__ __forceinline__ void store_ray(PRay* p, D3 o, D3 d) {
     double2* q = reinterpret_cast<double2*>(p);
-    q[0] = make_double2(o.x, o.y); q[1] = make_double2(o.z, d.x); q[2] = make_double2(d.y, d.z);
+    __stcs(q, make_double2(o.x, o.y)); __stcs(q + 1, make_double2(o.z, d.x)); __stcs(q + 2, make_double2(d.y, d.z));
 }
 __device__ __forceinline__ PAux load_aux(const PAux* p) {      // words: (bx,by) (bz,[pixel,sample]) ([dim,flags],pad)
     const double2* q = reinterpret_cast<const double2*>(p);
-    double2 a = q[0], b = q[1], c = q[2];
+    double2 a = __ldcs(q), b = __ldcs(q + 1), c = __ldcs(q + 2);
     PAux r; r.bx = a.x; r.by = a.y; r.bz = b.x;
     r.pixel = (uint32_t)__double2loint(b.y); r.sample = (uint32_t)__double2hiint(b.y);
     r.dim = (uint32_t)__double2loint(c.x); r.flags = (uint32_t)__double2hiint(c.x);
@@ -54,9 +54,9 @@ __device__ __forceinline__ PAux load_aux(const PAux* p) {      // words: (bx,by)
 }
 __device__ __forceinline__ void store_aux(PAux* p, double bx, double by, double bz, uint32_t pixel, uint32_t sample, uint32_t dim, uint32_t flags) {
     double2* q = reinterpret_cast<double2*>(p);
-    q[0] = make_double2(bx, by);
-    q[1] = make_double2(bz, __hiloint2double((int)sample, (int)pixel));
-    q[2] = make_double2(__hiloint2double((int)flags, (int)dim), 0.);
+    __stcs(q, make_double2(bx, by));
+    __stcs(q + 1, make_double2(bz, __hiloint2double((int)sample, (int)pixel)));
+    __stcs(q + 2, make_double2(__hiloint2double((int)flags, (int)dim), 0.));
 }
 struct ConnQ {             // shadow / probe queue: a ray (a→b or origin+dir), a pre-weighted contribution, a target
     double *ax, *ay, *az, *bx, *by, *bz, *cr, *cg, *cb;
@@ -244,8 +244,8 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
                             V3<R> ld = cmul(f, cast3<R>(color)) * (weight / (R)light_pdf);
                             V3<R> contrib = cmul(ld * (R)n_lights, beta);
                             uint32_t q = warp_append(&c->n_shadow);
-                            shq.ax[q] = rec.p.x; shq.ay[q] = rec.p.y; shq.az[q] = rec.p.z; shq.bx[q] = p1.x; shq.by[q] = p1.y; shq.bz[q] = p1.z;
-                            shq.cr[q] = contrib.x; shq.cg[q] = contrib.y; shq.cb[q] = contrib.z; shq.target[q] = light.prim; shq.pixel[q] = pixel;
+                            __stcs(shq.ax + q, rec.p.x); __stcs(shq.ay + q, rec.p.y); __stcs(shq.az + q, rec.p.z); __stcs(shq.bx + q, p1.x); __stcs(shq.by + q, p1.y); __stcs(shq.bz + q, p1.z);
+                            __stcs(shq.cr + q, (double)contrib.x); __stcs(shq.cg + q, (double)contrib.y); __stcs(shq.cb + q, (double)contrib.z); __stcs(shq.target + q, light.prim); __stcs(shq.pixel + q, pixel);
                         }
                     }
                 }
@@ -298,56 +298,55 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
     }
 }
 
-// ray type B: Visibility::unoccluded (hittable.rs:25-39) as an any-hit query: exact hit of the light primitive first
-// (a miss means "occluded"), then search for anything closer, stopping at the first one.
-struct ShadowJob {
-    const DScene* sc; ConnQ q; double* film;
+// Ray types B and C are traced by ONE persistent launch over the concatenated queue [shadow | probe]: the probe queue is
+// ~5 % of the shadow queue, and as a launch of its own it paid a whole persistent-kernel tail for it (ncu launch list r01:
+// 11 % of the step for 2.4 % of the rays).
+// B: Visibility::unoccluded (hittable.rs:25-39) as an any-hit query: exact hit of the light primitive first (a miss
+//    means "occluded"), then search for anything closer, stopping at the first one.
+// C: the MIS BSDF probe (integrator.rs:614-630): closest hit; counts only if it is the sampled light.
+struct ConnectJob {
+    const DScene* sc; ConnQ sh, pr; double* film; uint32_t n_shadow;
     __device__ __forceinline__ bool load(uint32_t i, TState& st, int32_t* stack) {
-        D3 p0 = mk3(q.ax[i], q.ay[i], q.az[i]), p1 = mk3(q.bx[i], q.by[i], q.bz[i]);
-        uint32_t target = q.target[i];
+        if (i >= n_shadow) {
+            uint32_t k = i - n_shadow;
+            tstate_init(st, stack, mk3(__ldcs(pr.ax + k), __ldcs(pr.ay + k), __ldcs(pr.az + k)), mk3(__ldcs(pr.bx + k), __ldcs(pr.by + k), __ldcs(pr.bz + k)), SMALL, INF, false, 0., 0u);
+            return true;
+        }
+        D3 p0 = mk3(__ldcs(sh.ax + i), __ldcs(sh.ay + i), __ldcs(sh.az + i)), p1 = mk3(__ldcs(sh.bx + i), __ldcs(sh.by + i), __ldcs(sh.bz + i));
+        uint32_t target = __ldcs(sh.target + i);
         D3 dir = p1 - p0;
         D3 org = p0 + dir * SMALL;
-        DPrim pr = sc->prims[target];
+        DPrim prm = sc->prims[target];
         double t_l;
-        if ((pr.info & 7u) == RT_PRIM_TRIANGLE) {
+        if ((prm.info & 7u) == RT_PRIM_TRIANGLE) {
             Rec r;
             if (!prim_record_t<1>(*sc, target, org, dir, 0., INF, true, r)) return false;
             t_l = r.t;
-        } else if (!shape_test(*sc, pr, org, dir, 0., INF, true, t_l)) return false;
+        } else if (!shape_test(*sc, prm, org, dir, 0., INF, true, t_l)) return false;
         tstate_init(st, stack, org, dir, 0., INF, true, t_l, target);
         return true;
     }
     __device__ __forceinline__ void finish(uint32_t i, const TState& st) {
-        if (!st.occluded) film_add(film, q.pixel[i], mk3(q.cr[i], q.cg[i], q.cb[i]));
-    }
-};
-__global__ void __launch_bounds__(128) k_connect_shadow(Ctrl* c, DScene sc, ConnQ q, double* film) {
-    ShadowJob job{&sc, q, film};
-    trace_jobs(sc, job, c->n_shadow, &c->fetch[1]);
-}
-// ray type C: the MIS BSDF probe (integrator.rs:614-630): closest hit; counts only if it is the sampled light
-struct ProbeJob {
-    const DScene* sc; ConnQ q; double* film;
-    __device__ __forceinline__ bool load(uint32_t i, TState& st, int32_t* stack) {
-        tstate_init(st, stack, mk3(q.ax[i], q.ay[i], q.az[i]), mk3(q.bx[i], q.by[i], q.bz[i]), SMALL, INF, false, 0., 0u);
-        return true;
-    }
-    __device__ __forceinline__ void finish(uint32_t i, const TState& st) {
+        if (i < n_shadow) {
+            if (!st.occluded) film_add(film, __ldcs(sh.pixel + i), mk3(__ldcs(sh.cr + i), __ldcs(sh.cg + i), __ldcs(sh.cb + i)));
+            return;
+        }
+        uint32_t k = i - n_shadow;
         uint32_t prim = st.best.prim;
         if (prim == RT_NONE) return;
         uint32_t li = sc->prims[prim].light;
-        if (li == RT_NONE || li != q.target[i]) return;           // `lights[index].eq(light)` (integrator.rs:621)
-        D3 o = mk3(q.ax[i], q.ay[i], q.az[i]), d = mk3(q.bx[i], q.by[i], q.bz[i]);
+        if (li == RT_NONE || li != pr.target[k]) return;           // `lights[index].eq(light)` (integrator.rs:621)
+        D3 o = mk3(pr.ax[k], pr.ay[k], pr.az[k]), d = mk3(pr.bx[k], pr.by[k], pr.bz[k]);
         Rec r;
         if (!prim_record(*sc, prim, o, d, SMALL, INF, true, r)) return;
         D3 le = light_l(sc->lights[li], r.n, -d);                  // new_record.le(&-wi)
         if (is_black(le)) return;
-        film_add(film, q.pixel[i], cmul(mk3(q.cr[i], q.cg[i], q.cb[i]), le));
+        film_add(film, pr.pixel[k], cmul(mk3(pr.cr[k], pr.cg[k], pr.cb[k]), le));
     }
 };
-__global__ void __launch_bounds__(128) k_connect_probe(Ctrl* c, DScene sc, ConnQ q, double* film) {
-    ProbeJob job{&sc, q, film};
-    trace_jobs(sc, job, c->n_probe, &c->fetch[2]);
+__global__ void __launch_bounds__(128, 5) k_connect(Ctrl* c, DScene sc, ConnQ shq, ConnQ prq, double* film) {
+    ConnectJob job{&sc, shq, prq, film, c->n_shadow};
+    trace_jobs(sc, job, c->n_shadow + c->n_probe, &c->fetch[1]);
 }
 
 // util::point_to_color (util.rs:441-471) with aces_comp (util.rs:400-408)
@@ -399,6 +398,28 @@ static Wavefront* get_wavefront(rt_scene& s) {
               dalloc(*w, w->bin_idx, n * N_BINS) && dalloc(*w, w->ctrl, 1) &&
               cudaMallocHost((void**)&w->h_ctrl, sizeof(Ctrl)) == cudaSuccess && cudaStreamCreateWithFlags(&w->stream, cudaStreamNonBlocking) == cudaSuccess;
     if (!ok) { set_error(std::string("wavefront allocation failed: ") + cudaGetErrorString(cudaGetLastError())); destroy_wavefront(w); return nullptr; }
+    // Keep the inner nodes of the BVH resident in L2 while ~1.4 GB of path state streams through every iteration:
+    // a persisting access-policy window over `nodes` on the render stream.  Measured on the dragon (r01, 64 spp): no gain
+    // for extend/connect (37.4 vs 37.8 ms, 26.6 vs 26.7 ms) and a 4 % loss for shade (55.1 vs 52.8 ms: less L2 left for the
+    // path-state gathers), so it is OFF unless RT_L2_PERSIST=1.
+    const char* pe = getenv("RT_L2_PERSIST");
+    if (pe && pe[0] == '1' && s.d.nodes && s.bytes_nodes) {
+        int max_persist = 0, max_window = 0;
+        cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, s.device);
+        cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, s.device);
+        if (max_persist > 0 && max_window > 0) {
+            size_t want = std::min<size_t>(s.bytes_nodes, (size_t)max_persist);
+            cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want);
+            cudaStreamAttrValue av{};
+            av.accessPolicyWindow.base_ptr = const_cast<DNode*>(s.d.nodes);
+            av.accessPolicyWindow.num_bytes = std::min<size_t>(s.bytes_nodes, (size_t)max_window);
+            av.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)want / (double)av.accessPolicyWindow.num_bytes);
+            av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+            av.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
+            cudaStreamSetAttribute(w->stream, cudaStreamAttributeAccessPolicyWindow, &av);
+            cudaGetLastError();
+        }
+    }
     s.wavefront = w;
     return w;
 }
@@ -493,8 +514,7 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
 #define RT_SHADE_ALL(R) RT_SHADE(R, RT_MAT_MATTE) RT_SHADE(R, RT_MAT_LIGHT) RT_SHADE(R, RT_MAT_PLASTIC) RT_SHADE(R, RT_MAT_GLASS) RT_SHADE(R, RT_MAT_METAL) RT_SHADE(R, RT_MAT_MIRROR)
             if (f32) { RT_SHADE_ALL(float) } else { RT_SHADE_ALL(double) }
             cudaEventRecord(ev(w, n_ev + 3), st);
-            k_connect_shadow<<<gtrace, 128, 0, st>>>(w.ctrl, s->d, w.shadow, film->d);
-            k_connect_probe<<<gtrace, 128, 0, st>>>(w.ctrl, s->d, w.probe, film->d);
+            k_connect<<<gtrace, 128, 0, st>>>(w.ctrl, s->d, w.shadow, w.probe, film->d);
             cudaEventRecord(ev(w, n_ev + 4), st);
             n_ev += 5;
             cur ^= 1;
