@@ -23,7 +23,9 @@ typedef struct rth_params {
                                     (commented metal_dragon, scenes.rs:424-471);
                                     cornell_box_statue: 0 = matte statue, 1 = metal (scenes.rs:243-246);
                                     two_dragons: 0 = as committed (metal dragon only), 1 = glass + metal
-                                    (commented block scenes.rs:608-611 enabled)                        */
+                                    (commented block scenes.rs:608-611 enabled);
+                                    material_hdr: mat_num 0 smooth plastic, 1 rose-gold metal, 2 mirror,
+                                    3 glass (scenes.rs:627,712-718)                                     */
     uint32_t    _pad;
     uint64_t    n_tris;          /* soup: triangle count; dragon/statue stand-ins: 0 = default          */
     uint64_t    seed;            /* generators                                                          */
@@ -33,7 +35,8 @@ typedef struct rth_params {
 
 /* name ∈ { "sphere_roughness" (scenes.rs:474), "make_world" (commented, scenes.rs:15-86, seeded),
  *          "cornell_box" (:89), "cornell_box_statue" (:200), "plastic_dragon" (:310),
- *          "two_dragons" (:549), "soup"  }                                    */
+ *          "two_dragons" (:549), "material_hdr" (:627, HDR environment = Light::Infinite),
+ *          "soup"  }                                                          */
 rt_status   rth_scene_build(const char* name, const rth_params* params, rth_scene** out);
 void        rth_scene_destroy(rth_scene* s);
 /* the (String path, Camera, Samplers) a scene function returns */
@@ -51,6 +54,15 @@ rt_status   rth_scene_copy_transforms(const rth_scene* s, double* out16_each);
 rt_status   rth_scene_copy_textures(const rth_scene* s, rt_texture* out);
 rt_status   rth_scene_copy_materials(const rth_scene* s, rt_material* out);
 rt_status   rth_scene_copy_lights(const rth_scene* s, rt_light* out);
+
+/* Hdr / Image texel blocks (Texture::Hdr{data}, Texture::Image{img}); info = width, height, is_hdr;
+ * copy writes width*height*3 floats (hdr) or bytes (rgb8)                                             */
+rt_status   rth_scene_num_images(const rth_scene* s, uint64_t* n);
+rt_status   rth_scene_image_info(const rth_scene* s, uint32_t image, uint32_t info[3]);
+rt_status   rth_scene_image_copy(const rth_scene* s, uint32_t image, void* out);
+/* Texture::new_hdr's decoder (material.rs:626-642): Radiance RGBE file -> Rgb<f32> pixels.  rgb_out may
+ * be NULL to query the size.                                                                          */
+rt_status   rth_load_hdr(const char* path, uint32_t* width, uint32_t* height, float* rgb_out, uint64_t capacity_floats);
 
 /* push every table into `dst` through the public rt_scene_* calls (does not commit) */
 rt_status   rth_scene_upload(const rth_scene* s, rt_scene* dst);

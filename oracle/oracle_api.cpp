@@ -41,6 +41,12 @@ uint32_t orc_scene_add_transform(void* sp, const double m[16]) {
 }
 void orc_scene_add_primitives(void* sp, uint64_t n, const rt_primitive* prims) { Scene& s = *(Scene*)sp; s.prims.insert(s.prims.end(), prims, prims + n); }
 void orc_scene_set_textures(void* sp, uint64_t n, const rt_texture* t) { ((Scene*)sp)->textures.assign(t, t + n); }
+uint32_t orc_scene_add_image_hdr(void* sp, uint32_t w, uint32_t h, const float* rgb) {
+    Scene& s = *(Scene*)sp; Image im; im.w = w; im.h = h; im.hdr = true; im.f.assign(rgb, rgb + (size_t)w * h * 3); s.images.push_back(std::move(im)); return (uint32_t)s.images.size() - 1;
+}
+uint32_t orc_scene_add_image_rgb8(void* sp, uint32_t w, uint32_t h, const uint8_t* rgb) {
+    Scene& s = *(Scene*)sp; Image im; im.w = w; im.h = h; im.hdr = false; im.b.assign(rgb, rgb + (size_t)w * h * 3); s.images.push_back(std::move(im)); return (uint32_t)s.images.size() - 1;
+}
 void orc_scene_set_materials(void* sp, uint64_t n, const rt_material* m) { ((Scene*)sp)->materials.assign(m, m + n); }
 void orc_scene_set_lights(void* sp, uint64_t n, const rt_light* l) {
     Scene& s = *(Scene*)sp; s.lights.clear();
@@ -51,7 +57,10 @@ void orc_scene_commit(void* sp, uint64_t bvh_seed) {
     Scene& s = *(Scene*)sp;
     s.boxes.resize(s.prims.size());
     for (size_t i = 0; i < s.prims.size(); i++) s.boxes[i] = prim_box(s, s.prims[i]);
-    for (auto& L : s.lights) L.area = prim_area(s, s.prims[L.d.prim_index]);   // light.rs:603
+    for (auto& L : s.lights) {
+        if (L.d.type == RT_LIGHT_INFINITE) make_infinite_light(s, L);           // light.rs:608-638
+        else L.area = prim_area(s, s.prims[L.d.prim_index]);                    // light.rs:603
+    }
     s.nodes.clear(); s.root = -1;
     if (!s.prims.empty()) {
         s.nodes.reserve(2 * s.prims.size());
@@ -192,6 +201,33 @@ void orc_bsdf_sample_f(void* sp, uint32_t mat, double u, double v, const double 
     V3 f, wi; double pdf; uint8_t st;
     bsdf_sample_f(r.bsdf, V3(wo[0], wo[1], wo[2]), V2(sample[0], sample[1]), (uint8_t)flags, rng, f, wi, pdf, st);
     out[0] = f.x; out[1] = f.y; out[2] = f.z; out[3] = wi.x; out[4] = wi.y; out[5] = wi.z; out[6] = pdf; out[7] = (double)st;
+}
+// Infinite-light probes: sample_li → out[0..2] wi, [3] pdf, [4..6] colour, [7..9] p1 ; pdf_li ; le
+void orc_light_sample_li(void* sp, uint32_t light, const double p[3], const double u[2], double out[10]) {
+    const Scene& s = *(Scene*)sp; HitRecord rec = record_basic(V3(p[0], p[1], p[2]), 0.);
+    LiSample o = sample_li(s, s.lights[light], rec, V2(u[0], u[1]));
+    out[0] = o.wi.x; out[1] = o.wi.y; out[2] = o.wi.z; out[3] = o.pdf; out[4] = o.color.x; out[5] = o.color.y; out[6] = o.color.z; out[7] = o.p1.x; out[8] = o.p1.y; out[9] = o.p1.z;
+}
+double orc_light_pdf_li(void* sp, uint32_t light, const double p[3], const double wi[3]) {
+    const Scene& s = *(Scene*)sp; HitRecord rec = record_basic(V3(p[0], p[1], p[2]), 0.);
+    return pdf_li(s, s.lights[light], rec, V3(wi[0], wi[1], wi[2]));
+}
+void orc_light_le(void* sp, uint32_t light, const double d[3], double out[3]) {
+    const Scene& s = *(Scene*)sp; Ray r{V3(0, 0, 0), V3(d[0], d[1], d[2]), 0.};
+    V3 c = light_le(s, s.lights[light], r); out[0] = c.x; out[1] = c.y; out[2] = c.z;
+}
+// the Distribution2D of an Infinite light: sizes → n[0] = nu, n[1] = nv; tables (any may be NULL): func of row 0..nv-1 is not
+// exported (it is the slice f[v..v+nu]); cdf rows nv*(nu+1), row integrals nv, marginal cdf nv+1, marginal integral
+void orc_light_dist(void* sp, uint32_t light, uint64_t n[2], double* cdf_rows, double* row_int, double* marg_cdf, double* marg_int) {
+    const Light& l = ((Scene*)sp)->lights[light];
+    size_t nv = l.dist.p_cond_v.size(), nu = nv ? l.dist.p_cond_v[0].count() : 0;
+    n[0] = nu; n[1] = nv;
+    for (size_t v = 0; v < nv; v++) {
+        if (cdf_rows) memcpy(cdf_rows + v * (nu + 1), l.dist.p_cond_v[v].cdf.data(), (nu + 1) * sizeof(double));
+        if (row_int) row_int[v] = l.dist.p_cond_v[v].func_int;
+    }
+    if (marg_cdf) memcpy(marg_cdf, l.dist.p_marginal.cdf.data(), (nv + 1) * sizeof(double));
+    if (marg_int) *marg_int = l.dist.p_marginal.func_int;
 }
 void orc_tex_value(void* sp, uint32_t id, double u, double v, double out[3]) { V3 c = tex_value(*(Scene*)sp, id, u, v); out[0] = c.x; out[1] = c.y; out[2] = c.z; }
 double orc_fr_dielectric(double c, double ei, double et) { return fr_dielectric(c, ei, et); }

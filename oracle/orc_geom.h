@@ -282,7 +282,12 @@ struct Scene;  // below
 
 struct Texture { rt_texture d; };
 struct Material { rt_material d; };
-struct Light { rt_light d; double area; };
+// distribution.rs:4-8, 93-96
+struct Distribution1D { std::vector<double> func, cdf; double func_int = 0.; size_t count() const { return func.size(); } };
+struct Distribution2D { std::vector<Distribution1D> p_cond_v; Distribution1D p_marginal; };
+struct Light { rt_light d; double area; Distribution2D dist; };
+// Texture::Hdr { meta, data: Vec<Rgb<f32>> } / Texture::Image { img: RgbImage } (material.rs:521-539)
+struct Image { uint32_t w = 0, h = 0; bool hdr = false; std::vector<float> f; std::vector<uint8_t> b; };
 
 struct BvhNode { Box box; int32_t left, right; uint32_t prim; };  // left<0 ⇒ leaf
 
@@ -294,6 +299,7 @@ struct Scene {
     std::vector<rt_texture> textures;
     std::vector<rt_material> materials;
     std::vector<Light> lights;
+    std::vector<Image> images;
     std::vector<BvhNode> nodes;   // faithful tree (hittable.rs:637-723), root = 0
     int32_t root = -1;
     // ordered tree statistics: counted by closest_ordered()

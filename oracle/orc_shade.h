@@ -363,14 +363,55 @@ inline double bsdf_pdf(const Bsdf& b, const V3& wow, const V3& wiw, uint8_t flag
 }
 
 // ------------------------------------------------------------------ material.rs
-// Texture::value / get_value (material.rs:542-589), SolidColor and Checkered
+// Rust `f64 as u32` / `as usize` / `f32 as u8`: saturating, NaN -> 0
+inline uint32_t as_u32(double x) { if (!(x > 0.)) return 0u; if (x >= 4294967295.) return 4294967295u; return (uint32_t)x; }
+inline size_t as_usize(double x) { if (!(x > 0.)) return 0; if (x >= 18446744073709551615.) return (size_t)-1; return (size_t)x; }
+inline uint8_t as_u8(float x) { if (!(x > 0.f)) return 0; if (x >= 255.f) return 255; return (uint8_t)x; }
+// image 0.23.12 (crates.io, not vendored) src/codecs/hdr/decoder.rs `to_rgbe8`, called by material.rs:578
+struct Rgbe8 { uint8_t c[3]; uint8_t e; };
+inline Rgbe8 to_rgbe8(const float pix[3]) {
+    float mx = std::fmax(pix[0], std::fmax(pix[1], pix[2]));
+    Rgbe8 o{{0, 0, 0}, 0};
+    if (mx <= 0.0f) return o;
+    int exp = (int)std::floor(std::log2(mx)) + 1;
+    float mul = std::pow(2.0f, (float)exp);                 // f32::powi(2.0, exp): exact for a power of two
+    for (int k = 0; k < 3; k++) o.c[k] = as_u8(std::trunc(pix[k] / mul * 256.0f));
+    o.e = (uint8_t)(exp + 128);
+    return o;
+}
+// Texture::value / get_value (material.rs:542-589): SolidColor, Checkered, Hdr; image_value (material.rs:601-611)
 inline V3 tex_value(const Scene& s, uint32_t id, double u, double v) {
     const rt_texture& t = s.textures[id];
     if (t.type == RT_TEX_CHECKERED) {
         double mult = std::sin(t.frequency * u * 2. * PI) * std::sin(t.frequency * v * 2. * PI);
         return mult < 0. ? tex_value(s, t.even, u, v) : tex_value(s, t.odd, u, v);
     }
+    if (t.type == RT_TEX_HDR) {
+        const Image& im = s.images[t.image];
+        uint32_t width = im.w, height = im.h;
+        uint32_t x = as_u32(std::round((1. - u) * (double)width));
+        uint32_t y = as_u32(std::round(v * (double)height));
+        x = x % width; y = y % height;
+        Rgbe8 q = to_rgbe8(&im.f[3 * ((size_t)y * width + x)]);
+        double sc = std::pow(2., (double)((int)q.e - 128));  // (2f64).powi(e - 128)
+        return V3(((double)q.c[0] + 0.5) * sc / 256., ((double)q.c[1] + 0.5) * sc / 256., ((double)q.c[2] + 0.5) * sc / 256.);
+    }
+    if (t.type == RT_TEX_IMAGE) {
+        const Image& im = s.images[t.image];
+        uint32_t x = as_u32(std::round(u * (double)im.w));
+        uint32_t y = as_u32(std::round((1. - v) * (double)im.h));
+        x = x % im.w; y = y % im.h;
+        const uint8_t* px = &im.b[3 * ((size_t)y * im.w + x)];
+        return V3((double)px[0] / 255., (double)px[1] / 255., (double)px[2] / 255.);
+    }
     return V3(t.color[0], t.color[1], t.color[2]);
+}
+// Texture::get_size (material.rs:591-599)
+inline void tex_size(const Scene& s, uint32_t id, uint32_t& w, uint32_t& h) {
+    const rt_texture& t = s.textures[id];
+    if (t.type == RT_TEX_HDR || t.type == RT_TEX_IMAGE) { w = s.images[t.image].w; h = s.images[t.image].h; }
+    else if (t.type == RT_TEX_SOLID) { w = h = 1; }
+    else { w = h = 0; }
 }
 // Material::compute_scattering (material.rs:80-244), mode = RADIANCE, allow_lobes = true in the path integrator
 inline void compute_scattering(const Scene& s, HitRecord& r, uint8_t mode, bool allow_lobes) {
@@ -485,6 +526,7 @@ inline double prim_pdf(const Scene& s, const rt_primitive& pr, const HitRecord& 
 }
 // Light::l (light.rs:475-496)
 inline V3 light_l(const Light& l, const HitRecord& rec, const V3& w) {
+    if (l.d.type != RT_LIGHT_DIFFUSE) return black();
     if (dot(rec.n, w) > 0. || l.d.two_sided) return V3(l.d.color[0], l.d.color[1], l.d.color[2]);
     return black();
 }
@@ -494,10 +536,109 @@ inline V3 record_le(const Scene& s, const HitRecord& rec, const V3& w) {
     if (li == RT_NONE) return black();
     return light_l(s.lights[li], rec, w);
 }
+// ------------------------------------------------------------------ distribution.rs
+// Distribution1D::make_distribution (distribution.rs:28-55)
+inline Distribution1D make_distribution(const double* f, size_t n) {
+    Distribution1D d; d.func.assign(f, f + n); d.cdf.assign(n + 1, 0.);
+    d.cdf[0] = 0.;
+    for (size_t i = 1; i < n + 1; i++) d.cdf[i] = d.cdf[i - 1] + d.func[i - 1] / (double)n;
+    d.func_int = d.cdf[n];
+    if (d.func_int == 0.) { for (size_t i = 1; i < n + 1; i++) d.cdf[i] = (double)i / (double)n; }
+    else { for (size_t i = 1; i < n + 1; i++) d.cdf[i] = d.cdf[i] / d.func_int; }
+    return d;
+}
+// find_interval (distribution.rs:150-166)
+template <class Pred> inline size_t find_interval(size_t size, Pred pred) {
+    size_t first = 0, len = size;
+    while (len > 0) {
+        size_t half = len >> 1, middle = first + half;
+        if (pred(middle)) { first = middle + 1; len = len - half - 1; } else len = half;
+    }
+    return as_usize(clampd((double)(first - 1), 0., (double)(size - 2)));   // `first - 1` would wrap at 0; cdf[0] <= u keeps first >= 1
+}
+// Distribution1D::sample_continuous (distribution.rs:64-78) → (x, pdf, offset)
+inline void dist1_sample_continuous(const Distribution1D& d, double u, double& x, double& pdf, size_t& offset) {
+    offset = find_interval(d.cdf.size(), [&](size_t i) { return d.cdf[i] <= u; });
+    double du = u - d.cdf[offset];
+    if (d.cdf[offset + 1] - d.cdf[offset] > 0.) du = du / (d.cdf[offset + 1] - d.cdf[offset]);
+    pdf = d.func_int > 0. ? d.func[offset] / d.func_int : 0.;
+    x = ((double)offset + du) / (double)d.count();
+}
+// Distribution2D::make_distribution_2d (distribution.rs:117-130): row v is built from the SLICE f[v..v+nu]
+inline Distribution2D make_distribution_2d(const std::vector<double>& f, size_t nu, size_t nv) {
+    Distribution2D d;
+    for (size_t v = 0; v < nv; v++) d.p_cond_v.push_back(make_distribution(&f[v], nu));
+    std::vector<double> marginal;
+    for (size_t v = 0; v < nv; v++) marginal.push_back(d.p_cond_v[v].func_int);
+    d.p_marginal = make_distribution(marginal.data(), nv);
+    return d;
+}
+// Distribution2D::sample_continuous (distribution.rs:135-139)
+inline void dist2_sample_continuous(const Distribution2D& d, const V2& u, V2& out, double& pdf) {
+    double d1, pdf1, d0, pdf0; size_t v, off;
+    dist1_sample_continuous(d.p_marginal, u.y, d1, pdf1, v);
+    dist1_sample_continuous(d.p_cond_v[v], u.x, d0, pdf0, off);
+    out = V2(d0, d1); pdf = pdf1 * pdf0;
+}
+// Distribution2D::pdf (distribution.rs:141-147)
+inline double dist2_pdf(const Distribution2D& d, const V2& p) {
+    size_t iu = as_usize(p.x * (double)d.p_cond_v[0].count()); iu = std::min(std::max(iu, (size_t)0), d.p_cond_v[0].count() - 1);
+    size_t iv = as_usize(p.y * (double)d.p_marginal.count()); iv = std::min(std::max(iv, (size_t)0), d.p_marginal.count() - 1);
+    return d.p_cond_v[iv].func[iu] / d.p_marginal.func_int;
+}
+// ------------------------------------------------------------------ light.rs (Infinite)
+constexpr double WORLD_RADIUS = 10000.;                                    // light.rs:636
+inline double color_to_luminance(const V3& v) { return 0.2126 * v.x + 0.7152 * v.y + 0.0722 * v.z; }   // util.rs:169-171
+inline double spherical_theta(const V3& v) { return std::acos(clampd(v.y, -1., 1.)); }                  // util.rs:153-155
+inline double spherical_phi(const V3& v) { double p = std::atan2(v.z, v.x); return p < 0. ? p + 2. * PI : p; }   // util.rs:160-167
+inline V3 light_to_world(const Scene& s, const Light& l, const V3& v) { return l.d.transform == RT_NONE ? v : xf_vector(s.xforms[l.d.transform].fwd, v); }
+inline V3 light_to_obj(const Scene& s, const Light& l, const V3& v) { return l.d.transform == RT_NONE ? v : xf_vector(s.xforms[l.d.transform].inv, v); }
+// Light::make_infinite_light (light.rs:608-638)
+inline bool make_infinite_light(const Scene& s, Light& l) {
+    uint32_t tw, th; tex_size(s, l.d.text_id, tw, th);
+    size_t width = (size_t)tw * 2, height = (size_t)th * 2;
+    if (width == 0 || height == 0) return false;
+    std::vector<double> img(width * height, 0.);
+    for (size_t v = 0; v < height; v++) {
+        double vp = ((double)v + 0.5) / (double)height;
+        double sin_theta = std::sin(PI * ((double)v + 0.5) / (double)height);
+        for (size_t u = 0; u < width; u++) {
+            double up = (double)u / (double)width;
+            V3 color = tex_value(s, l.d.text_id, up, vp);
+            img[u + v * width] = color_to_luminance(color);
+            img[u + v * width] = img[u + v * width] * sin_theta;
+        }
+    }
+    l.dist = make_distribution_2d(img, width, height);
+    return true;
+}
+// Light::le (light.rs:499-513)
+inline V3 light_le(const Scene& s, const Light& l, const Ray& ray) {
+    if (l.d.type != RT_LIGHT_INFINITE) return black();
+    V3 w = normalize(light_to_obj(s, l, ray.d));
+    V2 uv(spherical_phi(w) * INV_2PI, spherical_theta(w) * INV_PI);
+    return tex_value(s, l.d.text_id, uv.x, uv.y);
+}
+
 // Light::sample_li, Diffuse arm (light.rs:176-203) → wi, pdf, color, visibility target
 struct LiSample { V3 wi; double pdf; V3 color; V3 p1; uint32_t p1_prim; double p1_t; };
 inline LiSample sample_li(const Scene& s, const Light& l, const HitRecord& rec, const V2& u) {
     LiSample o;
+    if (l.d.type == RT_LIGHT_INFINITE) {                                   // light.rs:204-245
+        V2 uv; double map_pdf;
+        dist2_sample_continuous(l.dist, u, uv, map_pdf);
+        if (map_pdf == 0.) { o.wi = normalize(black()); o.pdf = 0.; o.color = black(); o.p1 = V3(0, 0, 0); o.p1_prim = 0; o.p1_t = 1.; return o; }
+        double theta = uv.y * PI, phi = uv.x * 2. * PI;
+        double cos_theta = std::cos(theta), sin_theta = std::sin(theta), cos_phi = std::cos(phi), sin_phi = std::sin(phi);
+        V3 v(sin_theta * cos_phi, sin_theta * sin_phi, cos_theta);
+        V3 wi = light_to_world(s, l, v);
+        double pdf = map_pdf / (2. * PI * PI * sin_theta);
+        if (sin_theta == 0.) pdf = 0.;
+        o.p1 = rec.p + wi * (2. * WORLD_RADIUS); o.p1_prim = 0; o.p1_t = rec.t;     // HitRecord::make_basic: prim_index 0
+        o.color = tex_value(s, l.d.text_id, uv.x, uv.y);
+        o.wi = normalize(wi); o.pdf = pdf;
+        return o;
+    }
     const rt_primitive& pr = s.prims[l.d.prim_index];
     HitRecord nr; double pdf; V3 wi;
     prim_sample(s, pr, rec, u, nr, pdf, wi);
@@ -514,7 +655,16 @@ inline LiSample sample_li(const Scene& s, const Light& l, const HitRecord& rec, 
     return o;
 }
 // Light::pdf_li, Diffuse arm (light.rs:284)
-inline double pdf_li(const Scene& s, const Light& l, const HitRecord& rec, const V3& wi) { return prim_pdf(s, s.prims[l.d.prim_index], rec, wi); }
+inline double pdf_li(const Scene& s, const Light& l, const HitRecord& rec, const V3& wi) {
+    if (l.d.type == RT_LIGHT_INFINITE) {                                   // light.rs:285-294
+        V3 w = light_to_world(s, l, wi);
+        double theta = spherical_theta(w), phi = spherical_phi(w);
+        double sin_theta = std::sin(theta);
+        if (sin_theta == 0.) return 0.;
+        return dist2_pdf(l.dist, V2(phi * INV_2PI, theta * INV_PI)) / (2. * PI * PI * sin_theta);
+    }
+    return prim_pdf(s, s.prims[l.d.prim_index], rec, wi);
+}
 
 // ------------------------------------------------------------------ integrator.rs (Path)
 struct RayCounts {
@@ -538,7 +688,7 @@ inline V3 estimate_direct(const Scene& s, const HitRecord& rec, const V2& u_scat
         double scattering_pdf = bsdf_pdf(rec.bsdf, rec.wo, ls.wi, flags);
         if (f != black()) {
             rc.shadow++;
-            if (!unoccluded(s, rec.p, ls.p1, ls.p1_prim, ls.p1_t, false)) color = black();
+            if (!unoccluded(s, rec.p, ls.p1, ls.p1_prim, ls.p1_t, light.d.type == RT_LIGHT_INFINITE)) color = black();
             if (color != black()) {
                 double weight = power_heuristic(1, light_pdf, 1, scattering_pdf);
                 ld = ld + cmul(f, color) * (weight / light_pdf);
@@ -563,7 +713,7 @@ inline V3 estimate_direct(const Scene& s, const HitRecord& rec, const V2& u_scat
             if (get_intersection(s, nray, nrec)) {
                 uint32_t li = s.prims[nrec.prim_index].light_index;
                 if (li != RT_NONE && li == light_num) c = record_le(s, nrec, -wi);
-            }   // else light.le(ray): black for area lights
+            } else c = light_le(s, light, nray);
             if (c != black()) ld = ld + cmul(f, c) * (weight / scattering_pdf);
         }
     }
@@ -594,7 +744,7 @@ inline V3 path_li(const Scene& s, Ray ray, uint32_t max_depth, bool invisible_li
                     if (invisible_light) { ray = spawn_ray(rec, ray.d); continue; }
                     l = l + cmul(record_le(s, rec, -ray.d), beta);
                 }
-            }   // miss: Σ light.le(ray) = 0 for area lights
+            } else { for (const Light& light : s.lights) l = l + cmul(light_le(s, light, ray), beta); }
         }
         if (!is_some || bounces >= max_depth) break;
         compute_scattering(s, rec, RADIANCE, true);

@@ -124,6 +124,20 @@ class Objects:
     def set_light_index(self, prim, light):
         check(lib().rt_scene_set_light_index(self.h, prim, light))
 
+    def add_image_hdr(self, rgb_f32):
+        """`Texture::new_hdr`'s decoded pixels (material.rs:626-642): (h, w, 3) float32."""
+        a = np.ascontiguousarray(rgb_f32, dtype=np.float32)
+        out = C.c_uint32()
+        check(lib().rt_scene_add_image_hdr(self.h, a.shape[1], a.shape[0], ptr(a), C.byref(out)))
+        return out.value
+
+    def add_image_rgb8(self, rgb_u8):
+        """`Texture::new_texture`'s RgbImage (material.rs:613-616): (h, w, 3) uint8."""
+        a = np.ascontiguousarray(rgb_u8, dtype=np.uint8)
+        out = C.c_uint32()
+        check(lib().rt_scene_add_image_rgb8(self.h, a.shape[1], a.shape[0], ptr(a), C.byref(out)))
+        return out.value
+
     def set_textures(self, t):
         t = np.ascontiguousarray(t, dtype=N.texture_dtype)
         check(lib().rt_scene_set_textures(self.h, len(t), ptr(t)))

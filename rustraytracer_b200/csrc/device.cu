@@ -44,7 +44,19 @@ rt_status upload_scene(rt_scene& s, const HostImage& img) {
     if ((st = up(s, s.xforms, d.xforms, b))) return st;
     if ((st = up(s, s.textures, d.textures, b))) return st;
     if ((st = up(s, s.materials, d.materials, b))) return st;
-    if ((st = up(s, img.lights, d.lights, b))) return st;
+    if ((st = up(s, s.images, d.images, b))) return st;
+    if ((st = up(s, s.texels, d.texels, b))) return st;
+    // Infinite lights: upload the flat Distribution2D tables and turn the offsets kept in DLight into device pointers
+    const double* d_dist = nullptr;
+    if ((st = up(s, img.dist, d_dist, b))) return st;
+    std::vector<DLight> lights = img.lights;
+    for (auto& l : lights) {
+        if (l.type != RT_LIGHT_INFINITE) continue;
+        d.has_infinite = 1;
+        l.dist_f = d_dist + ((uintptr_t)l.dist_f - 1); l.dist_cdf = d_dist + ((uintptr_t)l.dist_cdf - 1);
+        l.row_int = d_dist + ((uintptr_t)l.row_int - 1); l.marg_cdf = d_dist + ((uintptr_t)l.marg_cdf - 1);
+    }
+    if ((st = up(s, lights, d.lights, b))) return st;
     s.bytes_tables = b;
     d.n_nodes = (uint32_t)img.nodes.size(); d.n_prims = (uint32_t)img.prims.size();
     d.n_lights = (uint32_t)img.lights.size(); d.n_slots = (uint32_t)img.slots.size();

@@ -24,6 +24,8 @@ struct rth_scene {
     std::vector<rt_texture> textures;
     std::vector<rt_material> materials;
     std::vector<rt_light> lights;
+    struct Image { uint32_t w = 0, h = 0; bool hdr = false; std::vector<float> f; std::vector<uint8_t> b; };   // Texture::Hdr data / Texture::Image img
+    std::vector<Image> images;
     rt_camera camera{};
     std::string png;
     bool standin = false;
@@ -66,6 +68,11 @@ uint32_t push_xform(rth_scene& s, const double m[16]) { s.xforms.insert(s.xforms
 void camera(rth_scene& s, const double from[3], const double to[3], double aspect, double vfov, double aperture, double focus, double t0, double t1) {
     double up[3] = {0., 1., 0.};
     rt_camera_look_at(from, to, up, aspect, vfov, aperture, focus, t0, t1, &s.camera);
+}
+uint32_t push_hdr_texture(rth_scene& s, uint32_t image) { rt_texture t{}; t.type = RT_TEX_HDR; t.image = image; s.textures.push_back(t); return (uint32_t)s.textures.size() - 1; }      // Texture::new_hdr
+uint32_t push_image_texture(rth_scene& s, uint32_t image) { rt_texture t{}; t.type = RT_TEX_IMAGE; t.image = image; s.textures.push_back(t); return (uint32_t)s.textures.size() - 1; }  // Texture::new_texture
+uint32_t push_infinite_light(rth_scene& s, uint32_t text_id, uint32_t xf = RT_NONE) {     // Light::make_infinite_light(to_world, n_samples, text_id) light.rs:608
+    rt_light l{}; l.type = RT_LIGHT_INFINITE; l.prim_index = RT_NONE; l.text_id = text_id; l.transform = xf; s.lights.push_back(l); return (uint32_t)s.lights.size() - 1;
 }
 
 // ---- 4x4 helpers (row-major)
@@ -433,6 +440,123 @@ void build_two_dragons(rth_scene& s, const rth_params& p) {
     push_mesh_triangles(s, m1, 3);
     s.png = "two_dragons.png";
 }
+// ---- Radiance .hdr (RGBE) reader: what Texture::new_hdr gets from image 0.23's HdrDecoder::read_image_hdr
+// (material.rs:626-642): header lines up to a blank line, a "-Y H +X W" resolution line, then scanlines that are either
+// new-style RLE (2 2 hi lo, four component planes of runs / literals) or flat RGBE quadruples; each pixel becomes
+// Rgb<f32> = c * 2^(e-136), or 0 when e == 0 (`Rgbe8Pixel::to_hdr`).
+bool load_hdr(const char* path, rth_scene::Image& img, std::string& err) {
+    FILE* f = fopen(path, "rb");
+    if (!f) { err = std::string("cannot open ") + path; return false; }
+    char line[512]; bool magic = false; int W = 0, H = 0;
+    while (fgets(line, sizeof(line), f)) {
+        if (!magic) { if (strncmp(line, "#?", 2) != 0) { err = "not a Radiance HDR file"; fclose(f); return false; } magic = true; continue; }
+        if (line[0] == '\n' || (line[0] == '\r' && line[1] == '\n')) break;
+    }
+    if (!fgets(line, sizeof(line), f) || sscanf(line, "-Y %d +X %d", &H, &W) != 2 || W <= 0 || H <= 0) { err = "unsupported HDR orientation"; fclose(f); return false; }
+    std::vector<uint8_t> rgbe((size_t)W * H * 4), scan((size_t)W * 4);
+    for (int y = 0; y < H; y++) {
+        uint8_t* row = &rgbe[(size_t)y * W * 4];
+        uint8_t h4[4];
+        if (fread(h4, 1, 4, f) != 4) { err = "truncated HDR"; fclose(f); return false; }
+        if (W >= 8 && W < 32768 && h4[0] == 2 && h4[1] == 2 && ((h4[2] << 8) | h4[3]) == W) {
+            for (int c = 0; c < 4; c++) {
+                int x = 0;
+                while (x < W) {
+                    int n = fgetc(f); if (n == EOF) { err = "truncated HDR"; fclose(f); return false; }
+                    if (n > 128) { n -= 128; int v = fgetc(f); if (v == EOF || x + n > W) { err = "bad HDR run"; fclose(f); return false; } for (int k = 0; k < n; k++) scan[(size_t)c * W + x++] = (uint8_t)v; }
+                    else { if (n == 0 || x + n > W || fread(&scan[(size_t)c * W + x], 1, n, f) != (size_t)n) { err = "bad HDR literal"; fclose(f); return false; } x += n; }
+                }
+            }
+            for (int x = 0; x < W; x++) for (int c = 0; c < 4; c++) row[4 * x + c] = scan[(size_t)c * W + x];
+        } else {
+            memcpy(row, h4, 4);
+            if (W > 1 && fread(row + 4, 1, (size_t)(W - 1) * 4, f) != (size_t)(W - 1) * 4) { err = "truncated HDR"; fclose(f); return false; }
+        }
+    }
+    fclose(f);
+    img.w = (uint32_t)W; img.h = (uint32_t)H; img.hdr = true; img.f.resize((size_t)W * H * 3);
+    for (size_t i = 0; i < (size_t)W * H; i++) {
+        uint8_t e = rgbe[4 * i + 3];
+        float sc = e == 0 ? 0.0f : std::exp2((float)e - 136.0f);
+        for (int c = 0; c < 3; c++) img.f[3 * i + c] = e == 0 ? 0.0f : sc * (float)rgbe[4 * i + c];
+    }
+    return true;
+}
+// deterministic stand-in for data/material/textures/envmap.hdr when the file is not there (the GPU box has no reference
+// checkout): a sky gradient with a warm horizon band, a small very bright sun and a dim ground, W x H = 256 x 128,
+// snapped to RGBE8-representable f32 values like a decoded file would be.
+void envmap_standin(rth_scene::Image& img, uint32_t W = 256, uint32_t H = 128) {
+    img.w = W; img.h = H; img.hdr = true; img.f.resize((size_t)W * H * 3);
+    for (uint32_t y = 0; y < H; y++) for (uint32_t x = 0; x < W; x++) {
+        double v = (y + 0.5) / H, u = (x + 0.5) / W;
+        double up = std::cos(v * 3.14159265358979);                     // +1 zenith .. -1 nadir
+        double c[3];
+        if (up >= 0.) { double t = std::pow(1. - up, 3.); c[0] = 0.25 + 0.9 * t; c[1] = 0.45 + 0.6 * t; c[2] = 0.9 + 0.1 * t; }
+        else { double t = std::pow(1. + up, 6.); c[0] = 0.08 + 0.5 * t; c[1] = 0.07 + 0.4 * t; c[2] = 0.06 + 0.3 * t; }
+        double du = (u - 0.30) * 2., dv = (v - 0.28) * 1.;                // sun
+        double d2 = du * du + dv * dv;
+        double sun = 60. * std::exp(-d2 / (2. * 0.02 * 0.02)) + 2. * std::exp(-d2 / (2. * 0.08 * 0.08));
+        c[0] += sun; c[1] += sun * 0.92; c[2] += sun * 0.8;
+        double mx = std::fmax(c[0], std::fmax(c[1], c[2]));
+        int e; std::frexp(mx, &e);
+        for (int k = 0; k < 3; k++) { double q = std::floor(std::ldexp(c[k], 8 - e)); img.f[3 * ((size_t)y * W + x) + k] = (float)std::ldexp(q, e - 8); }
+    }
+}
+uint32_t add_envmap(rth_scene& s, const rth_params& p, const char* rel) {
+    rth_scene::Image img; bool loaded = false;
+    if (p.data_dir) { std::string path = std::string(p.data_dir) + "/" + rel, err; if (file_exists(path)) loaded = load_hdr(path.c_str(), img, err); }
+    if (!loaded) { envmap_standin(img); s.standin = true; }
+    s.images.push_back(std::move(img));
+    return (uint32_t)s.images.size() - 1;
+}
+// an OBJ of the reference's data/ directory under `xf`, or a blob stand-in in [lo,hi]
+uint32_t add_obj_or_blob(rth_scene& s, const rth_params& p, const char* rel, const double xf[16], uint32_t nu, uint32_t nv, uint64_t seed, const double lo[3], const double hi[3]) {
+    rt::HostMesh m; bool loaded = false;
+    if (p.data_dir) { std::string path = std::string(p.data_dir) + "/" + rel, err; if (file_exists(path)) loaded = load_obj(path.c_str(), xf, m, err); }
+    if (!loaded) { append_blob(m, nu, nv, seed, lo, hi); s.standin = true; }
+    s.meshes.push_back(std::move(m));
+    return (uint32_t)s.meshes.size() - 1;
+}
+void camera_up(rth_scene& s, const double from[3], const double to[3], const double up[3], double aspect, double vfov) {
+    rt_camera_look_at(from, to, up, aspect, vfov, 0.0, 10., 0., 0., &s.camera);     // Camera::new → t0 = t1 = 0
+}
+// scenes.rs:627-741 `material_hdr(mat_num)`: the material-test ball under an HDR environment (Light::Infinite), variant =
+// mat_num: 0 smooth_plastic (:824), 1 rosegold_metal (:839), 2 mirror (:876), 3 glass (:857)
+void build_material_hdr(rth_scene& s, const rth_params& p) {
+    const double from[3] = {3.04068, 3.17153, 3.20454}, dir[3] = {-0.583445, -0.538765, -0.60772}, up[3] = {-0.373123, 0.842456, -0.388647};
+    const double to[3] = {from[0] + dir[0], from[1] + dir[1], from[2] + dir[2]};
+    camera_up(s, from, to, up, aspect_of(p), 20.);
+    uint32_t env = push_hdr_texture(s, add_envmap(s, p, "material/textures/envmap.hdr"));     // texts[0]
+    push_infinite_light(s, env);
+    auto sim = [](double sc, double tx, double ty, double tz, double m[16]) { mat_identity(m); m[0] = m[5] = m[10] = sc; m[3] = tx; m[7] = ty; m[11] = tz; };
+    double m1[16], m2[16], m0[16];
+    sim(0.482906, 0.0571719, 0.213656, 0.0682078, m1); sim(0.482906, 0.156382, 0.777229, 0.161698, m2); sim(0.482906, 0.110507, 0.494301, 0.126194, m0);
+    const double rect_m[16] = {-1.88298, 1.9602, 2.50299e-007, -0.708772, -2.37623e-007, 1.18811e-007, -2.71809, 0., -1.9602, -1.88298, 8.90586e-008, -0.732108, 0., 0., 0., 1.};
+    // stand-in boxes: a base, a cap and the ball between them, where the transformed reference meshes sit
+    const double lo1[3] = {-0.38, 0.005, -0.37}, hi1[3] = {0.50, 0.42, 0.51}, lo2[3] = {-0.12, 0.60, -0.11}, hi2[3] = {0.43, 0.95, 0.44}, lo0[3] = {-0.30, 0.10, -0.28}, hi0[3] = {0.52, 0.90, 0.53};
+    uint32_t mesh1 = add_obj_or_blob(s, p, "material/models/Mesh001.obj", m1, 96, 95, 11, lo1, hi1);
+    uint32_t mesh2 = add_obj_or_blob(s, p, "material/models/Mesh002.obj", m2, 64, 63, 12, lo2, hi2);
+    uint32_t mesh0 = add_obj_or_blob(s, p, "material/models/Mesh000.obj", m0, 84, 83, 13, lo0, hi0);
+    (void)mesh2;
+    switch (p.variant) {
+        case 0: { uint32_t a = push_solid(s, 0.1608, 0.0014767, 0.4), b = push_solid(s, 1., 1., 1.); push_plastic(s, a, b, 0.002, false); break; }
+        case 1: { uint32_t a = push_solid(s, 1. - 0.718, 1. - 0.431, 1. - 0.475), b = push_solid(s, 1., 1., 1.), c = push_solid(s, 0.002, 0., 0.); push_metal(s, a, b, c, c, c, true); break; }
+        case 2: { uint32_t a = push_solid(s, 1., 1., 1.); push_mirror(s, a); break; }
+        default: { push_solid(s, 1. - 0.718, 1. - 0.431, 1. - 0.475); uint32_t b = push_solid(s, 1., 1., 1.); push_solid(s, 0.002, 0., 0.); push_glass(s, b, b, 0.01, 0.01, 1.5, true); break; }
+    }
+    uint32_t len = (uint32_t)s.textures.size();
+    push_solid(s, 0.2, 0.2, 0.2); push_solid(s, 0.325, 0.31, 0.325); push_solid(s, 0.725, 0.71, 0.68);
+    push_checkered(s, len + 1, len + 2, 10.);
+    push_matte(s, len, 0.);          // material 1
+    push_matte(s, len + 3, 0.);      // material 2
+    push_mesh_triangles(s, 0, 0);    // generate_triangles(meshes, 0, 0)
+    push_mesh_triangles(s, 1, 0);    // generate_triangles(meshes, 1, 0)
+    push_mesh_triangles(s, 2, 1);    // generate_triangles(meshes, 2, 1)
+    (void)mesh1; (void)mesh0;
+    push_prim(s, make_rect(RT_PRIM_XY_RECT, -1., -1., 1., 1., 0., 2, push_xform(s, rect_m)));
+    s.png = "material.png";
+}
+
 // triangle soup; centre ~ U[-1,1]^3, edges ~ U[-s,s]^3, s = 2 N^(-1/3), f32-exact values
 void build_soup(rth_scene& s, const rth_params& p) {
     uint64_t n = p.n_tris ? p.n_tris : 1000000;
@@ -478,6 +602,7 @@ rt_status rth_scene_build(const char* name, const rth_params* params, rth_scene*
     else if (n == "plastic_dragon") build_plastic_dragon(*s, *params);
     else if (n == "two_dragons") build_two_dragons(*s, *params);
     else if (n == "soup") build_soup(*s, *params);
+    else if (n == "material_hdr") build_material_hdr(*s, *params);
     else { delete s; rt::set_error("rth_scene_build: unknown scene '" + n + "'"); return RT_ERR_INVALID; }
     *out = s;
     return RT_OK;
@@ -518,9 +643,33 @@ rt_status rth_scene_copy_textures(const rth_scene* s, rt_texture* out) { if (!s 
 rt_status rth_scene_copy_materials(const rth_scene* s, rt_material* out) { if (!s || !out) return RT_ERR_INVALID; memcpy(out, s->materials.data(), s->materials.size() * sizeof(rt_material)); return RT_OK; }
 rt_status rth_scene_copy_lights(const rth_scene* s, rt_light* out) { if (!s || !out) return RT_ERR_INVALID; memcpy(out, s->lights.data(), s->lights.size() * sizeof(rt_light)); return RT_OK; }
 
+rt_status rth_scene_num_images(const rth_scene* s, uint64_t* n) { if (!s || !n) return RT_ERR_INVALID; *n = s->images.size(); return RT_OK; }
+rt_status rth_scene_image_info(const rth_scene* s, uint32_t i, uint32_t info[3]) {
+    if (!s || !info || i >= s->images.size()) return RT_ERR_INVALID;
+    info[0] = s->images[i].w; info[1] = s->images[i].h; info[2] = s->images[i].hdr ? 1u : 0u; return RT_OK;
+}
+rt_status rth_scene_image_copy(const rth_scene* s, uint32_t i, void* out) {
+    if (!s || !out || i >= s->images.size()) return RT_ERR_INVALID;
+    const auto& im = s->images[i];
+    if (im.hdr) memcpy(out, im.f.data(), im.f.size() * sizeof(float)); else memcpy(out, im.b.data(), im.b.size());
+    return RT_OK;
+}
+rt_status rth_load_hdr(const char* path, uint32_t* w, uint32_t* h, float* rgb_out, uint64_t capacity_floats) {
+    if (!path || !w || !h) { rt::set_error("rth_load_hdr: null argument"); return RT_ERR_INVALID; }
+    rth_scene::Image img; std::string err;
+    if (!load_hdr(path, img, err)) { rt::set_error("rth_load_hdr: " + err); return RT_ERR_IO; }
+    *w = img.w; *h = img.h;
+    if (rgb_out) { if (capacity_floats < img.f.size()) { rt::set_error("rth_load_hdr: buffer too small"); return RT_ERR_INVALID; } memcpy(rgb_out, img.f.data(), img.f.size() * sizeof(float)); }
+    return RT_OK;
+}
+
 rt_status rth_scene_upload(const rth_scene* s, rt_scene* dst) {
     if (!s || !dst) { rt::set_error("rth_scene_upload: null argument"); return RT_ERR_INVALID; }
     rt_status st;
+    for (auto& im : s->images) {
+        if (im.hdr) st = rt_scene_add_image_hdr(dst, im.w, im.h, im.f.data(), nullptr); else st = rt_scene_add_image_rgb8(dst, im.w, im.h, im.b.data(), nullptr);
+        if (st) return st;
+    }
     for (auto& m : s->meshes) {
         uint32_t idx;
         if ((st = rt_scene_add_mesh(dst, m.p.size() / 3, m.p.data(), m.n.size() / 3, m.n.empty() ? nullptr : m.n.data(), m.uv.size() / 2,

@@ -223,18 +223,23 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
                 uint32_t light_num = min(n_lights - 1, (uint32_t)(unsigned long long)(rng_next(rng) * (double)n_lights));
                 D2 u_light; u_light.x = rng_next(rng); u_light.y = rng_next(rng);
                 V2<R> u_scatter; u_scatter.x = rng_real<R>(rng); u_scatter.y = rng_real<R>(rng);
-                const DLight light = sc.lights[light_num];
+                const DLight& light = sc.lights[light_num];
                 const uint32_t nsf = BSDF_ALL - BSDF_SPECULAR;
-                // estimate_direct, light half (integrator.rs:573-597); Light::sample_li Diffuse (light.rs:176-203), Primitive::sample (primitive.rs:445-456)
+                // estimate_direct, light half (integrator.rs:573-597); Light::sample_li Diffuse (light.rs:176-203), Primitive::sample
+                // (primitive.rs:445-456) / Infinite (light.rs:204-245)
+                const bool inf_light = light.type == RT_LIGHT_INFINITE;
                 {
-                    D3 p1, n1; sample_area(sc, light.prim, u_light, p1, n1);
-                    double pdf = 1. / light.area;
-                    D3 wiu = p1 - rec.p;
-                    if (norm2(wiu) == 0.) pdf = 0.;
-                    else { D3 wn = normalize(wiu); pdf = pdf * norm2(rec.p - p1) / fabs(dot(n1, -wn)); }
-                    double light_pdf; D3 color, wid = mk3(0., 0., 0.);
-                    if (pdf == 0. || norm2(rec.p - p1) == 0.) { light_pdf = 0.; color = ld3(light.color); }
-                    else { wid = normalize(p1 - rec.p); light_pdf = pdf; color = light_l(light, n1, -wid); }
+                    D3 p1; double light_pdf; D3 color, wid = mk3(0., 0., 0.);
+                    if (inf_light) infinite_sample_li(sc, light, rec.p, u_light, wid, light_pdf, color, p1);
+                    else {
+                        D3 n1; sample_area(sc, light.prim, u_light, p1, n1);
+                        double pdf = 1. / light.area;
+                        D3 wiu = p1 - rec.p;
+                        if (norm2(wiu) == 0.) pdf = 0.;
+                        else { D3 wn = normalize(wiu); pdf = pdf * norm2(rec.p - p1) / fabs(dot(n1, -wn)); }
+                        if (pdf == 0. || norm2(rec.p - p1) == 0.) { light_pdf = 0.; color = ld3(light.color); }
+                        else { wid = normalize(p1 - rec.p); light_pdf = pdf; color = light_l(light, n1, -wid); }
+                    }
                     if (light_pdf > 0. && !is_black(color)) {
                         V3<R> wi = cast3<R>(wid);
                         V3<R> f = bsdf_f<R, KM>(bsdf, wo_w, wi, nsf) * fabs(dot(wi, sn));
@@ -245,7 +250,7 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
                             V3<R> contrib = cmul(ld * (R)n_lights, beta);
                             uint32_t q = warp_append(&c->n_shadow);
                             __stcs(shq.ax + q, rec.p.x); __stcs(shq.ay + q, rec.p.y); __stcs(shq.az + q, rec.p.z); __stcs(shq.bx + q, p1.x); __stcs(shq.by + q, p1.y); __stcs(shq.bz + q, p1.z);
-                            __stcs(shq.cr + q, (double)contrib.x); __stcs(shq.cg + q, (double)contrib.y); __stcs(shq.cb + q, (double)contrib.z); __stcs(shq.target + q, light.prim); __stcs(shq.pixel + q, pixel);
+                            __stcs(shq.cr + q, (double)contrib.x); __stcs(shq.cg + q, (double)contrib.y); __stcs(shq.cb + q, (double)contrib.z); __stcs(shq.target + q, inf_light ? RT_NONE : light.prim); __stcs(shq.pixel + q, pixel);
                         }
                     }
                 }
@@ -259,8 +264,10 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
                         D3 wid = dbl3(wi);
                         if ((st & BSDF_SPECULAR) == 0) {
                             // Light::pdf_li → Primitive::pdf (primitive.rs:462-473): re-intersect the ONE light primitive, tmin = 0, no leaf box
+                            // Infinite: Light::pdf_li (light.rs:285-294)
                             D3 lp, ln; double light_pdf = 0.;
-                            if (prim_hit_pn(sc, light.prim, rec.p, wid, 0., INF, lp, ln)) light_pdf = norm2(rec.p - lp) / (light.area * fabs(dot(ln, -wid)));
+                            if (inf_light) light_pdf = infinite_pdf_li(sc, light, wid);
+                            else if (prim_hit_pn(sc, light.prim, rec.p, wid, 0., INF, lp, ln)) light_pdf = norm2(rec.p - lp) / (light.area * fabs(dot(ln, -wid)));
                             if (light_pdf == 0.) go = false;
                             else weight = power_heuristic<R>(scattering_pdf, (R)light_pdf);
                         }
@@ -298,6 +305,22 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
     }
 }
 
+// Paths whose extend ray left the scene (bin 15).  Only launched when the scene has an Infinite light: at bounce 0 or after a
+// specular bounce every light's `le(ray)` is added (integrator.rs:406-410; Light::le is black for area lights).
+__global__ void __launch_bounds__(128) k_shade_miss(Ctrl* c, DScene sc, RenderParams rp, PathSet in, const uint2* __restrict__ bin_idx, double* film) {
+    const uint32_t n = c->bin_count[N_BINS - 1];
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+        const uint32_t i = bin_idx[(size_t)(N_BINS - 1) * rp.W + k].x;
+        const PAux pa = load_aux(in.aux + i);
+        if (!((pa.flags & 0xffffu) == 0 || ((pa.flags >> 16) & 1u))) continue;
+        const PRay pr = load_ray(in.ray + i);
+        D3 d = mk3(pr.dx, pr.dy, pr.dz), beta = mk3(pa.bx, pa.by, pa.bz), l = mk3(0., 0., 0.);
+        for (uint32_t li = 0; li < sc.n_lights; li++)
+            if (sc.lights[li].type == RT_LIGHT_INFINITE) l = l + cmul(infinite_le(sc, sc.lights[li], d), beta);
+        film_add(film, pa.pixel, l);
+    }
+}
+
 // Ray types B and C are traced by ONE persistent launch over the concatenated queue [shadow | probe]: the probe queue is
 // ~5 % of the shadow queue, and as a launch of its own it paid a whole persistent-kernel tail for it (ncu launch list r01:
 // 11 % of the step for 2.4 % of the rays).
@@ -316,6 +339,10 @@ struct ConnectJob {
         uint32_t target = __ldcs(sh.target + i);
         D3 dir = p1 - p0;
         D3 org = p0 + dir * SMALL;
+        if (target == RT_NONE) {       // Infinite light: unoccluded(true) — visible iff NOTHING is hit over (0, INF) (hittable.rs:31-33)
+            tstate_init(st, stack, org, dir, 0., INF, true, INF, RT_NONE);
+            return true;
+        }
         DPrim prm = sc->prims[target];
         double t_l;
         if ((prm.info & 7u) == RT_PRIM_TRIANGLE) {
@@ -333,7 +360,15 @@ struct ConnectJob {
         }
         uint32_t k = i - n_shadow;
         uint32_t prim = st.best.prim;
-        if (prim == RT_NONE) return;
+        if (prim == RT_NONE) {         // the probe left the scene: `color = light.le(&new_ray)` — non-black only for an Infinite light
+            if (!sc->has_infinite) return;
+            const DLight& l = sc->lights[pr.target[k]];
+            if (l.type != RT_LIGHT_INFINITE) return;
+            D3 le = infinite_le(*sc, l, mk3(pr.bx[k], pr.by[k], pr.bz[k]));
+            if (is_black(le)) return;
+            film_add(film, pr.pixel[k], cmul(mk3(pr.cr[k], pr.cg[k], pr.cb[k]), le));
+            return;
+        }
         uint32_t li = sc->prims[prim].light;
         if (li == RT_NONE || li != pr.target[k]) return;           // `lights[index].eq(light)` (integrator.rs:621)
         D3 o = mk3(pr.ax[k], pr.ay[k], pr.az[k]), d = mk3(pr.bx[k], pr.by[k], pr.bz[k]);
@@ -513,6 +548,7 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
             if (s->bin_mask & (1u << (M * 2 + 1))) k_shade<R, M, 1><<<g128, 128, 0, st>>>(w.ctrl, s->d, rp, w.set[cur], w.set[cur ^ 1], w.bin_idx, w.shadow, w.probe, film->d);
 #define RT_SHADE_ALL(R) RT_SHADE(R, RT_MAT_MATTE) RT_SHADE(R, RT_MAT_LIGHT) RT_SHADE(R, RT_MAT_PLASTIC) RT_SHADE(R, RT_MAT_GLASS) RT_SHADE(R, RT_MAT_METAL) RT_SHADE(R, RT_MAT_MIRROR)
             if (f32) { RT_SHADE_ALL(float) } else { RT_SHADE_ALL(double) }
+            if (s->d.has_infinite) k_shade_miss<<<g128, 128, 0, st>>>(w.ctrl, s->d, rp, w.set[cur], w.bin_idx, film->d);
             cudaEventRecord(ev(w, n_ev + 3), st);
             k_connect<<<gtrace, 128, 0, st>>>(w.ctrl, s->d, w.shadow, w.probe, film->d);
             cudaEventRecord(ev(w, n_ev + 4), st);

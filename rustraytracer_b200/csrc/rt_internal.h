@@ -41,7 +41,20 @@ struct DMesh { uint64_t p_base, n_base, uv_base; };               // element (ve
 
 struct DXform { double fwd[16], inv[16]; };
 
-struct DLight { uint32_t prim, two_sided, pad0, pad1; double color[3]; double area; };
+// Diffuse: prim/two_sided/color/area.  Infinite (light.rs:69-79): text_id, to_world/to_obj = xforms[xform] (RT_NONE =
+// identity), and the Distribution2D of make_infinite_light (light.rs:608-638, distribution.rs:98-148) as flat device tables:
+//   dist_f    [nu*nv]      the luminance*sin(theta) image; row v's `func` is the SLICE f[v .. v+nu) (distribution.rs:120)
+//   dist_cdf  [nv*(nu+1)]  row v's normalised cdf
+//   row_int   [nv]         row v's func_int  (= the marginal's `func`)
+//   marg_cdf  [nv+1]       the marginal's normalised cdf ;  marg_int = the marginal's func_int
+struct DLight {
+    uint32_t prim, two_sided, type, text_id; double color[3]; double area;
+    uint32_t xform, nu, nv, pad; const double *dist_f, *dist_cdf, *row_int, *marg_cdf; double marg_int;
+};
+// texel storage of Hdr / Image textures: one u32 per texel.  Hdr: the RGBE8 quadruple AFTER the re-quantisation of
+// material.rs:578 (r | g<<8 | b<<16 | e<<24); Image: r | g<<8 | b<<16.
+struct DImage { uint64_t offset; uint32_t w, h; };
+constexpr double WORLD_RADIUS = 10000.0;   // light.rs:636
 
 // everything the kernels read; all pointers are device pointers
 struct DScene {
@@ -49,7 +62,9 @@ struct DScene {
     const double* points; const double* normals; const double* uvs; const uint32_t* tri_index;
     const double* shapes; const DXform* xforms;
     const rt_texture* textures; const rt_material* materials; const DLight* lights;
+    const DImage* images; const uint32_t* texels;
     uint32_t n_nodes, n_prims, n_lights, n_slots;
+    uint32_t has_infinite, pad0;              // any Light::Infinite in `lights` (misses then emit, light.rs:499-513)
 };
 
 struct Box64 { double mn[3], mx[3]; };

@@ -12,6 +12,8 @@ struct rt_scene {
     std::vector<rt_texture> textures;
     std::vector<rt_material> materials;
     std::vector<rt_light> lights;
+    std::vector<rt::DImage> images;          // Hdr / Image texel blocks (rt_scene_add_image_*)
+    std::vector<uint32_t> texels;
     // committed
     bool committed = false;
     int device = 0;
@@ -36,6 +38,8 @@ struct HostImage {
     std::vector<DNode> nodes; std::vector<DSlot> slots; std::vector<DPrim> prims; std::vector<DMesh> meshes;
     std::vector<double> points, normals, uvs, shapes; std::vector<uint32_t> tri_index;
     std::vector<DLight> lights;
+    // Infinite lights: flat Distribution2D tables, concatenated; DLight pointers hold OFFSETS (in doubles) until upload
+    std::vector<double> dist;
 };
 rt_status build_host_image(const rt_scene& s, HostImage& img);
 rt_status upload_scene(rt_scene& s, const HostImage& img);   // device.cu

@@ -95,6 +95,78 @@ double prim_area(const rt_scene& s, const HostPrim& p) {
     return (v[2] - v[0]) * (v[3] - v[1]);
 }
 
+// ---- textures on the host: the same lookups the device performs (shade.cuh tex_value), needed at commit by
+// Light::make_infinite_light (light.rs:608-638), which evaluates the environment texture into its sampling table.
+static inline uint32_t sat_u32(double x) {                    // Rust `f64 as u32`: saturating, NaN -> 0
+    if (!(x > 0.)) return 0u;
+    if (x >= 4294967295.) return 4294967295u;
+    return (uint32_t)x;
+}
+static void texel_rgb(const rt_scene& s, const rt_texture& t, double u, double v, double out[3]) {
+    const DImage& im = s.images[t.image];
+    if (t.type == RT_TEX_HDR) {                               // material.rs:570-587
+        uint32_t x = sat_u32(std::round((1. - u) * (double)im.w)) % im.w, y = sat_u32(std::round(v * (double)im.h)) % im.h;
+        uint32_t q = s.texels[im.offset + (size_t)y * im.w + x];
+        double sc = std::ldexp(1.0, (int)(q >> 24) - 128);    // 2f64.powi(e - 128)
+        for (int k = 0; k < 3; k++) out[k] = ((double)((q >> (8 * k)) & 255u) + 0.5) * sc / 256.;
+    } else {                                                  // material.rs:601-611
+        uint32_t x = sat_u32(std::round(u * (double)im.w)) % im.w, y = sat_u32(std::round((1. - v) * (double)im.h)) % im.h;
+        uint32_t q = s.texels[im.offset + (size_t)y * im.w + x];
+        for (int k = 0; k < 3; k++) out[k] = (double)((q >> (8 * k)) & 255u) / 255.;
+    }
+}
+static void host_tex_value(const rt_scene& s, uint32_t id, double u, double v, double out[3]) {   // material.rs:542-589
+    for (int depth = 0; depth < 8; depth++) {
+        const rt_texture& t = s.textures[id];
+        if (t.type == RT_TEX_SOLID) { out[0] = t.color[0]; out[1] = t.color[1]; out[2] = t.color[2]; return; }
+        if (t.type == RT_TEX_HDR || t.type == RT_TEX_IMAGE) { texel_rgb(s, t, u, v, out); return; }
+        double mult = std::sin(t.frequency * u * 2. * PI) * std::sin(t.frequency * v * 2. * PI);
+        id = mult < 0. ? t.even : t.odd;
+    }
+    out[0] = out[1] = out[2] = 0.;
+}
+// Distribution1D::make_distribution (distribution.rs:28-55) of f[0..n): writes the normalised cdf[0..n], returns func_int
+static double make_distribution_1d(const double* f, size_t n, double* cdf) {
+    cdf[0] = 0.;
+    for (size_t i = 1; i < n + 1; i++) cdf[i] = cdf[i - 1] + f[i - 1] / (double)n;
+    double func_int = cdf[n];
+    if (func_int == 0.) { for (size_t i = 1; i < n + 1; i++) cdf[i] = (double)i / (double)n; }
+    else { for (size_t i = 1; i < n + 1; i++) cdf[i] = cdf[i] / func_int; }
+    return func_int;
+}
+// Light::make_infinite_light (light.rs:608-638) + Distribution2D::make_distribution_2d (distribution.rs:117-130).
+// The pointers of `d` receive OFFSETS into `dist` (in doubles, +1 so that 0 stays "null"); upload_scene rebases them.
+static rt_status build_infinite_light(const rt_scene& s, const rt_light& l, DLight& d, std::vector<double>& dist) {
+    if (l.text_id >= s.textures.size()) { set_error("commit: infinite light texture out of range"); return RT_ERR_INVALID; }
+    if (l.transform != RT_NONE && l.transform >= s.xforms.size()) { set_error("commit: infinite light transform out of range"); return RT_ERR_INVALID; }
+    const rt_texture& t = s.textures[l.text_id];
+    // Texture::get_size (material.rs:591-599): Image/Hdr -> (w,h); SolidColor -> (1,1); Checkered -> (0,0)
+    uint32_t tw = 0, th = 0;
+    if (t.type == RT_TEX_HDR || t.type == RT_TEX_IMAGE) { tw = s.images[t.image].w; th = s.images[t.image].h; }
+    else if (t.type == RT_TEX_SOLID) { tw = th = 1; }
+    if (tw == 0 || th == 0) { set_error("commit: infinite light needs a sized texture (the reference's table would be empty)"); return RT_ERR_INVALID; }
+    size_t nu = (size_t)tw * 2, nv = (size_t)th * 2;
+    d.text_id = l.text_id; d.xform = l.transform; d.nu = (uint32_t)nu; d.nv = (uint32_t)nv;
+    size_t base = dist.size();
+    dist.resize(base + nu * nv + nv * (nu + 1) + nv + (nv + 1));
+    double* f = &dist[base]; double* cdf = f + nu * nv; double* row_int = cdf + nv * (nu + 1); double* mcdf = row_int + nv;
+    for (size_t v = 0; v < nv; v++) {
+        double vp = ((double)v + 0.5) / (double)nv;
+        double sin_theta = std::sin(PI * ((double)v + 0.5) / (double)nv);
+        for (size_t u = 0; u < nu; u++) {
+            double up = (double)u / (double)nu, c[3];
+            host_tex_value(s, l.text_id, up, vp, c);
+            double lum = 0.2126 * c[0] + 0.7152 * c[1] + 0.0722 * c[2];       // util::color_to_luminance (util.rs:169-171)
+            f[u + v * nu] = lum * sin_theta;
+        }
+    }
+    for (size_t v = 0; v < nv; v++) row_int[v] = make_distribution_1d(f + v, nu, cdf + v * (nu + 1));   // `&f[v..(v + nu)]` (distribution.rs:120)
+    d.marg_int = make_distribution_1d(row_int, nv, mcdf);
+    d.dist_f = (const double*)(uintptr_t)(base + 1); d.dist_cdf = (const double*)(uintptr_t)(base + nu * nv + 1);
+    d.row_int = (const double*)(uintptr_t)(base + nu * nv + nv * (nu + 1) + 1); d.marg_cdf = (const double*)(uintptr_t)(base + nu * nv + nv * (nu + 1) + nv + 1);
+    return RT_OK;
+}
+
 rt_status build_host_image(const rt_scene& s, HostImage& img) {
     size_t n = s.prims.size();
     // validate cross indices
@@ -109,7 +181,8 @@ rt_status build_host_image(const rt_scene& s, HostImage& img) {
         if (k < used && m.tex[k] == RT_NONE && !(m.type == RT_MAT_METAL && k >= 3)) { set_error("material: missing texture id"); return RT_ERR_INVALID; }
     }
     for (auto& t : s.textures) if (t.type == RT_TEX_CHECKERED && (t.odd >= s.textures.size() || t.even >= s.textures.size())) { set_error("checkered texture: id out of range"); return RT_ERR_INVALID; }
-    for (auto& l : s.lights) if (l.prim_index >= n) { set_error("light: prim_index out of range"); return RT_ERR_INVALID; }
+    for (auto& l : s.lights) if (l.type == RT_LIGHT_DIFFUSE && l.prim_index >= n) { set_error("light: prim_index out of range"); return RT_ERR_INVALID; }
+    for (auto& t : s.textures) if ((t.type == RT_TEX_HDR || t.type == RT_TEX_IMAGE) && t.image >= s.images.size()) { set_error("texture: image index out of range"); return RT_ERR_INVALID; }
     // meshes → concatenated f64 arrays
     img.meshes.resize(s.meshes.size());
     std::vector<uint64_t> idx_base(s.meshes.size());
@@ -184,9 +257,17 @@ rt_status build_host_image(const rt_scene& s, HostImage& img) {
     img.lights.resize(s.lights.size());
     for (size_t i = 0; i < s.lights.size(); i++) {
         DLight d; memset(&d, 0, sizeof(d));
-        d.prim = s.lights[i].prim_index; d.two_sided = s.lights[i].two_sided;
-        for (int k = 0; k < 3; k++) d.color[k] = s.lights[i].color[k];
-        d.area = prim_area(s, s.prims[d.prim]);              // light.rs:603
+        const rt_light& l = s.lights[i];
+        d.type = l.type;
+        if (l.type == RT_LIGHT_DIFFUSE) {
+            if (l.prim_index >= s.prims.size()) { set_error("commit: light primitive out of range"); return RT_ERR_INVALID; }
+            d.prim = l.prim_index; d.two_sided = l.two_sided;
+            for (int k = 0; k < 3; k++) d.color[k] = l.color[k];
+            d.area = prim_area(s, s.prims[d.prim]);          // light.rs:603
+        } else {
+            rt_status st = build_infinite_light(s, l, d, img.dist);
+            if (st != RT_OK) return st;
+        }
         img.lights[i] = d;
     }
     return RT_OK;
@@ -295,8 +376,50 @@ rt_status rt_scene_set_light_index(rt_scene* s, uint32_t prim, uint32_t light) {
 }
 rt_status rt_scene_set_textures(rt_scene* s, uint64_t n, const rt_texture* t) {
     if (!s || (n && !t)) { set_error("rt_scene_set_textures: null argument"); return RT_ERR_INVALID; }
-    for (uint64_t i = 0; i < n; i++) if (t[i].type > RT_TEX_CHECKERED) { set_error("rt_scene_set_textures: unsupported texture type"); return RT_ERR_INVALID; }
+    for (uint64_t i = 0; i < n; i++) {
+        if (t[i].type > RT_TEX_IMAGE) { set_error("rt_scene_set_textures: unsupported texture type"); return RT_ERR_INVALID; }
+        if (t[i].type == RT_TEX_CHECKERED && (t[i].odd >= n || t[i].even >= n)) { set_error("rt_scene_set_textures: checkered texture id out of range"); return RT_ERR_INVALID; }
+        if ((t[i].type == RT_TEX_HDR || t[i].type == RT_TEX_IMAGE) && t[i].image >= s->images.size()) { set_error("rt_scene_set_textures: image index out of range (add images first)"); return RT_ERR_INVALID; }
+    }
     s->textures.assign(t, t + n); s->committed = false; return RT_OK;
+}
+// Texture::new_hdr (material.rs:626-642).  `data: Vec<Rgb<f32>>` is what image 0.23's HdrDecoder::read_image_hdr returns;
+// Texture::get_value re-quantises the texel with image::hdr::to_rgbe8 on every lookup (material.rs:578) — a pure function
+// of the texel, so it is applied once here (image 0.23.12, src/codecs/hdr/decoder.rs `to_rgbe8`: mx = max(r,g,b);
+// mx <= 0 -> (0,0,0,0); else exp = floor(log2(mx)) + 1, c = trunc(v / 2^exp * 256) as u8, e = exp + 128).
+rt_status rt_scene_add_image_hdr(rt_scene* s, uint32_t w, uint32_t h, const float* rgb, uint32_t* out) {
+    if (!s || !rgb || !w || !h) { set_error("rt_scene_add_image_hdr: bad argument"); return RT_ERR_INVALID; }
+    DImage im; im.offset = s->texels.size(); im.w = w; im.h = h;
+    s->texels.resize(im.offset + (size_t)w * h);
+    for (size_t i = 0; i < (size_t)w * h; i++) {
+        const float* p = rgb + 3 * i;
+        float mx = std::fmax(p[0], std::fmax(p[1], p[2]));
+        uint32_t q = 0;
+        if (mx > 0.0f) {
+            int e = (int)std::floor(std::log2(mx)) + 1;
+            float mul = std::ldexp(1.0f, e);                       // f32::powi(2.0, exp)
+            for (int k = 0; k < 3; k++) {
+                float c = std::trunc(p[k] / mul * 256.0f);
+                uint32_t cu = !(c > 0.0f) ? 0u : (c >= 255.0f ? 255u : (uint32_t)c);   // `as u8` saturates
+                q |= cu << (8 * k);
+            }
+            q |= ((uint32_t)(e + 128) & 255u) << 24;             // `(exp + 128) as u8` wraps
+        }
+        s->texels[im.offset + i] = q;
+    }
+    s->images.push_back(im); s->committed = false;
+    if (out) *out = (uint32_t)s->images.size() - 1;
+    return RT_OK;
+}
+// Texture::new_texture (material.rs:613-616)
+rt_status rt_scene_add_image_rgb8(rt_scene* s, uint32_t w, uint32_t h, const uint8_t* rgb, uint32_t* out) {
+    if (!s || !rgb || !w || !h) { set_error("rt_scene_add_image_rgb8: bad argument"); return RT_ERR_INVALID; }
+    DImage im; im.offset = s->texels.size(); im.w = w; im.h = h;
+    s->texels.resize(im.offset + (size_t)w * h);
+    for (size_t i = 0; i < (size_t)w * h; i++) s->texels[im.offset + i] = (uint32_t)rgb[3 * i] | ((uint32_t)rgb[3 * i + 1] << 8) | ((uint32_t)rgb[3 * i + 2] << 16);
+    s->images.push_back(im); s->committed = false;
+    if (out) *out = (uint32_t)s->images.size() - 1;
+    return RT_OK;
 }
 rt_status rt_scene_set_materials(rt_scene* s, uint64_t n, const rt_material* m) {
     if (!s || (n && !m)) { set_error("rt_scene_set_materials: null argument"); return RT_ERR_INVALID; }
@@ -305,7 +428,7 @@ rt_status rt_scene_set_materials(rt_scene* s, uint64_t n, const rt_material* m) 
 }
 rt_status rt_scene_set_lights(rt_scene* s, uint64_t n, const rt_light* l) {
     if (!s || (n && !l)) { set_error("rt_scene_set_lights: null argument"); return RT_ERR_INVALID; }
-    for (uint64_t i = 0; i < n; i++) if (l[i].type != RT_LIGHT_DIFFUSE) { set_error("rt_scene_set_lights: unsupported light type"); return RT_ERR_INVALID; }
+    for (uint64_t i = 0; i < n; i++) if (l[i].type > RT_LIGHT_INFINITE) { set_error("rt_scene_set_lights: unsupported light type"); return RT_ERR_INVALID; }
     s->lights.assign(l, l + n); s->committed = false; return RT_OK;
 }
 rt_status rt_scene_commit(rt_scene* s) {

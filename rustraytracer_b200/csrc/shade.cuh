@@ -401,12 +401,26 @@ template <class R, uint32_t KM> static __device__ __noinline__ void bsdf_sample_
 }
 
 // ---- material.rs
-// Texture::value (material.rs:542-589): SolidColor, Checkered (ids may nest).  Always f64: the checker's
+// Texture::value (material.rs:542-589): SolidColor, Checkered (ids may nest), Hdr, Image.  Always f64: the checker's
 // sin(frequency*u*2π) argument reaches ~3e4 rad in plastic_dragon and decides which colour a point gets.
+__device__ __forceinline__ uint32_t sat_u32(double x) { return !(x > 0.) ? 0u : (x >= 4294967295. ? 4294967295u : (uint32_t)x); }   // Rust `f64 as u32`
+static __device__ __noinline__ D3 texel_value(const DScene& sc, const rt_texture& t, double u, double v) {
+    const DImage im = sc.images[t.image];
+    if (t.type == RT_TEX_HDR) {              // nearest texel, RGBE8 re-quantised at upload, (c+0.5)*2^(e-128)/256 (material.rs:570-587)
+        uint32_t x = sat_u32(round((1. - u) * (double)im.w)) % im.w, y = sat_u32(round(v * (double)im.h)) % im.h;
+        uint32_t q = __ldg(sc.texels + im.offset + (size_t)y * im.w + x);
+        double scale = __hiloint2double((int)(((q >> 24) - 128u + 1023u) << 20), 0);     // 2^(e-128), exact
+        return mk3(((double)(q & 255u) + 0.5) * scale / 256., ((double)((q >> 8) & 255u) + 0.5) * scale / 256., ((double)((q >> 16) & 255u) + 0.5) * scale / 256.);
+    }
+    uint32_t x = sat_u32(round(u * (double)im.w)) % im.w, y = sat_u32(round((1. - v) * (double)im.h)) % im.h;      // material.rs:601-611
+    uint32_t q = __ldg(sc.texels + im.offset + (size_t)y * im.w + x);
+    return mk3((double)(q & 255u) / 255., (double)((q >> 8) & 255u) / 255., (double)((q >> 16) & 255u) / 255.);
+}
 static __device__ __noinline__ D3 tex_value(const DScene& sc, uint32_t id, double u, double v) {
     for (int depth = 0; depth < 8; depth++) {
         const rt_texture& t = sc.textures[id];
-        if (t.type != RT_TEX_CHECKERED) return mk3(t.color[0], t.color[1], t.color[2]);
+        if (t.type == RT_TEX_SOLID) return mk3(t.color[0], t.color[1], t.color[2]);
+        if (t.type != RT_TEX_CHECKERED) return texel_value(sc, t, u, v);
         double mult = sin(t.frequency * u * 2. * PI) * sin(t.frequency * v * 2. * PI);
         id = mult < 0. ? t.even : t.odd;
     }
@@ -546,6 +560,66 @@ static __device__ __noinline__ void sample_area(const DScene& sc, uint32_t prim,
         }
     }
     if (pr.info & PI_FLIP) n = -n;
+}
+
+// ---- light.rs Infinite + distribution.rs — f64 in both modes (directions and pdfs of light samples)
+constexpr double INV_PI_C = 1.0 / PI, INV_2PI_C = 1.0 / (2.0 * PI);           // consts.rs:41-42
+// find_interval (distribution.rs:150-166) with pred = |i| cdf[i] <= u
+__device__ __forceinline__ uint32_t find_interval_cdf(const double* __restrict__ cdf, uint32_t size, double u) {
+    uint32_t first = 0, len = size;
+    while (len > 0) {
+        uint32_t half = len >> 1, middle = first + half;
+        if (__ldg(cdf + middle) <= u) { first = middle + 1; len = len - half - 1; } else len = half;
+    }
+    double c = clampd((double)first - 1., 0., (double)size - 2.);            // cdf[0] = 0 <= u, so first >= 1
+    return (uint32_t)c;
+}
+// Distribution1D::sample_continuous (distribution.rs:64-78): cdf[0..n], func[i] = func[i * 1], → x, pdf, offset
+__device__ __forceinline__ void dist1d_sample(const double* __restrict__ cdf, const double* __restrict__ func, uint32_t n, double func_int, double u, double& x, double& pdf, uint32_t& offset) {
+    offset = find_interval_cdf(cdf, n + 1, u);
+    double c0 = __ldg(cdf + offset), c1 = __ldg(cdf + offset + 1);
+    double du = u - c0;
+    if (c1 - c0 > 0.) du = du / (c1 - c0);
+    pdf = func_int > 0. ? __ldg(func + offset) / func_int : 0.;
+    x = ((double)offset + du) / (double)n;
+}
+__device__ __forceinline__ D3 light_to_world(const DScene& sc, const DLight& l, D3 v) { return l.xform == RT_NONE ? v : xf_vector(sc.xforms[l.xform].fwd, v); }
+__device__ __forceinline__ D3 light_to_obj(const DScene& sc, const DLight& l, D3 v) { return l.xform == RT_NONE ? v : xf_vector(sc.xforms[l.xform].inv, v); }
+__device__ __forceinline__ double spherical_theta(D3 v) { return acos(clampd(v.y, -1., 1.)); }                 // util.rs:153-155
+__device__ __forceinline__ double spherical_phi(D3 v) { double p = atan2(v.z, v.x); return p < 0. ? p + 2. * PI : p; }   // util.rs:160-167
+// Light::sample_li, Infinite arm (light.rs:204-245): → wi (normalised), pdf, colour, shadow-ray end point
+static __device__ __noinline__ void infinite_sample_li(const DScene& sc, const DLight& l, D3 p, D2 u, D3& wi, double& pdf, D3& color, D3& p1) {
+    // Distribution2D::sample_continuous (distribution.rs:135-139): marginal with u[1], then row v with u[0]
+    double d1, pdf1, d0, pdf0; uint32_t v, off;
+    dist1d_sample(l.marg_cdf, l.row_int, l.nv, l.marg_int, u.y, d1, pdf1, v);
+    dist1d_sample(l.dist_cdf + (size_t)v * (l.nu + 1), l.dist_f + v, l.nu, __ldg(l.row_int + v), u.x, d0, pdf0, off);   // row v's func is f[v..v+nu)
+    double map_pdf = pdf1 * pdf0;
+    wi = mk3(0., 0., 0.); color = mk3(0., 0., 0.); p1 = p; pdf = 0.;
+    if (map_pdf == 0.) return;
+    double theta = d1 * PI, phi = d0 * 2. * PI;
+    double cos_theta = cos(theta), sin_theta = sin(theta), cos_phi = cos(phi), sin_phi = sin(phi);
+    D3 w = light_to_world(sc, l, mk3(sin_theta * cos_phi, sin_theta * sin_phi, cos_theta));      // Z-up here, Y-up in le/pdf_li (§8.1 #14)
+    pdf = map_pdf / (2. * PI * PI * sin_theta);
+    if (sin_theta == 0.) pdf = 0.;
+    p1 = p + w * (2. * WORLD_RADIUS);
+    color = tex_value(sc, l.text_id, d0, d1);
+    wi = normalize(w);
+}
+// Light::pdf_li, Infinite arm (light.rs:285-294) — transforms with to_world, as the reference does
+static __device__ __noinline__ double infinite_pdf_li(const DScene& sc, const DLight& l, D3 wi) {
+    D3 w = light_to_world(sc, l, wi);
+    double theta = spherical_theta(w), phi = spherical_phi(w);
+    double sin_theta = sin(theta);
+    if (sin_theta == 0.) return 0.;
+    // Distribution2D::pdf (distribution.rs:141-147)
+    double pu = phi * INV_2PI_C, pv = theta * INV_PI_C;
+    uint32_t iu = min(sat_u32(pu * (double)l.nu), l.nu - 1u), iv = min(sat_u32(pv * (double)l.nv), l.nv - 1u);
+    return (__ldg(l.dist_f + iv + iu) / l.marg_int) / (2. * PI * PI * sin_theta);
+}
+// Light::le (light.rs:499-513): radiance along a ray that leaves the scene
+static __device__ __noinline__ D3 infinite_le(const DScene& sc, const DLight& l, D3 ray_d) {
+    D3 w = normalize(light_to_obj(sc, l, ray_d));
+    return tex_value(sc, l.text_id, spherical_phi(w) * INV_2PI_C, spherical_theta(w) * INV_PI_C);
 }
 
 }  // namespace rt

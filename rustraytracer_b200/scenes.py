@@ -74,7 +74,16 @@ class HostScene:
         lig = np.zeros(cnt["lights"], dtype=N.light_dtype)
         if len(lig):
             check(lib().rth_scene_copy_lights(self.h, ptr(lig)))
-        return dict(meshes=meshes, prims=prims, transforms=xf, textures=tex, materials=mat, lights=lig)
+        images = []
+        n_img = C.c_uint64()
+        check(lib().rth_scene_num_images(self.h, C.byref(n_img)))
+        for i in range(n_img.value):
+            info = (C.c_uint32 * 3)()
+            check(lib().rth_scene_image_info(self.h, i, info))
+            px = np.zeros((info[1], info[0], 3), dtype=np.float32 if info[2] else np.uint8)
+            check(lib().rth_scene_image_copy(self.h, i, ptr(px)))
+            images.append(px)
+        return dict(meshes=meshes, prims=prims, transforms=xf, textures=tex, materials=mat, lights=lig, images=images)
 
     def upload(self, commit=True):
         """Push the tables through the public rt_scene_* ABI and commit (BVH build + device upload)."""
@@ -113,6 +122,10 @@ def plastic_dragon(width=720, height=720, spp=50, seed=0, variant=0, data_dir=No
 
 def two_dragons(width=720, height=720, spp=50, seed=0, variant=1, data_dir=None):                   # scenes.rs:549
     return _scene_kw("two_dragons", width, height, spp, seed, dict(variant=variant, data_dir=data_dir))
+
+
+def material_hdr(mat_num=0, width=720, height=720, spp=50, seed=0, data_dir=None):                   # scenes.rs:627
+    return _scene_kw("material_hdr", width, height, spp, seed, dict(variant=mat_num, data_dir=data_dir))
 
 
 def soup(n_tris, width=4096, height=4096, seed=0):

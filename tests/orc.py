@@ -52,6 +52,15 @@ def lib():
         L.orc_fr_dielectric.argtypes = [f64, f64, f64]
         L.orc_fr_dielectric.restype = f64
         L.orc_fr_conductor.argtypes = [f64, vp, vp, vp]
+        L.orc_scene_add_image_hdr.argtypes = [vp, u32, u32, vp]
+        L.orc_scene_add_image_hdr.restype = u32
+        L.orc_scene_add_image_rgb8.argtypes = [vp, u32, u32, vp]
+        L.orc_scene_add_image_rgb8.restype = u32
+        L.orc_light_sample_li.argtypes = [vp, u32, vp, vp, vp]
+        L.orc_light_pdf_li.argtypes = [vp, u32, vp, vp]
+        L.orc_light_pdf_li.restype = f64
+        L.orc_light_le.argtypes = [vp, u32, vp, vp]
+        L.orc_light_dist.argtypes = [vp, u32, vp, vp, vp, vp, vp]
         _lib = L
     return _lib
 
@@ -88,6 +97,11 @@ class OracleScene:
         prims = np.ascontiguousarray(t["prims"], dtype=N.prim_dtype)
         if len(prims):
             L.orc_scene_add_primitives(self.h, len(prims), _p(prims))
+        for im in t.get("images", []):
+            if im.dtype == np.uint8:
+                im = np.ascontiguousarray(im); L.orc_scene_add_image_rgb8(self.h, im.shape[1], im.shape[0], _p(im))
+            else:
+                im = np.ascontiguousarray(im, dtype=np.float32); L.orc_scene_add_image_hdr(self.h, im.shape[1], im.shape[0], _p(im))
         tex = np.ascontiguousarray(t["textures"], dtype=N.texture_dtype)
         L.orc_scene_set_textures(self.h, len(tex), _p(tex) if len(tex) else None)
         mat = np.ascontiguousarray(t["materials"], dtype=N.material_dtype)
@@ -100,6 +114,29 @@ class OracleScene:
 
     def num_primitives(self):
         return lib().orc_scene_num_primitives(self.h)
+
+    # ---- Infinite-light probes (light.rs:204-245, 285-294, 499-513; distribution.rs)
+    def light_sample_li(self, light, p, u):
+        p = np.ascontiguousarray(p, dtype=np.float64); u = np.ascontiguousarray(u, dtype=np.float64); out = np.zeros(10)
+        lib().orc_light_sample_li(self.h, light, _p(p), _p(u), _p(out))
+        return dict(wi=out[0:3], pdf=out[3], color=out[4:7], p1=out[7:10])
+
+    def light_pdf_li(self, light, p, wi):
+        p = np.ascontiguousarray(p, dtype=np.float64); wi = np.ascontiguousarray(wi, dtype=np.float64)
+        return lib().orc_light_pdf_li(self.h, light, _p(p), _p(wi))
+
+    def light_le(self, light, d):
+        d = np.ascontiguousarray(d, dtype=np.float64); out = np.zeros(3)
+        lib().orc_light_le(self.h, light, _p(d), _p(out))
+        return out
+
+    def light_dist(self, light):
+        n = np.zeros(2, dtype=np.uint64)
+        lib().orc_light_dist(self.h, light, _p(n), None, None, None, None)
+        nu, nv = int(n[0]), int(n[1])
+        cdf = np.zeros((nv, nu + 1)); row_int = np.zeros(nv); mcdf = np.zeros(nv + 1); mint = np.zeros(1)
+        lib().orc_light_dist(self.h, light, _p(n), _p(cdf), _p(row_int), _p(mcdf), _p(mint))
+        return dict(nu=nu, nv=nv, cdf=cdf, row_int=row_int, marg_cdf=mcdf, marg_int=float(mint[0]))
 
     def prim_box(self, i):
         out = np.zeros(6)
@@ -169,7 +206,7 @@ def resolve_rgb8(film):
     return out
 
 
-def simple_tables(prims, textures=None, materials=None, lights=None, meshes=(), transforms=()):
+def simple_tables(prims, textures=None, materials=None, lights=None, meshes=(), transforms=(), images=()):
     """Plain tables for hand-built KAT scenes."""
     if textures is None:
         textures = np.zeros(1, dtype=N.texture_dtype); textures[0]["color"] = (0.5, 0.5, 0.5)
@@ -178,7 +215,7 @@ def simple_tables(prims, textures=None, materials=None, lights=None, meshes=(), 
     if lights is None:
         lights = np.zeros(0, dtype=N.light_dtype)
     return dict(meshes=list(meshes), prims=np.asarray(prims, dtype=N.prim_dtype), transforms=np.asarray(transforms, dtype=np.float64).reshape(-1, 16),
-                textures=textures, materials=materials, lights=lights)
+                textures=textures, materials=materials, lights=lights, images=list(images))
 
 
 def prim(ptype, v, mat=0, flip=0, light=N.RT_NONE, mesh=0, ind=0, xf=N.RT_NONE):
@@ -196,6 +233,8 @@ def upload_tables(t):
         o.add_mesh(p, n, uv, ind)
     for m in t["transforms"]:
         o.add_transform(m)
+    for im in t.get("images", []):
+        o.add_image_rgb8(im) if im.dtype == np.uint8 else o.add_image_hdr(im)
     o.set_textures(t["textures"]); o.set_materials(t["materials"]); o.set_lights(t["lights"])
     if len(t["prims"]):
         o.add_primitives(t["prims"])

@@ -88,7 +88,7 @@ def test_empty_and_single_primitive_scenes():
     compare_hits(get_intersection(gpu, rays), oracle.intersect(rays, mode=1), None, "single sphere")
 
 
-@pytest.mark.parametrize("name", ["sphere_roughness", "cornell_box", "make_world"])
+@pytest.mark.parametrize("name", ["sphere_roughness", "cornell_box", "make_world", "material_hdr"])
 def test_builtin_scene_rays(name):
     hs = scenes.HostScene(name, 128, 128)
     gpu = hs.upload()
@@ -194,7 +194,9 @@ def film_compare(g, o, what, tol=1e-7, max_bad=2e-3):
 
 @pytest.mark.parametrize("name,kw,depth", [("sphere_roughness", {}, 25), ("cornell_box", {}, 25), ("make_world", {}, 16),
                                            ("plastic_dragon", {}, 8), ("plastic_dragon", {"variant": 1}, 8), ("two_dragons", {"variant": 1}, 16),
-                                           ("cornell_box_statue", {"n_tris": 20000}, 8)])
+                                           ("cornell_box_statue", {"n_tris": 20000}, 8),
+                                           ("material_hdr", {"variant": 0}, 8), ("material_hdr", {"variant": 1}, 8),
+                                           ("material_hdr", {"variant": 2}, 8), ("material_hdr", {"variant": 3}, 12)])
 def test_render_matches_oracle_per_pixel(name, kw, depth):
     w = h = 48
     spp = 4
@@ -264,7 +266,8 @@ def test_image_relmse_against_converged_oracle():
 
 
 @pytest.mark.parametrize("name,kw,depth", [("sphere_roughness", {}, 25), ("cornell_box", {}, 25), ("plastic_dragon", {}, 8),
-                                           ("plastic_dragon", {"variant": 1}, 8), ("two_dragons", {"variant": 1}, 16)])
+                                           ("plastic_dragon", {"variant": 1}, 8), ("two_dragons", {"variant": 1}, 16),
+                                           ("material_hdr", {"variant": 0}, 8), ("material_hdr", {"variant": 3}, 12)])
 def test_f32_shading_mode_against_oracle(name, kw, depth):
     """RT_SHADE_F32 (production mode): same formulas in f32, geometry still f64-exact.  Same RNG streams as the
     oracle, so most pixels agree to f32 rounding (1e-3 rel here); knife-edge branches flip more often than in f64
@@ -300,3 +303,74 @@ def test_f32_image_relmse_against_converged_oracle():
     print(f"f32 relMSE gpu {rel(G):.4g} oracle {rel(O):.4g}; means {G.mean():.5g} {O.mean():.5g} {R.mean():.5g}")
     assert rel(G) <= 1.5 * rel(O)
     assert abs(G.mean() - R.mean()) <= 0.05 * R.mean()
+
+
+def mixed_light_tables():
+    """Hand-built scene for SURVEY §8a rows 15/19/20 together: an Image-textured matte floor, a mirror and a glass
+    sphere, a rect area light AND a rotated Infinite light whose environment is an Image texture."""
+    rng = np.random.default_rng(11)
+    env = rng.integers(0, 256, (16, 32, 3), dtype=np.uint8); env[2:5, 6:9] = 255
+    tile = rng.integers(0, 256, (8, 8, 3), dtype=np.uint8)
+    a = 0.7
+    rot = [np.cos(a), -np.sin(a), 0, 0, np.sin(a), np.cos(a), 0, 0, 0, 0, 1, 0, 0, 0, 0, 1]      # env rotated about z
+    tex = np.zeros(5, dtype=N.texture_dtype)
+    tex[0]["type"] = N.TEX_IMAGE; tex[0]["image"] = 0            # environment
+    tex[1]["type"] = N.TEX_IMAGE; tex[1]["image"] = 1            # floor
+    tex[2]["color"] = (1, 1, 1); tex[3]["color"] = (0.9, 0.6, 0.2); tex[4]["color"] = (0, 0, 0)
+    mat = np.zeros(4, dtype=N.material_dtype); mat["tex"] = N.RT_NONE
+    mat[0]["type"] = N.MAT_MATTE; mat[0]["tex"][0] = 1
+    mat[1]["type"] = N.MAT_MIRROR; mat[1]["tex"][0] = 2
+    mat[2]["type"] = N.MAT_GLASS; mat[2]["tex"][0] = 2; mat[2]["tex"][1] = 2; mat[2]["f"] = (0.0, 0.0, 1.5)
+    mat[3]["type"] = N.MAT_MATTE; mat[3]["tex"][0] = 3; mat[3]["f"][0] = 20.0     # Oren-Nayar lamp housing
+    lig = np.zeros(2, dtype=N.light_dtype)
+    lig[0]["type"] = N.LIGHT_DIFFUSE; lig[0]["prim_index"] = 3; lig[0]["two_sided"] = 0; lig[0]["color"] = (6, 5, 4); lig[0]["transform"] = N.RT_NONE
+    lig[1]["type"] = N.LIGHT_INFINITE; lig[1]["prim_index"] = N.RT_NONE; lig[1]["text_id"] = 0; lig[1]["transform"] = 0
+    prims = [orc.prim(N.PRIM_XZ_RECT, [-6, -6, 6, 6, 0.0], mat=0), orc.prim(N.PRIM_SPHERE, [-1.2, 1.0, 0.0, 1.0], mat=1),
+             orc.prim(N.PRIM_SPHERE, [1.2, 1.0, 0.3, 1.0], mat=2), orc.prim(N.PRIM_XZ_RECT, [-1, -1, 1, 1, 4.0], mat=3, flip=1, light=0)]
+    return orc.simple_tables(prims, textures=tex, materials=mat, lights=lig, transforms=[rot], images=[env, tile])
+
+
+@pytest.mark.parametrize("f32", [False, True])
+def test_infinite_plus_area_light_image_textures(f32):
+    from rustraytracer_b200 import Camera
+    t = mixed_light_tables()
+    oracle = orc.OracleScene(t)
+    gpu = orc.upload_tables(t); gpu.commit()
+    w = h = 64
+    cam = Camera.new((0.5, 2.5, -7.0), (0.0, 1.0, 0.0), (0, 1, 0), 1.0, 45.0, 0.0, 10.0)
+    film = Film(w, h)
+    render_samples(gpu, cam, IntType.Path(10, shade_f32=f32), film, w, h, 0, 4, seed=9)
+    g = film.read()
+    o, counts, _ = oracle.render(cam, w, h, 0, 4, seed=9, max_depth=10)
+    assert o[..., :3].mean() > 0.05
+    if f32:
+        film_compare(g, o, "mixed lights f32", tol=1e-3, max_bad=0.03)
+    else:
+        film_compare(g, o, "mixed lights")
+    c = gpu.counters()
+    for k, v in zip(("extend_rays", "shadow_rays", "probe_rays"), counts):
+        assert abs(c[k] - int(v)) <= 0.01 * int(v) + 16, (k, c[k], int(v))
+    # rays that leave the scene see the environment: the background of the image is not black
+    assert (g[:8, :, :3].sum(axis=-1) > 0).mean() > 0.9
+
+
+def test_unoccluded_infinite_matches_oracle():
+    hs = scenes.HostScene("material_hdr", 64, 64)
+    gpu = hs.upload()
+    oracle = orc.OracleScene(hs.tables())
+    cam = hs.camera()
+    hits = oracle.intersect(cam.primary_rays(64, 64), mode=1)
+    hit = hits["prim_index"] != NONE
+    p0 = hits["p"][hit]
+    rng = np.random.default_rng(4)
+    d = rng.normal(size=p0.shape); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    # |p1 - p0| = 2e4 in the integrator, which pushes the origin 20 units — past this whole scene (§8.1 #14); a shorter
+    # segment keeps the query interesting: origin pushed 0.05 units, hits anywhere beyond count as occluders
+    p1 = p0 + d * 50.0
+    want = oracle.occluded(p0, p1, np.zeros(len(p0), dtype=np.uint32), infinite=True)
+    got = unoccluded(gpu, p0, p1, np.zeros(len(p0), dtype=np.uint32), infinite_light=True)
+    assert np.array_equal(got, want)
+    assert 0.1 < want.mean() < 0.95
+    far = p0 + d * 20000.0
+    assert np.array_equal(unoccluded(gpu, p0, far, np.zeros(len(p0), dtype=np.uint32), infinite_light=True),
+                          oracle.occluded(p0, far, np.zeros(len(p0), dtype=np.uint32), infinite=True))

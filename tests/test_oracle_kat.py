@@ -236,3 +236,107 @@ def test_tree_modes_agree_on_random_scene():
     s2 = orc.OracleScene(orc.simple_tables(prims, meshes=[mesh]), bvh_seed=99)
     h3 = s2.intersect(rays, mode=0)
     assert np.array_equal(h3["prim_index"], h0["prim_index"]) or np.all((h3["prim_index"] == h0["prim_index"]) | (h3["t"] == h0["t"]))
+
+
+# ---------------------------------------------------------------- Hdr / Image textures, Distribution, Light::Infinite
+def env_tables(img, tex_type=N.TEX_HDR, prims=(), transform=None):
+    """One environment texture (id 0) + a grey matte (texture 1, material 0) + one Infinite light."""
+    tex = np.zeros(2, dtype=N.texture_dtype)
+    tex[0]["type"] = tex_type; tex[0]["image"] = 0
+    tex[1]["color"] = (0.5, 0.5, 0.5)
+    mat = np.zeros(1, dtype=N.material_dtype); mat[0]["tex"] = N.RT_NONE; mat[0]["tex"][0] = 1
+    lig = np.zeros(1, dtype=N.light_dtype)
+    lig[0]["type"] = N.LIGHT_INFINITE; lig[0]["prim_index"] = N.RT_NONE; lig[0]["text_id"] = 0
+    lig[0]["transform"] = N.RT_NONE if transform is None else 0
+    return orc.simple_tables(list(prims), textures=tex, materials=mat, lights=lig, images=[img],
+                             transforms=[] if transform is None else [transform])
+
+
+def test_hdr_texture_requantisation_and_lookup():
+    # 2x2 Hdr image; material.rs:570-587: x = round((1-u)*W) % W, y = round(v*H) % H, to_rgbe8, (c+0.5)*2^(e-128)/256
+    img = np.zeros((2, 2, 3), dtype=np.float32)
+    img[0, 0] = (1.0, 0.5, 0.25)        # mx = 1 -> exp = floor(log2 1)+1 = 1, mul = 2, c = (128, 64, 32), e = 129
+    img[0, 1] = (0.75, 0.75, 0.75)      # mx = .75 -> exp = 0, mul = 1, c = 192, e = 128
+    img[1, 0] = (0.0, 0.0, 0.0)         # mx <= 0 -> (0,0,0,0) -> (0.5) * 2^-128 / 256
+    img[1, 1] = (3.0, 100.0, 7.0)       # mx = 100 -> exp = 7, mul = 128, c = (6, 200, 14), e = 135
+    s = orc.OracleScene(env_tables(img))
+    # u = 1 -> x = round(0) = 0 ; v = 0 -> y = 0
+    assert np.array_equal(s.tex_value(0, 1.0, 0.0), [128.5 * 2 / 256, 64.5 * 2 / 256, 32.5 * 2 / 256])
+    # u = 0.5 -> x = round(1.0) = 1
+    assert np.array_equal(s.tex_value(0, 0.5, 0.0), [192.5 / 256] * 3)
+    # u = 0 -> x = round(2) % 2 = 0 ; v = 0.5 -> y = 1
+    assert np.array_equal(s.tex_value(0, 0.0, 0.5), [0.5 * 2.0 ** -128 / 256] * 3)
+    # u = 0.26 -> (1-u)*2 = 1.48 -> 1 ; v = 0.74 -> 1.48 -> 1 ; v = 0.76 -> 1.52 -> 2 % 2 = 0
+    assert np.array_equal(s.tex_value(0, 0.26, 0.74), [6.5 * 128 / 256, 200.5 * 128 / 256, 14.5 * 128 / 256])
+    assert np.array_equal(s.tex_value(0, 0.26, 0.76), [192.5 / 256] * 3)
+    # out-of-range coordinates: `as u32` saturates negatives to 0; large values wrap by the modulo
+    assert np.array_equal(s.tex_value(0, 1.7, -0.3), s.tex_value(0, 1.0, 0.0))
+
+
+def test_image_texture_lookup():
+    # material.rs:601-611: x = round(u*W) % W, y = round((1-v)*H) % H, c / 255
+    img = np.arange(2 * 3 * 3, dtype=np.uint8).reshape(2, 3, 3) * 10
+    s = orc.OracleScene(env_tables(img, tex_type=N.TEX_IMAGE))
+    assert np.array_equal(s.tex_value(0, 0.0, 1.0), img[0, 0] / 255.0)
+    assert np.array_equal(s.tex_value(0, 0.4, 0.6), img[1, 1] / 255.0)      # round(1.2) = 1 ; round(0.8) = 1
+    assert np.array_equal(s.tex_value(0, 0.9, 0.0), img[0, 0] / 255.0)      # round(2.7) = 3 % 3 = 0 ; round(2) % 2 = 0
+
+
+def test_distribution_row_slicing_and_sampling():
+    # A 1x1 SolidColor-like case is degenerate, so use a 1x2 Hdr image -> table 2x4 (nu = 2, nv = 4).
+    img = np.zeros((2, 1, 3), dtype=np.float32); img[0, 0] = (1, 1, 1); img[1, 0] = (0.5, 0.5, 0.5)
+    s = orc.OracleScene(env_tables(img))
+    d = s.light_dist(0)
+    assert (d["nu"], d["nv"]) == (2, 4)
+    # f[u + v*2] = lum(texel(v)) * sin(PI*(v+.5)/4), texel row = round(vp*2) % 2 with vp = (v+.5)/4 -> rows 0,1,1,0
+    PI = 3.14159265358979
+    lum = lambda c: 0.2126 * c + 0.7152 * c + 0.0722 * c
+    texel = [128.5 * 2 / 256, 128.5 / 256, 128.5 / 256, 128.5 * 2 / 256]       # (1,1,1) -> c=128,e=129 ; (.5,.5,.5) -> c=128,e=128
+    f = np.array([lum(texel[v]) * math.sin(PI * (v + 0.5) / 4) for v in range(4) for _ in range(2)])
+    # distribution.rs:120: row v uses the SLICE f[v .. v+nu), not f[v*nu ..]
+    for v in range(4):
+        row = f[v:v + 2]
+        c1 = 0.0 + row[0] / 2; c2 = c1 + row[1] / 2
+        assert d["row_int"][v] == c2
+        assert np.array_equal(d["cdf"][v], [0.0, c1 / c2, c2 / c2])
+    m = d["row_int"]
+    acc = [0.0]
+    for v in range(4):
+        acc.append(acc[-1] + m[v] / 4)
+    assert d["marg_int"] == acc[4]
+    assert np.array_equal(d["marg_cdf"], [a / acc[4] if i else 0.0 for i, a in enumerate(acc)])
+
+
+def test_infinite_light_sample_pdf_le_consistency():
+    rng = np.random.default_rng(5)
+    img = rng.uniform(0.05, 4.0, (8, 16, 3)).astype(np.float32)
+    s = orc.OracleScene(env_tables(img))
+    PI = 3.14159265358979
+    # le: Y-up lookup (light.rs:499-513): direction +y -> theta = 0 -> v = 0 ; phi = atan2(z, x)
+    assert np.array_equal(s.light_le(0, [0, 2, 0]), s.tex_value(0, 0.0, 0.0))
+    assert np.array_equal(s.light_le(0, [0, 0, 3]), s.tex_value(0, 0.25, 0.5))       # phi = PI/2 (of the 15-digit PI), theta = PI/2
+    assert np.array_equal(s.light_le(0, [-1, 0, 0]), s.tex_value(0, math.atan2(0.0, -1.0) / (2 * PI), math.acos(0.0) / PI))
+    # sample_li builds the direction Z-up (light.rs:233): wi = (sin t cos p, sin t sin p, cos t), p1 = p + wi * 20000
+    p = np.array([1.0, 2.0, 3.0])
+    o = s.light_sample_li(0, p, [0.37, 0.81])
+    assert o["pdf"] > 0 and abs(np.linalg.norm(o["wi"]) - 1) < 1e-15
+    assert np.allclose(o["p1"], p + o["wi"] * 20000.0, rtol=1e-12)
+    # the colour returned is the texture at the sampled (u, v), where v = acos(wi.z)/PI, u = atan2(wi.y, wi.x)/2PI
+    theta = math.acos(o["wi"][2]); phi = math.atan2(o["wi"][1], o["wi"][0]) % (2 * PI)
+    assert np.array_equal(o["color"], s.tex_value(0, phi / (2 * PI), theta / PI))
+    # the solid-angle pdf of the sample is map_pdf / (2 PI^2 sin theta); dist.pdf at the same (u,v) equals map_pdf
+    d = s.light_dist(0)
+    # pdf_li reads the SAME table Y-up: feed it the direction whose Y-up angles are (theta, phi)
+    w_yup = [math.sin(theta) * math.cos(phi), math.cos(theta), math.sin(theta) * math.sin(phi)]
+    assert math.isclose(s.light_pdf_li(0, p, w_yup), o["pdf"], rel_tol=1e-9)
+    # degenerate: straight up has sin(theta) = 0 -> pdf 0
+    assert s.light_pdf_li(0, p, [0, 1, 0]) == 0.0
+    # unoccluded(infinite = true): visible iff nothing is hit
+    t = env_tables(img, prims=[orc.prim(N.PRIM_SPHERE, [0, 50, 0, 1.0]), orc.prim(N.PRIM_SPHERE, [0, 0, 5, 1.0])])
+    s2 = orc.OracleScene(t)
+    # §8.1 #14: |dir| = 2e4, so the shadow-ray origin is pushed 20 world units along wi — an occluder closer than that is skipped
+    assert s2.occluded([(0, 0, 0)], [(0, 0, 20000)], [0], infinite=True)[0]
+    # (OracleScene.occluded returns the reference's `unoccluded` boolean)
+    assert not s2.occluded([(0, 0, 0)], [(0, 20000, 0)], [0], infinite=True)[0]      # the sphere is in the way
+    assert s2.occluded([(0, 0, 0)], [(20000, 0, 0)], [0], infinite=True)[0]          # nothing hit -> visible
+    assert not s2.occluded([(0, 0, 0)], [(20000, 0, 0)], [0], infinite=False)[0]     # area-light semantics: no hit -> occluded
