@@ -167,7 +167,13 @@ struct ExtendJob {
         bin_idx[(size_t)key * W + base + __popc(peers & ((1u << lane) - 1u))] = make_uint2(i, prim);   // path index + hit primitive
     }
 };
-__global__ void __launch_bounds__(128) k_extend(Ctrl* c, DScene sc, PathSet ps, uint2* __restrict__ bin_idx, uint32_t W) {
+#ifndef TRACE_MIN_BLOCKS
+#define TRACE_MIN_BLOCKS 5      // resident 128-thread blocks per SM of the persistent traversal kernels (register cap 65536 / (128 * N))
+#endif
+#ifndef TRACE_GRID_BLOCKS
+#define TRACE_GRID_BLOCKS 8     // persistent grid = SMs x this
+#endif
+__global__ void __launch_bounds__(128, TRACE_MIN_BLOCKS) k_extend(Ctrl* c, DScene sc, PathSet ps, uint2* __restrict__ bin_idx, uint32_t W) {
     ExtendJob job{c, &sc, ps, bin_idx, W};
     trace_jobs(sc, job, c->n_tot, &c->fetch[0]);
 }
@@ -182,7 +188,9 @@ template <class R> __device__ __forceinline__ R power_heuristic(R f_pdf, R g_pdf
 // reference's arithmetic; R = float is the production path (geometry stays f64 in both, see shade.cuh).
 // One specialisation per shading bin (material type MAT x primitive class CLS): every warp runs one material's code.
 // Paths in the "miss" bin need no kernel at all: without an infinite light a miss adds nothing (light.rs:499-513).
-template <class R, int MAT, int CLS>
+// ENVL = the scene has a Light::Infinite: only then are the environment-light arms compiled in (they cost the area-light-only
+// scenes ~5 % of shade time when always present: 52.8 -> 55.6 ms on the dragon, r01).
+template <class R, int MAT, int CLS, bool ENVL>
 __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) k_shade(Ctrl* c, DScene sc, RenderParams rp, PathSet in, PathSet out,
                                               const uint2* __restrict__ bin_idx, ConnQ shq, ConnQ prq, double* film) {
     constexpr uint32_t KM = mat_km<MAT>();
@@ -227,7 +235,7 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
                 const uint32_t nsf = BSDF_ALL - BSDF_SPECULAR;
                 // estimate_direct, light half (integrator.rs:573-597); Light::sample_li Diffuse (light.rs:176-203), Primitive::sample
                 // (primitive.rs:445-456) / Infinite (light.rs:204-245)
-                const bool inf_light = light.type == RT_LIGHT_INFINITE;
+                const bool inf_light = ENVL && light.type == RT_LIGHT_INFINITE;
                 {
                     D3 p1; double light_pdf; D3 color, wid = mk3(0., 0., 0.);
                     if (inf_light) infinite_sample_li(sc, light, rec.p, u_light, wid, light_pdf, color, p1);
@@ -379,7 +387,7 @@ struct ConnectJob {
         film_add(film, pr.pixel[k], cmul(mk3(pr.cr[k], pr.cg[k], pr.cb[k]), le));
     }
 };
-__global__ void __launch_bounds__(128, 5) k_connect(Ctrl* c, DScene sc, ConnQ shq, ConnQ prq, double* film) {
+__global__ void __launch_bounds__(128, TRACE_MIN_BLOCKS) k_connect(Ctrl* c, DScene sc, ConnQ shq, ConnQ prq, double* film) {
     ConnectJob job{&sc, shq, prq, film, c->n_shadow};
     trace_jobs(sc, job, c->n_shadow + c->n_probe, &c->fetch[1]);
 }
@@ -527,7 +535,7 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
     cudaStream_t st = w.stream;
     CK(cudaMemcpyAsync(w.ctrl, &init, sizeof(Ctrl), cudaMemcpyHostToDevice, st));
     int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device);
-    int g128 = (int)std::min<uint64_t>((w.W + 127) / 128, (uint64_t)sms * 32), gtrace = sms * 8, g256 = (int)std::min<uint64_t>((w.W + 255) / 256, (uint64_t)sms * 8);
+    int g128 = (int)std::min<uint64_t>((w.W + 127) / 128, (uint64_t)sms * 32), gtrace = sms * TRACE_GRID_BLOCKS, g256 = (int)std::min<uint64_t>((w.W + 255) / 256, (uint64_t)sms * 8);
     cudaEvent_t e_begin = ev(w, 0), e_end = ev(w, 1);
     size_t n_ev = 2;
     CK(cudaEventRecord(e_begin, st));
@@ -543,17 +551,19 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
             cudaEventRecord(ev(w, n_ev + 1), st);
             k_extend<<<gtrace, 128, 0, st>>>(w.ctrl, s->d, w.set[cur], w.bin_idx, w.W);
             cudaEventRecord(ev(w, n_ev + 2), st);
-#define RT_SHADE(R, M) \
-            if (s->bin_mask & (1u << (M * 2))) k_shade<R, M, 0><<<g128, 128, 0, st>>>(w.ctrl, s->d, rp, w.set[cur], w.set[cur ^ 1], w.bin_idx, w.shadow, w.probe, film->d); \
-            if (s->bin_mask & (1u << (M * 2 + 1))) k_shade<R, M, 1><<<g128, 128, 0, st>>>(w.ctrl, s->d, rp, w.set[cur], w.set[cur ^ 1], w.bin_idx, w.shadow, w.probe, film->d);
-#define RT_SHADE_ALL(R) RT_SHADE(R, RT_MAT_MATTE) RT_SHADE(R, RT_MAT_LIGHT) RT_SHADE(R, RT_MAT_PLASTIC) RT_SHADE(R, RT_MAT_GLASS) RT_SHADE(R, RT_MAT_METAL) RT_SHADE(R, RT_MAT_MIRROR)
-            if (f32) { RT_SHADE_ALL(float) } else { RT_SHADE_ALL(double) }
+#define RT_SHADE(R, M, I) \
+            if (s->bin_mask & (1u << (M * 2))) k_shade<R, M, 0, I><<<g128, 128, 0, st>>>(w.ctrl, s->d, rp, w.set[cur], w.set[cur ^ 1], w.bin_idx, w.shadow, w.probe, film->d); \
+            if (s->bin_mask & (1u << (M * 2 + 1))) k_shade<R, M, 1, I><<<g128, 128, 0, st>>>(w.ctrl, s->d, rp, w.set[cur], w.set[cur ^ 1], w.bin_idx, w.shadow, w.probe, film->d);
+#define RT_SHADE_ALL(R, I) RT_SHADE(R, RT_MAT_MATTE, I) RT_SHADE(R, RT_MAT_LIGHT, I) RT_SHADE(R, RT_MAT_PLASTIC, I) RT_SHADE(R, RT_MAT_GLASS, I) RT_SHADE(R, RT_MAT_METAL, I) RT_SHADE(R, RT_MAT_MIRROR, I)
+            if (s->d.has_infinite) { if (f32) { RT_SHADE_ALL(float, true) } else { RT_SHADE_ALL(double, true) } }
+            else { if (f32) { RT_SHADE_ALL(float, false) } else { RT_SHADE_ALL(double, false) } }
             if (s->d.has_infinite) k_shade_miss<<<g128, 128, 0, st>>>(w.ctrl, s->d, rp, w.set[cur], w.bin_idx, film->d);
             cudaEventRecord(ev(w, n_ev + 3), st);
             k_connect<<<gtrace, 128, 0, st>>>(w.ctrl, s->d, w.shadow, w.probe, film->d);
             cudaEventRecord(ev(w, n_ev + 4), st);
             n_ev += 5;
             cur ^= 1;
+            { cudaError_t le = cudaPeekAtLastError(); if (le != cudaSuccess) { cudaGetLastError(); set_error(std::string("rt_render: kernel launch failed: ") + cudaGetErrorString(le)); return RT_ERR_CUDA; } }
         }
         CK(cudaStreamSynchronize(st));
         if (trace) {
