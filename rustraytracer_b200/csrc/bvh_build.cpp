@@ -134,8 +134,60 @@ void build_bvh(const std::vector<Box64>& boxes, BuiltBvh& out, int threads) {
     uint32_t root = b.alloc();
     int par_depth = 0; while ((1 << par_depth) < threads) par_depth++;
     b.build(root, 0, (uint32_t)n, par_depth + 1);
-    // flatten: internal nodes only; leaves are folded into the parent's child words
     uint32_t total = b.n_nodes.load();
+#if RT_BVH_WIDTH == 4
+    // collapse to arity 4: a BVH4 node takes a BVH2 inner node's two children and keeps replacing the inner child with the
+    // largest surface area by its own two children until it has four (or only leaves remain); leaves are folded into the
+    // parent's child words.  Breadth-first numbering, root = 0.
+    (void)total;
+    auto set_child = [&](DNode4& d, int k, const FBox& bx, int32_t word) {
+        d.mnx[k] = bx.mn[0]; d.mxx[k] = bx.mx[0]; d.mny[k] = bx.mn[1]; d.mxy[k] = bx.mx[1]; d.mnz[k] = bx.mn[2]; d.mxz[k] = bx.mx[2]; d.child[k] = word;
+    };
+    FBox never; for (int k = 0; k < 3; k++) { never.mn[k] = FLT_MAX; never.mx[k] = -FLT_MAX; }
+    if (b.nodes[root].left < 0) {
+        DNode4 d; memset(&d, 0, sizeof(d));
+        set_child(d, 0, b.nodes[root].box, encode_leaf(0, b.nodes[root].count));
+        for (int k = 1; k < 4; k++) set_child(d, k, never, EMPTY_CHILD);
+        out.nodes.push_back(d);
+    } else {
+        std::vector<uint32_t> queue;            // BVH2 inner node behind every BVH4 node, in BVH4 index order
+        queue.push_back(root);
+        out.nodes.reserve(n / 2 + 16);
+        for (size_t qi = 0; qi < queue.size(); qi++) {
+            const TmpNode& t = b.nodes[queue[qi]];
+            uint32_t kids[4] = {(uint32_t)t.left, (uint32_t)t.right, 0, 0}; int nk = 2;
+            while (nk < 4) {
+                int pick = -1; float best = -1.f;
+                for (int k = 0; k < nk; k++) if (b.nodes[kids[k]].left >= 0) { float a = half_area(b.nodes[kids[k]].box); if (a > best) { best = a; pick = k; } }
+                if (pick < 0) break;
+                const TmpNode& c = b.nodes[kids[pick]];
+                kids[pick] = (uint32_t)c.left; kids[nk++] = (uint32_t)c.right;
+            }
+            DNode4 d; memset(&d, 0, sizeof(d));
+            for (int k = 0; k < 4; k++) {
+                if (k >= nk) { set_child(d, k, never, EMPTY_CHILD); continue; }
+                const TmpNode& c = b.nodes[kids[k]];
+                if (c.left >= 0) { set_child(d, k, c.box, (int32_t)queue.size()); queue.push_back(kids[k]); }
+                else set_child(d, k, c.box, encode_leaf(c.first, c.count));
+            }
+            out.nodes.push_back(d);
+        }
+        // worst-case traversal stack: descending into one child leaves the node's other children on the stack
+        std::vector<int> need(out.nodes.size(), 0);
+        for (size_t i = out.nodes.size(); i-- > 0;) {
+            int kids_n = 0, deepest = 0;
+            for (int k = 0; k < 4; k++) {
+                int32_t c = out.nodes[i].child[k];
+                if (c == EMPTY_CHILD) continue;
+                kids_n++;
+                if (c >= 0) deepest = std::max(deepest, need[c]);
+            }
+            need[i] = kids_n - 1 + deepest;
+        }
+        out.max_stack = need[0] + 1;            // + the sentinel
+    }
+#else
+    // flatten: internal nodes only; leaves are folded into the parent's child words
     std::vector<int32_t> remap(total, -1);
     uint32_t n_internal = 0;
     for (uint32_t i = 0; i < total; i++) if (b.nodes[i].left >= 0) remap[i] = (int32_t)n_internal++;
@@ -165,6 +217,7 @@ void build_bvh(const std::vector<Box64>& boxes, BuiltBvh& out, int threads) {
             out.nodes[remap[i]] = d;
         }
     }
+#endif
     out.order = std::move(idx);
 }
 

@@ -454,7 +454,7 @@ static Wavefront* get_wavefront(rt_scene& s) {
             size_t want = std::min<size_t>(s.bytes_nodes, (size_t)max_persist);
             cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want);
             cudaStreamAttrValue av{};
-            av.accessPolicyWindow.base_ptr = const_cast<DNode*>(s.d.nodes);
+            av.accessPolicyWindow.base_ptr = const_cast<DNodeT*>(s.d.nodes);
             av.accessPolicyWindow.num_bytes = std::min<size_t>(s.bytes_nodes, (size_t)max_window);
             av.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)want / (double)av.accessPolicyWindow.num_bytes);
             av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;

@@ -30,6 +30,22 @@ struct DNode { float v[12]; int32_t left, right, pad0, pad1; };   // 64 B
 static_assert(sizeof(DNode) == 64, "node must be 64 bytes");
 // v[0..3] = l.minx,l.maxx,l.miny,l.maxy ; v[4..7] = r.minx,r.maxx,r.miny,r.maxy ; v[8..11] = l.minz,l.maxz,r.minz,r.maxz
 
+// BVH4 (default): the binned-SAH BVH2 collapsed to arity 4 on the host — half the dependent node fetches per ray, which is what
+// bounds the latency-bound traversal (ncu r01: ~950 cycles per BVH2 step per lane, long-scoreboard 45 % of stalls).  128 B/node,
+// eight 16-byte words: six planes of four child coordinates, four child words (>= 0 node, < 0 leaf, EMPTY_CHILD = unused slot
+// whose box is inverted so that it can never be hit), one pad word.
+struct DNode4 { float mnx[4], mxx[4], mny[4], mxy[4], mnz[4], mxz[4]; int32_t child[4]; int32_t pad[4]; };
+static_assert(sizeof(DNode4) == 128, "BVH4 node must be 128 bytes");
+constexpr int32_t EMPTY_CHILD = 0x7fffffff;
+#ifndef RT_BVH_WIDTH
+#define RT_BVH_WIDTH 4
+#endif
+#if RT_BVH_WIDTH == 4
+typedef DNode4 DNodeT;
+#else
+typedef DNode DNodeT;
+#endif
+
 struct DSlot { double v[9]; uint32_t prim; uint32_t kind; };      // 80 B ; kind 0 = triangle, 1 = other
 static_assert(sizeof(DSlot) == 80, "slot must be 80 bytes");
 
@@ -58,7 +74,7 @@ constexpr double WORLD_RADIUS = 10000.0;   // light.rs:636
 
 // everything the kernels read; all pointers are device pointers
 struct DScene {
-    const DNode* nodes; const DSlot* slots; const DPrim* prims; const DMesh* meshes;
+    const DNodeT* nodes; const DSlot* slots; const DPrim* prims; const DMesh* meshes;
     const double* points; const double* normals; const double* uvs; const uint32_t* tri_index;
     const double* shapes; const DXform* xforms;
     const rt_texture* textures; const rt_material* materials; const DLight* lights;
@@ -76,7 +92,8 @@ void set_error(const std::string& msg);
 
 // bvh_build.cpp: binned-SAH BVH2 over conservative f32 boxes.  Returns nodes (root = 0) and the
 // leaf-ordered primitive permutation.  max 4 prims per leaf.
-struct BuiltBvh { std::vector<DNode> nodes; std::vector<uint32_t> order; };
+struct BuiltBvh { std::vector<DNodeT> nodes; std::vector<uint32_t> order; int max_stack = 0; };
+constexpr int TRAVERSAL_STACK = 64;         // per-thread stack entries of the traversal kernels (traverse.cuh)
 void build_bvh(const std::vector<Box64>& boxes, BuiltBvh& out, int threads);
 
 }  // namespace rt

@@ -35,7 +35,7 @@ double prim_area(const rt_scene& s, const HostPrim& p);
 bool invert4(const double m[16], double out[16]);
 // what commit hands to the device uploader (device.cu)
 struct HostImage {
-    std::vector<DNode> nodes; std::vector<DSlot> slots; std::vector<DPrim> prims; std::vector<DMesh> meshes;
+    std::vector<DNodeT> nodes; std::vector<DSlot> slots; std::vector<DPrim> prims; std::vector<DMesh> meshes;
     std::vector<double> points, normals, uvs, shapes; std::vector<uint32_t> tri_index;
     std::vector<DLight> lights;
     // Infinite lights: flat Distribution2D tables, concatenated; DLight pointers hold OFFSETS (in doubles) until upload

@@ -1,6 +1,9 @@
 // Host half of the C ABI: scene tables, primitive boxes, commit (BVH + SoA flatten).
 // No CUDA in this file.  Reference items are cited per function.
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <string>
 #include <cstring>
 #include <thread>
 #include "scene.h"
@@ -228,6 +231,8 @@ rt_status build_host_image(const rt_scene& s, HostImage& img) {
     if (ib >= (1ull << 32)) { set_error("index buffer exceeds 2^32 entries"); return RT_ERR_INVALID; }
     BuiltBvh bvh;
     build_bvh(boxes, bvh, threads);
+    if (bvh.max_stack > TRAVERSAL_STACK) { set_error("commit: BVH needs a deeper traversal stack than the kernels have (" + std::to_string(bvh.max_stack) + " > " + std::to_string(TRAVERSAL_STACK) + ")"); return RT_ERR_INVALID; }
+    if (getenv("RT_TRACE_BUILD")) fprintf(stderr, "bvh: %zu nodes of %zu bytes, %zu slots, worst-case stack %d\n", bvh.nodes.size(), sizeof(DNodeT), n, bvh.max_stack);
     img.nodes = std::move(bvh.nodes);
     img.slots.resize(n);
     for (size_t sidx = 0; sidx < n; sidx++) {

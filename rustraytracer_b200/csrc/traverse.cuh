@@ -66,8 +66,62 @@ __device__ __forceinline__ float f32_down(double x) { return __double2float_rd(x
 
 struct Hit { double t; uint32_t prim; };
 
-constexpr int STACK = 64;
+constexpr int STACK = TRAVERSAL_STACK;
 constexpr int32_t SENTINEL = 0x7fffffff;
+
+#if RT_BVH_WIDTH == 4
+// One BVH4 node: the conservative slab test of box_test() on all four children.  Returns the hit mask; key[k] packs child
+// k's entry distance with its slot number in the two low mantissa bits (non-negative floats order like ints), +inf for a
+// miss — so four min/max compare-exchanges sort the children front to back without moving (distance, index) pairs around.
+__device__ __forceinline__ unsigned node4_test(const float4* __restrict__ np, const RayF& r, float tmin, float tmax, int32_t key[4], int4& ch) {
+    const float4 mnx = __ldg(np), mxx = __ldg(np + 1), mny = __ldg(np + 2), mxy = __ldg(np + 3), mnz = __ldg(np + 4), mxz = __ldg(np + 5);
+    ch = __ldg(reinterpret_cast<const int4*>(np + 6));
+    const float4 nx = r.sx ? mxx : mnx, fx = r.sx ? mnx : mxx, ny = r.sy ? mxy : mny, fy = r.sy ? mny : mxy, nz = r.sz ? mxz : mnz, fz = r.sz ? mnz : mxz;
+    unsigned mask = 0;
+#define RT_CHILD(c, k)                                                                                                              \
+    {                                                                                                                               \
+        float t0 = fmaxf(fmaxf(__fmaf_rn(nx.c, r.idx, -r.nx), __fmaf_rn(ny.c, r.idy, -r.ny)), fmaxf(__fmaf_rn(nz.c, r.idz, -r.nz), tmin)); \
+        float t1 = fminf(fminf(__fmaf_rn(fx.c, r.idx, -r.fx), __fmaf_rn(fy.c, r.idy, -r.fy)), fminf(__fmaf_rn(fz.c, r.idz, -r.fz), tmax)); \
+        t0 = t0 - fabsf(t0) * 4.8e-7f; t1 = t1 + fabsf(t1) * 4.8e-7f;                                                               \
+        const bool h = t0 <= t1;                                                                                                    \
+        key[k] = h ? ((__float_as_int(t0) & ~3) | k) : (0x7f800000 | k);                                                            \
+        mask |= h ? (1u << k) : 0u;                                                                                                 \
+    }
+    RT_CHILD(x, 0) RT_CHILD(y, 1) RT_CHILD(z, 2) RT_CHILD(w, 3)
+#undef RT_CHILD
+    return mask;
+}
+__device__ __forceinline__ int32_t child_of(const int4& ch, int32_t key) { int k = key & 3; return k == 0 ? ch.x : (k == 1 ? ch.y : (k == 2 ? ch.z : ch.w)); }
+__device__ __forceinline__ void sort4(int32_t k[4]) {
+#define RT_CSWAP(a, b) { int32_t lo = min(k[a], k[b]), hi = max(k[a], k[b]); k[a] = lo; k[b] = hi; }
+    RT_CSWAP(0, 1) RT_CSWAP(2, 3) RT_CSWAP(0, 2) RT_CSWAP(1, 3) RT_CSWAP(1, 2)
+#undef RT_CSWAP
+}
+// closest-hit descent: nearest hit child next, the others pushed far to near
+__device__ __forceinline__ int32_t node4_closest(const DScene& sc, int32_t cur, const RayF& rf, float ftmin, float ftmax, int32_t* stack, int& sp) {
+    int32_t key[4]; int4 ch;
+    const unsigned mask = node4_test(reinterpret_cast<const float4*>(sc.nodes) + 8 * (size_t)cur, rf, ftmin, ftmax, key, ch);
+    const int nh = __popc(mask);
+    if (nh == 0) return stack[--sp];
+    sort4(key);
+    if (nh > 3 && sp < STACK) stack[sp++] = child_of(ch, key[3]);
+    if (nh > 2 && sp < STACK) stack[sp++] = child_of(ch, key[2]);
+    if (nh > 1 && sp < STACK) stack[sp++] = child_of(ch, key[1]);
+    return child_of(ch, key[0]);
+}
+// any-hit descent: order does not matter
+__device__ __forceinline__ int32_t node4_any(const DScene& sc, int32_t cur, const RayF& rf, float ftmin, float ftmax, int32_t* stack, int& sp) {
+    int32_t key[4]; int4 ch;
+    const unsigned mask = node4_test(reinterpret_cast<const float4*>(sc.nodes) + 8 * (size_t)cur, rf, ftmin, ftmax, key, ch);
+    if (mask == 0u) return stack[--sp];
+    const int32_t c[4] = {ch.x, ch.y, ch.z, ch.w};
+    int32_t next = SENTINEL; bool have = false;
+#pragma unroll
+    for (int k = 0; k < 4; k++) if ((mask >> k) & 1u) { if (have) { if (sp < STACK) stack[sp++] = c[k]; } else { next = c[k]; have = true; } }
+    return next;
+}
+#endif
+
 
 // Candidate primitive in leaf slot `s`: the reference's exact accept test.  Returns true with t.
 __device__ __forceinline__ bool slot_test(const DScene& sc, const DSlot* __restrict__ slots, uint32_t s, const RayX& rx, double tmin, double tmax,
@@ -98,9 +152,14 @@ __device__ __forceinline__ Hit trace_closest(const DScene& sc, D3 o, D3 d, doubl
     int32_t stack[STACK]; int sp = 0;
     stack[sp++] = SENTINEL;
     int32_t cur = 0;
+#if RT_BVH_WIDTH != 4
     const float4* __restrict__ nodes = reinterpret_cast<const float4*>(sc.nodes);
+#endif
     while (cur != SENTINEL) {
         while (cur >= 0 && cur != SENTINEL) {
+#if RT_BVH_WIDTH == 4
+            cur = node4_closest(sc, cur, rf, ftmin, ftmax, stack, sp);
+#else
             const float4* np = nodes + 4 * (size_t)cur;
             float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2);
             int4 ch = __ldg(reinterpret_cast<const int4*>(np + 3));
@@ -115,6 +174,7 @@ __device__ __forceinline__ Hit trace_closest(const DScene& sc, D3 o, D3 d, doubl
             } else if (hl) cur = ch.x;
             else if (hr) cur = ch.y;
             else cur = stack[--sp];
+#endif
         }
         if (cur == SENTINEL) break;
         // leaf
@@ -145,9 +205,14 @@ __device__ __forceinline__ bool trace_any(const DScene& sc, D3 o, D3 d, double t
     int32_t stack[STACK]; int sp = 0;
     stack[sp++] = SENTINEL;
     int32_t cur = 0;
+#if RT_BVH_WIDTH != 4
     const float4* __restrict__ nodes = reinterpret_cast<const float4*>(sc.nodes);
+#endif
     while (cur != SENTINEL) {
         while (cur >= 0 && cur != SENTINEL) {
+#if RT_BVH_WIDTH == 4
+            cur = node4_any(sc, cur, rf, ftmin, ftmax, stack, sp);
+#else
             const float4* np = nodes + 4 * (size_t)cur;
             float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2);
             int4 ch = __ldg(reinterpret_cast<const int4*>(np + 3));
@@ -158,6 +223,7 @@ __device__ __forceinline__ bool trace_any(const DScene& sc, D3 o, D3 d, double t
             else if (hl) cur = ch.x;
             else if (hr) cur = ch.y;
             else cur = stack[--sp];
+#endif
         }
         if (cur == SENTINEL) break;
         uint32_t v = (uint32_t)~cur, first = v >> 2, count = (v & 3u) + 1u;
@@ -224,6 +290,10 @@ __device__ __forceinline__ void tstate_init(TState& s, int32_t* stack, D3 o, D3 
 }
 // one inner-node step: test both children, descend into the nearer hit child, push the other, or pop
 __device__ __forceinline__ void node_step(const DScene& sc, TState& s, int32_t* stack) {
+#if RT_BVH_WIDTH == 4
+    // front-to-back for any-hit rays too: one code path for the warp, and near occluders end a shadow ray sooner
+    s.cur = node4_closest(sc, s.cur, s.rf, s.ftmin, s.ftmax, stack, s.sp);
+#else
     const float4* np = reinterpret_cast<const float4*>(sc.nodes) + 4 * (size_t)s.cur;
     float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2);
     int4 ch = __ldg(reinterpret_cast<const int4*>(np + 3));
@@ -238,6 +308,7 @@ __device__ __forceinline__ void node_step(const DScene& sc, TState& s, int32_t* 
     } else if (hl) s.cur = ch.x;
     else if (hr) s.cur = ch.y;
     else s.cur = stack[--s.sp];
+#endif
 }
 // one leaf: the reference-exact test of its 1..4 slots, then pop
 __device__ __forceinline__ void leaf_step(const DScene& sc, TState& s, int32_t* stack) {
