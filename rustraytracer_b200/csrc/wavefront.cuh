@@ -1,0 +1,220 @@
+// Shared device declarations of the wavefront path tracer: path-state records, queues, the control block, and the shade
+// kernel template.  Included by render.cu (everything except the f32 shade instantiations) and by shade_f32.cu, which
+// instantiates k_shade<float, ...> in a translation unit of its own so that the production-mode radiometry can be compiled
+// with fast f32 division / square root (see the Makefile) while every f64 expression keeps the reference's rounding.
+#pragma once
+#include "scene.h"
+#include "shade.cuh"
+
+namespace rt {
+
+// Path state, one entry per path in flight, as two arrays of 48-byte records (three 16-byte words each).
+// extend streams `ray` in order (fully coalesced); shade reaches both through the bin index, so each path costs
+// 3 + 3 fully-used 32-byte sectors instead of the 13 quarter-used sectors of a field-per-array layout.
+struct __align__(16) PRay { double ox, oy, oz, dx, dy, dz; };
+struct __align__(16) PAux { double bx, by, bz; uint32_t pixel, sample, dim, flags; };   // flags: bits 0..15 bounces, bit 16 specular_bounce
+static_assert(sizeof(PRay) == 48 && sizeof(PAux) == 48, "path records must be 48 bytes");
+struct PathSet { PRay* ray; PAux* aux; };
+__device__ __forceinline__ PRay load_ray(const PRay* p) {
+    const double2* q = reinterpret_cast<const double2*>(p);
+    double2 a = __ldcs(q), b = __ldcs(q + 1), c = __ldcs(q + 2);     // streaming: path state must not evict the BVH from L2
+    PRay r; r.ox = a.x; r.oy = a.y; r.oz = b.x; r.dx = b.y; r.dy = c.x; r.dz = c.y; return r;
+}
+__device__ __forceinline__ void store_ray(PRay* p, D3 o, D3 d) {
+    double2* q = reinterpret_cast<double2*>(p);
+    __stcs(q, make_double2(o.x, o.y)); __stcs(q + 1, make_double2(o.z, d.x)); __stcs(q + 2, make_double2(d.y, d.z));
+}
+__device__ __forceinline__ PAux load_aux(const PAux* p) {      // words: (bx,by) (bz,[pixel,sample]) ([dim,flags],pad)
+    const double2* q = reinterpret_cast<const double2*>(p);
+    double2 a = __ldcs(q), b = __ldcs(q + 1), c = __ldcs(q + 2);
+    PAux r; r.bx = a.x; r.by = a.y; r.bz = b.x;
+    r.pixel = (uint32_t)__double2loint(b.y); r.sample = (uint32_t)__double2hiint(b.y);
+    r.dim = (uint32_t)__double2loint(c.x); r.flags = (uint32_t)__double2hiint(c.x);
+    return r;
+}
+__device__ __forceinline__ void store_aux(PAux* p, double bx, double by, double bz, uint32_t pixel, uint32_t sample, uint32_t dim, uint32_t flags) {
+    double2* q = reinterpret_cast<double2*>(p);
+    __stcs(q, make_double2(bx, by));
+    __stcs(q + 1, make_double2(bz, __hiloint2double((int)sample, (int)pixel)));
+    __stcs(q + 2, make_double2(__hiloint2double((int)flags, (int)dim), 0.));
+}
+struct ConnQ {             // shadow / probe queue: a ray (a→b or origin+dir), a pre-weighted contribution, a target
+    double *ax, *ay, *az, *bx, *by, *bz, *cr, *cg, *cb;
+    uint32_t *target, *pixel;                     // shadow: light primitive ; probe: light index
+};
+struct Ctrl {
+    uint32_t n_cur, n_new, n_tot, n_next, n_shadow, n_probe, pad0, pad1;
+    unsigned long long next_sample, sample_base, total_samples;
+    unsigned long long c_paths, c_extend, c_shadow, c_probe, c_iter;
+    uint32_t fetch[4];           // work counters of the persistent traversal kernels (extend, shadow, probe)
+    uint32_t bin_count[16];      // paths per shading bin after extend (material type x primitive class, 15 = miss)
+};
+constexpr int N_BINS = 16;
+#ifndef SHADE_MIN_BLOCKS
+#define SHADE_MIN_BLOCKS 4      // <= 128 registers: 16 warps/SM; measured against 3 and 5 in profiles/shade_r01_notes.md
+#endif
+struct RenderParams {
+    rt_camera cam; uint32_t width, height, x0, y0, ww, wh, sample_begin; uint32_t max_depth, invisible_light; uint32_t k0, k1; uint32_t W;
+};
+
+__device__ __forceinline__ uint32_t warp_append(uint32_t* counter) {
+    // warp-aggregated queue append: one atomic per warp (ballot + popc), everyone gets a unique slot
+    unsigned mask = __activemask();
+    int leader = __ffs(mask) - 1, lane = threadIdx.x & 31;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(counter, (uint32_t)__popc(mask));
+    base = __shfl_sync(mask, base, leader);
+    return base + __popc(mask & ((1u << lane) - 1u));
+}
+__device__ __forceinline__ void film_add(double* film, uint32_t pixel, D3 c) {
+    // util::increment_color (util.rs:208-232): the NaN guards there compare with `== NAN` and never fire
+    atomicAdd(film + 4 * (size_t)pixel + 0, c.x); atomicAdd(film + 4 * (size_t)pixel + 1, c.y); atomicAdd(film + 4 * (size_t)pixel + 2, c.z);
+}
+
+__device__ __forceinline__ D3 light_l(const DLight& l, D3 n, D3 w) {      // Light::l (light.rs:475-496)
+    if (dot(n, w) > 0. || l.two_sided) return ld3(l.color);
+    return mk3(0., 0., 0.);
+}
+template <class R> __device__ __forceinline__ R power_heuristic(R f_pdf, R g_pdf) { R f = R(1) * f_pdf, g = R(1) * g_pdf; return (f * f) / (f * f + g * g); }   // integrator.rs:655-659
+
+// The body of PathIntegrator::li's loop (integrator.rs:386-443) for one path vertex.  R = double reproduces the
+// reference's arithmetic; R = float is the production path (geometry stays f64 in both, see shade.cuh).
+// One specialisation per shading bin (material type MAT x primitive class CLS): every warp runs one material's code.
+// Paths in the "miss" bin need no kernel at all: without an infinite light a miss adds nothing (light.rs:499-513).
+// ENVL = the scene has a Light::Infinite: only then are the environment-light arms compiled in (they cost the area-light-only
+// scenes ~5 % of shade time when always present: 52.8 -> 55.6 ms on the dragon, r01).
+template <class R, int MAT, int CLS, bool ENVL>
+__global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) k_shade(Ctrl* c, DScene sc, RenderParams rp, PathSet in, PathSet out,
+                                              const uint2* __restrict__ bin_idx, ConnQ shq, ConnQ prq, double* film) {
+    constexpr uint32_t KM = mat_km<MAT>();
+    constexpr int BIN = MAT * 2 + CLS;
+    const uint32_t n = c->bin_count[BIN];
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+        const uint2 entry = bin_idx[(size_t)BIN * rp.W + k];
+        const uint32_t i = entry.x;
+        const PRay pr = load_ray(in.ray + i);
+        const PAux pa = load_aux(in.aux + i);
+        D3 o = mk3(pr.ox, pr.oy, pr.oz), d = mk3(pr.dx, pr.dy, pr.dz);
+        V3<R> beta = v3<R>((R)pa.bx, (R)pa.by, (R)pa.bz);
+        uint32_t pixel = pa.pixel, flags = pa.flags;
+        Rng rng; rng.k0 = rp.k0; rng.k1 = rp.k1; rng.pixel = pixel; rng.sample = pa.sample; rng.dim = pa.dim; rng.w2 = 0xffffffffu; rng.w3 = 0;
+        uint32_t bounces = flags & 0xffffu; bool specular_bounce = (flags >> 16) & 1u;
+        uint32_t prim = entry.y;
+        bool is_some = prim != RT_NONE;
+        Rec rec;
+        if (is_some) is_some = prim_record_t<CLS>(sc, prim, o, d, SMALL, INF, true, rec);
+        bool alive = false;
+        do {
+            if (bounces == 0 || specular_bounce) {
+                if (is_some) {
+                    uint32_t li = sc.prims[prim].light;
+                    if (li != RT_NONE) {
+                        if (rp.invisible_light) { o = rec.p; alive = true; break; }          // go straight through the light, same bounce
+                        film_add(film, pixel, dbl3(cmul(cast3<R>(light_l(sc.lights[li], rec.n, -d)), beta)));   // HitRecord::le (hittable.rs:215-225)
+                    }
+                }   // miss: only Infinite lights emit (light.rs:499-513) — none in scope
+            }
+            if (!is_some || bounces >= rp.max_depth) break;
+            Bsdf<R> bsdf;
+            compute_scattering<R, MAT>(sc, rec, bsdf);
+            const V3<R> wo_w = cast3<R>(rec.wo), sn = cast3<R>(rec.sn);
+            // uniform_sample_one_light (integrator.rs:530-557)
+            uint32_t n_lights = sc.n_lights;
+            if (n_lights != 0) {
+                uint32_t light_num = min(n_lights - 1, (uint32_t)(unsigned long long)(rng_next(rng) * (double)n_lights));
+                D2 u_light; u_light.x = rng_next(rng); u_light.y = rng_next(rng);
+                V2<R> u_scatter; u_scatter.x = rng_real<R>(rng); u_scatter.y = rng_real<R>(rng);
+                const DLight& light = sc.lights[light_num];
+                const uint32_t nsf = BSDF_ALL - BSDF_SPECULAR;
+                // estimate_direct, light half (integrator.rs:573-597); Light::sample_li Diffuse (light.rs:176-203), Primitive::sample
+                // (primitive.rs:445-456) / Infinite (light.rs:204-245)
+                const bool inf_light = ENVL && light.type == RT_LIGHT_INFINITE;
+                {
+                    D3 p1; double light_pdf; D3 color, wid = mk3(0., 0., 0.);
+                    if (inf_light) infinite_sample_li(sc, light, rec.p, u_light, wid, light_pdf, color, p1);
+                    else {
+                        D3 n1; sample_area(sc, light.prim, u_light, p1, n1);
+                        double pdf = 1. / light.area;
+                        D3 wiu = p1 - rec.p;
+                        if (norm2(wiu) == 0.) pdf = 0.;
+                        else { D3 wn = normalize(wiu); pdf = pdf * norm2(rec.p - p1) / fabs(dot(n1, -wn)); }
+                        if (pdf == 0. || norm2(rec.p - p1) == 0.) { light_pdf = 0.; color = ld3(light.color); }
+                        else { wid = normalize(p1 - rec.p); light_pdf = pdf; color = light_l(light, n1, -wid); }
+                    }
+                    if (light_pdf > 0. && !is_black(color)) {
+                        V3<R> wi = cast3<R>(wid);
+                        V3<R> f = bsdf_f<R, KM>(bsdf, wo_w, wi, nsf) * fabs(dot(wi, sn));
+                        R scattering_pdf = bsdf_pdf<R, KM>(bsdf, wo_w, wi, nsf);
+                        if (!is_black(f)) {
+                            R weight = power_heuristic<R>((R)light_pdf, scattering_pdf);
+                            V3<R> ld = cmul(f, cast3<R>(color)) * (weight / (R)light_pdf);
+                            V3<R> contrib = cmul(ld * (R)n_lights, beta);
+                            uint32_t q = warp_append(&c->n_shadow);
+                            __stcs(shq.ax + q, rec.p.x); __stcs(shq.ay + q, rec.p.y); __stcs(shq.az + q, rec.p.z); __stcs(shq.bx + q, p1.x); __stcs(shq.by + q, p1.y); __stcs(shq.bz + q, p1.z);
+                            __stcs(shq.cr + q, (double)contrib.x); __stcs(shq.cg + q, (double)contrib.y); __stcs(shq.cb + q, (double)contrib.z); __stcs(shq.target + q, inf_light ? RT_NONE : light.prim); __stcs(shq.pixel + q, pixel);
+                        }
+                    }
+                }
+                // estimate_direct, BSDF half (integrator.rs:601-632)
+                {
+                    V3<R> f, wi; R scattering_pdf; uint32_t st;
+                    bsdf_sample_f<R, KM>(bsdf, wo_w, u_scatter, nsf, rng, f, wi, scattering_pdf, st);
+                    f = f * fabs(dot(wi, sn));
+                    if (!is_black(f) && scattering_pdf > R(0)) {
+                        R weight = R(1); bool go = true;
+                        D3 wid = dbl3(wi);
+                        if ((st & BSDF_SPECULAR) == 0) {
+                            // Light::pdf_li → Primitive::pdf (primitive.rs:462-473): re-intersect the ONE light primitive, tmin = 0, no leaf box
+                            // Infinite: Light::pdf_li (light.rs:285-294)
+                            D3 lp, ln; double light_pdf = 0.;
+                            if (inf_light) light_pdf = infinite_pdf_li(sc, light, wid);
+                            else if (prim_hit_pn(sc, light.prim, rec.p, wid, 0., INF, lp, ln)) light_pdf = norm2(rec.p - lp) / (light.area * fabs(dot(ln, -wid)));
+                            if (light_pdf == 0.) go = false;
+                            else weight = power_heuristic<R>(scattering_pdf, (R)light_pdf);
+                        }
+                        if (go) {
+                            V3<R> contrib = cmul((f * (weight / scattering_pdf)) * (R)n_lights, beta);   // × Le decided by the probe ray
+                            uint32_t q = warp_append(&c->n_probe);
+                            prq.ax[q] = rec.p.x; prq.ay[q] = rec.p.y; prq.az[q] = rec.p.z; prq.bx[q] = wid.x; prq.by[q] = wid.y; prq.bz[q] = wid.z;
+                            prq.cr[q] = contrib.x; prq.cg[q] = contrib.y; prq.cb[q] = contrib.z; prq.target[q] = light_num; prq.pixel[q] = pixel;
+                        }
+                    }
+                }
+            }
+            // continuation (integrator.rs:421-441)
+            V3<R> wo = cast3<R>(-d);
+            V2<R> u; u.x = rng_real<R>(rng); u.y = rng_real<R>(rng);
+            V3<R> f, wi; R pdf; uint32_t sflags;
+            bsdf_sample_f<R, KM>(bsdf, wo, u, BSDF_ALL, rng, f, wi, pdf, sflags);
+            if (is_black(f) || pdf == R(0)) break;
+            beta = cmul(beta, f) * (fabs(dot(wi, sn)) / pdf);
+            specular_bounce = (sflags & BSDF_SPECULAR) != 0;
+            o = rec.p; d = dbl3(wi);
+            if (bounces > 3) {
+                R q = fmax(R(0.05), R(1) - fmax(beta.x, fmax(beta.y, beta.z)));
+                if (rng_real<R>(rng) < q) break;
+                beta = beta * (R(1) / (R(1) - q));
+            }
+            bounces++;
+            alive = true;
+        } while (false);
+        if (alive) {
+            uint32_t q = warp_append(&c->n_next);
+            store_ray(out.ray + q, o, d);
+            store_aux(out.aux + q, (double)beta.x, (double)beta.y, (double)beta.z, pixel, rng.sample, rng.dim, (bounces & 0xffffu) | (specular_bounce ? 0x10000u : 0u));
+        }
+    }
+}
+
+// one launch per shading bin present in the scene (render.cu: R = double ; shade_f32.cu: R = float)
+struct ShadeLaunch { Ctrl* ctrl; const DScene* sc; const RenderParams* rp; PathSet in, out; const uint2* bin_idx; ConnQ shadow, probe; double* film; uint32_t bin_mask; int grid; cudaStream_t stream; };
+template <class R, bool ENVL> inline void launch_shade_bins(const ShadeLaunch& L) {
+#define RT_SHADE(M) \
+    if (L.bin_mask & (1u << (M * 2))) k_shade<R, M, 0, ENVL><<<L.grid, 128, 0, L.stream>>>(L.ctrl, *L.sc, *L.rp, L.in, L.out, L.bin_idx, L.shadow, L.probe, L.film); \
+    if (L.bin_mask & (1u << (M * 2 + 1))) k_shade<R, M, 1, ENVL><<<L.grid, 128, 0, L.stream>>>(L.ctrl, *L.sc, *L.rp, L.in, L.out, L.bin_idx, L.shadow, L.probe, L.film);
+    RT_SHADE(RT_MAT_MATTE) RT_SHADE(RT_MAT_LIGHT) RT_SHADE(RT_MAT_PLASTIC) RT_SHADE(RT_MAT_GLASS) RT_SHADE(RT_MAT_METAL) RT_SHADE(RT_MAT_MIRROR)
+#undef RT_SHADE
+}
+void launch_shade_f32(const ShadeLaunch& L, bool envl);      // shade_f32.cu
+
+}  // namespace rt
