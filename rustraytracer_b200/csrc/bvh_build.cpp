@@ -10,6 +10,7 @@
 #include <atomic>
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <future>
 #include <thread>
@@ -39,6 +40,7 @@ struct Builder {
     std::atomic<uint32_t> n_nodes{0};
     static constexpr int BINS = 16;
     static constexpr uint32_t LEAF_MAX = 4;
+    float c_isect = 1.5f;      // SAH: cost of one f64 leaf test relative to one node step (RT_SAH_ISECT overrides, for tuning)
     Builder(const std::vector<FBox>& b, std::vector<uint32_t>& i) : pb(b), idx(i) { nodes.resize(std::max<size_t>(2 * b.size(), 2)); }
 
     uint32_t alloc() { return n_nodes.fetch_add(1); }
@@ -84,8 +86,8 @@ struct Builder {
         } else {
             // leaf cost: count * C_isect ; split cost: C_trav + SAH.  C_isect/C_trav = 1.5 (f64 leaf test)
             float ha = half_area(bounds);
-            float split_cost = 1.0f + 1.5f * best_cost / std::max(ha, 1e-30f);
-            if (count <= LEAF_MAX && 1.5f * (float)count <= split_cost) return;
+            float split_cost = 1.0f + c_isect * best_cost / std::max(ha, 1e-30f);
+            if (count <= LEAF_MAX && c_isect * (float)count <= split_cost) return;
             float lo = cb.mn[best_axis], scale = (float)BINS / (cb.mx[best_axis] - lo);
             auto it = std::partition(idx.begin() + first, idx.begin() + first + count, [&](uint32_t p) {
                 const FBox& b = pb[p];
@@ -131,6 +133,7 @@ void build_bvh(const std::vector<Box64>& boxes, BuiltBvh& out, int threads) {
     std::vector<uint32_t> idx(n);
     for (size_t i = 0; i < n; i++) idx[i] = (uint32_t)i;
     Builder b(pb, idx);
+    if (const char* e = getenv("RT_SAH_ISECT")) { float v = (float)atof(e); if (v > 0.f) b.c_isect = v; }
     uint32_t root = b.alloc();
     int par_depth = 0; while ((1 << par_depth) < threads) par_depth++;
     b.build(root, 0, (uint32_t)n, par_depth + 1);

@@ -1,6 +1,7 @@
 // Device half of the C ABI, part 1: scene upload and the ray-batch entry points
 // (rt_intersect*, rt_closest_device, rt_occluded*).  sm_100a only; there is no CPU fallback —
 // every entry point fails with RT_ERR_CUDA when no device is usable.
+#include <algorithm>
 #include <cstdio>
 #include <cstring>
 #include "scene.h"
@@ -58,6 +59,7 @@ rt_status upload_scene(rt_scene& s, const HostImage& img) {
     }
     if ((st = up(s, lights, d.lights, b))) return st;
     s.bytes_tables = b;
+    { void* cp = nullptr; CK(cudaMalloc(&cp, 16)); s.allocations.push_back(cp); s.d_counter = (uint32_t*)cp; }   // work counter of the persistent batch kernels
     d.n_nodes = (uint32_t)img.nodes.size(); d.n_prims = (uint32_t)img.prims.size();
     d.n_lights = (uint32_t)img.lights.size(); d.n_slots = (uint32_t)img.slots.size();
     s.d = d;
@@ -66,7 +68,7 @@ rt_status upload_scene(rt_scene& s, const HostImage& img) {
 
 void free_scene_device(rt_scene& s) {
     for (void* p : s.allocations) cudaFree(p);
-    s.allocations.clear(); s.d = DScene{}; s.committed = false;
+    s.allocations.clear(); s.d = DScene{}; s.d_counter = nullptr; s.committed = false;
 }
 
 // ---------------------------------------------------------------- kernels
@@ -99,6 +101,23 @@ __global__ void __launch_bounds__(128) k_closest(DScene sc, uint64_t n, const rt
         Hit h = trace_closest(sc, mk3(a.x, a.y, b.x), mk3(b.y, c.x, c.y), tmin, tmax);
         prim[i] = h.prim; t[i] = h.t;
     }
+}
+
+// The ray-cast sweep entry (rt_closest_device) through the persistent scheduler of traverse.cuh: lanes whose ray has finished
+// fetch the next one from a global counter instead of idling until the slowest ray of the warp is done — the soup's
+// incoherent rays differ by an order of magnitude in traversal length.
+struct ClosestJob {
+    const rt_ray* rays; double tmin, tmax; uint32_t* prim; double* t;
+    __device__ __forceinline__ bool load(uint32_t i, TState& st, int32_t* stack) {
+        const double2* rp = reinterpret_cast<const double2*>(rays + i);
+        double2 a = __ldg(rp), b = __ldg(rp + 1), c = __ldg(rp + 2);
+        tstate_init(st, stack, mk3(a.x, a.y, b.x), mk3(b.y, c.x, c.y), tmin, tmax, false, 0., 0u);
+        return true;
+    }
+    __device__ __forceinline__ void finish(uint32_t i, const TState& st) { prim[i] = st.best.prim; t[i] = st.best.t; }
+};
+__global__ void __launch_bounds__(128, 5) k_closest_persistent(DScene sc, ClosestJob job, uint32_t n, uint32_t* counter) {
+    trace_jobs(sc, job, n, counter);
 }
 
 __global__ void __launch_bounds__(128) k_occluded(DScene sc, uint64_t n, const rt_shadow_query* __restrict__ q, uint8_t* __restrict__ out) {
@@ -143,7 +162,15 @@ rt_status rt_closest_device(rt_scene* s, uint64_t n, const rt_ray* d_rays, doubl
     rt_status st = check_scene(s, "rt_closest_device"); if (st) return st;
     if (n == 0) return RT_OK;
     if (!d_rays || !d_prim || !d_t) { set_error("rt_closest_device: null buffer"); return RT_ERR_INVALID; }
-    k_closest<<<grid_for(n, 128), 128, 0, (cudaStream_t)stream>>>(s->d, n, d_rays, tmin, tmax, d_prim, d_t);
+    if (!s->d_counter) { k_closest<<<grid_for(n, 128), 128, 0, (cudaStream_t)stream>>>(s->d, n, d_rays, tmin, tmax, d_prim, d_t); CK(cudaGetLastError()); return RT_OK; }
+    int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device);
+    const uint64_t CHUNK = 1ull << 31;
+    for (uint64_t base = 0; base < n; base += CHUNK) {
+        uint32_t m = (uint32_t)std::min<uint64_t>(CHUNK, n - base);
+        CK(cudaMemsetAsync(s->d_counter, 0, sizeof(uint32_t), (cudaStream_t)stream));
+        ClosestJob job{d_rays + base, tmin, tmax, d_prim + base, d_t + base};
+        k_closest_persistent<<<sms * 5, 128, 0, (cudaStream_t)stream>>>(s->d, job, m, s->d_counter);
+    }
     CK(cudaGetLastError());
     return RT_OK;
 }

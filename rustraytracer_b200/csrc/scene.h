@@ -18,6 +18,7 @@ struct rt_scene {
     bool committed = false;
     int device = 0;
     rt::DScene d{};                          // device pointers
+    uint32_t* d_counter = nullptr;           // device work counter of the persistent batch kernels
     std::vector<void*> allocations;          // every cudaMalloc of this scene
     uint64_t bytes_nodes = 0, bytes_slots = 0, bytes_tables = 0;
     uint32_t bin_mask = 0;                   // shading bins (material type * 2 + is_triangle) that occur in the scene

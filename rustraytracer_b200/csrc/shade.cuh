@@ -61,6 +61,12 @@ template <class R> __device__ __forceinline__ V3<R> cmul(V3<R> a, V3<R> b) { ret
 template <class R> __device__ __forceinline__ V3<R> cdiv(V3<R> a, V3<R> b) { return v3<R>(a.x / b.x, a.y / b.y, a.z / b.z); }
 template <class R> __device__ __forceinline__ R dot(V3<R> a, V3<R> b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 template <class R> __device__ __forceinline__ V3<R> cross(V3<R> a, V3<R> b) { return v3<R>(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
+// f32 (production) mode: the library is compiled with -fmad=false for the sake of the f64 expressions, so the f32 vector
+// algebra asks for its fused multiply-adds explicitly (fewer instructions, one rounding less; R = double is untouched)
+template <> __device__ __forceinline__ float dot<float>(V3<float> a, V3<float> b) { return __fmaf_rn(a.z, b.z, __fmaf_rn(a.y, b.y, a.x * b.x)); }
+template <> __device__ __forceinline__ V3<float> cross<float>(V3<float> a, V3<float> b) {
+    return v3<float>(__fmaf_rn(a.y, b.z, -(a.z * b.y)), __fmaf_rn(a.z, b.x, -(a.x * b.z)), __fmaf_rn(a.x, b.y, -(a.y * b.x)));
+}
 template <class R> __device__ __forceinline__ R norm(V3<R> a) { return sqrt(dot(a, a)); }
 template <class R> __device__ __forceinline__ V3<R> normalize(V3<R> a) { R n = norm(a); return v3<R>(a.x / n, a.y / n, a.z / n); }
 template <class R> __device__ __forceinline__ R clampr(R x, R lo, R hi) { return fmin(fmax(x, lo), hi); }
@@ -348,6 +354,10 @@ template <class R> __device__ __forceinline__ V3<R> world_to_local(const Bsdf<R>
 template <class R> __device__ __forceinline__ V3<R> local_to_world(const Bsdf<R>& b, V3<R> v) {
     return v3<R>(b.ss.x * v.x + b.ts.x * v.y + b.ns.x * v.z, b.ss.y * v.x + b.ts.y * v.y + b.ns.y * v.z, b.ss.z * v.x + b.ts.z * v.y + b.ns.z * v.z);
 }
+template <> __device__ __forceinline__ V3<float> local_to_world<float>(const Bsdf<float>& b, V3<float> v) {
+    return v3<float>(__fmaf_rn(b.ns.x, v.z, __fmaf_rn(b.ts.x, v.y, b.ss.x * v.x)), __fmaf_rn(b.ns.y, v.z, __fmaf_rn(b.ts.y, v.y, b.ss.y * v.x)),
+                     __fmaf_rn(b.ns.z, v.z, __fmaf_rn(b.ts.z, v.y, b.ss.z * v.x)));
+}
 template <class R> __device__ __forceinline__ uint32_t num_components(const Bsdf<R>& b, uint32_t t) { uint32_t c = 0; for (int i = 0; i < b.n; i++) if (matches_flags(b.lobes[i].type, t)) c++; return c; }
 // Bsdf::f (bsdf.rs:83-98), `a && b || c` precedence kept (§8.1 #6)
 template <class R, uint32_t KM> static __device__ __noinline__ V3<R> bsdf_f(const Bsdf<R>& b, V3<R> wow, V3<R> wiw, uint32_t flags) {
@@ -416,13 +426,31 @@ static __device__ __noinline__ D3 texel_value(const DScene& sc, const rt_texture
     uint32_t q = __ldg(sc.texels + im.offset + (size_t)y * im.w + x);
     return mk3((double)(q & 255u) / 255., (double)((q >> 8) & 255u) / 255., (double)((q >> 16) & 255u) / 255.);
 }
+// Sign of sin(x) without evaluating it: k = round(x/π), r = x − kπ with π split into three doubles (Cody–Waite; the
+// reduction error is ~|k|·1e-33).  Returns +1 / −1, or 0 when r is too close to a zero of sin (or x too large) to be sure —
+// the caller then evaluates the real expression.  The checker texture only needs `sin(a)·sin(b) < 0` (material.rs:556-561),
+// and two f64 sin() were 13 % of the floor's shade kernel (ncu r01).
+__device__ __forceinline__ int sin_sign(double x) {
+    if (!(fabs(x) < 1e9)) return 0;
+    const double k = rint(x * 0.31830988618379067154);
+    double r = fma(-k, 3.141592653589793116, x);
+    r = fma(-k, 1.2246467991473532072e-16, r);
+    r = fma(-k, -2.9947698097183396659e-33, r);
+    if (!(fabs(r) > 1e-9)) return 0;
+    const bool odd = ((long long)k) & 1ll;
+    return ((r < 0.) != odd) ? -1 : 1;
+}
 static __device__ __noinline__ D3 tex_value(const DScene& sc, uint32_t id, double u, double v) {
     for (int depth = 0; depth < 8; depth++) {
         const rt_texture& t = sc.textures[id];
         if (t.type == RT_TEX_SOLID) return mk3(t.color[0], t.color[1], t.color[2]);
         if (t.type != RT_TEX_CHECKERED) return texel_value(sc, t, u, v);
-        double mult = sin(t.frequency * u * 2. * PI) * sin(t.frequency * v * 2. * PI);
-        id = mult < 0. ? t.even : t.odd;
+        const double a = t.frequency * u * 2. * PI, b = t.frequency * v * 2. * PI;
+        const int sa = sin_sign(a), sb = sin_sign(b);
+        bool neg;
+        if (sa != 0 && sb != 0) neg = sa != sb;               // both sines are safely non-zero: their product is negative iff the signs differ
+        else { double mult = sin(a) * sin(b); neg = mult < 0.; }
+        id = neg ? t.even : t.odd;
     }
     return mk3(0., 0., 0.);
 }
