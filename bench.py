@@ -122,6 +122,7 @@ def main():
     ap.add_argument("--spp", type=int, default=256)
     ap.add_argument("--size", type=int, default=1024)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--wavefront", type=int, default=1 << 25, help="paths in flight per GPU")
     ap.add_argument("--shade", default="f32", choices=["f32", "f64"], help="radiometric precision of the shade kernel (geometry is f64-exact in both)")
     args = ap.parse_args()
     rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
@@ -144,6 +145,7 @@ def main():
     t0 = time.time()
     objects = hs.upload()                                 # BVH build + flatten + H2D (outside the timed region: scene build is not the hot path)
     build_s = time.time() - t0
+    objects.set_wavefront_size(args.wavefront)          # paths in flight; ~480 B of queue state each (16 GB at 32 Mi)
     cam = hs.camera()
     integ = IntType.Path(DEPTH, shade_f32=(args.shade == "f32"))
     film_t = torch.zeros(H * W * 4, dtype=torch.float64, device=f"cuda:{local}")      # torch owns the film so NCCL can reduce it in place
@@ -222,8 +224,8 @@ def main():
         "dtype": "f64 geometry (intersection, hit points, rays) + f32 radiometry" if args.shade == "f32" else "f64", "data": "synthetic",
         "config": {"workload": f"{SCENE} rough-plastic (stand-in dragon mesh, 871,414 tris; dragon.obj is a missing blob) {W}x{H}, max_depth {DEPTH}, {spp} spp per GPU per step",
                    "parallelism": f"scene replicated, sample-range partition x{world}, NCCL all-reduce of the film" if world > 1 else "single GPU",
-                   "l2": "no explicit flush: every wavefront iteration streams ~1.4 GB of path/queue state (>> 126 MB L2); the BVH (33 MB nodes + 70 MB leaf slots) is meant to stay L2-resident",
-                   "wavefront_paths": 1 << 22, "bvh_build_s": round(build_s, 2)},
+                   "l2": "no explicit flush: every wavefront iteration streams several GB of path/queue state (>> 126 MB L2); the BVH (33 MB nodes + 70 MB leaf slots) is meant to stay L2-resident",
+                   "wavefront_paths": args.wavefront, "bvh_build_s": round(build_s, 2)},
         "samples_per_s": paths_all / wall,
         "rays": {"extend": tot["extend_rays"], "shadow": tot["shadow_rays"], "probe": tot["probe_rays"]},
         "device_ms_per_step": dev_ms / args.steps,

@@ -267,7 +267,7 @@ rt_status rt_render(rt_scene* scene, const rt_camera* camera, const rt_integrato
 /* GLOBAL_STATE.stop_render (main.rs:75,317-318; render.rs:93) */
 rt_status rt_render_cancel(rt_scene* scene);
 rt_status rt_get_counters(const rt_scene* scene, rt_counters* out);
-/* size of the wavefront (paths in flight); default 1<<22 */
+/* size of the wavefront (paths in flight, ~480 bytes of device queue state each); default 1<<24 */
 rt_status rt_set_wavefront_size(rt_scene* scene, uint32_t paths);
 
 #ifdef __cplusplus

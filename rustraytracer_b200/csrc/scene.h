@@ -24,7 +24,7 @@ struct rt_scene {
     uint32_t bin_mask = 0;                   // shading bins (material type * 2 + is_triangle) that occur in the scene
     // wavefront state (render.cu)
     void* wavefront = nullptr;
-    uint32_t wavefront_size = 1u << 22;
+    uint32_t wavefront_size = 1u << 24;   // paths in flight (≈ 480 B of queue state each: 8 GB); measured r01, dragon 128 spp: 4 Mi 1931, 8 Mi 2044, 16 Mi 2105, 32 Mi 2150 Mrays/s
     std::atomic<int> cancel{0};
     rt_counters counters{};
 };

@@ -184,7 +184,10 @@ __device__ __forceinline__ Hit trace_closest(const DScene& sc, D3 o, D3 d, doubl
             if (slot_test(sc, sc.slots, s, rx, tmin, tmax, t, prim)) {
                 if (best.prim == RT_NONE || t < best.t || (t == best.t && prim < best.prim)) {
                     best.t = t; best.prim = prim;
-                    ftmax = fminf(ftmax, f32_up(t));
+                    // Triangles ignore tmin (only t < 1e-4 is rejected, hittable.rs:360), so the best t can lie BELOW tmin; a closer
+                    // primitive then still has a box that straddles tmin (its f64 leaf-box test must pass), which is why the
+                    // culling interval never shrinks below [ftmin, ftmin]
+                    ftmax = fmaxf(fminf(ftmax, f32_up(t)), ftmin);
                 }
             }
         }
@@ -321,7 +324,7 @@ __device__ __forceinline__ void leaf_step(const DScene& sc, TState& s, int32_t* 
             if (prim != s.skip && (t < s.t_limit || (t == s.t_limit && prim < s.skip))) { s.occluded = true; s.cur = SENTINEL; return; }
         } else if (s.best.prim == RT_NONE || t < s.best.t || (t == s.best.t && prim < s.best.prim)) {
             s.best.t = t; s.best.prim = prim;
-            s.ftmax = fminf(s.ftmax, f32_up(t));
+            s.ftmax = fmaxf(fminf(s.ftmax, f32_up(t)), s.ftmin);     // see trace_closest: best t may lie below tmin for triangles
         }
     }
     s.cur = stack[--s.sp];

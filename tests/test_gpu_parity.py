@@ -374,3 +374,44 @@ def test_unoccluded_infinite_matches_oracle():
     far = p0 + d * 20000.0
     assert np.array_equal(unoccluded(gpu, p0, far, np.zeros(len(p0), dtype=np.uint32), infinite_light=True),
                           oracle.occluded(p0, far, np.zeros(len(p0), dtype=np.uint32), infinite=True))
+
+
+def test_device_resident_entry_points():
+    """rt_closest_device (persistent scheduler, the ray-cast sweep entry), rt_intersect_device and rt_occluded_device on
+    device buffers (torch tensors) against the host-buffer calls and the oracle."""
+    import ctypes as C
+    import torch
+    from rustraytracer_b200._native import check, lib
+    hs = scenes.HostScene("soup", 96, 96, n_tris=30000)
+    gpu = hs.upload()
+    oracle = orc.OracleScene(hs.tables())
+    cam = hs.camera()
+    rays = np.concatenate([cam.primary_rays(96, 96), random_rays(np.random.default_rng(7), 30000, -1.5, 1.5)])
+    n = len(rays)
+    d_rays = torch.from_numpy(rays.view(np.float64).reshape(n, 6).copy()).cuda()
+    d_prim = torch.full((n,), -2, dtype=torch.int32, device="cuda")
+    d_t = torch.zeros(n, dtype=torch.float64, device="cuda")
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    for _ in range(2):      # twice: the work counter must be reset between launches
+        d_prim.fill_(-2)
+        check(lib().rt_closest_device(gpu.h, n, C.c_void_p(d_rays.data_ptr()), 0.001, 1e308, C.c_void_p(d_prim.data_ptr()), C.c_void_p(d_t.data_ptr()), stream))
+        torch.cuda.synchronize()
+        prim = d_prim.cpu().numpy().view(np.uint32); t = d_t.cpu().numpy()
+        want, ties = oracle.intersect(rays, mode=1, want_ties=True)
+        same = prim == want["prim_index"]
+        in_tie = np.array([g in tt for g, tt in zip(prim, ties)]) & (prim != NONE)
+        bad = ~(same | in_tie)
+        assert not bad.any(), (f"{bad.sum()} of {n} differ; unwritten {(prim == np.uint32(0xFFFFFFFE)).sum()}; first bad ray {np.flatnonzero(bad)[:5]} got {prim[bad][:5]} "
+                               f"t {t[bad][:5]} want {want['prim_index'][bad][:5]} t {want['t'][bad][:5]}")
+        hit = same & (prim != NONE)
+        assert np.allclose(t[hit], want["t"][hit], rtol=T_RTOL, atol=0)
+        assert (prim != NONE).mean() > 0.3
+    host = get_intersection(gpu, rays)
+    assert np.array_equal(host["prim_index"], prim) and np.array_equal(host["t"][prim != NONE], t[prim != NONE])
+    d_hits = torch.zeros(n * N.hit_dtype.itemsize, dtype=torch.uint8, device="cuda")
+    check(lib().rt_intersect_device(gpu.h, n, C.c_void_p(d_rays.data_ptr()), 0.001, 1e308, C.c_void_p(d_hits.data_ptr()), stream))
+    torch.cuda.synchronize()
+    dev = d_hits.cpu().numpy().view(N.hit_dtype)
+    assert np.array_equal(dev["prim_index"], host["prim_index"]) and np.array_equal(dev["t"], host["t"]) and np.array_equal(dev["n"], host["n"])
+    # empty batch is a no-op
+    check(lib().rt_closest_device(gpu.h, 0, None, 0.001, 1e308, None, None, stream))

@@ -9,6 +9,8 @@ name = sys.argv[1] if len(sys.argv) > 1 else "plastic_dragon"
 variant, size, spp, depth, f32 = (int(x) for x in (sys.argv[2:7] + ["0", "512", "4", "8", "0"][len(sys.argv) - 2:]))
 hs = scenes.HostScene(name, size, size, variant=variant)
 gpu = hs.upload()
+if os.environ.get("RT_WAVEFRONT"):
+    gpu.set_wavefront_size(int(os.environ["RT_WAVEFRONT"]))
 cam = hs.camera()
 film = Film(size, size)
 for rep in range(2):
