@@ -74,6 +74,76 @@ template <class R> __device__ __forceinline__ V3<R> face_forward(V3<R> n, V3<R> 
 template <class R> __device__ __forceinline__ R pi() { return (R)PI; }
 template <class R> __device__ __forceinline__ R inv_pi() { return (R)(1.0 / PI); }          // consts.rs:41
 
+// ---- RT_SHADE_F32 mode, triangle hits: Mesh::intersects_triangle's record (hittable.rs:362-449) with the same f64 accept
+// arithmetic, hit point and uv as geom.cuh:prim_record_t<1> — the next ray starts at that point, textures are looked up at that
+// uv — but the shading frame (six normalisations, four cross products: a third of that function's instructions as f64
+// division / square-root sequences) in f32.  Its consumers in this mode are f32 anyway: the Bsdf frame and Light::l's sign test.
+__device__ __forceinline__ V3<float> nrm3f(V3<float> a) { float s = rsqrtf(__fmaf_rn(a.z, a.z, __fmaf_rn(a.y, a.y, a.x * a.x))); V3<float> r; r.x = a.x * s; r.y = a.y * s; r.z = a.z * s; return r; }
+__device__ __forceinline__ V3<float> crs3f(V3<float> a, V3<float> b) {
+    V3<float> r; r.x = __fmaf_rn(a.y, b.z, -(a.z * b.y)); r.y = __fmaf_rn(a.z, b.x, -(a.x * b.z)); r.z = __fmaf_rn(a.x, b.y, -(a.y * b.x)); return r;
+}
+__device__ __forceinline__ V3<float> f3(D3 a) { V3<float> r; r.x = (float)a.x; r.y = (float)a.y; r.z = (float)a.z; return r; }
+__device__ __forceinline__ D3 d3(V3<float> a) { return mk3((double)a.x, (double)a.y, (double)a.z); }
+static __device__ __noinline__ bool prim_record_tri_f32(const DScene& sc, uint32_t prim, D3 o, D3 d, double tmin, double tmax, Rec& r) {
+    const DPrim pr = sc.prims[prim];
+    r.prim = prim; r.mat = pr.mat;
+    const uint32_t* ti = sc.tri_index + pr.a;
+    const uint32_t i1 = ti[0], i2 = ti[1], i3 = ti[2];
+    const DMesh ms = sc.meshes[pr.info >> 6];
+    const D3 p0 = ld3(sc.points + 3 * (ms.p_base + i1)), p1 = ld3(sc.points + 3 * (ms.p_base + i2)), p2 = ld3(sc.points + 3 * (ms.p_base + i3));
+    const RayX rx = make_rayx(o, d);
+    double t, b0, b1, b2;
+    if (!tri_test(rx, p0, p1, p2, tmax, t, b0, b1, b2)) return false;
+    if (!tri_leaf_box(p0, p1, p2, o, d, tmin, tmax)) return false;
+    D2 uv0 = mk2(0., 0.), uv1 = mk2(1., 0.), uv2 = mk2(1., 1.);
+    if (pr.info & PI_HAS_UV) {
+        const double* u = sc.uvs; uv0 = mk2(u[2 * (ms.uv_base + i1)], u[2 * (ms.uv_base + i1) + 1]);
+        uv1 = mk2(u[2 * (ms.uv_base + i2)], u[2 * (ms.uv_base + i2) + 1]); uv2 = mk2(u[2 * (ms.uv_base + i3)], u[2 * (ms.uv_base + i3) + 1]);
+    }
+    const D2 duv02 = mk2(uv0.x - uv2.x, uv0.y - uv2.y), duv12 = mk2(uv1.x - uv2.x, uv1.y - uv2.y);
+    const D3 dp02 = p0 - p2, dp12 = p1 - p2;
+    const double determinant = duv02.x * duv12.y - duv02.y * duv12.x;
+    V3<float> dpdu;
+    if (fabs(determinant) < SMALL / 10000.) {
+        D3 n = cross(p2 - p0, p1 - p0);
+        if (norm2(n) == 0.) return false;                    // a hit/miss decision: stays f64
+        V3<float> nf = f3(n);                                // util::make_coordinate_system (util.rs:567-576), first vector only
+        if (fabsf(nf.x) > fabsf(nf.y)) { float s = rsqrtf(nf.x * nf.x + nf.z * nf.z); dpdu.x = -nf.z * s; dpdu.y = 0.f; dpdu.z = nf.x * s; }
+        else { float s = rsqrtf(nf.y * nf.y + nf.z * nf.z); dpdu.x = 0.f; dpdu.y = nf.z * s; dpdu.z = -nf.y * s; }
+    } else {
+        const double inv = 1. / determinant;
+        dpdu = f3((duv12.y * dp02 - duv02.y * dp12) * inv);
+    }
+    r.p = b0 * p0 + b1 * p1 + b2 * p2;
+    r.uv = mk2(b0 * uv0.x + b1 * uv1.x + b2 * uv2.x, b0 * uv0.y + b1 * uv1.y + b2 * uv2.y);
+    const V3<float> e02 = f3(dp02), e12 = f3(dp12);
+    V3<float> normal;
+    if (pr.info & PI_HAS_N) {
+        const double* nn = sc.normals;
+        normal = f3(b0 * ld3(nn + 3 * (ms.n_base + i1)) + b1 * ld3(nn + 3 * (ms.n_base + i2)) + b2 * ld3(nn + 3 * (ms.n_base + i3)));
+    } else normal = crs3f(e02, e12);
+    V3<float> gn = nrm3f(crs3f(e02, e12));
+    const V3<float> sn = nrm3f(normal);
+    V3<float> ss = nrm3f(dpdu);
+    V3<float> ts = nrm3f(crs3f(sn, ss));
+    if (ts.x * ts.x + ts.y * ts.y + ts.z * ts.z > 0.f) ss = nrm3f(crs3f(ts, sn));
+    else {                                                   // degenerate frame: make_coordinate_system(sn)
+        V3<float> a;
+        if (fabsf(sn.x) > fabsf(sn.y)) { float s = rsqrtf(sn.x * sn.x + sn.z * sn.z); a.x = -sn.z * s; a.y = 0.f; a.z = sn.x * s; }
+        else { float s = rsqrtf(sn.y * sn.y + sn.z * sn.z); a.x = 0.f; a.y = sn.z * s; a.z = -sn.y * s; }
+        ss = nrm3f(a); ts = nrm3f(crs3f(sn, a));
+    }
+    const V3<float> n2 = nrm3f(crs3f(ss, ts));               // set_shading_geometry(ss, ts, .., is_auth = true) (hittable.rs:191-210)
+    if (gn.x * n2.x + gn.y * n2.y + gn.z * n2.z < 0.f) { gn.x = -gn.x; gn.y = -gn.y; gn.z = -gn.z; }
+    const V3<float> df = f3(d);
+    r.front = df.x * gn.x + df.y * gn.y + df.z * gn.z < 0.f;   // set_front
+    r.sn = d3(n2); r.sdpdu = d3(ss);
+    r.n = r.front ? d3(gn) : -d3(gn);
+    r.t = t; r.wo = -d;
+    if (pr.info & PI_FLIP) r.front = !r.front;               // FlipFace (primitive.rs:300-310)
+    return true;
+}
+
 // ---- bxdf.rs:12-68
 template <class R> __device__ __forceinline__ R cos_sq_theta(V3<R> v) { return v.z * v.z; }
 template <class R> __device__ __forceinline__ R abs_cos_theta(V3<R> v) { return fabs(v.z); }
@@ -460,7 +530,9 @@ template <class R> __device__ __forceinline__ void lobe_init(Lobe<R>& l, int kin
     l.fresnel = F_NOOP; l.mfd_empty = true; l.alpha_x = R(0); l.alpha_y = R(0); l.eta_a = R(1); l.eta_b = R(1);
 }
 template <class R> __device__ __forceinline__ void bsdf_new(Bsdf<R>& b, const Rec& r) {                 // bsdf.rs:26-35
-    b.ns = cast3<R>(r.sn); b.ng = cast3<R>(r.n); b.ss = cast3<R>(r.sdpdu); b.ts = cast3<R>(normalize(cross(r.sn, r.sdpdu))); b.empty = false;
+    b.ns = cast3<R>(r.sn); b.ng = cast3<R>(r.n); b.ss = cast3<R>(r.sdpdu); b.empty = false;
+    if constexpr (sizeof(R) == 4) b.ts = nrm3f(crs3f(b.ns, b.ss));        // f32 mode: the frame is consumed in f32
+    else b.ts = cast3<R>(normalize(cross(r.sn, r.sdpdu)));
 }
 // Material::compute_scattering (material.rs:80-244), mode = RADIANCE, allow_lobes = true
 // lobe / fresnel arms a material type can build (material.rs:80-244); MAT < 0 = any

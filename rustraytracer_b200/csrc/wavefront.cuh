@@ -102,7 +102,10 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
         uint32_t prim = entry.y;
         bool is_some = prim != RT_NONE;
         Rec rec;
-        if (is_some) is_some = prim_record_t<CLS>(sc, prim, o, d, SMALL, INF, true, rec);
+        if (is_some) {
+            if constexpr (sizeof(R) == 4 && CLS == 1) is_some = prim_record_tri_f32(sc, prim, o, d, SMALL, INF, rec);   // f32 shading frame (shade.cuh)
+            else is_some = prim_record_t<CLS>(sc, prim, o, d, SMALL, INF, true, rec);
+        }
         bool alive = false;
         do {
             if (bounces == 0 || specular_bounce) {
