@@ -169,12 +169,25 @@ __device__ __forceinline__ void rec_from_partials(Rec& r, D3 p, D2 uv, D3 dpdu, 
     r.n = r.front ? n : -n;
 }
 
+// RT_SHADE_F32 mode: the same record with the two normalisations and the cross product in f32 (consumed in f32 there)
+__device__ __forceinline__ void rec_from_partials_f32(Rec& r, D3 p, D2 uv, D3 dpdu, D3 dpdv, double t, D3 ray_d) {
+    const float ux = (float)dpdu.x, uy = (float)dpdu.y, uz = (float)dpdu.z, vx = (float)dpdv.x, vy = (float)dpdv.y, vz = (float)dpdv.z;
+    float nx = __fmaf_rn(uy, vz, -(uz * vy)), ny = __fmaf_rn(uz, vx, -(ux * vz)), nz = __fmaf_rn(ux, vy, -(uy * vx));
+    const float sn = rsqrtf(__fmaf_rn(nz, nz, __fmaf_rn(ny, ny, nx * nx))), su = rsqrtf(__fmaf_rn(uz, uz, __fmaf_rn(uy, uy, ux * ux)));
+    nx *= sn; ny *= sn; nz *= sn;
+    r.sn = mk3((double)nx, (double)ny, (double)nz); r.sdpdu = mk3((double)(ux * su), (double)(uy * su), (double)(uz * su));
+    r.p = p; r.uv = uv; r.t = t; r.wo = -ray_d;
+    r.front = (float)ray_d.x * nx + (float)ray_d.y * ny + (float)ray_d.z * nz < 0.0f;
+    r.n = r.front ? r.sn : -r.sn;
+}
+
 // Primitive::intersects for ONE primitive with the full record (primitive.rs:247-316): used by shade and
 // by the rt_intersect epilogue on the closest primitive only.  Bitwise the same accept arithmetic as the
 // traversal, so it cannot disagree with it.  leaf_box = false gives Primitive::intersects_obj semantics
 // (primitive.rs:372-425) plus the FlipFace toggle being skipped by the caller.
 // CLS: 1 = the primitive is known to be a triangle, 0 = known parametric shape, 2 = decide at run time
-template <int CLS>
+// F32FRAME (RT_SHADE_F32 mode, parametric shapes): normal / dpdu normalisation in f32, everything else unchanged
+template <int CLS, bool F32FRAME = false>
 static __device__ __noinline__ bool prim_record_t(const DScene& sc, uint32_t prim, D3 o, D3 d, double tmin, double tmax, bool leaf_box, Rec& r) {
     DPrim pr = sc.prims[prim];
     uint32_t type = CLS == 1 ? (uint32_t)RT_PRIM_TRIANGLE : (pr.info & 7u);
@@ -248,7 +261,7 @@ static __device__ __noinline__ bool prim_record_t(const DScene& sc, uint32_t pri
             double cos_phi = p.x * inv_z_r, sin_phi = p.y * inv_z_r;
             D3 dpdu = mk3(-phi_max * p.y, phi_max * p.x, 0.);
             D3 dpdv = (theta_max - theta_min) * mk3(p.z * cos_phi, p.z * sin_phi, -rad * sin(theta));
-            rec_from_partials(r, p, mk2(u, v), dpdu, dpdv, t, d);
+            if (F32FRAME) rec_from_partials_f32(r, p, mk2(u, v), dpdu, dpdv, t, d); else rec_from_partials(r, p, mk2(u, v), dpdu, dpdv, t, d);
             r.p = r.p + center;
         } else {
             RectHit h;
@@ -260,7 +273,7 @@ static __device__ __noinline__ bool prim_record_t(const DScene& sc, uint32_t pri
             D3 dpdu = mk3(aa == 0 ? 1. : 0., aa == 1 ? 1. : 0., 0.);
             D3 dpdv = mk3(0., ba == 1 ? 1. : 0., ba == 2 ? 1. : 0.);
             if (sh[5] >= 0.) { const DXform& x = sc.xforms[(uint32_t)sh[5]]; p = xf_point(x.fwd, p); dpdu = xf_vector(x.fwd, dpdu); dpdv = xf_vector(x.fwd, dpdv); }
-            rec_from_partials(r, p, uv, dpdu, dpdv, h.t, d);
+            if (F32FRAME) rec_from_partials_f32(r, p, uv, dpdu, dpdv, h.t, d); else rec_from_partials(r, p, uv, dpdu, dpdv, h.t, d);
         }
     }
     if (leaf_box && (pr.info & PI_FLIP)) r.front = !r.front;                     // FlipFace (primitive.rs:300-310)

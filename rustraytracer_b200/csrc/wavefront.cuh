@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
         Rec rec;
         if (is_some) {
             if constexpr (sizeof(R) == 4 && CLS == 1) is_some = prim_record_tri_f32(sc, prim, o, d, SMALL, INF, rec);   // f32 shading frame (shade.cuh)
-            else is_some = prim_record_t<CLS>(sc, prim, o, d, SMALL, INF, true, rec);
+            else is_some = prim_record_t<CLS, sizeof(R) == 4>(sc, prim, o, d, SMALL, INF, true, rec);
         }
         bool alive = false;
         do {
@@ -137,12 +137,27 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
                     if (inf_light) infinite_sample_li(sc, light, rec.p, u_light, wid, light_pdf, color, p1);
                     else {
                         D3 n1; sample_area(sc, light.prim, u_light, p1, n1);
-                        double pdf = 1. / light.area;
-                        D3 wiu = p1 - rec.p;
-                        if (norm2(wiu) == 0.) pdf = 0.;
-                        else { D3 wn = normalize(wiu); pdf = pdf * norm2(rec.p - p1) / fabs(dot(n1, -wn)); }
-                        if (pdf == 0. || norm2(rec.p - p1) == 0.) { light_pdf = 0.; color = ld3(light.color); }
-                        else { wid = normalize(p1 - rec.p); light_pdf = pdf; color = light_l(light, n1, -wid); }
+                        if constexpr (sizeof(R) == 4) {
+                            // f32 mode: the sampled POINT stays f64 (it is the shadow ray's end point); the direction handed to the
+                            // BSDF and the area -> solid-angle factor are f32 (two f64 normalisations less)
+                            const D3 wiu = p1 - rec.p; const double d2 = norm2(wiu);
+                            if (d2 == 0.) { light_pdf = 0.; color = ld3(light.color); }
+                            else {
+                                const float inv = rsqrtf((float)d2);
+                                const V3<float> w = v3<float>((float)wiu.x * inv, (float)wiu.y * inv, (float)wiu.z * inv);
+                                const float cosl = fabsf((float)n1.x * w.x + (float)n1.y * w.y + (float)n1.z * w.z);
+                                wid = mk3((double)w.x, (double)w.y, (double)w.z);
+                                light_pdf = (double)((float)d2 / ((float)light.area * cosl));
+                                color = light_l(light, n1, -wid);
+                            }
+                        } else {
+                            double pdf = 1. / light.area;
+                            D3 wiu = p1 - rec.p;
+                            if (norm2(wiu) == 0.) pdf = 0.;
+                            else { D3 wn = normalize(wiu); pdf = pdf * norm2(rec.p - p1) / fabs(dot(n1, -wn)); }
+                            if (pdf == 0. || norm2(rec.p - p1) == 0.) { light_pdf = 0.; color = ld3(light.color); }
+                            else { wid = normalize(p1 - rec.p); light_pdf = pdf; color = light_l(light, n1, -wid); }
+                        }
                     }
                     if (light_pdf > 0. && !is_black(color)) {
                         V3<R> wi = cast3<R>(wid);
