@@ -45,6 +45,7 @@ rt_status upload_scene(rt_scene& s, const HostImage& img) {
     if ((st = up(s, s.xforms, d.xforms, b))) return st;
     if ((st = up(s, s.textures, d.textures, b))) return st;
     if ((st = up(s, s.materials, d.materials, b))) return st;
+    if ((st = up(s, img.mat_alpha, d.mat_alpha, b))) return st;
     if ((st = up(s, s.images, d.images, b))) return st;
     if ((st = up(s, s.texels, d.texels, b))) return st;
     // Infinite lights: upload the flat Distribution2D tables and turn the offsets kept in DLight into device pointers

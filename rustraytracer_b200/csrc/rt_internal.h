@@ -79,6 +79,8 @@ struct DScene {
     const double* shapes; const DXform* xforms;
     const rt_texture* textures; const rt_material* materials; const DLight* lights;
     const DImage* images; const uint32_t* texels;
+    const double* mat_alpha;                  // 2 per material: the microfacet alphas of Plastic / Glass / solid-textured Metal after the optional
+                                              // roughness remap (microfacet.rs:442-446: an f64 log per shaded vertex otherwise); NaN = evaluate on the device
     uint32_t n_nodes, n_prims, n_lights, n_slots;
     uint32_t has_infinite, pad0;              // any Light::Infinite in `lights` (misses then emit, light.rs:499-513)
 };

@@ -41,6 +41,7 @@ struct HostImage {
     std::vector<DLight> lights;
     // Infinite lights: flat Distribution2D tables, concatenated; DLight pointers hold OFFSETS (in doubles) until upload
     std::vector<double> dist;
+    std::vector<double> mat_alpha;           // 2 per material, NaN = not constant
 };
 rt_status build_host_image(const rt_scene& s, HostImage& img);
 rt_status upload_scene(rt_scene& s, const HostImage& img);   // device.cu

@@ -259,6 +259,26 @@ rt_status build_host_image(const rt_scene& s, HostImage& img) {
         } else sl.kind = 1;
         img.slots[sidx] = sl;
     }
+    // per-material microfacet alphas that do not depend on the hit point (material.rs:110-117,170-173,205-214)
+    auto remap_alpha = [](double roughness) {          // trowbridge_reitz_roughness_to_alpha (microfacet.rs:442-446)
+        roughness = std::fmax(roughness, 1e-5);
+        double x = std::log(roughness);
+        return 1.62142 + 0.819955 * x + 0.1734 * x * x + 0.0171201 * x * x * x + 0.000640711 * x * x * x * x;
+    };
+    img.mat_alpha.assign(2 * s.materials.size(), std::nan(""));
+    for (size_t i = 0; i < s.materials.size(); i++) {
+        const rt_material& m = s.materials[i];
+        double a[2] = {std::nan(""), std::nan("")};
+        if (m.type == RT_MAT_PLASTIC) { a[0] = a[1] = m.remap_roughness ? remap_alpha(m.f[0]) : m.f[0]; }
+        else if (m.type == RT_MAT_GLASS) { a[0] = m.remap_roughness ? remap_alpha(m.f[0]) : m.f[0]; a[1] = m.remap_roughness ? remap_alpha(m.f[1]) : m.f[1]; }
+        else if (m.type == RT_MAT_METAL) {
+            for (int k = 0; k < 2; k++) {
+                uint32_t tid = m.tex[3 + k] == RT_NONE ? m.tex[2] : m.tex[3 + k];
+                if (tid < s.textures.size() && s.textures[tid].type == RT_TEX_SOLID) a[k] = m.remap_roughness ? remap_alpha(s.textures[tid].color[0]) : s.textures[tid].color[0];
+            }
+        }
+        img.mat_alpha[2 * i] = a[0]; img.mat_alpha[2 * i + 1] = a[1];
+    }
     img.lights.resize(s.lights.size());
     for (size_t i = 0; i < s.lights.size(); i++) {
         DLight d; memset(&d, 0, sizeof(d));

@@ -94,7 +94,7 @@ static __device__ __noinline__ bool prim_record_tri_f32(const DScene& sc, uint32
     const RayX rx = make_rayx(o, d);
     double t, b0, b1, b2;
     if (!tri_test(rx, p0, p1, p2, tmax, t, b0, b1, b2)) return false;
-    if (!tri_leaf_box(p0, p1, p2, o, d, tmin, tmax)) return false;
+    // no leaf-box test here: extend has already accepted this primitive with the reference's full predicate (traverse.cuh)
     D2 uv0 = mk2(0., 0.), uv1 = mk2(1., 0.), uv2 = mk2(1., 1.);
     if (pr.info & PI_HAS_UV) {
         const double* u = sc.uvs; uv0 = mk2(u[2 * (ms.uv_base + i1)], u[2 * (ms.uv_base + i1) + 1]);
@@ -574,8 +574,8 @@ template <class R, int MAT> static __device__ __noinline__ void compute_scatteri
             D3 spec = tex_value(sc, m.tex[1], u, v);
             if (!is_black(spec)) {
                 if (b.empty) bsdf_new(b, r);
-                double rough = m.f[0];
-                if (m.remap_roughness) rough = tr_roughness_to_alpha(rough);
+                double rough = sc.mat_alpha[2 * r.mat];                                     // constant per material: remapped at commit
+                if (rough != rough) { rough = m.f[0]; if (m.remap_roughness) rough = tr_roughness_to_alpha(rough); }
                 Lobe<R>& l = b.lobes[b.n++];
                 lobe_init(l, L_MICRO_R, BSDF_REFLECTION | BSDF_GLOSSY, spec);
                 l.fresnel = F_DIELECTRIC; l.a = R(1.5); l.b = R(1);                        // eta_i, eta_t
@@ -595,7 +595,8 @@ template <class R, int MAT> static __device__ __noinline__ void compute_scatteri
                 l.aux = cast3<R>(t); l.eta_a = (R)eta; l.eta_b = R(1);
                 return;
             }
-            if (m.remap_roughness) { urough = tr_roughness_to_alpha(urough); vrough = tr_roughness_to_alpha(vrough); }
+            if (sc.mat_alpha[2 * r.mat] == sc.mat_alpha[2 * r.mat]) { urough = sc.mat_alpha[2 * r.mat]; vrough = sc.mat_alpha[2 * r.mat + 1]; }
+            else if (m.remap_roughness) { urough = tr_roughness_to_alpha(urough); vrough = tr_roughness_to_alpha(vrough); }
             if (!is_black(rr)) {
                 Lobe<R>& l = b.lobes[b.n++];
                 lobe_init(l, L_MICRO_R, BSDF_REFLECTION | BSDF_GLOSSY, rr);
@@ -614,8 +615,9 @@ template <class R, int MAT> static __device__ __noinline__ void compute_scatteri
             bsdf_new(b, r);
             D3 u_rough = tex_value(sc, m.tex[3] == RT_NONE ? m.tex[2] : m.tex[3], u, v);
             D3 v_rough = tex_value(sc, m.tex[4] == RT_NONE ? m.tex[2] : m.tex[4], u, v);
-            double ur = m.remap_roughness ? tr_roughness_to_alpha(u_rough.x) : u_rough.x;
-            double vr = m.remap_roughness ? tr_roughness_to_alpha(v_rough.x) : v_rough.x;
+            const double au = sc.mat_alpha[2 * r.mat], av = sc.mat_alpha[2 * r.mat + 1];
+            double ur = au == au ? au : (m.remap_roughness ? tr_roughness_to_alpha(u_rough.x) : u_rough.x);
+            double vr = av == av ? av : (m.remap_roughness ? tr_roughness_to_alpha(v_rough.x) : v_rough.x);
             Lobe<R>& l = b.lobes[b.n++];
             lobe_init(l, L_MICRO_R, BSDF_REFLECTION | BSDF_GLOSSY, mk3(1., 1., 1.));
             l.fresnel = F_CONDUCTOR; l.eta3 = cast3<R>(tex_value(sc, m.tex[0], u, v)); l.aux = cast3<R>(tex_value(sc, m.tex[1], u, v));

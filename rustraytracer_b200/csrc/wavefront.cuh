@@ -104,7 +104,10 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
         Rec rec;
         if (is_some) {
             if constexpr (sizeof(R) == 4 && CLS == 1) is_some = prim_record_tri_f32(sc, prim, o, d, SMALL, INF, rec);   // f32 shading frame (shade.cuh)
-            else is_some = prim_record_t<CLS, sizeof(R) == 4>(sc, prim, o, d, SMALL, INF, true, rec);
+            // leaf_box = false: extend has already accepted this primitive with the reference's full predicate (f64 leaf box ∧
+            // primitive test, traverse.cuh:slot_test); the record only needs t / barycentrics again, and `front` (the one field
+            // FlipFace toggles) is not consumed by the path integrator
+            else is_some = prim_record_t<CLS, sizeof(R) == 4>(sc, prim, o, d, SMALL, INF, false, rec);
         }
         bool alive = false;
         do {
