@@ -76,7 +76,18 @@ __global__ void __launch_bounds__(256) k_generate(const Ctrl* __restrict__ c, Re
         uint32_t k = n_cur + i;
         store_ray(ps.ray + k, o, d);
         store_aux(ps.aux + k, 1., 1., 1., pixel, rng.sample, rng.dim, 0u);
-        atomicAdd(film + 4 * (size_t)pixel + 3, 1.0);       // count += 1 (util.rs:231)
+        // the sample count `n += 1` of util::increment_color (util.rs:231) is added once per pixel by k_film_count at the end of the
+        // render: camera samples are generated in the fixed order g = sample * npix + pixel, so it is a function of the total alone
+    }
+}
+
+// cell.n += (samples of this pixel among the first `generated` camera samples) — replaces one f64 atomic per path in k_generate
+__global__ void k_film_count(RenderParams rp, unsigned long long generated, double* film) {
+    const unsigned long long npix = (unsigned long long)rp.ww * rp.wh;
+    const unsigned long long full = generated / npix, rest = generated % npix;
+    for (unsigned long long pi = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; pi < npix; pi += (unsigned long long)gridDim.x * blockDim.x) {
+        uint32_t px = rp.x0 + (uint32_t)(pi % rp.ww), py = rp.y0 + (uint32_t)(pi / rp.ww);
+        film[4 * ((size_t)py * rp.width + px) + 3] += (double)(full + (pi < rest ? 1ull : 0ull));
     }
 }
 
@@ -383,11 +394,15 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
     }
     k_prepare<<<1, 1, 0, st>>>(w.ctrl, w.W);         // account the last iteration
     CK(cudaMemcpyAsync(w.h_ctrl, w.ctrl, sizeof(Ctrl), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    // camera samples actually generated: all of them unless cancelled (the closing k_prepare claims n_new more that never run)
+    const unsigned long long generated = w.h_ctrl->c_paths - w.h_ctrl->n_new;
+    k_film_count<<<g256, 256, 0, st>>>(rp, generated, film->d);
     CK(cudaEventRecord(e_end, st));
     CK(cudaStreamSynchronize(st));
     CK(cudaGetLastError());
     rt_counters& c = s->counters;
-    c.paths = w.h_ctrl->c_paths; c.extend_rays = w.h_ctrl->c_extend; c.shadow_rays = w.h_ctrl->c_shadow; c.probe_rays = w.h_ctrl->c_probe; c.iterations = iter;
+    c.paths = generated; c.extend_rays = w.h_ctrl->c_extend; c.shadow_rays = w.h_ctrl->c_shadow; c.probe_rays = w.h_ctrl->c_probe; c.iterations = iter;
     float ms = 0; cudaEventElapsedTime(&ms, e_begin, e_end); c.render_ms = ms;
     for (size_t i = 2; i + 4 < n_ev; i += 5) {
         float a = 0, b = 0, cc = 0, d = 0;
