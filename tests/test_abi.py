@@ -166,3 +166,92 @@ def test_obj_parser_on_reference_asset():
     N.check(N.lib().rth_scene_mesh_sizes(h, 0, sz))
     assert sz[3] == 3 * 13312 and sz[0] == sz[1] == sz[2]       # 13,312 triangles, v/vt/vn
     N.lib().rth_scene_destroy(h)
+
+
+def _write_hdr(path, img_rgbe, rle):
+    """Radiance .hdr writer for the reader test: img_rgbe (h, w, 4) uint8; new-style RLE scanlines or flat quadruples."""
+    h, w, _ = img_rgbe.shape
+    with open(path, "wb") as f:
+        f.write(b"#?RADIANCE\nFORMAT=32-bit_rle_rgbe\n\n")
+        f.write(f"-Y {h} +X {w}\n".encode())
+        for y in range(h):
+            row = img_rgbe[y]
+            if not rle:
+                f.write(row.tobytes()); continue
+            f.write(bytes([2, 2, w >> 8, w & 255]))
+            for c in range(4):
+                x = 0
+                comp = row[:, c]
+                while x < w:
+                    run = 1
+                    while x + run < w and run < 127 and comp[x + run] == comp[x]:
+                        run += 1
+                    if run >= 3:
+                        f.write(bytes([128 + run, int(comp[x])])); x += run
+                    else:
+                        lit = 1
+                        while x + lit < w and lit < 128 and not (x + lit + 2 < w and comp[x + lit] == comp[x + lit + 1] == comp[x + lit + 2]):
+                            lit += 1
+                        f.write(bytes([lit])); f.write(comp[x:x + lit].tobytes()); x += lit
+
+
+@pytest.mark.parametrize("rle", [False, True])
+def test_hdr_reader_matches_rgbe_definition(tmp_path, rle):
+    """Texture::new_hdr's decoder (image 0.23 HdrDecoder): pixel = c * 2^(e-136) as f32, 0 when e == 0."""
+    rng = np.random.default_rng(3)
+    w, h = 40, 7
+    img = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+    img[:, 5:20, :] = img[:, 5:6, :]            # runs for the RLE path
+    img[2, 3, 3] = 0                            # e == 0 -> black
+    img[..., 3] = np.clip(img[..., 3].astype(int) % 40 + 110, 0, 255).astype(np.uint8); img[2, 3, 3] = 0
+    p = str(tmp_path / "t.hdr")
+    _write_hdr(p, img, rle)
+    ww, hh = C.c_uint32(), C.c_uint32()
+    N.check(N.lib().rth_load_hdr(p.encode(), C.byref(ww), C.byref(hh), None, 0))
+    assert (ww.value, hh.value) == (w, h)
+    out = np.zeros((h, w, 3), dtype=np.float32)
+    N.check(N.lib().rth_load_hdr(p.encode(), C.byref(ww), C.byref(hh), N.ptr(out), out.size))
+    e = img[..., 3].astype(np.float32)
+    want = img[..., :3].astype(np.float32) * np.exp2(e - 136.0)[..., None]
+    want[img[..., 3] == 0] = 0
+    assert np.array_equal(out, want.astype(np.float32))
+    assert N.lib().rth_load_hdr(str(tmp_path / "missing.hdr").encode(), C.byref(ww), C.byref(hh), None, 0) == N.RT_ERR_IO
+
+
+@pytest.mark.skipif(not os.path.exists(REF_DATA + "/material/textures/envmap.hdr"), reason="reference assets only exist in the build container")
+def test_hdr_reader_on_reference_asset():
+    ww, hh = C.c_uint32(), C.c_uint32()
+    N.check(N.lib().rth_load_hdr((REF_DATA + "/material/textures/envmap.hdr").encode(), C.byref(ww), C.byref(hh), None, 0))
+    assert (ww.value, hh.value) == (1024, 512)          # SURVEY.md appendix B: `-Y 512 +X 1024`
+    out = np.zeros((512, 1024, 3), dtype=np.float32)
+    N.check(N.lib().rth_load_hdr((REF_DATA + "/material/textures/envmap.hdr").encode(), C.byref(ww), C.byref(hh), N.ptr(out), out.size))
+    assert np.isfinite(out).all() and out.min() >= 0 and out.max() > 10
+    hs = scenes.HostScene("material_hdr", 32, 32, data_dir=REF_DATA)
+    assert hs.tables()["images"][0].shape == (512, 1024, 3)
+
+
+def test_image_and_infinite_light_validation():
+    """Errors are status codes, never a crash; these are all caught on the host before any device work."""
+    from rustraytracer_b200 import Objects
+    o = Objects()
+    tex = np.zeros(1, dtype=N.texture_dtype); tex[0]["type"] = N.TEX_HDR; tex[0]["image"] = 0
+    with pytest.raises(N.RtError):                       # image index out of range: images must be added first
+        o.set_textures(tex)
+    assert o.add_image_hdr(np.ones((2, 4, 3), dtype=np.float32)) == 0
+    assert o.add_image_rgb8(np.zeros((3, 3, 3), dtype=np.uint8)) == 1
+    o.set_textures(tex)
+    with pytest.raises(N.RtError):
+        N.check(N.lib().rt_scene_add_image_hdr(o.h, 0, 4, None, None))
+    lig = np.zeros(1, dtype=N.light_dtype); lig[0]["type"] = 7
+    with pytest.raises(N.RtError):
+        o.set_lights(lig)
+    # an Infinite light over a Checkered texture has a (0, 0) table in the reference (Texture::get_size) — refused at commit
+    tex = np.zeros(3, dtype=N.texture_dtype); tex[0]["type"] = N.TEX_CHECKERED; tex[0]["odd"] = 1; tex[0]["even"] = 2
+    o.set_textures(tex)
+    mat = np.zeros(1, dtype=N.material_dtype); mat[0]["tex"] = N.RT_NONE; mat[0]["tex"][0] = 1
+    o.set_materials(mat)
+    lig = np.zeros(1, dtype=N.light_dtype); lig[0]["type"] = N.LIGHT_INFINITE; lig[0]["text_id"] = 0; lig[0]["transform"] = N.RT_NONE; lig[0]["prim_index"] = N.RT_NONE
+    o.set_lights(lig)
+    with pytest.raises(N.RtError) as ei:
+        o.commit()
+    assert ei.value.status == N.RT_ERR_INVALID

@@ -415,3 +415,82 @@ def test_device_resident_entry_points():
     assert np.array_equal(dev["prim_index"], host["prim_index"]) and np.array_equal(dev["t"], host["t"]) and np.array_equal(dev["n"], host["n"])
     # empty batch is a no-op
     check(lib().rt_closest_device(gpu.h, 0, None, 0.001, 1e308, None, None, stream))
+
+
+def test_full_size_properties():
+    """BASELINE.json's headline size (dragon, 1024x1024, depth 8) through size-independent properties: every pixel gets
+    exactly spp samples, nothing is NaN/negative, sample ranges are additive, the wavefront size (scheduling) does not
+    change the film beyond the rounding of the f64 atomics' order, and the image agrees with a CPU-oracle render of a
+    pixel subset at the same sample indices."""
+    w = h = 1024
+    spp = 8
+    hs = scenes.HostScene("plastic_dragon", w, h)
+    gpu = hs.upload()
+    cam = hs.camera()
+    it = IntType.Path(8, shade_f32=True)
+    a = Film(w, h); render_samples(gpu, cam, it, a, w, h, 0, spp, seed=77)
+    A = a.read()
+    c = gpu.counters()
+    assert c["paths"] == w * h * spp and c["extend_rays"] >= c["paths"] and c["shadow_rays"] > 0
+    assert np.all(A[..., 3] == spp) and np.isfinite(A).all() and (A[..., :3] >= 0).all()
+    gpu.set_wavefront_size(1 << 19)                       # 16 wavefronts instead of 1: a different schedule
+    b = Film(w, h)
+    render_samples(gpu, cam, it, b, w, h, 0, 3, seed=77)
+    render_samples(gpu, cam, it, b, w, h, 3, spp, seed=77)
+    B = b.read()
+    assert np.allclose(A, B, rtol=1e-9, atol=1e-12)
+    # f64 parity mode on every 37th pixel row against the oracle at the same (pixel, sample) RNG keys
+    rows = list(range(5, h, 37))
+    g64 = Film(w, h)
+    for y in rows:
+        render_samples(gpu, cam, IntType.Path(8), g64, w, h, 0, 2, seed=77, window=(0, y, w, y + 1))
+    G = g64.read()
+    oracle = orc.OracleScene(hs.tables())
+    O = np.zeros((h, w, 4))
+    for y in rows:
+        oracle.render(cam, w, h, 0, 2, seed=77, max_depth=8, window=(0, y, w, y + 1), film=O)
+    sel = np.zeros((h, w), dtype=bool); sel[rows] = True
+    assert np.array_equal(G[..., 3], O[..., 3])
+    err = np.abs(G[sel][:, :3] - O[sel][:, :3]).max(-1) / (np.abs(O[sel][:, :3]).max(-1) + 1e-6)
+    assert (err > 1e-7).mean() < 2e-3, f"{(err > 1e-7).sum()} of {err.size} full-size pixels differ from the oracle"
+    # and the f32 production film agrees with the f64 one statistically on those rows (same RNG keys, first two samples)
+    f32 = Film(w, h)
+    for y in rows:
+        render_samples(gpu, cam, it, f32, w, h, 0, 2, seed=77, window=(0, y, w, y + 1))
+    F = f32.read()
+    assert abs(F[sel][:, :3].mean() - G[sel][:, :3].mean()) <= 0.01 * G[sel][:, :3].mean()
+
+
+def test_render_cancel():
+    """GLOBAL_STATE.stop_render (main.rs:317, render.rs:93) ⇔ rt_render_cancel from another thread: rt_render returns
+    RT_ERR_CANCELLED, and the film's sample counts follow the generation order (whole passes + a prefix of the next)."""
+    import threading
+    import time
+    from rustraytracer_b200._native import RtError, lib
+    w = h = 512
+    hs = scenes.HostScene("plastic_dragon", w, h)
+    gpu = hs.upload()
+    gpu.set_wavefront_size(1 << 16)                       # many iterations so that the flag is polled often
+    cam = hs.camera()
+    film = Film(w, h)
+    result = {}
+
+    def run():
+        try:
+            render_samples(gpu, cam, IntType.Path(8, shade_f32=True), film, w, h, 0, 4096, seed=1)
+            result["status"] = 0
+        except RtError as e:
+            result["status"] = e.status
+    th = threading.Thread(target=run); th.start()
+    time.sleep(0.3)
+    lib().rt_render_cancel(gpu.h)
+    th.join(timeout=60)
+    assert not th.is_alive()
+    assert result["status"] == N.RT_ERR_CANCELLED
+    n = film.read()[..., 3].reshape(-1)
+    c = gpu.counters()
+    assert 0 < c["paths"] < w * h * 4096 and n.sum() == c["paths"]
+    assert n.max() - n.min() <= 1 and np.all(np.diff(n) <= 0)       # generation order: a prefix of the pixels is one sample ahead
+    # the scene stays usable
+    film2 = Film(w, h); render_samples(gpu, cam, IntType.Path(8, shade_f32=True), film2, w, h, 0, 1, seed=1)
+    assert np.all(film2.read()[..., 3] == 1)
