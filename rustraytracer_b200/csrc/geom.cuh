@@ -43,7 +43,8 @@ __device__ __forceinline__ D3 ld3(const double* p) { return mk3(p[0], p[1], p[2]
 struct RayX {
     D3 o, d;
     int kz;
-    double sx, sy, sz;
+    double sx, sy;
+    D3 inv;                 // 1.0 / d per axis: the `inv_d` of BoundingBox::intersects (hittable.rs:497), computed once per ray; sz = inv[kz]
 };
 __device__ __forceinline__ RayX make_rayx(D3 o, D3 d) {
     RayX r; r.o = o; r.d = d;
@@ -54,7 +55,8 @@ __device__ __forceinline__ RayX make_rayx(D3 o, D3 d) {
     r.kz = kz;
     int kx = (kz + 1) % 3, ky = (kx + 1) % 3;
     double dx = comp(d, kx), dy = comp(d, ky), dz = comp(d, kz);
-    r.sx = -dx / dz; r.sy = -dy / dz; r.sz = 1. / dz;
+    r.sx = -dx / dz; r.sy = -dy / dz;
+    r.inv = mk3(1. / d.x, 1. / d.y, 1. / d.z);
     return r;
 }
 __device__ __forceinline__ D3 permute(D3 v, int kz) {  // (v[kx], v[ky], v[kz])
@@ -74,7 +76,8 @@ __device__ __forceinline__ bool tri_test(const RayX& r, D3 p0, D3 p1, D3 p2, dou
     if ((e0 < 0. || e1 < 0. || e2 < 0.) && (e0 > 0. || e1 > 0. || e2 > 0.)) return false;
     double det = e0 + e1 + e2;
     if (fabs(det) < SMALL / 10000.) return false;
-    p0t.z *= r.sz; p1t.z *= r.sz; p2t.z *= r.sz;
+    const double sz = comp(r.inv, r.kz);                // 1. / d[kz]
+    p0t.z *= sz; p1t.z *= sz; p2t.z *= sz;
     double t_scaled = e0 * p0t.z + e1 * p1t.z + e2 * p2t.z;
     if (det < 0. && (t_scaled >= 0. || t_scaled < tmax * det)) return false;
     else if (det > 0. && (t_scaled <= 0. || t_scaled > tmax * det)) return false;
@@ -97,6 +100,24 @@ __device__ __forceinline__ bool slab_test(D3 mn, D3 mx, D3 o, D3 d, double tmin,
         if (tmax <= tmin) return false;
     }
     return true;
+}
+// the same test with the ray's precomputed 1.0 / d (bitwise the same quotients)
+__device__ __forceinline__ bool slab_test_inv(D3 mn, D3 mx, D3 o, D3 inv, double tmin, double tmax) {
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+        double inv_d = comp(inv, a);
+        double val1 = (comp(mn, a) - comp(o, a)) * inv_d;
+        double val2 = (comp(mx, a) - comp(o, a)) * inv_d;
+        double t0 = fmin(val1, val2), t1 = fmax(val1, val2);
+        tmin = fmax(tmin, t0); tmax = fmin(tmax, t1);
+        if (tmax <= tmin) return false;
+    }
+    return true;
+}
+__device__ __forceinline__ bool tri_leaf_box_inv(D3 p0, D3 p1, D3 p2, D3 o, D3 inv, double tmin, double tmax) {
+    D3 mn = mk3(fmin(p0.x, fmin(p1.x, p2.x)), fmin(p0.y, fmin(p1.y, p2.y)), fmin(p0.z, fmin(p1.z, p2.z)));
+    D3 mx = mk3(fmax(p0.x, fmax(p1.x, p2.x)), fmax(p0.y, fmax(p1.y, p2.y)), fmax(p0.z, fmax(p1.z, p2.z)));
+    return slab_test_inv(mn, mx, o, inv, tmin, tmax);
 }
 __device__ __forceinline__ bool tri_leaf_box(D3 p0, D3 p1, D3 p2, D3 o, D3 d, double tmin, double tmax) {
     D3 mn = mk3(fmin(p0.x, fmin(p1.x, p2.x)), fmin(p0.y, fmin(p1.y, p2.y)), fmin(p0.z, fmin(p1.z, p2.z)));
@@ -146,10 +167,10 @@ __device__ __forceinline__ bool rect_test(uint32_t type, const double* sh, const
 }
 
 // Exact accept test of one non-triangle primitive incl. its f64 leaf box: hit(prim) = leafbox ∧ primtest
-__device__ __forceinline__ bool shape_test(const DScene& sc, const DPrim& pr, D3 o, D3 d, double tmin, double tmax, bool leaf_box, double& t) {
+__device__ __forceinline__ bool shape_test(const DScene& sc, const DPrim& pr, D3 o, D3 d, double tmin, double tmax, bool leaf_box, double& t, const D3* inv = nullptr) {
     uint32_t type = pr.info & 7u;
     const double* sh = sc.shapes + pr.a;
-    if (leaf_box && !slab_test(ld3(sh + 6), ld3(sh + 9), o, d, tmin, tmax)) return false;
+    if (leaf_box && !(inv ? slab_test_inv(ld3(sh + 6), ld3(sh + 9), o, *inv, tmin, tmax) : slab_test(ld3(sh + 6), ld3(sh + 9), o, d, tmin, tmax))) return false;
     if (type == RT_PRIM_SPHERE) return sphere_test(ld3(sh), sh[3], o, d, tmin, tmax, t);
     RectHit h;
     if (!rect_test(type, sh, sc.xforms, o, d, tmin, tmax, h)) return false;

@@ -74,9 +74,9 @@ constexpr int32_t SENTINEL = 0x7fffffff;
 // k's entry distance with its slot number in the two low mantissa bits (non-negative floats order like ints), +inf for a
 // miss — so four min/max compare-exchanges sort the children front to back without moving (distance, index) pairs around.
 __device__ __forceinline__ unsigned node4_test(const float4* __restrict__ np, const RayF& r, float tmin, float tmax, int32_t key[4], int4& ch) {
-    const float4 mnx = __ldg(np), mxx = __ldg(np + 1), mny = __ldg(np + 2), mxy = __ldg(np + 3), mnz = __ldg(np + 4), mxz = __ldg(np + 5);
+    // near / far planes picked by the load address (rows are min-x, max-x, min-y, ...; s* = 1 for a negative direction) instead of 24 selects
+    const float4 nx = __ldg(np + r.sx), fx = __ldg(np + (r.sx ^ 1)), ny = __ldg(np + 2 + r.sy), fy = __ldg(np + (3 - r.sy)), nz = __ldg(np + 4 + r.sz), fz = __ldg(np + (5 - r.sz));
     ch = __ldg(reinterpret_cast<const int4*>(np + 6));
-    const float4 nx = r.sx ? mxx : mnx, fx = r.sx ? mnx : mxx, ny = r.sy ? mxy : mny, fy = r.sy ? mny : mxy, nz = r.sz ? mxz : mnz, fz = r.sz ? mnz : mxz;
     unsigned mask = 0;
 #define RT_CHILD(c, k)                                                                                                              \
     {                                                                                                                               \
@@ -134,11 +134,11 @@ __device__ __forceinline__ bool slot_test(const DScene& sc, const DSlot* __restr
         D3 p0 = mk3(q0.x, q0.y, q1.x), p1 = mk3(q1.y, q2.x, q2.y), p2 = mk3(q3.x, q3.y, q4.x);
         double b0, b1, b2;
         if (!tri_test(rx, p0, p1, p2, tmax, t, b0, b1, b2)) return false;
-        return tri_leaf_box(p0, p1, p2, rx.o, rx.d, tmin, tmax);
+        return tri_leaf_box_inv(p0, p1, p2, rx.o, rx.inv, tmin, tmax);
     }
     if (tag.y == 2) return false;    // triangle the reference can never hit (degenerate uv frame ∧ zero normal, hittable.rs:373-378)
     DPrim pr = sc.prims[prim];
-    return shape_test(sc, pr, rx.o, rx.d, tmin, tmax, true, t);
+    return shape_test(sc, pr, rx.o, rx.d, tmin, tmax, true, t, &rx.inv);
 }
 
 // closest hit in the reference's sense over [tmin, tmax]
@@ -330,6 +330,81 @@ __device__ __forceinline__ void leaf_step(const DScene& sc, TState& s, int32_t* 
     s.cur = stack[--s.sp];
 }
 
+// Leaf phase, compacted over the warp.  After a node phase a warp holds a handful of lanes that sit on a leaf of 1..4 slots and
+// many lanes that do not; running leaf_step per lane leaves most of the warp idle for the most expensive code of the traversal
+// (the f64 reference-order tests; ncu: 7.4 of 32 lanes active in it).  Here the warp's (ray, slot) candidate pairs are
+// enumerated with a prefix sum and dealt out one per lane, whoever owns the ray: the tester lane reads the owner's ray from
+// shared memory (written once when the ray was fetched — it never changes during the walk), runs the exact test and posts
+// (t, prim); the owner then folds the results of its own slots.  The fold is a min over (t, prim) for closest-hit rays and an
+// "any" for shadow rays, so the order of the slots does not matter and the outcome is identical to leaf_step's.
+// MEASURED (dragon, 1024^2, 64 spp): extend 32.9 -> 34.3 ms, connect 21.5 -> 22.0 ms, i.e. slower, so it is OFF by default.  ncu shows why: the
+// lanes-per-instruction of the exact tests stays at 7.9 with compaction — the idle lanes come from the early-outs INSIDE the test (edge-function
+// reject, then det, then the leaf box), not from the 1..4 slot loop — while the 13 KB of shared memory per block costs 5 points of L1 hit rate.
+#ifndef RT_LEAF_COMPACT
+#define RT_LEAF_COMPACT 0
+#endif
+constexpr int TRACE_BLOCK = 128;            // block size of every persistent traversal kernel
+struct LeafShared {
+    double ray[13][TRACE_BLOCK];            // o.xyz, d.xyz, shear sx sy, 1/d xyz, tmin, tmax of the ray each thread owns
+    double res_t[TRACE_BLOCK];
+    uint32_t res_prim[TRACE_BLOCK];
+    int32_t kz[TRACE_BLOCK];
+    uint8_t pair[TRACE_BLOCK];              // per warp: pair p of this round -> owner lane | slot-in-leaf << 5
+};
+__device__ __forceinline__ void leaf_shared_store(LeafShared& sh, const TState& s) {
+    const int i = threadIdx.x;
+    sh.ray[0][i] = s.rx.o.x; sh.ray[1][i] = s.rx.o.y; sh.ray[2][i] = s.rx.o.z;
+    sh.ray[3][i] = s.rx.d.x; sh.ray[4][i] = s.rx.d.y; sh.ray[5][i] = s.rx.d.z;
+    sh.ray[6][i] = s.rx.sx; sh.ray[7][i] = s.rx.sy; sh.ray[8][i] = s.rx.inv.x; sh.ray[11][i] = s.rx.inv.y; sh.ray[12][i] = s.rx.inv.z;
+    sh.ray[9][i] = s.tmin; sh.ray[10][i] = s.tmax; sh.kz[i] = s.rx.kz;
+}
+__device__ __forceinline__ void leaf_phase_compact(const DScene& sc, LeafShared& sh, TState& s, int32_t* stack, bool active) {
+    const unsigned FULL = 0xffffffffu;
+    const int tid = threadIdx.x, lane = tid & 31, wbase = tid & ~31;
+    const bool at_leaf = active && s.cur < 0;
+    const uint32_t v = (uint32_t)~s.cur, first = v >> 2;
+    const int cnt = at_leaf ? (int)(v & 3u) + 1 : 0;
+    // prefix sum of the slot counts from three ballots (count - 1 has two bits)
+    const unsigned ml = __ballot_sync(FULL, at_leaf), b0 = __ballot_sync(FULL, at_leaf && (v & 1u)), b1 = __ballot_sync(FULL, at_leaf && (v & 2u));
+    const unsigned lt = (1u << lane) - 1u;
+    const int excl = __popc(ml & lt) + __popc(b0 & lt) + 2 * __popc(b1 & lt);
+    const int total = min(32, __popc(ml) + __popc(b0) + 2 * __popc(b1));
+    // one round of at most 32 pairs; a leaf that does not fit keeps its remaining slots for the next leaf phase
+    const int take = min(cnt, max(0, 32 - excl));
+    for (int k = 0; k < take; k++) sh.pair[wbase + excl + k] = (uint8_t)(lane | (k << 5));
+    __syncwarp();
+    const bool has = lane < total;
+    const int code = has ? sh.pair[tid] : lane;
+    const int owner = wbase + (code & 31);
+    const uint32_t slot = __shfl_sync(FULL, first, code & 31) + (uint32_t)(code >> 5);
+    double t = 0.; uint32_t prim = RT_NONE;
+    if (has) {
+        RayX rx;
+        rx.o = mk3(sh.ray[0][owner], sh.ray[1][owner], sh.ray[2][owner]); rx.d = mk3(sh.ray[3][owner], sh.ray[4][owner], sh.ray[5][owner]);
+        rx.sx = sh.ray[6][owner]; rx.sy = sh.ray[7][owner]; rx.inv = mk3(sh.ray[8][owner], sh.ray[11][owner], sh.ray[12][owner]); rx.kz = sh.kz[owner];
+        uint32_t p;
+        if (slot_test(sc, sc.slots, slot, rx, sh.ray[9][owner], sh.ray[10][owner], t, p)) prim = p;
+    }
+    sh.res_t[tid] = t; sh.res_prim[tid] = prim;
+    __syncwarp();
+    for (int k = 0; k < take; k++) {
+        const uint32_t hp = sh.res_prim[wbase + excl + k];
+        if (hp == RT_NONE) continue;
+        const double ht = sh.res_t[wbase + excl + k];
+        if (s.any) {
+            if (hp != s.skip && (ht < s.t_limit || (ht == s.t_limit && hp < s.skip))) s.occluded = true;
+        } else if (s.best.prim == RT_NONE || ht < s.best.t || (ht == s.best.t && hp < s.best.prim)) {
+            s.best.t = ht; s.best.prim = hp;
+            s.ftmax = fmaxf(fminf(s.ftmax, f32_up(ht)), s.ftmin);
+        }
+    }
+    if (at_leaf) {
+        if (s.any && s.occluded) s.cur = SENTINEL;
+        else if (take == cnt) s.cur = stack[--s.sp];
+        else s.cur = (int32_t)~(((first + (uint32_t)take) << 2) | (uint32_t)(cnt - take - 1));
+    }
+}
+
 #ifndef RT_REFILL
 #define RT_REFILL 20        // refetch when fewer than this many lanes of the warp hold a live ray
 #endif
@@ -345,6 +420,9 @@ __device__ __forceinline__ void trace_jobs(const DScene& sc, Job& job, uint32_t 
     TState st; st.cur = SENTINEL; st.sp = 0;
     bool active = false, exhausted = false;
     uint32_t idx = 0;
+#if RT_LEAF_COMPACT
+    __shared__ LeafShared lsh;
+#endif
     if (sc.n_nodes == 0) {      // empty scene: every ray misses
         for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
             if (job.load(i, st, stack)) { st.best.prim = RT_NONE; st.occluded = false; job.finish(i, st); }
@@ -361,6 +439,9 @@ __device__ __forceinline__ void trace_jobs(const DScene& sc, Job& job, uint32_t 
             if (!active) {
                 idx = base + __popc(idle & ((1u << lane) - 1u));
                 if (idx < n) active = job.load(idx, st, stack);
+#if RT_LEAF_COMPACT
+                if (active) leaf_shared_store(lsh, st);
+#endif
             }
             if (base + __popc(idle) >= n) exhausted = true;
         }
@@ -376,7 +457,11 @@ __device__ __forceinline__ void trace_jobs(const DScene& sc, Job& job, uint32_t 
                 if (at_node) node_step(sc, st, stack);
             }
             // leaf phase
+#if RT_LEAF_COMPACT
+            leaf_phase_compact(sc, lsh, st, stack, active);
+#else
             if (active && st.cur < 0) leaf_step(sc, st, stack);
+#endif
             if (active && st.cur == SENTINEL) { job.finish(idx, st); active = false; }
             unsigned act = __ballot_sync(FULL, active);
             if (act == 0u) break;

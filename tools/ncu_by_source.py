@@ -60,14 +60,15 @@ n = min(len(data), len(loc))
 tot_s, tot_i = sum(int(r[iS]) for r in data), sum(int(r[iI]) for r in data)
 by_file, by_line = collections.Counter(), collections.Counter()
 inst_file, inst_line = collections.Counter(), collections.Counter()
+thr_file = collections.Counter()
 static_file = collections.Counter()
 for k in range(n):
     f, ln = loc[k]
     by_file[f] += int(data[k][iS]); by_line[(f, ln)] += int(data[k][iS])
-    inst_file[f] += int(data[k][iI]); inst_line[(f, ln)] += int(data[k][iI]); static_file[f] += 1
-print("\nper file:            samples   warp-inst   static SASS")
+    inst_file[f] += int(data[k][iI]); inst_line[(f, ln)] += int(data[k][iI]); static_file[f] += 1; thr_file[f] += int(data[k][iT])
+print("\nper file:            samples   warp-inst   static SASS   lanes/inst")
 for f, v in by_file.most_common():
-    print(f"  {f:18s} {100 * v / tot_s:6.1f}%   {100 * inst_file[f] / tot_i:6.1f}%   {static_file[f]:6d}")
+    print(f"  {f:18s} {100 * v / tot_s:6.1f}%   {100 * inst_file[f] / tot_i:6.1f}%   {static_file[f]:6d}   {thr_file[f] / max(inst_file[f], 1):6.1f}")
 print("\ntop lines by samples:")
 for (f, ln), v in by_line.most_common(topn):
     print(f"  {f}:{ln:<5d} {100 * v / tot_s:5.2f}% samples  {100 * inst_line[(f, ln)] / tot_i:5.2f}% inst")
