@@ -217,7 +217,9 @@ def main():
     traffic = None
     tp = os.path.join(ROOT, "profiles", "extend_traffic_r01.json")
     if os.path.exists(tp):
-        traffic = json.load(open(tp)).get("dram_bytes_per_launch")
+        # ncu dram__bytes_read.sum + dram__bytes_write.sum of one captured k_extend launch, per ray of that launch, scaled to the
+        # average launch of this run (per launch, like `achieved`)
+        traffic = json.load(open(tp)).get("dram_bytes_per_ray", 0.0) * tot["extend_rays"] / max(launches, 1) or None
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * wall / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -230,7 +232,7 @@ def main():
         "rays": {"extend": tot["extend_rays"], "shadow": tot["shadow_rays"], "probe": tot["probe_rays"]},
         "device_ms_per_step": dev_ms / args.steps,
         "kernel_ms_per_step": {"extend": tot["extend_ms"] / args.steps, "shade+generate": tot["shade_ms"] / args.steps, "connect": tot["connect_ms"] / args.steps},
-        "gpu_launches": int(tot["iterations"] * 6 + args.steps),
+        "gpu_launches": int(tot["iterations"] * 6 + 2 * args.steps),      # per iteration: prepare, generate, extend, 2 shade bins, connect; per render: closing prepare + film count
         "clocks": clk,
         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": C.sizeof(N.Camera) + C.sizeof(N.IntegratorDesc) + C.sizeof(N.FilmDesc),
                 "d2h_bytes_per_step": H * W * 4 * 8, "ms_per_step": 1e3 * wall_e2e / args.steps},

@@ -36,7 +36,8 @@ typedef struct rth_params {
 /* name ∈ { "sphere_roughness" (scenes.rs:474), "make_world" (commented, scenes.rs:15-86, seeded),
  *          "cornell_box" (:89), "cornell_box_statue" (:200), "plastic_dragon" (:310),
  *          "two_dragons" (:549), "material_hdr" (:627, HDR environment = Light::Infinite),
- *          "soup"  }                                                          */
+ *          "teapot_hdr" (:744, plastic teapot on a transformed checkered floor rect under the HDR
+ *          environment), "soup"  }                                                          */
 rt_status   rth_scene_build(const char* name, const rth_params* params, rth_scene** out);
 void        rth_scene_destroy(rth_scene* s);
 /* the (String path, Camera, Samplers) a scene function returns */

@@ -557,6 +557,33 @@ void build_material_hdr(rth_scene& s, const rth_params& p) {
     s.png = "material.png";
 }
 
+// scenes.rs:744-811 `teapot_hdr()`: a nearly smooth white plastic teapot (lid = Mesh000, body = Mesh001; stand-in blobs where the
+// OBJ files are missing) on a checkered floor — an XY rect under the Tungsten floor transform — lit only by the HDR environment.
+void build_teapot_hdr(rth_scene& s, const rth_params& p) {
+    const double from[3] = {23.895, 11.2207, 0.0400773}, dir[3] = {-0.939631, -0.342149, -0.00519335}, up[3] = {-0.342144, 0.939646, -0.00189103};
+    const double to[3] = {from[0] + dir[0], from[1] + dir[1], from[2] + dir[2]};
+    camera_up(s, from, to, up, aspect_of(p), 35. / 2.);
+    uint32_t env = push_hdr_texture(s, add_envmap(s, p, "teapot/textures/envmap.hdr"));     // texts[0]
+    push_infinite_light(s, env);
+    double ident[16]; mat_identity(ident);
+    const double floor_m[16] = {-39.9766, 39.9766, -1.74743e-006, 0., 4.94249e-006, 2.47125e-006, -56.5355, 0., -39.9766, -39.9766, -5.2423e-006, 0., 0., 0., 0., 1.};
+    const double lo_lid[3] = {-1.35, 2.36, -1.35}, hi_lid[3] = {1.35, 3.15, 1.35}, lo_body[3] = {-3.0, 0.0, -2.0}, hi_body[3] = {3.43, 2.45, 2.0};
+    add_obj_or_blob(s, p, "teapot/models/Mesh000.obj", ident, 64, 63, 21, lo_lid, hi_lid);
+    add_obj_or_blob(s, p, "teapot/models/Mesh001.obj", ident, 128, 127, 22, lo_body, hi_body);
+    uint32_t len = (uint32_t)s.textures.size();
+    push_solid(s, 0.9, 0.9, 0.9); push_solid(s, 1., 1., 1.);
+    push_plastic(s, len, len + 1, 0.00001, true);      // material 0
+    len = (uint32_t)s.textures.size();
+    push_solid(s, 0.2, 0.2, 0.2); push_solid(s, 0.325, 0.31, 0.325); push_solid(s, 0.725, 0.71, 0.68);
+    push_checkered(s, len + 1, len + 2, 10.);
+    push_matte(s, len, 0.);          // material 1
+    push_matte(s, len + 3, 0.);      // material 2
+    push_mesh_triangles(s, 0, 0);
+    push_mesh_triangles(s, 1, 0);
+    push_prim(s, make_rect(RT_PRIM_XY_RECT, -1., -1., 1., 1., 0., 2, push_xform(s, floor_m)));
+    s.png = "teapot_hdr.png";
+}
+
 // triangle soup; centre ~ U[-1,1]^3, edges ~ U[-s,s]^3, s = 2 N^(-1/3), f32-exact values
 void build_soup(rth_scene& s, const rth_params& p) {
     uint64_t n = p.n_tris ? p.n_tris : 1000000;
@@ -603,6 +630,7 @@ rt_status rth_scene_build(const char* name, const rth_params* params, rth_scene*
     else if (n == "two_dragons") build_two_dragons(*s, *params);
     else if (n == "soup") build_soup(*s, *params);
     else if (n == "material_hdr") build_material_hdr(*s, *params);
+    else if (n == "teapot_hdr") build_teapot_hdr(*s, *params);
     else { delete s; rt::set_error("rth_scene_build: unknown scene '" + n + "'"); return RT_ERR_INVALID; }
     *out = s;
     return RT_OK;

@@ -128,5 +128,9 @@ def material_hdr(mat_num=0, width=720, height=720, spp=50, seed=0, data_dir=None
     return _scene_kw("material_hdr", width, height, spp, seed, dict(variant=mat_num, data_dir=data_dir))
 
 
+def teapot_hdr(width=1280, height=720, spp=50, seed=0, data_dir=None):                                     # scenes.rs:744
+    return _scene_kw("teapot_hdr", width, height, spp, seed, dict(data_dir=data_dir))
+
+
 def soup(n_tris, width=4096, height=4096, seed=0):
     return _scene_kw("soup", width, height, 1, 0, dict(n_tris=n_tris, seed=seed))

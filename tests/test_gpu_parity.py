@@ -88,7 +88,7 @@ def test_empty_and_single_primitive_scenes():
     compare_hits(get_intersection(gpu, rays), oracle.intersect(rays, mode=1), None, "single sphere")
 
 
-@pytest.mark.parametrize("name", ["sphere_roughness", "cornell_box", "make_world", "material_hdr"])
+@pytest.mark.parametrize("name", ["sphere_roughness", "cornell_box", "make_world", "material_hdr", "teapot_hdr"])
 def test_builtin_scene_rays(name):
     hs = scenes.HostScene(name, 128, 128)
     gpu = hs.upload()
@@ -196,7 +196,7 @@ def film_compare(g, o, what, tol=1e-7, max_bad=2e-3):
                                            ("plastic_dragon", {}, 8), ("plastic_dragon", {"variant": 1}, 8), ("two_dragons", {"variant": 1}, 16),
                                            ("cornell_box_statue", {"n_tris": 20000}, 8),
                                            ("material_hdr", {"variant": 0}, 8), ("material_hdr", {"variant": 1}, 8),
-                                           ("material_hdr", {"variant": 2}, 8), ("material_hdr", {"variant": 3}, 12)])
+                                           ("material_hdr", {"variant": 2}, 8), ("material_hdr", {"variant": 3}, 12), ("teapot_hdr", {}, 8)])
 def test_render_matches_oracle_per_pixel(name, kw, depth):
     w = h = 48
     spp = 4

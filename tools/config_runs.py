@@ -23,6 +23,7 @@ CONFIGS = [
     ("configs[2] plastic_dragon rough-metal 1024x1024 256spp depth8", "plastic_dragon", {"variant": 1}, 1024, 256, 8),
     ("configs[3] two_dragons glass+metal 2048x2048 128spp (one GPU's share of 1024) depth16", "two_dragons", {"variant": 1}, 2048, 128, 16),
     ("extra: material_hdr glass under the HDR environment 1024x1024 64spp depth12", "material_hdr", {"variant": 3}, 1024, 64, 12),
+    ("extra: teapot_hdr plastic teapot (stand-in) on the checkered floor under the HDR environment 1024x1024 64spp depth8", "teapot_hdr", {}, 1024, 64, 8),
 ]
 
 
