@@ -223,6 +223,23 @@ rt_status rt_scene_set_lights(rt_scene* scene, uint64_t n, const rt_light* light
 /* Builds the acceleration structure, flattens every table to its SoA device layout and
  * uploads it to the current device.  ⇔ BvhNode::new (hittable.rs:637-723).            */
 rt_status rt_scene_commit(rt_scene* scene);
+/* Which builder rt_scene_commit uses for the acceleration structure that replaces BvhNode::new (hittable.rs:637-752).
+ * The hit set does not depend on the tree, so both give bit-identical results; they trade build time for traversal speed.
+ *   RT_BUILD_HOST_SAH    (default) binned-SAH build on the host threads, ~0.7 s per million triangles, fastest traversal
+ *   RT_BUILD_DEVICE_LBVH Morton-code LBVH built on the GPU in milliseconds (time to first pixel; scenes that change often).
+ *                        Scenes of fewer than 8 primitives, or an LBVH deeper than the traversal stack allows, fall back to
+ *                        the host build (rt_build_stats.mode tells which one ran).
+ * The environment variable RT_BUILD=lbvh|sah overrides the call (benchmark tools).                                        */
+enum { RT_BUILD_HOST_SAH = 0, RT_BUILD_DEVICE_LBVH = 1 };
+rt_status rt_scene_set_build_mode(rt_scene* scene, uint32_t mode);
+typedef struct rt_build_stats {
+    uint32_t mode;           /* builder that produced the committed tree                       */
+    uint32_t max_stack;      /* worst-case traversal stack entries of the tree (limit 64)       */
+    uint64_t nodes;          /* BVH4 nodes                                                      */
+    double   build_ms;       /* tree build alone (host wall clock, or CUDA events for the LBVH) */
+    double   commit_ms;      /* whole rt_scene_commit: tables, build, upload                    */
+} rt_build_stats;
+rt_status rt_scene_build_stats(const rt_scene* scene, rt_build_stats* out);
 rt_status rt_scene_num_primitives(const rt_scene* scene, uint64_t* out);
 /* bytes of device memory held by the committed scene: nodes, leaf slots, tables */
 rt_status rt_scene_device_bytes(const rt_scene* scene, uint64_t* nodes, uint64_t* leaves, uint64_t* tables);

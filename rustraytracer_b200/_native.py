@@ -60,6 +60,13 @@ class HostParams(C.Structure):
                 ("n_tris", C.c_uint64), ("seed", C.c_uint64), ("data_dir", C.c_char_p)]
 
 
+BUILD_HOST_SAH, BUILD_DEVICE_LBVH = 0, 1
+
+
+class BuildStats(C.Structure):
+    _fields_ = [("mode", C.c_uint32), ("max_stack", C.c_uint32), ("nodes", C.c_uint64), ("build_ms", C.c_double), ("commit_ms", C.c_double)]
+
+
 # every symbol include/rtcore.h and include/rthost.h declare (tests check that they all resolve)
 RTCORE_SYMBOLS = [
     "rt_last_error_string", "rt_version_string", "rt_device_count", "rt_set_device", "rt_round_spp", "rt_camera_look_at",
@@ -68,7 +75,7 @@ RTCORE_SYMBOLS = [
     "rt_scene_set_lights", "rt_scene_commit", "rt_scene_num_primitives", "rt_scene_device_bytes", "rt_intersect",
     "rt_intersect_range", "rt_intersect_device", "rt_closest_device", "rt_occluded", "rt_occluded_device", "rt_film_create",
     "rt_film_create_external", "rt_film_destroy", "rt_film_clear", "rt_film_read", "rt_film_resolve_rgb8", "rt_render",
-    "rt_render_cancel", "rt_get_counters", "rt_set_wavefront_size",
+    "rt_render_cancel", "rt_get_counters", "rt_set_wavefront_size", "rt_scene_set_build_mode", "rt_scene_build_stats",
 ]
 RTHOST_SYMBOLS = [
     "rth_scene_build", "rth_scene_destroy", "rth_scene_camera", "rth_scene_png_name", "rth_scene_uses_standin", "rth_scene_counts",
@@ -117,6 +124,7 @@ def lib():
         "rt_film_create": [u32, u32, vp], "rt_film_create_external": [u32, u32, vp, vp], "rt_film_destroy": [vp],
         "rt_film_clear": [vp], "rt_film_read": [vp, vp], "rt_film_resolve_rgb8": [vp, vp],
         "rt_render": [vp, vp, vp, vp, vp], "rt_render_cancel": [vp], "rt_get_counters": [vp, vp], "rt_set_wavefront_size": [vp, u32],
+        "rt_scene_set_build_mode": [vp, u32], "rt_scene_build_stats": [vp, vp],
         "rth_scene_build": [C.c_char_p, vp, vp], "rth_scene_destroy": [vp], "rth_scene_camera": [vp, vp],
         "rth_scene_uses_standin": [vp], "rth_scene_counts": [vp, vp], "rth_scene_mesh_sizes": [vp, u32, vp],
         "rth_scene_mesh_copy": [vp, u32, vp, vp, vp, vp], "rth_scene_copy_primitives": [vp, vp], "rth_scene_copy_transforms": [vp, vp],

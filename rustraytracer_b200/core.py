@@ -159,6 +159,16 @@ class Objects:
         check(lib().rt_scene_num_primitives(self.h, C.byref(out)))
         return out.value
 
+    def set_build_mode(self, mode):
+        """"sah" (host binned SAH, default) or "lbvh" (Morton LBVH built on the GPU): which builder commit() uses."""
+        m = {"sah": N.BUILD_HOST_SAH, "lbvh": N.BUILD_DEVICE_LBVH}.get(mode, mode)
+        check(lib().rt_scene_set_build_mode(self.h, int(m)))
+
+    def build_stats(self):
+        b = N.BuildStats()
+        check(lib().rt_scene_build_stats(self.h, C.byref(b)))
+        return {k: getattr(b, k) for k, _ in N.BuildStats._fields_}
+
     def device_bytes(self):
         a, b, c = C.c_uint64(), C.c_uint64(), C.c_uint64()
         check(lib().rt_scene_device_bytes(self.h, C.byref(a), C.byref(b), C.byref(c)))

@@ -26,15 +26,38 @@ template <class T> static rt_status up(rt_scene& s, const std::vector<T>& h, con
     return RT_OK;
 }
 
-rt_status upload_scene(rt_scene& s, const HostImage& img) {
+rt_status upload_scene(rt_scene& s, HostImage& img) {
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) { set_error("no CUDA device: librtcore has no CPU path"); return RT_ERR_CUDA; }
     CK(cudaGetDevice(&s.device));
     DScene d{}; uint64_t b = 0;
     s.bytes_nodes = s.bytes_slots = s.bytes_tables = 0;
     rt_status st;
-    if ((st = up(s, img.nodes, d.nodes, s.bytes_nodes))) return st;
-    if ((st = up(s, img.slots, d.slots, s.bytes_slots))) return st;
+    uint32_t n_nodes = (uint32_t)img.nodes.size();
+    if (img.device_build) {
+#if RT_BVH_WIDTH == 4
+        // RT_BUILD_DEVICE_LBVH: boxes and primitive-ordered slots go up as temporaries, the tree is built where it will be walked
+        void *tb = nullptr, *ts = nullptr;
+        const uint32_t n = (uint32_t)img.slots.size();
+        CK(cudaMalloc(&tb, (size_t)n * sizeof(Box64)));
+        if (cudaMalloc(&ts, (size_t)n * sizeof(DSlot)) != cudaSuccess) { cudaFree(tb); set_error("upload: out of device memory"); return RT_ERR_CUDA; }
+        cudaMemcpy(tb, img.boxes.data(), (size_t)n * sizeof(Box64), cudaMemcpyHostToDevice);
+        cudaMemcpy(ts, img.slots.data(), (size_t)n * sizeof(DSlot), cudaMemcpyHostToDevice);
+        DNode4* nodes = nullptr; DSlot* slots = nullptr; float ms = 0.f;
+        st = build_bvh_device((const Box64*)tb, (const DSlot*)ts, n, &nodes, &n_nodes, &slots, &img.max_stack, &ms);
+        cudaFree(tb); cudaFree(ts);
+        if (st != RT_OK) return st;
+        s.allocations.push_back(nodes); s.allocations.push_back(slots);
+        d.nodes = nodes; d.slots = slots; img.build_ms = ms;
+        s.bytes_nodes = (uint64_t)n_nodes * sizeof(DNode4); s.bytes_slots = (uint64_t)n * sizeof(DSlot);
+        if (getenv("RT_TRACE_BUILD")) fprintf(stderr, "bvh: device LBVH, %u nodes, %u slots, worst-case stack %d, %.2f ms\n", n_nodes, n, img.max_stack, ms);
+#else
+        set_error("device BVH build needs RT_BVH_WIDTH == 4"); return RT_ERR_INVALID;
+#endif
+    } else {
+        if ((st = up(s, img.nodes, d.nodes, s.bytes_nodes))) return st;
+        if ((st = up(s, img.slots, d.slots, s.bytes_slots))) return st;
+    }
     if ((st = up(s, img.prims, d.prims, b))) return st;
     if ((st = up(s, img.meshes, d.meshes, b))) return st;
     if ((st = up(s, img.points, d.points, b))) return st;
@@ -61,7 +84,7 @@ rt_status upload_scene(rt_scene& s, const HostImage& img) {
     if ((st = up(s, lights, d.lights, b))) return st;
     s.bytes_tables = b;
     { void* cp = nullptr; CK(cudaMalloc(&cp, 16)); s.allocations.push_back(cp); s.d_counter = (uint32_t*)cp; }   // work counter of the persistent batch kernels
-    d.n_nodes = (uint32_t)img.nodes.size(); d.n_prims = (uint32_t)img.prims.size();
+    d.n_nodes = n_nodes; d.n_prims = (uint32_t)img.prims.size();
     d.n_lights = (uint32_t)img.lights.size(); d.n_slots = (uint32_t)img.slots.size();
     s.d = d;
     return RT_OK;

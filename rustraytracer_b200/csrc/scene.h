@@ -21,6 +21,8 @@ struct rt_scene {
     uint32_t* d_counter = nullptr;           // device work counter of the persistent batch kernels
     std::vector<void*> allocations;          // every cudaMalloc of this scene
     uint64_t bytes_nodes = 0, bytes_slots = 0, bytes_tables = 0;
+    uint32_t build_mode = 0;                 // RT_BUILD_*
+    rt_build_stats build_stats{};
     uint32_t bin_mask = 0;                   // shading bins (material type * 2 + is_triangle) that occur in the scene
     // wavefront state (render.cu)
     void* wavefront = nullptr;
@@ -42,9 +44,15 @@ struct HostImage {
     // Infinite lights: flat Distribution2D tables, concatenated; DLight pointers hold OFFSETS (in doubles) until upload
     std::vector<double> dist;
     std::vector<double> mat_alpha;           // 2 per material, NaN = not constant
+    // RT_BUILD_DEVICE_LBVH: `nodes` is empty, `slots` is in PRIMITIVE order and `boxes` holds the f64 primitive boxes; the uploader
+    // builds the tree on the device (bvh_device.cu) and permutes the slots into leaf order there
+    bool device_build = false; std::vector<Box64> boxes;
+    int max_stack = 0; double build_ms = 0.;
 };
-rt_status build_host_image(const rt_scene& s, HostImage& img);
-rt_status upload_scene(rt_scene& s, const HostImage& img);   // device.cu
+// bvh_device.cu
+rt_status build_bvh_device(const Box64* d_boxes, const DSlot* d_slots_in, uint32_t n, DNode4** nodes_out, uint32_t* n_nodes_out, DSlot** slots_out, int* max_stack_out, float* build_ms);
+rt_status build_host_image(const rt_scene& s, HostImage& img, bool device_build);
+rt_status upload_scene(rt_scene& s, HostImage& img);         // device.cu
 void free_scene_device(rt_scene& s);                          // device.cu
 void free_wavefront(rt_scene& s);                             // render.cu
 }

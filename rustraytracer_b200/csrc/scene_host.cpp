@@ -1,5 +1,6 @@
 // Host half of the C ABI: scene tables, primitive boxes, commit (BVH + SoA flatten).
 // No CUDA in this file.  Reference items are cited per function.
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -170,7 +171,7 @@ static rt_status build_infinite_light(const rt_scene& s, const rt_light& l, DLig
     return RT_OK;
 }
 
-rt_status build_host_image(const rt_scene& s, HostImage& img) {
+rt_status build_host_image(const rt_scene& s, HostImage& img, bool device_build) {
     size_t n = s.prims.size();
     // validate cross indices
     for (size_t i = 0; i < n; i++) {
@@ -230,12 +231,22 @@ rt_status build_host_image(const rt_scene& s, HostImage& img) {
     }
     if (ib >= (1ull << 32)) { set_error("index buffer exceeds 2^32 entries"); return RT_ERR_INVALID; }
     BuiltBvh bvh;
-    build_bvh(boxes, bvh, threads);
-    if (bvh.max_stack > TRAVERSAL_STACK) { set_error("commit: BVH needs a deeper traversal stack than the kernels have (" + std::to_string(bvh.max_stack) + " > " + std::to_string(TRAVERSAL_STACK) + ")"); return RT_ERR_INVALID; }
-    if (getenv("RT_TRACE_BUILD")) fprintf(stderr, "bvh: %zu nodes of %zu bytes, %zu slots, worst-case stack %d\n", bvh.nodes.size(), sizeof(DNodeT), n, bvh.max_stack);
-    img.nodes = std::move(bvh.nodes);
+    img.device_build = device_build && n >= 8;
+    if (img.device_build) {
+        bvh.order.resize(n);
+        for (size_t i = 0; i < n; i++) bvh.order[i] = (uint32_t)i;      // slots stay in primitive order; the device build permutes them
+    } else {
+        auto t0 = std::chrono::steady_clock::now();
+        build_bvh(boxes, bvh, threads);
+        img.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        img.max_stack = bvh.max_stack;
+        if (bvh.max_stack > TRAVERSAL_STACK) { set_error("commit: BVH needs a deeper traversal stack than the kernels have (" + std::to_string(bvh.max_stack) + " > " + std::to_string(TRAVERSAL_STACK) + ")"); return RT_ERR_INVALID; }
+        if (getenv("RT_TRACE_BUILD")) fprintf(stderr, "bvh: %zu nodes of %zu bytes, %zu slots, worst-case stack %d\n", bvh.nodes.size(), sizeof(DNodeT), n, bvh.max_stack);
+        img.nodes = std::move(bvh.nodes);
+    }
     img.slots.resize(n);
-    for (size_t sidx = 0; sidx < n; sidx++) {
+    auto fill_slots = [&](size_t sb, size_t se) {
+    for (size_t sidx = sb; sidx < se; sidx++) {
         uint32_t pi = bvh.order[sidx];
         const HostPrim& p = s.prims[pi];
         DSlot sl; memset(&sl, 0, sizeof(sl));
@@ -259,6 +270,13 @@ rt_status build_host_image(const rt_scene& s, HostImage& img) {
         } else sl.kind = 1;
         img.slots[sidx] = sl;
     }
+    };
+    {
+        std::vector<std::thread> pool; size_t chunk = (n + threads - 1) / std::max(threads, 1);
+        for (int t = 0; t < threads; t++) { size_t b = std::min(n, t * chunk), e = std::min(n, b + chunk); if (e > b) pool.emplace_back(fill_slots, b, e); }
+        for (auto& th : pool) th.join();
+    }
+    if (img.device_build) img.boxes = std::move(boxes);
     // per-material microfacet alphas that do not depend on the hit point (material.rs:110-117,170-173,205-214)
     auto remap_alpha = [](double roughness) {          // trowbridge_reitz_roughness_to_alpha (microfacet.rs:442-446)
         roughness = std::fmax(roughness, 1e-5);
@@ -458,16 +476,39 @@ rt_status rt_scene_set_lights(rt_scene* s, uint64_t n, const rt_light* l) {
 }
 rt_status rt_scene_commit(rt_scene* s) {
     if (!s) { set_error("rt_scene_commit: null scene"); return RT_ERR_INVALID; }
+    auto t0 = std::chrono::steady_clock::now();
+    bool device_build = s->build_mode == RT_BUILD_DEVICE_LBVH;
+    if (const char* e = getenv("RT_BUILD")) { if (!strcmp(e, "lbvh")) device_build = true; else if (!strcmp(e, "sah")) device_build = false; }
     HostImage img;
-    rt_status st = build_host_image(*s, img);
+    rt_status st = build_host_image(*s, img, device_build);
     if (st != RT_OK) return st;
     free_wavefront(*s); free_scene_device(*s);
     st = upload_scene(*s, img);
     if (st != RT_OK) return st;
+    if (img.device_build && img.max_stack > TRAVERSAL_STACK) {
+        // an LBVH over badly clustered Morton codes can be deeper than the traversal stack: take the host build instead
+        if (getenv("RT_TRACE_BUILD")) fprintf(stderr, "bvh: device LBVH needs a stack of %d > %d, falling back to the host build\n", img.max_stack, TRAVERSAL_STACK);
+        free_scene_device(*s);
+        img = HostImage();
+        if ((st = build_host_image(*s, img, false)) != RT_OK) return st;
+        if ((st = upload_scene(*s, img)) != RT_OK) return st;
+    }
+    s->build_stats.mode = img.device_build ? RT_BUILD_DEVICE_LBVH : RT_BUILD_HOST_SAH;
+    s->build_stats.max_stack = (uint32_t)img.max_stack; s->build_stats.nodes = s->d.n_nodes; s->build_stats.build_ms = img.build_ms;
+    s->build_stats.commit_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     s->bin_mask = 0;
     for (auto& p : s->prims) s->bin_mask |= 1u << (s->materials[p.mat].type * 2 + (p.type == RT_PRIM_TRIANGLE ? 1 : 0));
     s->committed = true;
     return RT_OK;
+}
+rt_status rt_scene_set_build_mode(rt_scene* s, uint32_t mode) {
+    if (!s || mode > RT_BUILD_DEVICE_LBVH) { set_error("rt_scene_set_build_mode: bad argument"); return RT_ERR_INVALID; }
+    s->build_mode = mode; return RT_OK;
+}
+rt_status rt_scene_build_stats(const rt_scene* s, rt_build_stats* out) {
+    if (!s || !out) { set_error("rt_scene_build_stats: null argument"); return RT_ERR_INVALID; }
+    if (!s->committed) { set_error("rt_scene_build_stats: scene not committed"); return RT_ERR_STATE; }
+    *out = s->build_stats; return RT_OK;
 }
 rt_status rt_scene_num_primitives(const rt_scene* s, uint64_t* out) {
     if (!s || !out) { set_error("rt_scene_num_primitives: null argument"); return RT_ERR_INVALID; }

@@ -85,10 +85,12 @@ class HostScene:
             images.append(px)
         return dict(meshes=meshes, prims=prims, transforms=xf, textures=tex, materials=mat, lights=lig, images=images)
 
-    def upload(self, commit=True):
-        """Push the tables through the public rt_scene_* ABI and commit (BVH build + device upload)."""
+    def upload(self, commit=True, build="sah"):
+        """Push the tables through the public rt_scene_* ABI and commit (BVH build + device upload).
+        build = "sah" (host binned SAH) or "lbvh" (device LBVH)."""
         obj = Objects()
         check(lib().rth_scene_upload(self.h, obj.h))
+        obj.set_build_mode(build)
         if commit:
             obj.commit()
         return obj

@@ -494,3 +494,55 @@ def test_render_cancel():
     # the scene stays usable
     film2 = Film(w, h); render_samples(gpu, cam, IntType.Path(8, shade_f32=True), film2, w, h, 0, 1, seed=1)
     assert np.all(film2.read()[..., 3] == 1)
+
+
+@pytest.mark.parametrize("name,kw", [("soup", {"n_tris": 200000}), ("plastic_dragon", {}), ("cornell_box_statue", {"n_tris": 20000}),
+                                     ("material_hdr", {"variant": 3}), ("sphere_roughness", {})])
+def test_device_lbvh_build_gives_the_same_hits(name, kw):
+    """RT_BUILD_DEVICE_LBVH (bvh_device.cu): the hit set is tree-independent (hit(prim) = f64 leaf box AND f64 primitive test), so
+    a scene committed with the device LBVH must answer every query exactly like the host SAH build — hit records bit for bit,
+    shadow queries, and a rendered film up to the order of the f64 film atomics."""
+    res = 192
+    hs = scenes.HostScene(name, res, res, **kw)
+    a = hs.upload(build="sah")
+    b = hs.upload(build="lbvh")
+    sa, sb = a.build_stats(), b.build_stats()
+    assert sa["mode"] == N.BUILD_HOST_SAH and sb["mode"] == N.BUILD_DEVICE_LBVH and 0 < sb["max_stack"] <= 64 and sb["nodes"] > 0
+    assert a.device_bytes()["leaves"] == b.device_bytes()["leaves"]
+    cam = hs.camera()
+    rays = cam.primary_rays(res, res)
+    ha, hb = get_intersection(a, rays), get_intersection(b, rays)
+    assert ha.tobytes() == hb.tobytes()
+    hit = ha["prim_index"] != NONE
+    assert hit.mean() > 0.2
+    rng = np.random.default_rng(8)
+    d = rng.normal(size=(hit.sum(), 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays2 = make_rays(ha["p"][hit], d)
+    h2a, h2b = get_intersection(a, rays2), get_intersection(b, rays2)
+    assert h2a.tobytes() == h2b.tobytes()
+    # against the oracle as well (a subset keeps the CPU side short)
+    oracle = orc.OracleScene(hs.tables())
+    compare_hits(h2b[::7], oracle.intersect(rays2[::7], mode=0), None, f"{name} lbvh bounce")
+    # shadow queries between pairs of hit points
+    p0 = ha["p"][hit]; p1 = np.roll(p0, 17, axis=0); tp = np.roll(ha["prim_index"][hit], 17)
+    assert np.array_equal(unoccluded(a, p0, p1, tp), unoccluded(b, p0, p1, tp))
+    # and a render: same RNG keys, same hits -> same film up to the summation order of the atomics
+    fa, fb = Film(res, res), Film(res, res)
+    render_samples(a, cam, IntType.Path(8), fa, res, res, 0, 2, seed=9)
+    render_samples(b, cam, IntType.Path(8), fb, res, res, 0, 2, seed=9)
+    assert np.allclose(fa.read(), fb.read(), rtol=1e-9, atol=1e-12, equal_nan=True)
+    ca, cb = a.counters(), b.counters()
+    assert (ca["extend_rays"], ca["shadow_rays"], ca["probe_rays"]) == (cb["extend_rays"], cb["shadow_rays"], cb["probe_rays"])
+
+
+def test_device_lbvh_small_scene_falls_back_to_host_build():
+    hs = scenes.HostScene("sphere_roughness", 32, 32)
+    tab = hs.tables()
+    tab["prims"] = tab["prims"][:5]
+    tab["lights"] = tab["lights"][:0]
+    tab["prims"]["light_index"] = NONE
+    obj = orc.upload_tables(tab)
+    obj.set_build_mode("lbvh"); obj.commit()
+    assert obj.build_stats()["mode"] == N.BUILD_HOST_SAH
+    rays = hs.camera().primary_rays(32, 32)
+    compare_hits(get_intersection(obj, rays), orc.OracleScene(tab).intersect(rays, mode=0), None, "5 prims")
