@@ -3,7 +3,7 @@
     python tools/soup_sweep.py [--sizes 1,2,5,10] [--res 4096] [--out profiles/soup_sweep_r01.json]
 
 For every triangle count N (in millions): builds the soup of SURVEY.md §8d (Philox-generated, f32-exact vertices), commits
-it (host binned-SAH build + upload, timed), then times `rt_closest_device` (closest-hit ids + t, 16 B out per ray) on
+it (host binned-SAH build + upload, or the device LBVH with RT_BUILD=lbvh; timed), then times `rt_closest_device` (closest-hit ids + t, 16 B out per ray) on
   * the coherent batch: res x res pixel-centre rays of a pinhole camera at (0,0,-4), vfov 40;
   * the incoherent batch: one cosine-distributed bounce ray per coherent hit (origin = hit point), uniform-sphere rays
     from U[-1,1]^3 origins where the primary missed.
@@ -92,9 +92,12 @@ def main():
         if dist:
             tt = torch.tensor([ms_c, ms_i], device=dev, dtype=torch.float64); dist.all_reduce(tt, op=dist.ReduceOp.MAX); ms_c, ms_i = tt.tolist()
         b = gpu.device_bytes()
+        bs = gpu.build_stats()
         row = {"tris": n_tris, "rays": n_all, "n_gpus": world, "coherent_Mrays_s": n_all / ms_c / 1e3, "incoherent_Mrays_s": n_all / ms_i / 1e3, "coherent_ms": ms_c, "incoherent_ms": ms_i,
                "hit_rate_coherent": hit_c, "hit_rate_incoherent": hit_i, "bvh_nodes_MB": b["nodes"] / 1e6, "leaf_slots_MB": b["leaves"] / 1e6, "tables_MB": b["tables"] / 1e6,
-               "scene_gen_s": round(gen_s, 2), "build_upload_s": round(build_s, 2)}
+               "scene_gen_s": round(gen_s, 2), "build_upload_s": round(build_s, 2),
+               "builder": "device LBVH" if bs["mode"] == 1 else "host binned SAH", "tree_build_ms": round(bs["build_ms"], 2), "commit_ms": round(bs["commit_ms"], 1),
+               "bvh4_nodes": bs["nodes"], "max_stack": bs["max_stack"]}
         if rank == 0:
             print(json.dumps(row), flush=True)
         rows.append(row)
