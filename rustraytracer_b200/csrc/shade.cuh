@@ -17,11 +17,27 @@ namespace rt {
 constexpr uint32_t BSDF_REFLECTION = 1, BSDF_TRANSMISSION = 2, BSDF_DIFFUSE = 4, BSDF_GLOSSY = 8, BSDF_SPECULAR = 16, BSDF_ALL = 31;  // consts.rs:14-20
 
 // ---- counter-based RNG replacing thread_rng()/StdRng::from_entropy() (sampler.rs:318,334-337; util.rs:32-34):
+// Inlining level of the shading code (measured r01, dragon 64 spp, shade ms: 0 = everything heavy is a call 40.8; 1 = BSDF code of the
+// Lambert / Oren-Nayar materials inlined 33.6; 2 = BSDF + lobe code of every material inlined 30.1; 3 / 4 see profiles/shade_r01_notes.md)
+#ifndef SHADE_INLINE_SMALL
+#define SHADE_INLINE_SMALL 2
+#endif
+#define RT_HELPER __noinline__          // microfacet / Fresnel helpers: inlining them too is slower (31.7 vs 30.2 ms)
+#if SHADE_INLINE_SMALL >= 3
+#define RT_HELPER2 __forceinline__      // functions that return through references (record, texture, area sample)
+#else
+#define RT_HELPER2 __noinline__
+#endif
+#if SHADE_INLINE_SMALL >= 4
+#define RT_HELPER3 __forceinline__      // the Philox block
+#else
+#define RT_HELPER3 __noinline__
+#endif
 // Philox4x32-10, key = seed, counter = (pixel, sample, dim >> 1, 'RTCX').
 // Each Philox block yields two uniforms: dimension d uses block d >> 1, words (0,1) when d is even, (2,3) when odd.
 // The block computed for an even dimension is kept for the odd one that follows.
 struct Rng { uint32_t k0, k1, pixel, sample, dim; uint32_t w2, w3; };
-static __device__ __noinline__ double rng_next(Rng& g) {
+static __device__ RT_HELPER3 double rng_next(Rng& g) {
     uint32_t d = g.dim++;
     if ((d & 1u) && g.w2 != 0xffffffffu) {                 // cached second half (0xffffffff marks "none"; a genuine all-ones word just recomputes)
         uint32_t a = g.w2, b = g.w3; g.w2 = 0xffffffffu;
@@ -84,7 +100,7 @@ __device__ __forceinline__ V3<float> crs3f(V3<float> a, V3<float> b) {
 }
 __device__ __forceinline__ V3<float> f3(D3 a) { V3<float> r; r.x = (float)a.x; r.y = (float)a.y; r.z = (float)a.z; return r; }
 __device__ __forceinline__ D3 d3(V3<float> a) { return mk3((double)a.x, (double)a.y, (double)a.z); }
-static __device__ __noinline__ bool prim_record_tri_f32(const DScene& sc, uint32_t prim, D3 o, D3 d, double tmin, double tmax, Rec& r) {
+static __device__ RT_HELPER2 bool prim_record_tri_f32(const DScene& sc, uint32_t prim, D3 o, D3 d, double tmin, double tmax, Rec& r) {
     const DPrim pr = sc.prims[prim];
     r.prim = prim; r.mat = pr.mat;
     const uint32_t* ti = sc.tri_index + pr.a;
@@ -156,7 +172,7 @@ template <class R> __device__ __forceinline__ R sin_phi(V3<R> v) { R s = sin_the
 __device__ __forceinline__ bool matches_flags(uint32_t flag, uint32_t other) { return (flag & other) == flag; }
 template <class R> __device__ __forceinline__ bool same_hemisphere(V3<R> v, V3<R> w) { return v.z * w.z > R(0); }              // util.rs:591-593
 template <class R> __device__ __forceinline__ V3<R> reflect(V3<R> v, V3<R> n) { R s = R(2) * dot(v, n); return -v + n * s; }   // util.rs:203-206
-template <class R> static __device__ __noinline__ bool refract(V3<R> vec, V3<R> n, R eta, V3<R>& out) {                        // util.rs:376-385
+template <class R> static __device__ RT_HELPER bool refract(V3<R> vec, V3<R> n, R eta, V3<R>& out) {                        // util.rs:376-385
     R cos_theta_i = dot(n, vec) / norm(vec);
     R sin2_theta_i = fmax(R(0), R(1) - cos_theta_i * cos_theta_i);
     R sin2_theta_t = eta * eta * sin2_theta_i;
@@ -165,7 +181,7 @@ template <class R> static __device__ __noinline__ bool refract(V3<R> vec, V3<R> 
     out = eta * (-vec) + (eta * cos_theta_i - cos_theta_t) * n;
     return true;
 }
-template <class R> static __device__ __noinline__ R fr_dielectric(R cos_theta_i, R eta_i, R eta_t) {                           // bxdf.rs:113-136
+template <class R> static __device__ RT_HELPER R fr_dielectric(R cos_theta_i, R eta_i, R eta_t) {                           // bxdf.rs:113-136
     cos_theta_i = clampr(cos_theta_i, R(-1), R(1));
     R index_i = eta_i, index_t = eta_t;
     if (cos_theta_i < R(0)) { index_i = eta_t; index_t = eta_i; cos_theta_i = fabs(cos_theta_i); }
@@ -177,7 +193,7 @@ template <class R> static __device__ __noinline__ R fr_dielectric(R cos_theta_i,
     R r_perp = ((index_i * cos_theta_i) - (index_t * cos_theta_t)) / ((index_i * cos_theta_i) + (index_t * cos_theta_t));
     return (r_parl * r_parl + r_perp * r_perp) / R(2);
 }
-template <class R> static __device__ __noinline__ V3<R> fr_conductor(R cos_theta_i, V3<R> eta, V3<R> eta_k) {                  // bxdf.rs:141-170
+template <class R> static __device__ RT_HELPER V3<R> fr_conductor(R cos_theta_i, V3<R> eta, V3<R> eta_k) {                  // bxdf.rs:141-170
     cos_theta_i = clampr(cos_theta_i, R(-1), R(1));
     R c2 = cos_theta_i * cos_theta_i, s2 = R(1) - c2;
     V3<R> eta2 = cmul(eta, eta), etak2 = cmul(eta_k, eta_k);
@@ -205,6 +221,10 @@ constexpr uint32_t KM_F_SHIFT = 8;
 __host__ __device__ constexpr uint32_t km(int k) { return 1u << k; }
 __host__ __device__ constexpr uint32_t kmf(int f) { return 1u << (KM_F_SHIFT + f); }
 constexpr uint32_t KM_ALL = 0xffffffffu;
+// A material whose lobes are only Lambert / Oren-Nayar (Matte, Light) gets its BSDF code inlined into the shade kernel: the code is
+// small, and as calls the Bsdf / Lobe structs go through local memory on every call (ncu r01: 14 % of the matte kernel's
+// instructions were local loads / stores).  The heavy materials keep the calls: inlined, their kernels overflow the instruction cache.
+__host__ __device__ constexpr bool km_small(uint32_t KM) { return SHADE_INLINE_SMALL >= 2 || (SHADE_INLINE_SMALL == 1 && (KM & 0xffu & ~(km(0) | km(1))) == 0u); }
 #define KM_HAS(k) ((KM & km(k)) != 0u)
 #define KM_HASF(f) ((KM & kmf(f)) != 0u)
 template <class R> struct Lobe {
@@ -226,7 +246,7 @@ template <class R, uint32_t KM> __device__ __forceinline__ V3<R> fresnel_eval(co
     return v3<R>(R(1), R(1), R(1));
 }
 // ---- microfacet.rs, TrowbridgeReitz{sample_visible_area:true} / Empty
-template <class R> static __device__ __noinline__ R mfd_d(const Lobe<R>& m, V3<R> wh) {                                        // microfacet.rs:53-68
+template <class R> static __device__ RT_HELPER R mfd_d(const Lobe<R>& m, V3<R> wh) {                                        // microfacet.rs:53-68
     if (m.mfd_empty) return R(0);
     R t2 = tan_sq_theta(wh);
     if (isinf(t2)) return R(0);
@@ -235,7 +255,7 @@ template <class R> static __device__ __noinline__ R mfd_d(const Lobe<R>& m, V3<R
     R e = ((cp * cp) / (m.alpha_x * m.alpha_x) + (sp * sp) / (m.alpha_y * m.alpha_y)) * t2;
     return R(1) / (pi<R>() * m.alpha_x * m.alpha_y * cos4 * (R(1) + e) * (R(1) + e));
 }
-template <class R> static __device__ __noinline__ R mfd_lambda(const Lobe<R>& m, V3<R> w) {                                    // microfacet.rs:109-123
+template <class R> static __device__ RT_HELPER R mfd_lambda(const Lobe<R>& m, V3<R> w) {                                    // microfacet.rs:109-123
     if (m.mfd_empty) return R(0);
     R att = fabs(tan_theta(w));
     if (isinf(att)) return R(0);
@@ -256,7 +276,7 @@ static __device__ __noinline__ double tr_roughness_to_alpha(double roughness) {
     double x = log(roughness);
     return 1.62142 + 0.819955 * x + 0.1734 * x * x + 0.0171201 * x * x * x + 0.000640711 * x * x * x * x;
 }
-template <class R> static __device__ __noinline__ V2<R> tr_sample_11(R cos_t, R u1, R u2) {                                    // microfacet.rs:469-512
+template <class R> static __device__ RT_HELPER V2<R> tr_sample_11(R cos_t, R u1, R u2) {                                    // microfacet.rs:469-512
     V2<R> out;
     if (cos_t > R(0.9999)) { R r = sqrt(u1 / (R(1) - u1)), phi = R(2) * pi<R>() * u2; out.x = r * cos(phi); out.y = r * sin(phi); return out; }
     R sin_t = fmax(R(0), sqrt(R(1) - cos_t * cos_t));
@@ -276,7 +296,7 @@ template <class R> static __device__ __noinline__ V2<R> tr_sample_11(R cos_t, R 
     out.x = slope_x; out.y = s * z * sqrt(R(1) + slope_x * slope_x);
     return out;
 }
-template <class R> static __device__ __noinline__ V3<R> mfd_sample_wh(const Lobe<R>& m, V3<R> wo, V2<R> u) {                   // microfacet.rs:240-283, 448-467
+template <class R> static __device__ RT_HELPER V3<R> mfd_sample_wh(const Lobe<R>& m, V3<R> wo, V2<R> u) {                   // microfacet.rs:240-283, 448-467
     if (m.mfd_empty) return normalize(v3<R>(R(0), R(0), R(0)));
     bool flip = wo.z < R(0);
     V3<R> wi = flip ? -wo : wo;
@@ -292,7 +312,7 @@ template <class R> static __device__ __noinline__ V3<R> mfd_sample_wh(const Lobe
 }
 
 // Bxdf::f (bxdf.rs:328-527)
-template <class R, uint32_t KM> static __device__ __noinline__ V3<R> lobe_f(const Lobe<R>& l, V3<R> wo, V3<R> wi) {
+template <class R, uint32_t KM> __device__ __forceinline__ V3<R> lobe_f_impl(const Lobe<R>& l, V3<R> wo, V3<R> wi) {
     const V3<R> zero = v3<R>(R(0), R(0), R(0));
     if (KM_HAS(L_LAMBERT) && l.kind == L_LAMBERT) return l.color * inv_pi<R>();
     {
@@ -332,9 +352,11 @@ template <class R, uint32_t KM> static __device__ __noinline__ V3<R> lobe_f(cons
         return zero;
     }
 }
+template <class R, uint32_t KM> static __device__ __noinline__ V3<R> lobe_f_call(const Lobe<R>& l, V3<R> wo, V3<R> wi) { return lobe_f_impl<R, KM>(l, wo, wi); }
+template <class R, uint32_t KM> __device__ __forceinline__ V3<R> lobe_f(const Lobe<R>& l, V3<R> wo, V3<R> wi) { if constexpr (km_small(KM)) { return lobe_f_impl<R, KM>(l, wo, wi); } else { return lobe_f_call<R, KM>(l, wo, wi); } }
 template <class R> __device__ __forceinline__ R default_pdf(V3<R> wo, V3<R> wi) { return same_hemisphere(wo, wi) ? abs_cos_theta(wi) * inv_pi<R>() : R(0); }   // bxdf.rs:829-835
 // Bxdf::pdf (bxdf.rs:721-813)
-template <class R, uint32_t KM> static __device__ __noinline__ R lobe_pdf(const Lobe<R>& l, V3<R> wo, V3<R> wi) {
+template <class R, uint32_t KM> __device__ __forceinline__ R lobe_pdf_impl(const Lobe<R>& l, V3<R> wo, V3<R> wi) {
     {
         if ((KM_HAS(L_LAMBERT) && l.kind == L_LAMBERT) || (KM_HAS(L_OREN_NAYAR) && l.kind == L_OREN_NAYAR) || (KM_HAS(L_SPEC_R) && l.kind == L_SPEC_R)) return default_pdf(wo, wi);
         if (KM_HAS(L_MICRO_R) && l.kind == L_MICRO_R) {
@@ -354,8 +376,10 @@ template <class R, uint32_t KM> static __device__ __noinline__ R lobe_pdf(const 
         return R(0);     // SpecularTransmission: 0 ; FresnelSpecular: "unimplemented" → 0 (bxdf.rs:777-791)
     }
 }
+template <class R, uint32_t KM> static __device__ __noinline__ R lobe_pdf_call(const Lobe<R>& l, V3<R> wo, V3<R> wi) { return lobe_pdf_impl<R, KM>(l, wo, wi); }
+template <class R, uint32_t KM> __device__ __forceinline__ R lobe_pdf(const Lobe<R>& l, V3<R> wo, V3<R> wi) { if constexpr (km_small(KM)) { return lobe_pdf_impl<R, KM>(l, wo, wi); } else { return lobe_pdf_call<R, KM>(l, wo, wi); } }
 // util::rand_cosine_dir (util.rs:127-148)
-template <class R> static __device__ __noinline__ V3<R> rand_cosine_dir(Rng& g) {
+template <class R> static __device__ RT_HELPER V3<R> rand_cosine_dir(Rng& g) {
     R r1 = rng_real<R>(g), r2 = rng_real<R>(g);
     R u1 = R(2) * r1 - R(1), u2 = R(2) * r2 - R(1);
     if (u1 == R(0) && u2 == R(0)) return v3<R>(R(0), R(0), R(1));
@@ -366,7 +390,7 @@ template <class R> static __device__ __noinline__ V3<R> rand_cosine_dir(Rng& g) 
     return v3<R>(x, y, sqrt(fmax(R(0), R(1) - x * x - y * y)));
 }
 // Bxdf::sample_f (bxdf.rs:532-719)
-template <class R, uint32_t KM> static __device__ __noinline__ void lobe_sample_f(const Lobe<R>& l, V3<R> wo, V2<R> sample, Rng& g, V3<R>& color, V3<R>& wi, R& pdf) {
+template <class R, uint32_t KM> __device__ __forceinline__ void lobe_sample_f_impl(const Lobe<R>& l, V3<R> wo, V2<R> sample, Rng& g, V3<R>& color, V3<R>& wi, R& pdf) {
     const V3<R> zero = v3<R>(R(0), R(0), R(0)), one = v3<R>(R(1), R(1), R(1));
     color = zero; wi = zero; pdf = R(0);
     {
@@ -418,6 +442,8 @@ template <class R, uint32_t KM> static __device__ __noinline__ void lobe_sample_
         }
     }
 }
+template <class R, uint32_t KM> static __device__ __noinline__ void lobe_sample_f_call(const Lobe<R>& l, V3<R> wo, V2<R> sample, Rng& g, V3<R>& color, V3<R>& wi, R& pdf) { lobe_sample_f_impl<R, KM>(l, wo, sample, g, color, wi, pdf); }
+template <class R, uint32_t KM> __device__ __forceinline__ void lobe_sample_f(const Lobe<R>& l, V3<R> wo, V2<R> sample, Rng& g, V3<R>& color, V3<R>& wi, R& pdf) { if constexpr (km_small(KM)) { lobe_sample_f_impl<R, KM>(l, wo, sample, g, color, wi, pdf); } else { lobe_sample_f_call<R, KM>(l, wo, sample, g, color, wi, pdf); } }
 
 // ---- bsdf.rs
 template <class R> __device__ __forceinline__ V3<R> world_to_local(const Bsdf<R>& b, V3<R> v) { return v3<R>(dot(v, b.ss), dot(v, b.ts), dot(v, b.ns)); }
@@ -430,7 +456,7 @@ template <> __device__ __forceinline__ V3<float> local_to_world<float>(const Bsd
 }
 template <class R> __device__ __forceinline__ uint32_t num_components(const Bsdf<R>& b, uint32_t t) { uint32_t c = 0; for (int i = 0; i < b.n; i++) if (matches_flags(b.lobes[i].type, t)) c++; return c; }
 // Bsdf::f (bsdf.rs:83-98), `a && b || c` precedence kept (§8.1 #6)
-template <class R, uint32_t KM> static __device__ __noinline__ V3<R> bsdf_f(const Bsdf<R>& b, V3<R> wow, V3<R> wiw, uint32_t flags) {
+template <class R, uint32_t KM> __device__ __forceinline__ V3<R> bsdf_f_impl(const Bsdf<R>& b, V3<R> wow, V3<R> wiw, uint32_t flags) {
     V3<R> wi = world_to_local(b, wiw), wo = world_to_local(b, wow);
     bool refl = dot(wiw, b.ng) * dot(wow, b.ng) > R(0);
     V3<R> f = v3<R>(R(0), R(0), R(0));
@@ -440,8 +466,10 @@ template <class R, uint32_t KM> static __device__ __noinline__ V3<R> bsdf_f(cons
     }
     return f;
 }
+template <class R, uint32_t KM> static __device__ __noinline__ V3<R> bsdf_f_call(const Bsdf<R>& b, V3<R> wow, V3<R> wiw, uint32_t flags) { return bsdf_f_impl<R, KM>(b, wow, wiw, flags); }
+template <class R, uint32_t KM> __device__ __forceinline__ V3<R> bsdf_f(const Bsdf<R>& b, V3<R> wow, V3<R> wiw, uint32_t flags) { if constexpr (km_small(KM)) { return bsdf_f_impl<R, KM>(b, wow, wiw, flags); } else { return bsdf_f_call<R, KM>(b, wow, wiw, flags); } }
 // Bsdf::pdf (bsdf.rs:166-189): sums, does not average (§8.1 #8); wo is NOT normalised here
-template <class R, uint32_t KM> static __device__ __noinline__ R bsdf_pdf(const Bsdf<R>& b, V3<R> wow, V3<R> wiw, uint32_t flags) {
+template <class R, uint32_t KM> __device__ __forceinline__ R bsdf_pdf_impl(const Bsdf<R>& b, V3<R> wow, V3<R> wiw, uint32_t flags) {
     if (b.n == 0) return R(0);
     V3<R> wo = world_to_local(b, wow), wi = world_to_local(b, wiw);
     if (wo.z == R(0)) return R(0);
@@ -449,8 +477,10 @@ template <class R, uint32_t KM> static __device__ __noinline__ R bsdf_pdf(const 
     for (int i = 0; i < b.n; i++) if (matches_flags(b.lobes[i].type, flags)) { matching++; pdf += lobe_pdf<R, KM>(b.lobes[i], wo, wi); }
     return matching > 0 ? pdf : R(0);
 }
+template <class R, uint32_t KM> static __device__ __noinline__ R bsdf_pdf_call(const Bsdf<R>& b, V3<R> wow, V3<R> wiw, uint32_t flags) { return bsdf_pdf_impl<R, KM>(b, wow, wiw, flags); }
+template <class R, uint32_t KM> __device__ __forceinline__ R bsdf_pdf(const Bsdf<R>& b, V3<R> wow, V3<R> wiw, uint32_t flags) { if constexpr (km_small(KM)) { return bsdf_pdf_impl<R, KM>(b, wow, wiw, flags); } else { return bsdf_pdf_call<R, KM>(b, wow, wiw, flags); } }
 // Bsdf::sample_f (bsdf.rs:102-164)
-template <class R, uint32_t KM> static __device__ __noinline__ void bsdf_sample_f(const Bsdf<R>& b, V3<R> wow, V2<R> sample, uint32_t bxdf_type, Rng& g, V3<R>& color, V3<R>& wiw, R& pdf, uint32_t& sampled) {
+template <class R, uint32_t KM> __device__ __forceinline__ void bsdf_sample_f_impl(const Bsdf<R>& b, V3<R> wow, V2<R> sample, uint32_t bxdf_type, Rng& g, V3<R>& color, V3<R>& wiw, R& pdf, uint32_t& sampled) {
     const V3<R> zero = v3<R>(R(0), R(0), R(0));
     color = zero; wiw = zero; pdf = R(0); sampled = 0;
     uint32_t matching = num_components(b, bxdf_type);
@@ -479,12 +509,14 @@ template <class R, uint32_t KM> static __device__ __noinline__ void bsdf_sample_
     }
     color = c; wiw = w; pdf = p; sampled = bx.type;
 }
+template <class R, uint32_t KM> static __device__ __noinline__ void bsdf_sample_f_call(const Bsdf<R>& b, V3<R> wow, V2<R> sample, uint32_t bxdf_type, Rng& g, V3<R>& color, V3<R>& wiw, R& pdf, uint32_t& sampled) { bsdf_sample_f_impl<R, KM>(b, wow, sample, bxdf_type, g, color, wiw, pdf, sampled); }
+template <class R, uint32_t KM> __device__ __forceinline__ void bsdf_sample_f(const Bsdf<R>& b, V3<R> wow, V2<R> sample, uint32_t bxdf_type, Rng& g, V3<R>& color, V3<R>& wiw, R& pdf, uint32_t& sampled) { if constexpr (km_small(KM)) { bsdf_sample_f_impl<R, KM>(b, wow, sample, bxdf_type, g, color, wiw, pdf, sampled); } else { bsdf_sample_f_call<R, KM>(b, wow, sample, bxdf_type, g, color, wiw, pdf, sampled); } }
 
 // ---- material.rs
 // Texture::value (material.rs:542-589): SolidColor, Checkered (ids may nest), Hdr, Image.  Always f64: the checker's
 // sin(frequency*u*2π) argument reaches ~3e4 rad in plastic_dragon and decides which colour a point gets.
 __device__ __forceinline__ uint32_t sat_u32(double x) { return !(x > 0.) ? 0u : (x >= 4294967295. ? 4294967295u : (uint32_t)x); }   // Rust `f64 as u32`
-static __device__ __noinline__ D3 texel_value(const DScene& sc, const rt_texture& t, double u, double v) {
+static __device__ RT_HELPER2 D3 texel_value(const DScene& sc, const rt_texture& t, double u, double v) {
     const DImage im = sc.images[t.image];
     if (t.type == RT_TEX_HDR) {              // nearest texel, RGBE8 re-quantised at upload, (c+0.5)*2^(e-128)/256 (material.rs:570-587)
         uint32_t x = sat_u32(round((1. - u) * (double)im.w)) % im.w, y = sat_u32(round(v * (double)im.h)) % im.h;
@@ -510,7 +542,7 @@ __device__ __forceinline__ int sin_sign(double x) {
     const bool odd = ((long long)k) & 1ll;
     return ((r < 0.) != odd) ? -1 : 1;
 }
-static __device__ __noinline__ D3 tex_value(const DScene& sc, uint32_t id, double u, double v) {
+static __device__ RT_HELPER2 D3 tex_value(const DScene& sc, uint32_t id, double u, double v) {
     for (int depth = 0; depth < 8; depth++) {
         const rt_texture& t = sc.textures[id];
         if (t.type == RT_TEX_SOLID) return mk3(t.color[0], t.color[1], t.color[2]);
@@ -545,7 +577,7 @@ template <int MAT> __host__ __device__ constexpr uint32_t mat_km() {
          : MAT == RT_MAT_MIRROR ? (km(L_SPEC_R) | kmf(F_NOOP))
          : KM_ALL;
 }
-template <class R, int MAT> static __device__ __noinline__ void compute_scattering(const DScene& sc, const Rec& r, Bsdf<R>& b) {
+template <class R, int MAT> __device__ __forceinline__ void compute_scattering_impl(const DScene& sc, const Rec& r, Bsdf<R>& b) {
     V3<R> e = cast3<R>(normalize(mk3(1., 1., 1.)));    // Bsdf::empty frame (bsdf.rs:37-47)
     b.ns = e; b.ng = e; b.ss = e; b.ts = e; b.n = 0; b.empty = true;
     const rt_material& m = sc.materials[r.mat];
@@ -632,10 +664,12 @@ template <class R, int MAT> static __device__ __noinline__ void compute_scatteri
         }
     }
 }
+template <class R, int MAT> static __device__ __noinline__ void compute_scattering_call(const DScene& sc, const Rec& r, Bsdf<R>& b) { compute_scattering_impl<R, MAT>(sc, r, b); }
+template <class R, int MAT> __device__ __forceinline__ void compute_scattering(const DScene& sc, const Rec& r, Bsdf<R>& b) { if constexpr (km_small(mat_km<MAT>())) { compute_scattering_impl<R, MAT>(sc, r, b); } else { compute_scattering_call<R, MAT>(sc, r, b); } }
 
 // ---- primitive.rs sampling / light.rs Diffuse — f64 in both modes (the sampled point is a shadow-ray endpoint)
 // Primitive::sample_area (primitive.rs:478-539): point and normal on the light's primitive
-static __device__ __noinline__ void sample_area(const DScene& sc, uint32_t prim, D2 u, D3& p, D3& n) {
+static __device__ RT_HELPER2 void sample_area(const DScene& sc, uint32_t prim, D2 u, D3& p, D3& n) {
     DPrim pr = sc.prims[prim];
     uint32_t type = pr.info & 7u;
     if (type == RT_PRIM_TRIANGLE) {

@@ -53,6 +53,10 @@ constexpr int N_BINS = 16;
 #ifndef SHADE_MIN_BLOCKS
 #define SHADE_MIN_BLOCKS 4      // <= 128 registers: 16 warps/SM; measured against 3 and 5 in profiles/shade_r01_notes.md
 #endif
+#ifndef SHADE_PREFETCH
+#define SHADE_PREFETCH 0      // measured r01: no change (40.9 vs 40.8 ms shade at 64 spp) — the kernel does not wait on these gathers
+#endif
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 struct RenderParams {
     rt_camera cam; uint32_t width, height, x0, y0, ww, wh, sample_begin; uint32_t max_depth, invisible_light; uint32_t k0, k1; uint32_t W;
 };
@@ -89,11 +93,17 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
     constexpr uint32_t KM = mat_km<MAT>();
     constexpr int BIN = MAT * 2 + CLS;
     const uint32_t n = c->bin_count[BIN];
-    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
-        const uint2 entry = bin_idx[(size_t)BIN * rp.W + k];
+    const uint32_t stride = gridDim.x * blockDim.x, k0 = blockIdx.x * blockDim.x + threadIdx.x;
+    uint2 entry = k0 < n ? bin_idx[(size_t)BIN * rp.W + k0] : make_uint2(0u, 0u);
+    for (uint32_t k = k0; k < n; k += stride) {
         const uint32_t i = entry.x;
         const PRay pr = load_ray(in.ray + i);
         const PAux pa = load_aux(in.aux + i);
+#if SHADE_PREFETCH
+        // the next entry of this thread and its path record: fetched one iteration ahead so that the first two levels of the
+        // dependent gather chain (bin entry -> 96 B of path state -> primitive) overlap this iteration's work
+        const uint2 entry_next = k + stride < n ? bin_idx[(size_t)BIN * rp.W + k + stride] : make_uint2(0u, 0u);
+#endif
         D3 o = mk3(pr.ox, pr.oy, pr.oz), d = mk3(pr.dx, pr.dy, pr.dz);
         V3<R> beta = v3<R>((R)pa.bx, (R)pa.by, (R)pa.bz);
         uint32_t pixel = pa.pixel, flags = pa.flags;
@@ -101,6 +111,13 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
         uint32_t bounces = flags & 0xffffu; bool specular_bounce = (flags >> 16) & 1u;
         uint32_t prim = entry.y;
         bool is_some = prim != RT_NONE;
+#if SHADE_PREFETCH
+        if (k + stride < n) {
+            prefetch_l2(in.ray + entry_next.x); prefetch_l2(reinterpret_cast<const char*>(in.ray + entry_next.x) + 32);
+            prefetch_l2(in.aux + entry_next.x); prefetch_l2(reinterpret_cast<const char*>(in.aux + entry_next.x) + 32);
+            if (entry_next.y != RT_NONE) prefetch_l2(sc.prims + entry_next.y);
+        }
+#endif
         Rec rec;
         if (is_some) {
             if constexpr (sizeof(R) == 4 && CLS == 1) is_some = prim_record_tri_f32(sc, prim, o, d, SMALL, INF, rec);   // f32 shading frame (shade.cuh)
@@ -224,6 +241,11 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
             store_ray(out.ray + q, o, d);
             store_aux(out.aux + q, (double)beta.x, (double)beta.y, (double)beta.z, pixel, rng.sample, rng.dim, (bounces & 0xffffu) | (specular_bounce ? 0x10000u : 0u));
         }
+#if SHADE_PREFETCH
+        entry = entry_next;
+#else
+        if (k + stride < n) entry = bin_idx[(size_t)BIN * rp.W + k + stride];
+#endif
     }
 }
 
