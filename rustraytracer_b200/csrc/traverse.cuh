@@ -406,10 +406,11 @@ __device__ __forceinline__ void leaf_phase_compact(const DScene& sc, LeafShared&
 }
 
 #ifndef RT_REFILL
-#define RT_REFILL 20        // refetch when fewer than this many lanes of the warp hold a live ray
+#define RT_REFILL 16        // refetch when fewer than this many lanes of the warp hold a live ray (BVH4, dragon 64 spp: 16 / 20 / 24 -> extend 31.6 / 31.7 / 32.5 ms)
 #endif
 #ifndef RT_NODE_MIN
-#define RT_NODE_MIN 12      // leave the node phase for the leaf phase when fewer lanes than this still walk inner nodes
+#define RT_NODE_MIN 6       // leave the node phase for the leaf phase when fewer lanes than this still walk inner nodes (2 / 4 / 6 / 8 / 12 / 16 -> extend
+                            // 34.1 / 32.2 / 31.6 / 31.6 / 32.2 / 33.5 ms, connect 21.1 / 20.3 / 20.1 / 20.2 / 21.1 / 22.4 ms)
 #endif
 
 template <class Job>
