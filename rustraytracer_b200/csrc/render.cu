@@ -11,6 +11,7 @@
 // host polls the control block every few iterations.  Randomness: counter-based Philox keyed by
 // (seed; pixel, sample, dimension) so a path's numbers do not depend on scheduling or on the GPU count.
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -27,14 +28,40 @@ namespace rt {
         if (e_ != cudaSuccess) { set_error(std::string(#call) + ": " + cudaGetErrorString(e_)); return RT_ERR_CUDA; } \
     } while (0)
 
+// RT_SORT_HITS: where the hit-cell bucket sort keeps its state, and the map from a hit point to its cell.  Scenes mix a 20,000-unit floor
+// with a 6-unit dragon, so the grid is not laid over the scene bounds: a point is first compressed with u / (1 + |u|), u = (p - centre) / scale
+// (centre = per-axis median of the primitive centroids, scale = 2 x the median centroid distance), which keeps most cells where the geometry is.
+struct SortParams {
+    float cx, cy, cz, inv_s;
+    uint32_t n_keys;                              // (bins present in the scene + miss) x SORT_CELLS
+    uint64_t slots;                               // shading bin -> key segment, 4 bits per bin, 0xf = bin absent from the scene (at most 13 segments exist)
+    __host__ __device__ uint32_t slot(uint32_t bin) const { return (uint32_t)(slots >> (4u * bin)) & 15u; }
+    uint32_t *hist, *offs;                        // per key: count (zeroed again by the scan) and running output position
+    uint2* ent;                                   // per path of the wavefront: (key, hit primitive), written by extend
+};
+__device__ __forceinline__ uint32_t spread3(uint32_t v) {       // 10 bits -> every third bit
+    v = (v | (v << 16)) & 0x030000ffu; v = (v | (v << 8)) & 0x0300f00fu; v = (v | (v << 4)) & 0x030c30c3u; v = (v | (v << 2)) & 0x09249249u;
+    return v;
+}
+__device__ __forceinline__ uint32_t hit_cell(const SortParams& sp, float x, float y, float z) {
+    const float G = (float)(1u << RT_SORT_BITS);
+    float ux = (x - sp.cx) * sp.inv_s, uy = (y - sp.cy) * sp.inv_s, uz = (z - sp.cz) * sp.inv_s;
+    ux = __fdividef(ux, 1.f + fabsf(ux)); uy = __fdividef(uy, 1.f + fabsf(uy)); uz = __fdividef(uz, 1.f + fabsf(uz));
+    const uint32_t m = (1u << RT_SORT_BITS) - 1u;
+    const uint32_t qx = min((uint32_t)fmaxf((ux * 0.5f + 0.5f) * G, 0.f), m), qy = min((uint32_t)fmaxf((uy * 0.5f + 0.5f) * G, 0.f), m), qz = min((uint32_t)fmaxf((uz * 0.5f + 0.5f) * G, 0.f), m);
+    return spread3(qx) | (spread3(qy) << 1) | (spread3(qz) << 2);
+}
+
 struct Wavefront {
     uint32_t W = 0;
     PathSet set[2]{}; ConnQ shadow{}, probe{};
-    uint2* bin_idx = nullptr;                     // N_BINS x W (path index, hit primitive), filled by extend
+    uint2* bin_idx = nullptr;                     // (path index, hit primitive) per shading bin: N_BINS x W filled by extend, or W sorted entries (RT_SORT_HITS)
+    SortParams sort{};
     Ctrl* ctrl = nullptr; Ctrl* h_ctrl = nullptr;
     cudaStream_t stream = nullptr;
     std::vector<void*> allocs;
     std::vector<cudaEvent_t> events;
+    cudaEvent_t dbg[2] = {nullptr, nullptr};      // RT_TRACE_ITER: after k_sort_scan / k_sort_scatter
 };
 
 __global__ void k_prepare(Ctrl* c, uint32_t W) {
@@ -49,6 +76,26 @@ __global__ void k_prepare(Ctrl* c, uint32_t W) {
     for (int b = 0; b < 4; b++) c->fetch[b] = 0;
 }
 
+// Order in which the pixels of the render window receive camera samples.  The reference hands out 16x16 tiles (render.rs:49-66);
+// any order gives the same film because the RNG is keyed by (pixel, sample).  Scanline order makes a warp a 32x1 strip; here, when the
+// window is a multiple of 32 in both directions, a warp is an 8x4 pixel tile and 32 consecutive warps fill a 32x32 super-tile, so the camera
+// rays of a warp — and the bounce-1 rays and shadow rays derived from them in queue order — start out close together in 2-D.
+// MEASURED (dragon, 1024^2, 64 spp): 81.97 vs 82.16 ms per render, extend 31.41 vs 31.54 ms — no gain, so scanline order stays the default.
+#ifndef RT_TILED_GEN
+#define RT_TILED_GEN 0
+#endif
+__device__ __forceinline__ void window_pixel(const RenderParams& rp, uint32_t pi, uint32_t& px, uint32_t& py) {
+#if RT_TILED_GEN
+    if (((rp.ww | rp.wh) & 31u) == 0u) {
+        const uint32_t st = pi >> 10, in = pi & 1023u, tile = in >> 5, l = in & 31u, stw = rp.ww >> 5;
+        px = rp.x0 + (st % stw) * 32u + (tile & 3u) * 8u + (l & 7u);
+        py = rp.y0 + (st / stw) * 32u + (tile >> 2) * 4u + (l >> 3);
+        return;
+    }
+#endif
+    px = rp.x0 + pi % rp.ww; py = rp.y0 + pi / rp.ww;
+}
+
 // PathIntegrator::single_sample up to the camera ray (integrator.rs:357-365), Samplers::get_camera_sample
 // (sampler.rs:606-613), Camera::get_ray (geometry.rs:177-190)
 __global__ void __launch_bounds__(256) k_generate(const Ctrl* __restrict__ c, RenderParams rp, PathSet ps, double* film) {
@@ -57,7 +104,7 @@ __global__ void __launch_bounds__(256) k_generate(const Ctrl* __restrict__ c, Re
         unsigned long long g = base + i;
         unsigned long long npix = (unsigned long long)rp.ww * rp.wh;
         uint32_t s = (uint32_t)(g / npix), pi = (uint32_t)(g % npix);
-        uint32_t px = rp.x0 + pi % rp.ww, py = rp.y0 + pi / rp.ww;
+        uint32_t px, py; window_pixel(rp, pi, px, py);
         uint32_t pixel = py * rp.width + px;
         Rng rng; rng.k0 = rp.k0; rng.k1 = rp.k1; rng.pixel = pixel; rng.sample = rp.sample_begin + s; rng.dim = 0; rng.w2 = 0xffffffffu; rng.w3 = 0;
         double offx = rng_next(rng), offy = rng_next(rng);
@@ -86,7 +133,7 @@ __global__ void k_film_count(RenderParams rp, unsigned long long generated, doub
     const unsigned long long npix = (unsigned long long)rp.ww * rp.wh;
     const unsigned long long full = generated / npix, rest = generated % npix;
     for (unsigned long long pi = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; pi < npix; pi += (unsigned long long)gridDim.x * blockDim.x) {
-        uint32_t px = rp.x0 + (uint32_t)(pi % rp.ww), py = rp.y0 + (uint32_t)(pi / rp.ww);
+        uint32_t px, py; window_pixel(rp, (uint32_t)pi, px, py);
         film[4 * ((size_t)py * rp.width + px) + 3] += (double)(full + (pi < rest ? 1ull : 0ull));
     }
 }
@@ -96,7 +143,7 @@ __global__ void k_film_count(RenderParams rp, unsigned long long generated, doub
 // per warp (__match_any_sync), so that the shade kernel runs warps of like work instead of diverging on the
 // reference's `match material` / `match primitive` arms.
 struct ExtendJob {
-    Ctrl* c; const DScene* sc; PathSet ps; uint2* bin_idx; uint32_t W;
+    Ctrl* c; const DScene* sc; PathSet ps; uint2* bin_idx; uint32_t W; const SortParams* sp;
     __device__ __forceinline__ bool load(uint32_t i, TState& st, int32_t* stack) {
         PRay r = load_ray(ps.ray + i);
         tstate_init(st, stack, mk3(r.ox, r.oy, r.oz), mk3(r.dx, r.dy, r.dz), SMALL, INF, false, 0., 0u);
@@ -106,12 +153,22 @@ struct ExtendJob {
         uint32_t prim = st.best.prim, key = N_BINS - 1;
         if (prim != RT_NONE) { DPrim pr = sc->prims[prim]; key = sc->materials[pr.mat].type * 2u + ((pr.info & 7u) == RT_PRIM_TRIANGLE ? 1u : 0u); }
         unsigned active = __activemask();
+#if RT_SORT_HITS
+        // count the (bin, hit cell) key — one atomic per distinct key per warp — and leave (key, primitive) for k_sort_scatter
+        uint32_t cell = 0;
+        if (prim != RT_NONE) cell = hit_cell(*sp, (float)(st.rx.o.x + st.best.t * st.rx.d.x), (float)(st.rx.o.y + st.best.t * st.rx.d.y), (float)(st.rx.o.z + st.best.t * st.rx.d.z));
+        const uint32_t skey = sp->slot(key) * SORT_CELLS + cell;
+        const unsigned same = __match_any_sync(active, skey);
+        if ((int)(threadIdx.x & 31) == __ffs(same) - 1) atomicAdd(&sp->hist[skey], (uint32_t)__popc(same));
+        sp->ent[i] = make_uint2(skey, prim);
+#else
         unsigned peers = __match_any_sync(active, key);
         int leader = __ffs(peers) - 1, lane = threadIdx.x & 31;
         uint32_t base = 0;
         if (lane == leader) base = atomicAdd(&c->bin_count[key], (uint32_t)__popc(peers));
         base = __shfl_sync(peers, base, leader);
         bin_idx[(size_t)key * W + base + __popc(peers & ((1u << lane) - 1u))] = make_uint2(i, prim);   // path index + hit primitive
+#endif
     }
 };
 #ifndef TRACE_MIN_BLOCKS
@@ -120,9 +177,67 @@ struct ExtendJob {
 #ifndef TRACE_GRID_BLOCKS
 #define TRACE_GRID_BLOCKS 8     // persistent grid = SMs x this
 #endif
-__global__ void __launch_bounds__(128, TRACE_MIN_BLOCKS) k_extend(Ctrl* c, DScene sc, PathSet ps, uint2* __restrict__ bin_idx, uint32_t W) {
-    ExtendJob job{c, &sc, ps, bin_idx, W};
+__global__ void __launch_bounds__(128, TRACE_MIN_BLOCKS) k_extend(Ctrl* c, DScene sc, PathSet ps, uint2* __restrict__ bin_idx, uint32_t W, SortParams sp) {
+    ExtendJob job{c, &sc, ps, bin_idx, W, &sp};
     trace_jobs(sc, job, c->n_tot, &c->fetch[0]);
+}
+
+// RT_SORT_HITS, step 2 of 3: exclusive prefix sum of the key counts (one block; every warp owns a contiguous run of keys and reads it
+// 128 keys at a time), the counts zeroed for the next iteration, and the bins' extents published for the shade kernels.
+__global__ void __launch_bounds__(1024) k_sort_scan(Ctrl* c, SortParams sp) {
+    __shared__ uint32_t wsum[32];
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t per_warp4 = sp.n_keys / 128;               // uint4 words per warp (n_keys is a multiple of 4096)
+    uint4* h = reinterpret_cast<uint4*>(sp.hist) + (size_t)warp * per_warp4;
+    uint4* o = reinterpret_cast<uint4*>(sp.offs) + (size_t)warp * per_warp4;
+    uint32_t s = 0;
+    for (uint32_t t = lane; t < per_warp4; t += 32) { const uint4 v = h[t]; s += v.x + v.y + v.z + v.w; }
+    for (int d = 16; d; d >>= 1) s += __shfl_xor_sync(FULL, s, d);
+    if (lane == 0) wsum[warp] = s;
+    __syncthreads();
+    if (warp == 0) {
+        const uint32_t v = wsum[lane]; uint32_t inc = v;
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(FULL, inc, d); if (lane >= d) inc += y; }
+        wsum[lane] = inc - v;
+    }
+    __syncthreads();
+    uint32_t carry = wsum[warp];
+    for (uint32_t t0 = 0; t0 < per_warp4; t0 += 32) {
+        const uint32_t t = t0 + lane;
+        const uint4 v = h[t];
+        const uint32_t loc = v.x + v.y + v.z + v.w; uint32_t inc = loc;
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(FULL, inc, d); if (lane >= d) inc += y; }
+        const uint32_t ex = carry + inc - loc;
+        o[t] = make_uint4(ex, ex + v.x, ex + v.x + v.y, ex + v.x + v.y + v.z);
+        h[t] = make_uint4(0u, 0u, 0u, 0u);
+        carry += __shfl_sync(FULL, inc, 31);
+    }
+    __syncthreads();
+    if (threadIdx.x < N_BINS) {
+        const uint32_t b = threadIdx.x, slot = sp.slot(b);
+        uint32_t base = 0, count = 0;
+        if (slot != 15u) {
+            base = sp.offs[(size_t)slot * SORT_CELLS];
+            const uint32_t end = ((slot + 1u) * SORT_CELLS < sp.n_keys) ? sp.offs[(size_t)(slot + 1u) * SORT_CELLS] : c->n_tot;
+            count = end - base;
+        }
+        c->bin_base[b] = base; c->bin_count[b] = count;
+    }
+}
+// step 3 of 3: every path's entry goes to the next free position of its key
+__global__ void __launch_bounds__(256) k_sort_scatter(const Ctrl* c, SortParams sp, uint2* __restrict__ sorted) {
+    const uint32_t n = c->n_tot;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint2 e = sp.ent[i];
+        const unsigned active = __activemask();
+        const unsigned peers = __match_any_sync(active, e.x);
+        const int leader = __ffs(peers) - 1, lane = threadIdx.x & 31;
+        uint32_t base = 0;
+        if (lane == leader) base = atomicAdd(&sp.offs[e.x], (uint32_t)__popc(peers));
+        base = __shfl_sync(peers, base, leader);
+        sorted[base + __popc(peers & ((1u << lane) - 1u))] = make_uint2(i, e.y);
+    }
 }
 
 // Paths whose extend ray left the scene (bin 15).  Only launched when the scene has an Infinite light: at bounce 0 or after a
@@ -130,7 +245,7 @@ __global__ void __launch_bounds__(128, TRACE_MIN_BLOCKS) k_extend(Ctrl* c, DScen
 __global__ void __launch_bounds__(128) k_shade_miss(Ctrl* c, DScene sc, RenderParams rp, PathSet in, const uint2* __restrict__ bin_idx, double* film) {
     const uint32_t n = c->bin_count[N_BINS - 1];
     for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
-        const uint32_t i = bin_idx[(size_t)(N_BINS - 1) * rp.W + k].x;
+        const uint32_t i = bin_idx[bin_first(c, rp, N_BINS - 1) + k].x;
         const PAux pa = load_aux(in.aux + i);
         if (!((pa.flags & 0xffffu) == 0 || ((pa.flags >> 16) & 1u))) continue;
         const PRay pr = load_ray(in.ray + i);
@@ -238,6 +353,7 @@ static void destroy_wavefront(Wavefront* w) {
     if (!w) return;
     for (void* p : w->allocs) cudaFree(p);
     for (auto e : w->events) cudaEventDestroy(e);
+    for (auto e : w->dbg) if (e) cudaEventDestroy(e);
     if (w->h_ctrl) cudaFreeHost(w->h_ctrl);
     if (w->stream) cudaStreamDestroy(w->stream);
     delete w;
@@ -249,8 +365,36 @@ static Wavefront* get_wavefront(rt_scene& s) {
     Wavefront* w = new Wavefront();
     w->W = s.wavefront_size;
     size_t n = w->W;
-    bool ok = alloc_set(*w, w->set[0], n) && alloc_set(*w, w->set[1], n) && alloc_q(*w, w->shadow, n) && alloc_q(*w, w->probe, n) &&
-              dalloc(*w, w->bin_idx, n * N_BINS) && dalloc(*w, w->ctrl, 1) &&
+#if RT_SORT_HITS
+    // key segments: one per shading bin that occurs in the scene, and the miss bin
+    SortParams& sp = w->sort;
+    uint32_t n_slots = 0;
+    sp.slots = 0;
+    for (int b = 0; b < N_BINS; b++) sp.slots |= (uint64_t)(((s.bin_mask >> b) & 1u) || b == N_BINS - 1 ? n_slots++ : 15u) << (4 * b);
+    sp.n_keys = n_slots * SORT_CELLS;
+    {   // centre and scale of the cell map: medians over the primitive centroids
+        const size_t np = s.prims.size();
+        std::vector<double> c[3], dev(np);
+        for (int a = 0; a < 3; a++) c[a].resize(np);
+        for (size_t i = 0; i < np; i++) { const Box64 b = prim_box(s, s.prims[i]); for (int a = 0; a < 3; a++) c[a][i] = 0.5 * (b.mn[a] + b.mx[a]); }
+        double med[3] = {0., 0., 0.}, scale = 1.;
+        if (np) {
+            for (int a = 0; a < 3; a++) { std::vector<double> t = c[a]; std::nth_element(t.begin(), t.begin() + np / 2, t.end()); med[a] = t[np / 2]; }
+            for (size_t i = 0; i < np; i++) dev[i] = std::max(std::fabs(c[0][i] - med[0]), std::max(std::fabs(c[1][i] - med[1]), std::fabs(c[2][i] - med[2])));
+            std::nth_element(dev.begin(), dev.begin() + np / 2, dev.end());
+            scale = 2. * dev[np / 2];
+            if (!(scale > 0.) || !std::isfinite(scale)) scale = 1.;
+        }
+        sp.cx = (float)med[0]; sp.cy = (float)med[1]; sp.cz = (float)med[2]; sp.inv_s = (float)(1. / scale);
+    }
+    const size_t n_entries = n;
+    bool ok = dalloc(*w, sp.hist, sp.n_keys) && dalloc(*w, sp.offs, sp.n_keys) && dalloc(*w, sp.ent, n) && cudaMemset(sp.hist, 0, sp.n_keys * sizeof(uint32_t)) == cudaSuccess;
+#else
+    const size_t n_entries = n * N_BINS;
+    bool ok = true;
+#endif
+    ok = ok && alloc_set(*w, w->set[0], n) && alloc_set(*w, w->set[1], n) && alloc_q(*w, w->shadow, n) && alloc_q(*w, w->probe, n) &&
+              dalloc(*w, w->bin_idx, n_entries) && dalloc(*w, w->ctrl, 1) &&
               cudaMallocHost((void**)&w->h_ctrl, sizeof(Ctrl)) == cudaSuccess && cudaStreamCreateWithFlags(&w->stream, cudaStreamNonBlocking) == cudaSuccess;
     if (!ok) { set_error(std::string("wavefront allocation failed: ") + cudaGetErrorString(cudaGetLastError())); destroy_wavefront(w); return nullptr; }
     // Keep the inner nodes of the BVH resident in L2 while ~1.4 GB of path state streams through every iteration:
@@ -346,6 +490,9 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
     if (init.total_samples == 0) return RT_OK;
     cudaStream_t st = w.stream;
     CK(cudaMemcpyAsync(w.ctrl, &init, sizeof(Ctrl), cudaMemcpyHostToDevice, st));
+#if RT_SORT_HITS
+    CK(cudaMemsetAsync(w.sort.hist, 0, w.sort.n_keys * sizeof(uint32_t), st));      // a cancelled render may have left counts behind
+#endif
     int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device);
     int g128 = (int)std::min<uint64_t>((w.W + 127) / 128, (uint64_t)sms * 32), gtrace = sms * TRACE_GRID_BLOCKS, g256 = (int)std::min<uint64_t>((w.W + 255) / 256, (uint64_t)sms * 8);
     cudaEvent_t e_begin = ev(w, 0), e_end = ev(w, 1);
@@ -354,6 +501,7 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
     int cur = 0; uint64_t iter = 0; bool done = false; rt_status result = RT_OK;
     const bool f32 = (integ->flags & RT_SHADE_F32) != 0;
     const bool trace = getenv("RT_TRACE_ITER") != nullptr;     // debugging aid: per-iteration sizes and kernel times on stderr
+    if (trace && !w.dbg[0]) { cudaEventCreate(&w.dbg[0]); cudaEventCreate(&w.dbg[1]); }
     while (!done) {
         for (int k = 0; k < (trace ? 1 : 4); k++, iter++) {
             k_prepare<<<1, 1, 0, st>>>(w.ctrl, w.W);
@@ -361,8 +509,14 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
             cudaEventRecord(ev(w, n_ev + 0), st);
             k_generate<<<g256, 256, 0, st>>>(w.ctrl, rp, w.set[cur], film->d);
             cudaEventRecord(ev(w, n_ev + 1), st);
-            k_extend<<<gtrace, 128, 0, st>>>(w.ctrl, s->d, w.set[cur], w.bin_idx, w.W);
+            k_extend<<<gtrace, 128, 0, st>>>(w.ctrl, s->d, w.set[cur], w.bin_idx, w.W, w.sort);
             cudaEventRecord(ev(w, n_ev + 2), st);
+#if RT_SORT_HITS
+            k_sort_scan<<<1, 1024, 0, st>>>(w.ctrl, w.sort);             // timed with the shade kernels, their consumer
+            if (trace) cudaEventRecord(w.dbg[0], st);
+            k_sort_scatter<<<g256, 256, 0, st>>>(w.ctrl, w.sort, w.bin_idx);
+            if (trace) cudaEventRecord(w.dbg[1], st);
+#endif
 {
                 ShadeLaunch L{w.ctrl, &s->d, &rp, w.set[cur], w.set[cur ^ 1], w.bin_idx, w.shadow, w.probe, film->d, s->bin_mask, g128, st};
                 if (f32) launch_shade_f32(L, s->d.has_infinite != 0);
@@ -386,6 +540,9 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
             fprintf(stderr, "iter %3llu n_tot %8u (new %8u) next %8u shadow %8u probe %7u | gen %.3f extend %.3f shade %.3f connect %.3f ms | bins", (unsigned long long)iter - 1,
                     w.h_ctrl->n_tot, w.h_ctrl->n_new, after.n_next, after.n_shadow, after.n_probe, a, b, cc, d);
             for (int q = 0; q < N_BINS; q++) if (after.bin_count[q]) fprintf(stderr, " %d:%u", q, after.bin_count[q]);
+#if RT_SORT_HITS
+            { float s1 = 0, s2 = 0; cudaEventElapsedTime(&s1, w.events[i + 2], w.dbg[0]); cudaEventElapsedTime(&s2, w.dbg[0], w.dbg[1]); fprintf(stderr, " | scan %.3f scatter %.3f", s1, s2); }
+#endif
             fprintf(stderr, "\n");
         }
         if (w.h_ctrl->n_tot == 0) done = true;       // snapshot taken right after a prepare: nothing in flight, nothing left to generate

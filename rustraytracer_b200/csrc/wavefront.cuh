@@ -48,8 +48,26 @@ struct Ctrl {
     unsigned long long c_paths, c_extend, c_shadow, c_probe, c_iter;
     uint32_t fetch[4];           // work counters of the persistent traversal kernels (extend, shadow, probe)
     uint32_t bin_count[16];      // paths per shading bin after extend (material type x primitive class, 15 = miss)
+    uint32_t bin_base[16];       // RT_SORT_HITS: first entry of each bin in the sorted entry array
 };
 constexpr int N_BINS = 16;
+// RT_SORT_HITS: the (path, primitive) entries extend hands to shade are bucket-sorted by (shading bin, Morton cell of the hit point)
+// instead of being appended per bin in completion order: a warp of k_shade then shades neighbouring surface points (its triangle
+// gathers share sectors), and the continuation and shadow rays it appends — the next extend / connect launches fetch them in queue
+// order — start close together (render.cu: ExtendJob::finish, k_sort_scan, k_sort_scatter).
+// MEASURED (dragon, 1024^2, 64 spp, one B200): extend 31.6 -> 30.3 ms, connect 20.2 -> 19.1 ms, but shade 30.1 -> 37.5 ms: the two sort
+// kernels cost 0.03 + 0.1..0.34 ms per iteration, and the shade kernels themselves run 20-27 % slower although their triangle gathers
+// are now coherent (ncu launch list: plastic/triangle kernel -6 % when every launch starts cold) — live they lose the near-sequential order
+// of the 2 x 48 B path-state gathers that completion order gives for free.  82.1 -> 87.1 ms per render, 2,628 -> 2,429 Mrays/s on the
+// bench: OFF.  What would make it pay: moving the path state along with the entry (another 192 B per path) — not with rays this short.
+#ifndef RT_SORT_HITS
+#define RT_SORT_HITS 0
+#endif
+#ifndef RT_SORT_BITS
+#define RT_SORT_BITS 5          // Morton bits per axis of the hit cell
+#endif
+static_assert(RT_SORT_BITS >= 4 && RT_SORT_BITS <= 7, "RT_SORT_BITS out of range");
+constexpr uint32_t SORT_CELLS = 1u << (3 * RT_SORT_BITS);
 #ifndef SHADE_MIN_BLOCKS
 #define SHADE_MIN_BLOCKS 4      // <= 128 registers: 16 warps/SM; measured against 3 and 5 in profiles/shade_r01_notes.md
 #endif
@@ -60,6 +78,14 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 struct RenderParams {
     rt_camera cam; uint32_t width, height, x0, y0, ww, wh, sample_begin; uint32_t max_depth, invisible_light; uint32_t k0, k1; uint32_t W;
 };
+// first entry of shading bin `bin` in the entry array filled for k_shade
+__device__ __forceinline__ size_t bin_first(const Ctrl* c, const RenderParams& rp, int bin) {
+#if RT_SORT_HITS
+    return c->bin_base[bin];
+#else
+    return (size_t)bin * rp.W;
+#endif
+}
 
 __device__ __forceinline__ uint32_t warp_append(uint32_t* counter) {
     // warp-aggregated queue append: one atomic per warp (ballot + popc), everyone gets a unique slot
@@ -94,7 +120,8 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
     constexpr int BIN = MAT * 2 + CLS;
     const uint32_t n = c->bin_count[BIN];
     const uint32_t stride = gridDim.x * blockDim.x, k0 = blockIdx.x * blockDim.x + threadIdx.x;
-    uint2 entry = k0 < n ? bin_idx[(size_t)BIN * rp.W + k0] : make_uint2(0u, 0u);
+    bin_idx += bin_first(c, rp, BIN);
+    uint2 entry = k0 < n ? bin_idx[k0] : make_uint2(0u, 0u);
     for (uint32_t k = k0; k < n; k += stride) {
         const uint32_t i = entry.x;
         const PRay pr = load_ray(in.ray + i);
@@ -102,7 +129,7 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
 #if SHADE_PREFETCH
         // the next entry of this thread and its path record: fetched one iteration ahead so that the first two levels of the
         // dependent gather chain (bin entry -> 96 B of path state -> primitive) overlap this iteration's work
-        const uint2 entry_next = k + stride < n ? bin_idx[(size_t)BIN * rp.W + k + stride] : make_uint2(0u, 0u);
+        const uint2 entry_next = k + stride < n ? bin_idx[k + stride] : make_uint2(0u, 0u);
 #endif
         D3 o = mk3(pr.ox, pr.oy, pr.oz), d = mk3(pr.dx, pr.dy, pr.dz);
         V3<R> beta = v3<R>((R)pa.bx, (R)pa.by, (R)pa.bz);
@@ -244,7 +271,7 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
 #if SHADE_PREFETCH
         entry = entry_next;
 #else
-        if (k + stride < n) entry = bin_idx[(size_t)BIN * rp.W + k + stride];
+        if (k + stride < n) entry = bin_idx[k + stride];
 #endif
     }
 }

@@ -483,8 +483,10 @@ def test_render_cancel():
             result["status"] = e.status
     th = threading.Thread(target=run); th.start()
     time.sleep(0.3)
-    lib().rt_render_cancel(gpu.h)
-    th.join(timeout=60)
+    t_end = time.time() + 60
+    while th.is_alive() and time.time() < t_end:          # rt_render clears the flag when it starts: repeat until the render has seen it
+        lib().rt_render_cancel(gpu.h)
+        th.join(timeout=0.05)
     assert not th.is_alive()
     assert result["status"] == N.RT_ERR_CANCELLED
     n = film.read()[..., 3].reshape(-1)
