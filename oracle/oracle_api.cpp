@@ -126,8 +126,8 @@ void orc_camera_look_at(const double from[3], const double to[3], const double u
 // counts[0..2] += extend, shadow, probe rays.  Returns wall seconds.
 // pixel_stride > 1 renders only pixels whose index py*width+px is a multiple of it (bounded CPU-baseline samples).
 // counts[3..4] += box / primitive tests of the extend rays under the ordered traversal when count_ordered != 0.
-double orc_render_ex(void* sp, const rt_camera* cam, uint32_t max_depth, uint32_t invisible_light, const rt_film_desc* d,
-                     int threads, double* film, uint64_t* counts, uint32_t pixel_stride, int count_ordered) {
+static double render_impl(void* sp, const rt_camera* cam, uint32_t kind, uint32_t max_depth, uint32_t invisible_light, const rt_film_desc* d,
+                          int threads, double* film, uint64_t* counts, uint32_t pixel_stride, int count_ordered) {
     const Scene& s = *(Scene*)sp;
     const uint32_t TILE = 16;   // consts.rs:10
     uint32_t tx0 = d->x0 / TILE, ty0 = d->y0 / TILE, tx1 = (d->x1 + TILE - 1) / TILE, ty1 = (d->y1 + TILE - 1) / TILE;
@@ -146,7 +146,7 @@ double orc_render_ex(void* sp, const rt_camera* cam, uint32_t max_depth, uint32_
                     if (((uint64_t)py * d->width + px) % pixel_stride != 0) continue;
                     double* cell = film + 4 * ((uint64_t)py * d->width + px);
                     for (uint32_t smp = d->sample_begin; smp < d->sample_end; smp++) {
-                        V3 c = single_sample(s, *cam, d->width, d->height, px, py, smp, d->seed, max_depth, invisible_light != 0, rcs[t]);
+                        V3 c = single_sample(s, *cam, d->width, d->height, px, py, smp, d->seed, max_depth, invisible_light != 0, rcs[t], kind);
                         cell[0] += c.x; cell[1] += c.y; cell[2] += c.z; cell[3] += 1.;   // util::increment_color (util.rs:208-232)
                     }
                 }
@@ -160,6 +160,15 @@ double orc_render_ex(void* sp, const rt_camera* cam, uint32_t max_depth, uint32_
         if (count_ordered) { counts[3] += r.ordered.box_tests; counts[4] += r.ordered.prim_tests; }
     }
     return secs;
+}
+double orc_render_ex(void* sp, const rt_camera* cam, uint32_t max_depth, uint32_t invisible_light, const rt_film_desc* d,
+                     int threads, double* film, uint64_t* counts, uint32_t pixel_stride, int count_ordered) {
+    return render_impl(sp, cam, 0, max_depth, invisible_light, d, threads, film, counts, pixel_stride, count_ordered);
+}
+// kind = rtcore.h RT_INTEGRATOR_*: 0 Path, 1 Direct{UniformOne}, 2 Direct{UniformAll}, 3 Whitted (max_depth >= 1 for 1..3)
+double orc_render_kind(void* sp, const rt_camera* cam, uint32_t kind, uint32_t max_depth, uint32_t invisible_light, const rt_film_desc* d,
+                       int threads, double* film, uint64_t* counts) {
+    return render_impl(sp, cam, kind, max_depth, invisible_light, d, threads, film, counts, 1, 0);
 }
 double orc_render(void* sp, const rt_camera* cam, uint32_t max_depth, uint32_t invisible_light, const rt_film_desc* d,
                   int threads, double* film, uint64_t* counts) {

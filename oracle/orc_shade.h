@@ -767,6 +767,62 @@ inline V3 path_li(const Scene& s, Ray ray, uint32_t max_depth, bool invisible_li
     return l;
 }
 
+// WhittedIntegrator::li (integrator.rs:131-165) and DirectLightingIntegrator::li (integrator.rs:257-297) with specular_reflect /
+// specular_transmit (integrator.rs:464-504) and uniform_sample_all_lights (integrator.rs:506-528: ONE (u_light, u_scatter) pair per
+// light, summed, not divided by the sample count — the loop over `samples` is commented out in the reference).
+// kind: 1 = Direct{UniformOne}, 2 = Direct{UniformAll}, 3 = Whitted (rtcore.h RT_INTEGRATOR_*).
+// Random numbers: the reference threads one sampler through the recursion depth-first; here both branch samples are drawn at the
+// vertex (reflect, then transmit) and each child continues from the vertex's dimension counter — the rule the wavefront kernel
+// follows, where the two children are independent queue entries.  Both are streams of iid uniforms.
+inline V3 sampler_li(const Scene& s, const Ray& ray, uint32_t depth, uint32_t kind, Rng& rng, RayCounts& rc) {
+    HitRecord rec; rc.extend++;
+    if (!get_intersection(s, ray, rec)) {
+        V3 a = black();
+        for (const Light& light : s.lights) a = a + light_le(s, light, ray);
+        return a;
+    }
+    V3 ans = record_le(s, rec, rec.wo);
+    const V3 n = rec.shading.n, wo = rec.wo;
+    compute_scattering(s, rec, RADIANCE, true);
+    if (kind == 3) {
+        for (const Light& light : s.lights) {
+            V2 u; u.x = rng.next(); u.y = rng.next();
+            LiSample ls = sample_li(s, light, rec, u);
+            if (ls.color == black() || ls.pdf == 0.) continue;
+            V3 f = bsdf_f(rec.bsdf, wo, ls.wi, BSDF_ALL);
+            if (f != black()) {
+                rc.shadow++;
+                if (unoccluded(s, rec.p, ls.p1, ls.p1_prim, ls.p1_t, light.d.type == RT_LIGHT_INFINITE)) ans = ans + cmul(f, ls.color) * (std::fabs(dot(ls.wi, n)) / ls.pdf);
+            }
+        }
+    } else if (!s.lights.empty()) {
+        if (kind == 2) {
+            for (size_t j = 0; j < s.lights.size(); j++) {
+                V2 u_light; u_light.x = rng.next(); u_light.y = rng.next();
+                V2 u_scatter; u_scatter.x = rng.next(); u_scatter.y = rng.next();
+                ans = ans + estimate_direct(s, rec, u_scatter, (uint32_t)j, u_light, rng, rc);
+            }
+        } else ans = ans + uniform_sample_one_light(s, rec, rng, rc);
+    }
+    if (depth - 1 > 0) {
+        V2 ur; ur.x = rng.next(); ur.y = rng.next();
+        V2 ut; ut.x = rng.next(); ut.y = rng.next();
+        const uint8_t want[2] = {(uint8_t)(BSDF_REFLECTION | BSDF_SPECULAR), (uint8_t)(BSDF_TRANSMISSION | BSDF_SPECULAR)};
+        const V2 us[2] = {ur, ut};
+        for (int b = 0; b < 2; b++) {
+            V3 f, wi; double pdf; uint8_t st;
+            Rng scratch = rng;            // specular lobes draw nothing
+            bsdf_sample_f(rec.bsdf, wo, us[b], want[b], scratch, f, wi, pdf, st);
+            if (pdf > 0. && f != black() && std::fabs(dot(n, wi)) != 0.) {
+                Rng child = rng;
+                V3 li = sampler_li(s, spawn_ray(rec, wi), depth - 1, kind, child, rc);
+                ans = ans + cmul(f, li) * (std::fabs(dot(n, wi)) / pdf);
+            }
+        }
+    }
+    return ans;
+}
+
 // Camera::get_ray (geometry.rs:177-190) with util::rand_in_disk (util.rs:105-113) and rand_range
 inline Ray camera_get_ray(const rt_camera& c, double u, double v, Rng& rng) {
     V3 in_disk;
@@ -785,13 +841,14 @@ inline Ray camera_get_ray(const rt_camera& c, double u, double v, Rng& rng) {
 }
 // PathIntegrator::single_sample (integrator.rs:357-369) + Samplers::get_camera_sample (sampler.rs:606-613)
 inline V3 single_sample(const Scene& s, const rt_camera& cam, uint32_t width, uint32_t height, uint32_t px, uint32_t py,
-                        uint32_t sample, uint64_t seed, uint32_t max_depth, bool invisible_light, RayCounts& rc) {
+                        uint32_t sample, uint64_t seed, uint32_t max_depth, bool invisible_light, RayCounts& rc, uint32_t kind = 0) {
     Rng rng(seed, py * width + px, sample);
     double ox = rng.next(), oy = rng.next();
     double fx = (double)px + ox, fy = (double)py + oy;
     rng.next();              // time
     rng.next(); rng.next();  // lens
     Ray ray = camera_get_ray(cam, fx / (double)width, fy / (double)height, rng);
+    if (kind != 0) return sampler_li(s, ray, max_depth, kind, rng, rc);
     return path_li(s, ray, max_depth, invisible_light, rng, rc);
 }
 

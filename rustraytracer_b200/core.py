@@ -50,17 +50,30 @@ class Camera:
 
 @dataclass
 class IntType:
-    """`IntType::Path { max_depth, invisible_light }` (integrator.rs:37-40); the only integrator the
-    reference ever selects (main.rs:262-265)."""
+    """`IntType` (integrator.rs:25-41).  `Path { max_depth, invisible_light }` is the only integrator the reference ever
+    selects (main.rs:262-265); `Direct { max_depth, strategy }` and `Whitted { max_depth }` run on the same wavefront
+    (f64 radiometry only).  `Basic` (geometry::cast_ray) is not implemented."""
     max_depth: int = MAX_DEPTH
     invisible_light: bool = False
     # radiometric precision of the shade kernel: False = f64 in the reference's operation order (per-pixel parity
     # with the f64 oracle), True = f32 (production speed).  Intersection decisions are f64-exact in both.
     shade_f32: bool = False
+    kind: int = 0                # rtcore.h RT_INTEGRATOR_*: 0 Path, 1 Direct{UniformOne}, 2 Direct{UniformAll}, 3 Whitted
 
     @staticmethod
     def Path(max_depth=MAX_DEPTH, invisible_light=False, shade_f32=False):
-        return IntType(max_depth, invisible_light, shade_f32)
+        return IntType(max_depth, invisible_light, shade_f32, 0)
+
+    @staticmethod
+    def Direct(max_depth=MAX_DEPTH, strategy="UniformOne"):
+        """`LightStrategy::UniformOne` / `UniformAll` (integrator.rs:19-23)"""
+        if strategy not in ("UniformOne", "UniformAll"):
+            raise ValueError("strategy must be 'UniformOne' or 'UniformAll'")
+        return IntType(max_depth, False, False, 1 if strategy == "UniformOne" else 2)
+
+    @staticmethod
+    def Whitted(max_depth=MAX_DEPTH):
+        return IntType(max_depth, False, False, 3)
 
 
 @dataclass
@@ -255,7 +268,7 @@ def render_samples(objects, camera, int_type, film, width, height, sample_begin,
     """`Integrator::render` over a pixel window and a sample range (integrator.rs:336-348): adds
     samples [sample_begin, sample_end) of every pixel in `window` = (x0, y0, x1, y1) to `film`."""
     x0, y0, x1, y1 = window if window is not None else (0, 0, width, height)
-    integ = N.IntegratorDesc(0, int(int_type.max_depth), 1 if int_type.invisible_light else 0, N.SHADE_F32 if int_type.shade_f32 else 0)
+    integ = N.IntegratorDesc(int(int_type.kind), int(int_type.max_depth), 1 if int_type.invisible_light else 0, N.SHADE_F32 if int_type.shade_f32 else 0)
     fd = N.FilmDesc(width, height, int(sample_begin), int(sample_end), x0, y0, x1, y1, int(seed))
     check(lib().rt_render(objects.h, C.byref(camera.c), C.byref(integ), C.byref(fd), film.h))
 

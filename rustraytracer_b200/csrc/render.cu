@@ -64,11 +64,13 @@ struct Wavefront {
     cudaEvent_t dbg[2] = {nullptr, nullptr};      // RT_TRACE_ITER: after k_sort_scan / k_sort_scatter
 };
 
-__global__ void k_prepare(Ctrl* c, uint32_t W) {
+// `cap` = most paths allowed in flight: W for Path (one continuation per path at most); W / max(2, n_lights) for the branching integrators,
+// whose vertices append up to two continuations and one shadow + one probe entry PER LIGHT
+__global__ void k_prepare(Ctrl* c, uint32_t cap) {
     c->c_extend += c->n_tot; c->c_shadow += c->n_shadow; c->c_probe += c->n_probe; c->c_iter += 1;
     uint32_t n_cur = c->n_next;
     unsigned long long remaining = c->total_samples - c->next_sample;
-    uint32_t room = W - n_cur;
+    uint32_t room = cap > n_cur ? cap - n_cur : 0u;
     uint32_t n_new = (uint32_t)(remaining < (unsigned long long)room ? remaining : (unsigned long long)room);
     c->n_cur = n_cur; c->n_new = n_new; c->n_tot = n_cur + n_new; c->n_next = 0; c->n_shadow = 0; c->n_probe = 0;
     c->sample_base = c->next_sample; c->next_sample += n_new; c->c_paths += n_new;
@@ -247,7 +249,7 @@ __global__ void __launch_bounds__(128) k_shade_miss(Ctrl* c, DScene sc, RenderPa
     for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
         const uint32_t i = bin_idx[bin_first(c, rp, N_BINS - 1) + k].x;
         const PAux pa = load_aux(in.aux + i);
-        if (!((pa.flags & 0xffffu) == 0 || ((pa.flags >> 16) & 1u))) continue;
+        if (rp.kind == RT_INTEGRATOR_PATH && !((pa.flags & 0xffffu) == 0 || ((pa.flags >> 16) & 1u))) continue;   // Whitted / Direct: every level (integrator.rs:135-140)
         const PRay pr = load_ray(in.ray + i);
         D3 d = mk3(pr.dx, pr.dy, pr.dz), beta = mk3(pa.bx, pa.by, pa.bz), l = mk3(0., 0., 0.);
         for (uint32_t li = 0; li < sc.n_lights; li++)
@@ -472,7 +474,9 @@ rt_status rt_film_resolve_rgb8(rt_film* f, uint8_t* host_rgb) {
 rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc* integ, const rt_film_desc* fd, rt_film* film) {
     if (!s || !cam || !integ || !fd || !film) { set_error("rt_render: null argument"); return RT_ERR_INVALID; }
     if (!s->committed) { set_error("rt_render: scene not committed"); return RT_ERR_STATE; }
-    if (integ->kind != RT_INTEGRATOR_PATH) { set_error("rt_render: only IntType::Path is implemented"); return RT_ERR_INVALID; }
+    if (integ->kind > RT_INTEGRATOR_WHITTED) { set_error("rt_render: unknown integrator kind (IntType::Basic is not implemented)"); return RT_ERR_INVALID; }
+    if (integ->kind != RT_INTEGRATOR_PATH && (integ->flags & RT_SHADE_F32)) { set_error("rt_render: RT_SHADE_F32 is implemented for IntType::Path only"); return RT_ERR_INVALID; }
+    if (integ->kind != RT_INTEGRATOR_PATH && integ->max_depth == 0) { set_error("rt_render: Whitted / Direct need max_depth >= 1 (`depth - 1` underflows in the reference)"); return RT_ERR_INVALID; }
     if (fd->width != film->w || fd->height != film->h) { set_error("rt_render: film size mismatch"); return RT_ERR_INVALID; }
     if (fd->x1 > fd->width || fd->y1 > fd->height || fd->x0 > fd->x1 || fd->y0 > fd->y1 || fd->sample_end < fd->sample_begin) { set_error("rt_render: bad window / sample range"); return RT_ERR_INVALID; }
     if (integ->max_depth > 0xfff0u) { set_error("rt_render: max_depth too large"); return RT_ERR_INVALID; }
@@ -484,7 +488,8 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
     RenderParams rp{};
     rp.cam = *cam; rp.width = fd->width; rp.height = fd->height; rp.x0 = fd->x0; rp.y0 = fd->y0; rp.ww = fd->x1 - fd->x0; rp.wh = fd->y1 - fd->y0;
     rp.sample_begin = fd->sample_begin; rp.max_depth = integ->max_depth; rp.invisible_light = integ->invisible_light;
-    rp.k0 = (uint32_t)fd->seed; rp.k1 = (uint32_t)(fd->seed >> 32); rp.W = w.W;
+    rp.k0 = (uint32_t)fd->seed; rp.k1 = (uint32_t)(fd->seed >> 32); rp.W = w.W; rp.kind = integ->kind;
+    const uint32_t cap = integ->kind == RT_INTEGRATOR_PATH ? w.W : w.W / std::max<uint32_t>(2u, (uint32_t)s->lights.size());
     Ctrl init{}; init.total_samples = (unsigned long long)rp.ww * rp.wh * (fd->sample_end - fd->sample_begin);
     s->counters = rt_counters{};
     if (init.total_samples == 0) return RT_OK;
@@ -504,7 +509,7 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
     if (trace && !w.dbg[0]) { cudaEventCreate(&w.dbg[0]); cudaEventCreate(&w.dbg[1]); }
     while (!done) {
         for (int k = 0; k < (trace ? 1 : 4); k++, iter++) {
-            k_prepare<<<1, 1, 0, st>>>(w.ctrl, w.W);
+            k_prepare<<<1, 1, 0, st>>>(w.ctrl, cap);
             if (k == 0) cudaMemcpyAsync(w.h_ctrl, w.ctrl, sizeof(Ctrl), cudaMemcpyDeviceToHost, st);
             cudaEventRecord(ev(w, n_ev + 0), st);
             k_generate<<<g256, 256, 0, st>>>(w.ctrl, rp, w.set[cur], film->d);
@@ -549,10 +554,11 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
         if (s->cancel.load()) { result = RT_ERR_CANCELLED; set_error("rt_render: cancelled"); done = true; }
         if (n_ev > 200000) n_ev = 2;                  // very long renders: stop growing the event pool (timing breakdown becomes partial)
     }
-    k_prepare<<<1, 1, 0, st>>>(w.ctrl, w.W);         // account the last iteration
+    k_prepare<<<1, 1, 0, st>>>(w.ctrl, cap);         // account the last iteration
     CK(cudaMemcpyAsync(w.h_ctrl, w.ctrl, sizeof(Ctrl), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     // camera samples actually generated: all of them unless cancelled (the closing k_prepare claims n_new more that never run)
+    if (w.h_ctrl->overflow) { set_error("rt_render: wavefront queue overflow (both specular branches taken at many vertices); raise rt_set_wavefront_size"); result = RT_ERR_STATE; }
     const unsigned long long generated = w.h_ctrl->c_paths - w.h_ctrl->n_new;
     k_film_count<<<g256, 256, 0, st>>>(rp, generated, film->d);
     CK(cudaEventRecord(e_end, st));

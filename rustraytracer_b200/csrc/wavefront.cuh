@@ -43,7 +43,7 @@ struct ConnQ {             // shadow / probe queue: a ray (a→b or origin+dir),
     uint32_t *target, *pixel;                     // shadow: light primitive ; probe: light index
 };
 struct Ctrl {
-    uint32_t n_cur, n_new, n_tot, n_next, n_shadow, n_probe, pad0, pad1;
+    uint32_t n_cur, n_new, n_tot, n_next, n_shadow, n_probe, overflow, pad1;   // overflow: a queue append beyond W was dropped (branching integrators only)
     unsigned long long next_sample, sample_base, total_samples;
     unsigned long long c_paths, c_extend, c_shadow, c_probe, c_iter;
     uint32_t fetch[4];           // work counters of the persistent traversal kernels (extend, shadow, probe)
@@ -77,6 +77,7 @@ constexpr uint32_t SORT_CELLS = 1u << (3 * RT_SORT_BITS);
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 struct RenderParams {
     rt_camera cam; uint32_t width, height, x0, y0, ww, wh, sample_begin; uint32_t max_depth, invisible_light; uint32_t k0, k1; uint32_t W;
+    uint32_t kind;               // RT_INTEGRATOR_* ; the f32 kernels are compiled for RT_INTEGRATOR_PATH only
 };
 // first entry of shading bin `bin` in the entry array filled for k_shade
 __device__ __forceinline__ size_t bin_first(const Ctrl* c, const RenderParams& rp, int bin) {
@@ -118,6 +119,11 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
                                               const uint2* __restrict__ bin_idx, ConnQ shq, ConnQ prq, double* film) {
     constexpr uint32_t KM = mat_km<MAT>();
     constexpr int BIN = MAT * 2 + CLS;
+    // Integrator: Path, or (f64 kernels only) Direct{UniformOne}, Direct{UniformAll}, Whitted — integrator.rs:131-165, 257-297.  These
+    // shade EVERY vertex with emission + direct light and continue only along perfectly specular lobes, reflection and transmission
+    // as two independent children (specular_reflect / specular_transmit, integrator.rs:464-504).
+    const uint32_t kind = sizeof(R) == 8 ? rp.kind : (uint32_t)RT_INTEGRATOR_PATH;
+    const bool path = kind == RT_INTEGRATOR_PATH;
     const uint32_t n = c->bin_count[BIN];
     const uint32_t stride = gridDim.x * blockDim.x, k0 = blockIdx.x * blockDim.x + threadIdx.x;
     bin_idx += bin_first(c, rp, BIN);
@@ -155,27 +161,36 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
         }
         bool alive = false;
         do {
-            if (bounces == 0 || specular_bounce) {
+            if (!path || bounces == 0 || specular_bounce) {
                 if (is_some) {
                     uint32_t li = sc.prims[prim].light;
                     if (li != RT_NONE) {
-                        if (rp.invisible_light) { o = rec.p; alive = true; break; }          // go straight through the light, same bounce
+                        if (path && rp.invisible_light) { o = rec.p; alive = true; break; }          // go straight through the light, same bounce
                         film_add(film, pixel, dbl3(cmul(cast3<R>(light_l(sc.lights[li], rec.n, -d)), beta)));   // HitRecord::le (hittable.rs:215-225)
                     }
                 }   // miss: only Infinite lights emit (light.rs:499-513) — none in scope
             }
-            if (!is_some || bounces >= rp.max_depth) break;
+            if (!is_some || (path && bounces >= rp.max_depth)) break;
             Bsdf<R> bsdf;
             compute_scattering<R, MAT>(sc, rec, bsdf);
             const V3<R> wo_w = cast3<R>(rec.wo), sn = cast3<R>(rec.sn);
             // uniform_sample_one_light (integrator.rs:530-557)
             uint32_t n_lights = sc.n_lights;
-            if (n_lights != 0) {
-                uint32_t light_num = min(n_lights - 1, (uint32_t)(unsigned long long)(rng_next(rng) * (double)n_lights));
+            // Path / Direct{UniformOne}: one light picked uniformly, estimate x n_lights.  Direct{UniformAll} (uniform_sample_all_lights,
+            // integrator.rs:506-528): every light once, unscaled.  Whitted (integrator.rs:148-158): every light's sample_li, no MIS, f over ALL lobes.
+            uint32_t l_begin = 0, l_end = n_lights;
+            if (n_lights != 0 && (path || kind == RT_INTEGRATOR_DIRECT)) {
+                l_begin = min(n_lights - 1, (uint32_t)(unsigned long long)(rng_next(rng) * (double)n_lights)); l_end = l_begin + 1;
+            }
+            const R l_scale = (path || kind == RT_INTEGRATOR_DIRECT) ? (R)n_lights : R(1);
+            const bool whitted = !path && kind == RT_INTEGRATOR_WHITTED;
+            // one body, called once (f32 kernels: Path only — the code the compiler sees is the plain `if (n_lights != 0) { ... }`) or per light
+            auto light_estimate = [&](const uint32_t light_num) {
                 D2 u_light; u_light.x = rng_next(rng); u_light.y = rng_next(rng);
-                V2<R> u_scatter; u_scatter.x = rng_real<R>(rng); u_scatter.y = rng_real<R>(rng);
+                V2<R> u_scatter; u_scatter.x = R(0); u_scatter.y = R(0);
+                if (!whitted) { u_scatter.x = rng_real<R>(rng); u_scatter.y = rng_real<R>(rng); }
                 const DLight& light = sc.lights[light_num];
-                const uint32_t nsf = BSDF_ALL - BSDF_SPECULAR;
+                const uint32_t nsf = whitted ? (uint32_t)BSDF_ALL : (uint32_t)(BSDF_ALL - BSDF_SPECULAR);
                 // estimate_direct, light half (integrator.rs:573-597); Light::sample_li Diffuse (light.rs:176-203), Primitive::sample
                 // (primitive.rs:445-456) / Infinite (light.rs:204-245)
                 const bool inf_light = ENVL && light.type == RT_LIGHT_INFINITE;
@@ -208,20 +223,23 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
                     }
                     if (light_pdf > 0. && !is_black(color)) {
                         V3<R> wi = cast3<R>(wid);
-                        V3<R> f = bsdf_f<R, KM>(bsdf, wo_w, wi, nsf) * fabs(dot(wi, sn));
-                        R scattering_pdf = bsdf_pdf<R, KM>(bsdf, wo_w, wi, nsf);
-                        if (!is_black(f)) {
-                            R weight = power_heuristic<R>((R)light_pdf, scattering_pdf);
+                        V3<R> f = bsdf_f<R, KM>(bsdf, wo_w, wi, nsf);
+                        const bool f_some = !is_black(f);         // Whitted tests f itself, estimate_direct f x |cos| (integrator.rs:155, 578-583)
+                        f = f * fabs(dot(wi, sn));
+                        R scattering_pdf = whitted ? R(0) : bsdf_pdf<R, KM>(bsdf, wo_w, wi, nsf);
+                        if (whitted ? f_some : !is_black(f)) {
+                            R weight = whitted ? R(1) : power_heuristic<R>((R)light_pdf, scattering_pdf);
                             V3<R> ld = cmul(f, cast3<R>(color)) * (weight / (R)light_pdf);
-                            V3<R> contrib = cmul(ld * (R)n_lights, beta);
+                            V3<R> contrib = cmul(ld * l_scale, beta);
                             uint32_t q = warp_append(&c->n_shadow);
+                            if (!path && q >= rp.W) { c->overflow = 1u; return; }
                             __stcs(shq.ax + q, rec.p.x); __stcs(shq.ay + q, rec.p.y); __stcs(shq.az + q, rec.p.z); __stcs(shq.bx + q, p1.x); __stcs(shq.by + q, p1.y); __stcs(shq.bz + q, p1.z);
                             __stcs(shq.cr + q, (double)contrib.x); __stcs(shq.cg + q, (double)contrib.y); __stcs(shq.cb + q, (double)contrib.z); __stcs(shq.target + q, inf_light ? RT_NONE : light.prim); __stcs(shq.pixel + q, pixel);
                         }
                     }
                 }
                 // estimate_direct, BSDF half (integrator.rs:601-632)
-                {
+                if (!whitted) {
                     V3<R> f, wi; R scattering_pdf; uint32_t st;
                     bsdf_sample_f<R, KM>(bsdf, wo_w, u_scatter, nsf, rng, f, wi, scattering_pdf, st);
                     f = f * fabs(dot(wi, sn));
@@ -238,13 +256,38 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
                             else weight = power_heuristic<R>(scattering_pdf, (R)light_pdf);
                         }
                         if (go) {
-                            V3<R> contrib = cmul((f * (weight / scattering_pdf)) * (R)n_lights, beta);   // × Le decided by the probe ray
+                            V3<R> contrib = cmul((f * (weight / scattering_pdf)) * l_scale, beta);   // × Le decided by the probe ray
                             uint32_t q = warp_append(&c->n_probe);
+                            if (!path && q >= rp.W) { c->overflow = 1u; return; }
                             prq.ax[q] = rec.p.x; prq.ay[q] = rec.p.y; prq.az[q] = rec.p.z; prq.bx[q] = wid.x; prq.by[q] = wid.y; prq.bz[q] = wid.z;
                             prq.cr[q] = contrib.x; prq.cg[q] = contrib.y; prq.cb[q] = contrib.z; prq.target[q] = light_num; prq.pixel[q] = pixel;
                         }
                     }
                 }
+            };
+            if constexpr (sizeof(R) == 4) { if (n_lights != 0) light_estimate(l_begin); }
+            else { for (uint32_t ln = l_begin; ln < l_end; ln++) light_estimate(ln); }
+            if (!path) {
+                // specular_reflect / specular_transmit (integrator.rs:464-504): `if depth - 1 > 0`, depth = max_depth - bounces.  Both samples are
+                // drawn at the vertex; each surviving branch becomes a queue entry of its own that continues from this dimension counter.
+                if (bounces + 1 >= rp.max_depth) break;
+                V2<R> ub[2];
+                ub[0].x = rng_real<R>(rng); ub[0].y = rng_real<R>(rng); ub[1].x = rng_real<R>(rng); ub[1].y = rng_real<R>(rng);
+#pragma unroll
+                for (int b = 0; b < 2; b++) {
+                    V3<R> f, wi; R pdf; uint32_t sflags;
+                    Rng scratch = rng;            // specular lobes draw nothing
+                    bsdf_sample_f<R, KM>(bsdf, wo_w, ub[b], b == 0 ? (uint32_t)(BSDF_REFLECTION | BSDF_SPECULAR) : (uint32_t)(BSDF_TRANSMISSION | BSDF_SPECULAR), scratch, f, wi, pdf, sflags);
+                    const R cs = fabs(dot(sn, wi));
+                    if (pdf > R(0) && !is_black(f) && cs != R(0)) {
+                        const V3<R> nb = cmul(beta, f) * (cs / pdf);
+                        const uint32_t q = warp_append(&c->n_next);
+                        if (q >= rp.W) { c->overflow = 1u; continue; }
+                        store_ray(out.ray + q, rec.p, dbl3(wi));
+                        store_aux(out.aux + q, (double)nb.x, (double)nb.y, (double)nb.z, pixel, rng.sample, rng.dim, ((bounces + 1u) & 0xffffu) | 0x10000u);
+                    }
+                }
+                break;
             }
             // continuation (integrator.rs:421-441)
             V3<R> wo = cast3<R>(-d);

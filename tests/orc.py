@@ -39,6 +39,8 @@ def lib():
         L.orc_camera_look_at.argtypes = [vp, vp, vp, f64, f64, f64, f64, f64, f64, vp]
         L.orc_render.argtypes = [vp, vp, u32, u32, vp, i32, vp, vp]
         L.orc_render.restype = f64
+        L.orc_render_kind.argtypes = [vp, vp, u32, u32, u32, vp, i32, vp, vp]
+        L.orc_render_kind.restype = f64
         L.orc_render_ex.argtypes = [vp, vp, u32, u32, vp, i32, vp, vp, u32, i32]
         L.orc_render_ex.restype = f64
         L.orc_single_sample.argtypes = [vp, vp, u32, u32, u32, u32, u32, u64, u32, u32, vp]
@@ -172,13 +174,14 @@ class OracleScene:
         secs = lib().orc_render_ex(self.h, C.byref(camera.c), max_depth, 0, C.byref(fd), threads, _p(film), _p(counts), pixel_stride, 1 if count_ordered else 0)
         return film, counts, secs
 
-    def render(self, camera, width, height, sample_begin, sample_end, seed=0, max_depth=25, invisible_light=False, threads=8, window=None, film=None):
+    def render(self, camera, width, height, sample_begin, sample_end, seed=0, max_depth=25, invisible_light=False, threads=8, window=None, film=None, kind=0):
+        """kind: 0 Path, 1 Direct{UniformOne}, 2 Direct{UniformAll}, 3 Whitted (IntType, integrator.rs:25-41)"""
         x0, y0, x1, y1 = window if window is not None else (0, 0, width, height)
         fd = N.FilmDesc(width, height, sample_begin, sample_end, x0, y0, x1, y1, seed)
         if film is None:
             film = np.zeros((height, width, 4), dtype=np.float64)
         counts = np.zeros(3, dtype=np.uint64)
-        secs = lib().orc_render(self.h, C.byref(camera.c), max_depth, 1 if invisible_light else 0, C.byref(fd), threads, _p(film), _p(counts))
+        secs = lib().orc_render_kind(self.h, C.byref(camera.c), kind, max_depth, 1 if invisible_light else 0, C.byref(fd), threads, _p(film), _p(counts))
         return film, counts, secs
 
     def bsdf_f_pdf(self, mat, wo, wi, flags=31, u=0.3, v=0.6):

@@ -217,6 +217,46 @@ def test_render_matches_oracle_per_pixel(name, kw, depth):
     assert np.array_equal(film.resolve_rgb8()[~np.isnan(g[..., 0])], orc.resolve_rgb8(g)[~np.isnan(g[..., 0])])      # point_to_color parity
 
 
+@pytest.mark.parametrize("kind", [1, 2, 3])
+@pytest.mark.parametrize("name,kw,depth", [("cornell_box", {}, 5), ("make_world", {}, 6), ("sphere_roughness", {}, 4),
+                                           ("material_hdr", {"variant": 2}, 5), ("material_hdr", {"variant": 3}, 5), ("plastic_dragon", {}, 3)])
+def test_direct_and_whitted_match_oracle_per_pixel(name, kw, depth, kind):
+    """IntType::Direct{UniformOne, UniformAll} and IntType::Whitted (integrator.rs:131-165, 257-297, 464-528) on the wavefront:
+    emission + direct light at every vertex, recursion along specular lobes only (mirror / smooth glass), per pixel against the oracle."""
+    w = h = 48
+    spp = 4
+    hs = scenes.HostScene(name, w, h, **kw)
+    gpu = hs.upload()
+    oracle = orc.OracleScene(hs.tables())
+    cam = hs.camera()
+    it = {1: IntType.Direct(depth, "UniformOne"), 2: IntType.Direct(depth, "UniformAll"), 3: IntType.Whitted(depth)}[kind]
+    film = Film(w, h)
+    render_samples(gpu, cam, it, film, w, h, 0, spp, seed=11)
+    g = film.read()
+    o, counts, _ = oracle.render(cam, w, h, 0, spp, seed=11, max_depth=depth, kind=kind)
+    film_compare(g, o, f"{name}{kw} kind {kind}")
+    c = gpu.counters()
+    assert c["paths"] == w * h * spp
+    for k, v in zip(("extend_rays", "shadow_rays", "probe_rays"), counts):
+        assert abs(c[k] - int(v)) <= 0.002 * int(v) + 8, (k, c[k], int(v))
+    if kind == 3:
+        assert c["probe_rays"] == 0                      # Whitted never samples the BSDF for direct light
+
+
+def test_integrator_kind_argument_errors():
+    from rustraytracer_b200._native import RtError
+    hs = scenes.HostScene("cornell_box", 32, 32)
+    gpu = hs.upload(); cam = hs.camera(); film = Film(32, 32)
+    bad = IntType.Direct(4); bad.shade_f32 = True        # f32 radiometry exists for Path only
+    with pytest.raises(RtError):
+        render_samples(gpu, cam, bad, film, 32, 32, 0, 1)
+    with pytest.raises(RtError):
+        render_samples(gpu, cam, IntType.Whitted(0), film, 32, 32, 0, 1)       # `depth - 1` underflows in the reference
+    bad = IntType.Path(4); bad.kind = 9
+    with pytest.raises(RtError):
+        render_samples(gpu, cam, bad, film, 32, 32, 0, 1)
+
+
 def test_render_partition_invariance():
     """Size-independent properties at the render level: sample ranges and pixel windows are additive, the
     wavefront size does not matter (RNG is keyed by pixel/sample/dimension, not by scheduling)."""

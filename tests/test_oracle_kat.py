@@ -340,3 +340,34 @@ def test_infinite_light_sample_pdf_le_consistency():
     assert not s2.occluded([(0, 0, 0)], [(0, 20000, 0)], [0], infinite=True)[0]      # the sphere is in the way
     assert s2.occluded([(0, 0, 0)], [(20000, 0, 0)], [0], infinite=True)[0]          # nothing hit -> visible
     assert not s2.occluded([(0, 0, 0)], [(20000, 0, 0)], [0], infinite=False)[0]     # area-light semantics: no hit -> occluded
+
+
+def test_direct_and_whitted_integrators_oracle_properties():
+    """IntType::Direct / Whitted (integrator.rs:131-165, 257-297, 464-528) in the oracle, against what their definitions imply:
+    * on a scene without specular lobes, Direct{UniformOne} with max_depth 1 IS Path with max_depth 1 (emission + one
+      uniform_sample_one_light at the first vertex, same random numbers);
+    * Whitted and Direct{UniformAll} estimate the same direct light (no MIS vs MIS) — equal image means within noise;
+    * recursion only adds non-negative radiance along specular lobes: deeper max_depth never darkens a pixel, and changes
+      nothing on a scene that has no specular lobe."""
+    from rustraytracer_b200 import scenes
+    w = h = 40
+    hs = scenes.HostScene("cornell_box", w, h)
+    s = orc.OracleScene(hs.tables()); cam = hs.camera()
+    path1, _, _ = s.render(cam, w, h, 0, 4, seed=7, max_depth=1, kind=0)
+    dir1, c1, _ = s.render(cam, w, h, 0, 4, seed=7, max_depth=1, kind=1)
+    assert np.allclose(dir1, path1, rtol=1e-12, atol=1e-14)
+    assert c1[0] == w * h * 4                                          # one extend ray per camera sample at depth 1
+    dir5, _, _ = s.render(cam, w, h, 0, 4, seed=7, max_depth=5, kind=1)
+    assert np.array_equal(dir5, dir1)                                  # matte + light materials only: no specular lobe to follow
+    whit, _, _ = s.render(cam, w, h, 0, 64, seed=3, max_depth=3, kind=3)
+    dall, _, _ = s.render(cam, w, h, 0, 64, seed=3, max_depth=3, kind=2)
+    mw, md = whit[..., :3].mean(), dall[..., :3].mean()
+    assert mw > 0 and abs(mw - md) <= 0.03 * md
+    # mirrors and glass: make_world (Lambertian + mirror + glass spheres)
+    hs = scenes.HostScene("make_world", w, h)
+    s = orc.OracleScene(hs.tables()); cam = hs.camera()
+    for kind in (1, 3):
+        d1, n1, _ = s.render(cam, w, h, 0, 2, seed=9, max_depth=1, kind=kind)
+        d6, n6, _ = s.render(cam, w, h, 0, 2, seed=9, max_depth=6, kind=kind)
+        assert np.all(d6[..., :3] >= d1[..., :3] - 1e-12)
+        assert n6[0] > n1[0] and np.any(d6[..., :3] > d1[..., :3] + 1e-9)     # the mirror spheres do recurse
