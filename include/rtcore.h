@@ -144,9 +144,9 @@ typedef struct rt_shadow_query {
 /* `IntType::Path{max_depth, invisible_light}` (integrator.rs:37-40) */
 /* IntType (integrator.rs:25-41).  PATH is the one the reference's main.rs selects.  DIRECT = Direct{strategy: UniformOne},
  * DIRECT_ALL = Direct{strategy: UniformAll}, WHITTED = Whitted: emission + direct light at every vertex, recursion only along
- * perfectly specular lobes (integrator.rs:131-165, 257-297, 464-528); f64 radiometry only, max_depth >= 1.  IntType::Basic
- * (geometry::cast_ray) is not implemented. */
-enum { RT_INTEGRATOR_PATH = 0, RT_INTEGRATOR_DIRECT = 1, RT_INTEGRATOR_DIRECT_ALL = 2, RT_INTEGRATOR_WHITTED = 3 };
+ * perfectly specular lobes (integrator.rs:131-165, 257-297, 464-528).  BASIC = Basic → geometry::cast_ray (geometry.rs:242-277):
+ * no light sampling, a hit light ends the walk, one BSDF sample per vertex.  All but PATH: f64 radiometry only, max_depth >= 1. */
+enum { RT_INTEGRATOR_PATH = 0, RT_INTEGRATOR_DIRECT = 1, RT_INTEGRATOR_DIRECT_ALL = 2, RT_INTEGRATOR_WHITTED = 3, RT_INTEGRATOR_BASIC = 4 };
 /* flags: radiometric precision of the shade kernel.  0 = f64 in the reference's operation order (films match the
  * f64 oracle per pixel); RT_SHADE_F32 = same formulas in f32 (production speed; image parity within the stated
  * relative MSE).  Geometry — intersection decisions, hit points, ray origins — is f64-exact in both. */

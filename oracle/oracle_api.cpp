@@ -165,7 +165,7 @@ double orc_render_ex(void* sp, const rt_camera* cam, uint32_t max_depth, uint32_
                      int threads, double* film, uint64_t* counts, uint32_t pixel_stride, int count_ordered) {
     return render_impl(sp, cam, 0, max_depth, invisible_light, d, threads, film, counts, pixel_stride, count_ordered);
 }
-// kind = rtcore.h RT_INTEGRATOR_*: 0 Path, 1 Direct{UniformOne}, 2 Direct{UniformAll}, 3 Whitted (max_depth >= 1 for 1..3)
+// kind = rtcore.h RT_INTEGRATOR_*: 0 Path, 1 Direct{UniformOne}, 2 Direct{UniformAll}, 3 Whitted, 4 Basic (max_depth >= 1 for 1..4)
 double orc_render_kind(void* sp, const rt_camera* cam, uint32_t kind, uint32_t max_depth, uint32_t invisible_light, const rt_film_desc* d,
                        int threads, double* film, uint64_t* counts) {
     return render_impl(sp, cam, kind, max_depth, invisible_light, d, threads, film, counts, 1, 0);

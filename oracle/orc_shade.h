@@ -770,7 +770,7 @@ inline V3 path_li(const Scene& s, Ray ray, uint32_t max_depth, bool invisible_li
 // WhittedIntegrator::li (integrator.rs:131-165) and DirectLightingIntegrator::li (integrator.rs:257-297) with specular_reflect /
 // specular_transmit (integrator.rs:464-504) and uniform_sample_all_lights (integrator.rs:506-528: ONE (u_light, u_scatter) pair per
 // light, summed, not divided by the sample count — the loop over `samples` is commented out in the reference).
-// kind: 1 = Direct{UniformOne}, 2 = Direct{UniformAll}, 3 = Whitted (rtcore.h RT_INTEGRATOR_*).
+// kind: 1 = Direct{UniformOne}, 2 = Direct{UniformAll}, 3 = Whitted (rtcore.h RT_INTEGRATOR_*; 4 = Basic is basic_li below).
 // Random numbers: the reference threads one sampler through the recursion depth-first; here both branch samples are drawn at the
 // vertex (reflect, then transmit) and each child continues from the vertex's dimension counter — the rule the wavefront kernel
 // follows, where the two children are independent queue entries.  Both are streams of iid uniforms.
@@ -823,6 +823,28 @@ inline V3 sampler_li(const Scene& s, const Ray& ray, uint32_t depth, uint32_t ki
     return ans;
 }
 
+// BasicIntegrator → geometry::cast_ray (geometry.rs:242-277): no light sampling; a hit light returns its emission and ends the walk,
+// anything else is continued through one BSDF sample over ALL lobes, weighted by color / pdf and by |ray.dir . ns| — the INCOMING,
+// unnormalised direction (so camera-ray lengths scale the image; kept, it is what the reference computes); a miss returns
+// sum(light.le) / 4 pi; `depth` counts vertices.
+inline V3 basic_li(const Scene& s, const Ray& ray, uint32_t depth, Rng& rng, RayCounts& rc) {
+    if (depth == 0) return black();
+    HitRecord rec; rc.extend++;
+    if (!get_intersection(s, ray, rec)) {
+        V3 l = black();
+        for (const Light& light : s.lights) l = l + light_le(s, light, ray) * (1. / (4. * PI));
+        return l;
+    }
+    if (s.prims[rec.prim_index].light_index != RT_NONE) return record_le(s, rec, -ray.d);
+    compute_scattering(s, rec, RADIANCE, true);
+    V2 u; u.x = rng.next(); u.y = rng.next();
+    V3 f, wi; double pdf; uint8_t st;
+    bsdf_sample_f(rec.bsdf, -ray.d, u, BSDF_ALL, rng, f, wi, pdf, st);
+    if (pdf == 0.) return black();
+    V3 incoming = basic_li(s, Ray{rec.p, wi, ray.time}, depth - 1, rng, rc);
+    return cmul(incoming, f * (1. / pdf)) * std::fabs(dot(ray.d, rec.shading.n));
+}
+
 // Camera::get_ray (geometry.rs:177-190) with util::rand_in_disk (util.rs:105-113) and rand_range
 inline Ray camera_get_ray(const rt_camera& c, double u, double v, Rng& rng) {
     V3 in_disk;
@@ -847,6 +869,10 @@ inline V3 single_sample(const Scene& s, const rt_camera& cam, uint32_t width, ui
     double fx = (double)px + ox, fy = (double)py + oy;
     rng.next();              // time
     rng.next(); rng.next();  // lens
+    if (kind == 4) {      // BasicIntegrator::single_sample (integrator.rs:196-204) divides by width - 1 / height - 1
+        Ray ray = camera_get_ray(cam, fx / (double)(width - 1), fy / (double)(height - 1), rng);
+        return basic_li(s, ray, max_depth, rng, rc);
+    }
     Ray ray = camera_get_ray(cam, fx / (double)width, fy / (double)height, rng);
     if (kind != 0) return sampler_li(s, ray, max_depth, kind, rng, rc);
     return path_li(s, ray, max_depth, invisible_light, rng, rc);

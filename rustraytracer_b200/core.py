@@ -52,13 +52,13 @@ class Camera:
 class IntType:
     """`IntType` (integrator.rs:25-41).  `Path { max_depth, invisible_light }` is the only integrator the reference ever
     selects (main.rs:262-265); `Direct { max_depth, strategy }` and `Whitted { max_depth }` run on the same wavefront
-    (f64 radiometry only).  `Basic` (geometry::cast_ray) is not implemented."""
+    (f64 radiometry only), as does `Basic { max_depth }` (geometry::cast_ray, geometry.rs:242-277)."""
     max_depth: int = MAX_DEPTH
     invisible_light: bool = False
     # radiometric precision of the shade kernel: False = f64 in the reference's operation order (per-pixel parity
     # with the f64 oracle), True = f32 (production speed).  Intersection decisions are f64-exact in both.
     shade_f32: bool = False
-    kind: int = 0                # rtcore.h RT_INTEGRATOR_*: 0 Path, 1 Direct{UniformOne}, 2 Direct{UniformAll}, 3 Whitted
+    kind: int = 0                # rtcore.h RT_INTEGRATOR_*: 0 Path, 1 Direct{UniformOne}, 2 Direct{UniformAll}, 3 Whitted, 4 Basic
 
     @staticmethod
     def Path(max_depth=MAX_DEPTH, invisible_light=False, shade_f32=False):
@@ -74,6 +74,10 @@ class IntType:
     @staticmethod
     def Whitted(max_depth=MAX_DEPTH):
         return IntType(max_depth, False, False, 3)
+
+    @staticmethod
+    def Basic(max_depth=MAX_DEPTH):
+        return IntType(max_depth, False, False, 4)
 
 
 @dataclass

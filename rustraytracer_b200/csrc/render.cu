@@ -113,7 +113,9 @@ __global__ void __launch_bounds__(256) k_generate(const Ctrl* __restrict__ c, Re
         double fx = (double)px + offx, fy = (double)py + offy;
         rng_next(rng);                       // time
         rng_next(rng); rng_next(rng);        // lens sample (unused by get_ray, which draws its own)
-        double u = fx / (double)rp.width, v = fy / (double)rp.height;
+        // BasicIntegrator::single_sample (integrator.rs:196-204) divides by width - 1 / height - 1
+        const bool basic = rp.kind == RT_INTEGRATOR_BASIC;
+        double u = fx / (double)(basic ? rp.width - 1u : rp.width), v = fy / (double)(basic ? rp.height - 1u : rp.height);
         D3 in_disk;
         for (;;) { double x = rng_next(rng), y = rng_next(rng); if (x * x + y * y < 1.) { in_disk = mk3(x, y, 0.); break; } }   // util::rand_in_disk
         in_disk = in_disk * rp.cam.lens_radius;
@@ -253,7 +255,11 @@ __global__ void __launch_bounds__(128) k_shade_miss(Ctrl* c, DScene sc, RenderPa
         const PRay pr = load_ray(in.ray + i);
         D3 d = mk3(pr.dx, pr.dy, pr.dz), beta = mk3(pa.bx, pa.by, pa.bz), l = mk3(0., 0., 0.);
         for (uint32_t li = 0; li < sc.n_lights; li++)
-            if (sc.lights[li].type == RT_LIGHT_INFINITE) l = l + cmul(infinite_le(sc, sc.lights[li], d), beta);
+            if (sc.lights[li].type == RT_LIGHT_INFINITE) {
+                D3 le = infinite_le(sc, sc.lights[li], d);
+                if (rp.kind == RT_INTEGRATOR_BASIC) le = le * (1. / (4. * PI));     // cast_ray's miss arm (geometry.rs:269-275)
+                l = l + cmul(le, beta);
+            }
         film_add(film, pa.pixel, l);
     }
 }
@@ -474,9 +480,9 @@ rt_status rt_film_resolve_rgb8(rt_film* f, uint8_t* host_rgb) {
 rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc* integ, const rt_film_desc* fd, rt_film* film) {
     if (!s || !cam || !integ || !fd || !film) { set_error("rt_render: null argument"); return RT_ERR_INVALID; }
     if (!s->committed) { set_error("rt_render: scene not committed"); return RT_ERR_STATE; }
-    if (integ->kind > RT_INTEGRATOR_WHITTED) { set_error("rt_render: unknown integrator kind (IntType::Basic is not implemented)"); return RT_ERR_INVALID; }
+    if (integ->kind > RT_INTEGRATOR_BASIC) { set_error("rt_render: unknown integrator kind"); return RT_ERR_INVALID; }
     if (integ->kind != RT_INTEGRATOR_PATH && (integ->flags & RT_SHADE_F32)) { set_error("rt_render: RT_SHADE_F32 is implemented for IntType::Path only"); return RT_ERR_INVALID; }
-    if (integ->kind != RT_INTEGRATOR_PATH && integ->max_depth == 0) { set_error("rt_render: Whitted / Direct need max_depth >= 1 (`depth - 1` underflows in the reference)"); return RT_ERR_INVALID; }
+    if (integ->kind != RT_INTEGRATOR_PATH && integ->max_depth == 0) { set_error("rt_render: Whitted / Direct / Basic need max_depth >= 1"); return RT_ERR_INVALID; }
     if (fd->width != film->w || fd->height != film->h) { set_error("rt_render: film size mismatch"); return RT_ERR_INVALID; }
     if (fd->x1 > fd->width || fd->y1 > fd->height || fd->x0 > fd->x1 || fd->y0 > fd->y1 || fd->sample_end < fd->sample_begin) { set_error("rt_render: bad window / sample range"); return RT_ERR_INVALID; }
     if (integ->max_depth > 0xfff0u) { set_error("rt_render: max_depth too large"); return RT_ERR_INVALID; }
@@ -489,7 +495,7 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
     rp.cam = *cam; rp.width = fd->width; rp.height = fd->height; rp.x0 = fd->x0; rp.y0 = fd->y0; rp.ww = fd->x1 - fd->x0; rp.wh = fd->y1 - fd->y0;
     rp.sample_begin = fd->sample_begin; rp.max_depth = integ->max_depth; rp.invisible_light = integ->invisible_light;
     rp.k0 = (uint32_t)fd->seed; rp.k1 = (uint32_t)(fd->seed >> 32); rp.W = w.W; rp.kind = integ->kind;
-    const uint32_t cap = integ->kind == RT_INTEGRATOR_PATH ? w.W : w.W / std::max<uint32_t>(2u, (uint32_t)s->lights.size());
+    const uint32_t cap = (integ->kind == RT_INTEGRATOR_PATH || integ->kind == RT_INTEGRATOR_BASIC) ? w.W : w.W / std::max<uint32_t>(2u, (uint32_t)s->lights.size());
     Ctrl init{}; init.total_samples = (unsigned long long)rp.ww * rp.wh * (fd->sample_end - fd->sample_begin);
     s->counters = rt_counters{};
     if (init.total_samples == 0) return RT_OK;

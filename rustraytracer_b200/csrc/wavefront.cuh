@@ -124,6 +124,7 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
     // as two independent children (specular_reflect / specular_transmit, integrator.rs:464-504).
     const uint32_t kind = sizeof(R) == 8 ? rp.kind : (uint32_t)RT_INTEGRATOR_PATH;
     const bool path = kind == RT_INTEGRATOR_PATH;
+    const bool basic = !path && kind == RT_INTEGRATOR_BASIC;       // geometry::cast_ray (geometry.rs:242-277)
     const uint32_t n = c->bin_count[BIN];
     const uint32_t stride = gridDim.x * blockDim.x, k0 = blockIdx.x * blockDim.x + threadIdx.x;
     bin_idx += bin_first(c, rp, BIN);
@@ -167,6 +168,7 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
                     if (li != RT_NONE) {
                         if (path && rp.invisible_light) { o = rec.p; alive = true; break; }          // go straight through the light, same bounce
                         film_add(film, pixel, dbl3(cmul(cast3<R>(light_l(sc.lights[li], rec.n, -d)), beta)));   // HitRecord::le (hittable.rs:215-225)
+                        if (basic) break;                                                 // cast_ray returns the emission (geometry.rs:251-253)
                     }
                 }   // miss: only Infinite lights emit (light.rs:499-513) — none in scope
             }
@@ -178,8 +180,8 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
             uint32_t n_lights = sc.n_lights;
             // Path / Direct{UniformOne}: one light picked uniformly, estimate x n_lights.  Direct{UniformAll} (uniform_sample_all_lights,
             // integrator.rs:506-528): every light once, unscaled.  Whitted (integrator.rs:148-158): every light's sample_li, no MIS, f over ALL lobes.
-            uint32_t l_begin = 0, l_end = n_lights;
-            if (n_lights != 0 && (path || kind == RT_INTEGRATOR_DIRECT)) {
+            uint32_t l_begin = 0, l_end = basic ? 0u : n_lights;
+            if (n_lights != 0 && !basic && (path || kind == RT_INTEGRATOR_DIRECT)) {
                 l_begin = min(n_lights - 1, (uint32_t)(unsigned long long)(rng_next(rng) * (double)n_lights)); l_end = l_begin + 1;
             }
             const R l_scale = (path || kind == RT_INTEGRATOR_DIRECT) ? (R)n_lights : R(1);
@@ -267,6 +269,17 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
             };
             if constexpr (sizeof(R) == 4) { if (n_lights != 0) light_estimate(l_begin); }
             else { for (uint32_t ln = l_begin; ln < l_end; ln++) light_estimate(ln); }
+            if (basic) {
+                // cast_ray: one sample over all lobes; weight color / pdf x |incoming ray.dir . ns| (unnormalised, as the reference has it)
+                if (bounces + 1 >= rp.max_depth) break;
+                V2<R> u; u.x = rng_real<R>(rng); u.y = rng_real<R>(rng);
+                V3<R> f, wi; R pdf; uint32_t sflags;
+                bsdf_sample_f<R, KM>(bsdf, cast3<R>(-d), u, BSDF_ALL, rng, f, wi, pdf, sflags);
+                if (pdf == R(0)) break;
+                beta = cmul(beta, f * (R(1) / pdf)) * fabs(dot(cast3<R>(d), sn));
+                o = rec.p; d = dbl3(wi); bounces++; alive = true;
+                break;
+            }
             if (!path) {
                 // specular_reflect / specular_transmit (integrator.rs:464-504): `if depth - 1 > 0`, depth = max_depth - bounces.  Both samples are
                 // drawn at the vertex; each surviving branch becomes a queue entry of its own that continues from this dimension counter.

@@ -217,11 +217,11 @@ def test_render_matches_oracle_per_pixel(name, kw, depth):
     assert np.array_equal(film.resolve_rgb8()[~np.isnan(g[..., 0])], orc.resolve_rgb8(g)[~np.isnan(g[..., 0])])      # point_to_color parity
 
 
-@pytest.mark.parametrize("kind", [1, 2, 3])
+@pytest.mark.parametrize("kind", [1, 2, 3, 4])
 @pytest.mark.parametrize("name,kw,depth", [("cornell_box", {}, 5), ("make_world", {}, 6), ("sphere_roughness", {}, 4),
                                            ("material_hdr", {"variant": 2}, 5), ("material_hdr", {"variant": 3}, 5), ("plastic_dragon", {}, 3)])
 def test_direct_and_whitted_match_oracle_per_pixel(name, kw, depth, kind):
-    """IntType::Direct{UniformOne, UniformAll} and IntType::Whitted (integrator.rs:131-165, 257-297, 464-528) on the wavefront:
+    """IntType::Direct{UniformOne, UniformAll}, IntType::Whitted (integrator.rs:131-165, 257-297, 464-528) and IntType::Basic on the wavefront:
     emission + direct light at every vertex, recursion along specular lobes only (mirror / smooth glass), per pixel against the oracle."""
     w = h = 48
     spp = 4
@@ -229,7 +229,7 @@ def test_direct_and_whitted_match_oracle_per_pixel(name, kw, depth, kind):
     gpu = hs.upload()
     oracle = orc.OracleScene(hs.tables())
     cam = hs.camera()
-    it = {1: IntType.Direct(depth, "UniformOne"), 2: IntType.Direct(depth, "UniformAll"), 3: IntType.Whitted(depth)}[kind]
+    it = {1: IntType.Direct(depth, "UniformOne"), 2: IntType.Direct(depth, "UniformAll"), 3: IntType.Whitted(depth), 4: IntType.Basic(depth)}[kind]
     film = Film(w, h)
     render_samples(gpu, cam, it, film, w, h, 0, spp, seed=11)
     g = film.read()
@@ -241,6 +241,8 @@ def test_direct_and_whitted_match_oracle_per_pixel(name, kw, depth, kind):
         assert abs(c[k] - int(v)) <= 0.002 * int(v) + 8, (k, c[k], int(v))
     if kind == 3:
         assert c["probe_rays"] == 0                      # Whitted never samples the BSDF for direct light
+    if kind == 4:
+        assert c["shadow_rays"] == 0 and c["probe_rays"] == 0       # IntType::Basic → geometry::cast_ray (geometry.rs:242-277): no light sampling
 
 
 def test_integrator_kind_argument_errors():

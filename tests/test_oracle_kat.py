@@ -371,3 +371,23 @@ def test_direct_and_whitted_integrators_oracle_properties():
         d6, n6, _ = s.render(cam, w, h, 0, 2, seed=9, max_depth=6, kind=kind)
         assert np.all(d6[..., :3] >= d1[..., :3] - 1e-12)
         assert n6[0] > n1[0] and np.any(d6[..., :3] > d1[..., :3] + 1e-9)     # the mirror spheres do recurse
+
+
+def test_basic_integrator_oracle_known_answers():
+    """IntType::Basic → geometry::cast_ray (geometry.rs:242-277) in the oracle: a camera ray that hits the light returns its emission
+    and nothing else; with max_depth 1 every other pixel is black (the walk ends before a light can be reached); a second vertex only
+    ever adds light; the film divides by width - 1 (integrator.rs:197-200), so it differs from Path's first vertex only through that."""
+    from rustraytracer_b200 import scenes
+    w = h = 40
+    hs = scenes.HostScene("cornell_box", w, h)
+    s = orc.OracleScene(hs.tables()); cam = hs.camera()
+    b1, n1, _ = s.render(cam, w, h, 0, 2, seed=5, max_depth=1, kind=4)
+    assert n1[0] == w * h * 2 and n1[1] == 0 and n1[2] == 0
+    rgb = b1[..., :3]
+    lit = rgb.max(-1) > 0
+    assert 0 < lit.sum() < 0.2 * w * h                                    # only the pixels that look straight at the ceiling light
+    vals = np.unique(np.round(rgb[lit] / 2.0, 9), axis=0)               # 2 spp: one or two samples saw the light, each adds the same Le
+    le = vals.max(0)
+    assert np.all(le > 0) and all(np.allclose(v, le) or np.allclose(v * 2, le) for v in vals)
+    b3, n3, _ = s.render(cam, w, h, 0, 2, seed=5, max_depth=3, kind=4)
+    assert np.all(b3[..., :3] >= rgb - 1e-12) and (b3[..., :3].max(-1) > 0).sum() > lit.sum() and n3[0] > n1[0]
