@@ -60,16 +60,19 @@ typedef struct rt_primitive {
                               xz: x0,z0,x1,z1,k; yz: y0,z0,y1,z1,k)                        */
 } rt_primitive;
 
-/* `enum Texture` (material.rs:520-539); Perlin is out of scope.
+/* `enum Texture` (material.rs:520-539).  Perlin{perlin} (perlin.rs): 0.5 * (1 + sin(scale * p.z + 10 * turb(p, 7))) in every channel,
+ * a function of the hit POINT; its permutation tables and gradient vectors are added with rt_scene_add_perlin (the reference draws
+ * them from its global RNG in Perlin::new; here the host passes them, so a render is reproducible).  A scene that holds a Perlin
+ * texture is shaded in f64 even when RT_SHADE_F32 is asked for.
  * Hdr{meta,data} and Image{img} keep their texels in an image added with rt_scene_add_image_*:
  * Hdr looks up the nearest texel at (round((1-u)*W) % W, round(v*H) % H), re-quantises it to RGBE8
  * and returns (c+0.5)*2^(e-128)/256 (material.rs:570-587); Image looks up (round(u*W) % W,
  * round((1-v)*H) % H) and returns c/255 (material.rs:601-611).                          */
-enum { RT_TEX_SOLID = 0, RT_TEX_CHECKERED = 1, RT_TEX_HDR = 2, RT_TEX_IMAGE = 3 };
+enum { RT_TEX_SOLID = 0, RT_TEX_CHECKERED = 1, RT_TEX_HDR = 2, RT_TEX_IMAGE = 3, RT_TEX_PERLIN = 4 };
 typedef struct rt_texture {
     uint32_t type;
     uint32_t odd, even;    /* checkered: texture ids (material.rs:528-532)                  */
-    uint32_t image;        /* hdr / image: index returned by rt_scene_add_image_*           */
+    uint32_t image;        /* hdr / image: index returned by rt_scene_add_image_* ; perlin: by rt_scene_add_perlin */
     double   color[3];     /* solid colour                                                  */
     double   frequency;    /* checkered                                                     */
 } rt_texture;
@@ -221,6 +224,9 @@ rt_status rt_scene_set_light_index(rt_scene* scene, uint32_t prim_index, uint32_
 rt_status rt_scene_add_image_hdr(rt_scene* scene, uint32_t width, uint32_t height, const float* rgb, uint32_t* image_index_out);
 /* Texture::new_texture (material.rs:613-616): an `RgbImage`, row-major, width*height*3 bytes       */
 rt_status rt_scene_add_image_rgb8(rt_scene* scene, uint32_t width, uint32_t height, const uint8_t* rgb, uint32_t* image_index_out);
+/* Perlin::new(256, scale) (perlin.rs:17-34, material.rs:628-631): perm = perm_x | perm_y | perm_z, 3 x 256 values < 256;
+ * vecs = 256 unit gradient vectors (xyz).  Texture.image of an RT_TEX_PERLIN texture is the index returned here. */
+rt_status rt_scene_add_perlin(rt_scene* scene, double scale, const uint32_t perm[768], const double vecs[768], uint32_t* perlin_index_out);
 rt_status rt_scene_set_textures(rt_scene* scene, uint64_t n, const rt_texture* textures);
 rt_status rt_scene_set_materials(rt_scene* scene, uint64_t n, const rt_material* materials);
 rt_status rt_scene_set_lights(rt_scene* scene, uint64_t n, const rt_light* lights);

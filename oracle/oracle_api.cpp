@@ -239,6 +239,14 @@ void orc_light_dist(void* sp, uint32_t light, uint64_t n[2], double* cdf_rows, d
     if (marg_int) *marg_int = l.dist.p_marginal.func_int;
 }
 void orc_tex_value(void* sp, uint32_t id, double u, double v, double out[3]) { V3 c = tex_value(*(Scene*)sp, id, u, v); out[0] = c.x; out[1] = c.y; out[2] = c.z; }
+void orc_tex_value_point(void* sp, uint32_t id, double u, double v, const double p[3], double out[3]) { V3 c = tex_value(*(Scene*)sp, id, u, v, V3(p[0], p[1], p[2])); out[0] = c.x; out[1] = c.y; out[2] = c.z; }
+// Texture::new_perlin (material.rs:628-631): perm = perm_x | perm_y | perm_z (3 x 256), vecs = 256 unit vectors
+uint32_t orc_scene_add_perlin(void* sp, double scale, const uint32_t* perm, const double* vecs) {
+    Scene& s = *(Scene*)sp; size_t base = s.perlin.size(); s.perlin.resize(base + 1537); s.perlin[base] = scale;
+    for (int i = 0; i < 768; i++) { s.perlin[base + 1 + i] = (double)perm[i]; s.perlin[base + 769 + i] = vecs[i]; }
+    return (uint32_t)(base / 1537);
+}
+double orc_perlin_noise(void* sp, uint32_t perlin, const double p[3]) { Scene& s = *(Scene*)sp; return perlin_noise(s.perlin.data() + (size_t)perlin * 1537, V3(p[0], p[1], p[2])); }
 double orc_fr_dielectric(double c, double ei, double et) { return fr_dielectric(c, ei, et); }
 void orc_fr_conductor(double c, const double eta[3], const double k[3], double out[3]) { V3 r = fr_conductor(c, V3(eta[0], eta[1], eta[2]), V3(k[0], k[1], k[2])); out[0] = r.x; out[1] = r.y; out[2] = r.z; }
 

@@ -300,6 +300,7 @@ struct Scene {
     std::vector<rt_material> materials;
     std::vector<Light> lights;
     std::vector<Image> images;
+    std::vector<double> perlin;      // 1 + 768 + 768 doubles per Texture::Perlin: scale, perm_x | perm_y | perm_z, 256 gradient vectors
     std::vector<BvhNode> nodes;   // faithful tree (hittable.rs:637-723), root = 0
     int32_t root = -1;
     // ordered tree statistics: counted by closest_ordered()

@@ -379,12 +379,49 @@ inline Rgbe8 to_rgbe8(const float pix[3]) {
     o.e = (uint8_t)(exp + 128);
     return o;
 }
-// Texture::value / get_value (material.rs:542-589): SolidColor, Checkered, Hdr; image_value (material.rs:601-611)
-inline V3 tex_value(const Scene& s, uint32_t id, double u, double v) {
+// perlin::Perlin::get_noise (perlin.rs:36-85).  `x.floor() as usize` saturates (negative -> 0); the gradient weights use the SMOOTHED u, v, w
+inline double perlin_noise(const double* pl, const V3& p) {
+    const double scale = pl[0];
+    const double *px = pl + 1, *py = pl + 257, *pz = pl + 513, *vec = pl + 769;
+    double x = p.x * scale, y = p.y * scale, z = p.z * scale;
+    auto as_usize = [](double f) -> uint64_t { if (!(f > 0.)) return 0; if (f >= 1.8446744073709552e19) return ~0ull; return (uint64_t)f; };
+    uint64_t i0 = as_usize(std::floor(x)), j0 = as_usize(std::floor(y)), k0 = as_usize(std::floor(z));
+    double u = x - std::trunc(x), v = y - std::trunc(y), w = z - std::trunc(z);      // f64::fract
+    if (u < 0.) u += 1.;
+    if (v < 0.) v += 1.;
+    if (w < 0.) w += 1.;
+    V3 c[8];
+    for (int di = 0; di < 2; di++) for (int dj = 0; dj < 2; dj++) for (int dk = 0; dk < 2; dk++) {
+        uint32_t index = (uint32_t)px[(i0 + di) & 255] ^ (uint32_t)py[(j0 + dj) & 255] ^ (uint32_t)pz[(k0 + dk) & 255];
+        c[di + 2 * dj + 4 * dk] = V3(vec[3 * index], vec[3 * index + 1], vec[3 * index + 2]);
+    }
+    u = u * u * (3. - 2. * u); v = v * v * (3. - 2. * v); w = w * w * (3. - 2. * w);
+    double accum = 0.;
+    for (int i = 0; i < 2; i++) for (int j = 0; j < 2; j++) for (int k = 0; k < 2; k++) {
+        V3 weight(u - i, v - j, w - k);
+        double i_part = i * u + (1 - i) * (1. - u), j_part = j * v + (1 - j) * (1. - v), k_part = k * w + (1 - k) * (1. - w);
+        accum += i_part * j_part * k_part * dot(c[i + 2 * j + 4 * k], weight);
+    }
+    return accum;
+}
+// perlin::Perlin::turb (perlin.rs:87-100)
+inline double perlin_turb(const double* pl, const V3& p, int depth) {
+    double accum = 0., weight = 1.; V3 q = p;
+    for (int d = 0; d < depth; d++) { accum += weight * perlin_noise(pl, q); weight *= 0.5; q = V3(q.x * 2., q.y * 2., q.z * 2.); }
+    return std::fabs(accum);
+}
+// Texture::value / get_value (material.rs:542-589): SolidColor, Checkered, Perlin, Hdr; image_value (material.rs:601-611)
+inline V3 tex_value(const Scene& s, uint32_t id, double u, double v, const V3& p = V3(0, 0, 0)) {
     const rt_texture& t = s.textures[id];
     if (t.type == RT_TEX_CHECKERED) {
         double mult = std::sin(t.frequency * u * 2. * PI) * std::sin(t.frequency * v * 2. * PI);
-        return mult < 0. ? tex_value(s, t.even, u, v) : tex_value(s, t.odd, u, v);
+        return mult < 0. ? tex_value(s, t.even, u, v, p) : tex_value(s, t.odd, u, v, p);
+    }
+    if (t.type == RT_TEX_PERLIN) {                                            // material.rs:566-569
+        const double* pl = s.perlin.data() + (size_t)t.image * 1537;
+        double noise = perlin_turb(pl, p, 7);
+        double c = 0.5 * (1. + std::sin(pl[0] * p.z + 10. * noise));
+        return V3(c, c, c);
     }
     if (t.type == RT_TEX_HDR) {
         const Image& im = s.images[t.image];
@@ -420,7 +457,7 @@ inline void compute_scattering(const Scene& s, HitRecord& r, uint8_t mode, bool 
     switch (m.type) {
         case RT_MAT_MATTE: {
             double sig = clampd(m.f[0], 0., 90.);
-            V3 color = tex_value(s, m.tex[0], u, v);
+            V3 color = tex_value(s, m.tex[0], u, v, r.p);
             if (color != black()) {
                 r.bsdf = bsdf_new(r, 1.);
                 if (sig == 0.) bsdf_add(r.bsdf, make_lambert(color)); else bsdf_add(r.bsdf, make_oren_nayar(color, sig));
@@ -429,9 +466,9 @@ inline void compute_scattering(const Scene& s, HitRecord& r, uint8_t mode, bool 
         }
         case RT_MAT_LIGHT: return;
         case RT_MAT_PLASTIC: {
-            V3 color = tex_value(s, m.tex[0], u, v);
+            V3 color = tex_value(s, m.tex[0], u, v, r.p);
             if (color != black()) { r.bsdf = bsdf_new(r, 1.); bsdf_add(r.bsdf, make_lambert(color)); }
-            V3 spec = tex_value(s, m.tex[1], u, v);
+            V3 spec = tex_value(s, m.tex[1], u, v, r.p);
             if (spec != black()) {
                 if (bsdf_is_empty(r.bsdf)) r.bsdf = bsdf_new(r, 1.);
                 Fresnel fr; fr.kind = F_DIELECTRIC; fr.eta_i = 1.5; fr.eta_t = 1.;
@@ -443,7 +480,7 @@ inline void compute_scattering(const Scene& s, HitRecord& r, uint8_t mode, bool 
         }
         case RT_MAT_GLASS: {
             double eta = m.f[2], urough = m.f[0], vrough = m.f[1];
-            V3 rr = tex_value(s, m.tex[0], u, v), t = tex_value(s, m.tex[1], u, v);
+            V3 rr = tex_value(s, m.tex[0], u, v, r.p), t = tex_value(s, m.tex[1], u, v, r.p);
             r.bsdf = bsdf_new(r, eta);
             if (rr == black() && t == black()) return;
             bool is_specular = urough == 0. && vrough == 0.;
@@ -461,17 +498,17 @@ inline void compute_scattering(const Scene& s, HitRecord& r, uint8_t mode, bool 
         }
         case RT_MAT_METAL: {
             r.bsdf = bsdf_new(r, 1.);
-            V3 u_rough = tex_value(s, m.tex[3] == RT_NONE ? m.tex[2] : m.tex[3], u, v);
-            V3 v_rough = tex_value(s, m.tex[4] == RT_NONE ? m.tex[2] : m.tex[4], u, v);
+            V3 u_rough = tex_value(s, m.tex[3] == RT_NONE ? m.tex[2] : m.tex[3], u, v, r.p);
+            V3 v_rough = tex_value(s, m.tex[4] == RT_NONE ? m.tex[2] : m.tex[4], u, v, r.p);
             double ur = m.remap_roughness ? tr_roughness_to_alpha(u_rough.x) : u_rough.x;
             double vr = m.remap_roughness ? tr_roughness_to_alpha(v_rough.x) : v_rough.x;
-            Fresnel fr; fr.kind = F_CONDUCTOR; fr.eta = tex_value(s, m.tex[0], u, v); fr.k = tex_value(s, m.tex[1], u, v);
+            Fresnel fr; fr.kind = F_CONDUCTOR; fr.eta = tex_value(s, m.tex[0], u, v, r.p); fr.k = tex_value(s, m.tex[1], u, v, r.p);
             bsdf_add(r.bsdf, make_microfacet_reflection(white(), fr, make_trowbridge_reitz(ur, vr)));
             return;
         }
         case RT_MAT_MIRROR: {
             r.bsdf = bsdf_new(r, 1.);
-            V3 color = tex_value(s, m.tex[0], u, v);
+            V3 color = tex_value(s, m.tex[0], u, v, r.p);
             if (color != black()) { Fresnel fr; fr.kind = F_NOOP; bsdf_add(r.bsdf, make_specular_reflection(color, fr)); }
             return;
         }

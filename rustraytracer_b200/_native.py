@@ -14,7 +14,7 @@ LIB_PATH = os.environ.get("RT_LIBRTCORE", os.path.join(_HERE, "librtcore.so"))  
 RT_NONE = 0xFFFFFFFF
 RT_OK, RT_ERR_INVALID, RT_ERR_CUDA, RT_ERR_STATE, RT_ERR_CANCELLED, RT_ERR_IO = range(6)
 PRIM_SPHERE, PRIM_TRIANGLE, PRIM_XY_RECT, PRIM_XZ_RECT, PRIM_YZ_RECT = range(5)
-TEX_SOLID, TEX_CHECKERED, TEX_HDR, TEX_IMAGE = 0, 1, 2, 3
+TEX_SOLID, TEX_CHECKERED, TEX_HDR, TEX_IMAGE, TEX_PERLIN = 0, 1, 2, 3, 4
 LIGHT_DIFFUSE, LIGHT_INFINITE = 0, 1
 SHADE_F32 = 1
 MAT_MATTE, MAT_LIGHT, MAT_PLASTIC, MAT_GLASS, MAT_METAL, MAT_MIRROR = range(6)
@@ -71,7 +71,7 @@ class BuildStats(C.Structure):
 RTCORE_SYMBOLS = [
     "rt_last_error_string", "rt_version_string", "rt_device_count", "rt_set_device", "rt_round_spp", "rt_camera_look_at",
     "rt_scene_create", "rt_scene_destroy", "rt_scene_add_mesh", "rt_scene_add_transform", "rt_scene_add_primitives",
-    "rt_scene_add_mesh_triangles", "rt_scene_set_light_index", "rt_scene_add_image_hdr", "rt_scene_add_image_rgb8", "rt_scene_set_textures", "rt_scene_set_materials",
+    "rt_scene_add_mesh_triangles", "rt_scene_set_light_index", "rt_scene_add_image_hdr", "rt_scene_add_image_rgb8", "rt_scene_add_perlin", "rt_scene_set_textures", "rt_scene_set_materials",
     "rt_scene_set_lights", "rt_scene_commit", "rt_scene_num_primitives", "rt_scene_device_bytes", "rt_intersect",
     "rt_intersect_range", "rt_intersect_device", "rt_closest_device", "rt_occluded", "rt_occluded_device", "rt_film_create",
     "rt_film_create_external", "rt_film_destroy", "rt_film_clear", "rt_film_read", "rt_film_resolve_rgb8", "rt_render",
@@ -115,7 +115,7 @@ def lib():
         "rt_scene_add_mesh": [vp, u64, vp, u64, vp, u64, vp, u64, vp, vp],
         "rt_scene_add_transform": [vp, vp, vp], "rt_scene_add_primitives": [vp, u64, vp, vp],
         "rt_scene_add_mesh_triangles": [vp, u32, u32, vp], "rt_scene_set_light_index": [vp, u32, u32],
-        "rt_scene_add_image_hdr": [vp, u32, u32, vp, vp], "rt_scene_add_image_rgb8": [vp, u32, u32, vp, vp],
+        "rt_scene_add_image_hdr": [vp, u32, u32, vp, vp], "rt_scene_add_image_rgb8": [vp, u32, u32, vp, vp], "rt_scene_add_perlin": [vp, f64, vp, vp, vp],
         "rt_scene_set_textures": [vp, u64, vp], "rt_scene_set_materials": [vp, u64, vp], "rt_scene_set_lights": [vp, u64, vp],
         "rt_scene_commit": [vp], "rt_scene_num_primitives": [vp, vp], "rt_scene_device_bytes": [vp, vp, vp, vp],
         "rt_intersect": [vp, u64, vp, vp], "rt_intersect_range": [vp, u64, vp, f64, f64, vp],

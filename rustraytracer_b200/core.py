@@ -155,6 +155,15 @@ class Objects:
         check(lib().rt_scene_add_image_rgb8(self.h, a.shape[1], a.shape[0], ptr(a), C.byref(out)))
         return out.value
 
+    def add_perlin(self, scale, perm, vecs):
+        """`Texture::new_perlin(scale)` → `Perlin::new(256, scale)` (material.rs:628-631, perlin.rs:17-34): perm = (3, 256) permutation
+        tables x / y / z, vecs = (256, 3) unit gradient vectors (the reference draws both from its global RNG)."""
+        pm = np.ascontiguousarray(perm, dtype=np.uint32).reshape(768)
+        vc = np.ascontiguousarray(vecs, dtype=np.float64).reshape(768)
+        out = C.c_uint32()
+        check(lib().rt_scene_add_perlin(self.h, float(scale), ptr(pm), ptr(vc), C.byref(out)))
+        return out.value
+
     def set_textures(self, t):
         t = np.ascontiguousarray(t, dtype=N.texture_dtype)
         check(lib().rt_scene_set_textures(self.h, len(t), ptr(t)))

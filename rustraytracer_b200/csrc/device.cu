@@ -71,6 +71,9 @@ rt_status upload_scene(rt_scene& s, HostImage& img) {
     if ((st = up(s, img.mat_alpha, d.mat_alpha, b))) return st;
     if ((st = up(s, s.images, d.images, b))) return st;
     if ((st = up(s, s.texels, d.texels, b))) return st;
+    if ((st = up(s, s.perlin, d.perlin, b))) return st;
+    d.has_perlin = 0;
+    for (auto& t : s.textures) if (t.type == RT_TEX_PERLIN) d.has_perlin = 1;
     // Infinite lights: upload the flat Distribution2D tables and turn the offsets kept in DLight into device pointers
     const double* d_dist = nullptr;
     if ((st = up(s, img.dist, d_dist, b))) return st;

@@ -79,12 +79,14 @@ struct DScene {
     const double* shapes; const DXform* xforms;
     const rt_texture* textures; const rt_material* materials; const DLight* lights;
     const DImage* images; const uint32_t* texels;
+    const double* perlin;                     // PERLIN_STRIDE doubles per Texture::Perlin: scale, perm_x[256], perm_y[256], perm_z[256], 256 gradient vectors
     const double* mat_alpha;                  // 2 per material: the microfacet alphas of Plastic / Glass / solid-textured Metal after the optional
                                               // roughness remap (microfacet.rs:442-446: an f64 log per shaded vertex otherwise); NaN = evaluate on the device
     uint32_t n_nodes, n_prims, n_lights, n_slots;
-    uint32_t has_infinite, pad0;              // any Light::Infinite in `lights` (misses then emit, light.rs:499-513)
+    uint32_t has_infinite, has_perlin;        // any Light::Infinite in `lights` (misses then emit, light.rs:499-513); any Texture::Perlin
 };
 
+constexpr size_t PERLIN_STRIDE = 1 + 3 * 256 + 3 * 256;
 struct Box64 { double mn[3], mx[3]; };
 
 // host-side primitive record kept by rt_scene (compact; triangles of a mesh are a run)

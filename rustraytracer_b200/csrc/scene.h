@@ -14,6 +14,7 @@ struct rt_scene {
     std::vector<rt_light> lights;
     std::vector<rt::DImage> images;          // Hdr / Image texel blocks (rt_scene_add_image_*)
     std::vector<uint32_t> texels;
+    std::vector<double> perlin;              // PERLIN_STRIDE doubles per rt_scene_add_perlin
     // committed
     bool committed = false;
     int device = 0;

@@ -420,7 +420,8 @@ rt_status rt_scene_set_light_index(rt_scene* s, uint32_t prim, uint32_t light) {
 rt_status rt_scene_set_textures(rt_scene* s, uint64_t n, const rt_texture* t) {
     if (!s || (n && !t)) { set_error("rt_scene_set_textures: null argument"); return RT_ERR_INVALID; }
     for (uint64_t i = 0; i < n; i++) {
-        if (t[i].type > RT_TEX_IMAGE) { set_error("rt_scene_set_textures: unsupported texture type"); return RT_ERR_INVALID; }
+        if (t[i].type > RT_TEX_PERLIN) { set_error("rt_scene_set_textures: unsupported texture type"); return RT_ERR_INVALID; }
+        if (t[i].type == RT_TEX_PERLIN && (size_t)t[i].image >= s->perlin.size() / PERLIN_STRIDE) { set_error("rt_scene_set_textures: perlin index out of range (rt_scene_add_perlin first)"); return RT_ERR_INVALID; }
         if (t[i].type == RT_TEX_CHECKERED && (t[i].odd >= n || t[i].even >= n)) { set_error("rt_scene_set_textures: checkered texture id out of range"); return RT_ERR_INVALID; }
         if ((t[i].type == RT_TEX_HDR || t[i].type == RT_TEX_IMAGE) && t[i].image >= s->images.size()) { set_error("rt_scene_set_textures: image index out of range (add images first)"); return RT_ERR_INVALID; }
     }
@@ -462,6 +463,18 @@ rt_status rt_scene_add_image_rgb8(rt_scene* s, uint32_t w, uint32_t h, const uin
     for (size_t i = 0; i < (size_t)w * h; i++) s->texels[im.offset + i] = (uint32_t)rgb[3 * i] | ((uint32_t)rgb[3 * i + 1] << 8) | ((uint32_t)rgb[3 * i + 2] << 16);
     s->images.push_back(im); s->committed = false;
     if (out) *out = (uint32_t)s->images.size() - 1;
+    return RT_OK;
+}
+// Texture::new_perlin → Perlin::new(256, scale) (material.rs:628-631, perlin.rs:17-34)
+rt_status rt_scene_add_perlin(rt_scene* s, double scale, const uint32_t* perm, const double* vecs, uint32_t* out) {
+    if (!s || !perm || !vecs) { set_error("rt_scene_add_perlin: null argument"); return RT_ERR_INVALID; }
+    for (int i = 0; i < 768; i++) if (perm[i] > 255u) { set_error("rt_scene_add_perlin: permutation value > 255"); return RT_ERR_INVALID; }
+    const size_t base = s->perlin.size();
+    s->perlin.resize(base + PERLIN_STRIDE);
+    s->perlin[base] = scale;
+    for (int i = 0; i < 768; i++) { s->perlin[base + 1 + i] = (double)perm[i]; s->perlin[base + 769 + i] = vecs[i]; }
+    s->committed = false;
+    if (out) *out = (uint32_t)(base / PERLIN_STRIDE);
     return RT_OK;
 }
 rt_status rt_scene_set_materials(rt_scene* s, uint64_t n, const rt_material* m) {

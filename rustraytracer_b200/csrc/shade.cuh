@@ -556,6 +556,58 @@ static __device__ RT_HELPER2 D3 tex_value(const DScene& sc, uint32_t id, double 
     }
     return mk3(0., 0., 0.);
 }
+// Texture::Perlin (material.rs:566-569) over perlin::Perlin::{get_noise, turb} (perlin.rs:36-100).  `x.floor() as usize` saturates:
+// negative coordinates index lattice cell 0 while the fractional part still wraps into [0, 1).
+__device__ __forceinline__ uint32_t sat_index(double x) { return !(x > 0.) ? 0u : (x >= 1.8446744073709552e19 ? 0xffffffffu : (uint32_t)((unsigned long long)x & 0xffffffffull)); }
+static __device__ __noinline__ double perlin_noise(const double* __restrict__ pl, D3 p) {
+    const double scale = pl[0];
+    const double* px = pl + 1; const double* py = pl + 257; const double* pz = pl + 513; const double* vec = pl + 769;
+    const double x = p.x * scale, y = p.y * scale, z = p.z * scale;
+    const uint32_t i0 = sat_index(floor(x)), j0 = sat_index(floor(y)), k0 = sat_index(floor(z));
+    double u = x - trunc(x), v = y - trunc(y), w = z - trunc(z);
+    if (u < 0.) u += 1.;
+    if (v < 0.) v += 1.;
+    if (w < 0.) w += 1.;
+    u = u * u * (3. - 2. * u); v = v * v * (3. - 2. * v); w = w * w * (3. - 2. * w);
+    double accum = 0.;
+    // the reference fills c[di + 2 dj + 4 dk] and then reads c[i + 2 j + 4 k] with weight (u - i, v - j, w - k) built from the SMOOTHED u, v, w
+    for (int i = 0; i < 2; i++)
+        for (int j = 0; j < 2; j++)
+            for (int k = 0; k < 2; k++) {
+                const uint32_t index = (uint32_t)px[(i0 + i) & 255u] ^ (uint32_t)py[(j0 + j) & 255u] ^ (uint32_t)pz[(k0 + k) & 255u];
+                const double cx = vec[3 * index], cy = vec[3 * index + 1], cz = vec[3 * index + 2];
+                const double wx = u - (double)i, wy = v - (double)j, wz = w - (double)k;
+                const double i_part = (double)i * u + (double)(1 - i) * (1. - u);
+                const double j_part = (double)j * v + (double)(1 - j) * (1. - v);
+                const double k_part = (double)k * w + (double)(1 - k) * (1. - w);
+                accum += i_part * j_part * k_part * (cx * wx + cy * wy + cz * wz);
+            }
+    return accum;
+}
+static __device__ __noinline__ D3 perlin_value(const DScene& sc, const rt_texture& t, D3 p) {
+    const double* pl = sc.perlin + (size_t)t.image * PERLIN_STRIDE;
+    double accum = 0., weight = 1.; D3 q = p;
+    for (int d = 0; d < 7; d++) { accum += weight * perlin_noise(pl, q); weight *= 0.5; q = mk3(q.x * 2., q.y * 2., q.z * 2.); }
+    const double c = 0.5 * (1. + sin(pl[0] * p.z + 10. * fabs(accum)));
+    return mk3(c, c, c);
+}
+// Texture::value with the hit point: only scenes that hold a Texture::Perlin take this path (DScene::has_perlin, uniform per launch)
+static __device__ __noinline__ D3 tex_value_point(const DScene& sc, uint32_t id, double u, double v, D3 p) {
+    for (int depth = 0; depth < 8; depth++) {
+        const rt_texture& t = sc.textures[id];
+        if (t.type == RT_TEX_PERLIN) return perlin_value(sc, t, p);
+        if (t.type != RT_TEX_CHECKERED) return tex_value(sc, id, u, v);
+        const double mult = sin(t.frequency * u * 2. * PI) * sin(t.frequency * v * 2. * PI);
+        id = mult < 0. ? t.even : t.odd;
+    }
+    return mk3(0., 0., 0.);
+}
+// POINT = false (the f32 production kernels): the Perlin arm is not compiled in — present, it cost the dragon scene 2 % of its shade time
+// (30.29 vs 29.67 ms at 64 spp, r01) — and rt_render shades scenes that hold a Texture::Perlin with the f64 kernels instead.
+template <bool POINT> __device__ __forceinline__ D3 tex_value_at(const DScene& sc, uint32_t id, double u, double v, const D3& p) {
+    if constexpr (POINT) { if (sc.has_perlin) return tex_value_point(sc, id, u, v, p); }
+    return tex_value(sc, id, u, v);
+}
 template <class R> __device__ __forceinline__ void lobe_init(Lobe<R>& l, int kind, uint32_t type, D3 color) {
     const V3<R> zero = v3<R>(R(0), R(0), R(0));
     l.kind = kind; l.type = type; l.color = cast3<R>(color); l.aux = zero; l.eta3 = zero; l.a = R(0); l.b = R(0);
@@ -586,7 +638,7 @@ template <class R, int MAT> __device__ __forceinline__ void compute_scattering_i
     {
         if (mt == RT_MAT_MATTE) {
             double sig = clampd(m.f[0], 0., 90.);
-            D3 color = tex_value(sc, m.tex[0], u, v);
+            D3 color = tex_value_at<sizeof(R) == 8>(sc, m.tex[0], u, v, r.p);
             if (!is_black(color)) {
                 bsdf_new(b, r);
                 Lobe<R>& l = b.lobes[b.n++];
@@ -601,9 +653,9 @@ template <class R, int MAT> __device__ __forceinline__ void compute_scattering_i
         }
         if (mt == RT_MAT_LIGHT) return;
         if (mt == RT_MAT_PLASTIC) {
-            D3 color = tex_value(sc, m.tex[0], u, v);
+            D3 color = tex_value_at<sizeof(R) == 8>(sc, m.tex[0], u, v, r.p);
             if (!is_black(color)) { bsdf_new(b, r); lobe_init(b.lobes[b.n++], L_LAMBERT, BSDF_REFLECTION | BSDF_DIFFUSE, color); }
-            D3 spec = tex_value(sc, m.tex[1], u, v);
+            D3 spec = tex_value_at<sizeof(R) == 8>(sc, m.tex[1], u, v, r.p);
             if (!is_black(spec)) {
                 if (b.empty) bsdf_new(b, r);
                 double rough = sc.mat_alpha[2 * r.mat];                                     // constant per material: remapped at commit
@@ -617,7 +669,7 @@ template <class R, int MAT> __device__ __forceinline__ void compute_scattering_i
         }
         if (mt == RT_MAT_GLASS) {
             double eta = m.f[2], urough = m.f[0], vrough = m.f[1];
-            D3 rr = tex_value(sc, m.tex[0], u, v), t = tex_value(sc, m.tex[1], u, v);
+            D3 rr = tex_value_at<sizeof(R) == 8>(sc, m.tex[0], u, v, r.p), t = tex_value_at<sizeof(R) == 8>(sc, m.tex[1], u, v, r.p);
             bsdf_new(b, r);
             if (is_black(rr) && is_black(t)) return;
             bool is_specular = urough == 0. && vrough == 0.;
@@ -645,20 +697,20 @@ template <class R, int MAT> __device__ __forceinline__ void compute_scattering_i
         }
         if (mt == RT_MAT_METAL) {
             bsdf_new(b, r);
-            D3 u_rough = tex_value(sc, m.tex[3] == RT_NONE ? m.tex[2] : m.tex[3], u, v);
-            D3 v_rough = tex_value(sc, m.tex[4] == RT_NONE ? m.tex[2] : m.tex[4], u, v);
+            D3 u_rough = tex_value_at<sizeof(R) == 8>(sc, m.tex[3] == RT_NONE ? m.tex[2] : m.tex[3], u, v, r.p);
+            D3 v_rough = tex_value_at<sizeof(R) == 8>(sc, m.tex[4] == RT_NONE ? m.tex[2] : m.tex[4], u, v, r.p);
             const double au = sc.mat_alpha[2 * r.mat], av = sc.mat_alpha[2 * r.mat + 1];
             double ur = au == au ? au : (m.remap_roughness ? tr_roughness_to_alpha(u_rough.x) : u_rough.x);
             double vr = av == av ? av : (m.remap_roughness ? tr_roughness_to_alpha(v_rough.x) : v_rough.x);
             Lobe<R>& l = b.lobes[b.n++];
             lobe_init(l, L_MICRO_R, BSDF_REFLECTION | BSDF_GLOSSY, mk3(1., 1., 1.));
-            l.fresnel = F_CONDUCTOR; l.eta3 = cast3<R>(tex_value(sc, m.tex[0], u, v)); l.aux = cast3<R>(tex_value(sc, m.tex[1], u, v));
+            l.fresnel = F_CONDUCTOR; l.eta3 = cast3<R>(tex_value_at<sizeof(R) == 8>(sc, m.tex[0], u, v, r.p)); l.aux = cast3<R>(tex_value_at<sizeof(R) == 8>(sc, m.tex[1], u, v, r.p));
             l.mfd_empty = false; l.alpha_x = (R)fmax(ur, 1e-3); l.alpha_y = (R)fmax(vr, 1e-3);
             return;
         }
         if (mt == RT_MAT_MIRROR) {
             bsdf_new(b, r);
-            D3 color = tex_value(sc, m.tex[0], u, v);
+            D3 color = tex_value_at<sizeof(R) == 8>(sc, m.tex[0], u, v, r.p);
             if (!is_black(color)) lobe_init(b.lobes[b.n++], L_SPEC_R, BSDF_REFLECTION | BSDF_SPECULAR, color);
             return;
         }

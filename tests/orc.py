@@ -58,6 +58,11 @@ def lib():
         L.orc_scene_add_image_hdr.restype = u32
         L.orc_scene_add_image_rgb8.argtypes = [vp, u32, u32, vp]
         L.orc_scene_add_image_rgb8.restype = u32
+        L.orc_scene_add_perlin.argtypes = [vp, f64, vp, vp]
+        L.orc_scene_add_perlin.restype = u32
+        L.orc_tex_value_point.argtypes = [vp, u32, f64, f64, vp, vp]
+        L.orc_perlin_noise.argtypes = [vp, u32, vp]
+        L.orc_perlin_noise.restype = f64
         L.orc_light_sample_li.argtypes = [vp, u32, vp, vp, vp]
         L.orc_light_pdf_li.argtypes = [vp, u32, vp, vp]
         L.orc_light_pdf_li.restype = f64
@@ -104,6 +109,9 @@ class OracleScene:
                 im = np.ascontiguousarray(im); L.orc_scene_add_image_rgb8(self.h, im.shape[1], im.shape[0], _p(im))
             else:
                 im = np.ascontiguousarray(im, dtype=np.float32); L.orc_scene_add_image_hdr(self.h, im.shape[1], im.shape[0], _p(im))
+        for (scale, perm, vecs) in t.get("perlins", []):
+            pm = np.ascontiguousarray(perm, dtype=np.uint32).reshape(768); vc = np.ascontiguousarray(vecs, dtype=np.float64).reshape(768)
+            L.orc_scene_add_perlin(self.h, float(scale), _p(pm), _p(vc))
         tex = np.ascontiguousarray(t["textures"], dtype=N.texture_dtype)
         L.orc_scene_set_textures(self.h, len(tex), _p(tex) if len(tex) else None)
         mat = np.ascontiguousarray(t["materials"], dtype=N.material_dtype)
@@ -196,6 +204,15 @@ class OracleScene:
         lib().orc_bsdf_sample_f(self.h, mat, u, v, _p(wo), _p(s), flags, seed, pixel, smp, _p(out))
         return out[0:3], out[3:6], out[6], int(out[7])
 
+    def tex_value_point(self, tid, u, v, p):
+        out = np.zeros(3); p = np.ascontiguousarray(p, dtype=np.float64)
+        lib().orc_tex_value_point(self.h, tid, u, v, _p(p), _p(out))
+        return out
+
+    def perlin_noise(self, perlin, p):
+        p = np.ascontiguousarray(p, dtype=np.float64)
+        return lib().orc_perlin_noise(self.h, perlin, _p(p))
+
     def tex_value(self, tid, u, v):
         out = np.zeros(3)
         lib().orc_tex_value(self.h, tid, u, v, _p(out))
@@ -209,7 +226,7 @@ def resolve_rgb8(film):
     return out
 
 
-def simple_tables(prims, textures=None, materials=None, lights=None, meshes=(), transforms=(), images=()):
+def simple_tables(prims, textures=None, materials=None, lights=None, meshes=(), transforms=(), images=(), perlins=()):
     """Plain tables for hand-built KAT scenes."""
     if textures is None:
         textures = np.zeros(1, dtype=N.texture_dtype); textures[0]["color"] = (0.5, 0.5, 0.5)
@@ -218,7 +235,15 @@ def simple_tables(prims, textures=None, materials=None, lights=None, meshes=(), 
     if lights is None:
         lights = np.zeros(0, dtype=N.light_dtype)
     return dict(meshes=list(meshes), prims=np.asarray(prims, dtype=N.prim_dtype), transforms=np.asarray(transforms, dtype=np.float64).reshape(-1, 16),
-                textures=textures, materials=materials, lights=lights, images=list(images))
+                textures=textures, materials=materials, lights=lights, images=list(images), perlins=list(perlins))
+
+
+def perlin_tables(seed, scale):
+    """What Perlin::new(256, scale) draws (perlin.rs:17-34): three shuffled permutations and 256 normalised vectors from [-1, 1]^3."""
+    rng = np.random.default_rng(seed)
+    perm = np.stack([rng.permutation(256) for _ in range(3)]).astype(np.uint32)
+    vecs = rng.uniform(-1, 1, (256, 3)); vecs /= np.linalg.norm(vecs, axis=1, keepdims=True)
+    return (scale, perm, vecs)
 
 
 def prim(ptype, v, mat=0, flip=0, light=N.RT_NONE, mesh=0, ind=0, xf=N.RT_NONE):
@@ -238,6 +263,8 @@ def upload_tables(t):
         o.add_transform(m)
     for im in t.get("images", []):
         o.add_image_rgb8(im) if im.dtype == np.uint8 else o.add_image_hdr(im)
+    for (scale, perm, vecs) in t.get("perlins", []):
+        o.add_perlin(scale, perm, vecs)
     o.set_textures(t["textures"]); o.set_materials(t["materials"]); o.set_lights(t["lights"])
     if len(t["prims"]):
         o.add_primitives(t["prims"])

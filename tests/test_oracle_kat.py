@@ -391,3 +391,63 @@ def test_basic_integrator_oracle_known_answers():
     assert np.all(le > 0) and all(np.allclose(v, le) or np.allclose(v * 2, le) for v in vals)
     b3, n3, _ = s.render(cam, w, h, 0, 2, seed=5, max_depth=3, kind=4)
     assert np.all(b3[..., :3] >= rgb - 1e-12) and (b3[..., :3].max(-1) > 0).sum() > lit.sum() and n3[0] > n1[0]
+
+
+def _perlin_noise_py(scale, perm, vecs, p):
+    """perlin.rs:36-85 restated with Python floats, for the oracle's Perlin to be checked against"""
+    x, y, z = (c * scale for c in p)
+    def cell(f): return 0 if not (math.floor(f) > 0) else int(math.floor(f))            # `as usize` saturates
+    i0, j0, k0 = cell(x), cell(y), cell(z)
+    def fract(f):
+        r = f - math.trunc(f)
+        return r + 1.0 if r < 0 else r
+    u, v, w = fract(x), fract(y), fract(z)
+    c = {}
+    for di in range(2):
+        for dj in range(2):
+            for dk in range(2):
+                c[(di, dj, dk)] = vecs[int(perm[0][(i0 + di) & 255]) ^ int(perm[1][(j0 + dj) & 255]) ^ int(perm[2][(k0 + dk) & 255])]
+    u, v, w = (t * t * (3.0 - 2.0 * t) for t in (u, v, w))
+    acc = 0.0
+    for i in range(2):
+        for j in range(2):
+            for k in range(2):
+                g = c[(i, j, k)]
+                acc += (i * u + (1 - i) * (1 - u)) * (j * v + (1 - j) * (1 - v)) * (k * w + (1 - k) * (1 - w)) * (g[0] * (u - i) + g[1] * (v - j) + g[2] * (w - k))
+    return acc
+
+
+def test_perlin_texture_known_answers():
+    """Texture::Perlin (material.rs:566-569) over perlin.rs: closed form for constant gradients, a Python restatement for random
+    tables (negative coordinates included: the lattice index saturates at 0 while the fraction wraps), turbulence and the marble formula."""
+    const = (2.0, np.tile(np.arange(256, dtype=np.uint32), (3, 1)), np.tile(np.array([0.0, 1.0, 0.0]), (256, 1)))
+    rnd = orc.perlin_tables(3, 1.7)
+    tex = np.zeros(3, dtype=N.texture_dtype)
+    tex[0]["type"] = N.TEX_PERLIN; tex[0]["image"] = 0
+    tex[1]["type"] = N.TEX_PERLIN; tex[1]["image"] = 1
+    tex[2]["type"] = N.TEX_CHECKERED; tex[2]["odd"] = 0; tex[2]["even"] = 1; tex[2]["frequency"] = 3.0
+    s = orc.OracleScene(orc.simple_tables([orc.prim(N.PRIM_SPHERE, [0, 0, 0, 1.0])], textures=tex, perlins=[const, rnd]))
+    # every gradient = +y (v' = smoothed fraction of y): corners j = 0 carry weight (1 - v') and value v', corners j = 1 carry weight v'
+    # and value v' - 1, so noise = (1 - v') v' + v' (v' - 1) = 0 everywhere — the weights use the SMOOTHED fraction (perlin.rs:71-79)
+    for p in ([0.3, 0.4, 0.5], [1.25, -0.7, 3.3], [-2.1, 5.55, -0.2]):
+        assert abs(s.perlin_noise(0, p)) < 1e-15
+    # lattice points: every weight vector that matters is zero
+    assert s.perlin_noise(1, [2.0 / 1.7, 3.0 / 1.7, 5.0 / 1.7]) == pytest.approx(0.0, abs=1e-14)
+    rng = np.random.default_rng(9)
+    pts = np.concatenate([rng.uniform(0, 40, (40, 3)), rng.uniform(-40, 40, (40, 3)), [[300.2, 0.1, 511.9]]])
+    for p in pts:
+        assert s.perlin_noise(1, p) == pytest.approx(_perlin_noise_py(rnd[0], rnd[1], rnd[2], p), abs=1e-14)
+    assert max(abs(s.perlin_noise(1, p)) for p in pts) > 0.05
+    for p in pts[:10]:
+        turb = abs(sum(0.5 ** d * _perlin_noise_py(rnd[0], rnd[1], rnd[2], p * 2.0 ** d) for d in range(7)))
+        want = 0.5 * (1.0 + math.sin(rnd[0] * p[2] + 10.0 * turb))
+        got = s.tex_value_point(1, 0.2, 0.9, p)
+        assert np.allclose(got, [want] * 3, atol=1e-12) and 0.0 <= got[0] <= 1.0
+    # a checker over two Perlin textures picks by (u, v), each child sees the point
+    for (u, v) in ((0.05, 0.05), (0.05, 0.25)):
+        pick = 1 if math.sin(3.0 * u * 2 * orc_pi()) * math.sin(3.0 * v * 2 * orc_pi()) < 0 else 0
+        assert np.array_equal(s.tex_value_point(2, u, v, pts[3]), s.tex_value_point(pick, u, v, pts[3]))
+
+
+def orc_pi():
+    return 3.14159265358979          # consts.rs:31
