@@ -91,20 +91,25 @@ typedef struct rt_material {
     double   f[3];
 } rt_material;
 
-/* `enum Light` (light.rs:30-80): Diffuse (area) lights and the Infinite (environment map)
- * light; the delta lights (Point / Spot / Distant) are out of scope.
+/* `enum Light` (light.rs:30-80): Diffuse (area) lights, the Infinite (environment map) light and
+ * the delta lights Point / Spot / Distant (light.rs:522-582; sample_li light.rs:142-175, pdf_li = 0,
+ * estimate_direct takes them without MIS and without the BSDF half, integrator.rs:587-601).
+ * Point / Spot: `transform` = to_world, the position is to_world x origin; Spot: param = {total_width,
+ * falloff} exactly as handed to Light::make_spot_light (the reference takes cos(x * 180 / PI) of each,
+ * light.rs:548-549); Distant: param = dir (not normalised by the constructor), world_radius = 1e10.
  * Infinite: Light::make_infinite_light(to_world, n_samples, text_id) (light.rs:608-638) — the
  * (2W x 2H) luminance*sin(theta) table and its Distribution2D (distribution.rs:98-148) are built
  * at commit from the texture; world_radius is the reference's fixed 10000 (light.rs:636).   */
-enum { RT_LIGHT_DIFFUSE = 0, RT_LIGHT_INFINITE = 1 };
+enum { RT_LIGHT_DIFFUSE = 0, RT_LIGHT_INFINITE = 1, RT_LIGHT_POINT = 2, RT_LIGHT_SPOT = 3, RT_LIGHT_DISTANT = 4 };
 typedef struct rt_light {
     uint32_t type;
     uint32_t prim_index;   /* diffuse: the emitting primitive (light.rs:62)                 */
     uint32_t two_sided;    /* diffuse                                                       */
     uint32_t text_id;      /* infinite: environment texture (light.rs:74)                   */
-    double   color[3];     /* diffuse                                                       */
-    uint32_t transform;    /* infinite: to_world as an index into transforms, RT_NONE = identity */
+    double   color[3];     /* diffuse, point, spot, distant                                 */
+    uint32_t transform;    /* infinite, point, spot: to_world as an index into transforms, RT_NONE = identity */
     uint32_t _pad;
+    double   param[3];     /* spot: {total_width, falloff, -}; distant: dir                 */
     /* `area` (light.rs:63) is derived from the primitive at commit (primitive.rs:339-359)  */
 } rt_light;
 

@@ -59,6 +59,7 @@ void orc_scene_commit(void* sp, uint64_t bvh_seed) {
     for (size_t i = 0; i < s.prims.size(); i++) s.boxes[i] = prim_box(s, s.prims[i]);
     for (auto& L : s.lights) {
         if (L.d.type == RT_LIGHT_INFINITE) make_infinite_light(s, L);           // light.rs:608-638
+        else if (is_delta_light(L)) make_delta_light(s, L);                    // light.rs:522-582
         else L.area = prim_area(s, s.prims[L.d.prim_index]);                    // light.rs:603
     }
     s.nodes.clear(); s.root = -1;

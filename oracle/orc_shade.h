@@ -657,10 +657,49 @@ inline V3 light_le(const Scene& s, const Light& l, const Ray& ray) {
     return tex_value(s, l.d.text_id, uv.x, uv.y);
 }
 
-// Light::sample_li, Diffuse arm (light.rs:176-203) → wi, pdf, color, visibility target
+// Light::is_delta_light (light.rs:124-127): Point / Spot carry DELTA_POSITION, Distant DELTA_DIRECTION
+inline bool is_delta_light(const Light& l) { return l.d.type == RT_LIGHT_POINT || l.d.type == RT_LIGHT_SPOT || l.d.type == RT_LIGHT_DISTANT; }
+constexpr double DISTANT_WORLD_RADIUS = 1e10;                              // light.rs:579
+// make_point_light / make_spot_light (light.rs:522-560): position = to_world x origin; the spot cosines are taken of
+// (angle x 180 / PI) — the reference converts radians to degrees and then calls cos() on the result; kept as is
+inline void make_delta_light(const Scene& s, Light& l) {
+    if (l.d.type == RT_LIGHT_DISTANT) return;
+    l.pos = l.d.transform == RT_NONE ? V3(0, 0, 0) : xf_point(s.xforms[l.d.transform].fwd, V3(0, 0, 0));
+    if (l.d.type == RT_LIGHT_SPOT) { l.cos_width = std::cos(l.d.param[0] * 180. * INV_PI); l.cos_falloff = std::cos(l.d.param[1] * 180. * INV_PI); }
+}
+// falloff (light.rs:15-26)
+inline double spot_falloff(const Scene& s, const Light& l, const V3& w) {
+    V3 wl = normalize(light_to_obj(s, l, w));
+    double cos_theta = wl.z;
+    if (cos_theta < l.cos_width) return 0.;
+    else if (cos_theta > l.cos_falloff) return 1.;
+    double delta = (cos_theta - l.cos_width) / (l.cos_falloff - l.cos_width);
+    return (delta * delta) * (delta * delta);
+}
+
+// Light::sample_li (light.rs:136-247) → wi, pdf, color, visibility target.  The delta lights' target record is
+// HitRecord::make_basic: prim_index 0, so Visibility::unoccluded (hittable.rs:25-39) lets their light through only where the
+// closest hit of the unbounded shadow ray is primitive 0 — the reference's behaviour, restated as it is.
 struct LiSample { V3 wi; double pdf; V3 color; V3 p1; uint32_t p1_prim; double p1_t; };
 inline LiSample sample_li(const Scene& s, const Light& l, const HitRecord& rec, const V2& u) {
     LiSample o;
+    if (l.d.type == RT_LIGHT_POINT || l.d.type == RT_LIGHT_SPOT) {          // light.rs:142-162
+        o.wi = normalize(l.pos - rec.p); o.pdf = 1.;
+        o.p1 = l.pos; o.p1_prim = 0; o.p1_t = rec.t;
+        V3 c(l.d.color[0], l.d.color[1], l.d.color[2]);
+        double scale = 1. / norm2(l.pos - rec.p);
+        if (l.d.type == RT_LIGHT_SPOT) scale = spot_falloff(s, l, -o.wi) / norm2(l.pos - rec.p);
+        o.color = c * scale;
+        return o;
+    }
+    if (l.d.type == RT_LIGHT_DISTANT) {                                     // light.rs:163-175
+        V3 dir(l.d.param[0], l.d.param[1], l.d.param[2]);
+        o.pdf = 1.;
+        o.p1 = rec.p + dir * (2. * DISTANT_WORLD_RADIUS); o.p1_prim = 0; o.p1_t = rec.t;
+        o.color = V3(l.d.color[0], l.d.color[1], l.d.color[2]);
+        o.wi = normalize(dir);
+        return o;
+    }
     if (l.d.type == RT_LIGHT_INFINITE) {                                   // light.rs:204-245
         V2 uv; double map_pdf;
         dist2_sample_continuous(l.dist, u, uv, map_pdf);
@@ -693,6 +732,7 @@ inline LiSample sample_li(const Scene& s, const Light& l, const HitRecord& rec, 
 }
 // Light::pdf_li, Diffuse arm (light.rs:284)
 inline double pdf_li(const Scene& s, const Light& l, const HitRecord& rec, const V3& wi) {
+    if (is_delta_light(l)) return 0.;                                       // light.rs:281-283
     if (l.d.type == RT_LIGHT_INFINITE) {                                   // light.rs:285-294
         V3 w = light_to_world(s, l, wi);
         double theta = spherical_theta(w), phi = spherical_phi(w);
@@ -713,7 +753,7 @@ inline double power_heuristic(int nf, double f_pdf, int ng, double g_pdf) {     
     double f = nf * f_pdf, g = ng * g_pdf;
     return (f * f) / (f * f + g * g);
 }
-// estimate_direct (integrator.rs:559-634), specular = false; area lights are never delta / infinite
+// estimate_direct (integrator.rs:559-634), specular = false
 inline V3 estimate_direct(const Scene& s, const HitRecord& rec, const V2& u_scatter, uint32_t light_num, const V2& u_light, Rng& rng, RayCounts& rc) {
     const Light& light = s.lights[light_num];
     uint8_t flags = BSDF_ALL - BSDF_SPECULAR;
@@ -727,12 +767,15 @@ inline V3 estimate_direct(const Scene& s, const HitRecord& rec, const V2& u_scat
             rc.shadow++;
             if (!unoccluded(s, rec.p, ls.p1, ls.p1_prim, ls.p1_t, light.d.type == RT_LIGHT_INFINITE)) color = black();
             if (color != black()) {
-                double weight = power_heuristic(1, light_pdf, 1, scattering_pdf);
-                ld = ld + cmul(f, color) * (weight / light_pdf);
+                if (is_delta_light(light)) ld = ld + cmul(f, color) * (1. / light_pdf);   // integrator.rs:587-588
+                else {
+                    double weight = power_heuristic(1, light_pdf, 1, scattering_pdf);
+                    ld = ld + cmul(f, color) * (weight / light_pdf);
+                }
             }
         }
     }
-    {
+    if (!is_delta_light(light)) {                                            // integrator.rs:601
         V3 f, wi; double scattering_pdf; uint8_t st;
         bsdf_sample_f(rec.bsdf, rec.wo, u_scatter, flags, rng, f, wi, scattering_pdf, st);
         f = f * std::fabs(dot(wi, rec.shading.n));

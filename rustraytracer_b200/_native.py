@@ -15,7 +15,7 @@ RT_NONE = 0xFFFFFFFF
 RT_OK, RT_ERR_INVALID, RT_ERR_CUDA, RT_ERR_STATE, RT_ERR_CANCELLED, RT_ERR_IO = range(6)
 PRIM_SPHERE, PRIM_TRIANGLE, PRIM_XY_RECT, PRIM_XZ_RECT, PRIM_YZ_RECT = range(5)
 TEX_SOLID, TEX_CHECKERED, TEX_HDR, TEX_IMAGE, TEX_PERLIN = 0, 1, 2, 3, 4
-LIGHT_DIFFUSE, LIGHT_INFINITE = 0, 1
+LIGHT_DIFFUSE, LIGHT_INFINITE, LIGHT_POINT, LIGHT_SPOT, LIGHT_DISTANT = range(5)
 SHADE_F32 = 1
 MAT_MATTE, MAT_LIGHT, MAT_PLASTIC, MAT_GLASS, MAT_METAL, MAT_MIRROR = range(6)
 
@@ -25,13 +25,13 @@ prim_dtype = np.dtype([("type", "<u4"), ("flip_face", "<u4"), ("mat_index", "<u4
 texture_dtype = np.dtype([("type", "<u4"), ("odd", "<u4"), ("even", "<u4"), ("image", "<u4"), ("color", "<f8", (3,)), ("frequency", "<f8")], align=True)
 material_dtype = np.dtype([("type", "<u4"), ("remap_roughness", "<u4"), ("tex", "<u4", (5,)), ("_pad", "<u4"), ("f", "<f8", (3,))], align=True)
 light_dtype = np.dtype([("type", "<u4"), ("prim_index", "<u4"), ("two_sided", "<u4"), ("text_id", "<u4"), ("color", "<f8", (3,)),
-                        ("transform", "<u4"), ("_pad", "<u4")], align=True)
+                        ("transform", "<u4"), ("_pad", "<u4"), ("param", "<f8", (3,))], align=True)
 ray_dtype = np.dtype([("origin", "<f8", (3,)), ("dir", "<f8", (3,))], align=True)
 hit_dtype = np.dtype([("t", "<f8"), ("p", "<f8", (3,)), ("n", "<f8", (3,)), ("ns", "<f8", (3,)), ("uv", "<f8", (2,)),
                       ("prim_index", "<u4"), ("front", "<u4")], align=True)
 shadow_dtype = np.dtype([("p0", "<f8", (3,)), ("p1", "<f8", (3,)), ("p1_prim_index", "<u4"), ("infinite_light", "<u4")], align=True)
 assert prim_dtype.itemsize == 72 and texture_dtype.itemsize == 48 and material_dtype.itemsize == 56
-assert light_dtype.itemsize == 48 and ray_dtype.itemsize == 48 and hit_dtype.itemsize == 104 and shadow_dtype.itemsize == 56
+assert light_dtype.itemsize == 72 and ray_dtype.itemsize == 48 and hit_dtype.itemsize == 104 and shadow_dtype.itemsize == 56
 
 
 class Camera(C.Structure):

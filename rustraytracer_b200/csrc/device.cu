@@ -78,7 +78,9 @@ rt_status upload_scene(rt_scene& s, HostImage& img) {
     const double* d_dist = nullptr;
     if ((st = up(s, img.dist, d_dist, b))) return st;
     std::vector<DLight> lights = img.lights;
+    d.has_delta = 0;
     for (auto& l : lights) {
+        if (l.type == RT_LIGHT_POINT || l.type == RT_LIGHT_SPOT || l.type == RT_LIGHT_DISTANT) d.has_delta = 1;
         if (l.type != RT_LIGHT_INFINITE) continue;
         d.has_infinite = 1;
         l.dist_f = d_dist + ((uintptr_t)l.dist_f - 1); l.dist_cdf = d_dist + ((uintptr_t)l.dist_cdf - 1);

@@ -66,7 +66,10 @@ struct DXform { double fwd[16], inv[16]; };
 struct DLight {
     uint32_t prim, two_sided, type, text_id; double color[3]; double area;
     uint32_t xform, nu, nv, pad; const double *dist_f, *dist_cdf, *row_int, *marg_cdf; double marg_int;
+    // delta lights (light.rs:522-582): Point / Spot position (to_world x origin) or the Distant direction; the Spot cosines
+    double pos[3]; double cos_width, cos_falloff;
 };
+constexpr double DISTANT_WORLD_RADIUS = 1e10;   // light.rs:579
 // texel storage of Hdr / Image textures: one u32 per texel.  Hdr: the RGBE8 quadruple AFTER the re-quantisation of
 // material.rs:578 (r | g<<8 | b<<16 | e<<24); Image: r | g<<8 | b<<16.
 struct DImage { uint64_t offset; uint32_t w, h; };
@@ -84,6 +87,7 @@ struct DScene {
                                               // roughness remap (microfacet.rs:442-446: an f64 log per shaded vertex otherwise); NaN = evaluate on the device
     uint32_t n_nodes, n_prims, n_lights, n_slots;
     uint32_t has_infinite, has_perlin;        // any Light::Infinite in `lights` (misses then emit, light.rs:499-513); any Texture::Perlin
+    uint32_t has_delta, pad_;                 // any Point / Spot / Distant light (f64 shade kernels only)
 };
 
 constexpr size_t PERLIN_STRIDE = 1 + 3 * 256 + 3 * 256;

@@ -307,6 +307,20 @@ rt_status build_host_image(const rt_scene& s, HostImage& img, bool device_build)
             d.prim = l.prim_index; d.two_sided = l.two_sided;
             for (int k = 0; k < 3; k++) d.color[k] = l.color[k];
             d.area = prim_area(s, s.prims[d.prim]);          // light.rs:603
+        } else if (l.type == RT_LIGHT_POINT || l.type == RT_LIGHT_SPOT || l.type == RT_LIGHT_DISTANT) {
+            // make_point_light / make_spot_light / make_distant_light (light.rs:522-582)
+            if (l.transform != RT_NONE && l.transform >= s.xforms.size()) { set_error("commit: light transform out of range"); return RT_ERR_INVALID; }
+            d.prim = 0; d.xform = l.transform;               // HitRecord::make_basic: the visibility target is primitive 0 (hittable.rs:138)
+            for (int k = 0; k < 3; k++) d.color[k] = l.color[k];
+            if (l.type == RT_LIGHT_DISTANT) { for (int k = 0; k < 3; k++) d.pos[k] = l.param[k]; }
+            else if (l.transform != RT_NONE) {
+                const double* m = s.xforms[l.transform].fwd;  // to_world.transform_point(origin): translation column over w
+                for (int k = 0; k < 3; k++) d.pos[k] = m[4 * k + 3] / m[15];
+            }
+            if (l.type == RT_LIGHT_SPOT) {
+                // light.rs:548-549 takes cos(angle * 180 / PI) of the radian arguments; restated as it is
+                d.cos_width = std::cos(l.param[0] * 180. * (1. / M_PI)); d.cos_falloff = std::cos(l.param[1] * 180. * (1. / M_PI));
+            }
         } else {
             rt_status st = build_infinite_light(s, l, d, img.dist);
             if (st != RT_OK) return st;
@@ -484,7 +498,7 @@ rt_status rt_scene_set_materials(rt_scene* s, uint64_t n, const rt_material* m) 
 }
 rt_status rt_scene_set_lights(rt_scene* s, uint64_t n, const rt_light* l) {
     if (!s || (n && !l)) { set_error("rt_scene_set_lights: null argument"); return RT_ERR_INVALID; }
-    for (uint64_t i = 0; i < n; i++) if (l[i].type > RT_LIGHT_INFINITE) { set_error("rt_scene_set_lights: unsupported light type"); return RT_ERR_INVALID; }
+    for (uint64_t i = 0; i < n; i++) if (l[i].type > RT_LIGHT_DISTANT) { set_error("rt_scene_set_lights: unsupported light type"); return RT_ERR_INVALID; }
     s->lights.assign(l, l + n); s->committed = false; return RT_OK;
 }
 rt_status rt_scene_commit(rt_scene* s) {

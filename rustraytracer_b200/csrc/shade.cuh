@@ -793,6 +793,26 @@ static __device__ __noinline__ void infinite_sample_li(const DScene& sc, const D
     color = tex_value(sc, l.text_id, d0, d1);
     wi = normalize(w);
 }
+// Light::sample_li, Point / Spot / Distant arms (light.rs:142-175): pdf = 1, the shadow ray ends at the light position (Distant:
+// 2 x 1e10 along dir).  The visibility target is primitive 0 (HitRecord::make_basic), as the reference has it.
+static __device__ __noinline__ void delta_sample_li(const DScene& sc, const DLight& l, D3 p, D3& wi, double& pdf, D3& color, D3& p1) {
+    const D3 lp = ld3(l.pos), c = ld3(l.color);
+    pdf = 1.;
+    if (l.type == RT_LIGHT_DISTANT) { p1 = p + lp * (2. * DISTANT_WORLD_RADIUS); color = c; wi = normalize(lp); return; }
+    wi = normalize(lp - p); p1 = lp;
+    double scale = 1. / norm2(lp - p);
+    if (l.type == RT_LIGHT_SPOT) {
+        // falloff (light.rs:15-26)
+        const D3 wl = normalize(light_to_obj(sc, l, -wi));
+        const double cos_theta = wl.z;
+        double fo;
+        if (cos_theta < l.cos_width) fo = 0.;
+        else if (cos_theta > l.cos_falloff) fo = 1.;
+        else { const double delta = (cos_theta - l.cos_width) / (l.cos_falloff - l.cos_width); fo = (delta * delta) * (delta * delta); }
+        scale = fo / norm2(lp - p);
+    }
+    color = c * scale;
+}
 // Light::pdf_li, Infinite arm (light.rs:285-294) — transforms with to_world, as the reference does
 static __device__ __noinline__ double infinite_pdf_li(const DScene& sc, const DLight& l, D3 wi) {
     D3 w = light_to_world(sc, l, wi);

@@ -196,9 +196,14 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
                 // estimate_direct, light half (integrator.rs:573-597); Light::sample_li Diffuse (light.rs:176-203), Primitive::sample
                 // (primitive.rs:445-456) / Infinite (light.rs:204-245)
                 const bool inf_light = ENVL && light.type == RT_LIGHT_INFINITE;
+                // Point / Spot / Distant (light.rs:142-175): f64 kernels only (rt_render shades a scene that holds one in f64); no MIS weight
+                // and no BSDF half (integrator.rs:587-601)
+                bool delta = false;
+                if constexpr (sizeof(R) == 8) delta = sc.has_delta != 0 && light.type >= RT_LIGHT_POINT;
                 {
                     D3 p1; double light_pdf; D3 color, wid = mk3(0., 0., 0.);
                     if (inf_light) infinite_sample_li(sc, light, rec.p, u_light, wid, light_pdf, color, p1);
+                    else if (delta) { if constexpr (sizeof(R) == 8) delta_sample_li(sc, light, rec.p, wid, light_pdf, color, p1); }
                     else {
                         D3 n1; sample_area(sc, light.prim, u_light, p1, n1);
                         if constexpr (sizeof(R) == 4) {
@@ -230,7 +235,7 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
                         f = f * fabs(dot(wi, sn));
                         R scattering_pdf = whitted ? R(0) : bsdf_pdf<R, KM>(bsdf, wo_w, wi, nsf);
                         if (whitted ? f_some : !is_black(f)) {
-                            R weight = whitted ? R(1) : power_heuristic<R>((R)light_pdf, scattering_pdf);
+                            R weight = (whitted || delta) ? R(1) : power_heuristic<R>((R)light_pdf, scattering_pdf);
                             V3<R> ld = cmul(f, cast3<R>(color)) * (weight / (R)light_pdf);
                             V3<R> contrib = cmul(ld * l_scale, beta);
                             uint32_t q = warp_append(&c->n_shadow);
@@ -241,7 +246,7 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
                     }
                 }
                 // estimate_direct, BSDF half (integrator.rs:601-632)
-                if (!whitted) {
+                if (!whitted && !delta) {
                     V3<R> f, wi; R scattering_pdf; uint32_t st;
                     bsdf_sample_f<R, KM>(bsdf, wo_w, u_scatter, nsf, rng, f, wi, scattering_pdf, st);
                     f = f * fabs(dot(wi, sn));

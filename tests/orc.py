@@ -238,6 +238,39 @@ def simple_tables(prims, textures=None, materials=None, lights=None, meshes=(), 
                 textures=textures, materials=materials, lights=lights, images=list(images), perlins=list(perlins))
 
 
+def delta_light_tables(area_light=True):
+    """Hand-built scene for Light::Point / Spot / Distant (light.rs:30-58, 142-175, 522-582).  Primitive 0 is the enclosing sphere: the
+    delta lights' visibility record is HitRecord::make_basic (prim_index 0), so Visibility::unoccluded (hittable.rs:25-39) lets their
+    light through only where the unbounded shadow ray's closest hit is primitive 0 — here wherever nothing stands between the shaded
+    point, the light and the wall behind it."""
+    tex = np.zeros(4, dtype=N.texture_dtype)
+    tex[0]["color"] = (0.7, 0.7, 0.7); tex[1]["color"] = (0.9, 0.5, 0.2); tex[2]["color"] = (1, 1, 1); tex[3]["color"] = (0.3, 0.6, 0.9)
+    mat = np.zeros(5, dtype=N.material_dtype); mat["tex"] = N.RT_NONE
+    mat[0]["type"] = N.MAT_MATTE; mat[0]["tex"][0] = 0                                    # Lambertian walls / floor
+    mat[1]["type"] = N.MAT_MATTE; mat[1]["tex"][0] = 1; mat[1]["f"][0] = 25.0             # Oren-Nayar ball
+    mat[2]["type"] = N.MAT_MIRROR; mat[2]["tex"][0] = 2
+    mat[3]["type"] = N.MAT_GLASS; mat[3]["tex"][0] = 2; mat[3]["tex"][1] = 2; mat[3]["f"] = (0.0, 0.0, 1.5)
+    mat[4]["type"] = N.MAT_PLASTIC; mat[4]["tex"][0] = 3; mat[4]["tex"][1] = 2; mat[4]["f"][0] = 0.2; mat[4]["remap_roughness"] = 1
+    a = 0.5                                                                               # spot: tilted about x, then lifted to (1.5, 4, -1)
+    ca, sa = np.cos(a), np.sin(a)
+    # falloff reads the object-space z of the direction (light.rs:17): the object z axis maps onto (0, -cos a, -sin a), down and towards -z
+    spot_xf = [1, 0, 0, 1.5, 0, -sa, -ca, 4.0, 0, ca, -sa, -1.0, 0, 0, 0, 1]
+    point_xf = [1, 0, 0, -2.0, 0, 1, 0, 3.0, 0, 0, 1, 1.0, 0, 0, 0, 1]
+    lig = np.zeros(4 if area_light else 3, dtype=N.light_dtype)
+    lig["prim_index"] = N.RT_NONE; lig["transform"] = N.RT_NONE
+    lig[0]["type"] = N.LIGHT_POINT; lig[0]["color"] = (30, 24, 18); lig[0]["transform"] = 1
+    # total_width / falloff go through cos(x * 180 / PI) (light.rs:548-549): 0.009 -> cos(0.5157) = 0.870, 0.004 -> cos(0.2292) = 0.974
+    lig[1]["type"] = N.LIGHT_SPOT; lig[1]["color"] = (60, 80, 100); lig[1]["transform"] = 0; lig[1]["param"] = (0.009, 0.004, 0.0)
+    lig[2]["type"] = N.LIGHT_DISTANT; lig[2]["color"] = (0.8, 0.7, 0.5); lig[2]["param"] = (0.3, 2.0, -0.4)    # dir is not normalised
+    prims = [prim(N.PRIM_SPHERE, [0, 0, 0, 30.0], mat=0), prim(N.PRIM_XZ_RECT, [-8, -8, 8, 8, 0.0], mat=0),
+             prim(N.PRIM_SPHERE, [-1.3, 1.0, 0.0, 1.0], mat=1), prim(N.PRIM_SPHERE, [1.2, 0.8, 0.6, 0.8], mat=2),
+             prim(N.PRIM_SPHERE, [0.2, 0.6, -1.6, 0.6], mat=3), prim(N.PRIM_SPHERE, [2.8, 0.7, -1.2, 0.7], mat=4)]
+    if area_light:
+        lig[3]["type"] = N.LIGHT_DIFFUSE; lig[3]["prim_index"] = 6; lig[3]["color"] = (5, 5, 5)
+        prims.append(prim(N.PRIM_XZ_RECT, [-1, -1, 1, 1, 6.0], mat=0, flip=1, light=3))
+    return simple_tables(prims, textures=tex, materials=mat, lights=lig, transforms=[spot_xf, point_xf])
+
+
 def perlin_tables(seed, scale):
     """What Perlin::new(256, scale) draws (perlin.rs:17-34): three shuffled permutations and 256 normalised vectors from [-1, 1]^3."""
     rng = np.random.default_rng(seed)

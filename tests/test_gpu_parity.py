@@ -629,3 +629,32 @@ def test_device_lbvh_small_scene_falls_back_to_host_build():
     assert obj.build_stats()["mode"] == N.BUILD_HOST_SAH
     rays = hs.camera().primary_rays(32, 32)
     compare_hits(get_intersection(obj, rays), orc.OracleScene(tab).intersect(rays, mode=0), None, "5 prims")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind,area,f32", [(0, True, False), (0, True, True), (0, False, False), (1, True, False), (2, True, False), (3, True, False), (3, False, False)])
+def test_delta_lights_match_oracle_per_pixel(kind, area, f32):
+    """Light::Point / Spot / Distant (light.rs:142-175; estimate_direct without MIS and without the BSDF half, integrator.rs:587-601) on
+    the wavefront, next to an area light, under Path / Direct{UniformOne, UniformAll} / Whitted, per pixel against the oracle.  RT_SHADE_F32
+    on a scene that holds a delta light is shaded by the f64 kernels (exact parity, not the f32 tolerance)."""
+    from rustraytracer_b200 import Camera
+    t = orc.delta_light_tables(area_light=area)
+    oracle = orc.OracleScene(t)
+    gpu = orc.upload_tables(t); gpu.commit()
+    w = h = 64
+    spp = 4
+    depth = 6
+    cam = Camera.new((0.5, 3.0, -8.0), (0.3, 0.8, 0.0), (0, 1, 0), 1.0, 42.0, 0.0, 10.0)
+    it = {0: IntType.Path(depth, shade_f32=f32), 1: IntType.Direct(depth, "UniformOne"), 2: IntType.Direct(depth, "UniformAll"), 3: IntType.Whitted(depth)}[kind]
+    film = Film(w, h)
+    render_samples(gpu, cam, it, film, w, h, 0, spp, seed=21)
+    g = film.read()
+    o, counts, _ = oracle.render(cam, w, h, 0, spp, seed=21, max_depth=depth, kind=kind)
+    film_compare(g, o, f"delta lights kind {kind} area {area} f32 {f32}")
+    assert o[..., :3].mean() > 0.01
+    c = gpu.counters()
+    assert c["paths"] == w * h * spp
+    for k, v in zip(("extend_rays", "shadow_rays", "probe_rays"), counts):
+        assert abs(c[k] - int(v)) <= 0.002 * int(v) + 8, (k, c[k], int(v))
+    if not area:
+        assert c["probe_rays"] == 0                      # delta lights only: estimate_direct never samples the BSDF

@@ -451,3 +451,72 @@ def test_perlin_texture_known_answers():
 
 def orc_pi():
     return 3.14159265358979          # consts.rs:31
+
+
+# ---------------------------------------------------------------- Light::Point / Spot / Distant (light.rs:142-175, 522-582)
+def test_delta_light_sample_li_closed_form():
+    t = orc.delta_light_tables()
+    s = orc.OracleScene(t)
+    p = np.array([0.5, 0.0, -2.0])
+    # Point: position = to_world x origin = (-2, 3, 1); wi = normalised (pos - p), pdf 1, colour / |pos - p|^2, p1 = pos
+    pos = np.array([-2.0, 3.0, 1.0])
+    r = s.light_sample_li(0, p, (0.3, 0.7))
+    d2 = float(((pos - p) ** 2).sum())
+    assert r["pdf"] == 1.0 and np.array_equal(r["p1"], pos)
+    assert np.allclose(r["wi"], (pos - p) / math.sqrt(d2), rtol=0, atol=1e-15)
+    assert np.allclose(r["color"], np.array([30, 24, 18]) / d2, rtol=1e-15)
+    # the sample does not depend on u
+    assert all(np.array_equal(r[k], s.light_sample_li(0, p, (0.9, 0.1))[k]) for k in ("wi", "color", "p1"))
+    # Spot at (1.5, 4, -1), axis (0, -cos .5, -sin .5); cosines are cos(x * 180 / PI) of the RADIAN arguments (light.rs:548-549)
+    spos = np.array([1.5, 4.0, -1.0]); axis = np.array([0.0, -math.cos(0.5), -math.sin(0.5)])
+    cw, cf = math.cos(0.009 * 180.0 * (1.0 / math.pi)), math.cos(0.004 * 180.0 * (1.0 / math.pi))
+    assert abs(cw - 0.8699) < 1e-3 and abs(cf - 0.9738) < 1e-3
+    seen = set()
+    for q in ([1.5, 0.0, -3.18], [1.5, 0.0, -1.2], [1.5, 0.0, 2.0], [3.0, 0.0, -4.5], [0.2, 1.2, -1.6]):
+        q = np.array(q)
+        r = s.light_sample_li(1, q, (0.5, 0.5))
+        w = (q - spos) / np.linalg.norm(q - spos)            # -wi, from the light to the point
+        ct = float(w @ axis)
+        fo = 0.0 if ct < cw else 1.0 if ct > cf else ((ct - cw) / (cf - cw)) ** 4
+        seen.add(0 if fo == 0.0 else 2 if fo == 1.0 else 1)
+        assert r["pdf"] == 1.0 and np.array_equal(r["p1"], spos)
+        assert np.allclose(r["color"], np.array([60, 80, 100]) * fo / float(((q - spos) ** 2).sum()), rtol=1e-9, atol=1e-15)
+    assert seen == {0, 1, 2}                                 # outside the cone, in the falloff band, inside the full-intensity cone
+    # Distant: wi = normalised dir, colour as given, p1 = p + dir * 2e10
+    dirv = np.array([0.3, 2.0, -0.4])
+    r = s.light_sample_li(2, p, (0.5, 0.5))
+    assert r["pdf"] == 1.0 and np.array_equal(r["color"], [0.8, 0.7, 0.5])
+    assert np.allclose(r["wi"], dirv / np.linalg.norm(dirv), rtol=0, atol=1e-15)
+    assert np.array_equal(r["p1"], p + dirv * 2e10)
+    # Light::pdf_li of a delta light is 0 (light.rs:281-283)
+    for li in (0, 1, 2):
+        assert s.light_pdf_li(li, p, (0.0, 1.0, 0.0)) == 0.0
+
+
+def test_point_and_distant_light_on_a_lambertian_floor():
+    """Direct / Whitted / Path under ONE delta light: a floor pixel is (R / PI) * I / d^2 * cos(theta), emission 0, no MIS and no
+    BSDF half for a delta light (integrator.rs:587-601).  Two behaviours of the reference that are restated as they are:
+    (1) a Point light only arrives where the shadow ray's closest hit is primitive 0, here the enclosing sphere
+    (Visibility::unoccluded compares prim_index with make_basic's 0, hittable.rs:37, 138) — with the floor and the sphere swapped in
+    the primitive list the same scene renders black;  (2) a Distant light never arrives: its shadow ray is 2e10 x dir long and the
+    origin is pushed SMALL x that, 2e7 units, far outside any scene, so nothing is hit and unoccluded() answers `infinite_light`."""
+    from rustraytracer_b200 import Camera
+    cam = Camera.new((0.0, 6.0, -0.001), (0.0, 0.0, 0.0), (0, 1, 0), 1.0, 2.0, 0.0, 10.0)
+    want = 0.5 / math.pi * np.array([30.0, 24.0, 18.0]) / 9.0        # light 3 above the floor, seen (almost) straight from above
+    for ltype in (N.LIGHT_POINT, N.LIGHT_DISTANT):
+        for swap in (False, True):
+            lig = np.zeros(1, dtype=N.light_dtype); lig["prim_index"] = N.RT_NONE
+            lig[0]["type"] = ltype; lig[0]["color"] = (30, 24, 18); lig[0]["param"] = (0.3, 2.0, -0.4); lig[0]["transform"] = 0
+            prims = [orc.prim(N.PRIM_SPHERE, [0, 0, 0, 30.0]), orc.prim(N.PRIM_XZ_RECT, [-8, -8, 8, 8, 0.0])]
+            if swap:
+                prims = prims[::-1]
+            s = orc.OracleScene(orc.simple_tables(prims, lights=lig, transforms=[[1, 0, 0, 0, 0, 1, 0, 3.0, 0, 0, 1, 0, 0, 0, 0, 1]]))
+            for kind in (0, 1, 2, 3):
+                o, counts, _ = s.render(cam, 8, 8, 0, 2, seed=3, max_depth=1 if kind == 0 else 2, kind=kind)
+                rgb = o[..., :3] / o[..., 3:4]
+                if swap or ltype == N.LIGHT_DISTANT:
+                    assert not rgb.any()
+                else:
+                    assert np.allclose(rgb, want[None, None, :], rtol=5e-3, atol=0), (kind, rgb[0, 0], want)
+                assert int(counts[2]) == 0                       # no MIS probe rays for a delta light
+                assert int(counts[1]) == 8 * 8 * 2               # one shadow ray per floor vertex
