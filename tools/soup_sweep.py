@@ -87,21 +87,26 @@ def main():
         del hits, h
         ms_c = timed(lambda: check(lib().rt_closest_device(gpu.h, n, C.c_void_p(rays.data_ptr()), 0.001, 1e308, C.c_void_p(prim.data_ptr()), C.c_void_p(t.data_ptr()), stream)))
         hit_c = float((prim != -1).float().mean())
+        # order-sensitive checksum of the closest-hit ids: equal between the host SAH tree and the device LBVH (and between 1 and N GPUs'
+        # slices summed) iff both trees return the same primitive for every ray — the size-independent parity property at full size
+        wgt = torch.arange(lo, hi, device=dev, dtype=torch.int64) % 65521 + 1
+        chk_c = int(((prim.to(torch.int64) + 1) * wgt).sum())
         ms_i = timed(lambda: check(lib().rt_closest_device(gpu.h, n, C.c_void_p(inc.data_ptr()), 0.001, 1e308, C.c_void_p(prim.data_ptr()), C.c_void_p(t.data_ptr()), stream)))
         hit_i = float((prim != -1).float().mean())
+        chk_i = int(((prim.to(torch.int64) + 1) * wgt).sum())
         if dist:
             tt = torch.tensor([ms_c, ms_i], device=dev, dtype=torch.float64); dist.all_reduce(tt, op=dist.ReduceOp.MAX); ms_c, ms_i = tt.tolist()
         b = gpu.device_bytes()
         bs = gpu.build_stats()
         row = {"tris": n_tris, "rays": n_all, "n_gpus": world, "coherent_Mrays_s": n_all / ms_c / 1e3, "incoherent_Mrays_s": n_all / ms_i / 1e3, "coherent_ms": ms_c, "incoherent_ms": ms_i,
-               "hit_rate_coherent": hit_c, "hit_rate_incoherent": hit_i, "bvh_nodes_MB": b["nodes"] / 1e6, "leaf_slots_MB": b["leaves"] / 1e6, "tables_MB": b["tables"] / 1e6,
+               "hit_rate_coherent": hit_c, "hit_rate_incoherent": hit_i, "id_checksum_coherent": chk_c, "id_checksum_incoherent": chk_i, "bvh_nodes_MB": b["nodes"] / 1e6, "leaf_slots_MB": b["leaves"] / 1e6, "tables_MB": b["tables"] / 1e6,
                "scene_gen_s": round(gen_s, 2), "build_upload_s": round(build_s, 2),
                "builder": "device LBVH" if bs["mode"] == 1 else "host binned SAH", "tree_build_ms": round(bs["build_ms"], 2), "commit_ms": round(bs["commit_ms"], 1),
                "bvh4_nodes": bs["nodes"], "max_stack": bs["max_stack"]}
         if rank == 0:
             print(json.dumps(row), flush=True)
         rows.append(row)
-        del gpu, hs, rays, inc, prim, t
+        del gpu, hs, rays, inc, prim, t, wgt
         torch.cuda.empty_cache()
     if rank == 0 and args.out:
         json.dump({"workload": "SURVEY 8d config 5: triangle soup, rt_closest_device, device-resident rays", "rows": rows}, open(args.out, "w"), indent=1)
