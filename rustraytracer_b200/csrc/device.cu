@@ -26,6 +26,64 @@ template <class T> static rt_status up(rt_scene& s, const std::vector<T>& h, con
     return RT_OK;
 }
 
+// The mesh tables (points, normals, uvs, indices of every mesh back to back; DMesh holds the element offsets): copied mesh by mesh
+// straight into one device allocation — no concatenated host copy (4.8 GB of it at 50 M triangles).
+template <class T, class F> static rt_status up_meshes(rt_scene& s, F field, const T*& dptr, uint64_t& bytes) {
+    dptr = nullptr;
+    size_t total = 0;
+    for (const HostMesh& m : s.meshes) total += field(m).size();
+    void* p = nullptr;
+    CK(cudaMalloc(&p, total ? total * sizeof(T) : 16));
+    s.allocations.push_back(p);
+    size_t off = 0;
+    for (const HostMesh& m : s.meshes) {
+        const std::vector<T>& v = field(m);
+        if (!v.empty()) CK(cudaMemcpy((T*)p + off, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+        off += v.size();
+    }
+    dptr = (const T*)p; bytes += total * sizeof(T);
+    return RT_OK;
+}
+
+// RT_BUILD_DEVICE_LBVH: the f64 box (scene_host.cpp:prim_box, triangle arm) and the 80-byte slot record (build_host_image:fill_slots)
+// of every triangle, computed from the uploaded tables instead of on the host — at 50 M triangles the host versions and their 6.4 GB
+// of uploads were most of the commit.  Same arithmetic (no FMA contraction in this library), so the records are the host's bit for bit.
+__global__ void __launch_bounds__(256) k_fill_tri_slots(uint32_t n, const DPrim* __restrict__ prims, const DMesh* __restrict__ meshes, const double* __restrict__ points,
+                                                        const double* __restrict__ uvs, const uint32_t* __restrict__ tri_index, Box64* __restrict__ boxes, DSlot* __restrict__ slots) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const DPrim p = prims[i];
+        if ((p.info & 7u) != RT_PRIM_TRIANGLE) continue;
+        const DMesh m = meshes[p.info >> 6];
+        const uint32_t id[3] = {tri_index[p.a], tri_index[p.a + 1], tri_index[p.a + 2]};
+        DSlot sl;
+        for (int v = 0; v < 3; v++) for (int k = 0; k < 3; k++) sl.v[3 * v + k] = points[3 * (m.p_base + id[v]) + k];
+        sl.prim = i; sl.kind = 0;
+        Box64 b;
+        for (int k = 0; k < 3; k++) { b.mn[k] = fmin(sl.v[k], fmin(sl.v[3 + k], sl.v[6 + k])); b.mx[k] = fmax(sl.v[k], fmax(sl.v[3 + k], sl.v[6 + k])); }
+        if (p.info & PI_HAS_UV) {
+            // hittable.rs:366-378: uv determinant below 1e-7 AND an exactly zero geometric normal: the triangle always returns None (kind 2)
+            const double* u0 = uvs + 2 * (m.uv_base + id[0]); const double* u1 = uvs + 2 * (m.uv_base + id[1]); const double* u2 = uvs + 2 * (m.uv_base + id[2]);
+            const double d02x = u0[0] - u2[0], d02y = u0[1] - u2[1], d12x = u1[0] - u2[0], d12y = u1[1] - u2[1];
+            const double determinant = d02x * d12y - d02y * d12x;
+            if (fabs(determinant) < SMALL / 10000.) {
+                const double a[3] = {sl.v[6] - sl.v[0], sl.v[7] - sl.v[1], sl.v[8] - sl.v[2]}, e[3] = {sl.v[3] - sl.v[0], sl.v[4] - sl.v[1], sl.v[5] - sl.v[2]};
+                const double c[3] = {a[1] * e[2] - a[2] * e[1], a[2] * e[0] - a[0] * e[2], a[0] * e[1] - a[1] * e[0]};
+                if (c[0] * c[0] + c[1] * c[1] + c[2] * c[2] == 0.) sl.kind = 2;
+            }
+        }
+        boxes[i] = b; slots[i] = sl;
+    }
+}
+// the non-triangle primitives' boxes come from the host (transforms, padding: scene_host.cpp:prim_box); their slot is {prim, kind 1}
+__global__ void k_scatter_other_slots(uint32_t n, const uint32_t* __restrict__ idx, const Box64* __restrict__ ob, Box64* __restrict__ boxes, DSlot* __restrict__ slots) {
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
+        const uint32_t i = idx[j];
+        DSlot sl; for (int k = 0; k < 9; k++) sl.v[k] = 0.;
+        sl.prim = i; sl.kind = 1;
+        boxes[i] = ob[j]; slots[i] = sl;
+    }
+}
+
 rt_status upload_scene(rt_scene& s, HostImage& img) {
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) { set_error("no CUDA device: librtcore has no CPU path"); return RT_ERR_CUDA; }
@@ -34,15 +92,32 @@ rt_status upload_scene(rt_scene& s, HostImage& img) {
     s.bytes_nodes = s.bytes_slots = s.bytes_tables = 0;
     rt_status st;
     uint32_t n_nodes = (uint32_t)img.nodes.size();
+    if ((st = up(s, img.prims, d.prims, b))) return st;
+    if ((st = up(s, img.meshes, d.meshes, b))) return st;
+    if ((st = up_meshes<double>(s, [](const HostMesh& m) -> const std::vector<double>& { return m.p; }, d.points, b))) return st;
+    if ((st = up_meshes<double>(s, [](const HostMesh& m) -> const std::vector<double>& { return m.n; }, d.normals, b))) return st;
+    if ((st = up_meshes<double>(s, [](const HostMesh& m) -> const std::vector<double>& { return m.uv; }, d.uvs, b))) return st;
+    if ((st = up_meshes<uint32_t>(s, [](const HostMesh& m) -> const std::vector<uint32_t>& { return m.ind; }, d.tri_index, b))) return st;
     if (img.device_build) {
 #if RT_BVH_WIDTH == 4
         // RT_BUILD_DEVICE_LBVH: boxes and primitive-ordered slots go up as temporaries, the tree is built where it will be walked
         void *tb = nullptr, *ts = nullptr;
-        const uint32_t n = (uint32_t)img.slots.size();
+        const uint32_t n = (uint32_t)img.n_slots;
         CK(cudaMalloc(&tb, (size_t)n * sizeof(Box64)));
         if (cudaMalloc(&ts, (size_t)n * sizeof(DSlot)) != cudaSuccess) { cudaFree(tb); set_error("upload: out of device memory"); return RT_ERR_CUDA; }
-        cudaMemcpy(tb, img.boxes.data(), (size_t)n * sizeof(Box64), cudaMemcpyHostToDevice);
-        cudaMemcpy(ts, img.slots.data(), (size_t)n * sizeof(DSlot), cudaMemcpyHostToDevice);
+        k_fill_tri_slots<<<148 * 8, 256>>>(n, d.prims, d.meshes, d.points, d.uvs, d.tri_index, (Box64*)tb, (DSlot*)ts);
+        if (!img.other_idx.empty()) {
+            const uint32_t no = (uint32_t)img.other_idx.size();
+            void *oi = nullptr, *ob = nullptr;
+            if (cudaMalloc(&oi, (size_t)no * sizeof(uint32_t)) != cudaSuccess || cudaMalloc(&ob, (size_t)no * sizeof(Box64)) != cudaSuccess) {
+                cudaFree(oi); cudaFree(tb); cudaFree(ts); set_error("upload: out of device memory"); return RT_ERR_CUDA;
+            }
+            cudaMemcpy(oi, img.other_idx.data(), (size_t)no * sizeof(uint32_t), cudaMemcpyHostToDevice);
+            cudaMemcpy(ob, img.other_boxes.data(), (size_t)no * sizeof(Box64), cudaMemcpyHostToDevice);
+            k_scatter_other_slots<<<(no + 255) / 256, 256>>>(no, (const uint32_t*)oi, (const Box64*)ob, (Box64*)tb, (DSlot*)ts);
+            cudaDeviceSynchronize(); cudaFree(oi); cudaFree(ob);
+        }
+        if (cudaDeviceSynchronize() != cudaSuccess || cudaGetLastError() != cudaSuccess) { cudaFree(tb); cudaFree(ts); set_error("upload: slot kernels failed"); return RT_ERR_CUDA; }
         DNode4* nodes = nullptr; DSlot* slots = nullptr; float ms = 0.f;
         st = build_bvh_device((const Box64*)tb, (const DSlot*)ts, n, &nodes, &n_nodes, &slots, &img.max_stack, &ms);
         cudaFree(tb); cudaFree(ts);
@@ -58,12 +133,6 @@ rt_status upload_scene(rt_scene& s, HostImage& img) {
         if ((st = up(s, img.nodes, d.nodes, s.bytes_nodes))) return st;
         if ((st = up(s, img.slots, d.slots, s.bytes_slots))) return st;
     }
-    if ((st = up(s, img.prims, d.prims, b))) return st;
-    if ((st = up(s, img.meshes, d.meshes, b))) return st;
-    if ((st = up(s, img.points, d.points, b))) return st;
-    if ((st = up(s, img.normals, d.normals, b))) return st;
-    if ((st = up(s, img.uvs, d.uvs, b))) return st;
-    if ((st = up(s, img.tri_index, d.tri_index, b))) return st;
     if ((st = up(s, img.shapes, d.shapes, b))) return st;
     if ((st = up(s, s.xforms, d.xforms, b))) return st;
     if ((st = up(s, s.textures, d.textures, b))) return st;
@@ -90,7 +159,7 @@ rt_status upload_scene(rt_scene& s, HostImage& img) {
     s.bytes_tables = b;
     { void* cp = nullptr; CK(cudaMalloc(&cp, 16)); s.allocations.push_back(cp); s.d_counter = (uint32_t*)cp; }   // work counter of the persistent batch kernels
     d.n_nodes = n_nodes; d.n_prims = (uint32_t)img.prims.size();
-    d.n_lights = (uint32_t)img.lights.size(); d.n_slots = (uint32_t)img.slots.size();
+    d.n_lights = (uint32_t)img.lights.size(); d.n_slots = (uint32_t)img.n_slots;
     s.d = d;
     return RT_OK;
 }

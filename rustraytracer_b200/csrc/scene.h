@@ -40,14 +40,16 @@ bool invert4(const double m[16], double out[16]);
 // what commit hands to the device uploader (device.cu)
 struct HostImage {
     std::vector<DNodeT> nodes; std::vector<DSlot> slots; std::vector<DPrim> prims; std::vector<DMesh> meshes;
-    std::vector<double> points, normals, uvs, shapes; std::vector<uint32_t> tri_index;
+    std::vector<double> shapes;              // points / normals / uvs / indices are uploaded from rt_scene::meshes directly
     std::vector<DLight> lights;
     // Infinite lights: flat Distribution2D tables, concatenated; DLight pointers hold OFFSETS (in doubles) until upload
     std::vector<double> dist;
     std::vector<double> mat_alpha;           // 2 per material, NaN = not constant
-    // RT_BUILD_DEVICE_LBVH: `nodes` is empty, `slots` is in PRIMITIVE order and `boxes` holds the f64 primitive boxes; the uploader
-    // builds the tree on the device (bvh_device.cu) and permutes the slots into leaf order there
-    bool device_build = false; std::vector<Box64> boxes;
+    // RT_BUILD_DEVICE_LBVH: `nodes` and `slots` are empty.  The uploader computes the f64 boxes and the slot records of the triangles on
+    // the device from the uploaded tables (device.cu:k_fill_tri_slots), scatters the few non-triangle ones prepared here (`other_*`,
+    // slot kind 1), builds the tree where it will be walked (bvh_device.cu) and permutes the slots into leaf order there
+    bool device_build = false; std::vector<uint32_t> other_idx; std::vector<Box64> other_boxes;
+    size_t n_slots = 0;
     int max_stack = 0; double build_ms = 0.;
 };
 // bvh_device.cu

@@ -6,6 +6,7 @@
 #include <cstdlib>
 #include <string>
 #include <cstring>
+#include <mutex>
 #include <thread>
 #include "scene.h"
 
@@ -187,7 +188,7 @@ rt_status build_host_image(const rt_scene& s, HostImage& img, bool device_build)
     for (auto& t : s.textures) if (t.type == RT_TEX_CHECKERED && (t.odd >= s.textures.size() || t.even >= s.textures.size())) { set_error("checkered texture: id out of range"); return RT_ERR_INVALID; }
     for (auto& l : s.lights) if (l.type == RT_LIGHT_DIFFUSE && l.prim_index >= n) { set_error("light: prim_index out of range"); return RT_ERR_INVALID; }
     for (auto& t : s.textures) if ((t.type == RT_TEX_HDR || t.type == RT_TEX_IMAGE) && t.image >= s.images.size()) { set_error("texture: image index out of range"); return RT_ERR_INVALID; }
-    // meshes → concatenated f64 arrays
+    // meshes → element offsets into the concatenated f64 / index arrays
     img.meshes.resize(s.meshes.size());
     std::vector<uint64_t> idx_base(s.meshes.size());
     uint64_t pb = 0, nb = 0, ub = 0, ib = 0;
@@ -196,17 +197,14 @@ rt_status build_host_image(const rt_scene& s, HostImage& img, bool device_build)
         idx_base[m] = ib;
         pb += s.meshes[m].p.size() / 3; nb += s.meshes[m].n.size() / 3; ub += s.meshes[m].uv.size() / 2; ib += s.meshes[m].ind.size();
     }
-    img.points.reserve(pb * 3); img.normals.reserve(nb * 3); img.uvs.reserve(ub * 2); img.tri_index.reserve(ib);
-    for (auto& m : s.meshes) {
-        img.points.insert(img.points.end(), m.p.begin(), m.p.end());
-        img.normals.insert(img.normals.end(), m.n.begin(), m.n.end());
-        img.uvs.insert(img.uvs.end(), m.uv.begin(), m.uv.end());
-        img.tri_index.insert(img.tri_index.end(), m.ind.begin(), m.ind.end());
-    }
+    // the arrays themselves go to the device mesh by mesh (device.cu:up_meshes)
     // per-primitive records and boxes
     img.shapes = s.shapes;
     img.prims.resize(n);
-    std::vector<Box64> boxes(n);
+    img.device_build = device_build && n >= 8;
+    img.n_slots = n;
+    std::vector<Box64> boxes(img.device_build ? 0 : n);
+    std::mutex other_mu;
     int threads = (int)std::max(1u, std::thread::hardware_concurrency());
     {
         std::vector<std::thread> pool; size_t chunk = (n + threads - 1) / std::max(threads, 1);
@@ -223,19 +221,18 @@ rt_status build_host_image(const rt_scene& s, HostImage& img, bool device_build)
                     d.a = (uint32_t)(idx_base[p.mesh] + p.ind);
                 } else d.a = p.shape;
                 img.prims[i] = d;
-                boxes[i] = prim_box(s, p);
-                if (p.type != RT_PRIM_TRIANGLE) for (int k = 0; k < 3; k++) { img.shapes[p.shape + 6 + k] = boxes[i].mn[k]; img.shapes[p.shape + 9 + k] = boxes[i].mx[k]; }
+                if (img.device_build && p.type == RT_PRIM_TRIANGLE) continue;      // box and slot record: device.cu:k_fill_tri_slots
+                const Box64 bx = prim_box(s, p);
+                if (!img.device_build) boxes[i] = bx;
+                else { std::lock_guard<std::mutex> g(other_mu); img.other_idx.push_back((uint32_t)i); img.other_boxes.push_back(bx); }
+                if (p.type != RT_PRIM_TRIANGLE) for (int k = 0; k < 3; k++) { img.shapes[p.shape + 6 + k] = bx.mn[k]; img.shapes[p.shape + 9 + k] = bx.mx[k]; }
             }
         });
         for (auto& th : pool) th.join();
     }
     if (ib >= (1ull << 32)) { set_error("index buffer exceeds 2^32 entries"); return RT_ERR_INVALID; }
     BuiltBvh bvh;
-    img.device_build = device_build && n >= 8;
-    if (img.device_build) {
-        bvh.order.resize(n);
-        for (size_t i = 0; i < n; i++) bvh.order[i] = (uint32_t)i;      // slots stay in primitive order; the device build permutes them
-    } else {
+    if (!img.device_build) {
         auto t0 = std::chrono::steady_clock::now();
         build_bvh(boxes, bvh, threads);
         img.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
@@ -244,7 +241,7 @@ rt_status build_host_image(const rt_scene& s, HostImage& img, bool device_build)
         if (getenv("RT_TRACE_BUILD")) fprintf(stderr, "bvh: %zu nodes of %zu bytes, %zu slots, worst-case stack %d\n", bvh.nodes.size(), sizeof(DNodeT), n, bvh.max_stack);
         img.nodes = std::move(bvh.nodes);
     }
-    img.slots.resize(n);
+    img.slots.resize(img.device_build ? 0 : n);
     auto fill_slots = [&](size_t sb, size_t se) {
     for (size_t sidx = sb; sidx < se; sidx++) {
         uint32_t pi = bvh.order[sidx];
@@ -271,12 +268,11 @@ rt_status build_host_image(const rt_scene& s, HostImage& img, bool device_build)
         img.slots[sidx] = sl;
     }
     };
-    {
+    if (!img.device_build) {
         std::vector<std::thread> pool; size_t chunk = (n + threads - 1) / std::max(threads, 1);
         for (int t = 0; t < threads; t++) { size_t b = std::min(n, t * chunk), e = std::min(n, b + chunk); if (e > b) pool.emplace_back(fill_slots, b, e); }
         for (auto& th : pool) th.join();
     }
-    if (img.device_build) img.boxes = std::move(boxes);
     // per-material microfacet alphas that do not depend on the hit point (material.rs:110-117,170-173,205-214)
     auto remap_alpha = [](double roughness) {          // trowbridge_reitz_roughness_to_alpha (microfacet.rs:442-446)
         roughness = std::fmax(roughness, 1e-5);

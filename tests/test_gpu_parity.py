@@ -658,3 +658,28 @@ def test_delta_lights_match_oracle_per_pixel(kind, area, f32):
         assert abs(c[k] - int(v)) <= 0.002 * int(v) + 8, (k, c[k], int(v))
     if not area:
         assert c["probe_rays"] == 0                      # delta lights only: estimate_direct never samples the BSDF
+
+
+def test_device_slot_records_degenerate_uv_and_mixed_primitives():
+    """RT_BUILD_DEVICE_LBVH computes the triangles' boxes and slot records on the device (device.cu:k_fill_tri_slots): a mesh whose uv
+    determinant vanishes everywhere (hittable.rs:366-378: such a triangle is hit only if its geometric normal is not exactly zero), one
+    exactly collinear triangle among them, next to a sphere and a transformed rect — same hits as the host-built tree and the oracle."""
+    rng = np.random.default_rng(5)
+    nt = 40
+    p = rng.uniform(-1, 1, (nt * 3, 3)).round(3)
+    p[0:3] = [[0, 0, 0], [0.5, 0, 0], [1.0, 0, 0]]                       # collinear: (p2-p0)x(p1-p0) is exactly zero
+    uv = np.full((nt * 3, 2), 0.25)                                      # determinant 0 for every triangle
+    uv[30:] = rng.uniform(0, 1, (nt * 3 - 30, 2))                        # ... except the last thirty
+    ind = np.arange(nt * 3, dtype=np.uint32)
+    rot = [0.8, -0.6, 0, 0.1, 0.6, 0.8, 0, 0.2, 0, 0, 1, 0, 0, 0, 0, 1]
+    prims = [orc.prim(N.PRIM_TRIANGLE, [], mesh=0, ind=3 * k) for k in range(nt)]
+    prims += [orc.prim(N.PRIM_SPHERE, [0.3, 0.2, 1.5, 0.4]), orc.prim(N.PRIM_XY_RECT, [-0.5, -0.5, 0.5, 0.5, -1.5], xf=0)]
+    t = orc.simple_tables(prims, meshes=[(p, np.zeros((0, 3)), uv, ind)], transforms=[rot])
+    a = orc.upload_tables(t); a.set_build_mode("sah"); a.commit()
+    b = orc.upload_tables(t); b.set_build_mode("lbvh"); b.commit()
+    assert b.build_stats()["mode"] == N.BUILD_DEVICE_LBVH
+    rays = random_rays(rng, 40000, -2.0, 2.0)
+    ha, hb = get_intersection(a, rays), get_intersection(b, rays)
+    assert ha.tobytes() == hb.tobytes()
+    assert (hb["prim_index"] != NONE).mean() > 0.1 and not (hb["prim_index"] == 0).any() and (hb["prim_index"] == 3).any()
+    compare_hits(hb, orc.OracleScene(t).intersect(rays, mode=0), None, "degenerate uv, mixed prims")
