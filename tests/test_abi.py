@@ -245,6 +245,14 @@ def test_image_and_infinite_light_validation():
     lig = np.zeros(1, dtype=N.light_dtype); lig[0]["type"] = 7
     with pytest.raises(N.RtError):
         o.set_lights(lig)
+    # rt_light is 72 bytes (type .. _pad, param[3]); Point / Spot / Distant are accepted, the first type past Distant is not
+    assert N.light_dtype.itemsize == 72 and N.light_dtype.fields["param"][1] == 48
+    for ltype in (N.LIGHT_POINT, N.LIGHT_SPOT, N.LIGHT_DISTANT):
+        lig[0]["type"] = ltype; lig[0]["transform"] = N.RT_NONE
+        o.set_lights(lig)
+    lig[0]["type"] = N.LIGHT_DISTANT + 1
+    with pytest.raises(N.RtError):
+        o.set_lights(lig)
     # an Infinite light over a Checkered texture has a (0, 0) table in the reference (Texture::get_size) — refused at commit
     tex = np.zeros(3, dtype=N.texture_dtype); tex[0]["type"] = N.TEX_CHECKERED; tex[0]["odd"] = 1; tex[0]["even"] = 2
     o.set_textures(tex)
