@@ -96,6 +96,10 @@ def main():
         chk_i = int(((prim.to(torch.int64) + 1) * wgt).sum())
         if dist:
             tt = torch.tensor([ms_c, ms_i], device=dev, dtype=torch.float64); dist.all_reduce(tt, op=dist.ReduceOp.MAX); ms_c, ms_i = tt.tolist()
+            # whole-batch checksum / hit rates: the ranks' slices summed (the coherent checksum then equals the 1-GPU one; the incoherent batch
+            # is drawn per rank, so its checksum is only comparable at equal N)
+            ck = torch.tensor([chk_c, chk_i], device=dev, dtype=torch.int64); dist.all_reduce(ck, op=dist.ReduceOp.SUM); chk_c, chk_i = [int(x) for x in ck.tolist()]
+            hr = torch.tensor([hit_c * n, hit_i * n], device=dev, dtype=torch.float64); dist.all_reduce(hr, op=dist.ReduceOp.SUM); hit_c, hit_i = [x / n_all for x in hr.tolist()]
         b = gpu.device_bytes()
         bs = gpu.build_stats()
         row = {"tris": n_tris, "rays": n_all, "n_gpus": world, "coherent_Mrays_s": n_all / ms_c / 1e3, "incoherent_Mrays_s": n_all / ms_i / 1e3, "coherent_ms": ms_c, "incoherent_ms": ms_i,
