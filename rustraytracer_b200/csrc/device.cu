@@ -50,7 +50,8 @@ template <class T, class F> static rt_status up_meshes(rt_scene& s, F field, con
 // of uploads were most of the commit.  Same arithmetic (no FMA contraction in this library), so the records are the host's bit for bit.
 __global__ void __launch_bounds__(256) k_fill_tri_slots(uint32_t n, const DPrim* __restrict__ prims, const DMesh* __restrict__ meshes, const double* __restrict__ points,
                                                         const double* __restrict__ uvs, const uint32_t* __restrict__ tri_index, Box64* __restrict__ boxes, DSlot* __restrict__ slots) {
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    for (uint64_t i64 = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i64 < n; i64 += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t i = (uint32_t)i64;
         const DPrim p = prims[i];
         if ((p.info & 7u) != RT_PRIM_TRIANGLE) continue;
         const DMesh m = meshes[p.info >> 6];
