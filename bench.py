@@ -122,7 +122,7 @@ def main():
     ap.add_argument("--spp", type=int, default=256)
     ap.add_argument("--size", type=int, default=1024)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--wavefront", type=int, default=1 << 25, help="paths in flight per GPU")
+    ap.add_argument("--wavefront", type=int, default=0, help="paths in flight per GPU; 0 = 128 Mi when the GPU has 100 GB free (64 GB of queue state), else 32 Mi")
     ap.add_argument("--shade", default="f32", choices=["f32", "f64"], help="radiometric precision of the shade kernel (geometry is f64-exact in both)")
     args = ap.parse_args()
     rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
@@ -145,7 +145,11 @@ def main():
     t0 = time.time()
     objects = hs.upload()                                 # BVH build + flatten + H2D (outside the timed region: scene build is not the hot path)
     build_s = time.time() - t0
-    objects.set_wavefront_size(args.wavefront)          # paths in flight; ~480 B of queue state each (16 GB at 32 Mi)
+    if args.wavefront <= 0:
+        # measured r01 (profiles/bench_r01_wavefront.json): 32 Mi 2,642, 64 Mi 2,683, 128 Mi 2,710 Mrays/s — fewer, larger launches;
+        # the queue state is laid out for the 180 GB of a B200
+        args.wavefront = 1 << 27 if torch.cuda.mem_get_info(local)[0] > 100e9 else 1 << 25
+    objects.set_wavefront_size(args.wavefront)          # paths in flight; ~480 B of queue state each (64 GB at 128 Mi)
     cam = hs.camera()
     integ = IntType.Path(DEPTH, shade_f32=(args.shade == "f32"))
     film_t = torch.zeros(H * W * 4, dtype=torch.float64, device=f"cuda:{local}")      # torch owns the film so NCCL can reduce it in place
