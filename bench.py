@@ -35,12 +35,52 @@ def load_peaks():
     return 6650.0, "fallback"
 
 
-def algorithmic_bytes_per_ray():
-    """bytes = 32 (ray) + 16 (hit) + N_box*32 + N_tri*48 with N_box / N_tri counted by the ORACLE's
-    ordered reference traversal on this workload's extend rays; measured once offline (tools/measure_work.py) and
-    committed — bench.py never calls the oracle for this."""
-    w = json.load(open(os.path.join(ROOT, "profiles", "algorithmic_work_r01.json")))[f"{SCENE}_v{VARIANT}"]
-    return 32 + 16 + w["n_box"] * 32 + w["n_tri"] * 48, w
+def load_json(name):
+    p = os.path.join(ROOT, "profiles", name)
+    return json.load(open(p)) if os.path.exists(p) else None
+
+
+def extend_rooflines(tot, launches, clk, sms=148):
+    """Rooflines of the dominant kernel, k_extend (closest-hit traversal).  Per-ray constants of the kernel (bytes its loads request, DRAM
+    bytes, warp / thread instructions) come from ONE committed ncu capture of this build (profiles/extend_work_r02.json, made by
+    tools/extend_work.py from `ncu --set full`); rays and kernel time are measured live (device counters + CUDA events on the render stream).
+    Denominators: measured L2 bandwidth and issue rate from tools/peaks.cu (profiles/peaks_r02.json), measured HBM copy bandwidth from
+    MEASURED_PEAKS.json.  The SURVEY §8d figure (bytes on the REFERENCE's median-split tree) is kept as `work_vs_reference_tree`: it says how
+    much less the kernel moves than the reference's traversal would, it is not a fraction of any peak."""
+    hbm_peak, peak_kind = load_peaks()
+    work = load_json("extend_work_r02.json") or {}
+    peaks = load_json("peaks_r02.json") or {}
+    rays, ms = tot["extend_rays"], tot["extend_ms"]
+    rays_per_s = rays / (ms * 1e-3) if ms > 0 else 0.0
+    per_launch = rays / max(launches, 1)
+    out = {"kernel": "k_extend (closest-hit BVH4 traversal, persistent)", "rays_per_launch": per_launch, "ms_per_launch": ms / max(launches, 1), "extend_Mrays_per_s": rays_per_s / 1e6,
+           "per_ray_constants": "profiles/extend_work_r02.json" if work else None}
+    l2_peak = (peaks.get("gather128_gbs") or {}).get("64MB")
+    ld_bytes = work.get("load_bytes_per_ray")
+    # headline roofline object: the kernel's own load bytes against the measured L2 bandwidth for its access pattern (independent 128-byte node reads)
+    out.update({"bound": "l2", "unit": "GB/s", "achieved": ld_bytes * rays_per_s / 1e9 if ld_bytes else None, "peak": l2_peak,
+                "peak_kind": "measured: tools/peaks.cu gather128 (independent random 128-byte records per lane, 64 MB footprint), profiles/peaks_r02.json",
+                "traffic": work.get("dram_bytes_per_ray") * per_launch if work.get("dram_bytes_per_ray") else None})
+    out["frac"] = out["achieved"] / l2_peak if out["achieved"] and l2_peak else None
+    if work.get("dram_bytes_per_ray"):
+        a = work["dram_bytes_per_ray"] * rays_per_s / 1e9
+        out["hbm"] = {"achieved": a, "peak": hbm_peak, "unit": "GB/s", "frac": a / hbm_peak, "peak_kind": f"{peak_kind} HBM copy bandwidth (MEASURED_PEAKS.json)",
+                      "dram_bytes_per_ray": work["dram_bytes_per_ray"]}
+    if work.get("warp_inst_per_ray"):
+        mhz = (clk or {}).get("sm_mhz") or (clk or {}).get("sm_max_mhz") or 1965
+        peak_issue = sms * 4 * mhz * 1e6
+        a = work["warp_inst_per_ray"] * rays_per_s
+        lanes = work.get("lanes_per_inst")
+        out["issue"] = {"achieved_warp_inst_per_s": a, "peak_warp_inst_per_s": peak_issue, "frac": a / peak_issue, "lanes_per_inst": lanes,
+                        "useful_lane_issue_frac": a / peak_issue * lanes / 32 if lanes else None,
+                        "peak_kind": f"{sms} SMs x 4 schedulers x {mhz} MHz (SM clock sampled during the timed region); measured FFMA-only rate: profiles/peaks_r02.json fp32_warp_inst_per_s"}
+    alg = load_json("algorithmic_work_r01.json")
+    if alg and f"{SCENE}_v{VARIANT}" in alg:
+        w = alg[f"{SCENE}_v{VARIANT}"]
+        bpr = 32 + 16 + w["n_box"] * 32 + w["n_tri"] * 48
+        out["work_vs_reference_tree"] = {"algorithmic_bytes_per_ray": bpr, "n_box": w["n_box"], "n_tri": w["n_tri"], "GB_per_s_equivalent": bpr * rays_per_s / 1e9,
+                                         "note": "SURVEY 8d bytes counted by the oracle's ordered traversal of the REFERENCE's median-split 1-prim-per-leaf tree; not a fraction of a peak"}
+    return out
 
 
 class ClockSampler:
@@ -101,7 +141,8 @@ def run_reference(args, rank, world):
         if step >= args.warmup:
             rays += s_rays; secs += s_secs; paths += s_paths
     v = rays / secs / 1e6
-    sample = f"every {stride}th pixel of the {args.size}^2 image x 1 spp per step ({paths // args.steps} paths/step), max_depth {DEPTH}"
+    sample = (f"every {stride}rd pixel of the {args.size}^2 image, {smp / (args.warmup + args.steps):.0f} one-sample passes per step on average "
+              f"({paths // max(args.steps, 1)} paths/step, ~{TARGET_S:.0f} s of {cores}-thread CPU work), max_depth {DEPTH}")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -123,6 +164,8 @@ def main():
     ap.add_argument("--size", type=int, default=1024)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--wavefront", type=int, default=0, help="paths in flight per GPU; 0 = 128 Mi when the GPU has 100 GB free (64 GB of queue state), else 32 Mi")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"], help="weak: --spp samples per GPU per step; strong: --spp samples per step in total, split over the GPUs")
+    ap.add_argument("--no-f64-leg", action="store_true")
     ap.add_argument("--shade", default="f32", choices=["f32", "f64"], help="radiometric precision of the shade kernel (geometry is f64-exact in both)")
     args = ap.parse_args()
     rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
@@ -162,12 +205,17 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
-    def step(i, e2e):
-        """One pass of the hot path on this rank's sample range of global sample space [0, world*spp)."""
+    strong = args.scaling == "strong"
+    spp_rank = spp // world if strong else spp            # strong: `spp` samples in TOTAL per step, split over the ranks; weak: `spp` per GPU
+    if strong and spp % world:
+        raise SystemExit(f"--scaling strong needs spp ({spp}) divisible by the number of GPUs ({world})")
+
+    def step(i, e2e, integ):
+        """One pass of the hot path on this rank's sample range of the step's global sample space."""
         film_t.zero_()
         torch.cuda.synchronize()
-        base = (i * world + rank) * spp
-        render_samples(objects, cam, integ, film, W, H, base, base + spp, seed=1234)    # blocking; H2D = camera + descriptors
+        base = (i * world + rank) * spp_rank
+        render_samples(objects, cam, integ, film, W, H, base, base + spp_rank, seed=1234)    # blocking; H2D = camera + descriptors
         c = objects.counters()
         if dist:
             dist.all_reduce(film_t)                       # NCCL sum of the (r,g,b,n) accumulation buffers over NVLink
@@ -176,86 +224,81 @@ def main():
         torch.cuda.synchronize()
         return c
 
-    for i in range(args.warmup):
-        step(i, False)
-    # ---- timed region 1: device-resident (value)
-    clocks = ClockSampler(local) if rank == 0 else None
-    barrier()
-    t_start = time.perf_counter()
-    tot = {k: 0.0 for k in ("extend_rays", "shadow_rays", "probe_rays", "paths", "iterations", "render_ms", "extend_ms", "shade_ms", "connect_ms")}
-    for i in range(args.steps):
-        c = step(args.warmup + i, False)
-        for k in tot:
-            tot[k] += c[k]
-    barrier()
-    wall = time.perf_counter() - t_start
-    clk = clocks.stop() if clocks else None
-    # ---- timed region 2: end to end through the public call with the host read-back (e2e)
-    barrier()
-    t_start = time.perf_counter()
-    for i in range(args.steps):
-        step(args.warmup + args.steps + i, True)
-    barrier()
-    wall_e2e = time.perf_counter() - t_start
+    KEYS = ("extend_rays", "shadow_rays", "probe_rays", "paths", "iterations", "render_ms", "extend_ms", "shade_ms", "connect_ms")
 
-    rays = tot["extend_rays"] + tot["shadow_rays"] + tot["probe_rays"]
-    stats = torch.tensor([rays, tot["paths"], wall, wall_e2e, tot["render_ms"]], dtype=torch.float64, device=f"cuda:{local}")
-    if dist:
-        s_sum = stats.clone(); dist.all_reduce(s_sum)
-        s_max = stats.clone(); dist.all_reduce(s_max, op=dist.ReduceOp.MAX)
-        rays_all, paths_all = s_sum[0].item(), s_sum[1].item()
-        wall, wall_e2e, dev_ms = s_max[2].item(), s_max[3].item(), s_max[4].item()
-    else:
-        rays_all, paths_all, dev_ms = rays, tot["paths"], tot["render_ms"]
+    def leg(integ, first_step, e2e, sample_clocks=False):
+        """W warm-up steps, then K timed steps bracketed by barrier + synchronize; returns (totals, wall seconds, clocks)."""
+        for i in range(args.warmup):
+            step(first_step + i, e2e, integ)
+        clocks = ClockSampler(local) if (sample_clocks and rank == 0) else None
+        barrier()
+        t_start = time.perf_counter()
+        tot = {k: 0.0 for k in KEYS}
+        for i in range(args.steps):
+            c = step(first_step + args.warmup + i, e2e, integ)
+            for k in tot:
+                tot[k] += c[k]
+        barrier()
+        wall = time.perf_counter() - t_start
+        return tot, wall, (clocks.stop() if clocks else None)
+
+    def reduce_leg(tot, wall):
+        """whole-job rays / paths (sum over ranks) and the MAX over ranks of the wall and device times"""
+        rays = tot["extend_rays"] + tot["shadow_rays"] + tot["probe_rays"]
+        st = torch.tensor([rays, tot["paths"], wall, tot["render_ms"]], dtype=torch.float64, device=f"cuda:{local}")
+        if dist:
+            s_sum = st.clone(); dist.all_reduce(s_sum)
+            s_max = st.clone(); dist.all_reduce(s_max, op=dist.ReduceOp.MAX)
+            return s_sum[0].item(), s_sum[1].item(), s_max[2].item(), s_max[3].item()
+        return rays, tot["paths"], wall, tot["render_ms"]
+
+    n_leg = args.warmup + args.steps
+    # ---- leg 1: device-resident (value) ; leg 2: the same through the public call with the host read-back every step (e2e)
+    tot, wall, clk = leg(integ, 0, False, sample_clocks=True)
+    _, wall_e2e, _ = leg(integ, n_leg, True)
+    rays_all, paths_all, wall, dev_ms = reduce_leg(tot, wall)
+    _, _, wall_e2e, _ = reduce_leg(tot, wall_e2e)
+    # ---- leg 3 (f32 headline only): the same workload with the shade kernels in the reference's own f64 arithmetic (per-pixel parity mode),
+    # warmed and timed exactly like leg 1 — r01's single un-warmed f64 render measured CUDA's lazy loading of the k_shade<double> kernels
+    f64 = None
+    if args.shade == "f32" and not args.no_f64_leg:
+        integ64 = IntType.Path(DEPTH, shade_f32=False)
+        tot64, wall64, _ = leg(integ64, 2 * n_leg, False)
+        r64, p64, wall64, dev64 = reduce_leg(tot64, wall64)
+        f64 = {"value": r64 / wall64 / 1e6, "unit": UNIT, "samples_per_s": p64 / wall64, "ms_per_step": 1e3 * wall64 / args.steps, "device_ms_per_step": dev64 / args.steps,
+               "steps": args.steps, "warmup": args.warmup, "dtype": "f64 (geometry and radiometry: the reference's arithmetic; films match the oracle per pixel)",
+               "kernel_ms_per_step": {"extend": tot64["extend_ms"] / args.steps, "shade+generate": tot64["shade_ms"] / args.steps, "connect": tot64["connect_ms"] / args.steps}}
     if rank != 0:
         if dist:
             dist.destroy_process_group()
         return
     value = rays_all / wall / 1e6
     e2e = rays_all / wall_e2e / 1e6
-    peak, peak_kind = load_peaks()
-    bpr, work = algorithmic_bytes_per_ray()
     launches = int(tot["iterations"])                      # one k_extend launch per wavefront iteration
-    ext_ms_per_launch = tot["extend_ms"] / max(launches, 1)
-    achieved = bpr * tot["extend_rays"] / (tot["extend_ms"] * 1e-3) / 1e9 if tot["extend_ms"] > 0 else 0.0
-    traffic = None
-    tp = os.path.join(ROOT, "profiles", "extend_traffic_r01.json")
-    if os.path.exists(tp):
-        # ncu dram__bytes_read.sum + dram__bytes_write.sum of one captured k_extend launch, per ray of that launch, scaled to the
-        # average launch of this run (per launch, like `achieved`)
-        traffic = json.load(open(tp)).get("dram_bytes_per_ray", 0.0) * tot["extend_rays"] / max(launches, 1) or None
+    tb = hs.tables()                                      # shading bins present = distinct (material type, triangle / parametric shape) pairs
+    n_bins = len({(int(tb["materials"]["type"][m]), int(t == N.PRIM_TRIANGLE)) for m, t in set(zip(tb["prims"]["mat_index"].tolist(), tb["prims"]["type"].tolist()))})
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": 1e3 * wall / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": 1e3 * wall / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
         "dtype": "f64 geometry (intersection, hit points, rays) + f32 radiometry" if args.shade == "f32" else "f64", "data": "synthetic",
-        "config": {"workload": f"{SCENE} rough-plastic (stand-in dragon mesh, 871,414 tris; dragon.obj is a missing blob) {W}x{H}, max_depth {DEPTH}, {spp} spp per GPU per step",
+        "config": {"workload": f"{SCENE} rough-plastic (stand-in dragon mesh, 871,414 tris; dragon.obj is a missing blob) {W}x{H}, max_depth {DEPTH}, "
+                               + (f"{spp} spp per step in total = {spp_rank} per GPU" if strong else f"{spp} spp per GPU per step"),
                    "parallelism": f"scene replicated, sample-range partition x{world}, NCCL all-reduce of the film" if world > 1 else "single GPU",
-                   "l2": "no explicit flush: every wavefront iteration streams several GB of path/queue state (>> 126 MB L2); the BVH (33 MB nodes + 70 MB leaf slots) is meant to stay L2-resident",
-                   "wavefront_paths": args.wavefront, "bvh_build_s": round(build_s, 2)},
+                   "l2": "no explicit flush: every wavefront iteration streams several GB of path/queue state (>> 126 MB L2); the BVH (33 MB nodes + 42 MB f32 prefilter records + 70 MB f64 leaf slots) is meant to stay L2-resident",
+                   "wavefront_paths": args.wavefront, "bvh_build_s": round(build_s, 2),
+                   "headline_precision": "RT_SHADE_F32: intersection decisions, hit points and rays are f64-exact (bit-exact ids vs the oracle); radiometry in f32, image parity within the relMSE / mean-bias bounds of tests/test_gpu_parity.py; the all-f64 figure of the same workload is `exact_f64_shading`"},
         "samples_per_s": paths_all / wall,
         "rays": {"extend": tot["extend_rays"], "shadow": tot["shadow_rays"], "probe": tot["probe_rays"]},
         "device_ms_per_step": dev_ms / args.steps,
         "kernel_ms_per_step": {"extend": tot["extend_ms"] / args.steps, "shade+generate": tot["shade_ms"] / args.steps, "connect": tot["connect_ms"] / args.steps},
-        "gpu_launches": int(tot["iterations"] * 6 + 2 * args.steps),      # per iteration: prepare, generate, extend, 2 shade bins, connect; per render: closing prepare + film count
+        "gpu_launches": int(tot["iterations"] * (4 + n_bins) + 2 * args.steps),      # per iteration: prepare, generate, extend, one shade kernel per bin in the scene, connect; per render: closing prepare + film count
         "clocks": clk,
         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": C.sizeof(N.Camera) + C.sizeof(N.IntegratorDesc) + C.sizeof(N.FilmDesc),
                 "d2h_bytes_per_step": H * W * 4 * 8, "ms_per_step": 1e3 * wall_e2e / args.steps},
-        "roofline": {"kernel": "k_extend (closest-hit BVH traversal)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "peak_kind": f"{peak_kind} HBM copy bandwidth (MEASURED_PEAKS.json)", "traffic": traffic,
-                     "algorithmic_bytes_per_ray": bpr, "n_box": work["n_box"], "n_tri": work["n_tri"], "rays_per_launch": tot["extend_rays"] / max(launches, 1),
-                     "ms_per_launch": ext_ms_per_launch, "extend_Mrays_per_s": tot["extend_rays"] / max(tot["extend_ms"], 1e-9) / 1e3,
-                     "note": "algorithmic bytes are counted on the ORACLE's reference traversal (median-split tree, 1 prim/leaf), so a better tree + L2 residency can exceed the HBM copy peak"},
+        "roofline": extend_rooflines(tot, launches, clk),
     }
-    if world == 1 and args.shade == "f32":
-        # for the record: the same step with the shade kernel in the reference's f64 arithmetic (per-pixel parity mode)
-        integ64 = IntType.Path(DEPTH, shade_f32=False)
-        film_t.zero_(); torch.cuda.synchronize()
-        t1 = time.perf_counter()
-        render_samples(objects, cam, integ64, film, W, H, 0, spp, seed=1234)
-        torch.cuda.synchronize()
-        c64 = objects.counters()
-        out["exact_f64_shading"] = {"value": (c64["extend_rays"] + c64["shadow_rays"] + c64["probe_rays"]) / (time.perf_counter() - t1) / 1e6, "unit": UNIT,
-                                    "kernel_ms": {"extend": c64["extend_ms"], "shade+generate": c64["shade_ms"], "connect": c64["connect_ms"]}}
+    if f64:
+        out["exact_f64_shading"] = f64
     if world == 1 and not args.no_cpu_baseline:
         sys.path.insert(0, os.path.join(ROOT, "tests"))
         import orc                                         # the checker, used here ONLY as the timed CPU baseline

@@ -277,6 +277,11 @@ rt_status rt_occluded(rt_scene* scene, uint64_t n, const rt_shadow_query* querie
 rt_status rt_occluded_device(rt_scene* scene, uint64_t n, const rt_shadow_query* d_queries,
                              uint8_t* d_unoccluded_out, void* cuda_stream);
 
+/* Audit of the conservative f32 triangle prefilter that runs in front of the exact f64 test (Mesh::intersects_triangle,
+ * hittable.rs:292-362).  Only a library built with -DRT_PREFILTER_CHECK=1 counts: out = {triangle slot tests, skipped by the
+ * prefilter, exact hits, VIOLATIONS (a skipped slot whose exact hit the traversal would have used; must stay 0)}; zeros otherwise. */
+rt_status rt_debug_prefilter_stats(uint64_t out[4]);
+
 /* ---------------------------------------------------------------- render
  * Film = the reference's `Vec<Vec<(f64,f64,f64,u32)>>` running sums (render.rs:18-22),
  * flattened row-major as 4 doubles (r,g,b,n) per pixel, pixel (0,0) = upper-left.      */

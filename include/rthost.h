@@ -1,5 +1,6 @@
 /*
- * rthost.h — host scene layer of librtcore.so (C ABI).
+ * rthost.h — host scene layer, librthost.so (C ABI).  Pure host code with no link-time dependency on the CUDA library librtcore.so:
+ * only rth_scene_upload talks to it, through the public rt_scene_* calls it looks up at run time.
  *
  * The reference keeps scene construction on the host (scenes.rs, parser.rs; north_star: "the Rust
  * host keeps scene parsing, material setup ..."); no Rust toolchain exists in this image, so the
@@ -38,6 +39,8 @@ typedef struct rth_params {
  *          "two_dragons" (:549), "material_hdr" (:627, HDR environment = Light::Infinite),
  *          "teapot_hdr" (:744, plastic teapot on a transformed checkered floor rect under the HDR
  *          environment), "soup"  }                                                          */
+/* message of the last failed rth_* call on the calling thread */
+const char* rth_last_error_string(void);
 rt_status   rth_scene_build(const char* name, const rth_params* params, rth_scene** out);
 void        rth_scene_destroy(rth_scene* s);
 /* the (String path, Camera, Samplers) a scene function returns */

@@ -52,8 +52,8 @@ void orc_scene_set_lights(void* sp, uint64_t n, const rt_light* l) {
     Scene& s = *(Scene*)sp; s.lights.clear();
     for (uint64_t i = 0; i < n; i++) { Light L; L.d = l[i]; L.area = 0; s.lights.push_back(L); }
 }
-// boxes + the faithful tree (hittable.rs:637-723) with a seeded axis choice
-void orc_scene_commit(void* sp, uint64_t bvh_seed) {
+// boxes and light tables, no tree (follow with orc_scene_build_fast_tree): the million-triangle soups, where the faithful builder takes minutes
+void orc_scene_commit_tables(void* sp) {
     Scene& s = *(Scene*)sp;
     s.boxes.resize(s.prims.size());
     for (size_t i = 0; i < s.prims.size(); i++) s.boxes[i] = prim_box(s, s.prims[i]);
@@ -63,6 +63,11 @@ void orc_scene_commit(void* sp, uint64_t bvh_seed) {
         else L.area = prim_area(s, s.prims[L.d.prim_index]);                    // light.rs:603
     }
     s.nodes.clear(); s.root = -1;
+}
+// boxes + the faithful tree (hittable.rs:637-723) with a seeded axis choice
+void orc_scene_commit(void* sp, uint64_t bvh_seed) {
+    Scene& s = *(Scene*)sp;
+    orc_scene_commit_tables(sp);
     if (!s.prims.empty()) {
         s.nodes.reserve(2 * s.prims.size());
         std::vector<uint32_t> idx(s.prims.size());
@@ -71,6 +76,9 @@ void orc_scene_commit(void* sp, uint64_t bvh_seed) {
         s.root = bvh_build(s, idx, 0, idx.size(), rng);
     }
 }
+// The quick median-split tree for the hit-set traversal (orc_intersect mode 3) on large soups; replaces the faithful tree of orc_scene_commit
+// (modes 0 and 2 then walk this tree: still a valid tree of the reference's shape, just not the seeded random-axis one).
+void orc_scene_build_fast_tree(void* sp, int threads) { bvh_build_fast(*(Scene*)sp, threads < 1 ? 1 : threads); }
 uint64_t orc_scene_num_primitives(void* sp) { return ((Scene*)sp)->prims.size(); }
 void orc_scene_prim_box(void* sp, uint32_t i, double out[6]) {
     const Box& b = ((Scene*)sp)->boxes[i];
@@ -87,7 +95,7 @@ static void fill_hit(rt_hit& h, bool hit, const HitRecord& r) {
 }
 
 // mode 0: faithful tree (both children, no shrinking); 1: brute force over all prims (+ tie set);
-// 2: ordered traversal (SURVEY.md §8d work counting).  stats[0..1] += box tests, prim tests.
+// 2: ordered traversal (SURVEY.md §8d work counting); 3: hit set + tie set over the tree (same answer as 1, for large scenes).  stats[0..1] += box tests, prim tests.
 // ties_out (mode 1, may be NULL): per ray up to 4 prim ids sharing t_min (RT_NONE padded).
 void orc_intersect(void* sp, uint64_t n, const rt_ray* rays, double tmin, double tmax, int mode, int threads,
                    rt_hit* hits, uint32_t* ties_out, uint64_t* stats) {
@@ -99,6 +107,10 @@ void orc_intersect(void* sp, uint64_t n, const rt_ray* rays, double tmin, double
         if (mode == 1) {
             std::vector<uint32_t> ties;
             hit = closest_brute(s, ray, tmin, tmax, rec, &ties);
+            if (ties_out) for (int k = 0; k < 4; k++) ties_out[4 * i + k] = (hit && k < (int)ties.size()) ? ties[k] : RT_NONE;
+        } else if (mode == 3) {
+            std::vector<uint32_t> ties;
+            hit = closest_hitset(s, ray, tmin, tmax, rec, &ties);
             if (ties_out) for (int k = 0; k < 4; k++) ties_out[4 * i + k] = (hit && k < (int)ties.size()) ? ties[k] : RT_NONE;
         } else if (mode == 2) {
             closest_ordered(s, ray, tmin, tmax, hit, rec, st[t]);

@@ -1,6 +1,7 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY (see orc_math.h).  PARITY UNPINNED.
 // L0 of the reference: rays, boxes, primitives, intersection, hit record, BVH.
 #pragma once
+#include <thread>
 #include "orc_math.h"
 #include "../include/rtcore.h"
 
@@ -441,6 +442,61 @@ inline bool get_intersection(const Scene& s, const Ray& ray, HitRecord& out, Tra
 inline bool intersect_range(const Scene& s, const Ray& ray, double tmin, double tmax, HitRecord& out, TravStats* st = nullptr) {
     if (s.root < 0) return false;
     return bvh_intersects(s, s.root, ray, tmin, tmax, out, st);
+}
+
+// ---- hit-set oracle over a tree (SURVEY.md §8c "a BVH-accelerated variant of the same predicate"): every node whose f64 box passes
+// BoundingBox::intersects with the UNCHANGED [tmin, tmax] is visited (a leaf box that passes implies every ancestor passes — monotonic IEEE
+// rounding, §8a row 4 — so no primitive of the hit set is missed), leaves run the reference's exact predicate, and the result is what
+// closest_brute returns: the min-t record and the tie set {prim : t == t_min}.  The tree only decides which boxes are looked at, not the
+// answer; bvh_build_fast builds one quickly for the 1 M - 50 M triangle soups (median split with nth_element on the widest axis of the
+// box minima, one primitive per leaf, subtrees in parallel), where the faithful builder's stable_sort per level takes minutes.
+inline bool closest_hitset(const Scene& s, const Ray& ray, double tmin, double tmax, HitRecord& best, std::vector<uint32_t>* ties) {
+    bool any = false; HitRecord rec;
+    if (ties) ties->clear();
+    if (s.root < 0) return false;
+    std::vector<int32_t> stack; stack.reserve(256); stack.push_back(s.root);
+    while (!stack.empty()) {
+        const BvhNode& nd = s.nodes[stack.back()]; stack.pop_back();
+        if (!box_intersects(nd.box, ray, tmin, tmax)) continue;
+        if (nd.left >= 0) { stack.push_back(nd.left); stack.push_back(nd.right); continue; }
+        if (!prim_intersects(s, nd.prim, ray, tmin, tmax, rec)) continue;
+        if (!any || rec.t < best.t) { best = rec; any = true; if (ties) { ties->clear(); ties->push_back(nd.prim); } }
+        else if (rec.t == best.t) { if (ties) ties->push_back(nd.prim); if (nd.prim > best.prim_index) best = rec; }
+    }
+    if (ties) std::sort(ties->begin(), ties->end());
+    return any;
+}
+inline int32_t bvh_build_fast_rec(Scene& s, uint32_t* idx, size_t n, int32_t base, int par_depth);
+inline void bvh_build_fast(Scene& s, int threads) {
+    s.nodes.clear(); s.root = -1;
+    const size_t n = s.prims.size();
+    if (n == 0) return;
+    s.nodes.resize(2 * n - 1);                       // subtree over k primitives occupies 2k-1 consecutive nodes, root first
+    std::vector<uint32_t> idx(n);
+    for (size_t i = 0; i < n; i++) idx[i] = (uint32_t)i;
+    int depth = 0; while ((1 << depth) < threads) depth++;
+    s.root = bvh_build_fast_rec(s, idx.data(), n, 0, depth + 1);
+}
+inline int32_t bvh_build_fast_rec(Scene& s, uint32_t* idx, size_t n, int32_t base, int par_depth) {
+    BvhNode& nd = s.nodes[base];
+    if (n == 1) { nd.box = s.boxes[idx[0]]; nd.left = -1; nd.right = -1; nd.prim = idx[0]; return base; }
+    double lo[3] = {1e308, 1e308, 1e308}, hi[3] = {-1e308, -1e308, -1e308};
+    for (size_t i = 0; i < n; i++) for (int a = 0; a < 3; a++) { lo[a] = rmin(lo[a], s.boxes[idx[i]].mn[a]); hi[a] = rmax(hi[a], s.boxes[idx[i]].mn[a]); }
+    int axis = 0; for (int a = 1; a < 3; a++) if (hi[a] - lo[a] > hi[axis] - lo[axis]) axis = a;
+    const size_t mid = n / 2;
+    std::nth_element(idx, idx + mid, idx + n, [&](uint32_t a, uint32_t b) { return s.boxes[a].mn[axis] < s.boxes[b].mn[axis]; });
+    const int32_t lbase = base + 1, rbase = base + 1 + (int32_t)(2 * mid - 1);
+    int32_t l, r;
+    if (par_depth > 0 && n > 100000) {
+        std::thread th([&]() { l = bvh_build_fast_rec(s, idx, mid, lbase, par_depth - 1); });
+        r = bvh_build_fast_rec(s, idx + mid, n - mid, rbase, par_depth - 1);
+        th.join();
+    } else {
+        l = bvh_build_fast_rec(s, idx, mid, lbase, 0);
+        r = bvh_build_fast_rec(s, idx + mid, n - mid, rbase, 0);
+    }
+    nd.box = box_union(s.nodes[l].box, s.nodes[r].box); nd.left = l; nd.right = r; nd.prim = RT_NONE;
+    return base;
 }
 
 // The "reference traversal" of SURVEY.md §8(d) used ONLY to count algorithmic work per ray:

@@ -76,15 +76,16 @@ RTCORE_SYMBOLS = [
     "rt_intersect_range", "rt_intersect_device", "rt_closest_device", "rt_occluded", "rt_occluded_device", "rt_film_create",
     "rt_film_create_external", "rt_film_destroy", "rt_film_clear", "rt_film_read", "rt_film_resolve_rgb8", "rt_render",
     "rt_render_cancel", "rt_get_counters", "rt_set_wavefront_size", "rt_scene_set_build_mode", "rt_scene_build_stats",
+    "rt_debug_prefilter_stats",
 ]
 RTHOST_SYMBOLS = [
     "rth_scene_build", "rth_scene_destroy", "rth_scene_camera", "rth_scene_png_name", "rth_scene_uses_standin", "rth_scene_counts",
     "rth_scene_mesh_sizes", "rth_scene_mesh_copy", "rth_scene_copy_primitives", "rth_scene_copy_transforms", "rth_scene_copy_textures",
     "rth_scene_copy_materials", "rth_scene_copy_lights", "rth_scene_upload", "rth_scene_add_obj", "rth_scene_create_empty", "rth_primary_rays",
-    "rth_scene_num_images", "rth_scene_image_info", "rth_scene_image_copy", "rth_load_hdr",
+    "rth_scene_num_images", "rth_scene_image_info", "rth_scene_image_copy", "rth_load_hdr", "rth_last_error_string",
 ]
 
-_lib = None
+HOST_LIB_PATH = os.environ.get("RT_LIBRTHOST", os.path.join(_HERE, "librthost.so"))
 
 
 class RtError(RuntimeError):
@@ -93,19 +94,18 @@ class RtError(RuntimeError):
         self.status = status
 
 
-def lib():
-    """Load librtcore.so (built in-tree by `make -C rustraytracer_b200/csrc` / __graft_entry__.build())."""
-    global _lib
-    if _lib is not None:
-        return _lib
+def _missing(path):
+    return ImportError(f"{path} is missing: build it with __graft_entry__.build(); there is no fallback path")
+
+
+def _load_core():
+    """librtcore.so: the CUDA library (include/rtcore.h)."""
     if not os.path.exists(LIB_PATH):
-        raise ImportError(f"{LIB_PATH} is missing: build it with __graft_entry__.build(); there is no fallback path")
+        raise _missing(LIB_PATH)
     L = C.CDLL(LIB_PATH)
     vp, u32, u64, f64 = C.c_void_p, C.c_uint32, C.c_uint64, C.c_double
     L.rt_last_error_string.restype = C.c_char_p
     L.rt_version_string.restype = C.c_char_p
-    L.rth_scene_png_name.restype = C.c_char_p
-    L.rth_scene_png_name.argtypes = [vp]
     L.rt_round_spp.restype = u32
     L.rt_round_spp.argtypes = [u32]
     sigs = {
@@ -124,7 +124,26 @@ def lib():
         "rt_film_create": [u32, u32, vp], "rt_film_create_external": [u32, u32, vp, vp], "rt_film_destroy": [vp],
         "rt_film_clear": [vp], "rt_film_read": [vp, vp], "rt_film_resolve_rgb8": [vp, vp],
         "rt_render": [vp, vp, vp, vp, vp], "rt_render_cancel": [vp], "rt_get_counters": [vp, vp], "rt_set_wavefront_size": [vp, u32],
-        "rt_scene_set_build_mode": [vp, u32], "rt_scene_build_stats": [vp, vp],
+        "rt_scene_set_build_mode": [vp, u32], "rt_scene_build_stats": [vp, vp], "rt_debug_prefilter_stats": [vp],
+    }
+    for name, args in sigs.items():
+        fn = getattr(L, name)
+        fn.argtypes = args
+        fn.restype = C.c_int32
+    L.rt_device_count.restype = C.c_int32
+    return L
+
+
+def _load_host():
+    """librthost.so: the host scene layer (include/rthost.h).  Pure host code: loading it does not map the CUDA library."""
+    if not os.path.exists(HOST_LIB_PATH):
+        raise _missing(HOST_LIB_PATH)
+    L = C.CDLL(HOST_LIB_PATH)
+    vp, u32, u64 = C.c_void_p, C.c_uint32, C.c_uint64
+    L.rth_scene_png_name.restype = C.c_char_p
+    L.rth_scene_png_name.argtypes = [vp]
+    L.rth_last_error_string.restype = C.c_char_p
+    sigs = {
         "rth_scene_build": [C.c_char_p, vp, vp], "rth_scene_destroy": [vp], "rth_scene_camera": [vp, vp],
         "rth_scene_uses_standin": [vp], "rth_scene_counts": [vp, vp], "rth_scene_mesh_sizes": [vp, u32, vp],
         "rth_scene_mesh_copy": [vp, u32, vp, vp, vp, vp], "rth_scene_copy_primitives": [vp, vp], "rth_scene_copy_transforms": [vp, vp],
@@ -138,14 +157,40 @@ def lib():
         fn = getattr(L, name)
         fn.argtypes = args
         fn.restype = None if name in ("rth_scene_destroy",) else C.c_int32
-    L.rt_device_count.restype = C.c_int32
-    _lib = L
     return L
+
+
+class _Libs:
+    """`lib().rt_*` resolves in librtcore.so, `lib().rth_*` in librthost.so; each library is loaded on first use, so a process that only
+    builds scene tables (bench.py --impl reference: host layer + oracle) never maps the CUDA library."""
+    core = None
+    host = None
+
+    def __getattr__(self, name):
+        if name.startswith("rth_"):
+            if _Libs.host is None:
+                _Libs.host = _load_host()
+            return getattr(_Libs.host, name)
+        if _Libs.core is None:
+            _Libs.core = _load_core()
+        return getattr(_Libs.core, name)
+
+
+_libs = _Libs()
+
+
+def lib():
+    return _libs
 
 
 def check(status):
     if status != RT_OK:
-        raise RtError(status, lib().rt_last_error_string().decode())
+        msgs = []
+        if _Libs.core is not None:
+            msgs.append(_Libs.core.rt_last_error_string().decode())
+        if _Libs.host is not None and _Libs.host.rth_last_error_string():
+            msgs.append("host layer: " + _Libs.host.rth_last_error_string().decode())
+        raise RtError(status, " | ".join(m for m in msgs if m))
 
 
 def ptr(a):

@@ -115,11 +115,19 @@ inline int32_t encode_leaf(uint32_t first_slot, uint32_t count) { return ~(int32
 
 }  // namespace
 
-void build_bvh(const std::vector<Box64>& boxes, BuiltBvh& out, int threads) {
-    out.nodes.clear(); out.order.clear();
+// Conservativeness of the f32 boxes (the same rule in bvh_device.cu:k_leaves).  The traversal's f32 slab test (traverse.cuh:node4_test) must never
+// reject a child whose f64 leaf test (hittable.rs:494-508 on the primitive's own f64 box) would pass.  Its error budget is carried on the RAY side:
+//   * planes: f64 -> f32 rounded outward here, so the f32 box contains the f64 box;
+//   * origin: o32 = fl(o), |o32 - o| <= 2^-24 |o|  -> make_rayf's `pad` (4.8e-7 max|o| per unit of |1/d|, 8x the bound);
+//   * q = fl(o32 * idx): 2^-24 |q|                 -> + 2.4e-7 |q| (4x);
+//   * idx = fl(1 / fl(d)): relative 2^-23, one rounding in the fma: 2^-24 -> t0 -= 4.8e-7 |t0|, t1 += 4.8e-7 |t1| (2.7x).
+// That already covers every rounding in the test; the relative pad of 2^-22 of the coordinate magnitude added here on top is a second,
+// independent margin (it loosens a box by 0.25 ppm and was measured to cost nothing), kept identical in both builders so that they cull alike.
+rt_status build_bvh(const std::vector<Box64>& boxes, BuiltBvh& out, int threads) {
+    out.nodes.clear(); out.order.clear(); out.max_stack = 0;
     size_t n = boxes.size();
-    if (n == 0) return;
-    if (n >= (1ull << 29)) { set_error("too many primitives for the leaf encoding"); return; }
+    if (n == 0) return RT_OK;
+    if (n >= (1ull << 29)) { set_error("too many primitives for the leaf encoding (2^29)"); return RT_ERR_INVALID; }
     std::vector<FBox> pb(n);
     for (size_t i = 0; i < n; i++)
         for (int k = 0; k < 3; k++) {
@@ -222,6 +230,7 @@ void build_bvh(const std::vector<Box64>& boxes, BuiltBvh& out, int threads) {
     }
 #endif
     out.order = std::move(idx);
+    return RT_OK;
 }
 
 }  // namespace rt

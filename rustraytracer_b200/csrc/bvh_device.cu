@@ -72,7 +72,11 @@ __global__ void __launch_bounds__(256) k_leaves(const Box64* __restrict__ boxes,
     for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
         const uint32_t p = order[j];
         FB b;
-        for (int k = 0; k < 3; k++) { b.mn[k] = __double2float_rd(boxes[p].mn[k]); b.mx[k] = __double2float_ru(boxes[p].mx[k]); }
+        // the same rule as the host build (bvh_build.cpp:leaf_box_f32): relative pad of 2^-22 of the coordinate magnitude, then outward rounding
+        for (int k = 0; k < 3; k++) {
+            const double lo = boxes[p].mn[k], hi = boxes[p].mx[k], pad = (fabs(lo) + fabs(hi)) * 2.4e-7;
+            b.mn[k] = __double2float_rd(lo - pad); b.mx[k] = __double2float_ru(hi + pad);
+        }
         fb[(size_t)(n - 1) + j] = b;
         const double2* s = reinterpret_cast<const double2*>(slots_in + p); double2* d = reinterpret_cast<double2*>(slots_out + j);
         d[0] = s[0]; d[1] = s[1]; d[2] = s[2]; d[3] = s[3]; d[4] = s[4];
@@ -174,10 +178,12 @@ __global__ void __launch_bounds__(256) k_stack_need(const DNode4* __restrict__ n
 rt_status build_bvh_device(const Box64* d_boxes, const DSlot* d_slots_in, uint32_t n, DNode4** nodes_out, uint32_t* n_nodes_out, DSlot** slots_out, int* max_stack_out, float* build_ms) {
     std::vector<void*> tmp;
     DNode4* nodes_big = nullptr; DSlot* slots = nullptr;
-    auto cleanup = [&]() { for (void* p : tmp) cudaFree(p); if (nodes_big) cudaFree(nodes_big); if (slots) cudaFree(slots); };
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    auto cleanup = [&]() { for (void* p : tmp) cudaFree(p); if (nodes_big) cudaFree(nodes_big); if (slots) cudaFree(slots); if (e0) cudaEventDestroy(e0); if (e1) cudaEventDestroy(e1); };
     auto alloc = [&](size_t bytes) -> void* { void* p = nullptr; if (cudaMalloc(&p, bytes ? bytes : 16) != cudaSuccess) return nullptr; tmp.push_back(p); return p; };
     if (n < 8) { set_error("device BVH build: needs at least 8 primitives"); return RT_ERR_INVALID; }
-    cudaEvent_t e0, e1; CKB(cudaEventCreate(&e0)); CKB(cudaEventCreate(&e1));
+    if (n >= (1u << 29)) { set_error("device BVH build: too many primitives for the leaf encoding (2^29)"); return RT_ERR_INVALID; }   // leaf word ~((first << 2) | count-1) must stay negative
+    CKB(cudaEventCreate(&e0)); CKB(cudaEventCreate(&e1));
     CKB(cudaEventRecord(e0, 0));
     const int grid = 148 * 8;
     unsigned long long* bounds = (unsigned long long*)alloc(6 * 8);
@@ -237,7 +243,7 @@ rt_status build_bvh_device(const Box64* d_boxes, const DSlot* d_slots_in, uint32
     if (cudaMalloc((void**)&nodes, (size_t)made * sizeof(DNode4)) != cudaSuccess) { set_error("device BVH build: out of device memory"); cleanup(); return RT_ERR_CUDA; }
     if (cudaMemcpy(nodes, nodes_big, (size_t)made * sizeof(DNode4), cudaMemcpyDeviceToDevice) != cudaSuccess) { cudaFree(nodes); set_error("device BVH build: copy failed"); cleanup(); return RT_ERR_CUDA; }
     cudaEventRecord(e1, 0); cudaEventSynchronize(e1);
-    float ms = 0; cudaEventElapsedTime(&ms, e0, e1); cudaEventDestroy(e0); cudaEventDestroy(e1);
+    float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
     if (build_ms) *build_ms = ms;
     *nodes_out = nodes; *n_nodes_out = made; *slots_out = slots; *max_stack_out = need0 + 1;
     slots = nullptr;                                         // ownership moves to the caller

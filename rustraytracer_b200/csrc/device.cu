@@ -85,6 +85,23 @@ __global__ void k_scatter_other_slots(uint32_t n, const uint32_t* __restrict__ i
     }
 }
 
+// The prefilter's 48-byte f32 record of every leaf slot (traverse.cuh:tri_prefilter), derived on the device from the leaf-ordered f64 slots of
+// either builder: vertices rounded to nearest f32, the primitive id and slot kind, and pmax = max |coordinate| of the f64 vertices rounded UP
+// (the error bound's |p| <= pmax must hold for the f64 values).
+__global__ void __launch_bounds__(256) k_make_tri32(uint32_t n, const DSlot* __restrict__ slots, float4* __restrict__ out) {
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        const double2* q = reinterpret_cast<const double2*>(slots + i);
+        const double2 q0 = q[0], q1 = q[1], q2 = q[2], q3 = q[3], q4 = q[4];
+        const uint2 tag = *reinterpret_cast<const uint2*>(&q4.y);
+        const double v[9] = {q0.x, q0.y, q1.x, q1.y, q2.x, q2.y, q3.x, q3.y, q4.x};
+        double m = 0.;
+        for (int k = 0; k < 9; k++) m = fmax(m, fabs(v[k]));
+        out[3 * i + 0] = make_float4((float)v[0], (float)v[1], (float)v[2], (float)v[3]);
+        out[3 * i + 1] = make_float4((float)v[4], (float)v[5], (float)v[6], (float)v[7]);
+        out[3 * i + 2] = make_float4((float)v[8], __uint_as_float(tag.x), __uint_as_float(tag.y), __double2float_ru(m));
+    }
+}
+
 rt_status upload_scene(rt_scene& s, HostImage& img) {
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) { set_error("no CUDA device: librtcore has no CPU path"); return RT_ERR_CUDA; }
@@ -134,6 +151,16 @@ rt_status upload_scene(rt_scene& s, HostImage& img) {
         if ((st = up(s, img.nodes, d.nodes, s.bytes_nodes))) return st;
         if ((st = up(s, img.slots, d.slots, s.bytes_slots))) return st;
     }
+    {   // f32 prefilter records, leaf order
+        void* tp = nullptr;
+        CK(cudaMalloc(&tp, std::max<size_t>(img.n_slots, 1) * 3 * sizeof(float4)));
+        s.allocations.push_back(tp);
+        if (img.n_slots) {
+            k_make_tri32<<<148 * 8, 256>>>((uint32_t)img.n_slots, d.slots, (float4*)tp);
+            CK(cudaGetLastError()); CK(cudaDeviceSynchronize());
+        }
+        d.tri32 = (const float*)tp; s.bytes_slots += (uint64_t)img.n_slots * 3 * sizeof(float4);
+    }
     if ((st = up(s, img.shapes, d.shapes, b))) return st;
     if ((st = up(s, s.xforms, d.xforms, b))) return st;
     if ((st = up(s, s.textures, d.textures, b))) return st;
@@ -158,7 +185,8 @@ rt_status upload_scene(rt_scene& s, HostImage& img) {
     }
     if ((st = up(s, lights, d.lights, b))) return st;
     s.bytes_tables = b;
-    { void* cp = nullptr; CK(cudaMalloc(&cp, 16)); s.allocations.push_back(cp); s.d_counter = (uint32_t*)cp; }   // work counter of the persistent batch kernels
+    // work counters of the persistent batch kernels: a ring, one per call in flight, so that calls on different streams never share one
+    { void* cp = nullptr; CK(cudaMalloc(&cp, N_BATCH_COUNTERS * sizeof(uint32_t))); s.allocations.push_back(cp); s.d_counter = (uint32_t*)cp; }
     d.n_nodes = n_nodes; d.n_prims = (uint32_t)img.prims.size();
     d.n_lights = (uint32_t)img.lights.size(); d.n_slots = (uint32_t)img.n_slots;
     s.d = d;
@@ -206,11 +234,17 @@ __global__ void __launch_bounds__(128) k_closest(DScene sc, uint64_t n, const rt
 // fetch the next one from a global counter instead of idling until the slowest ray of the warp is done — the soup's
 // incoherent rays differ by an order of magnitude in traversal length.
 struct ClosestJob {
-    const rt_ray* rays; double tmin, tmax; uint32_t* prim; double* t;
-    __device__ __forceinline__ bool load(uint32_t i, TState& st, int32_t* stack) {
+    const rt_ray* rays; double tmin_, tmax_; uint32_t* prim; double* t;
+    __device__ __forceinline__ double tmin(const TState&) const { return tmin_; }
+    __device__ __forceinline__ double tmax(const TState&) const { return tmax_; }
+    __device__ __forceinline__ void ray(uint32_t i, D3& o, D3& d) const {
         const double2* rp = reinterpret_cast<const double2*>(rays + i);
-        double2 a = __ldg(rp), b = __ldg(rp + 1), c = __ldg(rp + 2);
-        tstate_init(st, stack, mk3(a.x, a.y, b.x), mk3(b.y, c.x, c.y), tmin, tmax, false, 0., 0u);
+        const double2 a = __ldg(rp), b = __ldg(rp + 1), c = __ldg(rp + 2);
+        o = mk3(a.x, a.y, b.x); d = mk3(b.y, c.x, c.y);
+    }
+    __device__ __forceinline__ bool load(uint32_t i, TState& st, int32_t* stack) {
+        D3 o, d; ray(i, o, d);
+        tstate_init(st, stack, o, d, tmin_, tmax_, false, 0., 0u);
         return true;
     }
     __device__ __forceinline__ void finish(uint32_t i, const TState& st) { prim[i] = st.best.prim; t[i] = st.best.t; }
@@ -249,6 +283,17 @@ extern "C" {
 int32_t rt_device_count(void) { int c = 0; if (cudaGetDeviceCount(&c) != cudaSuccess) return 0; return c; }
 rt_status rt_set_device(int32_t device) { CK(cudaSetDevice(device)); return RT_OK; }
 
+// RT_PREFILTER_CHECK builds: {triangle slot tests, skipped by the f32 prefilter, exact hits, violations} summed over every traversal kernel
+// since the library was loaded; zeros otherwise.  A violation = the prefilter skipped a slot whose exact hit the traversal would have used.
+rt_status rt_debug_prefilter_stats(uint64_t out[4]) {
+    if (!out) { set_error("rt_debug_prefilter_stats: null argument"); return RT_ERR_INVALID; }
+    unsigned long long acc[4] = {0, 0, 0, 0};
+    cudaDeviceSynchronize();
+    prefilter_stats_add(acc); render_prefilter_stats(acc);
+    for (int k = 0; k < 4; k++) out[k] = acc[k];
+    return RT_OK;
+}
+
 rt_status rt_intersect_device(rt_scene* s, uint64_t n, const rt_ray* d_rays, double tmin, double tmax, rt_hit* d_hits, void* stream) {
     rt_status st = check_scene(s, "rt_intersect_device"); if (st) return st;
     if (n == 0) return RT_OK;
@@ -266,9 +311,10 @@ rt_status rt_closest_device(rt_scene* s, uint64_t n, const rt_ray* d_rays, doubl
     const uint64_t CHUNK = 1ull << 31;
     for (uint64_t base = 0; base < n; base += CHUNK) {
         uint32_t m = (uint32_t)std::min<uint64_t>(CHUNK, n - base);
-        CK(cudaMemsetAsync(s->d_counter, 0, sizeof(uint32_t), (cudaStream_t)stream));
+        uint32_t* counter = s->d_counter + (s->counter_next.fetch_add(1u) % N_BATCH_COUNTERS);
+        CK(cudaMemsetAsync(counter, 0, sizeof(uint32_t), (cudaStream_t)stream));
         ClosestJob job{d_rays + base, tmin, tmax, d_prim + base, d_t + base};
-        k_closest_persistent<<<sms * 5, 128, 0, (cudaStream_t)stream>>>(s->d, job, m, s->d_counter);
+        k_closest_persistent<<<sms * 5, 128, 0, (cudaStream_t)stream>>>(s->d, job, m, counter);
     }
     CK(cudaGetLastError());
     return RT_OK;

@@ -4,15 +4,23 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <dlfcn.h>
 #include <map>
+#include <mutex>
 #include <string>
 #include <tuple>
+#include <type_traits>
 #include <vector>
 #include "rt_internal.h"
+#include "camera_host.h"
 #include "../../include/rthost.h"
 
 using rt::PI;
 using rt::SMALL;
+
+// librthost.so keeps its own last-error string (rth_last_error_string): it does not link against librtcore.so
+static thread_local std::string g_host_error;
+static void host_error(const std::string& msg) { g_host_error = msg; }
 
 struct rth_scene {
     std::vector<rt::HostMesh> meshes;
@@ -67,7 +75,7 @@ uint32_t push_xform(rth_scene& s, const double m[16]) { s.xforms.insert(s.xforms
 
 void camera(rth_scene& s, const double from[3], const double to[3], double aspect, double vfov, double aperture, double focus, double t0, double t1) {
     double up[3] = {0., 1., 0.};
-    rt_camera_look_at(from, to, up, aspect, vfov, aperture, focus, t0, t1, &s.camera);
+    rt::camera_look_at(from, to, up, aspect, vfov, aperture, focus, t0, t1, &s.camera);
 }
 uint32_t push_hdr_texture(rth_scene& s, uint32_t image) { rt_texture t{}; t.type = RT_TEX_HDR; t.image = image; s.textures.push_back(t); return (uint32_t)s.textures.size() - 1; }      // Texture::new_hdr
 uint32_t push_image_texture(rth_scene& s, uint32_t image) { rt_texture t{}; t.type = RT_TEX_IMAGE; t.image = image; s.textures.push_back(t); return (uint32_t)s.textures.size() - 1; }  // Texture::new_texture
@@ -518,7 +526,7 @@ uint32_t add_obj_or_blob(rth_scene& s, const rth_params& p, const char* rel, con
     return (uint32_t)s.meshes.size() - 1;
 }
 void camera_up(rth_scene& s, const double from[3], const double to[3], const double up[3], double aspect, double vfov) {
-    rt_camera_look_at(from, to, up, aspect, vfov, 0.0, 10., 0., 0., &s.camera);     // Camera::new → t0 = t1 = 0
+    rt::camera_look_at(from, to, up, aspect, vfov, 0.0, 10., 0., 0., &s.camera);     // Camera::new → t0 = t1 = 0
 }
 // scenes.rs:627-741 `material_hdr(mat_num)`: the material-test ball under an HDR environment (Light::Infinite), variant =
 // mat_num: 0 smooth_plastic (:824), 1 rosegold_metal (:839), 2 mirror (:876), 3 glass (:857)
@@ -617,9 +625,9 @@ extern "C" {
 
 rt_status rth_scene_create_empty(rth_scene** out) { if (!out) return RT_ERR_INVALID; *out = new rth_scene(); return RT_OK; }
 rt_status rth_scene_build(const char* name, const rth_params* params, rth_scene** out) {
-    if (!name || !params || !out) { rt::set_error("rth_scene_build: null argument"); return RT_ERR_INVALID; }
-    if (params->width == 0 || params->height == 0) { rt::set_error("rth_scene_build: zero image size"); return RT_ERR_INVALID; }
-    if (params->n_tris > 170000000ull) { rt::set_error("rth_scene_build: n_tris too large"); return RT_ERR_INVALID; }
+    if (!name || !params || !out) { host_error("rth_scene_build: null argument"); return RT_ERR_INVALID; }
+    if (params->width == 0 || params->height == 0) { host_error("rth_scene_build: zero image size"); return RT_ERR_INVALID; }
+    if (params->n_tris > 170000000ull) { host_error("rth_scene_build: n_tris too large"); return RT_ERR_INVALID; }
     rth_scene* s = new rth_scene();
     std::string n(name);
     if (n == "sphere_roughness") build_sphere_roughness(*s, *params);
@@ -631,7 +639,7 @@ rt_status rth_scene_build(const char* name, const rth_params* params, rth_scene*
     else if (n == "soup") build_soup(*s, *params);
     else if (n == "material_hdr") build_material_hdr(*s, *params);
     else if (n == "teapot_hdr") build_teapot_hdr(*s, *params);
-    else { delete s; rt::set_error("rth_scene_build: unknown scene '" + n + "'"); return RT_ERR_INVALID; }
+    else { delete s; host_error("rth_scene_build: unknown scene '" + n + "'"); return RT_ERR_INVALID; }
     *out = s;
     return RT_OK;
 }
@@ -683,41 +691,81 @@ rt_status rth_scene_image_copy(const rth_scene* s, uint32_t i, void* out) {
     return RT_OK;
 }
 rt_status rth_load_hdr(const char* path, uint32_t* w, uint32_t* h, float* rgb_out, uint64_t capacity_floats) {
-    if (!path || !w || !h) { rt::set_error("rth_load_hdr: null argument"); return RT_ERR_INVALID; }
+    if (!path || !w || !h) { host_error("rth_load_hdr: null argument"); return RT_ERR_INVALID; }
     rth_scene::Image img; std::string err;
-    if (!load_hdr(path, img, err)) { rt::set_error("rth_load_hdr: " + err); return RT_ERR_IO; }
+    if (!load_hdr(path, img, err)) { host_error("rth_load_hdr: " + err); return RT_ERR_IO; }
     *w = img.w; *h = img.h;
-    if (rgb_out) { if (capacity_floats < img.f.size()) { rt::set_error("rth_load_hdr: buffer too small"); return RT_ERR_INVALID; } memcpy(rgb_out, img.f.data(), img.f.size() * sizeof(float)); }
+    if (rgb_out) { if (capacity_floats < img.f.size()) { host_error("rth_load_hdr: buffer too small"); return RT_ERR_INVALID; } memcpy(rgb_out, img.f.data(), img.f.size() * sizeof(float)); }
     return RT_OK;
 }
 
+// The core library's scene setters, bound at the first rth_scene_upload: librthost.so has NO link-time dependency on librtcore.so (the CPU
+// reference arm of bench.py builds its scene tables with this library and must not map the CUDA one).  A caller that holds an rt_scene* has
+// librtcore.so in the process already; it is looked up next to this library (RTLD_NOLOAD first).
+namespace {
+struct CoreApi {
+    rt_status (*add_image_hdr)(rt_scene*, uint32_t, uint32_t, const float*, uint32_t*) = nullptr;
+    rt_status (*add_image_rgb8)(rt_scene*, uint32_t, uint32_t, const uint8_t*, uint32_t*) = nullptr;
+    rt_status (*add_mesh)(rt_scene*, uint64_t, const double*, uint64_t, const double*, uint64_t, const double*, uint64_t, const uint32_t*, uint32_t*) = nullptr;
+    rt_status (*add_transform)(rt_scene*, const double*, uint32_t*) = nullptr;
+    rt_status (*set_textures)(rt_scene*, uint64_t, const rt_texture*) = nullptr;
+    rt_status (*set_materials)(rt_scene*, uint64_t, const rt_material*) = nullptr;
+    rt_status (*set_lights)(rt_scene*, uint64_t, const rt_light*) = nullptr;
+    rt_status (*add_mesh_triangles)(rt_scene*, uint32_t, uint32_t, uint32_t*) = nullptr;
+    rt_status (*add_primitives)(rt_scene*, uint64_t, const rt_primitive*, uint32_t*) = nullptr;
+    bool ok = false;
+};
+const CoreApi& core_api() {
+    static CoreApi api;
+    static std::once_flag once;
+    std::call_once(once, []() {
+        std::string path = "librtcore.so";
+        if (const char* e = getenv("RT_LIBRTCORE")) path = e;
+        else { Dl_info info; if (dladdr((const void*)&core_api, &info) && info.dli_fname) { std::string me = info.dli_fname; size_t sl = me.rfind('/'); if (sl != std::string::npos) path = me.substr(0, sl + 1) + "librtcore.so"; } }
+        void* h = dlopen(path.c_str(), RTLD_NOW | RTLD_NOLOAD);
+        if (!h) h = dlopen(path.c_str(), RTLD_NOW | RTLD_LOCAL);
+        if (!h) { host_error(std::string("rth_scene_upload: cannot open ") + path + ": " + dlerror()); return; }
+        bool all = true;
+        auto bind = [&](auto& fn, const char* name) { fn = reinterpret_cast<std::remove_reference_t<decltype(fn)>>(dlsym(h, name)); if (!fn) { all = false; host_error(std::string("rth_scene_upload: missing symbol ") + name); } };
+        bind(api.add_image_hdr, "rt_scene_add_image_hdr"); bind(api.add_image_rgb8, "rt_scene_add_image_rgb8"); bind(api.add_mesh, "rt_scene_add_mesh");
+        bind(api.add_transform, "rt_scene_add_transform"); bind(api.set_textures, "rt_scene_set_textures"); bind(api.set_materials, "rt_scene_set_materials");
+        bind(api.set_lights, "rt_scene_set_lights"); bind(api.add_mesh_triangles, "rt_scene_add_mesh_triangles"); bind(api.add_primitives, "rt_scene_add_primitives");
+        api.ok = all;
+    });
+    return api;
+}
+}  // namespace
+
 rt_status rth_scene_upload(const rth_scene* s, rt_scene* dst) {
-    if (!s || !dst) { rt::set_error("rth_scene_upload: null argument"); return RT_ERR_INVALID; }
+    if (!s || !dst) { host_error("rth_scene_upload: null argument"); return RT_ERR_INVALID; }
+    const CoreApi& core = core_api();
+    if (!core.ok) return RT_ERR_STATE;
     rt_status st;
     for (auto& im : s->images) {
-        if (im.hdr) st = rt_scene_add_image_hdr(dst, im.w, im.h, im.f.data(), nullptr); else st = rt_scene_add_image_rgb8(dst, im.w, im.h, im.b.data(), nullptr);
+        if (im.hdr) st = core.add_image_hdr(dst, im.w, im.h, im.f.data(), nullptr); else st = core.add_image_rgb8(dst, im.w, im.h, im.b.data(), nullptr);
         if (st) return st;
     }
     for (auto& m : s->meshes) {
         uint32_t idx;
-        if ((st = rt_scene_add_mesh(dst, m.p.size() / 3, m.p.data(), m.n.size() / 3, m.n.empty() ? nullptr : m.n.data(), m.uv.size() / 2,
-                                    m.uv.empty() ? nullptr : m.uv.data(), m.ind.size(), m.ind.data(), &idx))) return st;
+        if ((st = core.add_mesh(dst, m.p.size() / 3, m.p.data(), m.n.size() / 3, m.n.empty() ? nullptr : m.n.data(), m.uv.size() / 2,
+                                m.uv.empty() ? nullptr : m.uv.data(), m.ind.size(), m.ind.data(), &idx))) return st;
     }
-    for (size_t i = 0; i < s->xforms.size() / 16; i++) if ((st = rt_scene_add_transform(dst, &s->xforms[16 * i], nullptr))) return st;
-    if ((st = rt_scene_set_textures(dst, s->textures.size(), s->textures.data()))) return st;
-    if ((st = rt_scene_set_materials(dst, s->materials.size(), s->materials.data()))) return st;
-    if ((st = rt_scene_set_lights(dst, s->lights.size(), s->lights.data()))) return st;
+    for (size_t i = 0; i < s->xforms.size() / 16; i++) if ((st = core.add_transform(dst, &s->xforms[16 * i], nullptr))) return st;
+    if ((st = core.set_textures(dst, s->textures.size(), s->textures.data()))) return st;
+    if ((st = core.set_materials(dst, s->materials.size(), s->materials.data()))) return st;
+    if ((st = core.set_lights(dst, s->lights.size(), s->lights.data()))) return st;
     for (auto& it : s->items) {
-        if (it.run) st = rt_scene_add_mesh_triangles(dst, it.mesh, it.mat, nullptr);
-        else st = rt_scene_add_primitives(dst, 1, &it.prim, nullptr);
+        if (it.run) st = core.add_mesh_triangles(dst, it.mesh, it.mat, nullptr);
+        else st = core.add_primitives(dst, 1, &it.prim, nullptr);
         if (st) return st;
     }
     return RT_OK;
 }
+const char* rth_last_error_string(void) { return g_host_error.c_str(); }
 rt_status rth_scene_add_obj(rth_scene* s, const char* path, const double xf[16], uint32_t* out) {
-    if (!s || !path || !xf) { rt::set_error("rth_scene_add_obj: null argument"); return RT_ERR_INVALID; }
+    if (!s || !path || !xf) { host_error("rth_scene_add_obj: null argument"); return RT_ERR_INVALID; }
     rt::HostMesh m; std::string err;
-    if (!load_obj(path, xf, m, err)) { rt::set_error("Failed to parse obj " + std::string(path) + ": " + err); return RT_ERR_IO; }   // parser.rs:83-85 panics
+    if (!load_obj(path, xf, m, err)) { host_error("Failed to parse obj " + std::string(path) + ": " + err); return RT_ERR_IO; }   // parser.rs:83-85 panics
     s->meshes.push_back(std::move(m));
     if (out) *out = (uint32_t)s->meshes.size() - 1;
     return RT_OK;

@@ -66,9 +66,11 @@ struct Wavefront {
 
 // `cap` = most paths allowed in flight: W for Path (one continuation per path at most); W / max(2, n_lights) for the branching integrators,
 // whose vertices append up to two continuations and one shadow + one probe entry PER LIGHT
-__global__ void k_prepare(Ctrl* c, uint32_t cap) {
-    c->c_extend += c->n_tot; c->c_shadow += c->n_shadow; c->c_probe += c->n_probe; c->c_iter += 1;
-    uint32_t n_cur = c->n_next;
+// Queue appends beyond W are dropped by the shade kernels (branching integrators only; `overflow` is raised and the host aborts the
+// render), but the counters keep counting: every consumer clamps them to W so that nothing is ever read or filed past an allocation.
+__global__ void k_prepare(Ctrl* c, uint32_t cap, uint32_t W) {
+    c->c_extend += c->n_tot; c->c_shadow += min(c->n_shadow, W); c->c_probe += min(c->n_probe, W); c->c_iter += 1;
+    uint32_t n_cur = min(c->n_next, W);
     unsigned long long remaining = c->total_samples - c->next_sample;
     uint32_t room = cap > n_cur ? cap - n_cur : 0u;
     uint32_t n_new = (uint32_t)(remaining < (unsigned long long)room ? remaining : (unsigned long long)room);
@@ -148,9 +150,16 @@ __global__ void k_film_count(RenderParams rp, unsigned long long generated, doub
 // reference's `match material` / `match primitive` arms.
 struct ExtendJob {
     Ctrl* c; const DScene* sc; PathSet ps; uint2* bin_idx; uint32_t W; const SortParams* sp;
+    __device__ __forceinline__ double tmin(const TState&) const { return SMALL; }
+    __device__ __forceinline__ double tmax(const TState&) const { return INF; }
+    __device__ __forceinline__ void ray(uint32_t i, D3& o, D3& d) const {
+        const double2* q = reinterpret_cast<const double2*>(ps.ray + i);
+        const double2 a = __ldcs(q), b = __ldcs(q + 1), c = __ldcs(q + 2);     // streaming: path state must not evict the BVH from L2
+        o = mk3(a.x, a.y, b.x); d = mk3(b.y, c.x, c.y);
+    }
     __device__ __forceinline__ bool load(uint32_t i, TState& st, int32_t* stack) {
-        PRay r = load_ray(ps.ray + i);
-        tstate_init(st, stack, mk3(r.ox, r.oy, r.oz), mk3(r.dx, r.dy, r.dz), SMALL, INF, false, 0., 0u);
+        D3 o, d; ray(i, o, d);
+        tstate_init(st, stack, o, d, SMALL, INF, false, 0., 0u);
         return true;
     }
     __device__ __forceinline__ void finish(uint32_t i, const TState& st) {
@@ -160,7 +169,7 @@ struct ExtendJob {
 #if RT_SORT_HITS
         // count the (bin, hit cell) key — one atomic per distinct key per warp — and leave (key, primitive) for k_sort_scatter
         uint32_t cell = 0;
-        if (prim != RT_NONE) cell = hit_cell(*sp, (float)(st.rx.o.x + st.best.t * st.rx.d.x), (float)(st.rx.o.y + st.best.t * st.rx.d.y), (float)(st.rx.o.z + st.best.t * st.rx.d.z));
+        if (prim != RT_NONE) cell = hit_cell(*sp, 0.f, 0.f, 0.f /* RT_SORT_HITS is retired: the state no longer carries the f64 ray */);
         const uint32_t skey = sp->slot(key) * SORT_CELLS + cell;
         const unsigned same = __match_any_sync(active, skey);
         if ((int)(threadIdx.x & 31) == __ffs(same) - 1) atomicAdd(&sp->hist[skey], (uint32_t)__popc(same));
@@ -272,16 +281,22 @@ __global__ void __launch_bounds__(128) k_shade_miss(Ctrl* c, DScene sc, RenderPa
 // C: the MIS BSDF probe (integrator.rs:614-630): closest hit; counts only if it is the sampled light.
 struct ConnectJob {
     const DScene* sc; ConnQ sh, pr; double* film; uint32_t n_shadow;
-    __device__ __forceinline__ bool load(uint32_t i, TState& st, int32_t* stack) {
+    __device__ __forceinline__ double tmin(const TState& st) const { return st.any ? 0. : SMALL; }     // shadow rays (any-hit): (0, INF); probes: (SMALL, INF)
+    __device__ __forceinline__ double tmax(const TState&) const { return INF; }
+    __device__ __forceinline__ void ray(uint32_t i, D3& o, D3& d) const {
         if (i >= n_shadow) {
-            uint32_t k = i - n_shadow;
-            tstate_init(st, stack, mk3(__ldcs(pr.ax + k), __ldcs(pr.ay + k), __ldcs(pr.az + k)), mk3(__ldcs(pr.bx + k), __ldcs(pr.by + k), __ldcs(pr.bz + k)), SMALL, INF, false, 0., 0u);
-            return true;
+            const uint32_t k = i - n_shadow;
+            o = mk3(__ldcs(pr.ax + k), __ldcs(pr.ay + k), __ldcs(pr.az + k)); d = mk3(__ldcs(pr.bx + k), __ldcs(pr.by + k), __ldcs(pr.bz + k));
+            return;
         }
-        D3 p0 = mk3(__ldcs(sh.ax + i), __ldcs(sh.ay + i), __ldcs(sh.az + i)), p1 = mk3(__ldcs(sh.bx + i), __ldcs(sh.by + i), __ldcs(sh.bz + i));
+        const D3 p0 = mk3(__ldcs(sh.ax + i), __ldcs(sh.ay + i), __ldcs(sh.az + i)), p1 = mk3(__ldcs(sh.bx + i), __ldcs(sh.by + i), __ldcs(sh.bz + i));
+        d = p1 - p0;                    // Visibility::unoccluded (hittable.rs:25-30): dir = p1 - p0, origin pushed SMALL x dir along it
+        o = p0 + d * SMALL;
+    }
+    __device__ __forceinline__ bool load(uint32_t i, TState& st, int32_t* stack) {
+        D3 org, dir; ray(i, org, dir);
+        if (i >= n_shadow) { tstate_init(st, stack, org, dir, SMALL, INF, false, 0., 0u); return true; }
         uint32_t target = __ldcs(sh.target + i);
-        D3 dir = p1 - p0;
-        D3 org = p0 + dir * SMALL;
         if (target == RT_NONE) {       // Infinite light: unoccluded(true) — visible iff NOTHING is hit over (0, INF) (hittable.rs:31-33)
             tstate_init(st, stack, org, dir, 0., INF, true, INF, RT_NONE);
             return true;
@@ -322,9 +337,10 @@ struct ConnectJob {
         film_add(film, pr.pixel[k], cmul(mk3(pr.cr[k], pr.cg[k], pr.cb[k]), le));
     }
 };
-__global__ void __launch_bounds__(128, TRACE_MIN_BLOCKS) k_connect(Ctrl* c, DScene sc, ConnQ shq, ConnQ prq, double* film) {
-    ConnectJob job{&sc, shq, prq, film, c->n_shadow};
-    trace_jobs(sc, job, c->n_shadow + c->n_probe, &c->fetch[1]);
+__global__ void __launch_bounds__(128, TRACE_MIN_BLOCKS) k_connect(Ctrl* c, DScene sc, ConnQ shq, ConnQ prq, double* film, uint32_t W) {
+    const uint32_t n_shadow = min(c->n_shadow, W), n_probe = min(c->n_probe, W);      // see k_prepare: counters may run past W on overflow
+    ConnectJob job{&sc, shq, prq, film, n_shadow};
+    trace_jobs(sc, job, n_shadow + n_probe, &c->fetch[1]);
 }
 
 // util::point_to_color (util.rs:441-471) with aces_comp (util.rs:400-408)
@@ -366,6 +382,7 @@ static void destroy_wavefront(Wavefront* w) {
     if (w->stream) cudaStreamDestroy(w->stream);
     delete w;
 }
+void render_prefilter_stats(unsigned long long out[4]) { prefilter_stats_add(out); }
 void free_wavefront(rt_scene& s) { destroy_wavefront((Wavefront*)s.wavefront); s.wavefront = nullptr; }
 
 static Wavefront* get_wavefront(rt_scene& s) {
@@ -448,19 +465,29 @@ rt_status rt_film_create(uint32_t w, uint32_t h, rt_film** out) {
     if (cudaGetDevice(&f->device) != cudaSuccess || cudaMalloc((void**)&f->d, (size_t)w * h * 4 * sizeof(double)) != cudaSuccess) {
         set_error(std::string("rt_film_create: ") + cudaGetErrorString(cudaGetLastError())); delete f; return RT_ERR_CUDA;
     }
-    cudaMemset(f->d, 0, (size_t)w * h * 4 * sizeof(double));
+    // rt_render accumulates on its own non-blocking stream, which has no implicit ordering with the legacy stream the memset runs on:
+    // the film must be zero before the call returns
+    if (cudaMemset(f->d, 0, (size_t)w * h * 4 * sizeof(double)) != cudaSuccess || cudaStreamSynchronize(cudaStreamLegacy) != cudaSuccess) {
+        set_error(std::string("rt_film_create: ") + cudaGetErrorString(cudaGetLastError())); cudaFree(f->d); delete f; return RT_ERR_CUDA;
+    }
     *out = f; return RT_OK;
 }
 rt_status rt_film_create_external(uint32_t w, uint32_t h, void* dev, rt_film** out) {
     if (!out || !w || !h || !dev) { set_error("rt_film_create_external: bad argument"); return RT_ERR_INVALID; }
     rt_film* f = new rt_film(); f->w = w; f->h = h; f->owned = false; f->d = (double*)dev;
     if (cudaGetDevice(&f->device) != cudaSuccess) { set_error("rt_film_create_external: no CUDA device"); delete f; return RT_ERR_CUDA; }
+    cudaPointerAttributes pa{};                    // the device that owns the caller's allocation, not whichever happens to be current
+    if (cudaPointerGetAttributes(&pa, dev) == cudaSuccess && (pa.type == cudaMemoryTypeDevice || pa.type == cudaMemoryTypeManaged)) f->device = pa.device;
+    else cudaGetLastError();
     *out = f; return RT_OK;
 }
 rt_status rt_film_destroy(rt_film* f) { if (!f) return RT_OK; if (f->owned && f->d) cudaFree(f->d); delete f; return RT_OK; }
 rt_status rt_film_clear(rt_film* f) {
     if (!f) { set_error("rt_film_clear: null film"); return RT_ERR_INVALID; }
-    CK(cudaMemset(f->d, 0, (size_t)f->w * f->h * 4 * sizeof(double))); return RT_OK;
+    CK(cudaSetDevice(f->device));
+    CK(cudaMemset(f->d, 0, (size_t)f->w * f->h * 4 * sizeof(double)));
+    CK(cudaStreamSynchronize(cudaStreamLegacy));          // ordered before any later rt_render (see rt_film_create)
+    return RT_OK;
 }
 rt_status rt_film_read(rt_film* f, double* host) {
     if (!f || !host) { set_error("rt_film_read: null argument"); return RT_ERR_INVALID; }
@@ -486,6 +513,7 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
     if (fd->width != film->w || fd->height != film->h) { set_error("rt_render: film size mismatch"); return RT_ERR_INVALID; }
     if (fd->x1 > fd->width || fd->y1 > fd->height || fd->x0 > fd->x1 || fd->y0 > fd->y1 || fd->sample_end < fd->sample_begin) { set_error("rt_render: bad window / sample range"); return RT_ERR_INVALID; }
     if (integ->max_depth > 0xfff0u) { set_error("rt_render: max_depth too large"); return RT_ERR_INVALID; }
+    if (film->device != s->device) { set_error("rt_render: the film lives on another device than the scene"); return RT_ERR_INVALID; }
     CK(cudaSetDevice(s->device));
     Wavefront* wp = get_wavefront(*s);
     if (!wp) return RT_ERR_CUDA;
@@ -515,7 +543,7 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
     if (trace && !w.dbg[0]) { cudaEventCreate(&w.dbg[0]); cudaEventCreate(&w.dbg[1]); }
     while (!done) {
         for (int k = 0; k < (trace ? 1 : 4); k++, iter++) {
-            k_prepare<<<1, 1, 0, st>>>(w.ctrl, cap);
+            k_prepare<<<1, 1, 0, st>>>(w.ctrl, cap, w.W);
             if (k == 0) cudaMemcpyAsync(w.h_ctrl, w.ctrl, sizeof(Ctrl), cudaMemcpyDeviceToHost, st);
             cudaEventRecord(ev(w, n_ev + 0), st);
             k_generate<<<g256, 256, 0, st>>>(w.ctrl, rp, w.set[cur], film->d);
@@ -536,7 +564,7 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
             }
             if (s->d.has_infinite) k_shade_miss<<<g128, 128, 0, st>>>(w.ctrl, s->d, rp, w.set[cur], w.bin_idx, film->d);
             cudaEventRecord(ev(w, n_ev + 3), st);
-            k_connect<<<gtrace, 128, 0, st>>>(w.ctrl, s->d, w.shadow, w.probe, film->d);
+            k_connect<<<gtrace, 128, 0, st>>>(w.ctrl, s->d, w.shadow, w.probe, film->d, w.W);
             cudaEventRecord(ev(w, n_ev + 4), st);
             n_ev += 5;
             cur ^= 1;
@@ -557,10 +585,11 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
             fprintf(stderr, "\n");
         }
         if (w.h_ctrl->n_tot == 0) done = true;       // snapshot taken right after a prepare: nothing in flight, nothing left to generate
+        if (w.h_ctrl->overflow) done = true;          // a queue append was dropped: the film is already incomplete, stop here (RT_ERR_STATE below)
         if (s->cancel.load()) { result = RT_ERR_CANCELLED; set_error("rt_render: cancelled"); done = true; }
         if (n_ev > 200000) n_ev = 2;                  // very long renders: stop growing the event pool (timing breakdown becomes partial)
     }
-    k_prepare<<<1, 1, 0, st>>>(w.ctrl, cap);         // account the last iteration
+    k_prepare<<<1, 1, 0, st>>>(w.ctrl, cap, w.W);         // account the last iteration
     CK(cudaMemcpyAsync(w.h_ctrl, w.ctrl, sizeof(Ctrl), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     // camera samples actually generated: all of them unless cancelled (the closing k_prepare claims n_new more that never run)

@@ -78,6 +78,7 @@ constexpr double WORLD_RADIUS = 10000.0;   // light.rs:636
 // everything the kernels read; all pointers are device pointers
 struct DScene {
     const DNodeT* nodes; const DSlot* slots; const DPrim* prims; const DMesh* meshes;
+    const float* tri32;                       // 48 B per leaf slot: the f32 copy the prefilter reads (traverse.cuh:tri_prefilter): v0.xyz v1.x | v1.yz v2.xy | v2.z, prim, kind, pmax
     const double* points; const double* normals; const double* uvs; const uint32_t* tri_index;
     const double* shapes; const DXform* xforms;
     const rt_texture* textures; const rt_material* materials; const DLight* lights;
@@ -102,6 +103,6 @@ void set_error(const std::string& msg);
 // leaf-ordered primitive permutation.  max 4 prims per leaf.
 struct BuiltBvh { std::vector<DNodeT> nodes; std::vector<uint32_t> order; int max_stack = 0; };
 constexpr int TRAVERSAL_STACK = 64;         // per-thread stack entries of the traversal kernels (traverse.cuh)
-void build_bvh(const std::vector<Box64>& boxes, BuiltBvh& out, int threads);
+rt_status build_bvh(const std::vector<Box64>& boxes, BuiltBvh& out, int threads);
 
 }  // namespace rt

@@ -3,6 +3,7 @@
 #include <atomic>
 #include "rt_internal.h"
 
+namespace rt { constexpr uint32_t N_BATCH_COUNTERS = 256; }
 struct rt_scene {
     // host tables (mirror of `Objects`, reference geometry.rs:13-21)
     std::vector<rt::HostMesh> meshes;
@@ -19,7 +20,8 @@ struct rt_scene {
     bool committed = false;
     int device = 0;
     rt::DScene d{};                          // device pointers
-    uint32_t* d_counter = nullptr;           // device work counter of the persistent batch kernels
+    uint32_t* d_counter = nullptr;           // device work counters of the persistent batch kernels (ring of N_BATCH_COUNTERS)
+    std::atomic<uint32_t> counter_next{0};   // next ring slot: concurrent rt_closest_device calls on different streams get different counters
     std::vector<void*> allocations;          // every cudaMalloc of this scene
     uint64_t bytes_nodes = 0, bytes_slots = 0, bytes_tables = 0;
     uint32_t build_mode = 0;                 // RT_BUILD_*
@@ -58,4 +60,5 @@ rt_status build_host_image(const rt_scene& s, HostImage& img, bool device_build)
 rt_status upload_scene(rt_scene& s, HostImage& img);         // device.cu
 void free_scene_device(rt_scene& s);                          // device.cu
 void free_wavefront(rt_scene& s);                             // render.cu
+void render_prefilter_stats(unsigned long long out[4]);       // render.cu (RT_PREFILTER_CHECK builds)
 }

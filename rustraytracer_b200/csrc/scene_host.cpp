@@ -9,6 +9,7 @@
 #include <mutex>
 #include <thread>
 #include "scene.h"
+#include "camera_host.h"
 
 namespace rt {
 
@@ -234,7 +235,9 @@ rt_status build_host_image(const rt_scene& s, HostImage& img, bool device_build)
     BuiltBvh bvh;
     if (!img.device_build) {
         auto t0 = std::chrono::steady_clock::now();
-        build_bvh(boxes, bvh, threads);
+        rt_status bst = build_bvh(boxes, bvh, threads);
+        if (bst != RT_OK) return bst;
+        if (bvh.order.size() != n) { set_error("commit: BVH build returned an incomplete primitive order"); return RT_ERR_INVALID; }
         img.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
         img.max_stack = bvh.max_stack;
         if (bvh.max_stack > TRAVERSAL_STACK) { set_error("commit: BVH needs a deeper traversal stack than the kernels have (" + std::to_string(bvh.max_stack) + " > " + std::to_string(TRAVERSAL_STACK) + ")"); return RT_ERR_INVALID; }
@@ -340,21 +343,7 @@ uint32_t rt_round_spp(uint32_t spp) { uint32_t p = 1; while (p < spp) p <<= 1; r
 rt_status rt_camera_look_at(const double from[3], const double to[3], const double up[3], double aspect, double vfov,
                             double aperture, double focus, double t0, double t1, rt_camera* out) {
     if (!from || !to || !up || !out) { set_error("rt_camera_look_at: null argument"); return RT_ERR_INVALID; }
-    auto normalize = [](double* v) { double n = std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]); v[0] /= n; v[1] /= n; v[2] /= n; };
-    auto cross = [](const double* a, const double* b, double* c) { c[0] = a[1] * b[2] - a[2] * b[1]; c[1] = a[2] * b[0] - a[0] * b[2]; c[2] = a[0] * b[1] - a[1] * b[0]; };
-    double w[3] = {to[0] - from[0], to[1] - from[1], to[2] - from[2]}; normalize(w);
-    double u[3]; cross(up, w, u); normalize(u); for (int k = 0; k < 3; k++) u[k] = -u[k];
-    double v[3]; cross(w, u, v); normalize(v); for (int k = 0; k < 3; k++) v[k] = -v[k];
-    double theta = vfov * PI / 180., h = std::tan(theta / 2.);
-    double vh = 2. * h, vw = vh * aspect;
-    for (int k = 0; k < 3; k++) {
-        out->origin[k] = from[k];
-        out->horizontal_offset[k] = u[k] * (vw * focus);
-        out->vertical_offset[k] = v[k] * (vh * focus);
-        out->upper_left_corner[k] = from[k] - out->horizontal_offset[k] * 0.5 + out->vertical_offset[k] * 0.5 + w[k] * focus;
-        out->u[k] = u[k]; out->v[k] = v[k]; out->w[k] = w[k];
-    }
-    out->lens_radius = aperture / 2.; out->t0 = t0; out->t1 = t1;
+    camera_look_at(from, to, up, aspect, vfov, aperture, focus, t0, t1, out);
     return RT_OK;
 }
 

@@ -64,6 +64,80 @@ __device__ __forceinline__ bool box_test(const RayF& r, float minx, float maxx, 
 __device__ __forceinline__ float f32_up(double x) { return __double2float_ru(x); }
 __device__ __forceinline__ float f32_down(double x) { return __double2float_rd(x); }
 
+
+// ------------------------------------------------------------------------------------------------------------
+// Conservative f32 prefilter in front of the exact f64 triangle test (SURVEY.md §7 "hard parts").
+//
+// Every candidate slot used to go straight to the reference's f64 watertight test (geom.cuh:tri_test): five 16-byte loads and ~60 f64
+// operations, of which nine in ten end in "mixed edge-function signs -> miss".  The prefilter evaluates the SAME three edge functions
+// in f32 on a 48-byte f32 copy of the triangle (DScene::tri32, leaf order) together with a rigorous bound B on |e_f32 - e_exact|, and
+// lets a slot skip the f64 test only when the f64 test is certain to reject it — or certain to return a hit that cannot matter:
+//   (1) min(e0,e1,e2) < -B  and  max(e0,e1,e2) > +B   =>  the f64 edge functions have mixed signs (hittable.rs:336)          -> miss
+//   (2) every sheared z_k * (1/d[kz]) lies beyond the culling interval's far end, or all lie behind the origin: an accepted t is a
+//       convex combination of those three values (barycentric weights e_i/det >= 0), so t > best-so-far / t_limit, or t < 0.
+// Error budget, u = 2^-24 (f32 unit roundoff), coordinates |p| <= pmax (stored per triangle, rounded up), |o| <= omax:
+//   a   = fl(fl(p) - fl(o))                         |a - a*|   <= u(|p| + |o| + |a|)            <= D0 := 2u(pmax + omax)
+//   x   = fma(Sx, az, ax), |Sx*| <= 1 (kz = argmax|d|), Sx = fl(Sx*)
+//                                                   |x - x*|   <= 2 D0 + u|az| + u|x| (+ O(u D0))  <= E := 2 D0 + u(zm + 2 xm)
+//   e0  = fma(x1, y2, -fl(y1 x2))                   |e0 - e0*| <= 4 xm E + 2 E^2 + 3u xm^2     =: B0      (xm = max|x_k|,|y_k|, zm = max|az_k|)
+//   z_k = fl(az_k Sz), Sz = fl(1/d[kz])             |z - z*|   <= |Sz| D0 + 2u|z|              =: Ez0
+// and the tests use B = 2 B0, Ez = 2 Ez0.  The f64 test's own rounding (2^-53 of the same magnitudes) disappears in that factor.  Any
+// NaN / inf makes a comparison false, i.e. "go on to the exact test".  RT_PREFILTER_CHECK builds count — on the device, over every
+// slot test of a run — the cases where the prefilter would have skipped a hit the traversal then used (rt_debug_prefilter_violations()).
+#ifndef RT_PREFILTER
+#define RT_PREFILTER 1
+#endif
+#ifndef RT_PREFILTER_CHECK
+#define RT_PREFILTER_CHECK 0
+#endif
+struct RayP { float ox, oy, oz, shx, shy, shz, eo; int kz; };     // f32 origin, shear (sx, sy, 1/d[kz]) and 2u * max|o|
+constexpr float F32_U = 5.9604645e-8f;                            // 2^-24
+__device__ __forceinline__ RayP make_rayp(const RayX& rx) {
+    RayP r;
+    r.ox = (float)rx.o.x; r.oy = (float)rx.o.y; r.oz = (float)rx.o.z;
+    r.shx = (float)rx.sx; r.shy = (float)rx.sy; r.shz = (float)comp(rx.inv, rx.kz);
+    r.eo = 2.f * F32_U * 1.0000002f * fmaxf(fabsf(r.ox), fmaxf(fabsf(r.oy), fabsf(r.oz)));
+    r.kz = rx.kz;
+    return r;
+}
+// true = run the exact test; false = the exact test cannot produce a hit that matters for a culling interval ending at `ftmax`
+__device__ __forceinline__ bool tri_prefilter(const RayP& r, const float4 w0, const float4 w1, const float4 w2, float ftmax) {
+    const float d0 = __fmaf_rn(2.f * F32_U, w2.w, r.eo);                       // D0 = 2u(pmax + omax)
+    float ax0 = w0.x - r.ox, ay0 = w0.y - r.oy, az0 = w0.z - r.oz;
+    float ax1 = w0.w - r.ox, ay1 = w1.x - r.oy, az1 = w1.y - r.oz;
+    float ax2 = w1.z - r.ox, ay2 = w1.w - r.oy, az2 = w2.x - r.oz;
+    // permute to (kx, ky, kz) = ((kz+1)%3, (kz+2)%3, kz) as geom.cuh:permute does
+    if (r.kz == 0) { float t; t = ax0; ax0 = ay0; ay0 = az0; az0 = t; t = ax1; ax1 = ay1; ay1 = az1; az1 = t; t = ax2; ax2 = ay2; ay2 = az2; az2 = t; }
+    else if (r.kz == 1) { float t; t = ay0; ay0 = ax0; ax0 = az0; az0 = t; t = ay1; ay1 = ax1; ax1 = az1; az1 = t; t = ay2; ay2 = ax2; ax2 = az2; az2 = t; }
+    const float x0 = __fmaf_rn(r.shx, az0, ax0), y0 = __fmaf_rn(r.shy, az0, ay0);
+    const float x1 = __fmaf_rn(r.shx, az1, ax1), y1 = __fmaf_rn(r.shy, az1, ay1);
+    const float x2 = __fmaf_rn(r.shx, az2, ax2), y2 = __fmaf_rn(r.shy, az2, ay2);
+    const float e0 = __fmaf_rn(x1, y2, -(y1 * x2)), e1 = __fmaf_rn(x2, y0, -(y2 * x0)), e2 = __fmaf_rn(x0, y1, -(y0 * x1));
+    const float zm = fmaxf(fabsf(az0), fmaxf(fabsf(az1), fabsf(az2)));
+    const float xm = fmaxf(fmaxf(fmaxf(fabsf(x0), fabsf(y0)), fmaxf(fabsf(x1), fabsf(y1))), fmaxf(fabsf(x2), fabsf(y2)));
+    const float E = __fmaf_rn(F32_U, zm + 2.f * xm, 2.f * d0);
+    const float B = 2.f * (4.f * xm * E + 2.f * E * E + 3.f * F32_U * xm * xm);
+    const float emin = fminf(e0, fminf(e1, e2)), emax = fmaxf(e0, fmaxf(e1, e2));
+    if (emin < -B && emax > B) return false;
+    const float z0 = az0 * r.shz, z1 = az1 * r.shz, z2 = az2 * r.shz;
+    const float zlo = fminf(z0, fminf(z1, z2)), zhi = fmaxf(z0, fmaxf(z1, z2));
+    const float Ez = 2.f * (fabsf(r.shz) * d0 + 2.f * F32_U * fmaxf(fabsf(zlo), fabsf(zhi)));
+    if (zlo - Ez > ftmax || zhi + Ez < 0.f) return false;
+    return true;
+}
+#if RT_PREFILTER_CHECK
+static __device__ unsigned long long g_prefilter_stats[4];      // [0] triangle slot tests, [1] skipped by the prefilter, [2] exact hits, [3] VIOLATIONS: skipped, yet the exact hit would have been used
+#endif
+// host side: adds this translation unit's counters (every TU that includes this header has its own copy) to out[4]
+static inline void prefilter_stats_add(unsigned long long out[4]) {
+#if RT_PREFILTER_CHECK
+    unsigned long long h[4] = {0, 0, 0, 0};
+    if (cudaMemcpyFromSymbol(h, g_prefilter_stats, sizeof(h)) == cudaSuccess) for (int k = 0; k < 4; k++) out[k] += h[k];
+#else
+    (void)out;
+#endif
+}
+
 struct Hit { double t; uint32_t prim; };
 
 constexpr int STACK = TRAVERSAL_STACK;
@@ -123,30 +197,90 @@ __device__ __forceinline__ int32_t node4_any(const DScene& sc, int32_t cur, cons
 #endif
 
 
-// Candidate primitive in leaf slot `s`: the reference's exact accept test.  Returns true with t.
-__device__ __forceinline__ bool slot_test(const DScene& sc, const DSlot* __restrict__ slots, uint32_t s, const RayX& rx, double tmin, double tmax,
-                                          double& t, uint32_t& prim) {
-    const double2* q = reinterpret_cast<const double2*>(slots + s);
+// Candidate primitive in leaf slot `s`: the f32 prefilter, then the reference's exact accept test.  Returns true with t.
+// `ftmax` is the far end of the caller's CULLING interval (>= best-so-far t / the shadow ray's t_limit): a hit beyond it cannot matter.
+// skipped (RT_PREFILTER_CHECK only): the prefilter said "skip" — the exact test was run all the same so that the caller can audit the decision.
+// The exact test as a CALL (RT_EXACT_CALL): with the prefilter in front of it, it runs for one or two slots per ray; as a function of its own it
+// keeps its ~60 f64 temporaries out of the register allocation of the traversal loop.
+#ifndef RT_EXACT_CALL
+#define RT_EXACT_CALL 1
+#endif
+#if RT_EXACT_CALL
+#define RT_EXACT_FN static __device__ __noinline__
+#else
+#define RT_EXACT_FN __device__ __forceinline__
+#endif
+RT_EXACT_FN bool tri_exact(const DSlot* __restrict__ slot, D3 o, D3 d, double tmin, double tmax, double& t) {
+    const double2* q = reinterpret_cast<const double2*>(slot);
+    const double2 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3), q4 = __ldg(q + 4);
+    const D3 p0 = mk3(q0.x, q0.y, q1.x), p1 = mk3(q1.y, q2.x, q2.y), p2 = mk3(q3.x, q3.y, q4.x);
+    const RayX rx = make_rayx(o, d);
+    double b0, b1, b2;
+    if (!tri_test(rx, p0, p1, p2, tmax, t, b0, b1, b2)) return false;
+    return tri_leaf_box_inv(p0, p1, p2, rx.o, rx.inv, tmin, tmax);
+}
+// The f64 per-ray constants of the exact test (shear, 1/d: five f64 divisions) are rebuilt from (o, d) for the few slots that reach it instead of
+// living in registers for the whole walk: bitwise the same values, ten registers less in the persistent kernels.
+// `fetch(o, d)` hands out the ray's f64 origin and direction when — and only when — a slot reaches the exact test: the persistent kernels do not keep
+// them in registers either but read them back from the queue the ray came from (Job::ray).
+template <class Fetch>
+__device__ __forceinline__ bool slot_test(const DScene& sc, uint32_t s, const Fetch& fetch, const RayP& rp, double tmin, double tmax, float ftmax,
+                                          double& t, uint32_t& prim, bool* skipped = nullptr) {
+#if RT_PREFILTER
+    const float4* w = reinterpret_cast<const float4*>(sc.tri32) + 3 * (size_t)s;
+    const float4 w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2);
+    prim = __float_as_uint(w2.y);
+    const uint32_t kind = __float_as_uint(w2.z);
+    if (kind == 0) {
+        const bool pass = tri_prefilter(rp, w0, w1, w2, ftmax);
+#if RT_PREFILTER_CHECK
+        atomicAdd(&g_prefilter_stats[0], 1ull);
+        if (!pass) atomicAdd(&g_prefilter_stats[1], 1ull);
+        if (skipped) *skipped = !pass;
+#else
+        if (!pass) return false;
+#endif
+        D3 o, d; fetch(o, d);
+        if (!tri_exact(sc.slots + s, o, d, tmin, tmax, t)) return false;
+#if RT_PREFILTER_CHECK
+        atomicAdd(&g_prefilter_stats[2], 1ull);
+#endif
+        return true;
+    }
+    if (kind == 2) return false;     // triangle the reference can never hit (degenerate uv frame ∧ zero normal, hittable.rs:373-378)
+#else
+    const double2* q = reinterpret_cast<const double2*>(sc.slots + s);
     double2 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3), q4 = __ldg(q + 4);
     uint2 tag = *reinterpret_cast<uint2*>(&q4.y);
     prim = tag.x;
+    D3 o, d; fetch(o, d);
     if (tag.y == 0) {
         D3 p0 = mk3(q0.x, q0.y, q1.x), p1 = mk3(q1.y, q2.x, q2.y), p2 = mk3(q3.x, q3.y, q4.x);
+        const RayX rx = make_rayx(o, d);
         double b0, b1, b2;
         if (!tri_test(rx, p0, p1, p2, tmax, t, b0, b1, b2)) return false;
         return tri_leaf_box_inv(p0, p1, p2, rx.o, rx.inv, tmin, tmax);
     }
     if (tag.y == 2) return false;    // triangle the reference can never hit (degenerate uv frame ∧ zero normal, hittable.rs:373-378)
+#endif
     DPrim pr = sc.prims[prim];
-    return shape_test(sc, pr, rx.o, rx.d, tmin, tmax, true, t, &rx.inv);
+#if RT_PREFILTER
+    D3 o, d; fetch(o, d);
+#endif
+    return shape_test(sc, pr, o, d, tmin, tmax, true, t);
 }
+#if RT_PREFILTER_CHECK
+#define RT_AUDIT(skipped) do { if (skipped) atomicAdd(&g_prefilter_stats[3], 1ull); } while (0)
+#else
+#define RT_AUDIT(skipped) do { } while (0)
+#endif
 
 // closest hit in the reference's sense over [tmin, tmax]
 __device__ __forceinline__ Hit trace_closest(const DScene& sc, D3 o, D3 d, double tmin, double tmax) {
     Hit best; best.t = 0.; best.prim = RT_NONE;
     if (sc.n_nodes == 0) return best;
-    RayX rx = make_rayx(o, d);
     RayF rf = make_rayf(o, d);
+    RayP rp = make_rayp(make_rayx(o, d));
     float ftmin = f32_down(tmin); ftmin = ftmin - fabsf(ftmin) * 4.8e-7f;
     float ftmax = f32_up(fmin(tmax, 3.0e38));
     int32_t stack[STACK]; int sp = 0;
@@ -180,9 +314,10 @@ __device__ __forceinline__ Hit trace_closest(const DScene& sc, D3 o, D3 d, doubl
         // leaf
         uint32_t v = (uint32_t)~cur, first = v >> 2, count = (v & 3u) + 1u;
         for (uint32_t s = first; s < first + count; s++) {
-            double t; uint32_t prim;
-            if (slot_test(sc, sc.slots, s, rx, tmin, tmax, t, prim)) {
+            double t; uint32_t prim; bool skipped = false;
+            if (slot_test(sc, s, [&](D3& fo, D3& fd) { fo = o; fd = d; }, rp, tmin, tmax, ftmax, t, prim, &skipped)) {
                 if (best.prim == RT_NONE || t < best.t || (t == best.t && prim < best.prim)) {
+                    RT_AUDIT(skipped);
                     best.t = t; best.prim = prim;
                     // Triangles ignore tmin (only t < 1e-4 is rejected, hittable.rs:360), so the best t can lie BELOW tmin; a closer
                     // primitive then still has a box that straddles tmin (its f64 leaf-box test must pass), which is why the
@@ -201,8 +336,8 @@ __device__ __forceinline__ Hit trace_closest(const DScene& sc, D3 o, D3 d, doubl
 // is visible iff the closest hit is the light primitive itself.
 __device__ __forceinline__ bool trace_any(const DScene& sc, D3 o, D3 d, double tmin, double tmax, double t_limit, uint32_t skip) {
     if (sc.n_nodes == 0) return false;
-    RayX rx = make_rayx(o, d);
     RayF rf = make_rayf(o, d);
+    RayP rp = make_rayp(make_rayx(o, d));
     float ftmin = f32_down(tmin); ftmin = ftmin - fabsf(ftmin) * 4.8e-7f;
     float ftmax = f32_up(fmin(fmin(tmax, t_limit), 3.0e38));
     int32_t stack[STACK]; int sp = 0;
@@ -231,10 +366,10 @@ __device__ __forceinline__ bool trace_any(const DScene& sc, D3 o, D3 d, double t
         if (cur == SENTINEL) break;
         uint32_t v = (uint32_t)~cur, first = v >> 2, count = (v & 3u) + 1u;
         for (uint32_t s = first; s < first + count; s++) {
-            double t; uint32_t prim;
-            if (slot_test(sc, sc.slots, s, rx, tmin, tmax, t, prim) && prim != skip) {
+            double t; uint32_t prim; bool skipped = false;
+            if (slot_test(sc, s, [&](D3& fo, D3& fd) { fo = o; fd = d; }, rp, tmin, tmax, ftmax, t, prim, &skipped) && prim != skip) {
                 // the closest-hit rule keeps the smaller primitive index on an exact tie
-                if (t < t_limit || (t == t_limit && prim < skip)) return true;
+                if (t < t_limit || (t == t_limit && prim < skip)) { RT_AUDIT(skipped); return true; }
             }
         }
         cur = stack[--sp];
@@ -273,19 +408,21 @@ __device__ __forceinline__ bool unoccluded(const DScene& sc, D3 p0, D3 p1, uint3
 // resumable traversal state; a warp keeps stepping its live rays and, as soon as fewer than REFILL lanes are live,
 // the idle lanes fetch fresh rays from a global work counter (one atomic per warp per refill) — the scheme of
 // Aila & Laine, "Understanding the efficiency of ray traversal on GPUs", restated for this BVH and the f64 leaf tests.
-// A Job supplies: load(i, TState&) -> bool (false = nothing to trace, the job already finished ray i) and
-// finish(i, const TState&).
+// A Job supplies: load(i, TState&) -> bool (false = nothing to trace, the job already finished ray i), finish(i, const TState&),
+// ray(i, o, d) (the f64 ray of item i again, for the exact test) and tmin(state) / tmax(state).
+// The ray's f64 interval [tmin, tmax] is not part of the state: it is a property of the job (extend: (SMALL, INF); connect: (0, INF) for shadow
+// rays, (SMALL, INF) for probes; batch entry points: the caller's) and is asked for with job.tmin(state) / job.tmax(state) where the exact test needs it.
 struct TState {
-    RayX rx; RayF rf;
+    RayF rf; RayP rp;
     float ftmin, ftmax;
-    double tmin, tmax, t_limit;
+    double t_limit;
     uint32_t skip; bool any, occluded;
     Hit best;
     int32_t cur; int sp;
 };
 __device__ __forceinline__ void tstate_init(TState& s, int32_t* stack, D3 o, D3 d, double tmin, double tmax, bool any, double t_limit, uint32_t skip) {
-    s.rx = make_rayx(o, d); s.rf = make_rayf(o, d);
-    s.tmin = tmin; s.tmax = tmax; s.any = any; s.t_limit = t_limit; s.skip = skip; s.occluded = false;
+    s.rf = make_rayf(o, d); s.rp = make_rayp(make_rayx(o, d));
+    s.any = any; s.t_limit = t_limit; s.skip = skip; s.occluded = false;
     s.ftmin = f32_down(tmin); s.ftmin = s.ftmin - fabsf(s.ftmin) * 4.8e-7f;
     s.ftmax = f32_up(fmin(any ? fmin(tmax, t_limit) : tmax, 3.0e38));
     s.best.t = 0.; s.best.prim = RT_NONE;
@@ -314,15 +451,17 @@ __device__ __forceinline__ void node_step(const DScene& sc, TState& s, int32_t* 
 #endif
 }
 // one leaf: the reference-exact test of its 1..4 slots, then pop
-__device__ __forceinline__ void leaf_step(const DScene& sc, TState& s, int32_t* stack) {
+template <class Fetch>
+__device__ __forceinline__ void leaf_step(const DScene& sc, TState& s, int32_t* stack, double tmin, double tmax, const Fetch& fetch) {
     uint32_t v = (uint32_t)~s.cur, first = v >> 2, count = (v & 3u) + 1u;
     for (uint32_t k = first; k < first + count; k++) {
-        double t; uint32_t prim;
-        if (!slot_test(sc, sc.slots, k, s.rx, s.tmin, s.tmax, t, prim)) continue;
+        double t; uint32_t prim; bool skipped = false;
+        if (!slot_test(sc, k, fetch, s.rp, tmin, tmax, s.ftmax, t, prim, &skipped)) continue;
         if (s.any) {
             // the closest-hit rule keeps the smaller primitive index on an exact tie
-            if (prim != s.skip && (t < s.t_limit || (t == s.t_limit && prim < s.skip))) { s.occluded = true; s.cur = SENTINEL; return; }
+            if (prim != s.skip && (t < s.t_limit || (t == s.t_limit && prim < s.skip))) { RT_AUDIT(skipped); s.occluded = true; s.cur = SENTINEL; return; }
         } else if (s.best.prim == RT_NONE || t < s.best.t || (t == s.best.t && prim < s.best.prim)) {
+            RT_AUDIT(skipped);
             s.best.t = t; s.best.prim = prim;
             s.ftmax = fmaxf(fminf(s.ftmax, f32_up(t)), s.ftmin);     // see trace_closest: best t may lie below tmin for triangles
         }
@@ -330,80 +469,9 @@ __device__ __forceinline__ void leaf_step(const DScene& sc, TState& s, int32_t* 
     s.cur = stack[--s.sp];
 }
 
-// Leaf phase, compacted over the warp.  After a node phase a warp holds a handful of lanes that sit on a leaf of 1..4 slots and
-// many lanes that do not; running leaf_step per lane leaves most of the warp idle for the most expensive code of the traversal
-// (the f64 reference-order tests; ncu: 7.4 of 32 lanes active in it).  Here the warp's (ray, slot) candidate pairs are
-// enumerated with a prefix sum and dealt out one per lane, whoever owns the ray: the tester lane reads the owner's ray from
-// shared memory (written once when the ray was fetched — it never changes during the walk), runs the exact test and posts
-// (t, prim); the owner then folds the results of its own slots.  The fold is a min over (t, prim) for closest-hit rays and an
-// "any" for shadow rays, so the order of the slots does not matter and the outcome is identical to leaf_step's.
-// MEASURED (dragon, 1024^2, 64 spp): extend 32.9 -> 34.3 ms, connect 21.5 -> 22.0 ms, i.e. slower, so it is OFF by default.  ncu shows why: the
-// lanes-per-instruction of the exact tests stays at 7.9 with compaction — the idle lanes come from the early-outs INSIDE the test (edge-function
-// reject, then det, then the leaf box), not from the 1..4 slot loop — while the 13 KB of shared memory per block costs 5 points of L1 hit rate.
-#ifndef RT_LEAF_COMPACT
-#define RT_LEAF_COMPACT 0
-#endif
 constexpr int TRACE_BLOCK = 128;            // block size of every persistent traversal kernel
-struct LeafShared {
-    double ray[13][TRACE_BLOCK];            // o.xyz, d.xyz, shear sx sy, 1/d xyz, tmin, tmax of the ray each thread owns
-    double res_t[TRACE_BLOCK];
-    uint32_t res_prim[TRACE_BLOCK];
-    int32_t kz[TRACE_BLOCK];
-    uint8_t pair[TRACE_BLOCK];              // per warp: pair p of this round -> owner lane | slot-in-leaf << 5
-};
-__device__ __forceinline__ void leaf_shared_store(LeafShared& sh, const TState& s) {
-    const int i = threadIdx.x;
-    sh.ray[0][i] = s.rx.o.x; sh.ray[1][i] = s.rx.o.y; sh.ray[2][i] = s.rx.o.z;
-    sh.ray[3][i] = s.rx.d.x; sh.ray[4][i] = s.rx.d.y; sh.ray[5][i] = s.rx.d.z;
-    sh.ray[6][i] = s.rx.sx; sh.ray[7][i] = s.rx.sy; sh.ray[8][i] = s.rx.inv.x; sh.ray[11][i] = s.rx.inv.y; sh.ray[12][i] = s.rx.inv.z;
-    sh.ray[9][i] = s.tmin; sh.ray[10][i] = s.tmax; sh.kz[i] = s.rx.kz;
-}
-__device__ __forceinline__ void leaf_phase_compact(const DScene& sc, LeafShared& sh, TState& s, int32_t* stack, bool active) {
-    const unsigned FULL = 0xffffffffu;
-    const int tid = threadIdx.x, lane = tid & 31, wbase = tid & ~31;
-    const bool at_leaf = active && s.cur < 0;
-    const uint32_t v = (uint32_t)~s.cur, first = v >> 2;
-    const int cnt = at_leaf ? (int)(v & 3u) + 1 : 0;
-    // prefix sum of the slot counts from three ballots (count - 1 has two bits)
-    const unsigned ml = __ballot_sync(FULL, at_leaf), b0 = __ballot_sync(FULL, at_leaf && (v & 1u)), b1 = __ballot_sync(FULL, at_leaf && (v & 2u));
-    const unsigned lt = (1u << lane) - 1u;
-    const int excl = __popc(ml & lt) + __popc(b0 & lt) + 2 * __popc(b1 & lt);
-    const int total = min(32, __popc(ml) + __popc(b0) + 2 * __popc(b1));
-    // one round of at most 32 pairs; a leaf that does not fit keeps its remaining slots for the next leaf phase
-    const int take = min(cnt, max(0, 32 - excl));
-    for (int k = 0; k < take; k++) sh.pair[wbase + excl + k] = (uint8_t)(lane | (k << 5));
-    __syncwarp();
-    const bool has = lane < total;
-    const int code = has ? sh.pair[tid] : lane;
-    const int owner = wbase + (code & 31);
-    const uint32_t slot = __shfl_sync(FULL, first, code & 31) + (uint32_t)(code >> 5);
-    double t = 0.; uint32_t prim = RT_NONE;
-    if (has) {
-        RayX rx;
-        rx.o = mk3(sh.ray[0][owner], sh.ray[1][owner], sh.ray[2][owner]); rx.d = mk3(sh.ray[3][owner], sh.ray[4][owner], sh.ray[5][owner]);
-        rx.sx = sh.ray[6][owner]; rx.sy = sh.ray[7][owner]; rx.inv = mk3(sh.ray[8][owner], sh.ray[11][owner], sh.ray[12][owner]); rx.kz = sh.kz[owner];
-        uint32_t p;
-        if (slot_test(sc, sc.slots, slot, rx, sh.ray[9][owner], sh.ray[10][owner], t, p)) prim = p;
-    }
-    sh.res_t[tid] = t; sh.res_prim[tid] = prim;
-    __syncwarp();
-    for (int k = 0; k < take; k++) {
-        const uint32_t hp = sh.res_prim[wbase + excl + k];
-        if (hp == RT_NONE) continue;
-        const double ht = sh.res_t[wbase + excl + k];
-        if (s.any) {
-            if (hp != s.skip && (ht < s.t_limit || (ht == s.t_limit && hp < s.skip))) s.occluded = true;
-        } else if (s.best.prim == RT_NONE || ht < s.best.t || (ht == s.best.t && hp < s.best.prim)) {
-            s.best.t = ht; s.best.prim = hp;
-            s.ftmax = fmaxf(fminf(s.ftmax, f32_up(ht)), s.ftmin);
-        }
-    }
-    if (at_leaf) {
-        if (s.any && s.occluded) s.cur = SENTINEL;
-        else if (take == cnt) s.cur = stack[--s.sp];
-        else s.cur = (int32_t)~(((first + (uint32_t)take) << 2) | (uint32_t)(cnt - take - 1));
-    }
-}
+// (A leaf phase compacted over the warp — the (ray, slot) pairs of a warp dealt out one per lane through shared memory — was built and measured in
+// round 1: extend 32.9 -> 34.3 ms, i.e. slower; the idle lanes of the exact test come from its early-outs, not from the 1..4 slot loop.  Removed.)
 
 #ifndef RT_REFILL
 #define RT_REFILL 16        // refetch when fewer than this many lanes of the warp hold a live ray (BVH4, dragon 64 spp: 16 / 20 / 24 -> extend 31.6 / 31.7 / 32.5 ms)
@@ -421,9 +489,6 @@ __device__ __forceinline__ void trace_jobs(const DScene& sc, Job& job, uint32_t 
     TState st; st.cur = SENTINEL; st.sp = 0;
     bool active = false, exhausted = false;
     uint32_t idx = 0;
-#if RT_LEAF_COMPACT
-    __shared__ LeafShared lsh;
-#endif
     if (sc.n_nodes == 0) {      // empty scene: every ray misses
         for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
             if (job.load(i, st, stack)) { st.best.prim = RT_NONE; st.occluded = false; job.finish(i, st); }
@@ -440,9 +505,6 @@ __device__ __forceinline__ void trace_jobs(const DScene& sc, Job& job, uint32_t 
             if (!active) {
                 idx = base + __popc(idle & ((1u << lane) - 1u));
                 if (idx < n) active = job.load(idx, st, stack);
-#if RT_LEAF_COMPACT
-                if (active) leaf_shared_store(lsh, st);
-#endif
             }
             if (base + __popc(idle) >= n) exhausted = true;
         }
@@ -458,11 +520,7 @@ __device__ __forceinline__ void trace_jobs(const DScene& sc, Job& job, uint32_t 
                 if (at_node) node_step(sc, st, stack);
             }
             // leaf phase
-#if RT_LEAF_COMPACT
-            leaf_phase_compact(sc, lsh, st, stack, active);
-#else
-            if (active && st.cur < 0) leaf_step(sc, st, stack);
-#endif
+            if (active && st.cur < 0) leaf_step(sc, st, stack, job.tmin(st), job.tmax(st), [&](D3& fo, D3& fd) { job.ray(idx, fo, fd); });
             if (active && st.cur == SENTINEL) { job.finish(idx, st); active = false; }
             unsigned act = __ballot_sync(FULL, active);
             if (act == 0u) break;

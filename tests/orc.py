@@ -31,6 +31,7 @@ def lib():
         L.orc_scene_set_materials.argtypes = [vp, u64, vp]
         L.orc_scene_set_lights.argtypes = [vp, u64, vp]
         L.orc_scene_commit.argtypes = [vp, u64]
+        L.orc_scene_build_fast_tree.argtypes = [vp, i32]
         L.orc_scene_num_primitives.argtypes = [vp]
         L.orc_scene_num_primitives.restype = u64
         L.orc_scene_prim_box.argtypes = [vp, u32, vp]
@@ -122,6 +123,10 @@ class OracleScene:
     def commit(self, bvh_seed=1):
         lib().orc_scene_commit(self.h, bvh_seed)
 
+    def build_fast_tree(self, threads=8):
+        """median-split tree built with nth_element in parallel: for the hit-set traversal (mode 3) on million-triangle soups"""
+        lib().orc_scene_build_fast_tree(self.h, threads)
+
     def num_primitives(self):
         return lib().orc_scene_num_primitives(self.h)
 
@@ -154,7 +159,7 @@ class OracleScene:
         return out
 
     def intersect(self, rays, tmin=0.001, tmax=1e308, mode=0, threads=8, want_ties=False, want_stats=False):
-        """mode 0 = reference-faithful tree, 1 = brute force (+tie sets), 2 = ordered (work counting)."""
+        """mode 0 = reference-faithful tree, 1 = brute force (+tie sets), 2 = ordered (work counting), 3 = hit set + tie set over the tree."""
         rays = np.ascontiguousarray(rays, dtype=N.ray_dtype)
         hits = np.zeros(len(rays), dtype=N.hit_dtype)
         ties = np.full((len(rays), 4), N.RT_NONE, dtype=np.uint32) if want_ties else None
