@@ -77,19 +77,30 @@ typedef struct rt_texture {
     double   frequency;    /* checkered                                                     */
 } rt_texture;
 
-/* `enum Material` (material.rs:17-73); Disney is out of scope. */
-enum { RT_MAT_MATTE = 0, RT_MAT_LIGHT = 1, RT_MAT_PLASTIC = 2, RT_MAT_GLASS = 3, RT_MAT_METAL = 4, RT_MAT_MIRROR = 5 };
+/* `enum Material` (material.rs:17-73).  Disney (material.rs:55-73, 245-394) carries 14 texture ids + `thin`: they live in an rt_disney record
+ * added with rt_scene_add_disney, and the material's tex[0] is that record's index.  A scene that holds a Disney material is shaded by the f64
+ * kernels even when RT_SHADE_F32 is asked for (up to 8 lobes per BSDF).                                                                          */
+enum { RT_MAT_MATTE = 0, RT_MAT_LIGHT = 1, RT_MAT_PLASTIC = 2, RT_MAT_GLASS = 3, RT_MAT_METAL = 4, RT_MAT_MIRROR = 5, RT_MAT_DISNEY = 6 };
 typedef struct rt_material {
     uint32_t type;
     uint32_t remap_roughness;
     /* texture ids:  Matte {k_d}            Light {texture}      Plastic {k_d,k_s}
      *               Glass {k_r,k_t}        Mirror {color}
-     *               Metal {eta,k,rough,urough,vrough}  (urough/vrough may be RT_NONE)      */
+     *               Metal {eta,k,rough,urough,vrough}  (urough/vrough may be RT_NONE)
+     *               Disney {index of its rt_disney record}                                  */
     uint32_t tex[5];
     uint32_t _pad;
     /* scalars:      Matte {sigma}   Plastic {roughness}   Glass {u_roughness,v_roughness,index} */
     double   f[3];
 } rt_material;
+
+/* Material::Disney's fields (material.rs:55-73) in declaration order, `bump_id` (never read) dropped: texture ids, and the `thin` flag */
+typedef struct rt_disney {
+    uint32_t color, metallic, eta, roughness, specular_tint, anisotropic, sheen, sheen_tint;
+    uint32_t clearcoat, clearcoat_gloss, spec_trans, scatter_distance, flatness, diff_trans;
+    uint32_t thin;
+    uint32_t _pad;
+} rt_disney;
 
 /* `enum Light` (light.rs:30-80): Diffuse (area) lights, the Infinite (environment map) light and
  * the delta lights Point / Spot / Distant (light.rs:522-582; sample_li light.rs:142-175, pdf_li = 0,
@@ -232,6 +243,8 @@ rt_status rt_scene_add_image_rgb8(rt_scene* scene, uint32_t width, uint32_t heig
 /* Perlin::new(256, scale) (perlin.rs:17-34, material.rs:628-631): perm = perm_x | perm_y | perm_z, 3 x 256 values < 256;
  * vecs = 256 unit gradient vectors (xyz).  Texture.image of an RT_TEX_PERLIN texture is the index returned here. */
 rt_status rt_scene_add_perlin(rt_scene* scene, double scale, const uint32_t perm[768], const double vecs[768], uint32_t* perlin_index_out);
+/* Material::make_disney (material.rs:480-516): the record an RT_MAT_DISNEY material points at through tex[0] */
+rt_status rt_scene_add_disney(rt_scene* scene, const rt_disney* params, uint32_t* disney_index_out);
 rt_status rt_scene_set_textures(rt_scene* scene, uint64_t n, const rt_texture* textures);
 rt_status rt_scene_set_materials(rt_scene* scene, uint64_t n, const rt_material* materials);
 rt_status rt_scene_set_lights(rt_scene* scene, uint64_t n, const rt_light* lights);
@@ -306,6 +319,29 @@ rt_status rt_render_cancel(rt_scene* scene);
 rt_status rt_get_counters(const rt_scene* scene, rt_counters* out);
 /* size of the wavefront (paths in flight, ~480 bytes of device queue state each); default 1<<24 */
 rt_status rt_set_wavefront_size(rt_scene* scene, uint32_t paths);
+
+/* ---------------------------------------------------------------- several GPUs of one box
+ * Replaces render::tile_multithread's NUM_THREADS = 6 workers + Mutex-guarded film merge (render.rs:13-159, consts.rs:8): the scene is replicated
+ * on every GPU, the sample range is split across them (the RNG is keyed by the global sample index, so the partition does not change the image)
+ * and the (r,g,b,n) films are summed in place with one ncclAllReduce(f64, sum) over NVLink.  NCCL is bound at run time (dlopen libnccl.so.2);
+ * without it these calls fail with RT_ERR_STATE.                                                                                                */
+typedef struct rt_comm rt_comm;
+/* one process, one host thread per GPU: ncclCommInitAll over `devices` */
+rt_status rt_comm_create_local(const int32_t* devices, uint32_t n, rt_comm** out);
+/* one process per GPU (torchrun / MPI): rank 0 creates the id and hands it to every rank out of band; the communicator is formed on the
+ * calling thread's current device (rt_set_device)                                                                                              */
+rt_status rt_comm_unique_id(uint8_t id_out[128]);
+rt_status rt_comm_create_rank(const uint8_t id[128], uint32_t world, uint32_t rank, rt_comm** out);
+rt_status rt_comm_destroy(rt_comm* comm);
+rt_status rt_comm_size(const rt_comm* comm, uint32_t* world_out, uint32_t* n_local_out);
+/* in-place sum over all ranks; films[i] lives on the communicator's i-th local device (n_films = 1 for a rank communicator).  Blocking. */
+rt_status rt_film_allreduce(rt_comm* comm, rt_film* const* films, uint32_t n_films);
+/* a new scene with src's tables, committed on `device` (build mode and wavefront size carry over) */
+rt_status rt_scene_replicate(const rt_scene* src, int32_t device, rt_scene** out);
+/* rt_render on the n GPUs of a LOCAL communicator: scenes[g] / films[g] on its g-th device; GPU g adds samples
+ * [begin + g S / n, begin + (g+1) S / n) of desc's range to films[g], then the films are all-reduced (clear them first).  Blocking.             */
+rt_status rt_render_multi(rt_comm* comm, rt_scene* const* scenes, rt_film* const* films, uint32_t n, const rt_camera* camera,
+                          const rt_integrator_desc* integrator, const rt_film_desc* desc);
 
 #ifdef __cplusplus
 }

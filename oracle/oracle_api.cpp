@@ -48,6 +48,7 @@ uint32_t orc_scene_add_image_rgb8(void* sp, uint32_t w, uint32_t h, const uint8_
     Scene& s = *(Scene*)sp; Image im; im.w = w; im.h = h; im.hdr = false; im.b.assign(rgb, rgb + (size_t)w * h * 3); s.images.push_back(std::move(im)); return (uint32_t)s.images.size() - 1;
 }
 void orc_scene_set_materials(void* sp, uint64_t n, const rt_material* m) { ((Scene*)sp)->materials.assign(m, m + n); }
+uint32_t orc_scene_add_disney(void* sp, const rt_disney* d) { Scene& s = *(Scene*)sp; s.disneys.push_back(*d); return (uint32_t)s.disneys.size() - 1; }
 void orc_scene_set_lights(void* sp, uint64_t n, const rt_light* l) {
     Scene& s = *(Scene*)sp; s.lights.clear();
     for (uint64_t i = 0; i < n; i++) { Light L; L.d = l[i]; L.area = 0; s.lights.push_back(L); }

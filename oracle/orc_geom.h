@@ -41,20 +41,21 @@ struct Mesh {                                               // hittable.rs:242-2
 
 struct Shading { V3 n, dpdu, dpdv; };                       // hittable.rs:43-49 (dndu/dndv never read)
 
-// bxdf.rs:172-188 (DisneyFresnel out of scope)
-enum FresnelKind { F_DIELECTRIC = 0, F_CONDUCTOR = 1, F_NOOP = 2 };
+// bxdf.rs:172-188.  DisneyFresnel { r0, metallic, eta }: r0 in `eta`, metallic in `eta_i`, eta in `eta_t`
+enum FresnelKind { F_DIELECTRIC = 0, F_CONDUCTOR = 1, F_NOOP = 2, F_DISNEY = 3 };
 struct Fresnel { int kind = F_NOOP; double eta_i = 1, eta_t = 1; V3 eta, k; };
-// microfacet.rs:11-28: only TrowbridgeReitz{sample_visible_area: true} and Empty are ever built
-// by the in-scope materials (material.rs:129,166,168,228)
-struct Mfd { bool empty = true; double alpha_x = 0, alpha_y = 0; };
-// bxdf.rs:213-300, the in-scope lobes
-enum LobeKind { L_LAMBERT_R = 0, L_OREN_NAYAR = 1, L_SPEC_R = 2, L_SPEC_T = 3, L_FRESNEL_SPEC = 4, L_MICRO_R = 5, L_MICRO_T = 6 };
+// microfacet.rs:11-28: TrowbridgeReitz{sample_visible_area: true}, DisneyMicrofacet{sample_visible_area: true} (same D, lambda and sampling,
+// separable G: microfacet.rs:146-155) and Empty are what the materials build (material.rs:129,166,168,228,334,378); Beckmann is never constructed
+struct Mfd { bool empty = true; double alpha_x = 0, alpha_y = 0; bool disney = false; };
+// bxdf.rs:213-300: every lobe a Material can build.  ScaledBxdf and FresnelBlend have constructors (bxdf.rs:877,960) but no call site.
+enum LobeKind { L_LAMBERT_R = 0, L_OREN_NAYAR = 1, L_SPEC_R = 2, L_SPEC_T = 3, L_FRESNEL_SPEC = 4, L_MICRO_R = 5, L_MICRO_T = 6,
+                L_DISNEY_DIFFUSE = 7, L_DISNEY_FAKESS = 8, L_DISNEY_RETRO = 9, L_DISNEY_SHEEN = 10, L_DISNEY_CLEARCOAT = 11, L_LAMBERT_T = 12 };
 struct Lobe {
     int kind = L_LAMBERT_R;
     uint8_t type = 0;        // bxdf_type flag bits
     V3 color;                // color / r
     V3 t;                    // FresnelSpecular t
-    double a = 0, b = 0;     // OrenNayer
+    double a = 0, b = 0;     // OrenNayer A, B ; DisneyFakeSS / DisneyRetro roughness (a) ; DisneyClearCoat weight (a), gloss (b)
     Fresnel fresnel;
     Mfd mfd;
     double eta_a = 1, eta_b = 1;
@@ -64,7 +65,7 @@ struct Bsdf {                                               // bsdf.rs:13-20
     double eta = -100.0;                                    // EMPTY_ETA bsdf.rs:11
     V3 ns, ng, ss, ts;
     int n_lobes = 0;
-    Lobe lobes[2];           // Vec<Box<Bxdf>>: at most 2 for the in-scope materials
+    Lobe lobes[8];           // Vec<Box<Bxdf>>: at most 2 for Matte .. Mirror, at most 8 for Disney (material.rs:245-394)
 };
 
 struct HitRecord {                                          // hittable.rs:51-72
@@ -300,6 +301,7 @@ struct Scene {
     std::vector<Xform> xforms;
     std::vector<rt_texture> textures;
     std::vector<rt_material> materials;
+    std::vector<rt_disney> disneys;  // Material::Disney records (material.rs:55-73), indexed by the material's tex[0]
     std::vector<Light> lights;
     std::vector<Image> images;
     std::vector<double> perlin;      // 1 + 768 + 768 doubles per Texture::Perlin: scale, perm_x | perm_y | perm_z, 256 gradient vectors

@@ -63,11 +63,29 @@ inline V3 fr_conductor(double cos_theta_i, const V3& eta, const V3& eta_k) {
     V3 rp = cmul(rs, cdiv(t3 - t4, t3 + t4));
     return (rp + rs) * 0.5;
 }
+inline double color_to_luminance_(const V3& v) { return 0.2126 * v.x + 0.7152 * v.y + 0.0722 * v.z; }   // util.rs:169-171
+// bxdf.rs:73-108, util.rs:173-183: helpers of the Disney lobes
+inline double lerp(double t, double mn, double mx) { return (1. - t) * mn + t * mx; }
+inline V3 lerp_v(double t, const V3& mn, const V3& mx) { return V3(lerp(t, mn.x, mx.x), lerp(t, mn.y, mx.y), lerp(t, mn.z, mx.z)); }
+inline double schlick_weight(double u) { double m = clampd(1. - u, 0., 1.); double m2 = m * m; return m2 * m2 * m; }
+inline V3 fr_schlick(const V3& r0, double cos_theta) { double w = schlick_weight(cos_theta); return r0 + w * (white() - r0); }
+inline double gtr1(double cos_theta, double a) {
+    if (cos_theta > 1.) return INV_PI;
+    double a2 = a * a;
+    return (a2 - 1.) / (PI * std::log(a2) * (1. + (a2 - 1.) * cos_theta * cos_theta));
+}
+inline double smithg_ggx(double cos_theta, double alpha) { double a2 = alpha * alpha, c2 = cos_theta * cos_theta; return 2. / (1. + std::sqrt(a2 + (1. - a2) * c2)); }
+inline double eta_to_r0(double eta) { return (eta - 1.) * (eta - 1.) / ((eta + 1.) * (eta + 1.)); }
 // Fresnel::evaluate (bxdf.rs:190-211): the dielectric arm passes (|cos|, eta_t, eta_i) — swapped
 inline V3 fresnel_evaluate(const Fresnel& f, double cos_theta_i) {
     switch (f.kind) {
         case F_DIELECTRIC: { double v = fr_dielectric(std::fabs(cos_theta_i), f.eta_t, f.eta_i); return V3(v, v, v); }
         case F_CONDUCTOR: return fr_conductor(std::fabs(cos_theta_i), f.eta, f.k);
+        case F_DISNEY: {                                                       // bxdf.rs:199-208: no |cos| here
+            double mn = fr_dielectric(cos_theta_i, 1., f.eta_t);
+            V3 mx = fr_schlick(f.eta, cos_theta_i);
+            return V3(lerp(f.eta_i, mn, mx.x), lerp(f.eta_i, mn, mx.y), lerp(f.eta_i, mn, mx.z));
+        }
         default: return white();
     }
 }
@@ -90,7 +108,10 @@ inline double mfd_lambda(const Mfd& m, const V3& w) {                   // micro
     return (-1. + std::sqrt(1. + a2t2)) / 2.;
 }
 inline double mfd_g1(const Mfd& m, const V3& w) { return 1. / (1. + mfd_lambda(m, w)); }                 // :143-145
-inline double mfd_g(const Mfd& m, const V3& wo, const V3& wi) { return 1. / (1. + mfd_lambda(m, wo) + mfd_lambda(m, wi)); }  // :151-155
+inline double mfd_g(const Mfd& m, const V3& wo, const V3& wi) {          // :146-157: DisneyMicrofacet uses the separable form
+    if (m.disney) return mfd_g1(m, wo) * mfd_g1(m, wi);
+    return 1. / (1. + mfd_lambda(m, wo) + mfd_lambda(m, wi));
+}
 inline double mfd_pdf(const Mfd& m, const V3& wo, const V3& wh) {       // microfacet.rs:159-172
     if (!m.empty) return mfd_d(m, wh) * mfd_g1(m, wo) * std::fabs(dot(wo, wh)) / abs_cos_theta(wo);
     return mfd_d(m, wh) * abs_cos_theta(wh);
@@ -160,6 +181,14 @@ inline Lobe make_microfacet_transmission(const V3& c, const Mfd& m, double ea, d
     Lobe l; l.kind = L_MICRO_T; l.type = BSDF_TRANSMISSION | BSDF_GLOSSY; l.color = c; l.mfd = m; l.eta_a = ea; l.eta_b = eb; l.mode = mode;
     l.fresnel.kind = F_DIELECTRIC; l.fresnel.eta_i = ea; l.fresnel.eta_t = eb; return l;
 }
+inline Mfd make_disney_mfd(double ax, double ay) { Mfd m = make_trowbridge_reitz(ax, ay); m.disney = true; return m; }       // microfacet.rs:349-357
+// bxdf.rs:992-1030, 237
+inline Lobe make_disney_diffuse(const V3& c) { Lobe l; l.kind = L_DISNEY_DIFFUSE; l.type = BSDF_DIFFUSE | BSDF_REFLECTION; l.color = c; return l; }
+inline Lobe make_disney_fake_ss(const V3& c, double rough) { Lobe l; l.kind = L_DISNEY_FAKESS; l.type = BSDF_DIFFUSE | BSDF_REFLECTION; l.color = c; l.a = rough; return l; }
+inline Lobe make_disney_retro(const V3& c, double rough) { Lobe l; l.kind = L_DISNEY_RETRO; l.type = BSDF_DIFFUSE | BSDF_REFLECTION; l.color = c; l.a = rough; return l; }
+inline Lobe make_disney_sheen(const V3& c) { Lobe l; l.kind = L_DISNEY_SHEEN; l.type = BSDF_DIFFUSE | BSDF_REFLECTION; l.color = c; return l; }
+inline Lobe make_disney_clearcoat(double weight, double gloss) { Lobe l; l.kind = L_DISNEY_CLEARCOAT; l.type = BSDF_GLOSSY | BSDF_REFLECTION; l.a = weight; l.b = gloss; return l; }
+inline Lobe make_lambertian_transmission(const V3& c) { Lobe l; l.kind = L_LAMBERT_T; l.type = BSDF_TRANSMISSION | BSDF_DIFFUSE; l.color = c; return l; }
 inline Lobe make_fresnel_specular(const V3& r, const V3& t, double ea, double eb, uint8_t mode) {  // :974-990
     Lobe l; l.kind = L_FRESNEL_SPEC; l.type = BSDF_TRANSMISSION | BSDF_REFLECTION | BSDF_SPECULAR; l.color = r; l.t = t; l.eta_a = ea; l.eta_b = eb; l.mode = mode; return l;
 }
@@ -204,6 +233,46 @@ inline V3 lobe_f(const Lobe& l, const V3& wo, const V3& wi) {
             return c * std::fabs(mfd_d(l.mfd, wh) * mfd_g(l.mfd, wo, wi) * eta * eta * std::fabs(dot(wi, wh)) * std::fabs(dot(wo, wh)) * factor * factor /
                                  (cti * cto * sqrt_denom * sqrt_denom));
         }
+        case L_LAMBERT_T: return l.color * INV_PI;                             // bxdf.rs:337
+        case L_DISNEY_DIFFUSE: {                                               // bxdf.rs:465-470
+            double fo = schlick_weight(abs_cos_theta(wo)), fi = schlick_weight(abs_cos_theta(wi));
+            return (INV_PI * (1. - fo / 2.) * (1. - fi / 2.)) * l.color;
+        }
+        case L_DISNEY_FAKESS: {                                                // bxdf.rs:471-489
+            V3 wh = wi + wo;
+            if (wh == black()) return black();
+            wh = normalize(wh);
+            double cos_theta_d = dot(wi, wh);
+            double fss90 = cos_theta_d * cos_theta_d * l.a;
+            double fo = schlick_weight(abs_cos_theta(wo)), fi = schlick_weight(abs_cos_theta(wi));
+            double fss = lerp(fo, 1., fss90) * lerp(fi, 1., fss90);
+            double ss = 1.25 * (fss * (1. / (abs_cos_theta(wo) + abs_cos_theta(wi)) - 0.5) + 0.5);
+            return (INV_PI * ss) * l.color;
+        }
+        case L_DISNEY_RETRO: {                                                 // bxdf.rs:490-504
+            V3 wh = wi + wo;
+            if (wh == black()) return black();
+            wh = normalize(wh);
+            double cos_theta_d = dot(wi, wh);
+            double fo = schlick_weight(abs_cos_theta(wo)), fi = schlick_weight(abs_cos_theta(wi));
+            double rr = 2. * l.a * cos_theta_d * cos_theta_d;
+            return (INV_PI * rr * (fo + fi + fo * fi * (rr - 1.))) * l.color;
+        }
+        case L_DISNEY_SHEEN: {                                                 // bxdf.rs:505-513
+            V3 wh = wi + wo;
+            if (wh == black()) return black();
+            wh = normalize(wh);
+            return schlick_weight(dot(wi, wh)) * l.color;
+        }
+        case L_DISNEY_CLEARCOAT: {                                             // bxdf.rs:514-526
+            V3 wh = wi + wo;
+            if (wh == black()) return black();
+            wh = normalize(wh);
+            double dr = gtr1(abs_cos_theta(wh), l.b);
+            V3 fr = fr_schlick(white() * 0.04, dot(wo, wh));
+            double gr = smithg_ggx(abs_cos_theta(wo), 0.25) * smithg_ggx(abs_cos_theta(wi), 0.25);
+            return (l.a / 4. * gr * dr) * fr;
+        }
         default: return black();  // SpecularReflection / SpecularTransmission / FresnelSpecular
     }
 }
@@ -212,6 +281,16 @@ inline double default_pdf(const V3& wo, const V3& wi) { return same_hemisphere(w
 inline double lobe_pdf(const Lobe& l, const V3& wo, const V3& wi) {
     switch (l.kind) {
         case L_LAMBERT_R: case L_OREN_NAYAR: case L_SPEC_R: return default_pdf(wo, wi);
+        case L_DISNEY_DIFFUSE: case L_DISNEY_FAKESS: case L_DISNEY_RETRO: case L_DISNEY_SHEEN: return default_pdf(wo, wi);   // bxdf.rs:792-795
+        case L_LAMBERT_T: return !same_hemisphere(wo, wi) ? abs_cos_theta(wi) * INV_PI : 0.;                                // bxdf.rs:726-732
+        case L_DISNEY_CLEARCOAT: {                                                                                           // bxdf.rs:796-811
+            if (!same_hemisphere(wo, wi)) return 0.;
+            V3 wh = wi + wo;
+            if (wh == black()) return 0.;
+            wh = normalize(wh);
+            double dr = gtr1(abs_cos_theta(wh), l.b);
+            return dr * abs_cos_theta(wh) / (4. * dot(wo, wh));
+        }
         case L_SPEC_T: return 0.;
         case L_MICRO_R: {
             if (!same_hemisphere(wo, wi)) return 0.;
@@ -246,7 +325,33 @@ inline V3 rand_cosine_dir(Rng& rng) {
 inline void lobe_sample_f(const Lobe& l, const V3& wo, const V2& sample, Rng& rng, V3& color, V3& wi, double& pdf) {
     color = black(); wi = black(); pdf = 0.;
     switch (l.kind) {
-        case L_LAMBERT_R: case L_OREN_NAYAR: {                                  // default_sample_f bxdf.rs:815-827
+        case L_LAMBERT_T: {                                                    // bxdf.rs:709-717: uses the SUPPLIED sample (concentric map)
+            V2 uo(2. * sample.x - 1., 2. * sample.y - 1.);                      // util::concentric_sample_disk (util.rs:79-97)
+            V2 d(0., 0.);
+            if (!(uo.x == 0. && uo.y == 0.)) {
+                double theta, r;
+                if (std::fabs(uo.x) > std::fabs(uo.y)) { r = uo.x; theta = PI / 4. * (uo.y / uo.x); }
+                else { r = uo.y; theta = PI / 2. - PI / 4. * (uo.x / uo.y); }
+                d = V2(r * std::cos(theta), r * std::sin(theta));
+            }
+            wi = V3(d.x, d.y, std::sqrt(rmax(0., 1. - d.x * d.x - d.y * d.y)));
+            if (wi.z > 0.) wi.z = -wi.z;
+            pdf = lobe_pdf(l, wo, wi); color = lobe_f(l, wo, wi); return;
+        }
+        case L_DISNEY_CLEARCOAT: {                                             // bxdf.rs:689-708
+            if (wo.z == 0.) return;
+            double alpha2 = l.b * l.b;
+            double cos_t = std::sqrt(rmax(0., (1. - std::pow(alpha2, 1. - sample.x)) / (1. - alpha2)));
+            double sin_t = std::sqrt(rmax(0., 1. - cos_t * cos_t));
+            double phi = 2. * PI * sample.y;
+            V3 wh(sin_t * std::cos(phi), sin_t * std::sin(phi), cos_t);         // util::make_spherical
+            if (!same_hemisphere(wo, wh)) wh = -wh;
+            V3 w = reflect(wo, normalize(wh));
+            if (!same_hemisphere(wo, w)) return;
+            wi = w; color = lobe_f(l, wo, wi); pdf = lobe_pdf(l, wo, wi); return;
+        }
+        case L_LAMBERT_R: case L_OREN_NAYAR:                                    // default_sample_f bxdf.rs:815-827
+        case L_DISNEY_DIFFUSE: case L_DISNEY_FAKESS: case L_DISNEY_RETRO: case L_DISNEY_SHEEN: {
             wi = rand_cosine_dir(rng);
             if (wo.z < 0.) wi.z *= -1.;
             pdf = lobe_pdf(l, wo, wi); color = lobe_f(l, wo, wi); return;
@@ -510,6 +615,57 @@ inline void compute_scattering(const Scene& s, HitRecord& r, uint8_t mode, bool 
             r.bsdf = bsdf_new(r, 1.);
             V3 color = tex_value(s, m.tex[0], u, v, r.p);
             if (color != black()) { Fresnel fr; fr.kind = F_NOOP; bsdf_add(r.bsdf, make_specular_reflection(color, fr)); }
+            return;
+        }
+        case RT_MAT_DISNEY: {
+            // material.rs:245-394.  This arm never calls Bsdf::new: the lobes are added to the record's Bsdf::empty(), whose frame is
+            // ns = ng = ss = ts = normalize((1,1,1)) (bsdf.rs:37-47) — kept as it is.
+            const rt_disney& d = s.disneys[m.tex[0]];
+            const V3& p = r.p;
+            V3 color = tex_value(s, d.color, u, v, p);
+            double metallic_weight = tex_value(s, d.metallic, u, v, p).x;
+            double e = tex_value(s, d.eta, u, v, p).x;
+            double strans = tex_value(s, d.spec_trans, u, v, p).x;
+            double diffuse_weight = (1. - metallic_weight) * (1. - strans);
+            double dt = tex_value(s, d.diff_trans, u, v, p).x / 2.;
+            double rough = tex_value(s, d.roughness, u, v, p).x;
+            double lum = color_to_luminance_(color);
+            V3 c_tint = lum > 0. ? (1. / lum) * color : white();
+            double sheen_weight = tex_value(s, d.sheen, u, v, p).x;
+            V3 c_sheen = black();
+            if (sheen_weight > 0.) { double sheen_tint = tex_value(s, d.sheen_tint, u, v, p).x; c_sheen = lerp_v(sheen_tint, white(), c_tint); }
+            if (diffuse_weight > 0.) {
+                if (d.thin) {
+                    double flat = tex_value(s, d.flatness, u, v, p).x;
+                    bsdf_add(r.bsdf, make_disney_diffuse((diffuse_weight * (1. - flat) * (1. - dt)) * color));
+                    bsdf_add(r.bsdf, make_disney_fake_ss((diffuse_weight * flat * (1. - dt)) * color, rough));
+                } else {
+                    V3 sd = tex_value(s, d.scatter_distance, u, v, p);
+                    if (sd == black()) bsdf_add(r.bsdf, make_disney_diffuse(diffuse_weight * color));
+                    else bsdf_add(r.bsdf, make_specular_transmission(white(), 1., e, mode));
+                }
+                bsdf_add(r.bsdf, make_disney_retro(diffuse_weight * color, rough));
+                if (sheen_weight > 0.) bsdf_add(r.bsdf, make_disney_sheen((diffuse_weight * sheen_weight) * c_sheen));
+            }
+            double ani = tex_value(s, d.anisotropic, u, v, p).x;
+            double aspect = std::sqrt(1. - ani * 0.9);
+            double ax = rmax(0.001, rough * rough / aspect), ay = rmax(0.001, rough * rough * aspect);
+            Mfd dist = make_disney_mfd(ax, ay);
+            double spec_tint = tex_value(s, d.specular_tint, u, v, p).x;
+            V3 c_spec_0 = lerp_v(metallic_weight, eta_to_r0(e) * lerp_v(spec_tint, white(), c_tint), color);
+            Fresnel fr; fr.kind = F_DISNEY; fr.eta = c_spec_0; fr.eta_i = metallic_weight; fr.eta_t = e;
+            bsdf_add(r.bsdf, make_microfacet_reflection(white(), fr, dist));
+            double cc = tex_value(s, d.clearcoat, u, v, p).x;
+            if (cc > 0.) { double gloss = tex_value(s, d.clearcoat_gloss, u, v, p).x; bsdf_add(r.bsdf, make_disney_clearcoat(cc, lerp(gloss, 0.1, 0.001))); }
+            if (strans > 0.) {
+                V3 t(strans * std::sqrt(color.x), strans * std::sqrt(color.y), strans * std::sqrt(color.z));
+                if (d.thin) {
+                    double rscaled = (0.65 * e - 0.35) * rough;
+                    double sax = rmax(0.001, rscaled * rscaled / aspect), say = rmax(0.001, rscaled * rscaled * aspect);
+                    bsdf_add(r.bsdf, make_microfacet_transmission(t, make_trowbridge_reitz(sax, say), 1., e, mode));
+                } else bsdf_add(r.bsdf, make_microfacet_transmission(t, dist, 1., e, mode));
+            }
+            if (d.thin) bsdf_add(r.bsdf, make_lambertian_transmission(dt * color));
             return;
         }
     }

@@ -4,5 +4,5 @@ Only what the path needs: `csrc/` (hand-written sm_100a CUDA + the C ABI, built 
 the host-side mirror of the reference's interface (`core`, `scenes`).  See DESIGN.md / INTEGRATION.md.
 """
 from . import core, scenes  # noqa: F401
-from .core import (Camera, Film, IntType, Objects, Samplers, get_intersection, make_rays, render_samples,  # noqa: F401
+from .core import (Camera, Comm, Film, IntType, Objects, Samplers, get_intersection, make_rays, render_multi, render_samples, replicate,  # noqa: F401
                    tile_multithread, unoccluded)

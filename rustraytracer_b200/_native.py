@@ -77,6 +77,7 @@ RTCORE_SYMBOLS = [
     "rt_film_create_external", "rt_film_destroy", "rt_film_clear", "rt_film_read", "rt_film_resolve_rgb8", "rt_render",
     "rt_render_cancel", "rt_get_counters", "rt_set_wavefront_size", "rt_scene_set_build_mode", "rt_scene_build_stats",
     "rt_debug_prefilter_stats",
+    "rt_comm_create_local", "rt_comm_unique_id", "rt_comm_create_rank", "rt_comm_destroy", "rt_comm_size", "rt_film_allreduce", "rt_scene_replicate", "rt_render_multi",
 ]
 RTHOST_SYMBOLS = [
     "rth_scene_build", "rth_scene_destroy", "rth_scene_camera", "rth_scene_png_name", "rth_scene_uses_standin", "rth_scene_counts",
@@ -125,8 +126,12 @@ def _load_core():
         "rt_film_clear": [vp], "rt_film_read": [vp, vp], "rt_film_resolve_rgb8": [vp, vp],
         "rt_render": [vp, vp, vp, vp, vp], "rt_render_cancel": [vp], "rt_get_counters": [vp, vp], "rt_set_wavefront_size": [vp, u32],
         "rt_scene_set_build_mode": [vp, u32], "rt_scene_build_stats": [vp, vp], "rt_debug_prefilter_stats": [vp],
+        "rt_comm_create_local": [vp, u32, vp], "rt_comm_unique_id": [vp], "rt_comm_create_rank": [vp, u32, u32, vp], "rt_comm_destroy": [vp],
+        "rt_comm_size": [vp, vp, vp], "rt_film_allreduce": [vp, vp, u32], "rt_scene_replicate": [vp, C.c_int32, vp], "rt_render_multi": [vp, vp, vp, u32, vp, vp, vp],
     }
     for name, args in sigs.items():
+        if not hasattr(L, name):
+            continue          # an older A/B build of the library (RT_LIBRTCORE); tests/test_abi.py checks the real one exports everything
         fn = getattr(L, name)
         fn.argtypes = args
         fn.restype = C.c_int32

@@ -286,6 +286,75 @@ def render_samples(objects, camera, int_type, film, width, height, sample_begin,
     check(lib().rt_render(objects.h, C.byref(camera.c), C.byref(integ), C.byref(fd), film.h))
 
 
+class Comm:
+    """NCCL communicator behind the C ABI (include/rtcore.h, SURVEY §8e).  `Comm.local(devices)`: one process driving several GPUs;
+    `Comm.rank(id, world, rank)`: one process per GPU (torchrun), `id` = Comm.unique_id() of rank 0 handed round out of band."""
+
+    def __init__(self, h):
+        self.h = h
+
+    @staticmethod
+    def local(devices):
+        d = np.ascontiguousarray(devices, dtype=np.int32)
+        h = C.c_void_p()
+        check(lib().rt_comm_create_local(ptr(d), len(d), C.byref(h)))
+        return Comm(h)
+
+    @staticmethod
+    def unique_id():
+        out = np.zeros(128, dtype=np.uint8)
+        check(lib().rt_comm_unique_id(ptr(out)))
+        return out.tobytes()
+
+    @staticmethod
+    def rank(unique_id, world, rank):
+        buf = np.frombuffer(unique_id, dtype=np.uint8).copy()
+        h = C.c_void_p()
+        check(lib().rt_comm_create_rank(ptr(buf), int(world), int(rank), C.byref(h)))
+        return Comm(h)
+
+    def size(self):
+        w, n = C.c_uint32(), C.c_uint32()
+        check(lib().rt_comm_size(self.h, C.byref(w), C.byref(n)))
+        return w.value, n.value
+
+    def allreduce(self, films):
+        """in-place sum of the films over all ranks (one film per local device of the communicator)"""
+        arr = (C.c_void_p * len(films))(*[f.h for f in films])
+        check(lib().rt_film_allreduce(self.h, arr, len(films)))
+
+    def close(self):
+        if self.h:
+            lib().rt_comm_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def replicate(objects, device):
+    """the same scene committed on another GPU (rt_scene_replicate)"""
+    o = Objects.__new__(Objects)
+    o.h = C.c_void_p()
+    check(lib().rt_scene_replicate(objects.h, int(device), C.byref(o.h)))
+    return o
+
+
+def render_multi(comm, objects_per_gpu, films_per_gpu, camera, int_type, width, height, sample_begin, sample_end, seed=0, window=None):
+    """`render::tile_multithread` on the GPUs of a local communicator: the sample range is split across them and the films are summed
+    (rt_render_multi).  Films are added to: clear them first."""
+    x0, y0, x1, y1 = window if window is not None else (0, 0, width, height)
+    integ = N.IntegratorDesc(int(int_type.kind), int(int_type.max_depth), 1 if int_type.invisible_light else 0, N.SHADE_F32 if int_type.shade_f32 else 0)
+    fd = N.FilmDesc(width, height, int(sample_begin), int(sample_end), x0, y0, x1, y1, int(seed))
+    n = len(objects_per_gpu)
+    sc = (C.c_void_p * n)(*[o.h for o in objects_per_gpu])
+    fl = (C.c_void_p * n)(*[f.h for f in films_per_gpu])
+    check(lib().rt_render_multi(comm.h, sc, fl, n, C.byref(camera.c), C.byref(integ), C.byref(fd)))
+
+
 def tile_multithread(path, camera, sampler, int_type, objects, width, height, film=None, write_png=True):
     """`render::tile_multithread(path, camera, sampler, int_type)` (render.rs:13-159): renders
     `sampler.samples_per_pixel` samples for every pixel and (optionally) writes the tonemapped PNG to `path`.

@@ -2,6 +2,7 @@
 // (rt_intersect*, rt_closest_device, rt_occluded*).  sm_100a only; there is no CPU fallback —
 // every entry point fails with RT_ERR_CUDA when no device is usable.
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include "scene.h"
@@ -80,7 +81,7 @@ __global__ void k_scatter_other_slots(uint32_t n, const uint32_t* __restrict__ i
     for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
         const uint32_t i = idx[j];
         DSlot sl; for (int k = 0; k < 9; k++) sl.v[k] = 0.;
-        sl.prim = i; sl.kind = 1;
+        sl.prim = i; sl.kind = ob[j].mn[0] > ob[j].mx[0] ? 2u : 1u;      // inverted box = a direct shape: dead slot (scene_host.cpp)
         boxes[i] = ob[j]; slots[i] = sl;
     }
 }
@@ -151,6 +152,7 @@ rt_status upload_scene(rt_scene& s, HostImage& img) {
         if ((st = up(s, img.nodes, d.nodes, s.bytes_nodes))) return st;
         if ((st = up(s, img.slots, d.slots, s.bytes_slots))) return st;
     }
+#if RT_PREFILTER
     {   // f32 prefilter records, leaf order
         void* tp = nullptr;
         CK(cudaMalloc(&tp, std::max<size_t>(img.n_slots, 1) * 3 * sizeof(float4)));
@@ -161,6 +163,7 @@ rt_status upload_scene(rt_scene& s, HostImage& img) {
         }
         d.tri32 = (const float*)tp; s.bytes_slots += (uint64_t)img.n_slots * 3 * sizeof(float4);
     }
+#endif
     if ((st = up(s, img.shapes, d.shapes, b))) return st;
     if ((st = up(s, s.xforms, d.xforms, b))) return st;
     if ((st = up(s, s.textures, d.textures, b))) return st;
@@ -187,6 +190,16 @@ rt_status upload_scene(rt_scene& s, HostImage& img) {
     s.bytes_tables = b;
     // work counters of the persistent batch kernels: a ring, one per call in flight, so that calls on different streams never share one
     { void* cp = nullptr; CK(cudaMalloc(&cp, N_BATCH_COUNTERS * sizeof(uint32_t))); s.allocations.push_back(cp); s.d_counter = (uint32_t*)cp; }
+    d.n_direct = (uint32_t)std::min<size_t>(img.direct.size(), MAX_DIRECT);
+    for (uint32_t k = 0; k < d.n_direct; k++) {
+        d.direct[k] = img.direct[k];
+        // the shape's f64 leaf box (shapes[.. + 6 .. 11]) padded and rounded outward like every box of the tree (bvh_build.cpp)
+        const double* bx = &img.shapes[img.prims[img.direct[k]].a + 6];
+        for (int a = 0; a < 3; a++) {
+            const double lo = bx[a], hi = bx[3 + a], pad = (std::fabs(lo) + std::fabs(hi)) * 2.4e-7;
+            d.direct_box[k][a] = std::nextafterf((float)(lo - pad), -INFINITY); d.direct_box[k][3 + a] = std::nextafterf((float)(hi + pad), INFINITY);
+        }
+    }
     d.n_nodes = n_nodes; d.n_prims = (uint32_t)img.prims.size();
     d.n_lights = (uint32_t)img.lights.size(); d.n_slots = (uint32_t)img.n_slots;
     s.d = d;
@@ -234,7 +247,7 @@ __global__ void __launch_bounds__(128) k_closest(DScene sc, uint64_t n, const rt
 // fetch the next one from a global counter instead of idling until the slowest ray of the warp is done — the soup's
 // incoherent rays differ by an order of magnitude in traversal length.
 struct ClosestJob {
-    const rt_ray* rays; double tmin_, tmax_; uint32_t* prim; double* t;
+    const DScene* sc; const rt_ray* rays; double tmin_, tmax_; uint32_t* prim; double* t;
     __device__ __forceinline__ double tmin(const TState&) const { return tmin_; }
     __device__ __forceinline__ double tmax(const TState&) const { return tmax_; }
     __device__ __forceinline__ void ray(uint32_t i, D3& o, D3& d) const {
@@ -244,12 +257,13 @@ struct ClosestJob {
     }
     __device__ __forceinline__ bool load(uint32_t i, TState& st, int32_t* stack) {
         D3 o, d; ray(i, o, d);
-        tstate_init(st, stack, o, d, tmin_, tmax_, false, 0., 0u);
+        tstate_init(*sc, st, stack, o, d, tmin_, tmax_, false, 0., 0u);
         return true;
     }
     __device__ __forceinline__ void finish(uint32_t i, const TState& st) { prim[i] = st.best.prim; t[i] = st.best.t; }
 };
 __global__ void __launch_bounds__(128, 5) k_closest_persistent(DScene sc, ClosestJob job, uint32_t n, uint32_t* counter) {
+    job.sc = &sc;
     trace_jobs(sc, job, n, counter);
 }
 
@@ -313,7 +327,7 @@ rt_status rt_closest_device(rt_scene* s, uint64_t n, const rt_ray* d_rays, doubl
         uint32_t m = (uint32_t)std::min<uint64_t>(CHUNK, n - base);
         uint32_t* counter = s->d_counter + (s->counter_next.fetch_add(1u) % N_BATCH_COUNTERS);
         CK(cudaMemsetAsync(counter, 0, sizeof(uint32_t), (cudaStream_t)stream));
-        ClosestJob job{d_rays + base, tmin, tmax, d_prim + base, d_t + base};
+        ClosestJob job{nullptr, d_rays + base, tmin, tmax, d_prim + base, d_t + base};
         k_closest_persistent<<<sms * 5, 128, 0, (cudaStream_t)stream>>>(s->d, job, m, counter);
     }
     CK(cudaGetLastError());

@@ -18,8 +18,6 @@
 #include "wavefront.cuh"
 #include "traverse.cuh"
 
-struct rt_film { double* d = nullptr; uint32_t w = 0, h = 0; bool owned = false; int device = 0; };
-
 namespace rt {
 
 #define CK(call)                                                                                     \
@@ -159,7 +157,7 @@ struct ExtendJob {
     }
     __device__ __forceinline__ bool load(uint32_t i, TState& st, int32_t* stack) {
         D3 o, d; ray(i, o, d);
-        tstate_init(st, stack, o, d, SMALL, INF, false, 0., 0u);
+        tstate_init(*sc, st, stack, o, d, SMALL, INF, false, 0., 0u);
         return true;
     }
     __device__ __forceinline__ void finish(uint32_t i, const TState& st) {
@@ -295,20 +293,23 @@ struct ConnectJob {
     }
     __device__ __forceinline__ bool load(uint32_t i, TState& st, int32_t* stack) {
         D3 org, dir; ray(i, org, dir);
-        if (i >= n_shadow) { tstate_init(st, stack, org, dir, SMALL, INF, false, 0., 0u); return true; }
-        uint32_t target = __ldcs(sh.target + i);
-        if (target == RT_NONE) {       // Infinite light: unoccluded(true) — visible iff NOTHING is hit over (0, INF) (hittable.rs:31-33)
-            tstate_init(st, stack, org, dir, 0., INF, true, INF, RT_NONE);
-            return true;
+        // one tstate_init for the three kinds of entry (probe: closest hit over (SMALL, INF); shadow ray to an area light: any hit below the light
+        // primitive's own t; shadow ray to the Infinite light: any hit at all, hittable.rs:31-33), so that its body is inlined once
+        bool any = false; double t_limit = 0.; uint32_t skip = 0u;
+        if (i < n_shadow) {
+            const uint32_t target = __ldcs(sh.target + i);
+            any = true; t_limit = INF; skip = RT_NONE;
+            if (target != RT_NONE) {
+                const DPrim prm = sc->prims[target];
+                if ((prm.info & 7u) == RT_PRIM_TRIANGLE) {
+                    Rec r;
+                    if (!prim_record_t<1>(*sc, target, org, dir, 0., INF, true, r)) return false;
+                    t_limit = r.t;
+                } else if (!shape_test(*sc, prm, org, dir, 0., INF, true, t_limit)) return false;
+                skip = target;
+            }
         }
-        DPrim prm = sc->prims[target];
-        double t_l;
-        if ((prm.info & 7u) == RT_PRIM_TRIANGLE) {
-            Rec r;
-            if (!prim_record_t<1>(*sc, target, org, dir, 0., INF, true, r)) return false;
-            t_l = r.t;
-        } else if (!shape_test(*sc, prm, org, dir, 0., INF, true, t_l)) return false;
-        tstate_init(st, stack, org, dir, 0., INF, true, t_l, target);
+        tstate_init(*sc, st, stack, org, dir, any ? 0. : SMALL, INF, any, t_limit, skip);
         return true;
     }
     __device__ __forceinline__ void finish(uint32_t i, const TState& st) {
@@ -523,7 +524,10 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
     rp.cam = *cam; rp.width = fd->width; rp.height = fd->height; rp.x0 = fd->x0; rp.y0 = fd->y0; rp.ww = fd->x1 - fd->x0; rp.wh = fd->y1 - fd->y0;
     rp.sample_begin = fd->sample_begin; rp.max_depth = integ->max_depth; rp.invisible_light = integ->invisible_light;
     rp.k0 = (uint32_t)fd->seed; rp.k1 = (uint32_t)(fd->seed >> 32); rp.W = w.W; rp.kind = integ->kind;
-    const uint32_t cap = (integ->kind == RT_INTEGRATOR_PATH || integ->kind == RT_INTEGRATOR_BASIC) ? w.W : w.W / std::max<uint32_t>(2u, (uint32_t)s->lights.size());
+    uint32_t cap = (integ->kind == RT_INTEGRATOR_PATH || integ->kind == RT_INTEGRATOR_BASIC) ? w.W : w.W / std::max<uint32_t>(2u, (uint32_t)s->lights.size());
+    // test hook (tests/test_gpu_parity.py::test_wavefront_queue_overflow_is_contained): admit more camera paths than the branching integrators'
+    // queues can take, so that the overflow path — clamped counters, clean RT_ERR_STATE — is exercised; never set in production
+    if (const char* e = getenv("RT_TEST_FORCE_CAP")) { const long v = atol(e); if (v > 0) cap = (uint32_t)std::min<long>(v, (long)w.W); }
     Ctrl init{}; init.total_samples = (unsigned long long)rp.ww * rp.wh * (fd->sample_end - fd->sample_begin);
     s->counters = rt_counters{};
     if (init.total_samples == 0) return RT_OK;

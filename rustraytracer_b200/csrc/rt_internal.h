@@ -75,6 +75,7 @@ constexpr double DISTANT_WORLD_RADIUS = 1e10;   // light.rs:579
 struct DImage { uint64_t offset; uint32_t w, h; };
 constexpr double WORLD_RADIUS = 10000.0;   // light.rs:636
 
+constexpr uint32_t MAX_DIRECT = 8;
 // everything the kernels read; all pointers are device pointers
 struct DScene {
     const DNodeT* nodes; const DSlot* slots; const DPrim* prims; const DMesh* meshes;
@@ -88,7 +89,10 @@ struct DScene {
                                               // roughness remap (microfacet.rs:442-446: an f64 log per shaded vertex otherwise); NaN = evaluate on the device
     uint32_t n_nodes, n_prims, n_lights, n_slots;
     uint32_t has_infinite, has_perlin;        // any Light::Infinite in `lights` (misses then emit, light.rs:499-513); any Texture::Perlin
-    uint32_t has_delta, pad_;                 // any Point / Spot / Distant light (f64 shade kernels only)
+    uint32_t has_delta, n_direct;             // any Point / Spot / Distant light (f64 shade kernels only); direct shapes (below)
+    // the scene's few parametric shapes when they are kept OUT of the tree and tested once per ray before the walk (traverse.cuh:direct_shapes)
+    uint32_t direct[MAX_DIRECT];
+    float direct_box[MAX_DIRECT][6];          // their leaf boxes rounded outward to f32 (min xyz, max xyz): a conservative cull in front of the exact f64 test
 };
 
 constexpr size_t PERLIN_STRIDE = 1 + 3 * 256 + 3 * 256;

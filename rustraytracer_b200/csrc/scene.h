@@ -4,6 +4,8 @@
 #include "rt_internal.h"
 
 namespace rt { constexpr uint32_t N_BATCH_COUNTERS = 256; }
+// the film: (r, g, b, n) running sums as 4 doubles per pixel on `device`; `owned` = allocated by rt_film_create (else caller memory)
+struct rt_film { double* d = nullptr; uint32_t w = 0, h = 0; bool owned = false; int device = 0; };
 struct rt_scene {
     // host tables (mirror of `Objects`, reference geometry.rs:13-21)
     std::vector<rt::HostMesh> meshes;
@@ -51,6 +53,9 @@ struct HostImage {
     // the device from the uploaded tables (device.cu:k_fill_tri_slots), scatters the few non-triangle ones prepared here (`other_*`,
     // slot kind 1), builds the tree where it will be walked (bvh_device.cu) and permutes the slots into leaf order there
     bool device_build = false; std::vector<uint32_t> other_idx; std::vector<Box64> other_boxes;
+    // direct shapes (traverse.cuh:direct_shapes): the scene's parametric shapes when there are at most MAX_DIRECT of them next to triangles — kept out
+    // of the tree (host build: not handed to the builder; device build: a dead slot with an inverted box) and tested once per ray before the walk
+    std::vector<uint32_t> direct;
     size_t n_slots = 0;
     int max_stack = 0; double build_ms = 0.;
 };

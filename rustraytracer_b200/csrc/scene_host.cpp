@@ -204,6 +204,14 @@ rt_status build_host_image(const rt_scene& s, HostImage& img, bool device_build)
     img.prims.resize(n);
     img.device_build = device_build && n >= 8;
     img.n_slots = n;
+    {   // direct shapes: few parametric shapes next to at least one triangle (RT_DIRECT=0 keeps them in the tree, for A/B runs)
+        size_t n_shapes = 0, n_tris = 0;
+        for (size_t i = 0; i < n; i++) (s.prims[i].type == RT_PRIM_TRIANGLE ? n_tris : n_shapes)++;
+        const char* e = getenv("RT_DIRECT");
+        if (n_shapes >= 1 && n_shapes <= MAX_DIRECT && n_tris >= 8 && !(e && e[0] == '0'))
+            for (size_t i = 0; i < n; i++) if (s.prims[i].type != RT_PRIM_TRIANGLE) img.direct.push_back((uint32_t)i);
+    }
+    const bool use_direct = !img.direct.empty();
     std::vector<Box64> boxes(img.device_build ? 0 : n);
     std::mutex other_mu;
     int threads = (int)std::max(1u, std::thread::hardware_concurrency());
@@ -224,30 +232,44 @@ rt_status build_host_image(const rt_scene& s, HostImage& img, bool device_build)
                 img.prims[i] = d;
                 if (img.device_build && p.type == RT_PRIM_TRIANGLE) continue;      // box and slot record: device.cu:k_fill_tri_slots
                 const Box64 bx = prim_box(s, p);
-                if (!img.device_build) boxes[i] = bx;
-                else { std::lock_guard<std::mutex> g(other_mu); img.other_idx.push_back((uint32_t)i); img.other_boxes.push_back(bx); }
                 if (p.type != RT_PRIM_TRIANGLE) for (int k = 0; k < 3; k++) { img.shapes[p.shape + 6 + k] = bx.mn[k]; img.shapes[p.shape + 9 + k] = bx.mx[k]; }
+                if (!img.device_build) boxes[i] = bx;
+                else {
+                    // a direct shape keeps its slot (slots are indexed by primitive there) but can never be reached: inverted box, slot kind 2
+                    Box64 tb = bx;
+                    if (use_direct && p.type != RT_PRIM_TRIANGLE) for (int k = 0; k < 3; k++) { tb.mn[k] = 1e300; tb.mx[k] = -1e300; }
+                    std::lock_guard<std::mutex> g(other_mu); img.other_idx.push_back((uint32_t)i); img.other_boxes.push_back(tb);
+                }
             }
         });
         for (auto& th : pool) th.join();
     }
     if (ib >= (1ull << 32)) { set_error("index buffer exceeds 2^32 entries"); return RT_ERR_INVALID; }
     BuiltBvh bvh;
+    std::vector<uint32_t> tree_prims;              // host build with direct shapes: the primitives handed to the builder (the triangles), in scene order
     if (!img.device_build) {
+        if (use_direct) {
+            std::vector<Box64> tb; tb.reserve(n - img.direct.size()); tree_prims.reserve(n - img.direct.size());
+            for (size_t i = 0; i < n; i++) if (s.prims[i].type == RT_PRIM_TRIANGLE) { tree_prims.push_back((uint32_t)i); tb.push_back(boxes[i]); }
+            boxes.swap(tb);
+            img.n_slots = tree_prims.size();
+        }
+        const size_t n_tree = boxes.size();
         auto t0 = std::chrono::steady_clock::now();
         rt_status bst = build_bvh(boxes, bvh, threads);
         if (bst != RT_OK) return bst;
-        if (bvh.order.size() != n) { set_error("commit: BVH build returned an incomplete primitive order"); return RT_ERR_INVALID; }
+        if (bvh.order.size() != n_tree) { set_error("commit: BVH build returned an incomplete primitive order"); return RT_ERR_INVALID; }
         img.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
         img.max_stack = bvh.max_stack;
         if (bvh.max_stack > TRAVERSAL_STACK) { set_error("commit: BVH needs a deeper traversal stack than the kernels have (" + std::to_string(bvh.max_stack) + " > " + std::to_string(TRAVERSAL_STACK) + ")"); return RT_ERR_INVALID; }
         if (getenv("RT_TRACE_BUILD")) fprintf(stderr, "bvh: %zu nodes of %zu bytes, %zu slots, worst-case stack %d\n", bvh.nodes.size(), sizeof(DNodeT), n, bvh.max_stack);
         img.nodes = std::move(bvh.nodes);
     }
-    img.slots.resize(img.device_build ? 0 : n);
+    const size_t n_host_slots = img.device_build ? 0 : img.n_slots;
+    img.slots.resize(n_host_slots);
     auto fill_slots = [&](size_t sb, size_t se) {
     for (size_t sidx = sb; sidx < se; sidx++) {
-        uint32_t pi = bvh.order[sidx];
+        uint32_t pi = tree_prims.empty() ? bvh.order[sidx] : tree_prims[bvh.order[sidx]];
         const HostPrim& p = s.prims[pi];
         DSlot sl; memset(&sl, 0, sizeof(sl));
         sl.prim = pi;
@@ -272,8 +294,9 @@ rt_status build_host_image(const rt_scene& s, HostImage& img, bool device_build)
     }
     };
     if (!img.device_build) {
-        std::vector<std::thread> pool; size_t chunk = (n + threads - 1) / std::max(threads, 1);
-        for (int t = 0; t < threads; t++) { size_t b = std::min(n, t * chunk), e = std::min(n, b + chunk); if (e > b) pool.emplace_back(fill_slots, b, e); }
+        const size_t ns = n_host_slots;
+        std::vector<std::thread> pool; size_t chunk = (ns + threads - 1) / std::max(threads, 1);
+        for (int t = 0; t < threads; t++) { size_t b = std::min(ns, t * chunk), e = std::min(ns, b + chunk); if (e > b) pool.emplace_back(fill_slots, b, e); }
         for (auto& th : pool) th.join();
     }
     // per-material microfacet alphas that do not depend on the hit point (material.rs:110-117,170-173,205-214)

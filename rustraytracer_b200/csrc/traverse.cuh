@@ -85,10 +85,13 @@ __device__ __forceinline__ float f32_down(double x) { return __double2float_rd(x
 // NaN / inf makes a comparison false, i.e. "go on to the exact test".  RT_PREFILTER_CHECK builds count — on the device, over every
 // slot test of a run — the cases where the prefilter would have skipped a hit the traversal then used (rt_debug_prefilter_violations()).
 #ifndef RT_PREFILTER
-#define RT_PREFILTER 1
+#define RT_PREFILTER 0
 #endif
 #ifndef RT_PREFILTER_CHECK
 #define RT_PREFILTER_CHECK 0
+#endif
+#ifndef RT_LEAF_PREFETCH
+#define RT_LEAF_PREFETCH 0
 #endif
 struct RayP { float ox, oy, oz, shx, shy, shz, eo; int kz; };     // f32 origin, shear (sx, sy, 1/d[kz]) and 2u * max|o|
 constexpr float F32_U = 5.9604645e-8f;                            // 2^-24
@@ -197,13 +200,43 @@ __device__ __forceinline__ int32_t node4_any(const DScene& sc, int32_t cur, cons
 #endif
 
 
-// Candidate primitive in leaf slot `s`: the f32 prefilter, then the reference's exact accept test.  Returns true with t.
-// `ftmax` is the far end of the caller's CULLING interval (>= best-so-far t / the shadow ray's t_limit): a hit beyond it cannot matter.
-// skipped (RT_PREFILTER_CHECK only): the prefilter said "skip" — the exact test was run all the same so that the caller can audit the decision.
-// The exact test as a CALL (RT_EXACT_CALL): with the prefilter in front of it, it runs for one or two slots per ray; as a function of its own it
-// keeps its ~60 f64 temporaries out of the register allocation of the traversal loop.
+// ---- per-ray data of the leaf tests
+// RT_PREFILTER = 0 (default): the exact test's f64 constants (RayX: origin, direction, shear, 1/d) live in the traversal state, every candidate
+//                 slot goes straight to the reference's f64 test — round 1's scheme, and still the fastest on B200 (see below).
+// RT_PREFILTER = 1: the f32 prefilter's constants (RayP) live in the state; the f64 ray is kept too (RT_STATE_RAY = 1) or read back from the
+//                 queue the ray came from (Job::ray) for the slots that reach the exact test.
+// MEASURED (r02, dragon 1024^2 64 spp, extend / connect ms; profiles/prefilter_ab_r02.json): no prefilter 31.6 / 20.2; prefilter with the ray read
+// back + exact test as a call 36.9 / 24.3; ray in the state 36.0 / 24.0; ... + exact test inlined 34.9 / 23.0; + L1 prefetch of the leaf's records: no
+// change.  Why it loses here: B200's FP64 pipe is half-rate, not vestigial, so the f64 test's early-out path (~40 instructions up to the mixed-sign
+// reject) costs about what the f32 test with its error bound does (~60), the survivors pay both plus a second dependent fetch, and this scene runs
+// only ~0.5 triangle tests per ray (most rays meet the floor or leave).  The prefilter itself is sound: 0 violations in 214 M audited slot tests
+// (profiles/prefilter_audit_r02.json) with 80-88 % of the triangle slots skipped.  It stays in the tree as a build option for FP64-poor parts.
+#ifndef RT_STATE_RAY
+#define RT_STATE_RAY 1
+#endif
+#if RT_PREFILTER
+struct RayL {
+    RayP rp;
+#if RT_STATE_RAY
+    D3 o, d;
+#endif
+};
+__device__ __forceinline__ RayL make_rayl(const RayX& rx) {
+    RayL r; r.rp = make_rayp(rx);
+#if RT_STATE_RAY
+    r.o = rx.o; r.d = rx.d;
+#endif
+    return r;
+}
+#else
+struct RayL { RayX rx; };
+__device__ __forceinline__ RayL make_rayl(const RayX& rx) { RayL r; r.rx = rx; return r; }
+#endif
+
+// The exact test as a CALL (RT_EXACT_CALL, prefilter builds only): as a function of its own it keeps its ~60 f64 temporaries out of the register
+// allocation of the traversal loop.
 #ifndef RT_EXACT_CALL
-#define RT_EXACT_CALL 1
+#define RT_EXACT_CALL 0
 #endif
 #if RT_EXACT_CALL
 #define RT_EXACT_FN static __device__ __noinline__
@@ -219,20 +252,21 @@ RT_EXACT_FN bool tri_exact(const DSlot* __restrict__ slot, D3 o, D3 d, double tm
     if (!tri_test(rx, p0, p1, p2, tmax, t, b0, b1, b2)) return false;
     return tri_leaf_box_inv(p0, p1, p2, rx.o, rx.inv, tmin, tmax);
 }
-// The f64 per-ray constants of the exact test (shear, 1/d: five f64 divisions) are rebuilt from (o, d) for the few slots that reach it instead of
-// living in registers for the whole walk: bitwise the same values, ten registers less in the persistent kernels.
-// `fetch(o, d)` hands out the ray's f64 origin and direction when — and only when — a slot reaches the exact test: the persistent kernels do not keep
-// them in registers either but read them back from the queue the ray came from (Job::ray).
+// Candidate primitive in leaf slot `s`: (the f32 prefilter, then) the reference's exact accept test.  Returns true with t.
+// `ftmax` is the far end of the caller's CULLING interval (>= best-so-far t / the shadow ray's t_limit): a hit beyond it cannot matter.
+// `fetch(o, d)` hands out the ray's f64 origin and direction (prefilter builds without RT_STATE_RAY: read back from the ray's queue).
+// skipped (RT_PREFILTER_CHECK only): the prefilter said "skip" — the exact test was run all the same so that the caller can audit the decision.
 template <class Fetch>
-__device__ __forceinline__ bool slot_test(const DScene& sc, uint32_t s, const Fetch& fetch, const RayP& rp, double tmin, double tmax, float ftmax,
+__device__ __forceinline__ bool slot_test(const DScene& sc, uint32_t s, const RayL& rl, const Fetch& fetch, double tmin, double tmax, float ftmax,
                                           double& t, uint32_t& prim, bool* skipped = nullptr) {
 #if RT_PREFILTER
     const float4* w = reinterpret_cast<const float4*>(sc.tri32) + 3 * (size_t)s;
     const float4 w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2);
     prim = __float_as_uint(w2.y);
     const uint32_t kind = __float_as_uint(w2.z);
+    if (kind == 2) return false;     // never hit: a triangle the reference cannot hit (degenerate uv frame ∧ zero normal, hittable.rs:373-378), or a direct shape
     if (kind == 0) {
-        const bool pass = tri_prefilter(rp, w0, w1, w2, ftmax);
+        const bool pass = tri_prefilter(rl.rp, w0, w1, w2, ftmax);
 #if RT_PREFILTER_CHECK
         atomicAdd(&g_prefilter_stats[0], 1ull);
         if (!pass) atomicAdd(&g_prefilter_stats[1], 1ull);
@@ -240,34 +274,38 @@ __device__ __forceinline__ bool slot_test(const DScene& sc, uint32_t s, const Fe
 #else
         if (!pass) return false;
 #endif
-        D3 o, d; fetch(o, d);
+    }
+    D3 o, d;
+#if RT_STATE_RAY
+    o = rl.o; d = rl.d;
+#else
+    fetch(o, d);
+#endif
+    if (kind == 0) {
         if (!tri_exact(sc.slots + s, o, d, tmin, tmax, t)) return false;
 #if RT_PREFILTER_CHECK
         atomicAdd(&g_prefilter_stats[2], 1ull);
 #endif
         return true;
     }
-    if (kind == 2) return false;     // triangle the reference can never hit (degenerate uv frame ∧ zero normal, hittable.rs:373-378)
+    DPrim pr = sc.prims[prim];
+    return shape_test(sc, pr, o, d, tmin, tmax, true, t);
 #else
+    const RayX& rx = rl.rx;
     const double2* q = reinterpret_cast<const double2*>(sc.slots + s);
     double2 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3), q4 = __ldg(q + 4);
     uint2 tag = *reinterpret_cast<uint2*>(&q4.y);
     prim = tag.x;
-    D3 o, d; fetch(o, d);
     if (tag.y == 0) {
         D3 p0 = mk3(q0.x, q0.y, q1.x), p1 = mk3(q1.y, q2.x, q2.y), p2 = mk3(q3.x, q3.y, q4.x);
-        const RayX rx = make_rayx(o, d);
         double b0, b1, b2;
         if (!tri_test(rx, p0, p1, p2, tmax, t, b0, b1, b2)) return false;
         return tri_leaf_box_inv(p0, p1, p2, rx.o, rx.inv, tmin, tmax);
     }
-    if (tag.y == 2) return false;    // triangle the reference can never hit (degenerate uv frame ∧ zero normal, hittable.rs:373-378)
-#endif
+    if (tag.y == 2) return false;    // never hit: a triangle the reference cannot hit (degenerate uv frame ∧ zero normal, hittable.rs:373-378), or a direct shape
     DPrim pr = sc.prims[prim];
-#if RT_PREFILTER
-    D3 o, d; fetch(o, d);
+    return shape_test(sc, pr, rx.o, rx.d, tmin, tmax, true, t, &rx.inv);
 #endif
-    return shape_test(sc, pr, o, d, tmin, tmax, true, t);
 }
 #if RT_PREFILTER_CHECK
 #define RT_AUDIT(skipped) do { if (skipped) atomicAdd(&g_prefilter_stats[3], 1ull); } while (0)
@@ -275,17 +313,47 @@ __device__ __forceinline__ bool slot_test(const DScene& sc, uint32_t s, const Fe
 #define RT_AUDIT(skipped) do { } while (0)
 #endif
 
+// Direct shapes.  Every scene function of the reference (scenes.rs) sets a handful of parametric shapes — a 20,000-unit floor rect, a light rect,
+// the Cornell walls — next to its meshes.  Inside the BVH they sit in leaves right under the root, so nearly every ray ran their exact f64 test
+// (slab + rect: ~150 instructions with a division each) from a divergent leaf phase at ~6 of 32 lanes (ncu r02: 8 % of k_extend's warp instructions).
+// When a scene has at most MAX_DIRECT such shapes next to at least one triangle, commit leaves them OUT of the tree (DScene::direct) and every ray
+// tests them once, right where it is set up — all freshly fetched lanes of the warp together — BEFORE the walk: the closest-hit walk then starts with
+// its culling interval already cut at the floor / wall hit, and a shadow ray blocked by one of them never walks at all.  The hit set is unchanged
+// (hit(prim) = leafbox_f64 ∧ primtest_f64 does not depend on where a primitive is looked up), ties keep the smaller primitive index as everywhere.
+__device__ __forceinline__ void direct_shapes(const DScene& sc, const RayX& rx, const RayF& rf, double tmin, double tmax, bool any, double t_limit, uint32_t skip,
+                                              double& best_t, uint32_t& best_prim, bool& occluded, float& ftmax, float ftmin) {
+    for (uint32_t k = 0; k < sc.n_direct; k++) {
+        const uint32_t prim = sc.direct[k];
+        if (any && prim == skip) continue;            // the shadow ray's own target
+        // the same conservative f32 slab test the tree's nodes get, on the shape's own box: a shadow ray that leaves the floor towards the lamp
+        // does not pay for the floor's f64 test
+        float tn;
+        if (!box_test(rf, sc.direct_box[k][0], sc.direct_box[k][3], sc.direct_box[k][1], sc.direct_box[k][4], sc.direct_box[k][2], sc.direct_box[k][5], ftmin, ftmax, tn)) continue;
+        const DPrim pr = sc.prims[prim];
+        double t;
+        if (!shape_test(sc, pr, rx.o, rx.d, tmin, tmax, true, t, &rx.inv)) continue;
+        if (any) {
+            if (prim != skip && (t < t_limit || (t == t_limit && prim < skip))) { occluded = true; return; }
+        } else if (best_prim == RT_NONE || t < best_t || (t == best_t && prim < best_prim)) {
+            best_t = t; best_prim = prim;
+            ftmax = fmaxf(fminf(ftmax, __double2float_ru(t)), ftmin);
+        }
+    }
+}
+
 // closest hit in the reference's sense over [tmin, tmax]
 __device__ __forceinline__ Hit trace_closest(const DScene& sc, D3 o, D3 d, double tmin, double tmax) {
     Hit best; best.t = 0.; best.prim = RT_NONE;
-    if (sc.n_nodes == 0) return best;
+    if (sc.n_nodes == 0 && sc.n_direct == 0) return best;
     RayF rf = make_rayf(o, d);
-    RayP rp = make_rayp(make_rayx(o, d));
+    const RayX rx0 = make_rayx(o, d);
+    const RayL rl = make_rayl(rx0);
     float ftmin = f32_down(tmin); ftmin = ftmin - fabsf(ftmin) * 4.8e-7f;
     float ftmax = f32_up(fmin(tmax, 3.0e38));
+    { bool occ = false; direct_shapes(sc, rx0, rf, tmin, tmax, false, 0., 0u, best.t, best.prim, occ, ftmax, ftmin); }
     int32_t stack[STACK]; int sp = 0;
     stack[sp++] = SENTINEL;
-    int32_t cur = 0;
+    int32_t cur = sc.n_nodes ? 0 : SENTINEL;
 #if RT_BVH_WIDTH != 4
     const float4* __restrict__ nodes = reinterpret_cast<const float4*>(sc.nodes);
 #endif
@@ -315,7 +383,7 @@ __device__ __forceinline__ Hit trace_closest(const DScene& sc, D3 o, D3 d, doubl
         uint32_t v = (uint32_t)~cur, first = v >> 2, count = (v & 3u) + 1u;
         for (uint32_t s = first; s < first + count; s++) {
             double t; uint32_t prim; bool skipped = false;
-            if (slot_test(sc, s, [&](D3& fo, D3& fd) { fo = o; fd = d; }, rp, tmin, tmax, ftmax, t, prim, &skipped)) {
+            if (slot_test(sc, s, rl, [&](D3& fo, D3& fd) { fo = o; fd = d; }, tmin, tmax, ftmax, t, prim, &skipped)) {
                 if (best.prim == RT_NONE || t < best.t || (t == best.t && prim < best.prim)) {
                     RT_AUDIT(skipped);
                     best.t = t; best.prim = prim;
@@ -335,14 +403,16 @@ __device__ __forceinline__ Hit trace_closest(const DScene& sc, D3 o, D3 d, doubl
 // (or t <= t_limit when `tie_blocks`)?  Used for Visibility::unoccluded (hittable.rs:25-39): the light
 // is visible iff the closest hit is the light primitive itself.
 __device__ __forceinline__ bool trace_any(const DScene& sc, D3 o, D3 d, double tmin, double tmax, double t_limit, uint32_t skip) {
-    if (sc.n_nodes == 0) return false;
+    if (sc.n_nodes == 0 && sc.n_direct == 0) return false;
     RayF rf = make_rayf(o, d);
-    RayP rp = make_rayp(make_rayx(o, d));
+    const RayX rx0 = make_rayx(o, d);
+    const RayL rl = make_rayl(rx0);
     float ftmin = f32_down(tmin); ftmin = ftmin - fabsf(ftmin) * 4.8e-7f;
     float ftmax = f32_up(fmin(fmin(tmax, t_limit), 3.0e38));
+    { bool occ = false; double bt = 0.; uint32_t bp = RT_NONE; direct_shapes(sc, rx0, rf, tmin, tmax, true, t_limit, skip, bt, bp, occ, ftmax, ftmin); if (occ) return true; }
     int32_t stack[STACK]; int sp = 0;
     stack[sp++] = SENTINEL;
-    int32_t cur = 0;
+    int32_t cur = sc.n_nodes ? 0 : SENTINEL;
 #if RT_BVH_WIDTH != 4
     const float4* __restrict__ nodes = reinterpret_cast<const float4*>(sc.nodes);
 #endif
@@ -367,7 +437,7 @@ __device__ __forceinline__ bool trace_any(const DScene& sc, D3 o, D3 d, double t
         uint32_t v = (uint32_t)~cur, first = v >> 2, count = (v & 3u) + 1u;
         for (uint32_t s = first; s < first + count; s++) {
             double t; uint32_t prim; bool skipped = false;
-            if (slot_test(sc, s, [&](D3& fo, D3& fd) { fo = o; fd = d; }, rp, tmin, tmax, ftmax, t, prim, &skipped) && prim != skip) {
+            if (slot_test(sc, s, rl, [&](D3& fo, D3& fd) { fo = o; fd = d; }, tmin, tmax, ftmax, t, prim, &skipped) && prim != skip) {
                 // the closest-hit rule keeps the smaller primitive index on an exact tie
                 if (t < t_limit || (t == t_limit && prim < skip)) { RT_AUDIT(skipped); return true; }
             }
@@ -413,20 +483,25 @@ __device__ __forceinline__ bool unoccluded(const DScene& sc, D3 p0, D3 p1, uint3
 // The ray's f64 interval [tmin, tmax] is not part of the state: it is a property of the job (extend: (SMALL, INF); connect: (0, INF) for shadow
 // rays, (SMALL, INF) for probes; batch entry points: the caller's) and is asked for with job.tmin(state) / job.tmax(state) where the exact test needs it.
 struct TState {
-    RayF rf; RayP rp;
+    RayL rl; RayF rf;
     float ftmin, ftmax;
     double t_limit;
     uint32_t skip; bool any, occluded;
     Hit best;
     int32_t cur; int sp;
 };
-__device__ __forceinline__ void tstate_init(TState& s, int32_t* stack, D3 o, D3 d, double tmin, double tmax, bool any, double t_limit, uint32_t skip) {
-    s.rf = make_rayf(o, d); s.rp = make_rayp(make_rayx(o, d));
+__device__ __forceinline__ void tstate_init(const DScene& sc, TState& s, int32_t* stack, D3 o, D3 d, double tmin, double tmax, bool any, double t_limit, uint32_t skip) {
+    const RayX rx = make_rayx(o, d);
+    s.rl = make_rayl(rx); s.rf = make_rayf(o, d);
     s.any = any; s.t_limit = t_limit; s.skip = skip; s.occluded = false;
     s.ftmin = f32_down(tmin); s.ftmin = s.ftmin - fabsf(s.ftmin) * 4.8e-7f;
     s.ftmax = f32_up(fmin(any ? fmin(tmax, t_limit) : tmax, 3.0e38));
     s.best.t = 0.; s.best.prim = RT_NONE;
-    s.sp = 0; stack[s.sp++] = SENTINEL; s.cur = 0;
+    s.sp = 0; stack[s.sp++] = SENTINEL; s.cur = sc.n_nodes ? 0 : SENTINEL;
+    if (sc.n_direct) {
+        direct_shapes(sc, rx, s.rf, tmin, tmax, any, t_limit, skip, s.best.t, s.best.prim, s.occluded, s.ftmax, s.ftmin);
+        if (s.occluded) s.cur = SENTINEL;          // a blocked shadow ray is finished before it walks
+    }
 }
 // one inner-node step: test both children, descend into the nearer hit child, push the other, or pop
 __device__ __forceinline__ void node_step(const DScene& sc, TState& s, int32_t* stack) {
@@ -454,9 +529,19 @@ __device__ __forceinline__ void node_step(const DScene& sc, TState& s, int32_t* 
 template <class Fetch>
 __device__ __forceinline__ void leaf_step(const DScene& sc, TState& s, int32_t* stack, double tmin, double tmax, const Fetch& fetch) {
     uint32_t v = (uint32_t)~s.cur, first = v >> 2, count = (v & 3u) + 1u;
+#if RT_PREFILTER && RT_LEAF_PREFETCH
+    // the leaf's 2..4 prefilter records are contiguous (48 B each): pull the rest into L1 while the first one is being tested, so that the
+    // slot loop pays one L2 round trip per leaf instead of one per slot
+    if (count > 1u) {
+        const char* base = reinterpret_cast<const char*>(sc.tri32) + 48 * (size_t)first;
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(base + 64));
+        if (count > 2u) asm volatile("prefetch.global.L1 [%0];" ::"l"(base + 128));
+        if (count > 3u) asm volatile("prefetch.global.L1 [%0];" ::"l"(base + 176));
+    }
+#endif
     for (uint32_t k = first; k < first + count; k++) {
         double t; uint32_t prim; bool skipped = false;
-        if (!slot_test(sc, k, fetch, s.rp, tmin, tmax, s.ftmax, t, prim, &skipped)) continue;
+        if (!slot_test(sc, k, s.rl, fetch, tmin, tmax, s.ftmax, t, prim, &skipped)) continue;
         if (s.any) {
             // the closest-hit rule keeps the smaller primitive index on an exact tie
             if (prim != s.skip && (t < s.t_limit || (t == s.t_limit && prim < s.skip))) { RT_AUDIT(skipped); s.occluded = true; s.cur = SENTINEL; return; }
@@ -489,7 +574,7 @@ __device__ __forceinline__ void trace_jobs(const DScene& sc, Job& job, uint32_t 
     TState st; st.cur = SENTINEL; st.sp = 0;
     bool active = false, exhausted = false;
     uint32_t idx = 0;
-    if (sc.n_nodes == 0) {      // empty scene: every ray misses
+    if (sc.n_nodes == 0 && sc.n_direct == 0) {      // empty scene: every ray misses
         for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
             if (job.load(i, st, stack)) { st.best.prim = RT_NONE; st.occluded = false; job.finish(i, st); }
         }

@@ -263,3 +263,48 @@ def test_image_and_infinite_light_validation():
     with pytest.raises(N.RtError) as ei:
         o.commit()
     assert ei.value.status == N.RT_ERR_INVALID
+
+
+def test_multi_gpu_entry_points_argument_errors():
+    """rt_comm_* / rt_render_multi / rt_scene_replicate (SURVEY §8e behind the ABI): argument checking happens before any CUDA / NCCL work."""
+    L = N.lib()
+    h = C.c_void_p()
+    assert L.rt_comm_create_local(None, 0, C.byref(h)) == N.RT_ERR_INVALID
+    assert L.rt_comm_unique_id(None) == N.RT_ERR_INVALID
+    ident = np.zeros(128, dtype=np.uint8)
+    assert L.rt_comm_create_rank(N.ptr(ident), 2, 2, C.byref(h)) == N.RT_ERR_INVALID      # rank >= world
+    assert L.rt_comm_create_rank(None, 2, 0, C.byref(h)) == N.RT_ERR_INVALID
+    assert L.rt_film_allreduce(None, None, 0) == N.RT_ERR_INVALID
+    assert L.rt_render_multi(None, None, None, 0, None, None, None) == N.RT_ERR_INVALID
+    assert L.rt_scene_replicate(None, 0, C.byref(h)) == N.RT_ERR_INVALID
+    assert L.rt_comm_size(None, None, None) == N.RT_ERR_INVALID
+    assert L.rt_comm_destroy(None) == N.RT_OK
+    if L.rt_device_count() == 0:
+        dev = np.zeros(1, dtype=np.int32)
+        assert L.rt_comm_create_local(N.ptr(dev), 1, C.byref(h)) == N.RT_ERR_CUDA        # no CPU path here either
+        o = Objects()
+        assert L.rt_scene_replicate(o.h, 0, C.byref(h)) == N.RT_ERR_CUDA
+
+
+def test_rust_ffi_crate_declares_exactly_the_header():
+    """ffi/src/lib.rs (the thin C-ABI FFI crate north_star names; no rustc in this image, so it is kept honest here): its extern block lists
+    exactly the functions include/rtcore.h declares, and its #[repr(C)] structs have the header's fields in the header's order."""
+    hdr = open(os.path.join(ROOT, "include", "rtcore.h")).read()
+    rs = open(os.path.join(ROOT, "ffi", "src", "lib.rs")).read()
+    declared = set(re.findall(r"\b(rt_[a-z0-9_]+)\s*\(", hdr)) - {"rt_status"}
+    bound = set(re.findall(r"pub fn (rt_[a-z0-9_]+)\s*\(", rs))
+    assert declared == bound, declared ^ bound
+    for name in ("rt_primitive", "rt_texture", "rt_material", "rt_disney", "rt_light", "rt_camera", "rt_ray", "rt_hit", "rt_shadow_query", "rt_integrator_desc", "rt_film_desc",
+                 "rt_counters", "rt_build_stats"):
+        c_body = re.search(r"typedef struct " + name + r" \{(.*?)\} " + name + r";", hdr, re.S).group(1)
+        c_body = re.sub(r"/\*.*?\*/", "", c_body, flags=re.S)
+        c_fields = []
+        for decl in c_body.split(";"):
+            decl = decl.strip()
+            if not decl:
+                continue
+            for part in decl.split(",")[0:1] + [p for p in decl.split(",")[1:]]:
+                c_fields.append(re.sub(r"\[.*\]", "", part.strip().split()[-1]).lstrip("*"))
+        r_body = re.search(r"pub struct " + name + r" \{(.*?)\n\}", rs, re.S).group(1)
+        r_fields = [f.rstrip("_") if f in ("type_",) else f for f in re.findall(r"pub (\w+):", r_body)]
+        assert c_fields == r_fields, (name, c_fields, r_fields)

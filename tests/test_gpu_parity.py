@@ -6,6 +6,8 @@ normals within 1e-10 absolute (the device runs the reference's f64 expression or
 covers libm vs CUDA transcendental rounding in sphere records).  Rendered films use the same
 counter-based RNG on both sides, so they are compared per pixel, not just statistically.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -13,6 +15,7 @@ import orc
 from rustraytracer_b200 import Film, IntType, _native as N, get_intersection, make_rays, render_samples, scenes, unoccluded
 
 pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 NONE = N.RT_NONE
 T_RTOL = 1e-12
 N_ATOL = 1e-10
@@ -591,7 +594,9 @@ def test_device_lbvh_build_gives_the_same_hits(name, kw):
     b = hs.upload(build="lbvh")
     sa, sb = a.build_stats(), b.build_stats()
     assert sa["mode"] == N.BUILD_HOST_SAH and sb["mode"] == N.BUILD_DEVICE_LBVH and 0 < sb["max_stack"] <= 64 and sb["nodes"] > 0
-    assert a.device_bytes()["leaves"] == b.device_bytes()["leaves"]
+    # same leaf records, except that the host build leaves the scene's few direct shapes (traverse.cuh:direct_shapes) out of the tree while the
+    # device build keeps a dead 80-byte slot for each
+    assert 0 <= b.device_bytes()["leaves"] - a.device_bytes()["leaves"] <= 8 * 80
     cam = hs.camera()
     rays = cam.primary_rays(res, res)
     ha, hb = get_intersection(a, rays), get_intersection(b, rays)
@@ -683,3 +688,162 @@ def test_device_slot_records_degenerate_uv_and_mixed_primitives():
     assert ha.tobytes() == hb.tobytes()
     assert (hb["prim_index"] != NONE).mean() > 0.1 and not (hb["prim_index"] == 0).any() and (hb["prim_index"] == 3).any()
     compare_hits(hb, orc.OracleScene(t).intersect(rays, mode=0), None, "degenerate uv, mixed prims")
+
+
+# ---------------------------------------------------------------- round 2: configs at their own sizes, containment, progressive reads
+def test_soup_parity_subset_on_both_trees():
+    """configs[4] the way tools/soup_parity.py runs it at 1 M - 50 M triangles, here at 1 M: a strided subset of the
+    coherent and the incoherent batch traced with rt_closest_device on the host-SAH tree AND the device LBVH, ids exact-or-tied and t rel
+    1e-12 against the oracle's hit set (mode 3 = the reference's predicate over a tree, equal to brute force)."""
+    import ctypes as C
+    import sys
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import soup_parity
+    torch.cuda.set_device(0)
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    row = soup_parity.run_size(1_000_000, 1024, 1 << 16, "cuda:0", stream, os.cpu_count() or 8)
+    for b in ("sah", "lbvh"):
+        for k in ("coherent", "incoherent"):
+            c = row[b][k]
+            assert c["ok"] and c["id_mismatch"] == 0 and c["max_rel_t_err"] <= 1e-12, (b, k, c)
+            assert c["hits"] > 0.3 * c["rays"]
+    assert row["lbvh"]["builder"] == "device LBVH" and row["sah"]["builder"] == "host binned SAH"
+
+
+def test_f32_headline_mode_at_1024_rows():
+    """The bench's headline mode (RT_SHADE_F32) at the headline size: dragon 1024^2, depth 8, 64 pixel rows x 32 spp, against the f64 oracle at
+    the SAME (pixel, sample) RNG keys — so the comparison is per pixel, not statistical — plus SURVEY §8c's image criterion against an
+    independent oracle estimate R at 4x the samples: relMSE(G, R) <= 1.5 relMSE(O, R) and mean bias <= 1 % (+ the oracle's own seed-to-seed spread,
+    printed)."""
+    w = h = 1024
+    S = 32
+    rows = list(range(7, h, 16))[:64]
+    hs = scenes.HostScene("plastic_dragon", w, h)
+    gpu = hs.upload()
+    cam = hs.camera()
+    film = Film(w, h)
+    for y in rows:
+        render_samples(gpu, cam, IntType.Path(8, shade_f32=True), film, w, h, 0, S, seed=2024, window=(0, y, w, y + 1))
+    G = film.read()
+    oracle = orc.OracleScene(hs.tables())
+    threads = os.cpu_count() or 8
+    O = np.zeros((h, w, 4)); R = np.zeros((h, w, 4))
+    for y in rows:
+        oracle.render(cam, w, h, 0, S, seed=2024, max_depth=8, window=(0, y, w, y + 1), film=O, threads=threads)
+    for y in rows[::4]:
+        oracle.render(cam, w, h, 0, 4 * S, seed=99, max_depth=8, window=(0, y, w, y + 1), film=R, threads=threads)
+    sel = np.zeros((h, w), dtype=bool); sel[rows] = True
+    assert np.array_equal(G[..., 3], O[..., 3]) and np.all(G[sel][:, 3] == S)
+    g, o = G[sel][:, :3] / S, O[sel][:, :3] / S
+    # per pixel, same keys: f32 rounding only, except where a knife-edge branch (u < F, roulette) flips
+    err = np.abs(g - o).max(-1) / (np.abs(o).max(-1) + 1e-6)
+    assert (err > 1e-3).mean() < 0.03, f"{(err > 1e-3).mean():.4f} of the pixels differ by more than 1e-3"
+    rel_go = np.mean((g - o) ** 2 / (o ** 2 + 1e-2))
+    bias_go = abs(g.mean() - o.mean()) / o.mean()
+    # independent estimate on every 4th of those rows
+    sel4 = np.zeros((h, w), dtype=bool); sel4[rows[::4]] = True
+    r = R[sel4][:, :3] / (4 * S); g4 = G[sel4][:, :3] / S; o4 = O[sel4][:, :3] / S
+    rel = lambda a: np.mean((a - r) ** 2 / (r ** 2 + 1e-2))
+    spread = abs(o4.mean() - r.mean()) / r.mean()
+    bias_gr = abs(g4.mean() - r.mean()) / r.mean()
+    print(f"f32 headline mode, {len(rows)} rows x {S} spp: relMSE(G,O) {rel_go:.3g}, mean bias vs O {bias_go:.3g}; relMSE vs R: gpu {rel(g4):.4g} oracle {rel(o4):.4g}; "
+          f"mean bias vs R: gpu {bias_gr:.4g}, oracle seed-to-seed spread {spread:.4g}")
+    assert rel_go <= 1e-4 and bias_go <= 1e-3
+    assert rel(g4) <= 1.5 * rel(o4)
+    assert bias_gr <= 0.01 + spread
+
+
+def test_wavefront_queue_overflow_is_contained(monkeypatch):
+    """Advisor r01 (medium): a branching integrator whose queues outgrow the wavefront must end in a clean RT_ERR_STATE — counters clamped on
+    the device, no out-of-bounds queue reads, no sticky CUDA fault — and leave the scene usable.  With the lobes compute_scattering builds
+    (allow_lobes = true: smooth glass is ONE FresnelSpecular lobe, never a reflection + transmission pair) the admission cap W / max(2, n_lights)
+    cannot overflow by itself, so the test lifts the cap through the library's test hook: Direct{UniformAll} then appends one shadow and one
+    probe entry per light per vertex into queues sized for a third of that."""
+    from rustraytracer_b200._native import RtError
+    gpu = orc.upload_tables(orc.delta_light_tables(area_light=True))       # four lights
+    gpu.commit()
+    gpu.set_wavefront_size(1024)
+    from rustraytracer_b200 import Camera
+    cam = Camera.new((0., 3., -9.), (0., 1., 0.), (0., 1., 0.), 1.0, 40., 0.0, 10.)
+    w = h = 64
+    film = Film(w, h)
+    direct_all = IntType.Direct(4, "UniformAll")
+    monkeypatch.setenv("RT_TEST_FORCE_CAP", "1024")
+    with pytest.raises(RtError) as e:
+        render_samples(gpu, cam, direct_all, film, w, h, 0, 4, seed=3)
+    assert e.value.status == N.RT_ERR_STATE and "overflow" in str(e.value)
+    assert np.isfinite(film.read()).all()                 # whatever was accumulated before the abort is well-formed
+    monkeypatch.delenv("RT_TEST_FORCE_CAP")
+    # no sticky error: the same scene and wavefront render normally once the cap is back
+    f2 = Film(w, h)
+    render_samples(gpu, cam, direct_all, f2, w, h, 0, 2, seed=3)
+    assert np.all(f2.read()[..., 3] == 2)
+    f3 = Film(w, h)
+    render_samples(gpu, cam, IntType.Path(8), f3, w, h, 0, 2, seed=3)
+    assert np.all(f3.read()[..., 3] == 2)
+
+
+def test_progressive_film_reads_during_render():
+    """render::progressive_multithread's 50 ms saver thread (render.rs:117-153, 161-324) ⇔ rt_film_read / rt_film_resolve_rgb8 from a second
+    thread while rt_render runs: reads never block on the render, the running sums only grow, and the final film is the blocking render's."""
+    import threading
+    import time
+    w = h = 256
+    hs = scenes.HostScene("cornell_box", w, h)
+    gpu = hs.upload()
+    gpu.set_wavefront_size(1 << 14)                      # many iterations: the render takes long enough to be observed
+    cam = hs.camera()
+    film = Film(w, h)
+    spp = 64
+    done = threading.Event()
+
+    def run():
+        render_samples(gpu, cam, IntType.Path(6, shade_f32=True), film, w, h, 0, spp, seed=5)
+        done.set()
+    th = threading.Thread(target=run); th.start()
+    snaps = []
+    while not done.is_set() and len(snaps) < 400:
+        s = film.read()
+        png = film.resolve_rgb8()
+        assert png.shape == (h, w, 3)
+        snaps.append(float(s[..., :3].sum()))
+        time.sleep(0.002)
+    th.join()
+    final = film.read()
+    assert np.all(final[..., 3] == spp)
+    assert len(snaps) >= 2 and all(b >= a - 1e-9 for a, b in zip(snaps, snaps[1:])) and snaps[-1] <= final[..., :3].sum() + 1e-6
+    assert snaps[0] < final[..., :3].sum()               # at least one read saw the render in flight
+    ref = Film(w, h)
+    render_samples(gpu, cam, IntType.Path(6, shade_f32=True), ref, w, h, 0, spp, seed=5)
+    assert np.allclose(ref.read(), final, rtol=1e-9, atol=1e-12)
+
+
+def test_render_multi_matches_single_gpu():
+    """rt_render_multi (SURVEY §8e behind the ABI): two GPUs of one process, scene replicated, sample range split, films summed by the library's
+    ncclAllReduce — equals the single-GPU render of the same samples (RNG keyed by the global sample index) up to the order of the f64 sums."""
+    from rustraytracer_b200 import Comm, render_multi, replicate
+    from rustraytracer_b200._native import check, lib
+    if lib().rt_device_count() < 2:
+        pytest.skip("needs two GPUs")
+    w = h = 128
+    hs = scenes.HostScene("cornell_box", w, h)
+    check(lib().rt_set_device(0))
+    g0 = hs.upload()
+    cam = hs.camera()
+    ref = Film(w, h)
+    render_samples(g0, cam, IntType.Path(8), ref, w, h, 3, 19, seed=11)
+    g1 = replicate(g0, 1)
+    f0 = Film(w, h)
+    check(lib().rt_set_device(1))
+    f1 = Film(w, h)
+    check(lib().rt_set_device(0))
+    comm = Comm.local([0, 1])
+    assert comm.size() == (2, 2)
+    render_multi(comm, [g0, g1], [f0, f1], cam, IntType.Path(8), w, h, 3, 19, seed=11)
+    A, B, R = f0.read(), f1.read(), ref.read()
+    assert np.array_equal(A, B)                          # all-reduce: both devices hold the total
+    assert np.all(A[..., 3] == 16) and np.allclose(A, R, rtol=1e-9, atol=1e-12)
+    c0, c1 = g0.counters(), g1.counters()
+    assert c0["paths"] == c1["paths"] == w * h * 8
+    comm.close()
