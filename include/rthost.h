@@ -26,7 +26,7 @@ typedef struct rth_params {
                                     two_dragons: 0 = as committed (metal dragon only), 1 = glass + metal
                                     (commented block scenes.rs:608-611 enabled);
                                     material_hdr: mat_num 0 smooth plastic, 1 rose-gold metal, 2 mirror,
-                                    3 glass (scenes.rs:627,712-718)                                     */
+                                    3 glass (scenes.rs:627,712-718), 4 disney_mat (scenes.rs:867-904)                                     */
     uint32_t    _pad;
     uint64_t    n_tris;          /* soup: triangle count; dragon/statue stand-ins: 0 = default          */
     uint64_t    seed;            /* generators                                                          */
@@ -58,6 +58,9 @@ rt_status   rth_scene_copy_transforms(const rth_scene* s, double* out16_each);
 rt_status   rth_scene_copy_textures(const rth_scene* s, rt_texture* out);
 rt_status   rth_scene_copy_materials(const rth_scene* s, rt_material* out);
 rt_status   rth_scene_copy_lights(const rth_scene* s, rt_light* out);
+/* Material::Disney records (rt_disney), referenced by tex[0] of the RT_MAT_DISNEY materials */
+rt_status   rth_scene_num_disney(const rth_scene* s, uint64_t* n);
+rt_status   rth_scene_copy_disney(const rth_scene* s, rt_disney* out);
 
 /* Hdr / Image texel blocks (Texture::Hdr{data}, Texture::Image{img}); info = width, height, is_hdr;
  * copy writes width*height*3 floats (hdr) or bytes (rgb8)                                             */

@@ -17,13 +17,16 @@ PRIM_SPHERE, PRIM_TRIANGLE, PRIM_XY_RECT, PRIM_XZ_RECT, PRIM_YZ_RECT = range(5)
 TEX_SOLID, TEX_CHECKERED, TEX_HDR, TEX_IMAGE, TEX_PERLIN = 0, 1, 2, 3, 4
 LIGHT_DIFFUSE, LIGHT_INFINITE, LIGHT_POINT, LIGHT_SPOT, LIGHT_DISTANT = range(5)
 SHADE_F32 = 1
-MAT_MATTE, MAT_LIGHT, MAT_PLASTIC, MAT_GLASS, MAT_METAL, MAT_MIRROR = range(6)
+MAT_MATTE, MAT_LIGHT, MAT_PLASTIC, MAT_GLASS, MAT_METAL, MAT_MIRROR, MAT_DISNEY = range(7)
 
 # numpy mirrors of the POD structs (align=True reproduces the C layout)
 prim_dtype = np.dtype([("type", "<u4"), ("flip_face", "<u4"), ("mat_index", "<u4"), ("light_index", "<u4"),
                        ("mesh_index", "<u4"), ("ind", "<u4"), ("transform", "<u4"), ("_pad", "<u4"), ("v", "<f8", (5,))], align=True)
 texture_dtype = np.dtype([("type", "<u4"), ("odd", "<u4"), ("even", "<u4"), ("image", "<u4"), ("color", "<f8", (3,)), ("frequency", "<f8")], align=True)
 material_dtype = np.dtype([("type", "<u4"), ("remap_roughness", "<u4"), ("tex", "<u4", (5,)), ("_pad", "<u4"), ("f", "<f8", (3,))], align=True)
+DISNEY_FIELDS = ("color", "metallic", "eta", "roughness", "specular_tint", "anisotropic", "sheen", "sheen_tint", "clearcoat", "clearcoat_gloss",
+                 "spec_trans", "scatter_distance", "flatness", "diff_trans", "thin", "_pad")
+disney_dtype = np.dtype([(f, "<u4") for f in DISNEY_FIELDS], align=True)
 light_dtype = np.dtype([("type", "<u4"), ("prim_index", "<u4"), ("two_sided", "<u4"), ("text_id", "<u4"), ("color", "<f8", (3,)),
                         ("transform", "<u4"), ("_pad", "<u4"), ("param", "<f8", (3,))], align=True)
 ray_dtype = np.dtype([("origin", "<f8", (3,)), ("dir", "<f8", (3,))], align=True)
@@ -31,7 +34,7 @@ hit_dtype = np.dtype([("t", "<f8"), ("p", "<f8", (3,)), ("n", "<f8", (3,)), ("ns
                       ("prim_index", "<u4"), ("front", "<u4")], align=True)
 shadow_dtype = np.dtype([("p0", "<f8", (3,)), ("p1", "<f8", (3,)), ("p1_prim_index", "<u4"), ("infinite_light", "<u4")], align=True)
 assert prim_dtype.itemsize == 72 and texture_dtype.itemsize == 48 and material_dtype.itemsize == 56
-assert light_dtype.itemsize == 72 and ray_dtype.itemsize == 48 and hit_dtype.itemsize == 104 and shadow_dtype.itemsize == 56
+assert disney_dtype.itemsize == 64 and light_dtype.itemsize == 72 and ray_dtype.itemsize == 48 and hit_dtype.itemsize == 104 and shadow_dtype.itemsize == 56
 
 
 class Camera(C.Structure):
@@ -71,7 +74,7 @@ class BuildStats(C.Structure):
 RTCORE_SYMBOLS = [
     "rt_last_error_string", "rt_version_string", "rt_device_count", "rt_set_device", "rt_round_spp", "rt_camera_look_at",
     "rt_scene_create", "rt_scene_destroy", "rt_scene_add_mesh", "rt_scene_add_transform", "rt_scene_add_primitives",
-    "rt_scene_add_mesh_triangles", "rt_scene_set_light_index", "rt_scene_add_image_hdr", "rt_scene_add_image_rgb8", "rt_scene_add_perlin", "rt_scene_set_textures", "rt_scene_set_materials",
+    "rt_scene_add_mesh_triangles", "rt_scene_set_light_index", "rt_scene_add_image_hdr", "rt_scene_add_image_rgb8", "rt_scene_add_perlin", "rt_scene_add_disney", "rt_scene_set_textures", "rt_scene_set_materials",
     "rt_scene_set_lights", "rt_scene_commit", "rt_scene_num_primitives", "rt_scene_device_bytes", "rt_intersect",
     "rt_intersect_range", "rt_intersect_device", "rt_closest_device", "rt_occluded", "rt_occluded_device", "rt_film_create",
     "rt_film_create_external", "rt_film_destroy", "rt_film_clear", "rt_film_read", "rt_film_resolve_rgb8", "rt_render",
@@ -84,6 +87,7 @@ RTHOST_SYMBOLS = [
     "rth_scene_mesh_sizes", "rth_scene_mesh_copy", "rth_scene_copy_primitives", "rth_scene_copy_transforms", "rth_scene_copy_textures",
     "rth_scene_copy_materials", "rth_scene_copy_lights", "rth_scene_upload", "rth_scene_add_obj", "rth_scene_create_empty", "rth_primary_rays",
     "rth_scene_num_images", "rth_scene_image_info", "rth_scene_image_copy", "rth_load_hdr", "rth_last_error_string",
+    "rth_scene_num_disney", "rth_scene_copy_disney",
 ]
 
 HOST_LIB_PATH = os.environ.get("RT_LIBRTHOST", os.path.join(_HERE, "librthost.so"))
@@ -116,7 +120,7 @@ def _load_core():
         "rt_scene_add_mesh": [vp, u64, vp, u64, vp, u64, vp, u64, vp, vp],
         "rt_scene_add_transform": [vp, vp, vp], "rt_scene_add_primitives": [vp, u64, vp, vp],
         "rt_scene_add_mesh_triangles": [vp, u32, u32, vp], "rt_scene_set_light_index": [vp, u32, u32],
-        "rt_scene_add_image_hdr": [vp, u32, u32, vp, vp], "rt_scene_add_image_rgb8": [vp, u32, u32, vp, vp], "rt_scene_add_perlin": [vp, f64, vp, vp, vp],
+        "rt_scene_add_image_hdr": [vp, u32, u32, vp, vp], "rt_scene_add_image_rgb8": [vp, u32, u32, vp, vp], "rt_scene_add_perlin": [vp, f64, vp, vp, vp], "rt_scene_add_disney": [vp, vp, vp],
         "rt_scene_set_textures": [vp, u64, vp], "rt_scene_set_materials": [vp, u64, vp], "rt_scene_set_lights": [vp, u64, vp],
         "rt_scene_commit": [vp], "rt_scene_num_primitives": [vp, vp], "rt_scene_device_bytes": [vp, vp, vp, vp],
         "rt_intersect": [vp, u64, vp, vp], "rt_intersect_range": [vp, u64, vp, f64, f64, vp],
@@ -157,6 +161,7 @@ def _load_host():
         "rth_primary_rays": [vp, u32, u32, vp],
         "rth_scene_num_images": [vp, vp], "rth_scene_image_info": [vp, u32, vp], "rth_scene_image_copy": [vp, u32, vp],
         "rth_load_hdr": [C.c_char_p, vp, vp, vp, u64],
+        "rth_scene_num_disney": [vp, vp], "rth_scene_copy_disney": [vp, vp],
     }
     for name, args in sigs.items():
         fn = getattr(L, name)

@@ -176,6 +176,14 @@ class Objects:
         l = np.ascontiguousarray(l, dtype=N.light_dtype)
         check(lib().rt_scene_set_lights(self.h, len(l), ptr(l)))
 
+    def add_disney(self, params):
+        """`Material::make_disney(..)` (material.rs:480-516): one rt_disney record (a numpy record of _native.disney_dtype); returns its index,
+        which an RT_MAT_DISNEY material carries in tex[0]."""
+        d = np.ascontiguousarray(params, dtype=N.disney_dtype).reshape(1)
+        out = C.c_uint32()
+        check(lib().rt_scene_add_disney(self.h, ptr(d), C.byref(out)))
+        return out.value
+
     def commit(self):
         """`objects.node = BvhNode::new(..)` (e.g. scenes.rs:368-371): build + flatten + upload."""
         check(lib().rt_scene_commit(self.h))

@@ -168,6 +168,9 @@ rt_status upload_scene(rt_scene& s, HostImage& img) {
     if ((st = up(s, s.xforms, d.xforms, b))) return st;
     if ((st = up(s, s.textures, d.textures, b))) return st;
     if ((st = up(s, s.materials, d.materials, b))) return st;
+    if ((st = up(s, s.disneys, d.disneys, b))) return st;
+    d.has_disney = 0;
+    for (auto& m : s.materials) if (m.type == RT_MAT_DISNEY) d.has_disney = 1;
     if ((st = up(s, img.mat_alpha, d.mat_alpha, b))) return st;
     if ((st = up(s, s.images, d.images, b))) return st;
     if ((st = up(s, s.texels, d.texels, b))) return st;

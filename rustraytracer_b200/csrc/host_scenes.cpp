@@ -31,6 +31,7 @@ struct rth_scene {
     std::vector<double> xforms;                               // 16 each
     std::vector<rt_texture> textures;
     std::vector<rt_material> materials;
+    std::vector<rt_disney> disneys;                           // Material::Disney records (material tex[0] = index)
     std::vector<rt_light> lights;
     struct Image { uint32_t w = 0, h = 0; bool hdr = false; std::vector<float> f; std::vector<uint8_t> b; };   // Texture::Hdr data / Texture::Image img
     std::vector<Image> images;
@@ -529,7 +530,8 @@ void camera_up(rth_scene& s, const double from[3], const double to[3], const dou
     rt::camera_look_at(from, to, up, aspect, vfov, 0.0, 10., 0., 0., &s.camera);     // Camera::new → t0 = t1 = 0
 }
 // scenes.rs:627-741 `material_hdr(mat_num)`: the material-test ball under an HDR environment (Light::Infinite), variant =
-// mat_num: 0 smooth_plastic (:824), 1 rosegold_metal (:839), 2 mirror (:876), 3 glass (:857)
+// mat_num: 0 smooth_plastic (:824), 1 rosegold_metal (:839), 2 mirror (:876), 3 glass (:857); 4 = disney_mat (:867-904), which the
+// reference defines next to the other four but never wires into the match (its `_ =>` arm is glass)
 void build_material_hdr(rth_scene& s, const rth_params& p) {
     const double from[3] = {3.04068, 3.17153, 3.20454}, dir[3] = {-0.583445, -0.538765, -0.60772}, up[3] = {-0.373123, 0.842456, -0.388647};
     const double to[3] = {from[0] + dir[0], from[1] + dir[1], from[2] + dir[2]};
@@ -550,6 +552,18 @@ void build_material_hdr(rth_scene& s, const rth_params& p) {
         case 0: { uint32_t a = push_solid(s, 0.1608, 0.0014767, 0.4), b = push_solid(s, 1., 1., 1.); push_plastic(s, a, b, 0.002, false); break; }
         case 1: { uint32_t a = push_solid(s, 1. - 0.718, 1. - 0.431, 1. - 0.475), b = push_solid(s, 1., 1., 1.), c = push_solid(s, 0.002, 0., 0.); push_metal(s, a, b, c, c, c, true); break; }
         case 2: { uint32_t a = push_solid(s, 1., 1., 1.); push_mirror(s, a); break; }
+        case 4: {   // disney_mat (scenes.rs:867-904): 14 solid textures in declaration order, thin = false
+            const uint32_t c = (uint32_t)s.textures.size();
+            push_solid(s, 0.1608, 0.0014767, 0.4); push_solid(s, 0., 0., 0.); push_solid(s, 1.5, 0., 0.); push_solid(s, 0.5, 0., 0.); push_solid(s, 0., 0., 0.);
+            push_solid(s, 0., 0., 0.); push_solid(s, 0., 0., 0.); push_solid(s, 0.5, 0., 0.); push_solid(s, 0., 0., 0.); push_solid(s, 1., 0., 0.);
+            push_solid(s, 0., 0., 0.); push_solid(s, 0., 0., 0.); push_solid(s, 0., 0., 0.); push_solid(s, 1., 0., 0.);
+            rt_disney d{}; uint32_t* ids = &d.color; for (uint32_t k = 0; k < 14; k++) ids[k] = c + k;      // color .. clearcoat_gloss, spec_trans, scatter_distance, flatness, diff_trans
+            d.thin = 0;
+            s.disneys.push_back(d);
+            rt_material m{}; m.type = RT_MAT_DISNEY; for (int k = 0; k < 5; k++) m.tex[k] = RT_NONE; m.tex[0] = (uint32_t)s.disneys.size() - 1;
+            s.materials.push_back(m);
+            break;
+        }
         default: { push_solid(s, 1. - 0.718, 1. - 0.431, 1. - 0.475); uint32_t b = push_solid(s, 1., 1., 1.); push_solid(s, 0.002, 0., 0.); push_glass(s, b, b, 0.01, 0.01, 1.5, true); break; }
     }
     uint32_t len = (uint32_t)s.textures.size();
@@ -679,6 +693,8 @@ rt_status rth_scene_copy_textures(const rth_scene* s, rt_texture* out) { if (!s 
 rt_status rth_scene_copy_materials(const rth_scene* s, rt_material* out) { if (!s || !out) return RT_ERR_INVALID; memcpy(out, s->materials.data(), s->materials.size() * sizeof(rt_material)); return RT_OK; }
 rt_status rth_scene_copy_lights(const rth_scene* s, rt_light* out) { if (!s || !out) return RT_ERR_INVALID; memcpy(out, s->lights.data(), s->lights.size() * sizeof(rt_light)); return RT_OK; }
 
+rt_status rth_scene_num_disney(const rth_scene* s, uint64_t* n) { if (!s || !n) return RT_ERR_INVALID; *n = s->disneys.size(); return RT_OK; }
+rt_status rth_scene_copy_disney(const rth_scene* s, rt_disney* out) { if (!s || !out) return RT_ERR_INVALID; memcpy(out, s->disneys.data(), s->disneys.size() * sizeof(rt_disney)); return RT_OK; }
 rt_status rth_scene_num_images(const rth_scene* s, uint64_t* n) { if (!s || !n) return RT_ERR_INVALID; *n = s->images.size(); return RT_OK; }
 rt_status rth_scene_image_info(const rth_scene* s, uint32_t i, uint32_t info[3]) {
     if (!s || !info || i >= s->images.size()) return RT_ERR_INVALID;
@@ -713,6 +729,7 @@ struct CoreApi {
     rt_status (*set_lights)(rt_scene*, uint64_t, const rt_light*) = nullptr;
     rt_status (*add_mesh_triangles)(rt_scene*, uint32_t, uint32_t, uint32_t*) = nullptr;
     rt_status (*add_primitives)(rt_scene*, uint64_t, const rt_primitive*, uint32_t*) = nullptr;
+    rt_status (*add_disney)(rt_scene*, const rt_disney*, uint32_t*) = nullptr;
     bool ok = false;
 };
 const CoreApi& core_api() {
@@ -729,7 +746,7 @@ const CoreApi& core_api() {
         auto bind = [&](auto& fn, const char* name) { fn = reinterpret_cast<std::remove_reference_t<decltype(fn)>>(dlsym(h, name)); if (!fn) { all = false; host_error(std::string("rth_scene_upload: missing symbol ") + name); } };
         bind(api.add_image_hdr, "rt_scene_add_image_hdr"); bind(api.add_image_rgb8, "rt_scene_add_image_rgb8"); bind(api.add_mesh, "rt_scene_add_mesh");
         bind(api.add_transform, "rt_scene_add_transform"); bind(api.set_textures, "rt_scene_set_textures"); bind(api.set_materials, "rt_scene_set_materials");
-        bind(api.set_lights, "rt_scene_set_lights"); bind(api.add_mesh_triangles, "rt_scene_add_mesh_triangles"); bind(api.add_primitives, "rt_scene_add_primitives");
+        bind(api.set_lights, "rt_scene_set_lights"); bind(api.add_mesh_triangles, "rt_scene_add_mesh_triangles"); bind(api.add_primitives, "rt_scene_add_primitives"); bind(api.add_disney, "rt_scene_add_disney");
         api.ok = all;
     });
     return api;
@@ -752,6 +769,7 @@ rt_status rth_scene_upload(const rth_scene* s, rt_scene* dst) {
     }
     for (size_t i = 0; i < s->xforms.size() / 16; i++) if ((st = core.add_transform(dst, &s->xforms[16 * i], nullptr))) return st;
     if ((st = core.set_textures(dst, s->textures.size(), s->textures.data()))) return st;
+    for (auto& d : s->disneys) if ((st = core.add_disney(dst, &d, nullptr))) return st;
     if ((st = core.set_materials(dst, s->materials.size(), s->materials.data()))) return st;
     if ((st = core.set_lights(dst, s->lights.size(), s->lights.data()))) return st;
     for (auto& it : s->items) {

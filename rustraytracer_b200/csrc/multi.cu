@@ -171,7 +171,7 @@ rt_status rt_scene_replicate(const rt_scene* src, int32_t device, rt_scene** out
     if (device < 0 || device >= count) { set_error("rt_scene_replicate: device index out of range"); return RT_ERR_INVALID; }
     rt_scene* s = new rt_scene();
     s->meshes = src->meshes; s->prims = src->prims; s->shapes = src->shapes; s->xforms = src->xforms; s->textures = src->textures;
-    s->materials = src->materials; s->lights = src->lights; s->images = src->images; s->texels = src->texels; s->perlin = src->perlin;
+    s->materials = src->materials; s->disneys = src->disneys; s->lights = src->lights; s->images = src->images; s->texels = src->texels; s->perlin = src->perlin;
     s->build_mode = src->build_mode; s->wavefront_size = src->wavefront_size;
     int prev = 0; cudaGetDevice(&prev);
     rt_status st = RT_ERR_CUDA;

@@ -542,7 +542,7 @@ rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc*
     size_t n_ev = 2;
     CK(cudaEventRecord(e_begin, st));
     int cur = 0; uint64_t iter = 0; bool done = false; rt_status result = RT_OK;
-    const bool f32 = (integ->flags & RT_SHADE_F32) != 0 && !s->d.has_perlin && !s->d.has_delta;   // Texture::Perlin and the delta lights are evaluated by the f64 kernels only (shade.cuh:tex_value_at, delta_sample_li)
+    const bool f32 = (integ->flags & RT_SHADE_F32) != 0 && !s->d.has_perlin && !s->d.has_delta && !s->d.has_disney;   // Texture::Perlin and the delta lights are evaluated by the f64 kernels only (shade.cuh:tex_value_at, delta_sample_li)
     const bool trace = getenv("RT_TRACE_ITER") != nullptr;     // debugging aid: per-iteration sizes and kernel times on stderr
     if (trace && !w.dbg[0]) { cudaEventCreate(&w.dbg[0]); cudaEventCreate(&w.dbg[1]); }
     while (!done) {

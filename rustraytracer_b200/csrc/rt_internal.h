@@ -83,12 +83,14 @@ struct DScene {
     const double* points; const double* normals; const double* uvs; const uint32_t* tri_index;
     const double* shapes; const DXform* xforms;
     const rt_texture* textures; const rt_material* materials; const DLight* lights;
+    const rt_disney* disneys;                 // Material::Disney records, indexed by the material's tex[0]
     const DImage* images; const uint32_t* texels;
     const double* perlin;                     // PERLIN_STRIDE doubles per Texture::Perlin: scale, perm_x[256], perm_y[256], perm_z[256], 256 gradient vectors
     const double* mat_alpha;                  // 2 per material: the microfacet alphas of Plastic / Glass / solid-textured Metal after the optional
                                               // roughness remap (microfacet.rs:442-446: an f64 log per shaded vertex otherwise); NaN = evaluate on the device
     uint32_t n_nodes, n_prims, n_lights, n_slots;
     uint32_t has_infinite, has_perlin;        // any Light::Infinite in `lights` (misses then emit, light.rs:499-513); any Texture::Perlin
+    uint32_t has_disney, pad1_;               // any Material::Disney (f64 shade kernels only)
     uint32_t has_delta, n_direct;             // any Point / Spot / Distant light (f64 shade kernels only); direct shapes (below)
     // the scene's few parametric shapes when they are kept OUT of the tree and tested once per ray before the walk (traverse.cuh:direct_shapes)
     uint32_t direct[MAX_DIRECT];

@@ -14,6 +14,7 @@ struct rt_scene {
     std::vector<rt::DXform> xforms;
     std::vector<rt_texture> textures;
     std::vector<rt_material> materials;
+    std::vector<rt_disney> disneys;          // rt_scene_add_disney
     std::vector<rt_light> lights;
     std::vector<rt::DImage> images;          // Hdr / Image texel blocks (rt_scene_add_image_*)
     std::vector<uint32_t> texels;

@@ -181,7 +181,13 @@ rt_status build_host_image(const rt_scene& s, HostImage& img, bool device_build)
         if (p.mat >= s.materials.size()) { set_error("primitive " + std::to_string(i) + ": mat_index out of range"); return RT_ERR_INVALID; }
         if (p.light != RT_NONE && p.light >= s.lights.size()) { set_error("primitive: light_index out of range"); return RT_ERR_INVALID; }
     }
+    for (auto& m : s.materials) if (m.type == RT_MAT_DISNEY) {
+        if (m.tex[0] >= s.disneys.size()) { set_error("Disney material: record index out of range (rt_scene_add_disney first)"); return RT_ERR_INVALID; }
+        const uint32_t* ids = &s.disneys[m.tex[0]].color;       // the 14 texture ids are the record's first 14 words
+        for (int k = 0; k < 14; k++) if (ids[k] >= s.textures.size()) { set_error("Disney material: texture id out of range"); return RT_ERR_INVALID; }
+    }
     for (auto& m : s.materials) for (int k = 0; k < 5; k++) {
+        if (m.type == RT_MAT_DISNEY) break;
         int used = m.type == RT_MAT_METAL ? 5 : (m.type == RT_MAT_PLASTIC || m.type == RT_MAT_GLASS ? 2 : 1);
         if (k < used && m.tex[k] != RT_NONE && m.tex[k] >= s.textures.size()) { set_error("material: texture id out of range"); return RT_ERR_INVALID; }
         if (k < used && m.tex[k] == RT_NONE && !(m.type == RT_MAT_METAL && k >= 3)) { set_error("material: missing texture id"); return RT_ERR_INVALID; }
@@ -499,9 +505,16 @@ rt_status rt_scene_add_perlin(rt_scene* s, double scale, const uint32_t* perm, c
     if (out) *out = (uint32_t)(base / PERLIN_STRIDE);
     return RT_OK;
 }
+// Material::make_disney (material.rs:480-516)
+rt_status rt_scene_add_disney(rt_scene* s, const rt_disney* d, uint32_t* out) {
+    if (!s || !d) { set_error("rt_scene_add_disney: null argument"); return RT_ERR_INVALID; }
+    s->disneys.push_back(*d); s->committed = false;
+    if (out) *out = (uint32_t)s->disneys.size() - 1;
+    return RT_OK;
+}
 rt_status rt_scene_set_materials(rt_scene* s, uint64_t n, const rt_material* m) {
     if (!s || (n && !m)) { set_error("rt_scene_set_materials: null argument"); return RT_ERR_INVALID; }
-    for (uint64_t i = 0; i < n; i++) if (m[i].type > RT_MAT_MIRROR) { set_error("rt_scene_set_materials: unsupported material type"); return RT_ERR_INVALID; }
+    for (uint64_t i = 0; i < n; i++) if (m[i].type > RT_MAT_DISNEY) { set_error("rt_scene_set_materials: unsupported material type"); return RT_ERR_INVALID; }
     s->materials.assign(m, m + n); s->committed = false; return RT_OK;
 }
 rt_status rt_scene_set_lights(rt_scene* s, uint64_t n, const rt_light* l) {

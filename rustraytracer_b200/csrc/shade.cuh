@@ -212,19 +212,21 @@ template <class R> static __device__ RT_HELPER V3<R> fr_conductor(R cos_theta_i,
 }
 
 // ---- lobes (bxdf.rs:213-300, in-scope subset) kept in registers/local memory: no heap, no Vec<Box<..>>
-enum { F_DIELECTRIC = 0, F_CONDUCTOR = 1, F_NOOP = 2 };
-enum { L_LAMBERT = 0, L_OREN_NAYAR = 1, L_SPEC_R = 2, L_SPEC_T = 3, L_FRESNEL_SPEC = 4, L_MICRO_R = 5, L_MICRO_T = 6 };
+enum { F_DIELECTRIC = 0, F_CONDUCTOR = 1, F_NOOP = 2, F_DISNEY = 3 };
+// every lobe a Material can build (bxdf.rs:213-300); ScaledBxdf and FresnelBlend have constructors but no call site in the reference
+enum { L_LAMBERT = 0, L_OREN_NAYAR = 1, L_SPEC_R = 2, L_SPEC_T = 3, L_FRESNEL_SPEC = 4, L_MICRO_R = 5, L_MICRO_T = 6,
+       L_DISNEY_DIFFUSE = 7, L_DISNEY_FAKESS = 8, L_DISNEY_RETRO = 9, L_DISNEY_SHEEN = 10, L_DISNEY_CLEARCOAT = 11, L_LAMBERT_T = 12 };
 // Compile-time lobe/fresnel masks: the shade kernel is specialised per material type (the bins extend fills), and each
 // specialisation only keeps the arms its material can build — small kernels that fit the instruction cache instead of
 // one 200 KB kernel (profiles/shade_r01_notes.md).  KM_ALL keeps every arm.
-constexpr uint32_t KM_F_SHIFT = 8;
+constexpr uint32_t KM_F_SHIFT = 16;
 __host__ __device__ constexpr uint32_t km(int k) { return 1u << k; }
 __host__ __device__ constexpr uint32_t kmf(int f) { return 1u << (KM_F_SHIFT + f); }
 constexpr uint32_t KM_ALL = 0xffffffffu;
 // A material whose lobes are only Lambert / Oren-Nayar (Matte, Light) gets its BSDF code inlined into the shade kernel: the code is
 // small, and as calls the Bsdf / Lobe structs go through local memory on every call (ncu r01: 14 % of the matte kernel's
 // instructions were local loads / stores).  The heavy materials keep the calls: inlined, their kernels overflow the instruction cache.
-__host__ __device__ constexpr bool km_small(uint32_t KM) { return SHADE_INLINE_SMALL >= 2 || (SHADE_INLINE_SMALL == 1 && (KM & 0xffu & ~(km(0) | km(1))) == 0u); }
+__host__ __device__ constexpr bool km_small(uint32_t KM) { return SHADE_INLINE_SMALL >= 2 || (SHADE_INLINE_SMALL == 1 && (KM & 0xffffu & ~(km(0) | km(1))) == 0u); }
 #define KM_HAS(k) ((KM & km(k)) != 0u)
 #define KM_HASF(f) ((KM & kmf(f)) != 0u)
 template <class R> struct Lobe {
@@ -232,17 +234,34 @@ template <class R> struct Lobe {
     V3<R> color;              // color / r
     V3<R> aux;                // FresnelSpecular t ; conductor k
     V3<R> eta3;               // conductor eta
-    R a, b;                   // OrenNayer A,B ; or dielectric fresnel eta_i, eta_t
+    R a, b;                   // OrenNayer A,B ; dielectric fresnel eta_i, eta_t ; DisneyFresnel metallic, eta (r0 in eta3) ;
+                              // DisneyFakeSS / DisneyRetro roughness (a) ; DisneyClearCoat weight (a), gloss (b)
     int fresnel;
-    bool mfd_empty; R alpha_x, alpha_y;
+    bool mfd_empty, mfd_disney; R alpha_x, alpha_y;     // mfd_disney: MicrofacetDistribution::DisneyMicrofacet — TrowbridgeReitz with the separable G
     R eta_a, eta_b;
 };
-template <class R> struct Bsdf { V3<R> ns, ng, ss, ts; int n; bool empty; Lobe<R> lobes[2]; };
+// at most 2 lobes for Matte .. Mirror; Material::Disney builds up to 8 (material.rs:245-394) and is shaded by the f64 kernels only
+template <class R> struct Bsdf { V3<R> ns, ng, ss, ts; int n; bool empty; Lobe<R> lobes[sizeof(R) == 8 ? 8 : 2]; };
 
+// helpers of the Disney lobes (bxdf.rs:73-108, util.rs:173-183)
+template <class R> __device__ __forceinline__ R lerp_r(R t, R mn, R mx) { return (R(1) - t) * mn + t * mx; }
+template <class R> __device__ __forceinline__ R schlick_weight(R u) { const R m = clampr(R(1) - u, R(0), R(1)); const R m2 = m * m; return m2 * m2 * m; }
+template <class R> __device__ __forceinline__ V3<R> fr_schlick(V3<R> r0, R cos_theta) { const R w = schlick_weight<R>(cos_theta); return r0 + w * (v3<R>(R(1), R(1), R(1)) - r0); }
+template <class R> static __device__ RT_HELPER R gtr1(R cos_theta, R a) {
+    if (cos_theta > R(1)) return inv_pi<R>();
+    const R a2 = a * a;
+    return (a2 - R(1)) / (pi<R>() * log(a2) * (R(1) + (a2 - R(1)) * cos_theta * cos_theta));
+}
+template <class R> __device__ __forceinline__ R smithg_ggx(R cos_theta, R alpha) { const R a2 = alpha * alpha, c2 = cos_theta * cos_theta; return R(2) / (R(1) + sqrt(a2 + (R(1) - a2) * c2)); }
 // Fresnel::evaluate (bxdf.rs:190-211); dielectric arm passes (|cos|, eta_t, eta_i)
 template <class R, uint32_t KM> __device__ __forceinline__ V3<R> fresnel_eval(const Lobe<R>& l, R cos_theta_i) {
     if (KM_HASF(F_DIELECTRIC) && l.fresnel == F_DIELECTRIC) { R v = fr_dielectric<R>(fabs(cos_theta_i), l.b, l.a); return v3<R>(v, v, v); }
     if (KM_HASF(F_CONDUCTOR) && l.fresnel == F_CONDUCTOR) return fr_conductor<R>(fabs(cos_theta_i), l.eta3, l.aux);
+    if (KM_HASF(F_DISNEY) && l.fresnel == F_DISNEY) {            // bxdf.rs:199-208: no |cos| here; r0 = eta3, metallic = a, eta = b
+        const R mn = fr_dielectric<R>(cos_theta_i, R(1), l.b);
+        const V3<R> mx = fr_schlick<R>(l.eta3, cos_theta_i);
+        return v3<R>(lerp_r<R>(l.a, mn, mx.x), lerp_r<R>(l.a, mn, mx.y), lerp_r<R>(l.a, mn, mx.z));
+    }
     return v3<R>(R(1), R(1), R(1));
 }
 // ---- microfacet.rs, TrowbridgeReitz{sample_visible_area:true} / Empty
@@ -265,7 +284,10 @@ template <class R> static __device__ RT_HELPER R mfd_lambda(const Lobe<R>& m, V3
     return (R(-1) + sqrt(R(1) + a2t2)) / R(2);
 }
 template <class R> __device__ __forceinline__ R mfd_g1(const Lobe<R>& m, V3<R> w) { return R(1) / (R(1) + mfd_lambda(m, w)); }
-template <class R> __device__ __forceinline__ R mfd_g(const Lobe<R>& m, V3<R> wo, V3<R> wi) { return R(1) / (R(1) + mfd_lambda(m, wo) + mfd_lambda(m, wi)); }
+template <class R> __device__ __forceinline__ R mfd_g(const Lobe<R>& m, V3<R> wo, V3<R> wi) {       // microfacet.rs:146-157
+    if (sizeof(R) == 8 && m.mfd_disney) return mfd_g1(m, wo) * mfd_g1(m, wi);                       // DisneyMicrofacet: separable
+    return R(1) / (R(1) + mfd_lambda(m, wo) + mfd_lambda(m, wi));
+}
 template <class R> __device__ __forceinline__ R mfd_pdf(const Lobe<R>& m, V3<R> wo, V3<R> wh) {                                // microfacet.rs:159-172
     if (!m.mfd_empty) return mfd_d(m, wh) * mfd_g1(m, wo) * fabs(dot(wo, wh)) / abs_cos_theta(wo);
     return mfd_d(m, wh) * abs_cos_theta(wh);
@@ -349,6 +371,34 @@ template <class R, uint32_t KM> __device__ __forceinline__ V3<R> lobe_f_impl(con
             return c * fabs(mfd_d(l, wh) * mfd_g(l, wo, wi) * eta * eta * fabs(dot(wi, wh)) * fabs(dot(wo, wh)) * factor * factor /
                             (cti * cto * sqrt_denom * sqrt_denom));
         }
+        if (KM_HAS(L_LAMBERT_T) && l.kind == L_LAMBERT_T) return l.color * inv_pi<R>();                    // bxdf.rs:337
+        if (KM_HAS(L_DISNEY_DIFFUSE) && l.kind == L_DISNEY_DIFFUSE) {                                      // bxdf.rs:465-470
+            const R fo = schlick_weight<R>(abs_cos_theta(wo)), fi = schlick_weight<R>(abs_cos_theta(wi));
+            return (inv_pi<R>() * (R(1) - fo / R(2)) * (R(1) - fi / R(2))) * l.color;
+        }
+        if ((KM_HAS(L_DISNEY_FAKESS) && l.kind == L_DISNEY_FAKESS) || (KM_HAS(L_DISNEY_RETRO) && l.kind == L_DISNEY_RETRO) ||
+            (KM_HAS(L_DISNEY_SHEEN) && l.kind == L_DISNEY_SHEEN) || (KM_HAS(L_DISNEY_CLEARCOAT) && l.kind == L_DISNEY_CLEARCOAT)) {
+            V3<R> wh = wi + wo;
+            if (is_black(wh)) return zero;
+            wh = normalize(wh);
+            const R cos_theta_d = dot(wi, wh);
+            if (l.kind == L_DISNEY_SHEEN) return schlick_weight<R>(cos_theta_d) * l.color;                  // bxdf.rs:505-513
+            if (l.kind == L_DISNEY_CLEARCOAT) {                                                            // bxdf.rs:514-526
+                const R dr = gtr1<R>(abs_cos_theta(wh), l.b);
+                const V3<R> fr = fr_schlick<R>(v3<R>(R(1), R(1), R(1)) * R(0.04), dot(wo, wh));
+                const R gr = smithg_ggx<R>(abs_cos_theta(wo), R(0.25)) * smithg_ggx<R>(abs_cos_theta(wi), R(0.25));
+                return (l.a / R(4) * gr * dr) * fr;
+            }
+            const R fo = schlick_weight<R>(abs_cos_theta(wo)), fi = schlick_weight<R>(abs_cos_theta(wi));
+            if (l.kind == L_DISNEY_FAKESS) {                                                               // bxdf.rs:471-489
+                const R fss90 = cos_theta_d * cos_theta_d * l.a;
+                const R fss = lerp_r<R>(fo, R(1), fss90) * lerp_r<R>(fi, R(1), fss90);
+                const R ss = R(1.25) * (fss * (R(1) / (abs_cos_theta(wo) + abs_cos_theta(wi)) - R(0.5)) + R(0.5));
+                return (inv_pi<R>() * ss) * l.color;
+            }
+            const R rr = R(2) * l.a * cos_theta_d * cos_theta_d;                                            // DisneyRetro bxdf.rs:490-504
+            return (inv_pi<R>() * rr * (fo + fi + fo * fi * (rr - R(1)))) * l.color;
+        }
         return zero;
     }
 }
@@ -359,6 +409,16 @@ template <class R> __device__ __forceinline__ R default_pdf(V3<R> wo, V3<R> wi) 
 template <class R, uint32_t KM> __device__ __forceinline__ R lobe_pdf_impl(const Lobe<R>& l, V3<R> wo, V3<R> wi) {
     {
         if ((KM_HAS(L_LAMBERT) && l.kind == L_LAMBERT) || (KM_HAS(L_OREN_NAYAR) && l.kind == L_OREN_NAYAR) || (KM_HAS(L_SPEC_R) && l.kind == L_SPEC_R)) return default_pdf(wo, wi);
+        if ((KM_HAS(L_DISNEY_DIFFUSE) && l.kind == L_DISNEY_DIFFUSE) || (KM_HAS(L_DISNEY_FAKESS) && l.kind == L_DISNEY_FAKESS) ||
+            (KM_HAS(L_DISNEY_RETRO) && l.kind == L_DISNEY_RETRO) || (KM_HAS(L_DISNEY_SHEEN) && l.kind == L_DISNEY_SHEEN)) return default_pdf(wo, wi);   // bxdf.rs:792-795
+        if (KM_HAS(L_LAMBERT_T) && l.kind == L_LAMBERT_T) return !same_hemisphere(wo, wi) ? abs_cos_theta(wi) * inv_pi<R>() : R(0);                   // bxdf.rs:726-732
+        if (KM_HAS(L_DISNEY_CLEARCOAT) && l.kind == L_DISNEY_CLEARCOAT) {                                                                              // bxdf.rs:796-811
+            if (!same_hemisphere(wo, wi)) return R(0);
+            V3<R> wh = wi + wo;
+            if (is_black(wh)) return R(0);
+            wh = normalize(wh);
+            return gtr1<R>(abs_cos_theta(wh), l.b) * abs_cos_theta(wh) / (R(4) * dot(wo, wh));
+        }
         if (KM_HAS(L_MICRO_R) && l.kind == L_MICRO_R) {
             if (!same_hemisphere(wo, wi)) return R(0);
             V3<R> wh = normalize(wo + wi);
@@ -394,7 +454,34 @@ template <class R, uint32_t KM> __device__ __forceinline__ void lobe_sample_f_im
     const V3<R> zero = v3<R>(R(0), R(0), R(0)), one = v3<R>(R(1), R(1), R(1));
     color = zero; wi = zero; pdf = R(0);
     {
-        if ((KM_HAS(L_LAMBERT) && l.kind == L_LAMBERT) || (KM_HAS(L_OREN_NAYAR) && l.kind == L_OREN_NAYAR)) {             // default_sample_f (bxdf.rs:815-827): ignores `sample`
+        if (KM_HAS(L_LAMBERT_T) && l.kind == L_LAMBERT_T) {            // bxdf.rs:709-717: util::cosine_sample_hemisphere of the SUPPLIED sample (util.rs:69-97)
+            const R ux = R(2) * sample.x - R(1), uy = R(2) * sample.y - R(1);
+            R dx = R(0), dy = R(0);
+            if (!(ux == R(0) && uy == R(0))) {
+                R theta, r;
+                if (fabs(ux) > fabs(uy)) { r = ux; theta = pi<R>() / R(4) * (uy / ux); }
+                else { r = uy; theta = pi<R>() / R(2) - pi<R>() / R(4) * (ux / uy); }
+                dx = r * cos(theta); dy = r * sin(theta);
+            }
+            wi = v3<R>(dx, dy, sqrt(fmax(R(0), R(1) - dx * dx - dy * dy)));
+            if (wi.z > R(0)) wi.z = -wi.z;
+            pdf = lobe_pdf<R, KM>(l, wo, wi); color = lobe_f<R, KM>(l, wo, wi); return;
+        }
+        if (KM_HAS(L_DISNEY_CLEARCOAT) && l.kind == L_DISNEY_CLEARCOAT) {       // bxdf.rs:689-708
+            if (wo.z == R(0)) return;
+            const R alpha2 = l.b * l.b;
+            const R cos_t = sqrt(fmax(R(0), (R(1) - pow(alpha2, R(1) - sample.x)) / (R(1) - alpha2)));
+            const R sin_t = sqrt(fmax(R(0), R(1) - cos_t * cos_t));
+            const R phi = R(2) * pi<R>() * sample.y;
+            V3<R> wh = v3<R>(sin_t * cos(phi), sin_t * sin(phi), cos_t);         // util::make_spherical
+            if (!same_hemisphere(wo, wh)) wh = -wh;
+            const V3<R> w = reflect(wo, normalize(wh));
+            if (!same_hemisphere(wo, w)) return;
+            wi = w; color = lobe_f<R, KM>(l, wo, wi); pdf = lobe_pdf<R, KM>(l, wo, wi); return;
+        }
+        if ((KM_HAS(L_LAMBERT) && l.kind == L_LAMBERT) || (KM_HAS(L_OREN_NAYAR) && l.kind == L_OREN_NAYAR) ||
+            (KM_HAS(L_DISNEY_DIFFUSE) && l.kind == L_DISNEY_DIFFUSE) || (KM_HAS(L_DISNEY_FAKESS) && l.kind == L_DISNEY_FAKESS) ||
+            (KM_HAS(L_DISNEY_RETRO) && l.kind == L_DISNEY_RETRO) || (KM_HAS(L_DISNEY_SHEEN) && l.kind == L_DISNEY_SHEEN)) {     // default_sample_f (bxdf.rs:815-827): ignores `sample`
             wi = rand_cosine_dir<R>(g);
             if (wo.z < R(0)) wi.z *= R(-1);
             pdf = lobe_pdf<R, KM>(l, wo, wi); color = lobe_f<R, KM>(l, wo, wi); return;
@@ -611,7 +698,7 @@ template <bool POINT> __device__ __forceinline__ D3 tex_value_at(const DScene& s
 template <class R> __device__ __forceinline__ void lobe_init(Lobe<R>& l, int kind, uint32_t type, D3 color) {
     const V3<R> zero = v3<R>(R(0), R(0), R(0));
     l.kind = kind; l.type = type; l.color = cast3<R>(color); l.aux = zero; l.eta3 = zero; l.a = R(0); l.b = R(0);
-    l.fresnel = F_NOOP; l.mfd_empty = true; l.alpha_x = R(0); l.alpha_y = R(0); l.eta_a = R(1); l.eta_b = R(1);
+    l.fresnel = F_NOOP; l.mfd_empty = true; l.mfd_disney = false; l.alpha_x = R(0); l.alpha_y = R(0); l.eta_a = R(1); l.eta_b = R(1);
 }
 template <class R> __device__ __forceinline__ void bsdf_new(Bsdf<R>& b, const Rec& r) {                 // bsdf.rs:26-35
     b.ns = cast3<R>(r.sn); b.ng = cast3<R>(r.n); b.ss = cast3<R>(r.sdpdu); b.empty = false;
@@ -627,6 +714,8 @@ template <int MAT> __host__ __device__ constexpr uint32_t mat_km() {
          : MAT == RT_MAT_GLASS ? (km(L_FRESNEL_SPEC) | km(L_MICRO_R) | km(L_MICRO_T) | kmf(F_DIELECTRIC))
          : MAT == RT_MAT_METAL ? (km(L_MICRO_R) | kmf(F_CONDUCTOR))
          : MAT == RT_MAT_MIRROR ? (km(L_SPEC_R) | kmf(F_NOOP))
+         : MAT == RT_MAT_DISNEY ? (km(L_DISNEY_DIFFUSE) | km(L_DISNEY_FAKESS) | km(L_DISNEY_RETRO) | km(L_DISNEY_SHEEN) | km(L_DISNEY_CLEARCOAT) | km(L_LAMBERT_T) |
+                                   km(L_SPEC_T) | km(L_MICRO_R) | km(L_MICRO_T) | kmf(F_DISNEY) | kmf(F_DIELECTRIC))
          : KM_ALL;
 }
 template <class R, int MAT> __device__ __forceinline__ void compute_scattering_impl(const DScene& sc, const Rec& r, Bsdf<R>& b) {
@@ -713,6 +802,72 @@ template <class R, int MAT> __device__ __forceinline__ void compute_scattering_i
             D3 color = tex_value_at<sizeof(R) == 8>(sc, m.tex[0], u, v, r.p);
             if (!is_black(color)) lobe_init(b.lobes[b.n++], L_SPEC_R, BSDF_REFLECTION | BSDF_SPECULAR, color);
             return;
+        }
+        if constexpr (sizeof(R) == 8) {
+        if (mt == RT_MAT_DISNEY) {
+            // material.rs:245-394.  The arm never calls Bsdf::new: the lobes go into the record's Bsdf::empty(), whose frame is
+            // ns = ng = ss = ts = normalize((1,1,1)) (bsdf.rs:37-47) — `b` holds exactly that frame at this point.  Kept as the reference has it.
+            const rt_disney d = sc.disneys[m.tex[0]];
+            auto tex1 = [&](uint32_t id) { return tex_value_at<true>(sc, id, u, v, r.p).x; };
+            const D3 color = tex_value_at<true>(sc, d.color, u, v, r.p);
+            const double metallic_weight = tex1(d.metallic), e = tex1(d.eta), strans = tex1(d.spec_trans);
+            const double diffuse_weight = (1. - metallic_weight) * (1. - strans);
+            const double dt = tex1(d.diff_trans) / 2.;
+            const double rough = tex1(d.roughness);
+            const double lum = 0.2126 * color.x + 0.7152 * color.y + 0.0722 * color.z;       // util::color_to_luminance
+            const D3 white = mk3(1., 1., 1.);
+            const D3 c_tint = lum > 0. ? (1. / lum) * color : white;
+            const double sheen_weight = tex1(d.sheen);
+            auto lerp_d = [](double t, double a, double bb) { return (1. - t) * a + t * bb; };
+            auto lerp_v = [&](double t, D3 a, D3 bb) { return mk3(lerp_d(t, a.x, bb.x), lerp_d(t, a.y, bb.y), lerp_d(t, a.z, bb.z)); };
+            D3 c_sheen = mk3(0., 0., 0.);
+            if (sheen_weight > 0.) c_sheen = lerp_v(tex1(d.sheen_tint), white, c_tint);
+            b.empty = false;
+            if (diffuse_weight > 0.) {
+                if (d.thin) {
+                    const double flat = tex1(d.flatness);
+                    lobe_init(b.lobes[b.n++], L_DISNEY_DIFFUSE, BSDF_DIFFUSE | BSDF_REFLECTION, (diffuse_weight * (1. - flat) * (1. - dt)) * color);
+                    Lobe<R>& l = b.lobes[b.n++];
+                    lobe_init(l, L_DISNEY_FAKESS, BSDF_DIFFUSE | BSDF_REFLECTION, (diffuse_weight * flat * (1. - dt)) * color); l.a = rough;
+                } else {
+                    const D3 sd = tex_value_at<true>(sc, d.scatter_distance, u, v, r.p);
+                    if (is_black(sd)) lobe_init(b.lobes[b.n++], L_DISNEY_DIFFUSE, BSDF_DIFFUSE | BSDF_REFLECTION, diffuse_weight * color);
+                    else {                               // "use bssrdf instead; right now, that doesn't exist, so just specular transmission" (material.rs:300-307)
+                        Lobe<R>& l = b.lobes[b.n++];
+                        lobe_init(l, L_SPEC_T, BSDF_TRANSMISSION | BSDF_SPECULAR, white);
+                        l.fresnel = F_DIELECTRIC; l.a = 1.; l.b = e; l.eta_a = 1.; l.eta_b = e;
+                    }
+                }
+                { Lobe<R>& l = b.lobes[b.n++]; lobe_init(l, L_DISNEY_RETRO, BSDF_DIFFUSE | BSDF_REFLECTION, diffuse_weight * color); l.a = rough; }
+                if (sheen_weight > 0.) lobe_init(b.lobes[b.n++], L_DISNEY_SHEEN, BSDF_DIFFUSE | BSDF_REFLECTION, (diffuse_weight * sheen_weight) * c_sheen);
+            }
+            const double ani = tex1(d.anisotropic);
+            const double aspect = sqrt(1. - ani * 0.9);
+            const double ax = fmax(0.001, rough * rough / aspect), ay = fmax(0.001, rough * rough * aspect);
+            const double spec_tint = tex1(d.specular_tint);
+            const double r0e = (e - 1.) * (e - 1.) / ((e + 1.) * (e + 1.));                  // eta_to_r0
+            const D3 c_spec_0 = lerp_v(metallic_weight, r0e * lerp_v(spec_tint, white, c_tint), color);
+            {   // MicrofacetReflection(white, DisneyFresnel{r0, metallic, eta}, DisneyMicrofacet(ax, ay)); make_disney clamps alpha at 1e-3
+                Lobe<R>& l = b.lobes[b.n++];
+                lobe_init(l, L_MICRO_R, BSDF_REFLECTION | BSDF_GLOSSY, white);
+                l.fresnel = F_DISNEY; l.eta3 = cast3<R>(c_spec_0); l.a = metallic_weight; l.b = e;
+                l.mfd_empty = false; l.mfd_disney = true; l.alpha_x = fmax(ax, 1e-3); l.alpha_y = fmax(ay, 1e-3);
+            }
+            const double cc = tex1(d.clearcoat);
+            if (cc > 0.) { Lobe<R>& l = b.lobes[b.n++]; lobe_init(l, L_DISNEY_CLEARCOAT, BSDF_GLOSSY | BSDF_REFLECTION, mk3(0., 0., 0.)); l.a = cc; l.b = lerp_d(tex1(d.clearcoat_gloss), 0.1, 0.001); }
+            if (strans > 0.) {
+                const D3 t = mk3(strans * sqrt(color.x), strans * sqrt(color.y), strans * sqrt(color.z));
+                Lobe<R>& l = b.lobes[b.n++];
+                lobe_init(l, L_MICRO_T, BSDF_TRANSMISSION | BSDF_GLOSSY, t);
+                l.fresnel = F_DIELECTRIC; l.a = 1.; l.b = e; l.eta_a = 1.; l.eta_b = e; l.mfd_empty = false;
+                if (d.thin) {                            // "approximate with scaled distribution" (Burley 2015): a plain TrowbridgeReitz
+                    const double rscaled = (0.65 * e - 0.35) * rough;
+                    l.alpha_x = fmax(fmax(0.001, rscaled * rscaled / aspect), 1e-3); l.alpha_y = fmax(fmax(0.001, rscaled * rscaled * aspect), 1e-3);
+                } else { l.mfd_disney = true; l.alpha_x = fmax(ax, 1e-3); l.alpha_y = fmax(ay, 1e-3); }
+            }
+            if (d.thin) lobe_init(b.lobes[b.n++], L_LAMBERT_T, BSDF_TRANSMISSION | BSDF_DIFFUSE, dt * color);
+            return;
+        }
         }
     }
 }

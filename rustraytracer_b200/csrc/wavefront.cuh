@@ -344,6 +344,7 @@ template <class R, bool ENVL> inline void launch_shade_bins(const ShadeLaunch& L
     if (L.bin_mask & (1u << (M * 2))) k_shade<R, M, 0, ENVL><<<L.grid, 128, 0, L.stream>>>(L.ctrl, *L.sc, *L.rp, L.in, L.out, L.bin_idx, L.shadow, L.probe, L.film); \
     if (L.bin_mask & (1u << (M * 2 + 1))) k_shade<R, M, 1, ENVL><<<L.grid, 128, 0, L.stream>>>(L.ctrl, *L.sc, *L.rp, L.in, L.out, L.bin_idx, L.shadow, L.probe, L.film);
     RT_SHADE(RT_MAT_MATTE) RT_SHADE(RT_MAT_LIGHT) RT_SHADE(RT_MAT_PLASTIC) RT_SHADE(RT_MAT_GLASS) RT_SHADE(RT_MAT_METAL) RT_SHADE(RT_MAT_MIRROR)
+    if constexpr (sizeof(R) == 8) { RT_SHADE(RT_MAT_DISNEY) }        // Material::Disney: f64 kernels only (rt_render shades such a scene in f64)
 #undef RT_SHADE
 }
 void launch_shade_f32(const ShadeLaunch& L, bool envl);      // shade_f32.cu

@@ -83,7 +83,12 @@ class HostScene:
             px = np.zeros((info[1], info[0], 3), dtype=np.float32 if info[2] else np.uint8)
             check(lib().rth_scene_image_copy(self.h, i, ptr(px)))
             images.append(px)
-        return dict(meshes=meshes, prims=prims, transforms=xf, textures=tex, materials=mat, lights=lig, images=images)
+        n_dis = C.c_uint64()
+        check(lib().rth_scene_num_disney(self.h, C.byref(n_dis)))
+        dis = np.zeros(n_dis.value, dtype=N.disney_dtype)
+        if len(dis):
+            check(lib().rth_scene_copy_disney(self.h, ptr(dis)))
+        return dict(meshes=meshes, prims=prims, transforms=xf, textures=tex, materials=mat, lights=lig, images=images, disneys=dis)
 
     def upload(self, commit=True, build="sah"):
         """Push the tables through the public rt_scene_* ABI and commit (BVH build + device upload).

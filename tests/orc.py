@@ -30,6 +30,8 @@ def lib():
         L.orc_scene_set_textures.argtypes = [vp, u64, vp]
         L.orc_scene_set_materials.argtypes = [vp, u64, vp]
         L.orc_scene_set_lights.argtypes = [vp, u64, vp]
+        L.orc_scene_add_disney.argtypes = [vp, vp]
+        L.orc_scene_add_disney.restype = u32
         L.orc_scene_commit.argtypes = [vp, u64]
         L.orc_scene_build_fast_tree.argtypes = [vp, i32]
         L.orc_scene_num_primitives.argtypes = [vp]
@@ -115,6 +117,9 @@ class OracleScene:
             L.orc_scene_add_perlin(self.h, float(scale), _p(pm), _p(vc))
         tex = np.ascontiguousarray(t["textures"], dtype=N.texture_dtype)
         L.orc_scene_set_textures(self.h, len(tex), _p(tex) if len(tex) else None)
+        for d in np.ascontiguousarray(t.get("disneys", np.zeros(0, dtype=N.disney_dtype)), dtype=N.disney_dtype):
+            rec = np.ascontiguousarray(d).reshape(1)
+            L.orc_scene_add_disney(self.h, _p(rec))
         mat = np.ascontiguousarray(t["materials"], dtype=N.material_dtype)
         L.orc_scene_set_materials(self.h, len(mat), _p(mat) if len(mat) else None)
         lig = np.ascontiguousarray(t["lights"], dtype=N.light_dtype)
@@ -231,7 +236,7 @@ def resolve_rgb8(film):
     return out
 
 
-def simple_tables(prims, textures=None, materials=None, lights=None, meshes=(), transforms=(), images=(), perlins=()):
+def simple_tables(prims, textures=None, materials=None, lights=None, meshes=(), transforms=(), images=(), perlins=(), disneys=None):
     """Plain tables for hand-built KAT scenes."""
     if textures is None:
         textures = np.zeros(1, dtype=N.texture_dtype); textures[0]["color"] = (0.5, 0.5, 0.5)
@@ -240,7 +245,8 @@ def simple_tables(prims, textures=None, materials=None, lights=None, meshes=(), 
     if lights is None:
         lights = np.zeros(0, dtype=N.light_dtype)
     return dict(meshes=list(meshes), prims=np.asarray(prims, dtype=N.prim_dtype), transforms=np.asarray(transforms, dtype=np.float64).reshape(-1, 16),
-                textures=textures, materials=materials, lights=lights, images=list(images), perlins=list(perlins))
+                textures=textures, materials=materials, lights=lights, images=list(images), perlins=list(perlins),
+                disneys=np.zeros(0, dtype=N.disney_dtype) if disneys is None else np.asarray(disneys, dtype=N.disney_dtype))
 
 
 def delta_light_tables(area_light=True):
@@ -303,6 +309,8 @@ def upload_tables(t):
         o.add_image_rgb8(im) if im.dtype == np.uint8 else o.add_image_hdr(im)
     for (scale, perm, vecs) in t.get("perlins", []):
         o.add_perlin(scale, perm, vecs)
+    for d in t.get("disneys", []):
+        o.add_disney(d)
     o.set_textures(t["textures"]); o.set_materials(t["materials"]); o.set_lights(t["lights"])
     if len(t["prims"]):
         o.add_primitives(t["prims"])
