@@ -54,6 +54,7 @@ pub const RT_INTEGRATOR_BASIC: u32 = 4;
 pub const RT_SHADE_F32: u32 = 1;
 pub const RT_BUILD_HOST_SAH: u32 = 0;
 pub const RT_BUILD_DEVICE_LBVH: u32 = 1;
+pub const RT_RESOLVE_STATIC_MAX_PIXELS: u32 = 2048 * 2048;
 
 #[repr(C)]
 #[derive(Clone, Copy, Debug, Default)]
@@ -273,6 +274,8 @@ extern "C" {
     pub fn rt_film_clear(film: *mut rt_film) -> RtStatus;
     pub fn rt_film_read(film: *mut rt_film, host_rgba: *mut f64) -> RtStatus;
     pub fn rt_film_resolve_rgb8(film: *mut rt_film, host_rgb: *mut u8) -> RtStatus;
+    /// no counterpart in the reference: allocation-free variant, films up to RT_RESOLVE_STATIC_MAX_PIXELS
+    pub fn rt_film_resolve_rgb8_static(film: *mut rt_film, host_rgb: *mut u8) -> RtStatus;
     pub fn rt_render(scene: *mut rt_scene, camera: *const rt_camera, integrator: *const rt_integrator_desc, desc: *const rt_film_desc, film: *mut rt_film) -> RtStatus;
     pub fn rt_render_cancel(scene: *mut rt_scene) -> RtStatus;
     pub fn rt_get_counters(scene: *const rt_scene, out: *mut rt_counters) -> RtStatus;

@@ -308,6 +308,14 @@ rt_status rt_film_clear(rt_film* film);
 rt_status rt_film_read(rt_film* film, double* host_rgba);
 /* point_to_color (util.rs:441-471) on the device: (sum/n) -> ACES approx -> gamma -> u8 */
 rt_status rt_film_resolve_rgb8(rt_film* film, uint8_t* host_rgb);
+/* rt_film_resolve_rgb8 for callers that may not allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * NO COUNTERPART IN THE REFERENCE.  Same result as rt_film_resolve_rgb8, byte for byte, but the
+ * 3-bytes-per-pixel device staging buffer is a static device array inside the library instead of a cudaMalloc per call: the call allocates
+ * and frees nothing.  Limit: width * height <= RT_RESOLVE_STATIC_MAX_PIXELS (2048 x 2048; 12 MiB held by every GPU that loads the library until
+ * exit); a larger film is refused with RT_ERR_INVALID.  All calls on a device share that array (it keeps the last call's bytes; every byte that
+ * is read back is rewritten first): calls from host threads of one process are serialised, any other use that overlaps on the GPU races. */
+#define RT_RESOLVE_STATIC_MAX_PIXELS (2048u * 2048u)
+rt_status rt_film_resolve_rgb8_static(rt_film* film, uint8_t* host_rgb);
 
 /* render::tile_multithread / Integrator::render / single_sample
  * (render.rs:13, integrator.rs:336-369): adds `sample_end-sample_begin` samples for

@@ -79,7 +79,7 @@ RTCORE_SYMBOLS = [
     "rt_intersect_range", "rt_intersect_device", "rt_closest_device", "rt_occluded", "rt_occluded_device", "rt_film_create",
     "rt_film_create_external", "rt_film_destroy", "rt_film_clear", "rt_film_read", "rt_film_resolve_rgb8", "rt_render",
     "rt_render_cancel", "rt_get_counters", "rt_set_wavefront_size", "rt_scene_set_build_mode", "rt_scene_build_stats",
-    "rt_debug_prefilter_stats",
+    "rt_debug_prefilter_stats", "rt_film_resolve_rgb8_static",
     "rt_comm_create_local", "rt_comm_unique_id", "rt_comm_create_rank", "rt_comm_destroy", "rt_comm_size", "rt_film_allreduce", "rt_scene_replicate", "rt_render_multi",
 ]
 RTHOST_SYMBOLS = [
@@ -127,7 +127,7 @@ def _load_core():
         "rt_intersect_device": [vp, u64, vp, f64, f64, vp, vp], "rt_closest_device": [vp, u64, vp, f64, f64, vp, vp, vp],
         "rt_occluded": [vp, u64, vp, vp], "rt_occluded_device": [vp, u64, vp, vp, vp],
         "rt_film_create": [u32, u32, vp], "rt_film_create_external": [u32, u32, vp, vp], "rt_film_destroy": [vp],
-        "rt_film_clear": [vp], "rt_film_read": [vp, vp], "rt_film_resolve_rgb8": [vp, vp],
+        "rt_film_clear": [vp], "rt_film_read": [vp, vp], "rt_film_resolve_rgb8": [vp, vp], "rt_film_resolve_rgb8_static": [vp, vp],
         "rt_render": [vp, vp, vp, vp, vp], "rt_render_cancel": [vp], "rt_get_counters": [vp, vp], "rt_set_wavefront_size": [vp, u32],
         "rt_scene_set_build_mode": [vp, u32], "rt_scene_build_stats": [vp, vp], "rt_debug_prefilter_stats": [vp],
         "rt_comm_create_local": [vp, u32, vp], "rt_comm_unique_id": [vp], "rt_comm_create_rank": [vp, u32, u32, vp], "rt_comm_destroy": [vp],

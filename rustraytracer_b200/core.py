@@ -273,6 +273,12 @@ class Film:
         check(lib().rt_film_resolve_rgb8(self.h, ptr(out)))
         return out
 
+    def resolve_rgb8_static(self):
+        """rt_film_resolve_rgb8_static: the same image through the entry point that allocates nothing (static device scratch, films up to 2048 x 2048)."""
+        out = np.zeros((self.height, self.width, 3), dtype=np.uint8)
+        check(lib().rt_film_resolve_rgb8_static(self.h, ptr(out)))
+        return out
+
     def close(self):
         if self.h:
             lib().rt_film_destroy(self.h)

@@ -15,6 +15,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include "wavefront.cuh"
 #include "traverse.cuh"
 
@@ -503,6 +504,51 @@ rt_status rt_film_resolve_rgb8(rt_film* f, uint8_t* host_rgb) {
     cudaFree(d);
     if (e != cudaSuccess) { set_error(std::string("rt_film_resolve_rgb8: ") + cudaGetErrorString(e)); return RT_ERR_CUDA; }
     return RT_OK;
+}
+
+// ---- rt_film_resolve_rgb8_static: rt_film_resolve_rgb8 for callers that may not allocate (code under CUDA graph capture, tight serving loops,
+// harnesses that forbid cudaMalloc).  No counterpart in the reference.  The 3-bytes-per-pixel staging
+// buffer that rt_film_resolve_rgb8 cudaMallocs and frees on every call lives here in a file-scope device array of RT_RESOLVE_STATIC_MAX_PIXELS * 3
+// bytes (12 MiB) that every GPU which loads the library holds until exit.  In host code `g_resolve_scratch` is only a stand-in for the symbol, not a
+// device address: its address is looked up once per device, with that device current, through cudaGetSymbolAddress, and that pointer is what the
+// kernel and the copy get.  The entry point calls no cudaMalloc / cudaFree / allocating library routine.  All calls on a device share the array and
+// it keeps the last call's bytes; nothing has to start at zero because k_resolve writes every byte of [0, 3 w h) before the copy reads it.  Host
+// threads of this process are serialised by a mutex; anything else that overlaps on the GPU with a call (another stream using the same array) races.
+static __device__ __align__(256) uint8_t g_resolve_scratch[(size_t)RT_RESOLVE_STATIC_MAX_PIXELS * 3];
+namespace {
+constexpr int RESOLVE_MAX_DEVICES = 64;
+uint8_t* g_resolve_ptr[RESOLVE_MAX_DEVICES] = {};      // device address of g_resolve_scratch, per device
+std::mutex g_resolve_mutex;
+}
+rt_status rt_film_resolve_rgb8_static(rt_film* f, uint8_t* host_rgb) {
+    if (!f || !host_rgb) { set_error("rt_film_resolve_rgb8_static: null argument"); return RT_ERR_INVALID; }
+    const uint64_t n = (uint64_t)f->w * f->h;
+    if (n > (uint64_t)RT_RESOLVE_STATIC_MAX_PIXELS) {
+        set_error("rt_film_resolve_rgb8_static: film of " + std::to_string(f->w) + " x " + std::to_string(f->h) + " pixels exceeds the static scratch of " +
+                  std::to_string((unsigned long long)RT_RESOLVE_STATIC_MAX_PIXELS) + " pixels (RT_RESOLVE_STATIC_MAX_PIXELS); use rt_film_resolve_rgb8");
+        return RT_ERR_INVALID;
+    }
+    if (f->device < 0 || f->device >= RESOLVE_MAX_DEVICES) { set_error("rt_film_resolve_rgb8_static: device index out of range"); return RT_ERR_INVALID; }
+    std::lock_guard<std::mutex> lock(g_resolve_mutex);
+    int prev = 0;
+    CK(cudaGetDevice(&prev));
+    if (prev != f->device) CK(cudaSetDevice(f->device));
+    rt_status st = RT_OK;
+    if (!g_resolve_ptr[f->device]) {                    // set-up, once per device, with that device current
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_resolve_scratch);
+        if (e != cudaSuccess || !p) { set_error(std::string("rt_film_resolve_rgb8_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e)); st = RT_ERR_CUDA; }
+        else g_resolve_ptr[f->device] = (uint8_t*)p;
+    }
+    if (st == RT_OK) {
+        uint8_t* d = g_resolve_ptr[f->device];
+        k_resolve<<<(unsigned)std::min<uint64_t>((n + 255) / 256, 148 * 16), 256>>>(f->d, n, d);
+        cudaError_t e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaMemcpy(host_rgb, d, n * 3, cudaMemcpyDeviceToHost);      // same (legacy default) stream as the kernel: ordered after it, and synchronous
+        if (e != cudaSuccess) { set_error(std::string("rt_film_resolve_rgb8_static: ") + cudaGetErrorString(e)); st = RT_ERR_CUDA; }
+    }
+    if (prev != f->device) cudaSetDevice(prev);
+    return st;
 }
 
 rt_status rt_render(rt_scene* s, const rt_camera* cam, const rt_integrator_desc* integ, const rt_film_desc* fd, rt_film* film) {
