@@ -56,12 +56,20 @@ def extend_rooflines(tot, launches, clk, sms=148):
     out = {"kernel": "k_extend (closest-hit BVH4 traversal, persistent)", "rays_per_launch": per_launch, "ms_per_launch": ms / max(launches, 1), "extend_Mrays_per_s": rays_per_s / 1e6,
            "per_ray_constants": "profiles/extend_work_r02.json" if work else None}
     l2_peak = (peaks.get("gather128_gbs") or {}).get("64MB")
-    ld_bytes = work.get("load_bytes_per_ray")
-    # headline roofline object: the kernel's own load bytes against the measured L2 bandwidth for its access pattern (independent 128-byte node reads)
-    out.update({"bound": "l2", "unit": "GB/s", "achieved": ld_bytes * rays_per_s / 1e9 if ld_bytes else None, "peak": l2_peak,
+    l2_bytes = work.get("l2_to_l1_bytes_per_ray")
+    # headline roofline object: the bytes the kernel actually pulls out of L2 (L2 -> L1 sectors x 32 B, ncu) against the measured L2 bandwidth for its access
+    # pattern — independent 128-byte node / slot records per lane (tools/peaks.cu gather128), not the 17.9-25 TB/s a coalesced stream reaches
+    out.update({"bound": "l2", "unit": "GB/s", "achieved": l2_bytes * rays_per_s / 1e9 if l2_bytes else None, "peak": l2_peak,
                 "peak_kind": "measured: tools/peaks.cu gather128 (independent random 128-byte records per lane, 64 MB footprint), profiles/peaks_r02.json",
-                "traffic": work.get("dram_bytes_per_ray") * per_launch if work.get("dram_bytes_per_ray") else None})
+                "traffic": work.get("dram_bytes_per_ray") * per_launch if work.get("dram_bytes_per_ray") else None,
+                "l2_to_l1_bytes_per_ray": l2_bytes})
     out["frac"] = out["achieved"] / l2_peak if out["achieved"] and l2_peak else None
+    ld_bytes = work.get("load_bytes_per_ray")
+    stream_peak = (peaks.get("ld128_gbs") or {}).get("100MB")
+    if ld_bytes and stream_peak:
+        a = ld_bytes * rays_per_s / 1e9      # what the kernel's loads REQUEST at L1 (l1tex global-load sectors x 32 B): part of it is served by L1 hits
+        out["l1_requests"] = {"achieved": a, "unit": "GB/s", "load_bytes_per_ray": ld_bytes, "vs_l2_stream_peak": a / stream_peak, "l2_stream_peak": stream_peak,
+                              "note": "requested bytes incl. L1 hits; shown against the coalesced L2 -> SM stream bandwidth (ld128, 100 MB footprint) as an upper reference"}
     if work.get("dram_bytes_per_ray"):
         a = work["dram_bytes_per_ray"] * rays_per_s / 1e9
         out["hbm"] = {"achieved": a, "peak": hbm_peak, "unit": "GB/s", "frac": a / hbm_peak, "peak_kind": f"{peak_kind} HBM copy bandwidth (MEASURED_PEAKS.json)",
@@ -178,10 +186,16 @@ def main():
     assert N.lib().rt_device_count() > 0, "no CUDA device: librtcore has no CPU path"
     torch.cuda.set_device(local)
     N.check(N.lib().rt_set_device(local))
-    dist = None
+    dist = comm = None
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        # the film reduce goes through the library's own entry point (rt_film_allreduce = ncclAllReduce f64 sum over NVLink, include/rtcore.h);
+        # torch.distributed is the launcher's plumbing: it carries the communicator id to the ranks, the barriers and the timing statistics
+        from rustraytracer_b200 import Comm
+        ident = [Comm.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ident, src=0)
+        comm = Comm.rank(ident[0], world, rank)
     W = H = args.size
     spp = int(N.lib().rt_round_spp(args.spp))            # sampler.rs:637-640
     hs = scenes.HostScene(SCENE, W, H, variant=VARIANT)
@@ -217,8 +231,8 @@ def main():
         base = (i * world + rank) * spp_rank
         render_samples(objects, cam, integ, film, W, H, base, base + spp_rank, seed=1234)    # blocking; H2D = camera + descriptors
         c = objects.counters()
-        if dist:
-            dist.all_reduce(film_t)                       # NCCL sum of the (r,g,b,n) accumulation buffers over NVLink
+        if comm:
+            comm.allreduce([film])                        # rt_film_allreduce: NCCL sum of the (r,g,b,n) accumulation buffers over NVLink, in place, blocking
         if e2e and rank == 0:
             host_film.copy_(film_t, non_blocking=False)   # D2H read of the step's result
         torch.cuda.synchronize()
@@ -270,6 +284,7 @@ def main():
                "kernel_ms_per_step": {"extend": tot64["extend_ms"] / args.steps, "shade+generate": tot64["shade_ms"] / args.steps, "connect": tot64["connect_ms"] / args.steps}}
     if rank != 0:
         if dist:
+            comm.close()
             dist.destroy_process_group()
         return
     value = rays_all / wall / 1e6
@@ -283,7 +298,7 @@ def main():
         "dtype": "f64 geometry (intersection, hit points, rays) + f32 radiometry" if args.shade == "f32" else "f64", "data": "synthetic",
         "config": {"workload": f"{SCENE} rough-plastic (stand-in dragon mesh, 871,414 tris; dragon.obj is a missing blob) {W}x{H}, max_depth {DEPTH}, "
                                + (f"{spp} spp per step in total = {spp_rank} per GPU" if strong else f"{spp} spp per GPU per step"),
-                   "parallelism": f"scene replicated, sample-range partition x{world}, NCCL all-reduce of the film" if world > 1 else "single GPU",
+                   "parallelism": f"scene replicated, sample-range partition x{world}, rt_film_allreduce (ncclAllReduce f64 sum, behind the C ABI) of the film" if world > 1 else "single GPU",
                    "l2": "no explicit flush: every wavefront iteration streams several GB of path/queue state (>> 126 MB L2); the BVH (33 MB nodes + 42 MB f32 prefilter records + 70 MB f64 leaf slots) is meant to stay L2-resident",
                    "wavefront_paths": args.wavefront, "bvh_build_s": round(build_s, 2),
                    "headline_precision": "RT_SHADE_F32: intersection decisions, hit points and rays are f64-exact (bit-exact ids vs the oracle); radiometry in f32, image parity within the relMSE / mean-bias bounds of tests/test_gpu_parity.py; the all-f64 figure of the same workload is `exact_f64_shading`"},
@@ -312,6 +327,7 @@ def main():
                                "sample": f"every {stride}rd pixel of the {W}x{H} image x {smp} spp ({c_secs:.1f} s of {cores}-thread CPU work)"}
     print(json.dumps(out))
     if dist:
+        comm.close()
         dist.destroy_process_group()
 
 

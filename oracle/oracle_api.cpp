@@ -63,6 +63,18 @@ void orc_scene_commit_tables(void* sp) {
         else if (is_delta_light(L)) make_delta_light(s, L);                    // light.rs:522-582
         else L.area = prim_area(s, s.prims[L.d.prim_index]);                    // light.rs:603
     }
+    // Light::eq (derived PartialEq, light.rs:28): same variant and every field equal.  The fields this ABI carries: type, prim_index, two_sided, text_id,
+    // colour, transform, param (area / tables are functions of those).  A NaN field makes a light unequal to everything, itself included — kept.
+    for (size_t i = 0; i < s.lights.size(); i++) {
+        const rt_light& a = s.lights[i].d;
+        auto same = [](const rt_light& x, const rt_light& y) {
+            if (x.type != y.type || x.prim_index != y.prim_index || x.two_sided != y.two_sided || x.text_id != y.text_id || x.transform != y.transform) return false;
+            for (int k = 0; k < 3; k++) if (!(x.color[k] == y.color[k]) || !(x.param[k] == y.param[k])) return false;
+            return true;
+        };
+        s.lights[i].eq_class = same(a, a) ? (uint32_t)i : RT_NONE - 1 - (uint32_t)i;     // NaN: a class of its own that matches nothing (see below)
+        for (size_t j = 0; j < i; j++) if (same(s.lights[j].d, a)) { s.lights[i].eq_class = s.lights[j].eq_class; break; }
+    }
     s.nodes.clear(); s.root = -1;
 }
 // boxes + the faithful tree (hittable.rs:637-723) with a seeded axis choice

@@ -288,7 +288,8 @@ struct Material { rt_material d; };
 struct Distribution1D { std::vector<double> func, cdf; double func_int = 0.; size_t count() const { return func.size(); } };
 struct Distribution2D { std::vector<Distribution1D> p_cond_v; Distribution1D p_marginal; };
 // pos / cos_width / cos_falloff: what make_point_light / make_spot_light derive at construction (light.rs:522-560)
-struct Light { rt_light d; double area; Distribution2D dist; V3 pos; double cos_width = 0., cos_falloff = 0.; };
+// eq_class: the smallest index of a light that is field-equal to this one — `#[derive(PartialEq)] enum Light` (light.rs:28) as integrator.rs:621 uses it
+struct Light { rt_light d; double area; Distribution2D dist; V3 pos; double cos_width = 0., cos_falloff = 0.; uint32_t eq_class = 0; };
 // Texture::Hdr { meta, data: Vec<Rgb<f32>> } / Texture::Image { img: RgbImage } (material.rs:521-539)
 struct Image { uint32_t w = 0, h = 0; bool hdr = false; std::vector<float> f; std::vector<uint8_t> b; };
 

@@ -948,7 +948,7 @@ inline V3 estimate_direct(const Scene& s, const HitRecord& rec, const V2& u_scat
             V3 c = black();
             if (get_intersection(s, nray, nrec)) {
                 uint32_t li = s.prims[nrec.prim_index].light_index;
-                if (li != RT_NONE && li == light_num) c = record_le(s, nrec, -wi);
+                if (li != RT_NONE && s.lights[li].eq_class == light.eq_class && s.lights[li].eq_class < RT_NONE / 2) c = record_le(s, nrec, -wi);      // `lights[index].eq(light)`: field equality, not identity
             } else c = light_le(s, light, nray);
             if (c != black()) ld = ld + cmul(f, c) * (weight / scattering_pdf);
         }

@@ -330,7 +330,11 @@ struct ConnectJob {
             return;
         }
         uint32_t li = sc->prims[prim].light;
-        if (li == RT_NONE || li != pr.target[k]) return;           // `lights[index].eq(light)` (integrator.rs:621)
+        if (li == RT_NONE) return;
+        {   // `lights[index].eq(light)` (integrator.rs:621): field equality (classes computed at commit), not identity; NaN colours never match
+            const DLight& a = sc->lights[li]; const DLight& b = sc->lights[pr.target[k]];
+            if (a.eq_class != b.eq_class || !(a.color[0] == a.color[0] && a.color[1] == a.color[1] && a.color[2] == a.color[2])) return;
+        }
         D3 o = mk3(pr.ax[k], pr.ay[k], pr.az[k]), d = mk3(pr.bx[k], pr.by[k], pr.bz[k]);
         Rec r;
         if (!prim_record(*sc, prim, o, d, SMALL, INF, true, r)) return;
@@ -339,7 +343,10 @@ struct ConnectJob {
         film_add(film, pr.pixel[k], cmul(mk3(pr.cr[k], pr.cg[k], pr.cb[k]), le));
     }
 };
-__global__ void __launch_bounds__(128, TRACE_MIN_BLOCKS) k_connect(Ctrl* c, DScene sc, ConnQ shq, ConnQ prq, double* film, uint32_t W) {
+#ifndef CONNECT_MIN_BLOCKS
+#define CONNECT_MIN_BLOCKS TRACE_MIN_BLOCKS     // resident blocks per SM of k_connect alone (its load() / finish() carry more state than k_extend's)
+#endif
+__global__ void __launch_bounds__(128, CONNECT_MIN_BLOCKS) k_connect(Ctrl* c, DScene sc, ConnQ shq, ConnQ prq, double* film, uint32_t W) {
     const uint32_t n_shadow = min(c->n_shadow, W), n_probe = min(c->n_probe, W);      // see k_prepare: counters may run past W on overflow
     ConnectJob job{&sc, shq, prq, film, n_shadow};
     trace_jobs(sc, job, n_shadow + n_probe, &c->fetch[1]);

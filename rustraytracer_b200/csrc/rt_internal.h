@@ -63,9 +63,10 @@ struct DXform { double fwd[16], inv[16]; };
 //   dist_cdf  [nv*(nu+1)]  row v's normalised cdf
 //   row_int   [nv]         row v's func_int  (= the marginal's `func`)
 //   marg_cdf  [nv+1]       the marginal's normalised cdf ;  marg_int = the marginal's func_int
+// eq_class: smallest index of a light field-equal to this one (`#[derive(PartialEq)] enum Light`, light.rs:28; used by integrator.rs:621)
 struct DLight {
     uint32_t prim, two_sided, type, text_id; double color[3]; double area;
-    uint32_t xform, nu, nv, pad; const double *dist_f, *dist_cdf, *row_int, *marg_cdf; double marg_int;
+    uint32_t xform, nu, nv, eq_class; const double *dist_f, *dist_cdf, *row_int, *marg_cdf; double marg_int;
     // delta lights (light.rs:522-582): Point / Spot position (to_world x origin) or the Distant direction; the Spot cosines
     double pos[3]; double cos_width, cos_falloff;
 };

@@ -355,6 +355,17 @@ rt_status build_host_image(const rt_scene& s, HostImage& img, bool device_build)
         }
         img.lights[i] = d;
     }
+    // `lights[index].eq(light)` (integrator.rs:621) is the derived PartialEq of `enum Light` (light.rs:28): field equality, so two entries that
+    // describe the same light (same primitive, colour, ...) count as one.  A NaN field makes a light unequal to everything, itself included.
+    auto same = [](const rt_light& x, const rt_light& y) {
+        if (x.type != y.type || x.prim_index != y.prim_index || x.two_sided != y.two_sided || x.text_id != y.text_id || x.transform != y.transform) return false;
+        for (int k = 0; k < 3; k++) if (!(x.color[k] == y.color[k]) || !(x.param[k] == y.param[k])) return false;
+        return true;
+    };
+    for (size_t i = 0; i < s.lights.size(); i++) {
+        img.lights[i].eq_class = (uint32_t)i;
+        for (size_t j = 0; j < i; j++) if (same(s.lights[j], s.lights[i])) { img.lights[i].eq_class = img.lights[j].eq_class; break; }
+    }
     return RT_OK;
 }
 

@@ -87,6 +87,7 @@ template <class R> __device__ __forceinline__ R norm(V3<R> a) { return sqrt(dot(
 template <class R> __device__ __forceinline__ V3<R> normalize(V3<R> a) { R n = norm(a); return v3<R>(a.x / n, a.y / n, a.z / n); }
 template <class R> __device__ __forceinline__ R clampr(R x, R lo, R hi) { return fmin(fmax(x, lo), hi); }
 template <class R> __device__ __forceinline__ V3<R> face_forward(V3<R> n, V3<R> v) { return dot(n, v) < R(0) ? -n : n; }
+template <class R> __device__ __forceinline__ bool finite3(V3<R> a) { return isfinite(a.x) && isfinite(a.y) && isfinite(a.z); }
 template <class R> __device__ __forceinline__ R pi() { return (R)PI; }
 template <class R> __device__ __forceinline__ R inv_pi() { return (R)(1.0 / PI); }          // consts.rs:41
 
@@ -202,6 +203,9 @@ template <class R> static __device__ RT_HELPER V3<R> fr_conductor(R cos_theta_i,
     a2pb2 = v3<R>(sqrt(a2pb2.x), sqrt(a2pb2.y), sqrt(a2pb2.z));
     V3<R> t1 = a2pb2 + v3<R>(c2, c2, c2);
     V3<R> a = (a2pb2 + t0) * R(0.5);
+    // f32 (production) mode only: with k = 0 and eta^2 < sin^2 the exact value is 0, but sqrt(t0^2) from the fast f32 square root can come out an ulp
+    // below |t0| and the next sqrt would take the root of -1e-9: clamp.  The f64 kernels keep the reference's expression as it is (bxdf.rs:141-170).
+    if constexpr (sizeof(R) == 4) a = v3<R>(fmaxf(a.x, 0.f), fmaxf(a.y, 0.f), fmaxf(a.z, 0.f));
     a = v3<R>(sqrt(a.x), sqrt(a.y), sqrt(a.z));
     V3<R> t2 = a * (R(2) * cos_theta_i);
     V3<R> rs = cdiv(t1 - t2, t1 + t2);

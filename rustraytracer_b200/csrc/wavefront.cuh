@@ -238,6 +238,9 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
                             R weight = (whitted || delta) ? R(1) : power_heuristic<R>((R)light_pdf, scattering_pdf);
                             V3<R> ld = cmul(f, cast3<R>(color)) * (weight / (R)light_pdf);
                             V3<R> contrib = cmul(ld * l_scale, beta);
+                            // RT_SHADE_F32 only: a sample whose f32 radiometry overflowed (inf / inf at a grazing microfacet, ...) is dropped instead of
+                            // poisoning its pixel for good; the f64 kernels propagate NaN as the reference does (util.rs:208-232: its guards never fire)
+                            if constexpr (sizeof(R) == 4) { if (!finite3(contrib)) contrib = v3<R>(R(0), R(0), R(0)); }
                             uint32_t q = warp_append(&c->n_shadow);
                             if (!path && q >= rp.W) { c->overflow = 1u; return; }
                             __stcs(shq.ax + q, rec.p.x); __stcs(shq.ay + q, rec.p.y); __stcs(shq.az + q, rec.p.z); __stcs(shq.bx + q, p1.x); __stcs(shq.by + q, p1.y); __stcs(shq.bz + q, p1.z);
@@ -264,10 +267,13 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
                         }
                         if (go) {
                             V3<R> contrib = cmul((f * (weight / scattering_pdf)) * l_scale, beta);   // × Le decided by the probe ray
+                            if constexpr (sizeof(R) == 4) { if (!finite3(contrib)) go = false; }
+                            if (go) {
                             uint32_t q = warp_append(&c->n_probe);
                             if (!path && q >= rp.W) { c->overflow = 1u; return; }
                             prq.ax[q] = rec.p.x; prq.ay[q] = rec.p.y; prq.az[q] = rec.p.z; prq.bx[q] = wid.x; prq.by[q] = wid.y; prq.bz[q] = wid.z;
                             prq.cr[q] = contrib.x; prq.cg[q] = contrib.y; prq.cb[q] = contrib.z; prq.target[q] = light_num; prq.pixel[q] = pixel;
+                            }
                         }
                     }
                 }
@@ -314,6 +320,7 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
             bsdf_sample_f<R, KM>(bsdf, wo, u, BSDF_ALL, rng, f, wi, pdf, sflags);
             if (is_black(f) || pdf == R(0)) break;
             beta = cmul(beta, f) * (fabs(dot(wi, sn)) / pdf);
+            if constexpr (sizeof(R) == 4) { if (!finite3(beta)) break; }          // f32 mode: end a path whose throughput overflowed (see above)
             specular_bounce = (sflags & BSDF_SPECULAR) != 0;
             o = rec.p; d = dbl3(wi);
             if (bounces > 3) {
