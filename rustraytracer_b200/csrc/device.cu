@@ -169,6 +169,11 @@ rt_status upload_scene(rt_scene& s, HostImage& img) {
     if ((st = up(s, s.textures, d.textures, b))) return st;
     if ((st = up(s, s.materials, d.materials, b))) return st;
     if ((st = up(s, s.disneys, d.disneys, b))) return st;
+    {   // per-primitive shading bin
+        std::vector<uint8_t> bins(img.prims.size());
+        for (size_t i = 0; i < bins.size(); i++) bins[i] = (uint8_t)(s.materials[img.prims[i].mat].type * 2u + ((img.prims[i].info & 7u) == RT_PRIM_TRIANGLE ? 1u : 0u));
+        if ((st = up(s, bins, d.prim_bin, b))) return st;
+    }
     d.has_disney = 0;
     for (auto& m : s.materials) if (m.type == RT_MAT_DISNEY) d.has_disney = 1;
     if ((st = up(s, img.mat_alpha, d.mat_alpha, b))) return st;

@@ -163,7 +163,7 @@ struct ExtendJob {
     }
     __device__ __forceinline__ void finish(uint32_t i, const TState& st) {
         uint32_t prim = st.best.prim, key = N_BINS - 1;
-        if (prim != RT_NONE) { DPrim pr = sc->prims[prim]; key = sc->materials[pr.mat].type * 2u + ((pr.info & 7u) == RT_PRIM_TRIANGLE ? 1u : 0u); }
+        if (prim != RT_NONE) key = __ldg(sc->prim_bin + prim);
         unsigned active = __activemask();
 #if RT_SORT_HITS
         // count the (bin, hit cell) key — one atomic per distinct key per warp — and leave (key, primitive) for k_sort_scatter

@@ -85,6 +85,7 @@ struct DScene {
     const double* shapes; const DXform* xforms;
     const rt_texture* textures; const rt_material* materials; const DLight* lights;
     const rt_disney* disneys;                 // Material::Disney records, indexed by the material's tex[0]
+    const uint8_t* prim_bin;                  // shading bin of every primitive (material type * 2 + is_triangle), built at commit: one gather in ExtendJob::finish instead of prims -> materials
     const DImage* images; const uint32_t* texels;
     const double* perlin;                     // PERLIN_STRIDE doubles per Texture::Perlin: scale, perm_x[256], perm_y[256], perm_z[256], 256 gradient vectors
     const double* mat_alpha;                  // 2 per material: the microfacet alphas of Plastic / Glass / solid-textured Metal after the optional

@@ -2,8 +2,9 @@
 # round 2, GPU pass I: full-set ncu captures of the RIGHT launches (a render here is 16 iterations: the second render's iteration 1 = launch 17 of
 # k_extend / k_connect, launches 34-35 of k_shade), A/B of k_connect's launch bound
 set -x
+(timeout 1800 python -m pytest tests -m gpu -x -q 2>&1 | tail -15) > gpurun_out/pytest_gpu.log 2>&1; cat gpurun_out/pytest_gpu.log
 R="python tools/profile_render.py plastic_dragon 0 1024 8 8 1"
-for so in rustraytracer_b200/librtcore.so rustraytracer_b200/librtcore_c4.so rustraytracer_b200/librtcore_c3.so rustraytracer_b200/librtcore_t4.so; do
+for so in rustraytracer_b200/librtcore.so rustraytracer_b200/librtcore_c4.so rustraytracer_b200/librtcore_t4.so; do
   tag=$(basename $so .so)
   RT_LIBRTCORE=$PWD/$so timeout 200 python tools/profile_render.py plastic_dragon 0 1024 64 8 1 > gpurun_out/ab_$tag.log 2>&1; echo $tag; tail -n 1 gpurun_out/ab_$tag.log
 done
