@@ -39,7 +39,7 @@ struct Builder {
     std::vector<TmpNode> nodes;
     std::atomic<uint32_t> n_nodes{0};
     static constexpr int BINS = 16;
-    static constexpr uint32_t LEAF_MAX = 4;
+    uint32_t LEAF_MAX = 4;            // hard cap on primitives per leaf (the leaf word has room for 4); RT_SAH_MAXLEAF overrides (A/B runs)
     float c_isect = 1.5f;      // SAH: cost of one f64 leaf test relative to one node step (RT_SAH_ISECT overrides, for tuning)
     Builder(const std::vector<FBox>& b, std::vector<uint32_t>& i) : pb(b), idx(i) { nodes.resize(std::max<size_t>(2 * b.size(), 2)); }
 
@@ -142,6 +142,7 @@ rt_status build_bvh(const std::vector<Box64>& boxes, BuiltBvh& out, int threads)
     for (size_t i = 0; i < n; i++) idx[i] = (uint32_t)i;
     Builder b(pb, idx);
     if (const char* e = getenv("RT_SAH_ISECT")) { float v = (float)atof(e); if (v > 0.f) b.c_isect = v; }
+    if (const char* e = getenv("RT_SAH_MAXLEAF")) { int v = atoi(e); if (v >= 1 && v <= 4) b.LEAF_MAX = (uint32_t)v; }
     uint32_t root = b.alloc();
     int par_depth = 0; while ((1 << par_depth) < threads) par_depth++;
     b.build(root, 0, (uint32_t)n, par_depth + 1);

@@ -38,7 +38,7 @@ template <class T, class F> static rt_status up_meshes(rt_scene& s, F field, con
     s.allocations.push_back(p);
     size_t off = 0;
     for (const HostMesh& m : s.meshes) {
-        const std::vector<T>& v = field(m);
+        const HVec<T>& v = field(m);
         if (!v.empty()) CK(cudaMemcpy((T*)p + off, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
         off += v.size();
     }
@@ -113,10 +113,10 @@ rt_status upload_scene(rt_scene& s, HostImage& img) {
     uint32_t n_nodes = (uint32_t)img.nodes.size();
     if ((st = up(s, img.prims, d.prims, b))) return st;
     if ((st = up(s, img.meshes, d.meshes, b))) return st;
-    if ((st = up_meshes<double>(s, [](const HostMesh& m) -> const std::vector<double>& { return m.p; }, d.points, b))) return st;
-    if ((st = up_meshes<double>(s, [](const HostMesh& m) -> const std::vector<double>& { return m.n; }, d.normals, b))) return st;
-    if ((st = up_meshes<double>(s, [](const HostMesh& m) -> const std::vector<double>& { return m.uv; }, d.uvs, b))) return st;
-    if ((st = up_meshes<uint32_t>(s, [](const HostMesh& m) -> const std::vector<uint32_t>& { return m.ind; }, d.tri_index, b))) return st;
+    if ((st = up_meshes<double>(s, [](const HostMesh& m) -> const HVec<double>& { return m.p; }, d.points, b))) return st;
+    if ((st = up_meshes<double>(s, [](const HostMesh& m) -> const HVec<double>& { return m.n; }, d.normals, b))) return st;
+    if ((st = up_meshes<double>(s, [](const HostMesh& m) -> const HVec<double>& { return m.uv; }, d.uvs, b))) return st;
+    if ((st = up_meshes<uint32_t>(s, [](const HostMesh& m) -> const HVec<uint32_t>& { return m.ind; }, d.tri_index, b))) return st;
     if (img.device_build) {
 #if RT_BVH_WIDTH == 4
         // RT_BUILD_DEVICE_LBVH: boxes and primitive-ordered slots go up as temporaries, the tree is built where it will be walked

@@ -5,7 +5,8 @@
 #include <cstdlib>
 #include <cstring>
 #include <dlfcn.h>
-#include <map>
+#include <cstdint>
+#include <thread>
 #include <mutex>
 #include <string>
 #include <tuple>
@@ -199,55 +200,130 @@ void statue_standin(rt::HostMesh& m, uint64_t seed, uint64_t n_tris) {
 }
 
 // ---- parser::parse_obj (parser.rs:8-87) over a tobj-2.0.2-style loader -------------------------
+// Two passes.  (1) text -> numbers, PARALLEL: the file is cut into one chunk per host thread at line boundaries; every chunk parses its `v` / `vn` / `vt`
+// lines into its own arrays and keeps its faces as raw (v, vt, vn) index tokens together with how many v / vt / vn lines of the chunk precede the face
+// (relative indices count back from there).  (2) single-index re-indexing, SEQUENTIAL because tobj numbers the (v, vt, vn) triples in order of first
+// appearance: an open-addressing hash on the triple instead of a tree map.  Only models[0] is used (parser.rs:21): reading stops at the first `o` / `g`
+// line that follows a face.  Values are f32 (tobj) widened to f64; strtof and Rust's str::parse::<f32> both round correctly, so they agree.
+struct ObjCorner { int iv, it, in; bool ht, hn; };
+struct ObjChunk {
+    std::vector<float> v, vn, vt;
+    std::vector<ObjCorner> corners;
+    struct Face { size_t off; uint32_t first, n, nv, nt, nn; };      // byte offset of the line; corners [first, first + n); v / vt / vn lines of this chunk seen before it
+    std::vector<Face> faces;
+    std::vector<size_t> og;                                          // byte offsets of `o` / `g` lines
+};
+static void obj_parse_chunk(const char* buf, size_t begin, size_t end, ObjChunk& c) {
+    size_t pos = begin;
+    while (pos < end) {
+        size_t eol = pos; while (eol < end && buf[eol] != '\n') eol++;
+        const char* p = buf + pos; const char* le = buf + eol;
+        while (p < le && (*p == ' ' || *p == '\t')) p++;
+        auto num = [&](const char*& q) -> float {            // next float of the line, 0 when there is none (sscanf leaves its default)
+            while (q < le && (*q == ' ' || *q == '\t')) q++;
+            if (q >= le) return 0.f;
+            char* e = nullptr; float x = strtof(q, &e);
+            if (e == q) { q = le; return 0.f; }
+            q = e; return x;
+        };
+        if (le - p >= 2 && p[0] == 'v' && (p[1] == ' ' || p[1] == '\t')) { const char* q = p + 2; float a = num(q), b = num(q), d = num(q); c.v.push_back(a); c.v.push_back(b); c.v.push_back(d); }
+        else if (le - p >= 2 && p[0] == 'v' && p[1] == 'n') { const char* q = p + 2; float a = num(q), b = num(q), d = num(q); c.vn.push_back(a); c.vn.push_back(b); c.vn.push_back(d); }
+        else if (le - p >= 2 && p[0] == 'v' && p[1] == 't') { const char* q = p + 2; float a = num(q), b = num(q); c.vt.push_back(a); c.vt.push_back(b); }
+        else if (le - p >= 2 && p[0] == 'f' && (p[1] == ' ' || p[1] == '\t')) {
+            ObjChunk::Face f; f.off = pos; f.first = (uint32_t)c.corners.size(); f.nv = (uint32_t)(c.v.size() / 3); f.nt = (uint32_t)(c.vt.size() / 2); f.nn = (uint32_t)(c.vn.size() / 3);
+            const char* q = p + 1;
+            for (;;) {
+                while (q < le && (*q == ' ' || *q == '\t')) q++;
+                if (q >= le || *q == '\r' || *q == '#' || *q == 0) break;
+                ObjCorner k{0, 0, 0, false, false};
+                char* e = nullptr;
+                k.iv = (int)strtol(q, &e, 10); if (e == q) break; q = e;
+                if (q < le && *q == '/') { q++; if (q < le && *q != '/') { k.it = (int)strtol(q, &e, 10); q = e; k.ht = true; } if (q < le && *q == '/') { q++; k.in = (int)strtol(q, &e, 10); q = e; k.hn = true; } }
+                c.corners.push_back(k);
+            }
+            f.n = (uint32_t)c.corners.size() - f.first;
+            c.faces.push_back(f);
+        } else if (le - p >= 1 && (p[0] == 'o' || p[0] == 'g') && (le - p == 1 || p[1] == ' ' || p[1] == '\t' || p[1] == '\r')) c.og.push_back(pos);
+        pos = eol + 1;
+    }
+}
+struct ObjKeySlot { int a, b, c; uint32_t id; };
 bool load_obj(const char* path, const double* xf, rt::HostMesh& out, std::string& err) {
     FILE* f = fopen(path, "rb");
     if (!f) { err = std::string("cannot open ") + path; return false; }
-    std::vector<float> v, vn, vt;
-    std::map<std::tuple<int, int, int>, uint32_t> remap;      // tobj reindexes (v,vt,vn) triples to a single index
-    std::vector<float> pos, nor, tex; std::vector<uint32_t> ind;
-    char line[4096]; bool have_faces = false, done = false;
-    while (!done && fgets(line, sizeof(line), f)) {
-        char* p = line; while (*p == ' ' || *p == '\t') p++;
-        if (p[0] == 'v' && (p[1] == ' ' || p[1] == '\t')) { float a = 0, b = 0, c = 0; sscanf(p + 2, "%f %f %f", &a, &b, &c); v.push_back(a); v.push_back(b); v.push_back(c); }
-        else if (p[0] == 'v' && p[1] == 'n') { float a = 0, b = 0, c = 0; sscanf(p + 3, "%f %f %f", &a, &b, &c); vn.push_back(a); vn.push_back(b); vn.push_back(c); }
-        else if (p[0] == 'v' && p[1] == 't') { float a = 0, b = 0; sscanf(p + 3, "%f %f", &a, &b); vt.push_back(a); vt.push_back(b); }
-        else if (p[0] == 'f' && (p[1] == ' ' || p[1] == '\t')) {
-            std::vector<uint32_t> poly;
-            char* q = p + 1;
-            for (;;) {
-                while (*q == ' ' || *q == '\t') q++;
-                if (*q == 0 || *q == '\n' || *q == '\r' || *q == '#') break;
-                int iv = 0, it = 0, in = 0; bool ht = false, hn = false;
-                iv = (int)strtol(q, &q, 10);
-                if (*q == '/') { q++; if (*q != '/') { it = (int)strtol(q, &q, 10); ht = true; } if (*q == '/') { q++; in = (int)strtol(q, &q, 10); hn = true; } }
-                int nv = (int)(v.size() / 3), nt = (int)(vt.size() / 2), nn = (int)(vn.size() / 3);
-                iv = iv < 0 ? nv + iv : iv - 1; it = ht ? (it < 0 ? nt + it : it - 1) : -1; in = hn ? (in < 0 ? nn + in : in - 1) : -1;
-                if (iv < 0 || iv >= nv) { err = "face index out of range"; fclose(f); return false; }
-                auto key = std::make_tuple(iv, it, in);
-                auto found = remap.find(key);
-                uint32_t id;
-                if (found == remap.end()) {
-                    id = (uint32_t)(pos.size() / 3); remap[key] = id;
-                    pos.push_back(v[3 * iv]); pos.push_back(v[3 * iv + 1]); pos.push_back(v[3 * iv + 2]);
-                    if (it >= 0 && it < nt) { tex.push_back(vt[2 * it]); tex.push_back(vt[2 * it + 1]); }
-                    if (in >= 0 && in < nn) { nor.push_back(vn[3 * in]); nor.push_back(vn[3 * in + 1]); nor.push_back(vn[3 * in + 2]); }
-                } else id = found->second;
-                poly.push_back(id);
-            }
-            for (size_t k = 1; k + 1 < poly.size(); k++) { ind.push_back(poly[0]); ind.push_back(poly[k]); ind.push_back(poly[k + 1]); }   // fan triangulation
-            have_faces = true;
-        } else if ((p[0] == 'o' || p[0] == 'g') && (p[1] == ' ' || p[1] == '\t' || p[1] == '\n' || p[1] == '\r')) {
-            if (have_faces) done = true;     // only models[0] is used (parser.rs:21)
-        }
-    }
+    fseek(f, 0, SEEK_END); const long fsz = ftell(f); fseek(f, 0, SEEK_SET);
+    std::vector<char> buf((size_t)std::max(fsz, 0L) + 1);
+    const size_t got = fsz > 0 ? fread(buf.data(), 1, (size_t)fsz, f) : 0;
     fclose(f);
+    buf[got] = '\n';                                           // strtof / strtol always meet a terminator
+    const size_t size = got;
+    // pass 1: chunks at line boundaries
+    size_t n_chunks = std::max<size_t>(1, std::min<size_t>(std::thread::hardware_concurrency(), size / (256 * 1024) + 1));
+    std::vector<size_t> cut(n_chunks + 1, size);
+    cut[0] = 0;
+    for (size_t k = 1; k < n_chunks; k++) { size_t q = std::max(cut[k - 1], size * k / n_chunks); while (q < size && buf[q] != '\n') q++; cut[k] = std::min(size, q + 1); }
+    std::vector<ObjChunk> chunks(n_chunks);
+    {
+        std::vector<std::thread> pool;
+        for (size_t k = 0; k < n_chunks; k++) pool.emplace_back([&, k]() { obj_parse_chunk(buf.data(), cut[k], cut[k + 1], chunks[k]); });
+        for (auto& t : pool) t.join();
+    }
+    // where models[0] ends: the first o / g line after the first face
+    size_t first_face = SIZE_MAX, stop = SIZE_MAX;
+    for (auto& c : chunks) if (!c.faces.empty()) { first_face = c.faces[0].off; break; }
+    if (first_face != SIZE_MAX) for (auto& c : chunks) { for (size_t o : c.og) if (o > first_face) { stop = o; break; } if (stop != SIZE_MAX) break; }
+    // concatenated attribute arrays + per-chunk bases
+    std::vector<size_t> bv(n_chunks + 1, 0), bt(n_chunks + 1, 0), bn(n_chunks + 1, 0);
+    size_t n_corners = 0;
+    for (size_t k = 0; k < n_chunks; k++) { bv[k + 1] = bv[k] + chunks[k].v.size() / 3; bt[k + 1] = bt[k] + chunks[k].vt.size() / 2; bn[k + 1] = bn[k] + chunks[k].vn.size() / 3; n_corners += chunks[k].corners.size(); }
+    std::vector<float> v(3 * bv[n_chunks]), vt(2 * bt[n_chunks]), vn(3 * bn[n_chunks]);
+    for (size_t k = 0; k < n_chunks; k++) {
+        if (!chunks[k].v.empty()) memcpy(&v[3 * bv[k]], chunks[k].v.data(), chunks[k].v.size() * 4);
+        if (!chunks[k].vt.empty()) memcpy(&vt[2 * bt[k]], chunks[k].vt.data(), chunks[k].vt.size() * 4);
+        if (!chunks[k].vn.empty()) memcpy(&vn[3 * bn[k]], chunks[k].vn.data(), chunks[k].vn.size() * 4);
+    }
+    // pass 2: (v, vt, vn) triples -> single index, in order of first appearance
+    size_t cap = 16; while (cap < 2 * n_corners + 16) cap <<= 1;
+    std::vector<ObjKeySlot> table(cap, ObjKeySlot{0, 0, 0, 0xffffffffu});
+    std::vector<float> pos, nor, tex; rt::HVec<uint32_t> ind;
+    pos.reserve(3 * bv[n_chunks]); ind.reserve(3 * n_corners);
+    std::vector<uint32_t> poly;
+    for (size_t k = 0; k < n_chunks; k++) {
+        const ObjChunk& c = chunks[k];
+        for (const ObjChunk::Face& fc : c.faces) {
+            if (fc.off >= stop) break;
+            const int nv = (int)(bv[k] + fc.nv), nt = (int)(bt[k] + fc.nt), nn = (int)(bn[k] + fc.nn);
+            poly.clear();
+            for (uint32_t j = fc.first; j < fc.first + fc.n; j++) {
+                const ObjCorner& q = c.corners[j];
+                const int iv = q.iv < 0 ? nv + q.iv : q.iv - 1, it = q.ht ? (q.it < 0 ? nt + q.it : q.it - 1) : -1, in = q.hn ? (q.in < 0 ? nn + q.in : q.in - 1) : -1;
+                if (iv < 0 || iv >= nv) { err = "face index out of range"; return false; }
+                uint64_t h = ((uint64_t)(uint32_t)iv * 0x9E3779B97F4A7C15ull) ^ ((uint64_t)(uint32_t)it * 0xC2B2AE3D27D4EB4Full) ^ ((uint64_t)(uint32_t)in * 0x165667B19E3779F9ull);
+                size_t slot = (size_t)(h ^ (h >> 29)) & (cap - 1);
+                while (table[slot].id != 0xffffffffu && !(table[slot].a == iv && table[slot].b == it && table[slot].c == in)) slot = (slot + 1) & (cap - 1);
+                if (table[slot].id == 0xffffffffu) {
+                    table[slot] = ObjKeySlot{iv, it, in, (uint32_t)(pos.size() / 3)};
+                    pos.push_back(v[3 * (size_t)iv]); pos.push_back(v[3 * (size_t)iv + 1]); pos.push_back(v[3 * (size_t)iv + 2]);
+                    if (it >= 0 && it < nt) { tex.push_back(vt[2 * (size_t)it]); tex.push_back(vt[2 * (size_t)it + 1]); }
+                    if (in >= 0 && in < nn) { nor.push_back(vn[3 * (size_t)in]); nor.push_back(vn[3 * (size_t)in + 1]); nor.push_back(vn[3 * (size_t)in + 2]); }
+                }
+                poly.push_back(table[slot].id);
+            }
+            for (size_t j = 1; j + 1 < poly.size(); j++) { ind.push_back(poly[0]); ind.push_back(poly[j]); ind.push_back(poly[j + 1]); }   // fan triangulation
+        }
+        if (!c.faces.empty() && c.faces.back().off >= stop) break;
+    }
     if (ind.empty()) { err = std::string("no faces in ") + path; return false; }
-    size_t np = pos.size() / 3;
+    const size_t np = pos.size() / 3;
     out.p.resize(3 * np);
-    for (size_t i = 0; i < np; i++) { double pt[3] = {(double)pos[3 * i], (double)pos[3 * i + 1], (double)pos[3 * i + 2]}, o[3]; xf_point(xf, pt, o); out.p[3 * i] = o[0]; out.p[3 * i + 1] = o[1]; out.p[3 * i + 2] = o[2]; }
+    rt::par_for(np, 1 << 16, [&](size_t b, size_t e) {
+        for (size_t i = b; i < e; i++) { double pt[3] = {(double)pos[3 * i], (double)pos[3 * i + 1], (double)pos[3 * i + 2]}, o[3]; xf_point(xf, pt, o); out.p[3 * i] = o[0]; out.p[3 * i + 1] = o[1]; out.p[3 * i + 2] = o[2]; }
+    });
     if (nor.size() == pos.size()) {
         out.n.resize(3 * np);
-        for (size_t i = 0; i < np; i++) { double vv[3] = {(double)nor[3 * i], (double)nor[3 * i + 1], (double)nor[3 * i + 2]}, o[3]; xf_vector(xf, vv, o); out.n[3 * i] = o[0]; out.n[3 * i + 1] = o[1]; out.n[3 * i + 2] = o[2]; }
+        rt::par_for(np, 1 << 16, [&](size_t b, size_t e) {
+            for (size_t i = b; i < e; i++) { double vv[3] = {(double)nor[3 * i], (double)nor[3 * i + 1], (double)nor[3 * i + 2]}, o[3]; xf_vector(xf, vv, o); out.n[3 * i] = o[0]; out.n[3 * i + 1] = o[1]; out.n[3 * i + 2] = o[2]; }
+        });
     }
     if (tex.size() / 2 == np) { out.uv.resize(2 * np); for (size_t i = 0; i < 2 * np; i++) out.uv[i] = (double)tex[i]; }
     out.ind = std::move(ind);
@@ -615,7 +691,8 @@ void build_soup(rth_scene& s, const rth_params& p) {
     uint64_t key = 0x5EED0000ull + (uint64_t)bucket + (p.seed << 32);
     double sz = 2. * std::pow((double)n, -1. / 3.);
     rt::HostMesh m; m.p.resize(9 * n); m.ind.resize(3 * n);
-    for (uint64_t i = 0; i < n; i++) {
+    rt::par_for(n, 1 << 16, [&](size_t tb, size_t te) {       // counter-based generator: triangle i depends on i alone
+    for (uint64_t i = tb; i < te; i++) {
         uint32_t c0[4] = {(uint32_t)i, (uint32_t)(i >> 32), 0, 0}, c1[4] = {(uint32_t)i, (uint32_t)(i >> 32), 1, 0}, c2[4] = {(uint32_t)i, (uint32_t)(i >> 32), 2, 0};
         philox(c0, (uint32_t)key, (uint32_t)(key >> 32)); philox(c1, (uint32_t)key, (uint32_t)(key >> 32)); philox(c2, (uint32_t)key, (uint32_t)(key >> 32));
         auto u = [](uint32_t x) { return (double)(x >> 8) * (1.0 / 16777216.0); };
@@ -627,6 +704,7 @@ void build_soup(rth_scene& s, const rth_params& p) {
         }
         m.ind[3 * i] = (uint32_t)(3 * i); m.ind[3 * i + 1] = (uint32_t)(3 * i + 1); m.ind[3 * i + 2] = (uint32_t)(3 * i + 2);
     }
+    });
     s.meshes.push_back(std::move(m));
     uint32_t t = push_solid(s, 0.7, 0.7, 0.7);
     push_mesh_triangles(s, 0, push_matte(s, t, 0.));

@@ -10,8 +10,13 @@
 //   points / normals / uvs / tri_index : the meshes, concatenated, f64 (read by shade only);
 //   shapes  : f64 payload of spheres and rects; xforms: forward + inverse 4x4 per transform.
 #pragma once
+#include <algorithm>
 #include <cstdint>
+#include <cstring>
+#include <memory>
 #include <string>
+#include <thread>
+#include <utility>
 #include <vector>
 #include "../../include/rtcore.h"
 
@@ -21,9 +26,35 @@ constexpr double SMALL = 0.001;          // consts.rs:32
 constexpr double INF = 1e308;            // consts.rs:30
 constexpr double PI = 3.14159265358979;  // consts.rs:31
 
+// Host-side bulk arrays (mesh tables, primitive runs: gigabytes at 50 M triangles).  HVec is a std::vector whose resize() leaves trivially constructible
+// elements uninitialised, so that the pages are first touched by the THREADS that fill them (par_for) instead of being zeroed by one thread first.
+template <class T> struct NoInitAlloc : std::allocator<T> {
+    template <class U> struct rebind { typedef NoInitAlloc<U> other; };
+    NoInitAlloc() = default;
+    template <class U> NoInitAlloc(const NoInitAlloc<U>&) {}
+    template <class U, class... A> void construct(U* p, A&&... a) {
+        if constexpr (sizeof...(A) == 0) ::new ((void*)p) U; else ::new ((void*)p) U(std::forward<A>(a)...);
+    }
+};
+template <class T> using HVec = std::vector<T, NoInitAlloc<T>>;
+// fn(begin, end) over [0, n) on the host threads (one chunk each); runs inline for small n
+template <class F> inline void par_for(size_t n, size_t min_per_thread, F fn) {
+    size_t t = std::max<size_t>(1, std::min<size_t>(std::thread::hardware_concurrency(), n / std::max<size_t>(min_per_thread, 1)));
+    if (t <= 1) { fn((size_t)0, n); return; }
+    std::vector<std::thread> pool;
+    const size_t chunk = (n + t - 1) / t;
+    for (size_t k = 0; k < t; k++) { const size_t b = std::min(n, k * chunk), e = std::min(n, b + chunk); if (e > b) pool.emplace_back([=]() { fn(b, e); }); }
+    for (auto& th : pool) th.join();
+}
+template <class T> inline void par_assign(HVec<T>& dst, const T* src, size_t n) {
+    dst.resize(n);
+    T* d = dst.data();
+    par_for(n, (size_t)1 << 18, [=](size_t b, size_t e) { memcpy(d + b, src + b, (e - b) * sizeof(T)); });
+}
+
 struct HostMesh {
-    std::vector<double> p, n, uv;        // xyz / xyz / uv
-    std::vector<uint32_t> ind;
+    HVec<double> p, n, uv;               // xyz / xyz / uv
+    HVec<uint32_t> ind;
 };
 
 struct DNode { float v[12]; int32_t left, right, pad0, pad1; };   // 64 B

@@ -9,7 +9,7 @@ struct rt_film { double* d = nullptr; uint32_t w = 0, h = 0; bool owned = false;
 struct rt_scene {
     // host tables (mirror of `Objects`, reference geometry.rs:13-21)
     std::vector<rt::HostMesh> meshes;
-    std::vector<rt::HostPrim> prims;
+    rt::HVec<rt::HostPrim> prims;
     std::vector<double> shapes;              // 12 per shape: v[0..4], xform (-1 none), f64 leaf box mn[3], mx[3]
     std::vector<rt::DXform> xforms;
     std::vector<rt_texture> textures;

@@ -401,8 +401,12 @@ rt_status rt_scene_add_mesh(rt_scene* s, uint64_t n_points, const double* p, uin
     if (n_ind % 3) { set_error("rt_scene_add_mesh: index count not a multiple of 3"); return RT_ERR_INVALID; }
     if (n_normals && n_normals != n_points) { set_error("rt_scene_add_mesh: normals must be per point (single-index mesh)"); return RT_ERR_INVALID; }
     if (n_uvs && n_uvs != n_points) { set_error("rt_scene_add_mesh: uvs must be per point (single-index mesh)"); return RT_ERR_INVALID; }
-    for (uint64_t i = 0; i < n_ind; i++) if (ind[i] >= n_points) { set_error("rt_scene_add_mesh: index out of range"); return RT_ERR_INVALID; }
-    HostMesh m; m.p.assign(p, p + 3 * n_points); if (n_normals) m.n.assign(n, n + 3 * n_normals); if (n_uvs) m.uv.assign(uv, uv + 2 * n_uvs); m.ind.assign(ind, ind + n_ind);
+    {   // validation and the copies run on all host threads (3.6 GB of points at 50 M soup triangles)
+        std::atomic<int> bad{0};
+        par_for(n_ind, (size_t)1 << 20, [&](size_t b, size_t e) { for (size_t i = b; i < e; i++) if (ind[i] >= n_points) { bad.store(1); break; } });
+        if (bad.load()) { set_error("rt_scene_add_mesh: index out of range"); return RT_ERR_INVALID; }
+    }
+    HostMesh m; par_assign(m.p, p, 3 * n_points); if (n_normals) par_assign(m.n, n, 3 * n_normals); if (n_uvs) par_assign(m.uv, uv, 2 * n_uvs); par_assign(m.ind, ind, n_ind);
     s->meshes.push_back(std::move(m)); s->committed = false;
     if (out) *out = (uint32_t)s->meshes.size() - 1;
     return RT_OK;
@@ -443,12 +447,15 @@ rt_status rt_scene_add_primitives(rt_scene* s, uint64_t n, const rt_primitive* p
 rt_status rt_scene_add_mesh_triangles(rt_scene* s, uint32_t mesh, uint32_t mat, uint32_t* first) {
     if (!s || mesh >= s->meshes.size()) { set_error("rt_scene_add_mesh_triangles: bad mesh"); return RT_ERR_INVALID; }
     if (first) *first = (uint32_t)s->prims.size();
-    size_t ni = s->meshes[mesh].ind.size();
-    s->prims.reserve(s->prims.size() + ni / 3);
-    for (size_t i = 0; i < ni; i += 3) {
-        HostPrim h{}; h.type = RT_PRIM_TRIANGLE; h.flip = 0; h.mat = mat; h.light = RT_NONE; h.mesh = mesh; h.ind = (uint32_t)i; h.xform = RT_NONE; h.shape = 0;
-        s->prims.push_back(h);
-    }
+    const size_t nt = s->meshes[mesh].ind.size() / 3, base = s->prims.size();
+    s->prims.resize(base + nt);                            // HVec: not zeroed first; filled by the threads below
+    HostPrim* out = s->prims.data() + base;
+    par_for(nt, (size_t)1 << 18, [=](size_t b, size_t e) {
+        for (size_t t = b; t < e; t++) {
+            HostPrim h{}; h.type = RT_PRIM_TRIANGLE; h.flip = 0; h.mat = mat; h.light = RT_NONE; h.mesh = mesh; h.ind = (uint32_t)(3 * t); h.xform = RT_NONE; h.shape = 0;
+            out[t] = h;
+        }
+    });
     s->committed = false;
     return RT_OK;
 }

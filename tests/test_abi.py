@@ -308,3 +308,107 @@ def test_rust_ffi_crate_declares_exactly_the_header():
         r_body = re.search(r"pub struct " + name + r" \{(.*?)\n\}", rs, re.S).group(1)
         r_fields = [f.rstrip("_") if f in ("type_",) else f for f in re.findall(r"pub (\w+):", r_body)]
         assert c_fields == r_fields, (name, c_fields, r_fields)
+
+
+def _py_obj(path, xf):
+    """Plain-Python restatement of tobj 2.0.2's load_obj(triangulate = true) as parser.rs:8-87 uses it: models[0] only, (v, vt, vn) triples
+    re-indexed to a single index in order of first appearance, f32 values, fan triangulation, `transform` on points (with w) and normals."""
+    v, vt, vn, pos, tex, nor, ind, remap = [], [], [], [], [], [], [], {}
+    have_faces = False
+    for raw in open(path, "rb").read().split(b"\n"):
+        line = raw.decode("latin1").lstrip(" \t")
+        flt = lambda toks, k: [np.float32(float(t)) if i < len(toks) else np.float32(0) for i, t in list(enumerate(toks + ["0"] * k))[:k]]
+        if line[:2] in ("v ", "v\t"):
+            v.append(flt(line[2:].split(), 3))
+        elif line[:2] == "vn":
+            vn.append(flt(line[2:].split(), 3))
+        elif line[:2] == "vt":
+            vt.append(flt(line[2:].split(), 2))
+        elif line[:2] in ("f ", "f\t"):
+            poly = []
+            for tok in line[1:].split("#")[0].split():
+                parts = tok.split("/")
+                iv = int(parts[0]); it = int(parts[1]) if len(parts) > 1 and parts[1] else None; inn = int(parts[2]) if len(parts) > 2 and parts[2] else None
+                iv = len(v) + iv if iv < 0 else iv - 1
+                it = -1 if it is None else (len(vt) + it if it < 0 else it - 1)
+                inn = -1 if inn is None else (len(vn) + inn if inn < 0 else inn - 1)
+                key = (iv, it, inn)
+                if key not in remap:
+                    remap[key] = len(pos); pos.append(v[iv])
+                    if 0 <= it < len(vt): tex.append(vt[it])
+                    if 0 <= inn < len(vn): nor.append(vn[inn])
+                poly.append(remap[key])
+            for k in range(1, len(poly) - 1):
+                ind += [poly[0], poly[k], poly[k + 1]]
+            have_faces = True
+        elif line[:1] in ("o", "g") and (len(line.rstrip("\r")) == 1 or line[1] in " \t\r") and have_faces:
+            break
+    m = np.asarray(xf, dtype=np.float64).reshape(4, 4)
+    P = np.asarray(pos, dtype=np.float64).reshape(-1, 3)
+    Ph = np.stack([m[r, 0] * P[:, 0] + m[r, 1] * P[:, 1] + m[r, 2] * P[:, 2] + m[r, 3] for r in range(4)], 1)
+    out_p = Ph[:, :3] / Ph[:, 3:4]
+    Nn = np.asarray(nor, dtype=np.float64).reshape(-1, 3)
+    out_n = np.stack([m[r, 0] * Nn[:, 0] + m[r, 1] * Nn[:, 1] + m[r, 2] * Nn[:, 2] for r in range(3)], 1) if len(nor) == len(pos) else np.zeros((0, 3))
+    out_uv = np.asarray(tex, dtype=np.float64).reshape(-1, 2) if len(tex) == len(pos) else np.zeros((0, 2))
+    return out_p, out_n, out_uv, np.asarray(ind, dtype=np.uint32)
+
+
+def _load_obj_native(path, xf):
+    h = C.c_void_p()
+    N.check(N.lib().rth_scene_create_empty(C.byref(h)))
+    N.check(N.lib().rth_scene_add_obj(h, str(path).encode(), N.ptr(np.asarray(xf, dtype=np.float64)), None))
+    sz = (C.c_uint64 * 4)()
+    N.check(N.lib().rth_scene_mesh_sizes(h, 0, sz))
+    p = np.zeros((sz[0], 3)); n = np.zeros((sz[1], 3)); uv = np.zeros((sz[2], 2)); ind = np.zeros(sz[3], dtype=np.uint32)
+    N.check(N.lib().rth_scene_mesh_copy(h, 0, N.ptr(p), N.ptr(n), N.ptr(uv), N.ptr(ind)))
+    N.lib().rth_scene_destroy(h)
+    return p, n, uv, ind
+
+
+def test_parallel_obj_parser_matches_a_sequential_restatement(tmp_path):
+    """The OBJ reader parses the file in one chunk per host thread (f-2: parallel ingest).  A synthetic file large enough for several chunks, with the
+    features that make chunking delicate — relative (negative) indices that count back across chunk boundaries, polygons, `v//vn` and `v/vt` corners,
+    tabs, CRLF lines, comments, a second object that must be ignored — must give exactly what a line-by-line restatement of tobj gives."""
+    rng = np.random.default_rng(4)
+    lines = ["# synthetic", "o first"]
+    nv = nvt = nvn = 0
+    for block in range(400):
+        k = int(rng.integers(3, 9))
+        for _ in range(k):
+            x, y, z = rng.normal(size=3)
+            lines.append(("v\t%.7g %.7g %.7g" if block % 7 == 0 else "v %.7g %.7g %.7g") % (x, y, z)); nv += 1
+            lines.append("vn %.6f %.6f %.6f" % tuple(rng.normal(size=3))); nvn += 1
+            lines.append("vt %.5f %.5f" % tuple(rng.uniform(size=2))); nvt += 1
+        for _ in range(20):
+            m = int(rng.integers(3, 6))
+            style = int(rng.integers(0, 4))
+            toks = []
+            for _ in range(m):
+                if style == 0:      # absolute, all three, possibly far back
+                    i = int(rng.integers(1, nv + 1)); toks.append(f"{i}/{int(rng.integers(1, nvt + 1))}/{int(rng.integers(1, nvn + 1))}")
+                elif style == 1:    # relative
+                    i = -int(rng.integers(1, min(nv, 50) + 1)); toks.append(f"{i}/{i}/{i}")
+                elif style == 2:
+                    i = int(rng.integers(1, nv + 1)); toks.append(f"{i}//{i}")
+                else:
+                    i = int(rng.integers(1, nv + 1)); toks.append(f"{i}/{i}/{i}")
+            lines.append("f " + " ".join(toks) + ("\r" if block % 5 == 0 else "") + (" # c" if block % 11 == 0 and not block % 5 == 0 else ""))
+    lines += ["o second", "v 9 9 9", "f 1 2 -1"]
+    path = tmp_path / "big.obj"
+    path.write_bytes(("\n".join(lines) + "\n").encode())
+    assert path.stat().st_size > 3 * 256 * 1024 // 2          # several 256 KB chunks
+    xf = [2, 0, 0, 1, 0, 3, 0, -2, 0.5, 0, 1, 0, 0, 0, 0, 2]
+    got, want = _load_obj_native(path, xf), _py_obj(path, xf)
+    for g, w, what in zip(got, want, ("points", "normals", "uvs", "indices")):
+        assert g.shape == w.shape and np.array_equal(g, w), what
+
+
+@pytest.mark.skipif(not os.path.exists(REF_DATA + "/stormtrooper/shape_0.obj"), reason="reference assets only exist in the build container")
+@pytest.mark.parametrize("asset", ["material/models/Mesh001.obj", "stormtrooper/shape_0.obj", "stormtrooper/shape_mesh.obj"])
+def test_parallel_obj_parser_on_reference_assets(asset):
+    if not os.path.exists(REF_DATA + "/" + asset):
+        pytest.skip("asset absent")
+    xf = np.eye(4).reshape(16)
+    got, want = _load_obj_native(REF_DATA + "/" + asset, xf), _py_obj(REF_DATA + "/" + asset, xf)
+    for g, w, what in zip(got, want, ("points", "normals", "uvs", "indices")):
+        assert g.shape == w.shape and np.array_equal(g, w), (asset, what)
