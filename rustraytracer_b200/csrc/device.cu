@@ -16,7 +16,7 @@ namespace rt {
         if (e_ != cudaSuccess) { set_error(std::string(#call) + ": " + cudaGetErrorString(e_)); return RT_ERR_CUDA; } \
     } while (0)
 
-template <class T> static rt_status up(rt_scene& s, const std::vector<T>& h, const T*& dptr, uint64_t& bytes) {
+template <class T, class A> static rt_status up(rt_scene& s, const std::vector<T, A>& h, const T*& dptr, uint64_t& bytes) {
     dptr = nullptr;
     size_t n = h.size() * sizeof(T);
     void* p = nullptr;
@@ -170,8 +170,11 @@ rt_status upload_scene(rt_scene& s, HostImage& img) {
     if ((st = up(s, s.materials, d.materials, b))) return st;
     if ((st = up(s, s.disneys, d.disneys, b))) return st;
     {   // per-primitive shading bin
-        std::vector<uint8_t> bins(img.prims.size());
-        for (size_t i = 0; i < bins.size(); i++) bins[i] = (uint8_t)(s.materials[img.prims[i].mat].type * 2u + ((img.prims[i].info & 7u) == RT_PRIM_TRIANGLE ? 1u : 0u));
+        HVec<uint8_t> bins; bins.resize(img.prims.size());
+        uint8_t* bp = bins.data(); const DPrim* pp = img.prims.data(); const rt_material* mp = s.materials.data();
+        par_for(bins.size(), (size_t)1 << 18, [=](size_t b0, size_t e0) {
+            for (size_t i = b0; i < e0; i++) bp[i] = (uint8_t)(mp[pp[i].mat].type * 2u + ((pp[i].info & 7u) == RT_PRIM_TRIANGLE ? 1u : 0u));
+        });
         if ((st = up(s, bins, d.prim_bin, b))) return st;
     }
     d.has_disney = 0;

@@ -5,6 +5,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <dlfcn.h>
+#include <atomic>
 #include <cstdint>
 #include <thread>
 #include <mutex>
@@ -202,8 +203,8 @@ void statue_standin(rt::HostMesh& m, uint64_t seed, uint64_t n_tris) {
 // ---- parser::parse_obj (parser.rs:8-87) over a tobj-2.0.2-style loader -------------------------
 // Two passes.  (1) text -> numbers, PARALLEL: the file is cut into one chunk per host thread at line boundaries; every chunk parses its `v` / `vn` / `vt`
 // lines into its own arrays and keeps its faces as raw (v, vt, vn) index tokens together with how many v / vt / vn lines of the chunk precede the face
-// (relative indices count back from there).  (2) single-index re-indexing, SEQUENTIAL because tobj numbers the (v, vt, vn) triples in order of first
-// appearance: an open-addressing hash on the triple instead of a tree map.  Only models[0] is used (parser.rs:21): reading stops at the first `o` / `g`
+// (relative indices count back from there).  (2) single-index re-indexing, parallel as well: tobj numbers the (v, vt, vn) triples in order of first
+// appearance, which is the rank of each triple's smallest corner number — a concurrent hash table finds those minima, a prefix sum ranks them.  Only models[0] is used (parser.rs:21): reading stops at the first `o` / `g`
 // line that follows a face.  Values are f32 (tobj) widened to f64; strtof and Rust's str::parse::<f32> both round correctly, so they agree.
 struct ObjCorner { int iv, it, in; bool ht, hn; };
 struct ObjChunk {
@@ -247,7 +248,6 @@ static void obj_parse_chunk(const char* buf, size_t begin, size_t end, ObjChunk&
         pos = eol + 1;
     }
 }
-struct ObjKeySlot { int a, b, c; uint32_t id; };
 bool load_obj(const char* path, const double* xf, rt::HostMesh& out, std::string& err) {
     FILE* f = fopen(path, "rb");
     if (!f) { err = std::string("cannot open ") + path; return false; }
@@ -258,7 +258,7 @@ bool load_obj(const char* path, const double* xf, rt::HostMesh& out, std::string
     buf[got] = '\n';                                           // strtof / strtol always meet a terminator
     const size_t size = got;
     // pass 1: chunks at line boundaries
-    size_t n_chunks = std::max<size_t>(1, std::min<size_t>(std::thread::hardware_concurrency(), size / (256 * 1024) + 1));
+    size_t n_chunks = std::max<size_t>(1, std::min<size_t>(rt::host_threads(), size / (256 * 1024) + 1));
     std::vector<size_t> cut(n_chunks + 1, size);
     cut[0] = 0;
     for (size_t k = 1; k < n_chunks; k++) { size_t q = std::max(cut[k - 1], size * k / n_chunks); while (q < size && buf[q] != '\n') q++; cut[k] = std::min(size, q + 1); }
@@ -282,51 +282,116 @@ bool load_obj(const char* path, const double* xf, rt::HostMesh& out, std::string
         if (!chunks[k].vt.empty()) memcpy(&vt[2 * bt[k]], chunks[k].vt.data(), chunks[k].vt.size() * 4);
         if (!chunks[k].vn.empty()) memcpy(&vn[3 * bn[k]], chunks[k].vn.data(), chunks[k].vn.size() * 4);
     }
-    // pass 2: (v, vt, vn) triples -> single index, in order of first appearance
-    size_t cap = 16; while (cap < 2 * n_corners + 16) cap <<= 1;
-    std::vector<ObjKeySlot> table(cap, ObjKeySlot{0, 0, 0, 0xffffffffu});
-    std::vector<float> pos, nor, tex; rt::HVec<uint32_t> ind;
-    pos.reserve(3 * bv[n_chunks]); ind.reserve(3 * n_corners);
-    std::vector<uint32_t> poly;
+    // pass 2: (v, vt, vn) triples -> single index in order of first appearance (tobj's numbering), without a sequential walk:
+    //   a. every corner of models[0] gets its absolute key — relative indices resolved against the v / vt / vn counts in front of its face (per chunk)
+    //   b. concurrent open-addressing table on the triple; a slot ends up holding the SMALLEST global corner number that carries its key
+    //      (compare-and-swap into an empty slot, atomic minimum afterwards: whatever sits in a slot always has the slot's key)
+    //   c. a corner is a first appearance iff it is its slot's minimum; the exclusive prefix sum of those flags in corner order is the numbering
+    //   d. attributes of the first appearances and the fan triangulation are written straight to their final places
+    std::vector<size_t> nf(n_chunks, 0), cb(n_chunks + 1, 0), tb(n_chunks + 1, 0);      // faces in front of `stop`, corner / triangle bases per chunk
     for (size_t k = 0; k < n_chunks; k++) {
         const ObjChunk& c = chunks[k];
-        for (const ObjChunk::Face& fc : c.faces) {
-            if (fc.off >= stop) break;
-            const int nv = (int)(bv[k] + fc.nv), nt = (int)(bt[k] + fc.nt), nn = (int)(bn[k] + fc.nn);
-            poly.clear();
-            for (uint32_t j = fc.first; j < fc.first + fc.n; j++) {
-                const ObjCorner& q = c.corners[j];
-                const int iv = q.iv < 0 ? nv + q.iv : q.iv - 1, it = q.ht ? (q.it < 0 ? nt + q.it : q.it - 1) : -1, in = q.hn ? (q.in < 0 ? nn + q.in : q.in - 1) : -1;
-                if (iv < 0 || iv >= nv) { err = "face index out of range"; return false; }
-                uint64_t h = ((uint64_t)(uint32_t)iv * 0x9E3779B97F4A7C15ull) ^ ((uint64_t)(uint32_t)it * 0xC2B2AE3D27D4EB4Full) ^ ((uint64_t)(uint32_t)in * 0x165667B19E3779F9ull);
-                size_t slot = (size_t)(h ^ (h >> 29)) & (cap - 1);
-                while (table[slot].id != 0xffffffffu && !(table[slot].a == iv && table[slot].b == it && table[slot].c == in)) slot = (slot + 1) & (cap - 1);
-                if (table[slot].id == 0xffffffffu) {
-                    table[slot] = ObjKeySlot{iv, it, in, (uint32_t)(pos.size() / 3)};
-                    pos.push_back(v[3 * (size_t)iv]); pos.push_back(v[3 * (size_t)iv + 1]); pos.push_back(v[3 * (size_t)iv + 2]);
-                    if (it >= 0 && it < nt) { tex.push_back(vt[2 * (size_t)it]); tex.push_back(vt[2 * (size_t)it + 1]); }
-                    if (in >= 0 && in < nn) { nor.push_back(vn[3 * (size_t)in]); nor.push_back(vn[3 * (size_t)in + 1]); nor.push_back(vn[3 * (size_t)in + 2]); }
+        size_t f = 0, tris = 0;
+        while (f < c.faces.size() && c.faces[f].off < stop) { tris += c.faces[f].n >= 3 ? c.faces[f].n - 2 : 0; f++; }
+        nf[k] = f;
+        cb[k + 1] = cb[k] + (f ? (size_t)c.faces[f - 1].first + c.faces[f - 1].n : 0);
+        tb[k + 1] = tb[k] + tris;
+    }
+    const size_t NC = cb[n_chunks], NT = tb[n_chunks];
+    if (NT == 0) { err = std::string("no faces in ") + path; return false; }
+    if (NC >= 0x7fffffffull) { err = "too many face corners"; return false; }
+    rt::HVec<int> kv, kt, kn; rt::HVec<uint8_t> cflag; rt::HVec<uint32_t> slot_of, cid;
+    kv.resize(NC); kt.resize(NC); kn.resize(NC); cflag.resize(NC); slot_of.resize(NC); cid.resize(NC);
+    std::atomic<int> bad{0};
+    rt::par_for(n_chunks, 1, [&](size_t k0, size_t k1) {
+        for (size_t k = k0; k < k1; k++) {
+            const ObjChunk& c = chunks[k];
+            for (size_t f = 0; f < nf[k]; f++) {
+                const ObjChunk::Face& fc = c.faces[f];
+                const int nv = (int)(bv[k] + fc.nv), nt = (int)(bt[k] + fc.nt), nn = (int)(bn[k] + fc.nn);
+                for (uint32_t j = fc.first; j < fc.first + fc.n; j++) {
+                    const ObjCorner& q = c.corners[j];
+                    const int iv = q.iv < 0 ? nv + q.iv : q.iv - 1, it = q.ht ? (q.it < 0 ? nt + q.it : q.it - 1) : -1, in = q.hn ? (q.in < 0 ? nn + q.in : q.in - 1) : -1;
+                    if (iv < 0 || iv >= nv) { bad.store(1); return; }
+                    const size_t g = cb[k] + j;
+                    kv[g] = iv; kt[g] = it; kn[g] = in;
+                    cflag[g] = (uint8_t)((it >= 0 && it < nt ? 1 : 0) | (in >= 0 && in < nn ? 2 : 0));
                 }
-                poly.push_back(table[slot].id);
             }
-            for (size_t j = 1; j + 1 < poly.size(); j++) { ind.push_back(poly[0]); ind.push_back(poly[j]); ind.push_back(poly[j + 1]); }   // fan triangulation
         }
-        if (!c.faces.empty() && c.faces.back().off >= stop) break;
-    }
-    if (ind.empty()) { err = std::string("no faces in ") + path; return false; }
-    const size_t np = pos.size() / 3;
-    out.p.resize(3 * np);
-    rt::par_for(np, 1 << 16, [&](size_t b, size_t e) {
-        for (size_t i = b; i < e; i++) { double pt[3] = {(double)pos[3 * i], (double)pos[3 * i + 1], (double)pos[3 * i + 2]}, o[3]; xf_point(xf, pt, o); out.p[3 * i] = o[0]; out.p[3 * i + 1] = o[1]; out.p[3 * i + 2] = o[2]; }
     });
-    if (nor.size() == pos.size()) {
-        out.n.resize(3 * np);
-        rt::par_for(np, 1 << 16, [&](size_t b, size_t e) {
-            for (size_t i = b; i < e; i++) { double vv[3] = {(double)nor[3 * i], (double)nor[3 * i + 1], (double)nor[3 * i + 2]}, o[3]; xf_vector(xf, vv, o); out.n[3 * i] = o[0]; out.n[3 * i + 1] = o[1]; out.n[3 * i + 2] = o[2]; }
-        });
-    }
-    if (tex.size() / 2 == np) { out.uv.resize(2 * np); for (size_t i = 0; i < 2 * np; i++) out.uv[i] = (double)tex[i]; }
-    out.ind = std::move(ind);
+    if (bad.load()) { err = "face index out of range"; return false; }
+    size_t cap = 16; while (cap < 2 * NC + 16) cap <<= 1;
+    const uint32_t EMPTY = 0xffffffffu;
+    std::unique_ptr<std::atomic<uint32_t>[]> table(new std::atomic<uint32_t>[cap]);
+    rt::par_for(cap, (size_t)1 << 18, [&](size_t b0, size_t e0) { for (size_t i = b0; i < e0; i++) table[i].store(EMPTY, std::memory_order_relaxed); });
+    rt::par_for(NC, (size_t)1 << 15, [&](size_t b0, size_t e0) {
+        for (size_t g = b0; g < e0; g++) {
+            const int iv = kv[g], it = kt[g], in = kn[g];
+            const uint64_t h = ((uint64_t)(uint32_t)iv * 0x9E3779B97F4A7C15ull) ^ ((uint64_t)(uint32_t)it * 0xC2B2AE3D27D4EB4Full) ^ ((uint64_t)(uint32_t)in * 0x165667B19E3779F9ull);
+            size_t slot = (size_t)(h ^ (h >> 29)) & (cap - 1);
+            for (;;) {
+                uint32_t cur = table[slot].load(std::memory_order_relaxed);
+                if (cur == EMPTY && table[slot].compare_exchange_strong(cur, (uint32_t)g)) break;
+                if (kv[cur] == iv && kt[cur] == it && kn[cur] == in) {            // the slot's key is ours: keep the smaller corner number
+                    while ((uint32_t)g < cur && !table[slot].compare_exchange_weak(cur, (uint32_t)g)) {}
+                    break;
+                }
+                slot = (slot + 1) & (cap - 1);
+            }
+            slot_of[g] = (uint32_t)slot;
+        }
+    });
+    // first appearances, numbered in corner order
+    const size_t NB = std::max<size_t>(1, std::min<size_t>(rt::host_threads() * 4, NC / 4096 + 1)), blk = (NC + NB - 1) / NB;
+    std::vector<size_t> first_base(NB + 1, 0), tex_ok(NB, 0), nor_ok(NB, 0);
+    rt::par_for(NB, 1, [&](size_t q0, size_t q1) {
+        for (size_t q = q0; q < q1; q++) {
+            size_t n = 0, t = 0, m = 0;
+            for (size_t g = q * blk, e = std::min(NC, g + blk); g < e; g++) if (table[slot_of[g]].load(std::memory_order_relaxed) == (uint32_t)g) { n++; t += cflag[g] & 1; m += (cflag[g] >> 1) & 1; }
+            first_base[q + 1] = n; tex_ok[q] = t; nor_ok[q] = m;
+        }
+    });
+    size_t n_tex = 0, n_nor = 0;
+    for (size_t q = 0; q < NB; q++) { first_base[q + 1] += first_base[q]; n_tex += tex_ok[q]; n_nor += nor_ok[q]; }
+    const size_t np = first_base[NB];
+    const bool with_uv = n_tex == np, with_n = n_nor == np;        // parser.rs keeps normals / uvs only when every vertex has one
+    out.p.resize(3 * np);
+    if (with_n) out.n.resize(3 * np);
+    if (with_uv) out.uv.resize(2 * np);
+    rt::par_for(NB, 1, [&](size_t q0, size_t q1) {
+        for (size_t q = q0; q < q1; q++) {
+            size_t id = first_base[q];
+            for (size_t g = q * blk, e = std::min(NC, g + blk); g < e; g++) {
+                if (table[slot_of[g]].load(std::memory_order_relaxed) != (uint32_t)g) continue;
+                cid[g] = (uint32_t)id;
+                const float* pv = &v[3 * (size_t)kv[g]];
+                double pt[3] = {(double)pv[0], (double)pv[1], (double)pv[2]}, o[3];
+                xf_point(xf, pt, o); out.p[3 * id] = o[0]; out.p[3 * id + 1] = o[1]; out.p[3 * id + 2] = o[2];
+                if (with_n) { const float* pn = &vn[3 * (size_t)kn[g]]; double vv[3] = {(double)pn[0], (double)pn[1], (double)pn[2]}; xf_vector(xf, vv, o); out.n[3 * id] = o[0]; out.n[3 * id + 1] = o[1]; out.n[3 * id + 2] = o[2]; }
+                if (with_uv) { out.uv[2 * id] = (double)vt[2 * (size_t)kt[g]]; out.uv[2 * id + 1] = (double)vt[2 * (size_t)kt[g] + 1]; }
+                id++;
+            }
+        }
+    });
+    out.ind.resize(3 * NT);
+    rt::par_for(n_chunks, 1, [&](size_t k0, size_t k1) {
+        for (size_t k = k0; k < k1; k++) {
+            const ObjChunk& c = chunks[k];
+            size_t t = tb[k];
+            for (size_t f = 0; f < nf[k]; f++) {
+                const ObjChunk::Face& fc = c.faces[f];
+                auto id_of = [&](uint32_t j) { return cid[table[slot_of[cb[k] + j]].load(std::memory_order_relaxed)]; };
+                if (fc.n < 3) continue;
+                const uint32_t i0 = id_of(fc.first);
+                uint32_t prev = id_of(fc.first + 1);
+                for (uint32_t j = fc.first + 2; j < fc.first + fc.n; j++) {                 // fan triangulation
+                    const uint32_t cur = id_of(j);
+                    out.ind[3 * t] = i0; out.ind[3 * t + 1] = prev; out.ind[3 * t + 2] = cur; t++; prev = cur;
+                }
+            }
+        }
+    });
     return true;
 }
 bool file_exists(const std::string& p) { FILE* f = fopen(p.c_str(), "rb"); if (f) { fclose(f); return true; } return false; }

@@ -12,12 +12,15 @@
 #pragma once
 #include <algorithm>
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <new>
 #include <string>
 #include <thread>
 #include <utility>
 #include <vector>
+#include <sys/mman.h>
 #include "../../include/rtcore.h"
 
 namespace rt {
@@ -28,18 +31,38 @@ constexpr double PI = 3.14159265358979;  // consts.rs:31
 
 // Host-side bulk arrays (mesh tables, primitive runs: gigabytes at 50 M triangles).  HVec is a std::vector whose resize() leaves trivially constructible
 // elements uninitialised, so that the pages are first touched by the THREADS that fill them (par_for) instead of being zeroed by one thread first.
+// Blocks of 4 MB and more are 2 MB-aligned and marked MADV_HUGEPAGE: a cold 10 M-triangle ingest is otherwise bound by ~400 K first-touch page faults
+// (measured here: 1.06 s cold against 0.17 s into already-mapped memory, 8 threads), with transparent huge pages in `madvise` mode it is ~800.
 template <class T> struct NoInitAlloc : std::allocator<T> {
     template <class U> struct rebind { typedef NoInitAlloc<U> other; };
     NoInitAlloc() = default;
     template <class U> NoInitAlloc(const NoInitAlloc<U>&) {}
+    T* allocate(size_t n) {
+        const size_t bytes = n * sizeof(T);
+        if (bytes >= ((size_t)4 << 20)) {
+            void* p = nullptr;
+            if (posix_memalign(&p, (size_t)2 << 20, bytes) != 0 || !p) throw std::bad_alloc();
+            madvise(p, bytes, MADV_HUGEPAGE);                  // advisory: failure leaves ordinary pages
+            return (T*)p;
+        }
+        T* p = (T*)malloc(bytes ? bytes : 1);
+        if (!p) throw std::bad_alloc();
+        return p;
+    }
+    void deallocate(T* p, size_t) { free(p); }
     template <class U, class... A> void construct(U* p, A&&... a) {
         if constexpr (sizeof...(A) == 0) ::new ((void*)p) U; else ::new ((void*)p) U(std::forward<A>(a)...);
     }
 };
 template <class T> using HVec = std::vector<T, NoInitAlloc<T>>;
+// host threads used by the ingest / build code: all of them, or RT_HOST_THREADS (measurement knob: ingest on 1 thread vs all)
+inline size_t host_threads() {
+    if (const char* e = getenv("RT_HOST_THREADS")) { const long v = atol(e); if (v > 0) return (size_t)v; }
+    return std::max<size_t>(1, std::thread::hardware_concurrency());
+}
 // fn(begin, end) over [0, n) on the host threads (one chunk each); runs inline for small n
 template <class F> inline void par_for(size_t n, size_t min_per_thread, F fn) {
-    size_t t = std::max<size_t>(1, std::min<size_t>(std::thread::hardware_concurrency(), n / std::max<size_t>(min_per_thread, 1)));
+    size_t t = std::max<size_t>(1, std::min<size_t>(host_threads(), n / std::max<size_t>(min_per_thread, 1)));
     if (t <= 1) { fn((size_t)0, n); return; }
     std::vector<std::thread> pool;
     const size_t chunk = (n + t - 1) / t;

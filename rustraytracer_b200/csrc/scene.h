@@ -44,7 +44,7 @@ double prim_area(const rt_scene& s, const HostPrim& p);
 bool invert4(const double m[16], double out[16]);
 // what commit hands to the device uploader (device.cu)
 struct HostImage {
-    std::vector<DNodeT> nodes; std::vector<DSlot> slots; std::vector<DPrim> prims; std::vector<DMesh> meshes;
+    std::vector<DNodeT> nodes; HVec<DSlot> slots; HVec<DPrim> prims; std::vector<DMesh> meshes;      // slots / prims: filled in full by the flatten threads (HVec: not zeroed first)
     std::vector<double> shapes;              // points / normals / uvs / indices are uploaded from rt_scene::meshes directly
     std::vector<DLight> lights;
     // Infinite lights: flat Distribution2D tables, concatenated; DLight pointers hold OFFSETS (in doubles) until upload

@@ -220,7 +220,7 @@ rt_status build_host_image(const rt_scene& s, HostImage& img, bool device_build)
     const bool use_direct = !img.direct.empty();
     std::vector<Box64> boxes(img.device_build ? 0 : n);
     std::mutex other_mu;
-    int threads = (int)std::max(1u, std::thread::hardware_concurrency());
+    int threads = (int)host_threads();
     {
         std::vector<std::thread> pool; size_t chunk = (n + threads - 1) / std::max(threads, 1);
         for (int t = 0; t < threads; t++) pool.emplace_back([&, t]() {

@@ -412,3 +412,30 @@ def test_parallel_obj_parser_on_reference_assets(asset):
     got, want = _load_obj_native(REF_DATA + "/" + asset, xf), _py_obj(REF_DATA + "/" + asset, xf)
     for g, w, what in zip(got, want, ("points", "normals", "uvs", "indices")):
         assert g.shape == w.shape and np.array_equal(g, w), (asset, what)
+
+
+@pytest.mark.parametrize("text,ok", [
+    (b"", False), (b"# only comments\n", False), (b"v 0 0 0\nv 1 0 0\n", False),                      # no faces: parser.rs unwraps models[0]
+    (b"v 0 0 0\nv 1 0 0\nv 0 1 0\nf 1 2 4\n", False), (b"v 0 0 0\nv 1 0 0\nv 0 1 0\nf -1 -2 -4\n", False),   # index past the vertices read so far
+    (b"v 0 0 0\nv 1 0 0\nv 0 1 0\nf 0 1 2\n", False),                                                     # OBJ indices start at 1
+    (b"v 0 0 0\nv 1 0 0\nf 1 2 3\nv 0 1 0\n", False),                                                     # a face may only look back
+    (b"v 0 0 0\nv 1 0 0\nv 0 1 0\nf 1 2 3", True),                                                        # no newline at the end of the file
+    (b"v\t0 0 0\r\nv 1 0 0\r\nv 0 1 0\r\nf\t1 2 3\r\n", True),
+    (b"v 0 0 0\nv 1 0 0\nv 0 1 0\nf 1 2\nf 1 2 3\n", True),                                             # a two-corner face yields no triangle
+])
+def test_obj_reader_edge_cases(tmp_path, text, ok):
+    path = tmp_path / "case.obj"
+    path.write_bytes(text)
+    h = C.c_void_p()
+    N.check(N.lib().rth_scene_create_empty(C.byref(h)))
+    rc = N.lib().rth_scene_add_obj(h, str(path).encode(), N.ptr(np.eye(4).reshape(16)), None)
+    if ok:
+        assert rc == 0
+        sz = (C.c_uint64 * 4)()
+        N.check(N.lib().rth_scene_mesh_sizes(h, 0, sz))
+        assert (sz[0], sz[3]) == (3, 3)
+    else:
+        assert rc != 0
+        N.lib().rth_last_error_string.restype = C.c_char_p
+        assert b"Failed to parse obj" in N.lib().rth_last_error_string()
+    N.lib().rth_scene_destroy(h)
