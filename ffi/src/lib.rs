@@ -287,6 +287,8 @@ extern "C" {
     pub fn rt_comm_destroy(comm: *mut rt_comm) -> RtStatus;
     pub fn rt_comm_size(comm: *const rt_comm, world_out: *mut u32, n_local_out: *mut u32) -> RtStatus;
     pub fn rt_film_allreduce(comm: *mut rt_comm, films: *const *mut rt_film, n_films: u32) -> RtStatus;
+    /// sum + resolve in one kernel over NVLink peer loads (one process, no NCCL); the films are not modified
+    pub fn rt_film_reduce_resolve_rgb8(films: *const *mut rt_film, n_films: u32, host_rgb: *mut u8) -> RtStatus;
     pub fn rt_scene_replicate(src: *const rt_scene, device: i32, out: *mut *mut rt_scene) -> RtStatus;
     pub fn rt_render_multi(comm: *mut rt_comm, scenes: *const *mut rt_scene, films: *const *mut rt_film, n: u32, camera: *const rt_camera,
                            integrator: *const rt_integrator_desc, desc: *const rt_film_desc) -> RtStatus;

@@ -344,6 +344,12 @@ rt_status rt_comm_destroy(rt_comm* comm);
 rt_status rt_comm_size(const rt_comm* comm, uint32_t* world_out, uint32_t* n_local_out);
 /* in-place sum over all ranks; films[i] lives on the communicator's i-th local device (n_films = 1 for a rank communicator).  Blocking. */
 rt_status rt_film_allreduce(rt_comm* comm, rt_film* const* films, uint32_t n_films);
+/* Sum AND resolve in one kernel, for the GPUs of ONE process: films[0]'s GPU reads the other accumulators in place over NVLink (peer access,
+ * enabled on first use), adds them in the order given — the same bits whatever a ring or a tree would have done — applies point_to_color
+ * (util.rs:441-471) and returns width*height*3 bytes.  No NCCL, no communicator, no reduced film in memory; the films are not modified.  This is
+ * what follows a multi-GPU render when only the picture is wanted (render.rs:117-153 merges the workers' tiles, then saves it); rt_film_allreduce
+ * stays for callers that go on accumulating.  At most 16 films; RT_ERR_STATE when the GPUs have no peer access to each other.            */
+rt_status rt_film_reduce_resolve_rgb8(rt_film* const* films, uint32_t n_films, uint8_t* host_rgb);
 /* a new scene with src's tables, committed on `device` (build mode and wavefront size carry over) */
 rt_status rt_scene_replicate(const rt_scene* src, int32_t device, rt_scene** out);
 /* rt_render on the n GPUs of a LOCAL communicator: scenes[g] / films[g] on its g-th device; GPU g adds samples

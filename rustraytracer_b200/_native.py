@@ -81,6 +81,7 @@ RTCORE_SYMBOLS = [
     "rt_render_cancel", "rt_get_counters", "rt_set_wavefront_size", "rt_scene_set_build_mode", "rt_scene_build_stats",
     "rt_debug_prefilter_stats", "rt_film_resolve_rgb8_static",
     "rt_comm_create_local", "rt_comm_unique_id", "rt_comm_create_rank", "rt_comm_destroy", "rt_comm_size", "rt_film_allreduce", "rt_scene_replicate", "rt_render_multi",
+    "rt_film_reduce_resolve_rgb8",
 ]
 RTHOST_SYMBOLS = [
     "rth_scene_build", "rth_scene_destroy", "rth_scene_camera", "rth_scene_png_name", "rth_scene_uses_standin", "rth_scene_counts",
@@ -132,6 +133,7 @@ def _load_core():
         "rt_scene_set_build_mode": [vp, u32], "rt_scene_build_stats": [vp, vp], "rt_debug_prefilter_stats": [vp],
         "rt_comm_create_local": [vp, u32, vp], "rt_comm_unique_id": [vp], "rt_comm_create_rank": [vp, u32, u32, vp], "rt_comm_destroy": [vp],
         "rt_comm_size": [vp, vp, vp], "rt_film_allreduce": [vp, vp, u32], "rt_scene_replicate": [vp, C.c_int32, vp], "rt_render_multi": [vp, vp, vp, u32, vp, vp, vp],
+        "rt_film_reduce_resolve_rgb8": [vp, u32, vp],
     }
     for name, args in sigs.items():
         if not hasattr(L, name):

@@ -279,6 +279,15 @@ class Film:
         check(lib().rt_film_resolve_rgb8_static(self.h, ptr(out)))
         return out
 
+    @staticmethod
+    def reduce_resolve_rgb8(films):
+        """rt_film_reduce_resolve_rgb8: the films of one process's GPUs summed (in list order) and resolved to RGB8 by one kernel on films[0]'s GPU,
+        which reads the others over NVLink; no NCCL, the films stay as they are."""
+        out = np.zeros((films[0].height, films[0].width, 3), dtype=np.uint8)
+        arr = (C.c_void_p * len(films))(*[f.h for f in films])
+        check(lib().rt_film_reduce_resolve_rgb8(arr, len(films), ptr(out)))
+        return out
+
     def close(self):
         if self.h:
             lib().rt_film_destroy(self.h)

@@ -17,6 +17,7 @@
 #include <cstring>
 #include <mutex>
 #include "wavefront.cuh"
+#include "film.cuh"
 #include "traverse.cuh"
 
 namespace rt {
@@ -352,18 +353,10 @@ __global__ void __launch_bounds__(128, CONNECT_MIN_BLOCKS) k_connect(Ctrl* c, DS
     trace_jobs(sc, job, n_shadow + n_probe, &c->fetch[1]);
 }
 
-// util::point_to_color (util.rs:441-471) with aces_comp (util.rs:400-408)
+// util::point_to_color (util.rs:441-471): film.cuh
 __global__ void k_resolve(const double* __restrict__ film, uint64_t n, uint8_t* __restrict__ rgb) {
-    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
-        double scale = 1. / film[4 * i + 3];
-        for (int k = 0; k < 3; k++) {
-            double x = film[4 * i + k] * scale * 0.6;
-            double a = 2.51, b = 0.03, cc = 2.43, dd = 0.59, e = 0.14;
-            double v = clampd((x * (a * x + b)) / (x * (cc * x + dd) + e), 0., 1.);
-            double r = round(pow(v, 1. / 2.2) * 256.);
-            rgb[3 * i + k] = !(r > 0.) ? 0 : (r > 255. ? 255 : (uint8_t)r);          // Rust `as u8` saturates, NaN → 0
-        }
-    }
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+        resolve_pixel(film[4 * i], film[4 * i + 1], film[4 * i + 2], film[4 * i + 3], rgb + 3 * i);
 }
 
 }  // namespace rt

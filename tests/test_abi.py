@@ -275,6 +275,7 @@ def test_multi_gpu_entry_points_argument_errors():
     assert L.rt_comm_create_rank(N.ptr(ident), 2, 2, C.byref(h)) == N.RT_ERR_INVALID      # rank >= world
     assert L.rt_comm_create_rank(None, 2, 0, C.byref(h)) == N.RT_ERR_INVALID
     assert L.rt_film_allreduce(None, None, 0) == N.RT_ERR_INVALID
+    assert L.rt_film_reduce_resolve_rgb8(None, 0, None) == N.RT_ERR_INVALID
     assert L.rt_render_multi(None, None, None, 0, None, None, None) == N.RT_ERR_INVALID
     assert L.rt_scene_replicate(None, 0, C.byref(h)) == N.RT_ERR_INVALID
     assert L.rt_comm_size(None, None, None) == N.RT_ERR_INVALID

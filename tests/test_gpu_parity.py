@@ -9,6 +9,7 @@ counter-based RNG on both sides, so they are compared per pixel, not just statis
 import os
 
 import numpy as np
+import torch  # noqa: F401  (first: librtcore's run-time NCCL binding must find torch's copy, not load the system one under it)
 import pytest
 
 import orc
@@ -847,6 +848,67 @@ def test_render_multi_matches_single_gpu():
     c0, c1 = g0.counters(), g1.counters()
     assert c0["paths"] == c1["paths"] == w * h * 8
     comm.close()
+
+
+def _resolve_of_sum(parts, w, h):
+    """the one-GPU resolve of a film that holds the f64 sum of `parts` taken in list order (numpy adds round like the device's)"""
+    import torch
+    total = parts[0].copy()
+    for q in parts[1:]:
+        total = total + q
+    t = torch.from_numpy(np.ascontiguousarray(total)).to("cuda:0")
+    torch.cuda.synchronize()
+    ext = Film(w, h, device_ptr=t.data_ptr())                 # rt_film_create_external over the tensor (kept alive until after the resolve)
+    out = ext.resolve_rgb8()
+    ext.close()
+    return out
+
+
+def test_fused_reduce_resolve_on_one_gpu():
+    """rt_film_reduce_resolve_rgb8 with every film on the same GPU (no peer access needed): three sample ranges of one render, summed in list order
+    and resolved by ONE kernel, give byte for byte the one-GPU resolve of the film that holds that sum; the inputs are left untouched."""
+    from rustraytracer_b200._native import check, lib
+    check(lib().rt_set_device(0))
+    w = h = 96
+    hs = scenes.HostScene("cornell_box", w, h)
+    g = hs.upload(); cam = hs.camera()
+    films = [Film(w, h) for _ in range(3)]
+    for f, (a, b) in zip(films, ((0, 5), (5, 6), (6, 16))):
+        render_samples(g, cam, IntType.Path(6, shade_f32=True), f, w, h, a, b, seed=21)
+    before = [f.read() for f in films]
+    got = Film.reduce_resolve_rgb8(films)
+    assert np.array_equal(got, _resolve_of_sum(before, w, h))
+    assert all(np.array_equal(f.read(), b) for f, b in zip(films, before))
+    assert np.array_equal(Film.reduce_resolve_rgb8(films[:1]), films[0].resolve_rgb8())          # one film: the plain resolve
+    whole = Film(w, h)
+    render_samples(g, cam, IntType.Path(6, shade_f32=True), whole, w, h, 0, 16, seed=21)
+    diff = np.abs(got.astype(np.int32) - whole.resolve_rgb8().astype(np.int32))                   # same samples, other summation order: <= 1 code value
+    assert diff.max() <= 1
+    small = Film(w // 2, h)
+    with pytest.raises(Exception):
+        Film.reduce_resolve_rgb8([films[0], small])
+
+
+def test_fused_reduce_resolve_over_nvlink():
+    """The same with the films on two GPUs: GPU 0 reads GPU 1's accumulator in place over NVLink (peer loads) inside the resolve kernel."""
+    from rustraytracer_b200 import replicate
+    from rustraytracer_b200._native import check, lib
+    if lib().rt_device_count() < 2:
+        pytest.skip("needs two GPUs")
+    w = h = 128
+    hs = scenes.HostScene("cornell_box", w, h)
+    check(lib().rt_set_device(0))
+    g0 = hs.upload(); cam = hs.camera()
+    g1 = replicate(g0, 1)
+    f0 = Film(w, h)
+    check(lib().rt_set_device(1))
+    f1 = Film(w, h)
+    render_samples(g1, cam, IntType.Path(8), f1, w, h, 8, 16, seed=11)
+    check(lib().rt_set_device(0))
+    render_samples(g0, cam, IntType.Path(8), f0, w, h, 0, 8, seed=11)
+    got = Film.reduce_resolve_rgb8([f0, f1])
+    assert np.array_equal(got, _resolve_of_sum([f0.read(), f1.read()], w, h))
+    assert np.array_equal(Film.reduce_resolve_rgb8([f1, f0]), got)           # two terms: a + b == b + a, also with GPU 1 as the root
 
 
 # ---------------------------------------------------------------- Material::Disney (SURVEY §8f rank 4)
