@@ -27,11 +27,13 @@ def timed(fn):
     t0 = time.perf_counter(); r = fn(); return r, round(time.perf_counter() - t0, 3)
 
 
-def soup(n_tris, threads, gpu):
+def soup(n_tris, threads, gpu, plain_h2d=False):
+    if plain_h2d: os.environ["RT_H2D_PLAIN"] = "1"
+    else: os.environ.pop("RT_H2D_PLAIN", None)
     if threads: os.environ["RT_HOST_THREADS"] = str(threads)
     else: os.environ.pop("RT_HOST_THREADS", None)
     hs, t_gen = timed(lambda: scenes.HostScene("soup", 256, 256, n_tris=n_tris))
-    row = {"tris": n_tris, "host_threads": threads or os.cpu_count(), "generate_s": t_gen}
+    row = {"tris": n_tris, "host_threads": threads or os.cpu_count(), "h2d": "cudaMemcpy from pageable memory" if plain_h2d else "staged through two pinned buffers by the host threads", "generate_s": t_gen}
     if gpu:
         obj = Objects()
         _, row["upload_s"] = timed(lambda: check(lib().rth_scene_upload(hs.h, obj.h)))
@@ -94,8 +96,9 @@ def main():
     soup(100000, 0, gpu)                            # library loading (and the CUDA context, module load) stay out of the timings
     res = {"host_cores": os.cpu_count(), "soup": [], "obj": {}}
     for m in [float(x) for x in a.sizes.split(",")]:
-        for th in (1, 0):
-            reps = [soup(int(m * 1e6), th, gpu) for _ in range(a.reps)]
+        for th, plain in ((1, True), (0, True), (0, False)):
+            if plain and not gpu and th == 0: continue
+            reps = [soup(int(m * 1e6), th, gpu, plain) for _ in range(a.reps)]
             row = {k: (min(r[k] for r in reps) if k.endswith("_s") else reps[0][k]) for k in reps[0]}       # best of --reps; every repetition is kept below
             row["all_reps"] = [{k: r[k] for k in r if k.endswith("_s")} for r in reps]
             print(json.dumps(row), flush=True); res["soup"].append(row)
