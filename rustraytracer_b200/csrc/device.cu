@@ -266,7 +266,7 @@ void free_scene_device(rt_scene& s) {
 }
 
 // ---------------------------------------------------------------- kernels
-__global__ void __launch_bounds__(128) k_intersect(DScene sc, uint64_t n, const rt_ray* __restrict__ rays, double tmin, double tmax, rt_hit* __restrict__ hits) {
+__global__ void __launch_bounds__(128) k_intersect(const __grid_constant__ DScene sc, uint64_t n, const rt_ray* __restrict__ rays, double tmin, double tmax, rt_hit* __restrict__ hits) {
     for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
         const double2* rp = reinterpret_cast<const double2*>(rays + i);
         double2 a = __ldg(rp), b = __ldg(rp + 1), c = __ldg(rp + 2);
@@ -287,7 +287,7 @@ __global__ void __launch_bounds__(128) k_intersect(DScene sc, uint64_t n, const 
     }
 }
 
-__global__ void __launch_bounds__(128) k_closest(DScene sc, uint64_t n, const rt_ray* __restrict__ rays, double tmin, double tmax,
+__global__ void __launch_bounds__(128) k_closest(const __grid_constant__ DScene sc, uint64_t n, const rt_ray* __restrict__ rays, double tmin, double tmax,
                                                  uint32_t* __restrict__ prim, double* __restrict__ t) {
     for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
         const double2* rp = reinterpret_cast<const double2*>(rays + i);
@@ -316,12 +316,12 @@ struct ClosestJob {
     }
     __device__ __forceinline__ void finish(uint32_t i, const TState& st) { prim[i] = st.best.prim; t[i] = st.best.t; }
 };
-__global__ void __launch_bounds__(128, 5) k_closest_persistent(DScene sc, ClosestJob job, uint32_t n, uint32_t* counter) {
+__global__ void __launch_bounds__(128, 5) k_closest_persistent(const __grid_constant__ DScene sc, ClosestJob job, uint32_t n, uint32_t* counter) {
     job.sc = &sc;
     trace_jobs(sc, job, n, counter);
 }
 
-__global__ void __launch_bounds__(128) k_occluded(DScene sc, uint64_t n, const rt_shadow_query* __restrict__ q, uint8_t* __restrict__ out) {
+__global__ void __launch_bounds__(128) k_occluded(const __grid_constant__ DScene sc, uint64_t n, const rt_shadow_query* __restrict__ q, uint8_t* __restrict__ out) {
     for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
         rt_shadow_query s = q[i];
         out[i] = unoccluded(sc, mk3(s.p0[0], s.p0[1], s.p0[2]), mk3(s.p1[0], s.p1[1], s.p1[2]), s.p1_prim_index, s.infinite_light != 0) ? 1 : 0;

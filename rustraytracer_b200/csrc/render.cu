@@ -190,7 +190,7 @@ struct ExtendJob {
 #ifndef TRACE_GRID_BLOCKS
 #define TRACE_GRID_BLOCKS 8     // persistent grid = SMs x this
 #endif
-__global__ void __launch_bounds__(128, TRACE_MIN_BLOCKS) k_extend(Ctrl* c, DScene sc, PathSet ps, uint2* __restrict__ bin_idx, uint32_t W, SortParams sp) {
+__global__ void __launch_bounds__(128, TRACE_MIN_BLOCKS) k_extend(Ctrl* c, const __grid_constant__ DScene sc, PathSet ps, uint2* __restrict__ bin_idx, uint32_t W, SortParams sp) {
     ExtendJob job{c, &sc, ps, bin_idx, W, &sp};
     trace_jobs(sc, job, c->n_tot, &c->fetch[0]);
 }
@@ -255,7 +255,7 @@ __global__ void __launch_bounds__(256) k_sort_scatter(const Ctrl* c, SortParams 
 
 // Paths whose extend ray left the scene (bin 15).  Only launched when the scene has an Infinite light: at bounce 0 or after a
 // specular bounce every light's `le(ray)` is added (integrator.rs:406-410; Light::le is black for area lights).
-__global__ void __launch_bounds__(128) k_shade_miss(Ctrl* c, DScene sc, RenderParams rp, PathSet in, const uint2* __restrict__ bin_idx, double* film) {
+__global__ void __launch_bounds__(128) k_shade_miss(Ctrl* c, const __grid_constant__ DScene sc, const __grid_constant__ RenderParams rp, PathSet in, const uint2* __restrict__ bin_idx, double* film) {
     const uint32_t n = c->bin_count[N_BINS - 1];
     for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
         const uint32_t i = bin_idx[bin_first(c, rp, N_BINS - 1) + k].x;
@@ -347,7 +347,7 @@ struct ConnectJob {
 #ifndef CONNECT_MIN_BLOCKS
 #define CONNECT_MIN_BLOCKS TRACE_MIN_BLOCKS     // resident blocks per SM of k_connect alone (its load() / finish() carry more state than k_extend's)
 #endif
-__global__ void __launch_bounds__(128, CONNECT_MIN_BLOCKS) k_connect(Ctrl* c, DScene sc, ConnQ shq, ConnQ prq, double* film, uint32_t W) {
+__global__ void __launch_bounds__(128, CONNECT_MIN_BLOCKS) k_connect(Ctrl* c, const __grid_constant__ DScene sc, ConnQ shq, ConnQ prq, double* film, uint32_t W) {
     const uint32_t n_shadow = min(c->n_shadow, W), n_probe = min(c->n_probe, W);      // see k_prepare: counters may run past W on overflow
     ConnectJob job{&sc, shq, prq, film, n_shadow};
     trace_jobs(sc, job, n_shadow + n_probe, &c->fetch[1]);

@@ -37,13 +37,11 @@ constexpr uint32_t BSDF_REFLECTION = 1, BSDF_TRANSMISSION = 2, BSDF_DIFFUSE = 4,
 // Each Philox block yields two uniforms: dimension d uses block d >> 1, words (0,1) when d is even, (2,3) when odd.
 // The block computed for an even dimension is kept for the odd one that follows.
 struct Rng { uint32_t k0, k1, pixel, sample, dim; uint32_t w2, w3; };
-static __device__ RT_HELPER3 double rng_next(Rng& g) {
-    uint32_t d = g.dim++;
-    if ((d & 1u) && g.w2 != 0xffffffffu) {                 // cached second half (0xffffffff marks "none"; a genuine all-ones word just recomputes)
-        uint32_t a = g.w2, b = g.w3; g.w2 = 0xffffffffu;
-        return ((double)(a >> 5) * 67108864.0 + (double)(b >> 6)) / 9007199254740992.0;
-    }
-    uint32_t c0 = g.pixel, c1 = g.sample, c2 = d >> 1, c3 = 0x52544358u, k0 = g.k0, k1 = g.k1;
+// The block function is pure (registers in, registers out); the bookkeeping around it is always inlined, so that an Rng lives in the caller's
+// registers.  (As one out-of-line function taking Rng& it forced the generator into local memory: five local loads and up to three stores per draw,
+// about a third of the matte shade kernel's local-memory sectors — profiles/shade_matte_mem_by_source_r02.txt.)
+static __device__ RT_HELPER3 uint4 philox4x32_10(uint32_t k0, uint32_t k1, uint32_t c0, uint32_t c1, uint32_t c2) {
+    uint32_t c3 = 0x52544358u;
 #pragma unroll
     for (int r = 0; r < 10; r++) {
         uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
@@ -52,9 +50,19 @@ static __device__ RT_HELPER3 double rng_next(Rng& g) {
         c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
         k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
     }
-    if (d & 1u) return ((double)(c2 >> 5) * 67108864.0 + (double)(c3 >> 6)) / 9007199254740992.0;
-    g.w2 = c2; g.w3 = c3;
-    return ((double)(c0 >> 5) * 67108864.0 + (double)(c1 >> 6)) / 9007199254740992.0;
+    return make_uint4(c0, c1, c2, c3);
+}
+__device__ __forceinline__ double rng_next(Rng& g) {
+    const uint32_t d = g.dim++;
+    uint32_t a, b;
+    if ((d & 1u) && g.w2 != 0xffffffffu) {                 // cached second half (0xffffffff marks "none"; a genuine all-ones word just recomputes)
+        a = g.w2; b = g.w3; g.w2 = 0xffffffffu;
+    } else {
+        const uint4 r = philox4x32_10(g.k0, g.k1, g.pixel, g.sample, d >> 1);
+        if (d & 1u) { a = r.z; b = r.w; }
+        else { g.w2 = r.z; g.w3 = r.w; a = r.x; b = r.y; }
+    }
+    return ((double)(a >> 5) * 67108864.0 + (double)(b >> 6)) / 9007199254740992.0;
 }
 template <class R> __device__ __forceinline__ R to_unit(double u);
 template <> __device__ __forceinline__ double to_unit<double>(double u) { return u; }
@@ -443,8 +451,7 @@ template <class R, uint32_t KM> __device__ __forceinline__ R lobe_pdf_impl(const
 template <class R, uint32_t KM> static __device__ __noinline__ R lobe_pdf_call(const Lobe<R>& l, V3<R> wo, V3<R> wi) { return lobe_pdf_impl<R, KM>(l, wo, wi); }
 template <class R, uint32_t KM> __device__ __forceinline__ R lobe_pdf(const Lobe<R>& l, V3<R> wo, V3<R> wi) { if constexpr (km_small(KM)) { return lobe_pdf_impl<R, KM>(l, wo, wi); } else { return lobe_pdf_call<R, KM>(l, wo, wi); } }
 // util::rand_cosine_dir (util.rs:127-148)
-template <class R> static __device__ RT_HELPER V3<R> rand_cosine_dir(Rng& g) {
-    R r1 = rng_real<R>(g), r2 = rng_real<R>(g);
+template <class R> static __device__ RT_HELPER V3<R> cosine_dir_of(R r1, R r2) {
     R u1 = R(2) * r1 - R(1), u2 = R(2) * r2 - R(1);
     if (u1 == R(0) && u2 == R(0)) return v3<R>(R(0), R(0), R(1));
     R theta, r;
@@ -453,6 +460,7 @@ template <class R> static __device__ RT_HELPER V3<R> rand_cosine_dir(Rng& g) {
     R x = r * cos(theta), y = r * sin(theta);
     return v3<R>(x, y, sqrt(fmax(R(0), R(1) - x * x - y * y)));
 }
+template <class R> __device__ __forceinline__ V3<R> rand_cosine_dir(Rng& g) { const R r1 = rng_real<R>(g), r2 = rng_real<R>(g); return cosine_dir_of<R>(r1, r2); }   // the draws stay in the caller: no Rng&
 // Bxdf::sample_f (bxdf.rs:532-719)
 template <class R, uint32_t KM> __device__ __forceinline__ void lobe_sample_f_impl(const Lobe<R>& l, V3<R> wo, V2<R> sample, Rng& g, V3<R>& color, V3<R>& wi, R& pdf) {
     const V3<R> zero = v3<R>(R(0), R(0), R(0)), one = v3<R>(R(1), R(1), R(1));

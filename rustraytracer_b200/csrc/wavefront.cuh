@@ -115,7 +115,7 @@ template <class R> __device__ __forceinline__ R power_heuristic(R f_pdf, R g_pdf
 // ENVL = the scene has a Light::Infinite: only then are the environment-light arms compiled in (they cost the area-light-only
 // scenes ~5 % of shade time when always present: 52.8 -> 55.6 ms on the dragon, r01).
 template <class R, int MAT, int CLS, bool ENVL>
-__global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) k_shade(Ctrl* c, DScene sc, RenderParams rp, PathSet in, PathSet out,
+__global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) k_shade(Ctrl* c, const __grid_constant__ DScene sc, const __grid_constant__ RenderParams rp, PathSet in, PathSet out,
                                               const uint2* __restrict__ bin_idx, ConnQ shq, ConnQ prq, double* film) {
     constexpr uint32_t KM = mat_km<MAT>();
     constexpr int BIN = MAT * 2 + CLS;
