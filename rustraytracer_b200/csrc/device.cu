@@ -301,6 +301,7 @@ __global__ void __launch_bounds__(128) k_closest(const __grid_constant__ DScene 
 // fetch the next one from a global counter instead of idling until the slowest ray of the warp is done — the soup's
 // incoherent rays differ by an order of magnitude in traversal length.
 struct ClosestJob {
+    static constexpr bool shared_leaf_ray = false;      // traverse.cuh:trace_jobs
     const DScene* sc; const rt_ray* rays; double tmin_, tmax_; uint32_t* prim; double* t;
     __device__ __forceinline__ double tmin(const TState&) const { return tmin_; }
     __device__ __forceinline__ double tmax(const TState&) const { return tmax_; }

@@ -149,6 +149,7 @@ __global__ void k_film_count(RenderParams rp, unsigned long long generated, doub
 // per warp (__match_any_sync), so that the shade kernel runs warps of like work instead of diverging on the
 // reference's `match material` / `match primitive` arms.
 struct ExtendJob {
+    static constexpr bool shared_leaf_ray = false;      // traverse.cuh:trace_jobs
     Ctrl* c; const DScene* sc; PathSet ps; uint2* bin_idx; uint32_t W; const SortParams* sp;
     __device__ __forceinline__ double tmin(const TState&) const { return SMALL; }
     __device__ __forceinline__ double tmax(const TState&) const { return INF; }
@@ -280,6 +281,7 @@ __global__ void __launch_bounds__(128) k_shade_miss(Ctrl* c, const __grid_consta
 //    means "occluded"), then search for anything closer, stopping at the first one.
 // C: the MIS BSDF probe (integrator.rs:614-630): closest hit; counts only if it is the sampled light.
 struct ConnectJob {
+    static constexpr bool shared_leaf_ray = !RT_PREFILTER;      // traverse.cuh:trace_jobs
     const DScene* sc; ConnQ sh, pr; double* film; uint32_t n_shadow;
     __device__ __forceinline__ double tmin(const TState& st) const { return st.any ? 0. : SMALL; }     // shadow rays (any-hit): (0, INF); probes: (SMALL, INF)
     __device__ __forceinline__ double tmax(const TState&) const { return INF; }

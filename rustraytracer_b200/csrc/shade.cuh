@@ -253,7 +253,25 @@ template <class R> struct Lobe {
     R eta_a, eta_b;
 };
 // at most 2 lobes for Matte .. Mirror; Material::Disney builds up to 8 (material.rs:245-394) and is shaded by the f64 kernels only
-template <class R> struct Bsdf { V3<R> ns, ng, ss, ts; int n; bool empty; Lobe<R> lobes[sizeof(R) == 8 ? 8 : 2]; };
+template <class R> struct Bsdf { V3<R> ns, ng, ss, ts; int n; uint32_t mask; bool empty; Lobe<R> lobes[sizeof(R) == 8 ? 8 : 2]; };
+// The f32 (production) BSDF never indexes `lobes` with a run-time value: a material's lobes have FIXED slots (Plastic: 0 = Lambert, 1 = microfacet, ...) and
+// `mask` says which are present, so walking the present slots in slot order visits exactly the lobes, in exactly the order, that the reference's
+// `bxdfs` vector holds (a lobe that is left out there is a cleared bit here).  With static indices and no address handed to an out-of-line function
+// the whole Bsdf lives in registers and the constant fields (kind, type, fresnel) fold away; as an array in local memory it was the largest part of the
+// shade kernels' local-memory sectors, which outnumbered their global ones (profiles/shade_*_mem_by_source_r02.txt).  The f64 BSDF (up to 8 lobes,
+// Material::Disney) keeps the dense `n`-long array.
+template <class R> __device__ __forceinline__ Lobe<R>& add_lobe(Bsdf<R>& b, int slot) {
+    if constexpr (sizeof(R) == 4) { b.mask |= 1u << slot; b.n++; return b.lobes[slot]; }
+    else { b.mask |= 1u << b.n; return b.lobes[b.n++]; }       // dense append; `slot` is ignored
+}
+template <class R, class F> __device__ __forceinline__ void for_lobes(const Bsdf<R>& b, F&& fn) {          // fn(lobe, slot), present lobes in order
+    if constexpr (sizeof(R) == 4) { if (b.mask & 1u) fn(b.lobes[0], 0); if (b.mask & 2u) fn(b.lobes[1], 1); }
+    else { for (int i = 0; i < b.n; i++) fn(b.lobes[i], i); }
+}
+template <class R, class F> __device__ __forceinline__ void with_lobe(const Bsdf<R>& b, int slot, F&& fn) {   // fn(lobe) for one slot chosen at run time
+    if constexpr (sizeof(R) == 4) { if (slot == 0) fn(b.lobes[0]); else fn(b.lobes[1]); }
+    else fn(b.lobes[slot]);
+}
 
 // helpers of the Disney lobes (bxdf.rs:73-108, util.rs:173-183)
 template <class R> __device__ __forceinline__ R lerp_r(R t, R mn, R mx) { return (R(1) - t) * mn + t * mx; }
@@ -277,7 +295,10 @@ template <class R, uint32_t KM> __device__ __forceinline__ V3<R> fresnel_eval(co
     return v3<R>(R(1), R(1), R(1));
 }
 // ---- microfacet.rs, TrowbridgeReitz{sample_visible_area:true} / Empty
-template <class R> static __device__ RT_HELPER R mfd_d(const Lobe<R>& m, V3<R> wh) {                                        // microfacet.rs:53-68
+// the distribution's four fields travel BY VALUE into the out-of-line helpers: a `const Lobe&` parameter would pin the caller's lobe in local memory
+template <class R> struct Mfd { R alpha_x, alpha_y; bool mfd_empty, mfd_disney; };
+template <class R> __device__ __forceinline__ Mfd<R> mfd_of(const Lobe<R>& l) { Mfd<R> m; m.alpha_x = l.alpha_x; m.alpha_y = l.alpha_y; m.mfd_empty = l.mfd_empty; m.mfd_disney = l.mfd_disney; return m; }
+template <class R> static __device__ RT_HELPER R mfd_d(const Mfd<R> m, V3<R> wh) {                                        // microfacet.rs:53-68
     if (m.mfd_empty) return R(0);
     R t2 = tan_sq_theta(wh);
     if (isinf(t2)) return R(0);
@@ -286,7 +307,7 @@ template <class R> static __device__ RT_HELPER R mfd_d(const Lobe<R>& m, V3<R> w
     R e = ((cp * cp) / (m.alpha_x * m.alpha_x) + (sp * sp) / (m.alpha_y * m.alpha_y)) * t2;
     return R(1) / (pi<R>() * m.alpha_x * m.alpha_y * cos4 * (R(1) + e) * (R(1) + e));
 }
-template <class R> static __device__ RT_HELPER R mfd_lambda(const Lobe<R>& m, V3<R> w) {                                    // microfacet.rs:109-123
+template <class R> static __device__ RT_HELPER R mfd_lambda(const Mfd<R> m, V3<R> w) {                                    // microfacet.rs:109-123
     if (m.mfd_empty) return R(0);
     R att = fabs(tan_theta(w));
     if (isinf(att)) return R(0);
@@ -295,12 +316,12 @@ template <class R> static __device__ RT_HELPER R mfd_lambda(const Lobe<R>& m, V3
     R a2t2 = (alpha * att) * (alpha * att);
     return (R(-1) + sqrt(R(1) + a2t2)) / R(2);
 }
-template <class R> __device__ __forceinline__ R mfd_g1(const Lobe<R>& m, V3<R> w) { return R(1) / (R(1) + mfd_lambda(m, w)); }
-template <class R> __device__ __forceinline__ R mfd_g(const Lobe<R>& m, V3<R> wo, V3<R> wi) {       // microfacet.rs:146-157
+template <class R> __device__ __forceinline__ R mfd_g1(const Mfd<R> m, V3<R> w) { return R(1) / (R(1) + mfd_lambda(m, w)); }
+template <class R> __device__ __forceinline__ R mfd_g(const Mfd<R> m, V3<R> wo, V3<R> wi) {       // microfacet.rs:146-157
     if (sizeof(R) == 8 && m.mfd_disney) return mfd_g1(m, wo) * mfd_g1(m, wi);                       // DisneyMicrofacet: separable
     return R(1) / (R(1) + mfd_lambda(m, wo) + mfd_lambda(m, wi));
 }
-template <class R> __device__ __forceinline__ R mfd_pdf(const Lobe<R>& m, V3<R> wo, V3<R> wh) {                                // microfacet.rs:159-172
+template <class R> __device__ __forceinline__ R mfd_pdf(const Mfd<R> m, V3<R> wo, V3<R> wh) {                                // microfacet.rs:159-172
     if (!m.mfd_empty) return mfd_d(m, wh) * mfd_g1(m, wo) * fabs(dot(wo, wh)) / abs_cos_theta(wo);
     return mfd_d(m, wh) * abs_cos_theta(wh);
 }
@@ -330,7 +351,7 @@ template <class R> static __device__ RT_HELPER V2<R> tr_sample_11(R cos_t, R u1,
     out.x = slope_x; out.y = s * z * sqrt(R(1) + slope_x * slope_x);
     return out;
 }
-template <class R> static __device__ RT_HELPER V3<R> mfd_sample_wh(const Lobe<R>& m, V3<R> wo, V2<R> u) {                   // microfacet.rs:240-283, 448-467
+template <class R> static __device__ RT_HELPER V3<R> mfd_sample_wh(const Mfd<R> m, V3<R> wo, V2<R> u) {                   // microfacet.rs:240-283, 448-467
     if (m.mfd_empty) return normalize(v3<R>(R(0), R(0), R(0)));
     bool flip = wo.z < R(0);
     V3<R> wi = flip ? -wo : wo;
@@ -365,7 +386,7 @@ template <class R, uint32_t KM> __device__ __forceinline__ V3<R> lobe_f_impl(con
             if (is_black(wh)) return zero;
             wh = normalize(wh);
             V3<R> f = fresnel_eval<R, KM>(l, dot(wi, face_forward(wh, v3<R>(R(0), R(0), R(1)))));
-            V3<R> comp1 = l.color * mfd_d(l, wh) * mfd_g(l, wo, wi);
+            V3<R> comp1 = l.color * mfd_d(mfd_of(l), wh) * mfd_g(mfd_of(l), wo, wi);
             return cmul(comp1, f * (R(1) / (R(4) * cti * cto)));
         }
         if (KM_HAS(L_MICRO_T) && l.kind == L_MICRO_T) {
@@ -380,7 +401,7 @@ template <class R, uint32_t KM> __device__ __forceinline__ V3<R> lobe_f_impl(con
             R sqrt_denom = dot(wo, wh) + eta * dot(wi, wh);
             R factor = R(1) / eta;                                                           // mode == RADIANCE
             V3<R> c = cmul(v3<R>(R(1), R(1), R(1)) - f, l.color);
-            return c * fabs(mfd_d(l, wh) * mfd_g(l, wo, wi) * eta * eta * fabs(dot(wi, wh)) * fabs(dot(wo, wh)) * factor * factor /
+            return c * fabs(mfd_d(mfd_of(l), wh) * mfd_g(mfd_of(l), wo, wi) * eta * eta * fabs(dot(wi, wh)) * fabs(dot(wo, wh)) * factor * factor /
                             (cti * cto * sqrt_denom * sqrt_denom));
         }
         if (KM_HAS(L_LAMBERT_T) && l.kind == L_LAMBERT_T) return l.color * inv_pi<R>();                    // bxdf.rs:337
@@ -434,7 +455,7 @@ template <class R, uint32_t KM> __device__ __forceinline__ R lobe_pdf_impl(const
         if (KM_HAS(L_MICRO_R) && l.kind == L_MICRO_R) {
             if (!same_hemisphere(wo, wi)) return R(0);
             V3<R> wh = normalize(wo + wi);
-            return mfd_pdf(l, wo, wh) / (R(4) * dot(wo, wh));
+            return mfd_pdf(mfd_of(l), wo, wh) / (R(4) * dot(wo, wh));
         }
         if (KM_HAS(L_MICRO_T) && l.kind == L_MICRO_T) {
             if (same_hemisphere(wo, wi)) return R(0);
@@ -443,7 +464,7 @@ template <class R, uint32_t KM> __device__ __forceinline__ R lobe_pdf_impl(const
             if (dot(wo, wh) * dot(wi, wh) > R(0)) return R(0);
             R sqrt_denom = dot(wo, wh) + eta * dot(wi, wh);
             R dwh_dwi = fabs(eta * eta * dot(wi, wh)) / (sqrt_denom * sqrt_denom);
-            return mfd_pdf(l, wo, wh) * dwh_dwi;
+            return mfd_pdf(mfd_of(l), wo, wh) * dwh_dwi;
         }
         return R(0);     // SpecularTransmission: 0 ; FresnelSpecular: "unimplemented" → 0 (bxdf.rs:777-791)
     }
@@ -513,15 +534,15 @@ template <class R, uint32_t KM> __device__ __forceinline__ void lobe_sample_f_im
         }
         if (KM_HAS(L_MICRO_R) && l.kind == L_MICRO_R) {
             if (wo.z == R(0)) return;
-            V3<R> wh = mfd_sample_wh<R>(l, wo, sample);   // the wo·wh<0 guard has no `return` (bxdf.rs:598-600)
+            V3<R> wh = mfd_sample_wh<R>(mfd_of(l), wo, sample);   // the wo·wh<0 guard has no `return` (bxdf.rs:598-600)
             V3<R> w = reflect(wo, wh);
             if (!same_hemisphere(wo, w)) return;
-            pdf = mfd_pdf(l, wo, wh) / (R(4) * dot(wo, wh));
+            pdf = mfd_pdf(mfd_of(l), wo, wh) / (R(4) * dot(wo, wh));
             wi = w; color = lobe_f<R, KM>(l, wo, wi); return;
         }
         if (KM_HAS(L_MICRO_T) && l.kind == L_MICRO_T) {
             if (wo.z == R(0)) return;
-            V3<R> wh = mfd_sample_wh<R>(l, wo, sample);
+            V3<R> wh = mfd_sample_wh<R>(mfd_of(l), wo, sample);
             if (dot(wo, wh) < R(0)) return;
             R eta = wo.z > R(0) ? l.eta_a / l.eta_b : l.eta_b / l.eta_a;
             V3<R> w;
@@ -553,16 +574,16 @@ template <> __device__ __forceinline__ V3<float> local_to_world<float>(const Bsd
     return v3<float>(__fmaf_rn(b.ns.x, v.z, __fmaf_rn(b.ts.x, v.y, b.ss.x * v.x)), __fmaf_rn(b.ns.y, v.z, __fmaf_rn(b.ts.y, v.y, b.ss.y * v.x)),
                      __fmaf_rn(b.ns.z, v.z, __fmaf_rn(b.ts.z, v.y, b.ss.z * v.x)));
 }
-template <class R> __device__ __forceinline__ uint32_t num_components(const Bsdf<R>& b, uint32_t t) { uint32_t c = 0; for (int i = 0; i < b.n; i++) if (matches_flags(b.lobes[i].type, t)) c++; return c; }
+template <class R> __device__ __forceinline__ uint32_t num_components(const Bsdf<R>& b, uint32_t t) { uint32_t c = 0; for_lobes(b, [&](const Lobe<R>& l, int) { if (matches_flags(l.type, t)) c++; }); return c; }
 // Bsdf::f (bsdf.rs:83-98), `a && b || c` precedence kept (§8.1 #6)
 template <class R, uint32_t KM> __device__ __forceinline__ V3<R> bsdf_f_impl(const Bsdf<R>& b, V3<R> wow, V3<R> wiw, uint32_t flags) {
     V3<R> wi = world_to_local(b, wiw), wo = world_to_local(b, wow);
     bool refl = dot(wiw, b.ng) * dot(wow, b.ng) > R(0);
     V3<R> f = v3<R>(R(0), R(0), R(0));
-    for (int i = 0; i < b.n; i++) {
-        uint32_t ty = b.lobes[i].type;
-        if ((matches_flags(ty, flags) && (refl && (ty & BSDF_REFLECTION) > 0)) || (!refl && (ty & BSDF_TRANSMISSION) > 0)) f = f + lobe_f<R, KM>(b.lobes[i], wo, wi);
-    }
+    for_lobes(b, [&](const Lobe<R>& l, int) {
+        const uint32_t ty = l.type;
+        if ((matches_flags(ty, flags) && (refl && (ty & BSDF_REFLECTION) > 0)) || (!refl && (ty & BSDF_TRANSMISSION) > 0)) f = f + lobe_f<R, KM>(l, wo, wi);
+    });
     return f;
 }
 template <class R, uint32_t KM> static __device__ __noinline__ V3<R> bsdf_f_call(const Bsdf<R>& b, V3<R> wow, V3<R> wiw, uint32_t flags) { return bsdf_f_impl<R, KM>(b, wow, wiw, flags); }
@@ -573,7 +594,7 @@ template <class R, uint32_t KM> __device__ __forceinline__ R bsdf_pdf_impl(const
     V3<R> wo = world_to_local(b, wow), wi = world_to_local(b, wiw);
     if (wo.z == R(0)) return R(0);
     R pdf = R(0); int matching = 0;
-    for (int i = 0; i < b.n; i++) if (matches_flags(b.lobes[i].type, flags)) { matching++; pdf += lobe_pdf<R, KM>(b.lobes[i], wo, wi); }
+    for_lobes(b, [&](const Lobe<R>& l, int) { if (matches_flags(l.type, flags)) { matching++; pdf += lobe_pdf<R, KM>(l, wo, wi); } });
     return matching > 0 ? pdf : R(0);
 }
 template <class R, uint32_t KM> static __device__ __noinline__ R bsdf_pdf_call(const Bsdf<R>& b, V3<R> wow, V3<R> wiw, uint32_t flags) { return bsdf_pdf_impl<R, KM>(b, wow, wiw, flags); }
@@ -585,28 +606,28 @@ template <class R, uint32_t KM> __device__ __forceinline__ void bsdf_sample_f_im
     uint32_t matching = num_components(b, bxdf_type);
     if (matching == 0) return;
     uint32_t comp = min((uint32_t)floor(sample.x * (R)matching), matching - 1);
-    uint32_t count = comp; int used = 0;
-    for (int i = 0; i < b.n; i++) if (matches_flags(b.lobes[i].type, bxdf_type)) { if (count == 0) { used = i; break; } count--; }
-    const Lobe<R>& bx = b.lobes[used];
+    uint32_t count = comp; int used = -1;
+    for_lobes(b, [&](const Lobe<R>& l, int i) { if (used < 0 && matches_flags(l.type, bxdf_type)) { if (count == 0) used = i; else count--; } });
+    if (used < 0) used = 0;                        // cannot happen (comp < matching); the reference's `used` starts at 0
     V3<R> wo = normalize(world_to_local(b, wow));
     if (wo.z == R(0)) return;
-    V3<R> c, wi; R p;
-    lobe_sample_f<R, KM>(bx, wo, sample, g, c, wi, p);
+    V3<R> c, wi; R p; uint32_t bx_type = 0;
+    with_lobe(b, used, [&](const Lobe<R>& bx) { bx_type = bx.type; lobe_sample_f<R, KM>(bx, wo, sample, g, c, wi, p); });
     if (p == R(0)) return;
     V3<R> w = local_to_world(b, wi);
-    bool spec = (bx.type & BSDF_SPECULAR) != 0;
+    bool spec = (bx_type & BSDF_SPECULAR) != 0;
     if (!spec && matching > 1)
-        for (int i = 0; i < b.n; i++) if (i != used && matches_flags(b.lobes[i].type, bxdf_type)) p += lobe_pdf<R, KM>(b.lobes[i], wo, wi);
+        for_lobes(b, [&](const Lobe<R>& l, int i) { if (i != used && matches_flags(l.type, bxdf_type)) p += lobe_pdf<R, KM>(l, wo, wi); });
     if (matching > 1) p = p / (R)matching;
     if (!spec) {
         bool refl = dot(w, b.ng) * dot(wow, b.ng) > R(0);
         c = zero;
-        for (int i = 0; i < b.n; i++) {
-            uint32_t ty = b.lobes[i].type;
-            if (matches_flags(ty, bxdf_type) && ((refl && (ty & BSDF_REFLECTION) > 0) || (!refl && (ty & BSDF_TRANSMISSION) > 0))) c = c + lobe_f<R, KM>(b.lobes[i], wo, wi);
-        }
+        for_lobes(b, [&](const Lobe<R>& l, int) {
+            const uint32_t ty = l.type;
+            if (matches_flags(ty, bxdf_type) && ((refl && (ty & BSDF_REFLECTION) > 0) || (!refl && (ty & BSDF_TRANSMISSION) > 0))) c = c + lobe_f<R, KM>(l, wo, wi);
+        });
     }
-    color = c; wiw = w; pdf = p; sampled = bx.type;
+    color = c; wiw = w; pdf = p; sampled = bx_type;
 }
 template <class R, uint32_t KM> static __device__ __noinline__ void bsdf_sample_f_call(const Bsdf<R>& b, V3<R> wow, V2<R> sample, uint32_t bxdf_type, Rng& g, V3<R>& color, V3<R>& wiw, R& pdf, uint32_t& sampled) { bsdf_sample_f_impl<R, KM>(b, wow, sample, bxdf_type, g, color, wiw, pdf, sampled); }
 template <class R, uint32_t KM> __device__ __forceinline__ void bsdf_sample_f(const Bsdf<R>& b, V3<R> wow, V2<R> sample, uint32_t bxdf_type, Rng& g, V3<R>& color, V3<R>& wiw, R& pdf, uint32_t& sampled) { if constexpr (km_small(KM)) { bsdf_sample_f_impl<R, KM>(b, wow, sample, bxdf_type, g, color, wiw, pdf, sampled); } else { bsdf_sample_f_call<R, KM>(b, wow, sample, bxdf_type, g, color, wiw, pdf, sampled); } }
@@ -732,7 +753,7 @@ template <int MAT> __host__ __device__ constexpr uint32_t mat_km() {
 }
 template <class R, int MAT> __device__ __forceinline__ void compute_scattering_impl(const DScene& sc, const Rec& r, Bsdf<R>& b) {
     V3<R> e = cast3<R>(normalize(mk3(1., 1., 1.)));    // Bsdf::empty frame (bsdf.rs:37-47)
-    b.ns = e; b.ng = e; b.ss = e; b.ts = e; b.n = 0; b.empty = true;
+    b.ns = e; b.ng = e; b.ss = e; b.ts = e; b.n = 0; b.mask = 0u; b.empty = true;
     const rt_material& m = sc.materials[r.mat];
     double u = r.uv.x, v = r.uv.y;
     const uint32_t mt = MAT >= 0 ? (uint32_t)MAT : m.type;
@@ -742,7 +763,7 @@ template <class R, int MAT> __device__ __forceinline__ void compute_scattering_i
             D3 color = tex_value_at<sizeof(R) == 8>(sc, m.tex[0], u, v, r.p);
             if (!is_black(color)) {
                 bsdf_new(b, r);
-                Lobe<R>& l = b.lobes[b.n++];
+                Lobe<R>& l = add_lobe(b, 0);
                 if (sig == 0.) lobe_init(l, L_LAMBERT, BSDF_REFLECTION | BSDF_DIFFUSE, color);
                 else {
                     lobe_init(l, L_OREN_NAYAR, BSDF_REFLECTION | BSDF_DIFFUSE, color);     // bxdf.rs:909-921
@@ -755,13 +776,13 @@ template <class R, int MAT> __device__ __forceinline__ void compute_scattering_i
         if (mt == RT_MAT_LIGHT) return;
         if (mt == RT_MAT_PLASTIC) {
             D3 color = tex_value_at<sizeof(R) == 8>(sc, m.tex[0], u, v, r.p);
-            if (!is_black(color)) { bsdf_new(b, r); lobe_init(b.lobes[b.n++], L_LAMBERT, BSDF_REFLECTION | BSDF_DIFFUSE, color); }
+            if (!is_black(color)) { bsdf_new(b, r); lobe_init(add_lobe(b, 0), L_LAMBERT, BSDF_REFLECTION | BSDF_DIFFUSE, color); }
             D3 spec = tex_value_at<sizeof(R) == 8>(sc, m.tex[1], u, v, r.p);
             if (!is_black(spec)) {
                 if (b.empty) bsdf_new(b, r);
                 double rough = sc.mat_alpha[2 * r.mat];                                     // constant per material: remapped at commit
                 if (rough != rough) { rough = m.f[0]; if (m.remap_roughness) rough = tr_roughness_to_alpha(rough); }
-                Lobe<R>& l = b.lobes[b.n++];
+                Lobe<R>& l = add_lobe(b, 1);
                 lobe_init(l, L_MICRO_R, BSDF_REFLECTION | BSDF_GLOSSY, spec);
                 l.fresnel = F_DIELECTRIC; l.a = R(1.5); l.b = R(1);                        // eta_i, eta_t
                 l.mfd_empty = false; l.alpha_x = (R)fmax(rough, 1e-3); l.alpha_y = (R)fmax(rough, 1e-3);
@@ -775,7 +796,7 @@ template <class R, int MAT> __device__ __forceinline__ void compute_scattering_i
             if (is_black(rr) && is_black(t)) return;
             bool is_specular = urough == 0. && vrough == 0.;
             if (is_specular) {                                                             // allow_lobes = true
-                Lobe<R>& l = b.lobes[b.n++];
+                Lobe<R>& l = add_lobe(b, 0);
                 lobe_init(l, L_FRESNEL_SPEC, BSDF_TRANSMISSION | BSDF_REFLECTION | BSDF_SPECULAR, rr);
                 l.aux = cast3<R>(t); l.eta_a = (R)eta; l.eta_b = R(1);
                 return;
@@ -783,13 +804,13 @@ template <class R, int MAT> __device__ __forceinline__ void compute_scattering_i
             if (sc.mat_alpha[2 * r.mat] == sc.mat_alpha[2 * r.mat]) { urough = sc.mat_alpha[2 * r.mat]; vrough = sc.mat_alpha[2 * r.mat + 1]; }
             else if (m.remap_roughness) { urough = tr_roughness_to_alpha(urough); vrough = tr_roughness_to_alpha(vrough); }
             if (!is_black(rr)) {
-                Lobe<R>& l = b.lobes[b.n++];
+                Lobe<R>& l = add_lobe(b, 0);
                 lobe_init(l, L_MICRO_R, BSDF_REFLECTION | BSDF_GLOSSY, rr);
                 l.fresnel = F_DIELECTRIC; l.a = (R)eta; l.b = R(1);
                 l.mfd_empty = false; l.alpha_x = (R)fmax(urough, 1e-3); l.alpha_y = (R)fmax(vrough, 1e-3);
             }
             if (!is_black(t)) {
-                Lobe<R>& l = b.lobes[b.n++];
+                Lobe<R>& l = add_lobe(b, 1);
                 lobe_init(l, L_MICRO_T, BSDF_TRANSMISSION | BSDF_GLOSSY, t);
                 l.fresnel = F_DIELECTRIC; l.a = (R)eta; l.b = R(1); l.eta_a = (R)eta; l.eta_b = R(1);
                 l.mfd_empty = false; l.alpha_x = (R)fmax(urough, 1e-3); l.alpha_y = (R)fmax(vrough, 1e-3);
@@ -803,7 +824,7 @@ template <class R, int MAT> __device__ __forceinline__ void compute_scattering_i
             const double au = sc.mat_alpha[2 * r.mat], av = sc.mat_alpha[2 * r.mat + 1];
             double ur = au == au ? au : (m.remap_roughness ? tr_roughness_to_alpha(u_rough.x) : u_rough.x);
             double vr = av == av ? av : (m.remap_roughness ? tr_roughness_to_alpha(v_rough.x) : v_rough.x);
-            Lobe<R>& l = b.lobes[b.n++];
+            Lobe<R>& l = add_lobe(b, 0);
             lobe_init(l, L_MICRO_R, BSDF_REFLECTION | BSDF_GLOSSY, mk3(1., 1., 1.));
             l.fresnel = F_CONDUCTOR; l.eta3 = cast3<R>(tex_value_at<sizeof(R) == 8>(sc, m.tex[0], u, v, r.p)); l.aux = cast3<R>(tex_value_at<sizeof(R) == 8>(sc, m.tex[1], u, v, r.p));
             l.mfd_empty = false; l.alpha_x = (R)fmax(ur, 1e-3); l.alpha_y = (R)fmax(vr, 1e-3);
@@ -812,7 +833,7 @@ template <class R, int MAT> __device__ __forceinline__ void compute_scattering_i
         if (mt == RT_MAT_MIRROR) {
             bsdf_new(b, r);
             D3 color = tex_value_at<sizeof(R) == 8>(sc, m.tex[0], u, v, r.p);
-            if (!is_black(color)) lobe_init(b.lobes[b.n++], L_SPEC_R, BSDF_REFLECTION | BSDF_SPECULAR, color);
+            if (!is_black(color)) lobe_init(add_lobe(b, 0), L_SPEC_R, BSDF_REFLECTION | BSDF_SPECULAR, color);
             return;
         }
         if constexpr (sizeof(R) == 8) {
@@ -838,20 +859,20 @@ template <class R, int MAT> __device__ __forceinline__ void compute_scattering_i
             if (diffuse_weight > 0.) {
                 if (d.thin) {
                     const double flat = tex1(d.flatness);
-                    lobe_init(b.lobes[b.n++], L_DISNEY_DIFFUSE, BSDF_DIFFUSE | BSDF_REFLECTION, (diffuse_weight * (1. - flat) * (1. - dt)) * color);
-                    Lobe<R>& l = b.lobes[b.n++];
+                    lobe_init(add_lobe(b, 0), L_DISNEY_DIFFUSE, BSDF_DIFFUSE | BSDF_REFLECTION, (diffuse_weight * (1. - flat) * (1. - dt)) * color);
+                    Lobe<R>& l = add_lobe(b, 0);
                     lobe_init(l, L_DISNEY_FAKESS, BSDF_DIFFUSE | BSDF_REFLECTION, (diffuse_weight * flat * (1. - dt)) * color); l.a = rough;
                 } else {
                     const D3 sd = tex_value_at<true>(sc, d.scatter_distance, u, v, r.p);
-                    if (is_black(sd)) lobe_init(b.lobes[b.n++], L_DISNEY_DIFFUSE, BSDF_DIFFUSE | BSDF_REFLECTION, diffuse_weight * color);
+                    if (is_black(sd)) lobe_init(add_lobe(b, 0), L_DISNEY_DIFFUSE, BSDF_DIFFUSE | BSDF_REFLECTION, diffuse_weight * color);
                     else {                               // "use bssrdf instead; right now, that doesn't exist, so just specular transmission" (material.rs:300-307)
-                        Lobe<R>& l = b.lobes[b.n++];
+                        Lobe<R>& l = add_lobe(b, 0);
                         lobe_init(l, L_SPEC_T, BSDF_TRANSMISSION | BSDF_SPECULAR, white);
                         l.fresnel = F_DIELECTRIC; l.a = 1.; l.b = e; l.eta_a = 1.; l.eta_b = e;
                     }
                 }
-                { Lobe<R>& l = b.lobes[b.n++]; lobe_init(l, L_DISNEY_RETRO, BSDF_DIFFUSE | BSDF_REFLECTION, diffuse_weight * color); l.a = rough; }
-                if (sheen_weight > 0.) lobe_init(b.lobes[b.n++], L_DISNEY_SHEEN, BSDF_DIFFUSE | BSDF_REFLECTION, (diffuse_weight * sheen_weight) * c_sheen);
+                { Lobe<R>& l = add_lobe(b, 0); lobe_init(l, L_DISNEY_RETRO, BSDF_DIFFUSE | BSDF_REFLECTION, diffuse_weight * color); l.a = rough; }
+                if (sheen_weight > 0.) lobe_init(add_lobe(b, 0), L_DISNEY_SHEEN, BSDF_DIFFUSE | BSDF_REFLECTION, (diffuse_weight * sheen_weight) * c_sheen);
             }
             const double ani = tex1(d.anisotropic);
             const double aspect = sqrt(1. - ani * 0.9);
@@ -860,16 +881,16 @@ template <class R, int MAT> __device__ __forceinline__ void compute_scattering_i
             const double r0e = (e - 1.) * (e - 1.) / ((e + 1.) * (e + 1.));                  // eta_to_r0
             const D3 c_spec_0 = lerp_v(metallic_weight, r0e * lerp_v(spec_tint, white, c_tint), color);
             {   // MicrofacetReflection(white, DisneyFresnel{r0, metallic, eta}, DisneyMicrofacet(ax, ay)); make_disney clamps alpha at 1e-3
-                Lobe<R>& l = b.lobes[b.n++];
+                Lobe<R>& l = add_lobe(b, 0);
                 lobe_init(l, L_MICRO_R, BSDF_REFLECTION | BSDF_GLOSSY, white);
                 l.fresnel = F_DISNEY; l.eta3 = cast3<R>(c_spec_0); l.a = metallic_weight; l.b = e;
                 l.mfd_empty = false; l.mfd_disney = true; l.alpha_x = fmax(ax, 1e-3); l.alpha_y = fmax(ay, 1e-3);
             }
             const double cc = tex1(d.clearcoat);
-            if (cc > 0.) { Lobe<R>& l = b.lobes[b.n++]; lobe_init(l, L_DISNEY_CLEARCOAT, BSDF_GLOSSY | BSDF_REFLECTION, mk3(0., 0., 0.)); l.a = cc; l.b = lerp_d(tex1(d.clearcoat_gloss), 0.1, 0.001); }
+            if (cc > 0.) { Lobe<R>& l = add_lobe(b, 0); lobe_init(l, L_DISNEY_CLEARCOAT, BSDF_GLOSSY | BSDF_REFLECTION, mk3(0., 0., 0.)); l.a = cc; l.b = lerp_d(tex1(d.clearcoat_gloss), 0.1, 0.001); }
             if (strans > 0.) {
                 const D3 t = mk3(strans * sqrt(color.x), strans * sqrt(color.y), strans * sqrt(color.z));
-                Lobe<R>& l = b.lobes[b.n++];
+                Lobe<R>& l = add_lobe(b, 0);
                 lobe_init(l, L_MICRO_T, BSDF_TRANSMISSION | BSDF_GLOSSY, t);
                 l.fresnel = F_DIELECTRIC; l.a = 1.; l.b = e; l.eta_a = 1.; l.eta_b = e; l.mfd_empty = false;
                 if (d.thin) {                            // "approximate with scaled distribution" (Burley 2015): a plain TrowbridgeReitz
@@ -877,7 +898,7 @@ template <class R, int MAT> __device__ __forceinline__ void compute_scattering_i
                     l.alpha_x = fmax(fmax(0.001, rscaled * rscaled / aspect), 1e-3); l.alpha_y = fmax(fmax(0.001, rscaled * rscaled * aspect), 1e-3);
                 } else { l.mfd_disney = true; l.alpha_x = fmax(ax, 1e-3); l.alpha_y = fmax(ay, 1e-3); }
             }
-            if (d.thin) lobe_init(b.lobes[b.n++], L_LAMBERT_T, BSDF_TRANSMISSION | BSDF_DIFFUSE, dt * color);
+            if (d.thin) lobe_init(add_lobe(b, 0), L_LAMBERT_T, BSDF_TRANSMISSION | BSDF_DIFFUSE, dt * color);
             return;
         }
         }

@@ -566,12 +566,20 @@ constexpr int TRACE_BLOCK = 128;            // block size of every persistent tr
                             // 34.1 / 32.2 / 31.6 / 31.6 / 32.2 / 33.5 ms, connect 21.1 / 20.3 / 20.1 / 20.2 / 21.1 / 22.4 ms)
 #endif
 
+// Job::shared_leaf_ray: the per-ray f64 constants that only the exact leaf test reads (1/d per axis and the two shear factors of the watertight test: 10
+// registers) wait in shared memory between leaves (5 KB per block) instead of occupying registers through the node loop.  For k_connect only: under
+// its 96-register cap ptxas had chosen to spill the f32 culling ray instead — 8 local loads in EVERY node step, 47 % of that kernel's local-memory
+// sectors (profiles/connect_mem_by_source_r02.txt); connect -1 % (dragon) ... -3.5 % (Cornell + statue).  k_extend does not spill and pays +0.7 % for the
+// round trip, so it keeps everything in registers; parking origin and direction as well (22 registers) was slower for both (pass V).
 template <class Job>
 __device__ __forceinline__ void trace_jobs(const DScene& sc, Job& job, uint32_t n, uint32_t* counter) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     int32_t stack[STACK];
     TState st; st.cur = SENTINEL; st.sp = 0;
+    constexpr bool PARK = Job::shared_leaf_ray;
+    __shared__ double sh_leaf[PARK ? 5 : 1][PARK ? TRACE_BLOCK : 1];
+    const int tid = threadIdx.x;
     bool active = false, exhausted = false;
     uint32_t idx = 0;
     if (sc.n_nodes == 0 && sc.n_direct == 0) {      // empty scene: every ray misses
@@ -590,6 +598,9 @@ __device__ __forceinline__ void trace_jobs(const DScene& sc, Job& job, uint32_t 
             if (!active) {
                 idx = base + __popc(idle & ((1u << lane) - 1u));
                 if (idx < n) active = job.load(idx, st, stack);
+                if constexpr (PARK) {
+                    if (active) { sh_leaf[0][tid] = st.rl.rx.inv.x; sh_leaf[1][tid] = st.rl.rx.inv.y; sh_leaf[2][tid] = st.rl.rx.inv.z; sh_leaf[3][tid] = st.rl.rx.sx; sh_leaf[4][tid] = st.rl.rx.sy; }
+                }
             }
             if (base + __popc(idle) >= n) exhausted = true;
         }
@@ -605,7 +616,12 @@ __device__ __forceinline__ void trace_jobs(const DScene& sc, Job& job, uint32_t 
                 if (at_node) node_step(sc, st, stack);
             }
             // leaf phase
-            if (active && st.cur < 0) leaf_step(sc, st, stack, job.tmin(st), job.tmax(st), [&](D3& fo, D3& fd) { job.ray(idx, fo, fd); });
+            if (active && st.cur < 0) {
+                if constexpr (PARK) {      // live for this leaf only
+                    st.rl.rx.inv = mk3(sh_leaf[0][tid], sh_leaf[1][tid], sh_leaf[2][tid]); st.rl.rx.sx = sh_leaf[3][tid]; st.rl.rx.sy = sh_leaf[4][tid];
+                }
+                leaf_step(sc, st, stack, job.tmin(st), job.tmax(st), [&](D3& fo, D3& fd) { job.ray(idx, fo, fd); });
+            }
             if (active && st.cur == SENTINEL) { job.finish(idx, st); active = false; }
             unsigned act = __ballot_sync(FULL, active);
             if (act == 0u) break;

@@ -1,6 +1,6 @@
 """Memory traffic of one kernel launch in an .ncu-rep by source line: which loads / stores are the uncoalesced ones.
 
-    python tools/ncu_mem_by_source.py report.ncu-rep launch_index object.o [top_n]
+    python tools/ncu_mem_by_source.py report.ncu-rep launch_index|name_substring object.o [top_n]
 
 For every memory column of ncu's source page (requests, sectors, wavefronts: global / local / shared) the totals and the top source lines, with
 sectors per request (32 = every lane its own sector, 16 = a fully coalesced 16-byte load, 1-2 = a broadcast).
@@ -18,7 +18,7 @@ import subprocess
 import sys
 import tempfile
 
-rep, which, obj = sys.argv[1], int(sys.argv[2]), sys.argv[3]
+rep, which, obj = sys.argv[1], sys.argv[2], sys.argv[3]          # `which`: launch index, or a substring of the kernel name (first match)
 topn = int(sys.argv[4]) if len(sys.argv) > 4 else 30
 raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "sass"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
@@ -27,7 +27,7 @@ for r in rows:
     if r and r[0] == "Kernel Name": cur = {"name": r[1], "hdr": None, "data": []}; sections.append(cur)
     elif cur is not None and cur["hdr"] is None: cur["hdr"] = r
     elif cur is not None and len(r) == len(cur["hdr"]): cur["data"].append(r)
-s = sections[which]; hdr, data = s["hdr"], s["data"]
+s = sections[int(which)] if which.isdigit() else [x for x in sections if which in x["name"]][0]; hdr, data = s["hdr"], s["data"]
 iS, iI, iT = hdr.index("# Samples"), hdr.index("Instructions Executed"), hdr.index("Thread Instructions Executed")
 name = s["name"]
 print(name[:120])
@@ -89,3 +89,8 @@ for rq, sc in pairs:
     for key, v in per[b].most_common(topn):
         r = per[a].get(key, 0)
         print(f"  {key[0]}:{key[1]:<5d} {100 * v / tot[b]:5.2f}%   {v / r if r else 0:5.1f} sectors/request   {r:12.0f} requests   {100 * inst_line[key] / tot_i:5.2f}% inst")
+lc = col("L2 Theoretical Sectors Local")
+if lc is not None and tot[lc]:
+    print(f"\ntop lines by {hdr[lc]} (share of the launch; sectors per warp instruction executed on the line):")
+    for key, v in per[lc].most_common(topn):
+        print(f"  {key[0]}:{key[1]:<5d} {100 * v / tot[lc]:5.2f}%   {v:12.0f} sectors   {100 * inst_line[key] / tot_i:5.2f}% inst")
