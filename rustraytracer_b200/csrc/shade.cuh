@@ -258,18 +258,23 @@ template <class R> struct Bsdf { V3<R> ns, ng, ss, ts; int n; uint32_t mask; boo
 // `mask` says which are present, so walking the present slots in slot order visits exactly the lobes, in exactly the order, that the reference's
 // `bxdfs` vector holds (a lobe that is left out there is a cleared bit here).  With static indices and no address handed to an out-of-line function
 // the whole Bsdf lives in registers and the constant fields (kind, type, fresnel) fold away; as an array in local memory it was the largest part of the
-// shade kernels' local-memory sectors, which outnumbered their global ones (profiles/shade_*_mem_by_source_r02.txt).  The f64 BSDF (up to 8 lobes,
-// Material::Disney) keeps the dense `n`-long array.
-template <class R> __device__ __forceinline__ Lobe<R>& add_lobe(Bsdf<R>& b, int slot) {
-    if constexpr (sizeof(R) == 4) { b.mask |= 1u << slot; b.n++; return b.lobes[slot]; }
+// shade kernels' local-memory sectors, which outnumbered their global ones (profiles/shade_*_mem_by_source_r02.txt).  Only a Material::Disney BSDF (up to
+// 8 lobes, f64 kernels) keeps the dense `n`-long array.
+// Static slots apply whenever the kernel's compile-time lobe mask KM rules out Material::Disney (the only material with more than two lobes): every f32
+// kernel, and the f64 kernels of Matte .. Mirror.
+template <uint32_t KM, class R> __host__ __device__ constexpr bool lobes_static() {
+    return sizeof(R) == 4 || (KM & (km(L_DISNEY_DIFFUSE) | km(L_DISNEY_FAKESS) | km(L_DISNEY_RETRO) | km(L_DISNEY_SHEEN) | km(L_DISNEY_CLEARCOAT) | km(L_LAMBERT_T) | kmf(F_DISNEY))) == 0u;
+}
+template <uint32_t KM, class R> __device__ __forceinline__ Lobe<R>& add_lobe(Bsdf<R>& b, int slot) {
+    if constexpr (lobes_static<KM, R>()) { b.mask |= 1u << slot; b.n++; return b.lobes[slot]; }
     else { b.mask |= 1u << b.n; return b.lobes[b.n++]; }       // dense append; `slot` is ignored
 }
-template <class R, class F> __device__ __forceinline__ void for_lobes(const Bsdf<R>& b, F&& fn) {          // fn(lobe, slot), present lobes in order
-    if constexpr (sizeof(R) == 4) { if (b.mask & 1u) fn(b.lobes[0], 0); if (b.mask & 2u) fn(b.lobes[1], 1); }
+template <uint32_t KM, class R, class F> __device__ __forceinline__ void for_lobes(const Bsdf<R>& b, F&& fn) {          // fn(lobe, slot), present lobes in order
+    if constexpr (lobes_static<KM, R>()) { if (b.mask & 1u) fn(b.lobes[0], 0); if (b.mask & 2u) fn(b.lobes[1], 1); }
     else { for (int i = 0; i < b.n; i++) fn(b.lobes[i], i); }
 }
-template <class R, class F> __device__ __forceinline__ void with_lobe(const Bsdf<R>& b, int slot, F&& fn) {   // fn(lobe) for one slot chosen at run time
-    if constexpr (sizeof(R) == 4) { if (slot == 0) fn(b.lobes[0]); else fn(b.lobes[1]); }
+template <uint32_t KM, class R, class F> __device__ __forceinline__ void with_lobe(const Bsdf<R>& b, int slot, F&& fn) {   // fn(lobe) for one slot chosen at run time
+    if constexpr (lobes_static<KM, R>()) { if (slot == 0) fn(b.lobes[0]); else fn(b.lobes[1]); }
     else fn(b.lobes[slot]);
 }
 
@@ -574,13 +579,13 @@ template <> __device__ __forceinline__ V3<float> local_to_world<float>(const Bsd
     return v3<float>(__fmaf_rn(b.ns.x, v.z, __fmaf_rn(b.ts.x, v.y, b.ss.x * v.x)), __fmaf_rn(b.ns.y, v.z, __fmaf_rn(b.ts.y, v.y, b.ss.y * v.x)),
                      __fmaf_rn(b.ns.z, v.z, __fmaf_rn(b.ts.z, v.y, b.ss.z * v.x)));
 }
-template <class R> __device__ __forceinline__ uint32_t num_components(const Bsdf<R>& b, uint32_t t) { uint32_t c = 0; for_lobes(b, [&](const Lobe<R>& l, int) { if (matches_flags(l.type, t)) c++; }); return c; }
+template <uint32_t KM, class R> __device__ __forceinline__ uint32_t num_components(const Bsdf<R>& b, uint32_t t) { uint32_t c = 0; for_lobes<KM>(b, [&](const Lobe<R>& l, int) { if (matches_flags(l.type, t)) c++; }); return c; }
 // Bsdf::f (bsdf.rs:83-98), `a && b || c` precedence kept (§8.1 #6)
 template <class R, uint32_t KM> __device__ __forceinline__ V3<R> bsdf_f_impl(const Bsdf<R>& b, V3<R> wow, V3<R> wiw, uint32_t flags) {
     V3<R> wi = world_to_local(b, wiw), wo = world_to_local(b, wow);
     bool refl = dot(wiw, b.ng) * dot(wow, b.ng) > R(0);
     V3<R> f = v3<R>(R(0), R(0), R(0));
-    for_lobes(b, [&](const Lobe<R>& l, int) {
+    for_lobes<KM>(b, [&](const Lobe<R>& l, int) {
         const uint32_t ty = l.type;
         if ((matches_flags(ty, flags) && (refl && (ty & BSDF_REFLECTION) > 0)) || (!refl && (ty & BSDF_TRANSMISSION) > 0)) f = f + lobe_f<R, KM>(l, wo, wi);
     });
@@ -594,7 +599,7 @@ template <class R, uint32_t KM> __device__ __forceinline__ R bsdf_pdf_impl(const
     V3<R> wo = world_to_local(b, wow), wi = world_to_local(b, wiw);
     if (wo.z == R(0)) return R(0);
     R pdf = R(0); int matching = 0;
-    for_lobes(b, [&](const Lobe<R>& l, int) { if (matches_flags(l.type, flags)) { matching++; pdf += lobe_pdf<R, KM>(l, wo, wi); } });
+    for_lobes<KM>(b, [&](const Lobe<R>& l, int) { if (matches_flags(l.type, flags)) { matching++; pdf += lobe_pdf<R, KM>(l, wo, wi); } });
     return matching > 0 ? pdf : R(0);
 }
 template <class R, uint32_t KM> static __device__ __noinline__ R bsdf_pdf_call(const Bsdf<R>& b, V3<R> wow, V3<R> wiw, uint32_t flags) { return bsdf_pdf_impl<R, KM>(b, wow, wiw, flags); }
@@ -603,26 +608,26 @@ template <class R, uint32_t KM> __device__ __forceinline__ R bsdf_pdf(const Bsdf
 template <class R, uint32_t KM> __device__ __forceinline__ void bsdf_sample_f_impl(const Bsdf<R>& b, V3<R> wow, V2<R> sample, uint32_t bxdf_type, Rng& g, V3<R>& color, V3<R>& wiw, R& pdf, uint32_t& sampled) {
     const V3<R> zero = v3<R>(R(0), R(0), R(0));
     color = zero; wiw = zero; pdf = R(0); sampled = 0;
-    uint32_t matching = num_components(b, bxdf_type);
+    uint32_t matching = num_components<KM>(b, bxdf_type);
     if (matching == 0) return;
     uint32_t comp = min((uint32_t)floor(sample.x * (R)matching), matching - 1);
     uint32_t count = comp; int used = -1;
-    for_lobes(b, [&](const Lobe<R>& l, int i) { if (used < 0 && matches_flags(l.type, bxdf_type)) { if (count == 0) used = i; else count--; } });
+    for_lobes<KM>(b, [&](const Lobe<R>& l, int i) { if (used < 0 && matches_flags(l.type, bxdf_type)) { if (count == 0) used = i; else count--; } });
     if (used < 0) used = 0;                        // cannot happen (comp < matching); the reference's `used` starts at 0
     V3<R> wo = normalize(world_to_local(b, wow));
     if (wo.z == R(0)) return;
     V3<R> c, wi; R p; uint32_t bx_type = 0;
-    with_lobe(b, used, [&](const Lobe<R>& bx) { bx_type = bx.type; lobe_sample_f<R, KM>(bx, wo, sample, g, c, wi, p); });
+    with_lobe<KM>(b, used, [&](const Lobe<R>& bx) { bx_type = bx.type; lobe_sample_f<R, KM>(bx, wo, sample, g, c, wi, p); });
     if (p == R(0)) return;
     V3<R> w = local_to_world(b, wi);
     bool spec = (bx_type & BSDF_SPECULAR) != 0;
     if (!spec && matching > 1)
-        for_lobes(b, [&](const Lobe<R>& l, int i) { if (i != used && matches_flags(l.type, bxdf_type)) p += lobe_pdf<R, KM>(l, wo, wi); });
+        for_lobes<KM>(b, [&](const Lobe<R>& l, int i) { if (i != used && matches_flags(l.type, bxdf_type)) p += lobe_pdf<R, KM>(l, wo, wi); });
     if (matching > 1) p = p / (R)matching;
     if (!spec) {
         bool refl = dot(w, b.ng) * dot(wow, b.ng) > R(0);
         c = zero;
-        for_lobes(b, [&](const Lobe<R>& l, int) {
+        for_lobes<KM>(b, [&](const Lobe<R>& l, int) {
             const uint32_t ty = l.type;
             if (matches_flags(ty, bxdf_type) && ((refl && (ty & BSDF_REFLECTION) > 0) || (!refl && (ty & BSDF_TRANSMISSION) > 0))) c = c + lobe_f<R, KM>(l, wo, wi);
         });
@@ -763,7 +768,7 @@ template <class R, int MAT> __device__ __forceinline__ void compute_scattering_i
             D3 color = tex_value_at<sizeof(R) == 8>(sc, m.tex[0], u, v, r.p);
             if (!is_black(color)) {
                 bsdf_new(b, r);
-                Lobe<R>& l = add_lobe(b, 0);
+                Lobe<R>& l = add_lobe<mat_km<MAT>()>(b, 0);
                 if (sig == 0.) lobe_init(l, L_LAMBERT, BSDF_REFLECTION | BSDF_DIFFUSE, color);
                 else {
                     lobe_init(l, L_OREN_NAYAR, BSDF_REFLECTION | BSDF_DIFFUSE, color);     // bxdf.rs:909-921
@@ -776,13 +781,13 @@ template <class R, int MAT> __device__ __forceinline__ void compute_scattering_i
         if (mt == RT_MAT_LIGHT) return;
         if (mt == RT_MAT_PLASTIC) {
             D3 color = tex_value_at<sizeof(R) == 8>(sc, m.tex[0], u, v, r.p);
-            if (!is_black(color)) { bsdf_new(b, r); lobe_init(add_lobe(b, 0), L_LAMBERT, BSDF_REFLECTION | BSDF_DIFFUSE, color); }
+            if (!is_black(color)) { bsdf_new(b, r); lobe_init(add_lobe<mat_km<MAT>()>(b, 0), L_LAMBERT, BSDF_REFLECTION | BSDF_DIFFUSE, color); }
             D3 spec = tex_value_at<sizeof(R) == 8>(sc, m.tex[1], u, v, r.p);
             if (!is_black(spec)) {
                 if (b.empty) bsdf_new(b, r);
                 double rough = sc.mat_alpha[2 * r.mat];                                     // constant per material: remapped at commit
                 if (rough != rough) { rough = m.f[0]; if (m.remap_roughness) rough = tr_roughness_to_alpha(rough); }
-                Lobe<R>& l = add_lobe(b, 1);
+                Lobe<R>& l = add_lobe<mat_km<MAT>()>(b, 1);
                 lobe_init(l, L_MICRO_R, BSDF_REFLECTION | BSDF_GLOSSY, spec);
                 l.fresnel = F_DIELECTRIC; l.a = R(1.5); l.b = R(1);                        // eta_i, eta_t
                 l.mfd_empty = false; l.alpha_x = (R)fmax(rough, 1e-3); l.alpha_y = (R)fmax(rough, 1e-3);
@@ -796,7 +801,7 @@ template <class R, int MAT> __device__ __forceinline__ void compute_scattering_i
             if (is_black(rr) && is_black(t)) return;
             bool is_specular = urough == 0. && vrough == 0.;
             if (is_specular) {                                                             // allow_lobes = true
-                Lobe<R>& l = add_lobe(b, 0);
+                Lobe<R>& l = add_lobe<mat_km<MAT>()>(b, 0);
                 lobe_init(l, L_FRESNEL_SPEC, BSDF_TRANSMISSION | BSDF_REFLECTION | BSDF_SPECULAR, rr);
                 l.aux = cast3<R>(t); l.eta_a = (R)eta; l.eta_b = R(1);
                 return;
@@ -804,13 +809,13 @@ template <class R, int MAT> __device__ __forceinline__ void compute_scattering_i
             if (sc.mat_alpha[2 * r.mat] == sc.mat_alpha[2 * r.mat]) { urough = sc.mat_alpha[2 * r.mat]; vrough = sc.mat_alpha[2 * r.mat + 1]; }
             else if (m.remap_roughness) { urough = tr_roughness_to_alpha(urough); vrough = tr_roughness_to_alpha(vrough); }
             if (!is_black(rr)) {
-                Lobe<R>& l = add_lobe(b, 0);
+                Lobe<R>& l = add_lobe<mat_km<MAT>()>(b, 0);
                 lobe_init(l, L_MICRO_R, BSDF_REFLECTION | BSDF_GLOSSY, rr);
                 l.fresnel = F_DIELECTRIC; l.a = (R)eta; l.b = R(1);
                 l.mfd_empty = false; l.alpha_x = (R)fmax(urough, 1e-3); l.alpha_y = (R)fmax(vrough, 1e-3);
             }
             if (!is_black(t)) {
-                Lobe<R>& l = add_lobe(b, 1);
+                Lobe<R>& l = add_lobe<mat_km<MAT>()>(b, 1);
                 lobe_init(l, L_MICRO_T, BSDF_TRANSMISSION | BSDF_GLOSSY, t);
                 l.fresnel = F_DIELECTRIC; l.a = (R)eta; l.b = R(1); l.eta_a = (R)eta; l.eta_b = R(1);
                 l.mfd_empty = false; l.alpha_x = (R)fmax(urough, 1e-3); l.alpha_y = (R)fmax(vrough, 1e-3);
@@ -824,7 +829,7 @@ template <class R, int MAT> __device__ __forceinline__ void compute_scattering_i
             const double au = sc.mat_alpha[2 * r.mat], av = sc.mat_alpha[2 * r.mat + 1];
             double ur = au == au ? au : (m.remap_roughness ? tr_roughness_to_alpha(u_rough.x) : u_rough.x);
             double vr = av == av ? av : (m.remap_roughness ? tr_roughness_to_alpha(v_rough.x) : v_rough.x);
-            Lobe<R>& l = add_lobe(b, 0);
+            Lobe<R>& l = add_lobe<mat_km<MAT>()>(b, 0);
             lobe_init(l, L_MICRO_R, BSDF_REFLECTION | BSDF_GLOSSY, mk3(1., 1., 1.));
             l.fresnel = F_CONDUCTOR; l.eta3 = cast3<R>(tex_value_at<sizeof(R) == 8>(sc, m.tex[0], u, v, r.p)); l.aux = cast3<R>(tex_value_at<sizeof(R) == 8>(sc, m.tex[1], u, v, r.p));
             l.mfd_empty = false; l.alpha_x = (R)fmax(ur, 1e-3); l.alpha_y = (R)fmax(vr, 1e-3);
@@ -833,7 +838,7 @@ template <class R, int MAT> __device__ __forceinline__ void compute_scattering_i
         if (mt == RT_MAT_MIRROR) {
             bsdf_new(b, r);
             D3 color = tex_value_at<sizeof(R) == 8>(sc, m.tex[0], u, v, r.p);
-            if (!is_black(color)) lobe_init(add_lobe(b, 0), L_SPEC_R, BSDF_REFLECTION | BSDF_SPECULAR, color);
+            if (!is_black(color)) lobe_init(add_lobe<mat_km<MAT>()>(b, 0), L_SPEC_R, BSDF_REFLECTION | BSDF_SPECULAR, color);
             return;
         }
         if constexpr (sizeof(R) == 8) {
@@ -859,20 +864,20 @@ template <class R, int MAT> __device__ __forceinline__ void compute_scattering_i
             if (diffuse_weight > 0.) {
                 if (d.thin) {
                     const double flat = tex1(d.flatness);
-                    lobe_init(add_lobe(b, 0), L_DISNEY_DIFFUSE, BSDF_DIFFUSE | BSDF_REFLECTION, (diffuse_weight * (1. - flat) * (1. - dt)) * color);
-                    Lobe<R>& l = add_lobe(b, 0);
+                    lobe_init(add_lobe<mat_km<MAT>()>(b, 0), L_DISNEY_DIFFUSE, BSDF_DIFFUSE | BSDF_REFLECTION, (diffuse_weight * (1. - flat) * (1. - dt)) * color);
+                    Lobe<R>& l = add_lobe<mat_km<MAT>()>(b, 0);
                     lobe_init(l, L_DISNEY_FAKESS, BSDF_DIFFUSE | BSDF_REFLECTION, (diffuse_weight * flat * (1. - dt)) * color); l.a = rough;
                 } else {
                     const D3 sd = tex_value_at<true>(sc, d.scatter_distance, u, v, r.p);
-                    if (is_black(sd)) lobe_init(add_lobe(b, 0), L_DISNEY_DIFFUSE, BSDF_DIFFUSE | BSDF_REFLECTION, diffuse_weight * color);
+                    if (is_black(sd)) lobe_init(add_lobe<mat_km<MAT>()>(b, 0), L_DISNEY_DIFFUSE, BSDF_DIFFUSE | BSDF_REFLECTION, diffuse_weight * color);
                     else {                               // "use bssrdf instead; right now, that doesn't exist, so just specular transmission" (material.rs:300-307)
-                        Lobe<R>& l = add_lobe(b, 0);
+                        Lobe<R>& l = add_lobe<mat_km<MAT>()>(b, 0);
                         lobe_init(l, L_SPEC_T, BSDF_TRANSMISSION | BSDF_SPECULAR, white);
                         l.fresnel = F_DIELECTRIC; l.a = 1.; l.b = e; l.eta_a = 1.; l.eta_b = e;
                     }
                 }
-                { Lobe<R>& l = add_lobe(b, 0); lobe_init(l, L_DISNEY_RETRO, BSDF_DIFFUSE | BSDF_REFLECTION, diffuse_weight * color); l.a = rough; }
-                if (sheen_weight > 0.) lobe_init(add_lobe(b, 0), L_DISNEY_SHEEN, BSDF_DIFFUSE | BSDF_REFLECTION, (diffuse_weight * sheen_weight) * c_sheen);
+                { Lobe<R>& l = add_lobe<mat_km<MAT>()>(b, 0); lobe_init(l, L_DISNEY_RETRO, BSDF_DIFFUSE | BSDF_REFLECTION, diffuse_weight * color); l.a = rough; }
+                if (sheen_weight > 0.) lobe_init(add_lobe<mat_km<MAT>()>(b, 0), L_DISNEY_SHEEN, BSDF_DIFFUSE | BSDF_REFLECTION, (diffuse_weight * sheen_weight) * c_sheen);
             }
             const double ani = tex1(d.anisotropic);
             const double aspect = sqrt(1. - ani * 0.9);
@@ -881,16 +886,16 @@ template <class R, int MAT> __device__ __forceinline__ void compute_scattering_i
             const double r0e = (e - 1.) * (e - 1.) / ((e + 1.) * (e + 1.));                  // eta_to_r0
             const D3 c_spec_0 = lerp_v(metallic_weight, r0e * lerp_v(spec_tint, white, c_tint), color);
             {   // MicrofacetReflection(white, DisneyFresnel{r0, metallic, eta}, DisneyMicrofacet(ax, ay)); make_disney clamps alpha at 1e-3
-                Lobe<R>& l = add_lobe(b, 0);
+                Lobe<R>& l = add_lobe<mat_km<MAT>()>(b, 0);
                 lobe_init(l, L_MICRO_R, BSDF_REFLECTION | BSDF_GLOSSY, white);
                 l.fresnel = F_DISNEY; l.eta3 = cast3<R>(c_spec_0); l.a = metallic_weight; l.b = e;
                 l.mfd_empty = false; l.mfd_disney = true; l.alpha_x = fmax(ax, 1e-3); l.alpha_y = fmax(ay, 1e-3);
             }
             const double cc = tex1(d.clearcoat);
-            if (cc > 0.) { Lobe<R>& l = add_lobe(b, 0); lobe_init(l, L_DISNEY_CLEARCOAT, BSDF_GLOSSY | BSDF_REFLECTION, mk3(0., 0., 0.)); l.a = cc; l.b = lerp_d(tex1(d.clearcoat_gloss), 0.1, 0.001); }
+            if (cc > 0.) { Lobe<R>& l = add_lobe<mat_km<MAT>()>(b, 0); lobe_init(l, L_DISNEY_CLEARCOAT, BSDF_GLOSSY | BSDF_REFLECTION, mk3(0., 0., 0.)); l.a = cc; l.b = lerp_d(tex1(d.clearcoat_gloss), 0.1, 0.001); }
             if (strans > 0.) {
                 const D3 t = mk3(strans * sqrt(color.x), strans * sqrt(color.y), strans * sqrt(color.z));
-                Lobe<R>& l = add_lobe(b, 0);
+                Lobe<R>& l = add_lobe<mat_km<MAT>()>(b, 0);
                 lobe_init(l, L_MICRO_T, BSDF_TRANSMISSION | BSDF_GLOSSY, t);
                 l.fresnel = F_DIELECTRIC; l.a = 1.; l.b = e; l.eta_a = 1.; l.eta_b = e; l.mfd_empty = false;
                 if (d.thin) {                            // "approximate with scaled distribution" (Burley 2015): a plain TrowbridgeReitz
@@ -898,7 +903,7 @@ template <class R, int MAT> __device__ __forceinline__ void compute_scattering_i
                     l.alpha_x = fmax(fmax(0.001, rscaled * rscaled / aspect), 1e-3); l.alpha_y = fmax(fmax(0.001, rscaled * rscaled * aspect), 1e-3);
                 } else { l.mfd_disney = true; l.alpha_x = fmax(ax, 1e-3); l.alpha_y = fmax(ay, 1e-3); }
             }
-            if (d.thin) lobe_init(add_lobe(b, 0), L_LAMBERT_T, BSDF_TRANSMISSION | BSDF_DIFFUSE, dt * color);
+            if (d.thin) lobe_init(add_lobe<mat_km<MAT>()>(b, 0), L_LAMBERT_T, BSDF_TRANSMISSION | BSDF_DIFFUSE, dt * color);
             return;
         }
         }
