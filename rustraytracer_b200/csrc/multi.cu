@@ -32,7 +32,7 @@ namespace rt {
 // profiles/reduce_resolve_r02.json).  The sum runs in the order given, so its bits do not depend on how a ring or a tree associates the additions.
 constexpr int REDUCE_MAX_FILMS = 16;
 struct FilmPtrs { const double2* p[REDUCE_MAX_FILMS]; };
-__global__ void __launch_bounds__(256) k_reduce_resolve(FilmPtrs f, int n_films, uint64_t begin, uint64_t end, uint8_t* __restrict__ rgb) {
+__global__ void __launch_bounds__(256) k_reduce_resolve(const __grid_constant__ FilmPtrs f, int n_films, uint64_t begin, uint64_t end, uint8_t* __restrict__ rgb) {
     for (uint64_t i = begin + blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < end; i += (uint64_t)gridDim.x * blockDim.x) {
         double2 rg = __ldcs(f.p[0] + 2 * i), bn = __ldcs(f.p[0] + 2 * i + 1);                  // streamed: every byte is used once
         for (int k = 1; k < n_films; k++) {
