@@ -69,7 +69,8 @@ constexpr int N_BINS = 16;
 static_assert(RT_SORT_BITS >= 4 && RT_SORT_BITS <= 7, "RT_SORT_BITS out of range");
 constexpr uint32_t SORT_CELLS = 1u << (3 * RT_SORT_BITS);
 #ifndef SHADE_MIN_BLOCKS
-#define SHADE_MIN_BLOCKS 4      // <= 128 registers: 16 warps/SM; measured against 3 and 5 in profiles/shade_r01_notes.md
+#define SHADE_MIN_BLOCKS 4      // <= 128 registers: 16 warps/SM; measured against 3 and 5 in profiles/shade_r01_notes.md, and again after the register-BSDF change (r02 pass AC,
+                                // dragon / Cornell 64 spp shade ms: 3 blocks 22.54 / 44.73, 4 blocks 22.53 / 44.79, 5 blocks 22.46 / 44.18): the kernel does not care between 12 and 20 warps
 #endif
 #ifndef SHADE_PREFETCH
 #define SHADE_PREFETCH 0      // measured r01: no change (40.9 vs 40.8 ms shade at 64 spp) — the kernel does not wait on these gathers

@@ -911,6 +911,62 @@ def test_fused_reduce_resolve_over_nvlink():
     assert np.array_equal(Film.reduce_resolve_rgb8([f1, f0]), got)           # two terms: a + b == b + a, also with GPU 1 as the root
 
 
+def partial_lobe_tables():
+    """Materials whose compute_scattering arm leaves lobes OUT (material.rs:110-214: a lobe is only pushed when its colour is not black): Plastic with a
+    black diffuse colour (microfacet lobe only) and with a black specular colour (Lambert only), rough Glass with a black reflectance (transmission
+    only) and with a black transmittance (reflection only), a black Matte and a black Mirror (empty BSDFs), next to a complete Plastic and a complete
+    rough Glass.  On the GPU a material's lobes sit in fixed slots with a presence mask (shade.cuh:add_lobe / for_lobes); the reference's `bxdfs` vector
+    is dense — component selection, the pdf sums and the MIS weights must not notice the difference."""
+    tex = np.zeros(6, dtype=N.texture_dtype)
+    tex[0]["color"] = (0, 0, 0); tex[1]["color"] = (0.7, 0.4, 0.2); tex[2]["color"] = (0.9, 0.9, 0.9); tex[3]["color"] = (0.6, 0.6, 0.6); tex[4]["color"] = (1, 1, 1); tex[5]["color"] = (0.2, 0.5, 0.8)
+    mat = np.zeros(10, dtype=N.material_dtype); mat["tex"] = N.RT_NONE
+    def plastic(i, kd, ks, rough): mat[i]["type"] = N.MAT_PLASTIC; mat[i]["tex"][0] = kd; mat[i]["tex"][1] = ks; mat[i]["f"][0] = rough; mat[i]["remap_roughness"] = 1
+    def glass(i, kr, kt, ur, vr): mat[i]["type"] = N.MAT_GLASS; mat[i]["tex"][0] = kr; mat[i]["tex"][1] = kt; mat[i]["f"] = (ur, vr, 1.5); mat[i]["remap_roughness"] = 1
+    plastic(0, 0, 2, 0.2)                    # specular lobe only
+    plastic(1, 1, 0, 0.2)                    # diffuse lobe only
+    plastic(2, 5, 2, 0.05)                   # both
+    glass(3, 0, 2, 0.3, 0.2)                 # transmission lobe only
+    glass(4, 2, 0, 0.3, 0.2)                 # reflection lobe only
+    glass(5, 2, 2, 0.15, 0.4)                # both, anisotropic
+    mat[6]["type"] = N.MAT_MATTE; mat[6]["tex"][0] = 0               # black matte: empty BSDF
+    mat[7]["type"] = N.MAT_MIRROR; mat[7]["tex"][0] = 0              # black mirror: empty BSDF
+    mat[8]["type"] = N.MAT_MATTE; mat[8]["tex"][0] = 3               # floor
+    mat[9]["type"] = N.MAT_LIGHT; mat[9]["tex"][0] = 4
+    lig = np.zeros(1, dtype=N.light_dtype); lig[0]["type"] = N.LIGHT_DIFFUSE; lig[0]["prim_index"] = 1; lig[0]["color"] = (7, 7, 7); lig[0]["transform"] = N.RT_NONE; lig[0]["two_sided"] = 1
+    prims = [orc.prim(N.PRIM_XZ_RECT, [-9, -9, 9, 9, 0.0], mat=8), orc.prim(N.PRIM_XZ_RECT, [-2.5, -2.5, 2.5, 2.5, 6.0], mat=9, flip=1, light=0)]
+    for k in range(8):
+        prims.append(orc.prim(N.PRIM_SPHERE, [-3.5 + 2.0 * (k % 4), 0.8, -1.0 + 2.2 * (k // 4), 0.8], mat=k))
+    return orc.simple_tables(prims, textures=tex, materials=mat, lights=lig)
+
+
+@pytest.mark.parametrize("f32", [False, True])
+def test_partial_lobe_sets_match_oracle_per_pixel(f32):
+    from rustraytracer_b200 import Camera
+    t = partial_lobe_tables()
+    gpu = orc.upload_tables(t); gpu.commit()
+    oracle = orc.OracleScene(t)
+    cam = Camera.new((0.3, 4.5, -8.5), (0.0, 0.6, 0.3), (0.0, 1.0, 0.0), 1.0, 48.0, 0.0, 10.0)
+    w = h = 64
+    spp = 4
+    film = Film(w, h)
+    render_samples(gpu, cam, IntType.Path(10, shade_f32=f32), film, w, h, 0, spp, seed=33)
+    o, counts, _ = oracle.render(cam, w, h, 0, spp, seed=33, max_depth=10)
+    assert o[..., :3].mean() > 0.05
+    if f32:
+        film_compare(film.read(), o, "partial lobe sets f32", tol=1e-3, max_bad=0.03)
+    else:
+        film_compare(film.read(), o, "partial lobe sets")
+    c = gpu.counters()
+    for k, v in zip(("extend_rays", "shadow_rays", "probe_rays"), counts):
+        assert abs(c[k] - int(v)) <= (0.01 if f32 else 0.002) * int(v) + 16, (k, c[k], int(v))
+    if not f32:          # the branching integrators walk the lobes through the same accessors: Whitted asks for f over ALL lobes, Direct samples every light
+        for it, kind in ((IntType.Whitted(5), 3), (IntType.Direct(5, "UniformAll"), 2)):
+            film = Film(w, h)
+            render_samples(gpu, cam, it, film, w, h, 0, 2, seed=34)
+            o2, _, _ = oracle.render(cam, w, h, 0, 2, seed=34, max_depth=it.max_depth, kind=kind)
+            film_compare(film.read(), o2, f"partial lobe sets kind {kind}")
+
+
 # ---------------------------------------------------------------- Material::Disney (SURVEY §8f rank 4)
 def disney_scene_tables(thin, over):
     """Three spheres and a mesh quad carrying ONE Disney material (material 0, test_oracle_kat.disney_tables) on a matte floor under a rect light."""
