@@ -113,8 +113,8 @@ __global__ void __launch_bounds__(256) k_generate(const Ctrl* __restrict__ c, Re
         Rng rng; rng.k0 = rp.k0; rng.k1 = rp.k1; rng.pixel = pixel; rng.sample = rp.sample_begin + s; rng.dim = 0; rng.w2 = 0xffffffffu; rng.w3 = 0;
         double offx = rng_next(rng), offy = rng_next(rng);
         double fx = (double)px + offx, fy = (double)py + offy;
-        rng_next(rng);                       // time
-        rng_next(rng); rng_next(rng);        // lens sample (unused by get_ray, which draws its own)
+        rng_skip(rng, 3);                    // time, lens sample (2): drawn by get_camera_sample, read by nobody (get_ray draws its own lens point) — the
+                                             // dimensions are consumed, their Philox block is not computed
         // BasicIntegrator::single_sample (integrator.rs:196-204) divides by width - 1 / height - 1
         const bool basic = rp.kind == RT_INTEGRATOR_BASIC;
         double u = fx / (double)(basic ? rp.width - 1u : rp.width), v = fy / (double)(basic ? rp.height - 1u : rp.height);
@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(256) k_generate(const Ctrl* __restrict__ c, Re
         D3 offset = ld3(rp.cam.u) * in_disk.x + ld3(rp.cam.v) * in_disk.y;
         D3 to = ld3(rp.cam.upper_left_corner) + ld3(rp.cam.horizontal_offset) * u - ld3(rp.cam.vertical_offset) * v;
         D3 dir = to - ld3(rp.cam.origin);
-        rng_next(rng);                       // util::rand_range(t0, t1): ray time, unused by geometry
+        rng_skip(rng, 1);                    // util::rand_range(t0, t1): ray time, unused by geometry
         D3 o = ld3(rp.cam.origin) + offset, d = dir - offset;
         uint32_t k = n_cur + i;
         store_ray(ps.ray + k, o, d);

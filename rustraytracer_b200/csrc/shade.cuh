@@ -64,6 +64,9 @@ __device__ __forceinline__ double rng_next(Rng& g) {
     }
     return ((double)(a >> 5) * 67108864.0 + (double)(b >> 6)) / 9007199254740992.0;
 }
+// n dimensions whose values nobody reads: the counter moves on, the block function is not run.  Later draws are keyed by their absolute dimension, so
+// they are the same numbers either way.
+__device__ __forceinline__ void rng_skip(Rng& g, uint32_t n) { g.dim += n; g.w2 = 0xffffffffu; }
 template <class R> __device__ __forceinline__ R to_unit(double u);
 template <> __device__ __forceinline__ double to_unit<double>(double u) { return u; }
 template <> __device__ __forceinline__ float to_unit<float>(double u) { return fminf((float)u, 0.99999994f); }   // keep [0,1)
@@ -756,6 +759,10 @@ template <int MAT> __host__ __device__ constexpr uint32_t mat_km() {
                                    km(L_SPEC_T) | km(L_MICRO_R) | km(L_MICRO_T) | kmf(F_DISNEY) | kmf(F_DIELECTRIC))
          : KM_ALL;
 }
+// Materials whose BSDF holds at most ONE lobe and whose lobe ignores the 2-D sample handed to Bsdf::sample_f: Matte (Lambert / Oren-Nayar sample through
+// default_sample_f = rand_cosine_dir's own two draws, bxdf.rs:815-827; the component pick floor(u.x * 1) is 0) and Mirror (SpecularReflection, bxdf.rs:571-578).
+// The shade kernels of these materials advance the dimension counter over the two sample pairs of a vertex without running Philox for them.
+template <int MAT> __host__ __device__ constexpr bool mat_ignores_sample2d() { return MAT == RT_MAT_MATTE || MAT == RT_MAT_MIRROR; }
 template <class R, int MAT> __device__ __forceinline__ void compute_scattering_impl(const DScene& sc, const Rec& r, Bsdf<R>& b) {
     V3<R> e = cast3<R>(normalize(mk3(1., 1., 1.)));    // Bsdf::empty frame (bsdf.rs:37-47)
     b.ns = e; b.ng = e; b.ss = e; b.ts = e; b.n = 0; b.mask = 0u; b.empty = true;

@@ -191,7 +191,10 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
             auto light_estimate = [&](const uint32_t light_num) {
                 D2 u_light; u_light.x = rng_next(rng); u_light.y = rng_next(rng);
                 V2<R> u_scatter; u_scatter.x = R(0); u_scatter.y = R(0);
-                if (!whitted) { u_scatter.x = rng_real<R>(rng); u_scatter.y = rng_real<R>(rng); }
+                if (!whitted) {
+                    if constexpr (mat_ignores_sample2d<MAT>()) rng_skip(rng, 2);       // never read (shade.cuh); the values stay 0
+                    else { u_scatter.x = rng_real<R>(rng); u_scatter.y = rng_real<R>(rng); }
+                }
                 const DLight& light = sc.lights[light_num];
                 const uint32_t nsf = whitted ? (uint32_t)BSDF_ALL : (uint32_t)(BSDF_ALL - BSDF_SPECULAR);
                 // estimate_direct, light half (integrator.rs:573-597); Light::sample_li Diffuse (light.rs:176-203), Primitive::sample
@@ -316,7 +319,9 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
             }
             // continuation (integrator.rs:421-441)
             V3<R> wo = cast3<R>(-d);
-            V2<R> u; u.x = rng_real<R>(rng); u.y = rng_real<R>(rng);
+            V2<R> u; u.x = R(0); u.y = R(0);
+            if constexpr (mat_ignores_sample2d<MAT>()) rng_skip(rng, 2);
+            else { u.x = rng_real<R>(rng); u.y = rng_real<R>(rng); }
             V3<R> f, wi; R pdf; uint32_t sflags;
             bsdf_sample_f<R, KM>(bsdf, wo, u, BSDF_ALL, rng, f, wi, pdf, sflags);
             if (is_black(f) || pdf == R(0)) break;
