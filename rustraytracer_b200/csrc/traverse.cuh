@@ -159,7 +159,7 @@ __device__ __forceinline__ unsigned node4_test(const float4* __restrict__ np, co
     {                                                                                                                               \
         float t0 = fmaxf(fmaxf(__fmaf_rn(nx.c, r.idx, -r.nx), __fmaf_rn(ny.c, r.idy, -r.ny)), fmaxf(__fmaf_rn(nz.c, r.idz, -r.nz), tmin)); \
         float t1 = fminf(fminf(__fmaf_rn(fx.c, r.idx, -r.fx), __fmaf_rn(fy.c, r.idy, -r.fy)), fminf(__fmaf_rn(fz.c, r.idz, -r.fz), tmax)); \
-        t0 = t0 - fabsf(t0) * 4.8e-7f; t1 = t1 + fabsf(t1) * 4.8e-7f;                                                               \
+        t0 = __fmaf_rn(-fabsf(t0), 4.8e-7f, t0); t1 = __fmaf_rn(fabsf(t1), 4.8e-7f, t1);   /* one FFMA each: the library is built with -fmad=false */ \
         const bool h = t0 <= t1;                                                                                                    \
         key[k] = h ? ((__float_as_int(t0) & ~3) | k) : (0x7f800000 | k);                                                            \
         mask |= h ? (1u << k) : 0u;                                                                                                 \
@@ -168,7 +168,14 @@ __device__ __forceinline__ unsigned node4_test(const float4* __restrict__ np, co
 #undef RT_CHILD
     return mask;
 }
-__device__ __forceinline__ int32_t child_of(const int4& ch, int32_t key) { int k = key & 3; return k == 0 ? ch.x : (k == 1 ? ch.y : (k == 2 ? ch.z : ch.w)); }
+// child word of the slot number packed in a key's two low bits — as bit masks, not as `k == 0 ? ... : ...`: nvcc turned the nested conditional into
+// three divergent branches with a reconvergence barrier (13 instructions, the lanes of a warp hold different slot numbers and walked all four arms one
+// after the other), four times per node step (r02 SASS: 52 of the step's ~190 instructions, 14 of them branches).  Seven instructions, no branch.
+__device__ __forceinline__ int32_t child_of(const int4& ch, int32_t key) {
+    const int32_t m0 = (key << 31) >> 31, m1 = (key << 30) >> 31;        // all ones where bit 0 / bit 1 of the slot number is set
+    const int32_t lo = (ch.x & ~m0) | (ch.y & m0), hi = (ch.z & ~m0) | (ch.w & m0);
+    return (lo & ~m1) | (hi & m1);
+}
 __device__ __forceinline__ void sort4(int32_t k[4]) {
 #define RT_CSWAP(a, b) { int32_t lo = min(k[a], k[b]), hi = max(k[a], k[b]); k[a] = lo; k[b] = hi; }
     RT_CSWAP(0, 1) RT_CSWAP(2, 3) RT_CSWAP(0, 2) RT_CSWAP(1, 3) RT_CSWAP(1, 2)
@@ -181,9 +188,11 @@ __device__ __forceinline__ int32_t node4_closest(const DScene& sc, int32_t cur, 
     const int nh = __popc(mask);
     if (nh == 0) return stack[--sp];
     sort4(key);
-    if (nh > 3 && sp < STACK) stack[sp++] = child_of(ch, key[3]);
-    if (nh > 2 && sp < STACK) stack[sp++] = child_of(ch, key[2]);
-    if (nh > 1 && sp < STACK) stack[sp++] = child_of(ch, key[1]);
+    // three stores without a branch: a push that does not happen (fewer hit children; a full stack, which the commit-time bound rules out) goes to
+    // the spare entry behind the stack instead of around a divergent `if` (r02 SASS: each conditional push was a branch + reconvergence barrier)
+    const bool v3 = nh > 3 && sp < STACK; stack[v3 ? sp : STACK] = child_of(ch, key[3]); sp += v3;
+    const bool v2 = nh > 2 && sp < STACK; stack[v2 ? sp : STACK] = child_of(ch, key[2]); sp += v2;
+    const bool v1 = nh > 1 && sp < STACK; stack[v1 ? sp : STACK] = child_of(ch, key[1]); sp += v1;
     return child_of(ch, key[0]);
 }
 // any-hit descent: order does not matter
@@ -351,7 +360,7 @@ __device__ __forceinline__ Hit trace_closest(const DScene& sc, D3 o, D3 d, doubl
     float ftmin = f32_down(tmin); ftmin = ftmin - fabsf(ftmin) * 4.8e-7f;
     float ftmax = f32_up(fmin(tmax, 3.0e38));
     { bool occ = false; direct_shapes(sc, rx0, rf, tmin, tmax, false, 0., 0u, best.t, best.prim, occ, ftmax, ftmin); }
-    int32_t stack[STACK]; int sp = 0;
+    int32_t stack[STACK + 1]; int sp = 0;          // [STACK]: the write-only slot of node4_closest's suppressed pushes
     stack[sp++] = SENTINEL;
     int32_t cur = sc.n_nodes ? 0 : SENTINEL;
 #if RT_BVH_WIDTH != 4
@@ -410,7 +419,7 @@ __device__ __forceinline__ bool trace_any(const DScene& sc, D3 o, D3 d, double t
     float ftmin = f32_down(tmin); ftmin = ftmin - fabsf(ftmin) * 4.8e-7f;
     float ftmax = f32_up(fmin(fmin(tmax, t_limit), 3.0e38));
     { bool occ = false; double bt = 0.; uint32_t bp = RT_NONE; direct_shapes(sc, rx0, rf, tmin, tmax, true, t_limit, skip, bt, bp, occ, ftmax, ftmin); if (occ) return true; }
-    int32_t stack[STACK]; int sp = 0;
+    int32_t stack[STACK + 1]; int sp = 0;          // [STACK]: the write-only slot of node4_closest's suppressed pushes
     stack[sp++] = SENTINEL;
     int32_t cur = sc.n_nodes ? 0 : SENTINEL;
 #if RT_BVH_WIDTH != 4
@@ -575,7 +584,7 @@ template <class Job>
 __device__ __forceinline__ void trace_jobs(const DScene& sc, Job& job, uint32_t n, uint32_t* counter) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
-    int32_t stack[STACK];
+    int32_t stack[STACK + 1];                      // [STACK]: the write-only slot of node4_closest's suppressed pushes
     TState st; st.cur = SENTINEL; st.sp = 0;
     constexpr bool PARK = Job::shared_leaf_ray;
     __shared__ double sh_leaf[PARK ? 5 : 1][PARK ? TRACE_BLOCK : 1];
