@@ -181,6 +181,9 @@ __device__ __forceinline__ void sort4(int32_t k[4]) {
     RT_CSWAP(0, 1) RT_CSWAP(2, 3) RT_CSWAP(0, 2) RT_CSWAP(1, 3) RT_CSWAP(1, 2)
 #undef RT_CSWAP
 }
+#ifndef RT_PREFETCH_PUSHED
+#define RT_PREFETCH_PUSHED 0      // measured r02 (pass AG): extend 29.5 -> 30.2 ms, soup casts -3...4 %: the extra L1 fills cost more than the early fetch saves
+#endif
 // closest-hit descent: nearest hit child next, the others pushed far to near
 __device__ __forceinline__ int32_t node4_closest(const DScene& sc, int32_t cur, const RayF& rf, float ftmin, float ftmax, int32_t* stack, int& sp) {
     int32_t key[4]; int4 ch;
@@ -192,7 +195,15 @@ __device__ __forceinline__ int32_t node4_closest(const DScene& sc, int32_t cur, 
     // the spare entry behind the stack instead of around a divergent `if` (r02 SASS: each conditional push was a branch + reconvergence barrier)
     const bool v3 = nh > 3 && sp < STACK; stack[v3 ? sp : STACK] = child_of(ch, key[3]); sp += v3;
     const bool v2 = nh > 2 && sp < STACK; stack[v2 ? sp : STACK] = child_of(ch, key[2]); sp += v2;
-    const bool v1 = nh > 1 && sp < STACK; stack[v1 ? sp : STACK] = child_of(ch, key[1]); sp += v1;
+    const int32_t c1 = child_of(ch, key[1]);
+    const bool v1 = nh > 1 && sp < STACK; stack[v1 ? sp : STACK] = c1; sp += v1;
+#if RT_PREFETCH_PUSHED
+    // the entry now on top of the stack is the next one popped unless the near child's subtree ends the ray: start its fetch now
+    if (v1) {
+        const char* a = c1 >= 0 ? reinterpret_cast<const char*>(sc.nodes) + 128 * (size_t)c1 : reinterpret_cast<const char*>(sc.slots) + sizeof(DSlot) * (size_t)((uint32_t)~c1 >> 2);
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(a));
+    }
+#endif
     return child_of(ch, key[0]);
 }
 // any-hit descent: order does not matter
