@@ -304,6 +304,9 @@ static __device__ __noinline__ bool prim_record_t(const DScene& sc, uint32_t pri
 // Primitive::pdf's re-intersection of ONE (light) primitive (primitive.rs:462-473 → intersects_obj, no leaf box, no
 // FlipFace toggle): only the hit point and the geometric normal UP TO SIGN are consumed there
 // (`dist.magnitude_squared() / (area * |n · -dir|)`), so the triangle arm skips the shading frame.
+// F32N (RT_SHADE_F32 kernels, where the pdf this feeds is an f32 MIS weight): the normal is normalised in f32 — the f64 record of a parametric light cost
+// two f64 normalisations (a square root and three divisions each, ~280 instructions) per shaded vertex for a value consumed as a float.
+template <bool F32N = false>
 static __device__ __noinline__ bool prim_hit_pn(const DScene& sc, uint32_t prim, D3 o, D3 d, double tmin, double tmax, D3& p, D3& n) {
     DPrim pr = sc.prims[prim];
     if ((pr.info & 7u) == RT_PRIM_TRIANGLE) {
@@ -322,11 +325,17 @@ static __device__ __noinline__ bool prim_hit_pn(const DScene& sc, uint32_t prim,
             if (fabs(determinant) < SMALL / 10000. && norm2(cross(p2 - p0, p1 - p0)) == 0.) return false;
         }
         p = b0 * p0 + b1 * p1 + b2 * p2;
-        n = normalize(cross(p0 - p2, p1 - p2));
+        if constexpr (F32N) {
+            const D3 e1 = p0 - p2, e2 = p1 - p2;
+            const float ax = (float)e1.x, ay = (float)e1.y, az = (float)e1.z, bx = (float)e2.x, by = (float)e2.y, bz = (float)e2.z;
+            float nx = __fmaf_rn(ay, bz, -(az * by)), ny = __fmaf_rn(az, bx, -(ax * bz)), nz = __fmaf_rn(ax, by, -(ay * bx));
+            const float s = rsqrtf(__fmaf_rn(nz, nz, __fmaf_rn(ny, ny, nx * nx)));
+            n = mk3((double)(nx * s), (double)(ny * s), (double)(nz * s));
+        } else n = normalize(cross(p0 - p2, p1 - p2));
         return true;
     }
     Rec r;
-    if (!prim_record_t<0>(sc, prim, o, d, tmin, tmax, false, r)) return false;
+    if (!prim_record_t<0, F32N>(sc, prim, o, d, tmin, tmax, false, r)) return false;
     p = r.p; n = r.n;
     return true;
 }
