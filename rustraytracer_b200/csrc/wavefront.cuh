@@ -265,7 +265,10 @@ __global__ void __launch_bounds__(128, (sizeof(R) == 4 ? SHADE_MIN_BLOCKS : 2)) 
                             // Infinite: Light::pdf_li (light.rs:285-294)
                             D3 lp, ln; double light_pdf = 0.;
                             if (inf_light) light_pdf = infinite_pdf_li(sc, light, wid);
-                            else if (prim_hit_pn<sizeof(R) == 4>(sc, light.prim, rec.p, wid, 0., INF, lp, ln)) light_pdf = norm2(rec.p - lp) / (light.area * fabs(dot(ln, -wid)));
+                            else if (prim_hit_pn<sizeof(R) == 4>(sc, light.prim, rec.p, wid, 0., INF, lp, ln)) {
+                                if constexpr (sizeof(R) == 4) light_pdf = (double)((float)norm2(rec.p - lp) / ((float)light.area * fabsf((float)dot(ln, -wid))));   // an f32 MIS weight: f32 quotient
+                                else light_pdf = norm2(rec.p - lp) / (light.area * fabs(dot(ln, -wid)));
+                            }
                             if (light_pdf == 0.) go = false;
                             else weight = power_heuristic<R>(scattering_pdf, (R)light_pdf);
                         }

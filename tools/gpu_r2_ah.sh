@@ -1,5 +1,5 @@
 #!/bin/bash
-# round 2, GPU pass AH: f32 kernels take the light-pdf re-intersection's normal in f32 (no f64 normalisations for an f32 MIS weight): A/B, f32 film distance, suite, bench
+# round 2, GPU pass AH/AJ: f32-mode light pdf A/B (normal, then quotient, in f32), f32 film distance, suite, bench
 set -x
 for lib in librtcore_base.so librtcore.so; do
   for sc in "plastic_dragon 0 1024 64 8 1" "cornell_box_statue 0 1024 64 8 1"; do

@@ -15,7 +15,7 @@ import subprocess
 import sys
 import tempfile
 
-rep, which, obj = sys.argv[1], int(sys.argv[2]), sys.argv[3]
+rep, which, obj = sys.argv[1], sys.argv[2], sys.argv[3]          # `which`: launch index, or a substring of the kernel name (first match)
 topn = int(sys.argv[4]) if len(sys.argv) > 4 else 30
 raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "sass"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
@@ -24,7 +24,7 @@ for r in rows:
     if r and r[0] == "Kernel Name": cur = {"name": r[1], "hdr": None, "data": []}; sections.append(cur)
     elif cur is not None and cur["hdr"] is None: cur["hdr"] = r
     elif cur is not None and len(r) == len(cur["hdr"]): cur["data"].append(r)
-s = sections[which]; hdr, data = s["hdr"], s["data"]
+s = sections[int(which)] if which.isdigit() else [x for x in sections if which in x["name"]][0]; hdr, data = s["hdr"], s["data"]
 iS, iI, iT = hdr.index("# Samples"), hdr.index("Instructions Executed"), hdr.index("Thread Instructions Executed")
 name = s["name"]
 print(name[:120])
