@@ -182,9 +182,10 @@ struct Rec {
     double t; D3 p, n, sn, sdpdu; D2 uv; D3 wo; uint32_t prim, mat; bool front;
 };
 // HitRecord::new + set_front (hittable.rs:75-117,186-189) for parametric shapes
-__device__ __forceinline__ void rec_from_partials(Rec& r, D3 p, D2 uv, D3 dpdu, D3 dpdv, double t, D3 ray_d) {
+// PN: only the point and the normal are wanted (prim_hit_pn): the shading tangent is left unnormalised
+template <bool PN = false> __device__ __forceinline__ void rec_from_partials(Rec& r, D3 p, D2 uv, D3 dpdu, D3 dpdv, double t, D3 ray_d) {
     D3 n = normalize(cross(dpdu, dpdv));
-    r.sn = n; r.sdpdu = normalize(dpdu);
+    r.sn = n; r.sdpdu = PN ? dpdu : normalize(dpdu);
     r.p = p; r.uv = uv; r.t = t; r.wo = -ray_d;
     r.front = dot(ray_d, n) < 0.0;
     r.n = r.front ? n : -n;
@@ -208,7 +209,8 @@ __device__ __forceinline__ void rec_from_partials_f32(Rec& r, D3 p, D2 uv, D3 dp
 // (primitive.rs:372-425) plus the FlipFace toggle being skipped by the caller.
 // CLS: 1 = the primitive is known to be a triangle, 0 = known parametric shape, 2 = decide at run time
 // F32FRAME (RT_SHADE_F32 mode, parametric shapes): normal / dpdu normalisation in f32, everything else unchanged
-template <int CLS, bool F32FRAME = false>
+// PN (prim_hit_pn): the caller reads p and n only — uv (two f64 divisions for a rect) and the normalised tangent are not computed
+template <int CLS, bool F32FRAME = false, bool PN = false>
 static __device__ __noinline__ bool prim_record_t(const DScene& sc, uint32_t prim, D3 o, D3 d, double tmin, double tmax, bool leaf_box, Rec& r) {
     DPrim pr = sc.prims[prim];
     uint32_t type = CLS == 1 ? (uint32_t)RT_PRIM_TRIANGLE : (pr.info & 7u);
@@ -282,19 +284,20 @@ static __device__ __noinline__ bool prim_record_t(const DScene& sc, uint32_t pri
             double cos_phi = p.x * inv_z_r, sin_phi = p.y * inv_z_r;
             D3 dpdu = mk3(-phi_max * p.y, phi_max * p.x, 0.);
             D3 dpdv = (theta_max - theta_min) * mk3(p.z * cos_phi, p.z * sin_phi, -rad * sin(theta));
-            if (F32FRAME) rec_from_partials_f32(r, p, mk2(u, v), dpdu, dpdv, t, d); else rec_from_partials(r, p, mk2(u, v), dpdu, dpdv, t, d);
+            if (F32FRAME) rec_from_partials_f32(r, p, mk2(u, v), dpdu, dpdv, t, d); else rec_from_partials<PN>(r, p, mk2(u, v), dpdu, dpdv, t, d);
             r.p = r.p + center;
         } else {
             RectHit h;
             if (!rect_test(type, sh, sc.xforms, o, d, tmin, tmax, h)) return false;
             int kaxis = type == RT_PRIM_XY_RECT ? 2 : (type == RT_PRIM_XZ_RECT ? 1 : 0);
             int aa = kaxis == 0 ? 1 : 0, ba = kaxis == 2 ? 1 : 2;
-            D2 uv = mk2((h.a - sh[0]) / (sh[2] - sh[0]), (h.b - sh[1]) / (sh[3] - sh[1]));
+            D2 uv = mk2(0., 0.);
+            if (!PN) uv = mk2((h.a - sh[0]) / (sh[2] - sh[0]), (h.b - sh[1]) / (sh[3] - sh[1]));
             D3 p = h.to + h.td * h.t;
             D3 dpdu = mk3(aa == 0 ? 1. : 0., aa == 1 ? 1. : 0., 0.);
             D3 dpdv = mk3(0., ba == 1 ? 1. : 0., ba == 2 ? 1. : 0.);
             if (sh[5] >= 0.) { const DXform& x = sc.xforms[(uint32_t)sh[5]]; p = xf_point(x.fwd, p); dpdu = xf_vector(x.fwd, dpdu); dpdv = xf_vector(x.fwd, dpdv); }
-            if (F32FRAME) rec_from_partials_f32(r, p, uv, dpdu, dpdv, h.t, d); else rec_from_partials(r, p, uv, dpdu, dpdv, h.t, d);
+            if (F32FRAME) rec_from_partials_f32(r, p, uv, dpdu, dpdv, h.t, d); else rec_from_partials<PN>(r, p, uv, dpdu, dpdv, h.t, d);
         }
     }
     if (leaf_box && (pr.info & PI_FLIP)) r.front = !r.front;                     // FlipFace (primitive.rs:300-310)
@@ -335,7 +338,7 @@ static __device__ __noinline__ bool prim_hit_pn(const DScene& sc, uint32_t prim,
         return true;
     }
     Rec r;
-    if (!prim_record_t<0, F32N>(sc, prim, o, d, tmin, tmax, false, r)) return false;
+    if (!prim_record_t<0, F32N, true>(sc, prim, o, d, tmin, tmax, false, r)) return false;
     p = r.p; n = r.n;
     return true;
 }
