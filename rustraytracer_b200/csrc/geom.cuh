@@ -27,7 +27,25 @@ __device__ __forceinline__ double dot(D3 a, D3 b) { return a.x * b.x + a.y * b.y
 __device__ __forceinline__ D3 cross(D3 a, D3 b) { return mk3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
 __device__ __forceinline__ double norm2(D3 a) { return dot(a, a); }
 __device__ __forceinline__ double norm(D3 a) { return sqrt(norm2(a)); }
-__device__ __forceinline__ D3 normalize(D3 a) { double n = norm(a); return mk3(a.x / n, a.y / n, a.z / n); }
+// a / n, bit for bit, for the components of a vector divided by its own norm.  A ZERO numerator takes the slow path of the f64 division (the inline
+// fast path only covers numerators of ordinary magnitude; the rest is an out-of-line routine of ~60 instructions the whole warp waits for), and the
+// vectors normalised here are mostly axis-aligned — rect normals and tangents, frames built from them: two zero components in three.  ncu r02: that
+// routine ran 11 times per shaded vertex and was 19 % of the f64 matte kernel's executed instructions.  +-0 / n = +-0 for any n > 0 (n = 0 or NaN
+// still goes through the division and gives the reference's NaN).  The division itself is the same IEEE operation, kept behind an opaque asm so that
+// the compiler does not turn the test back into an unconditional quotient plus a select.
+// Only in the f64 shade kernels' translation unit (f64 shade -2.3 % dragon / -6.3 % Cornell, all-f64 bench 2,337 -> 2,440 Mrays/s): the f32 kernels
+// normalise few f64 vectors, and there the opaque division cost more than the slow path it avoids (shade +2.5 %), so shade_f32.cu keeps the plain quotient.
+__device__ __forceinline__ double div_by_norm(double a, double n) {
+#ifndef RT_PLAIN_NORMALIZE
+    if (a == 0. && n > 0.) return a;
+    double q;
+    asm volatile("div.rn.f64 %0, %1, %2;" : "=d"(q) : "d"(a), "d"(n));
+    return q;
+#else
+    return a / n;
+#endif
+}
+__device__ __forceinline__ D3 normalize(D3 a) { double n = norm(a); return mk3(div_by_norm(a.x, n), div_by_norm(a.y, n), div_by_norm(a.z, n)); }
 __device__ __forceinline__ double comp(D3 a, int i) { return i == 0 ? a.x : (i == 1 ? a.y : a.z); }
 __device__ __forceinline__ double clampd(double x, double lo, double hi) { return fmin(fmax(x, lo), hi); }
 __device__ __forceinline__ D3 face_forward(D3 n, D3 v) { return dot(n, v) < 0. ? -n : n; }          // util.rs:578-581

@@ -95,7 +95,11 @@ template <> __device__ __forceinline__ V3<float> cross<float>(V3<float> a, V3<fl
     return v3<float>(__fmaf_rn(a.y, b.z, -(a.z * b.y)), __fmaf_rn(a.z, b.x, -(a.x * b.z)), __fmaf_rn(a.x, b.y, -(a.y * b.x)));
 }
 template <class R> __device__ __forceinline__ R norm(V3<R> a) { return sqrt(dot(a, a)); }
-template <class R> __device__ __forceinline__ V3<R> normalize(V3<R> a) { R n = norm(a); return v3<R>(a.x / n, a.y / n, a.z / n); }
+template <class R> __device__ __forceinline__ V3<R> normalize(V3<R> a) {
+    R n = norm(a);
+    if constexpr (sizeof(R) == 8) return v3<R>(div_by_norm(a.x, n), div_by_norm(a.y, n), div_by_norm(a.z, n));      // geom.cuh: zero numerators skip the f64 slow path
+    else return v3<R>(a.x / n, a.y / n, a.z / n);
+}
 template <class R> __device__ __forceinline__ R clampr(R x, R lo, R hi) { return fmin(fmax(x, lo), hi); }
 template <class R> __device__ __forceinline__ V3<R> face_forward(V3<R> n, V3<R> v) { return dot(n, v) < R(0) ? -n : n; }
 template <class R> __device__ __forceinline__ bool finite3(V3<R> a) { return isfinite(a.x) && isfinite(a.y) && isfinite(a.z); }

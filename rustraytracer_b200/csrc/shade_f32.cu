@@ -3,6 +3,7 @@
 // radiometric lobes, BSDF frame and MIS weights of RT_SHADE_F32 mode, whose contract is an image within the stated relative
 // MSE — and leave every f64 expression (hit points, normals, light sample points, ray origins and directions) rounding like
 // the reference.  ncu r01: IEEE f32 sqrt alone was 8.7 % of this kernel's executed instructions, f32 division more.
+#define RT_PLAIN_NORMALIZE 1        // geom.cuh:div_by_norm — the zero-numerator shortcut pays in the f64 kernels only
 #include "wavefront.cuh"
 
 namespace rt {

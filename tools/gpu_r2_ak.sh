@@ -1,5 +1,5 @@
 #!/bin/bash
-# round 2, GPU pass AK: lean (point + normal) record for the light-pdf re-intersection: f64 and f32 A/B, f64 films must be unchanged, suite, bench
+# round 2, GPU pass AK/AN: A/B against the previous build (f64 and f32), f64 films must be unchanged, suite, bench
 set -x
 for lib in librtcore_base.so librtcore.so; do
   for sc in "plastic_dragon 0 1024 64 8 1" "plastic_dragon 0 1024 16 8 0" "cornell_box_statue 0 1024 16 8 0"; do
