@@ -38,6 +38,7 @@ template <class T> struct NoInitAlloc : std::allocator<T> {
     NoInitAlloc() = default;
     template <class U> NoInitAlloc(const NoInitAlloc<U>&) {}
     T* allocate(size_t n) {
+        if (n > SIZE_MAX / sizeof(T)) throw std::bad_alloc();
         const size_t bytes = n * sizeof(T);
         if (bytes >= ((size_t)4 << 20)) {
             void* p = nullptr;
